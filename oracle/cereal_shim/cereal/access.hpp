@@ -1,0 +1,3 @@
+// Part of the oracle-only cereal stand-in; see cereal/cereal.hpp.
+#pragma once
+#include <cereal/cereal.hpp>
