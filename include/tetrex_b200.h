@@ -1,0 +1,219 @@
+/* tetrex_b200.h — C ABI of libtetrex_cuda.so: the B200 (sm_100a) implementation of TetRex's
+ * index-probe + verify hot path.
+ *
+ * The reference (remyschwab/TetRex @ 6e856c0) has no FFI; its boundary for this path is the C++
+ * API in its include/ headers.  Every entry point below names the reference function whose inner loop it
+ * replaces.  The host C++ layer (tetrex_b200/host/) implements the reference's own types
+ * (TetrexIndex, process_query, iter_disk_search, drive_index, drive_query) on top of these calls;
+ * Python (the tetrex_b200 package, ctypes) binds the same symbols for tests and bench.py.
+ *
+ * Conventions
+ *   - every call returns int: 0 = TRX_OK, negative = TRX_E*; text via trx_last_error() (thread local)
+ *   - opaque handles, created/destroyed in pairs; a handle belongs to one context = one CUDA
+ *     device + one stream; one context per host thread (mirrors hibf's "one agent per thread")
+ *   - plain entry points take HOST buffers, copy in/out and return after the result is in the
+ *     caller's buffer; *_dev entry points take DEVICE pointers, only enqueue work on the context's
+ *     stream and return immediately (trx_ctx_sync waits)
+ *   - there is no CPU fallback anywhere: without a usable sm_100 device trx_ctx_create fails
+ *   - bit matrix layout = seqan::hibf::interleaved_bloom_filter's (lib/hibf/include/hibf/
+ *     interleaved_bloom_filter.hpp:463-477): bit (row r, bin b) is bit b%64 (LSB first) of
+ *     uint64 word r*bin_words + b/64
+ */
+#ifndef TETREX_B200_H
+#define TETREX_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TRX_ABI_VERSION 1
+
+enum {
+    TRX_OK = 0,
+    TRX_EINVAL = -1,     /* bad argument (std::logic_error / std::invalid_argument in the reference) */
+    TRX_ECUDA = -2,      /* CUDA runtime error, text in trx_last_error() */
+    TRX_ENODEV = -3,     /* no sm_100 device: the product never falls back to the CPU */
+    TRX_ENOMEM = -4,
+    TRX_ECAPACITY = -5,  /* caller-provided output buffer too small; required size is reported */
+    TRX_EREGEX = -6,     /* pattern not supported / malformed / matches the empty string */
+    TRX_ERANGE = -7      /* index out of range (bin id >= bins, slot >= capacity, ...) */
+};
+
+enum { TRX_MOL_NA = 0, TRX_MOL_AA = 1 };                      /* TetrexIndex::molecule_ "na" / "aa" */
+enum { TRX_RED_BASE = 0, TRX_RED_MURPHY = 1, TRX_RED_LI = 2 }; /* TetrexIndex::reduction_ */
+
+typedef struct trx_ctx trx_ctx_t;
+typedef struct trx_ibf trx_ibf_t;
+typedef struct trx_hibf trx_hibf_t;
+typedef struct trx_paths trx_paths_t;
+typedef struct trx_text trx_text_t;
+typedef struct trx_regex trx_regex_t;
+
+/* ------------------------------------------------------------------------------------------ context */
+const char *trx_last_error(void);
+int trx_abi_version(void);
+/* device: CUDA ordinal.  stream: a cudaStream_t owned by the caller (e.g. torch's current stream) or
+ * NULL to let the context create its own non-blocking stream. */
+int trx_ctx_create(int device, void *stream, trx_ctx_t **out);
+void trx_ctx_destroy(trx_ctx_t *ctx);
+int trx_ctx_sync(trx_ctx_t *ctx);
+void *trx_ctx_stream(trx_ctx_t *ctx);
+/* number of kernels this context has launched since creation (bench.py's gpu_launches) */
+uint64_t trx_ctx_launches(trx_ctx_t *ctx);
+/* raw device memory for callers that have no CUDA runtime of their own (the C++ host layer) */
+int trx_dev_alloc(trx_ctx_t *ctx, uint64_t bytes, void **out);
+int trx_dev_free(trx_ctx_t *ctx, void *ptr);
+int trx_dev_memset(trx_ctx_t *ctx, void *dst, int value, uint64_t bytes);
+int trx_copy_h2d(trx_ctx_t *ctx, void *dst_dev, const void *src_host, uint64_t bytes); /* synchronous */
+int trx_copy_d2h(trx_ctx_t *ctx, void *dst_host, const void *src_dev, uint64_t bytes); /* synchronous */
+/* CUDA-event timing on the context's stream (so callers without torch can time kernels) */
+int trx_timer_start(trx_ctx_t *ctx);
+int trx_timer_stop_ms(trx_ctx_t *ctx, float *ms); /* records, synchronises, returns elapsed ms */
+
+/* ------------------------------------------------------------------- a1/a2: k-mer decomposition */
+/* Host-side helpers (no device work), so the caller can size buffers like IBFIndex::find_largest_bin
+ * (include/index_ibf.h:81-86) without hashing: emits per record = L+1 (DNA, the wrap-around quirk of
+ * nucleotide_decomposer.h:104-111) or L-k+1 (peptide, peptide_decomposer.h:280-291); 0 if L < k. */
+uint64_t trx_emit_count(int molecule, uint32_t k, uint64_t record_len);
+/* PeptideDecomposer::create_residue_maps / create_r2r_maps (peptide_decomposer.h:59-213) */
+void trx_peptide_maps(int reduction, uint8_t aamap[256], uint8_t redmap[256]);
+/* IBFIndex::compute_bitcount (include/index_ibf.h:133-139): float log, double arithmetic, ceil */
+uint64_t trx_compute_bitcount(uint64_t max_bin_emits, float fpr);
+
+/* Emits the packed k-mers of n_records records exactly as {Nucleotide,Peptide}Decomposer::
+ * decompose_record would hand them to TetrexIndex::emplace, in order.  residues: concatenated
+ * record bytes; rec_offsets: n_records+1 byte offsets; out_offsets: n_records+1 emit offsets
+ * (exclusive prefix sum of trx_emit_count); out_values: out_offsets[n_records] values. */
+int trx_decompose_records(trx_ctx_t *ctx, int molecule, uint32_t k, int reduction, const uint8_t *residues,
+                          const uint64_t *rec_offsets, uint64_t n_records, uint64_t *out_values,
+                          uint64_t out_capacity, uint64_t *out_offsets);
+
+/* ----------------------------------------------------------------------- a3/a4/a5: flat IBF */
+/* seqan::hibf::interleaved_bloom_filter ctor (lib/hibf/src/interleaved_bloom_filter.cpp:32-53).
+ * The matrix lives in HBM, zeroed.  shard_index/shard_count partition the bin_words columns of
+ * every row in contiguous 64-bin blocks: this handle then owns words
+ * [shard_index*bin_words/shard_count, (shard_index+1)*bin_words/shard_count) of each row
+ * (shard_count must divide bin_words; 0/1 = whole matrix).  Row indices are shard independent. */
+int trx_ibf_create(trx_ctx_t *ctx, uint64_t bins, uint64_t bin_size, uint32_t hash_funs, uint32_t shard_index,
+                   uint32_t shard_count, trx_ibf_t **out);
+void trx_ibf_destroy(trx_ibf_t *ibf);
+/* out[0..10) = bins, technical_bins, bin_size, hash_shift, bin_words, hash_funs, n_words (whole
+ * matrix), shard_word_begin, shard_words (per row), shard_n_words */
+int trx_ibf_geometry(const trx_ibf_t *ibf, uint64_t out[10]);
+void *trx_ibf_device_words(trx_ibf_t *ibf);
+int trx_ibf_clear(trx_ibf_t *ibf);
+/* words = the whole matrix in file layout (n_words); a shard keeps only its columns. */
+int trx_ibf_upload(trx_ibf_t *ibf, const uint64_t *words, uint64_t n_words);
+/* inverse; a shard writes only its columns into `words` (caller zero-fills / merges shards). */
+int trx_ibf_download(trx_ibf_t *ibf, uint64_t *words, uint64_t n_words);
+
+/* K1a — interleaved_bloom_filter::emplace (…cpp:119-140) for n (value, bin) pairs.  A shard ignores
+ * pairs whose bin it does not own. */
+int trx_emplace_values(trx_ibf_t *ibf, const uint64_t *values, const uint32_t *bins, uint64_t n);
+int trx_emplace_values_dev(trx_ibf_t *ibf, const uint64_t *d_values, const uint32_t *d_bins, uint64_t n);
+/* K1b — IBFIndex::populate_index's inner loops fused (include/index_ibf.h:101-131: decompose_record
+ * → emplace → hash_and_fit → set bit) straight from residues; nothing is buffered per k-mer.
+ * rec_bin[i] = user bin of record i.  Records shorter than k are skipped like the reference does. */
+int trx_emplace_records(trx_ibf_t *ibf, int molecule, uint32_t k, int reduction, const uint8_t *residues,
+                        const uint64_t *rec_offsets, const uint32_t *rec_bin, uint64_t n_records);
+int trx_emplace_records_dev(trx_ibf_t *ibf, int molecule, uint32_t k, int reduction, const uint8_t *d_residues,
+                            uint64_t n_residues, const uint64_t *d_rec_offsets, const uint32_t *d_rec_bin,
+                            uint64_t n_records);
+
+/* K2 — containment_agent_type::bulk_contains (…cpp:203-290) / IBFIndex::query (index_ibf.h:146-150)
+ * for a batch: out_words[i*shard_words + w] = AND_h row_h(kmers[i])[w]. */
+int trx_bulk_contains(trx_ibf_t *ibf, const uint64_t *kmers, uint64_t n, uint64_t *out_words);
+int trx_bulk_contains_dev(trx_ibf_t *ibf, const uint64_t *d_kmers, uint64_t n, uint64_t *d_out_words);
+
+/* ------------------------------------------------------ a6: collector path algebra in HBM */
+/* A pool of `capacity` path bitvectors ("slots") of words_per_slot uint64 each — the path_ member
+ * of every live CollectorsItem (include/otf_collector.h:19-37) — resident in HBM. */
+int trx_paths_create(trx_ctx_t *ctx, uint64_t words_per_slot, uint64_t capacity, trx_paths_t **out);
+void trx_paths_destroy(trx_paths_t *p);
+void *trx_paths_device_words(trx_paths_t *p);
+/* slots [first, first+n): bits [0,bins) set, padding clear = bitvector(bins, true)
+ * (otf_collector.h:344); bins == 0 → all clear = bitvector(bins) (path_matrix, :343). */
+int trx_paths_fill(trx_paths_t *p, uint64_t first, uint64_t n, uint64_t bins);
+/* update_path's probe + `path_ &= hits` + `path_.none()` (otf_collector.h:247-279,383) for n items
+ * in one launch: slot[slots[i]] &= bulk_contains(kmers[i]); alive[i] = any bit left.  Each slot may
+ * appear once per call.  Host arrays in, alive (n bytes) out. */
+int trx_paths_step(trx_ibf_t *ibf, trx_paths_t *p, const uint64_t *kmers, const uint32_t *slots, uint64_t n,
+                   uint8_t *alive);
+/* same, against precomputed hit vectors resident on the device (HIBF route: trx_hibf_membership_dev
+ * wrote d_hits[hit_index[i]*words_per_slot ...]) */
+int trx_paths_and_hits(trx_paths_t *p, const uint64_t *d_hits, const uint32_t *hit_index, const uint32_t *slots,
+                       uint64_t n, uint8_t *alive);
+/* push/absorb/split_procedure and `path_matrix |= top.path_` (otf_collector.h:190-208,283-288,363):
+ * slot[dst[i]] |= slot[src[i]] for n pairs, any multiplicity of dst (atomic OR). */
+int trx_paths_or(trx_paths_t *p, const uint32_t *dst, const uint32_t *src, uint64_t n);
+int trx_paths_read(trx_paths_t *p, uint64_t first, uint64_t n, uint64_t *out_words);
+
+/* -------------------------------------------------------------------------- a8: HIBF probe */
+/* Flattened seqan::hibf::hierarchical_interleaved_bloom_filter (…/hierarchical_interleaved_bloom_
+ * filter.hpp:209-238).  Per IBF i: geometry, matrix words, and per technical bin next_ibf_id and
+ * ibf_bin_to_user_bin_id (UINT64_MAX = merged, UINT64_MAX-1 = deleted). */
+typedef struct trx_hibf_desc {
+    uint64_t n_ibfs;
+    uint64_t n_user_bins;
+    const uint64_t *bins;            /* [n_ibfs] ibf.bin_count() */
+    const uint64_t *bin_size;        /* [n_ibfs] */
+    const uint64_t *hash_funs;       /* [n_ibfs] */
+    const uint64_t *const *words;    /* [n_ibfs] → technical_bins*bin_size/64 words each */
+    const uint64_t *const *next_ibf; /* [n_ibfs] → table_len[i] entries */
+    const uint64_t *const *user_bin; /* [n_ibfs] → table_len[i] entries */
+    const uint64_t *table_len;       /* [n_ibfs] */
+} trx_hibf_desc;
+int trx_hibf_upload(trx_ctx_t *ctx, const trx_hibf_desc *desc, trx_hibf_t **out);
+void trx_hibf_destroy(trx_hibf_t *h);
+/* K3 — HIBFIndex::query = membership_for({kmer}, 1) → populate_bitvector (include/index_hibf.h:
+ * 132-147; …hpp:321-355) as a level-synchronous frontier.  out_words: n × ceil(n_user_bins/64).
+ * stats (nullable, host): [0] = IBFs visited in total, [1] = levels run. */
+int trx_hibf_membership(trx_hibf_t *h, const uint64_t *kmers, uint64_t n, uint64_t *out_words, uint64_t *stats);
+int trx_hibf_membership_dev(trx_hibf_t *h, const uint64_t *d_kmers, uint64_t n, uint64_t *d_out_words,
+                            uint64_t *stats);
+uint64_t trx_hibf_user_bin_words(const trx_hibf_t *h);
+
+/* ------------------------------------------------------------------------ a9/a10: verify */
+/* Residue store in HBM: what iter_disk_search re-reads from disk on every query
+ * (include/query.h:97-188).  Records are grouped by bin, bins ascending, file order inside a bin:
+ * rec_bin must be non-decreasing. */
+int trx_text_upload(trx_ctx_t *ctx, const uint8_t *residues, const uint64_t *rec_offsets, const uint32_t *rec_bin,
+                    uint64_t n_records, uint64_t n_bins, trx_text_t **out);
+void trx_text_destroy(trx_text_t *t);
+
+/* Compiles the verify regex as iter_disk_search does ("(" + query + ")"): posix_longest = 1 →
+ * RE2::POSIX, leftmost-longest (peptide, query.h:146-149); 0 → default RE2, leftmost-first (DNA,
+ * query.h:101-104).  Supported syntax = what TetRex's own lexer accepts (include/utils.h:96-468):
+ * literals, '.', [..] / [^..] without ranges, ( ) | * + ? {m} {m,n}, backslash escapes.  Anything
+ * else, more than TRX_REGEX_MAX_POSITIONS symbol positions after {m,n} expansion, or a pattern that
+ * matches the empty string (the reference spins forever on those) → TRX_EREGEX. */
+#define TRX_REGEX_MAX_POSITIONS 128
+int trx_regex_compile(const char *pattern, int posix_longest, trx_regex_t **out);
+void trx_regex_destroy(trx_regex_t *re);
+int trx_regex_positions(const trx_regex_t *re);
+
+typedef struct trx_hit {
+    uint32_t bin;
+    uint32_t record; /* global record index as uploaded */
+    uint32_t start;  /* byte offset in the record (reverse strand: in the reverse-complemented record) */
+    uint32_t end;    /* exclusive */
+} trx_hit;
+
+/* K4 — verify_fasta_hit / verify_reduced_fasta_hit / reverse_verify_fasta_hit (src/query.cpp:167-315):
+ * every record of every bin whose bit is set in candidate_bin_words (ceil(n_bins/64) words, host) is
+ * scanned with non-overlapping FindAndConsume semantics.  map256 (nullable, host): byte map applied
+ * to the text before matching (redmap_ of a reduced index).  reverse_strand: scan comp_tab-
+ * complemented, reversed records (src/query.cpp:7-16,167-191).  hits come back sorted by
+ * (bin, record, start) = the reference's -t 1 print order.  If more than cap hits exist the first
+ * cap are returned, *n_hits holds the total and the call returns TRX_ECAPACITY.
+ * stats (nullable): [0] = residues scanned. */
+int trx_regex_scan(trx_text_t *text, trx_regex_t *re, const uint64_t *candidate_bin_words, int reverse_strand,
+                   const uint8_t *map256, trx_hit *hits, uint64_t cap, uint64_t *n_hits, uint64_t *stats);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TETREX_B200_H */

@@ -1,0 +1,588 @@
+// ibf.cu — C ABI for the flat IBF (rows a1–a7 of SURVEY.md §8): create/upload/download, K1 emplace,
+// K2 bulk_contains and the collector's path algebra.
+#include <type_traits>
+
+#include "ibf_kernels.cuh"
+
+namespace trx
+{
+
+static ibf_geom geom_of(trx_ibf const * f)
+{
+    return ibf_geom{f->d_words, f->bin_size, f->shard_words, f->shard_word_begin,
+                    static_cast<uint32_t>(f->hash_shift), static_cast<uint32_t>(f->hash_funs)};
+}
+
+static int pow2_ceil(uint64_t x)
+{
+    int g = 1;
+    while (static_cast<uint64_t>(g) < x && g < 32)
+        g <<= 1;
+    return g;
+}
+
+template <int H, int V, int MODE>
+static int launch_probe_g(trx_ctx * ctx, ibf_geom g, int G, uint64_t const * kmers, uint64_t n, uint64_t * out,
+                          uint32_t const * slots, uint8_t * alive, uint64_t const * hits, uint32_t const * hit_index)
+{
+    auto go = [&](auto gtag) -> int
+    {
+        constexpr int GG = decltype(gtag)::value;
+        unsigned grid = grid_for(n, 256 / GG, ctx->sm_count, 8);
+        probe_kernel<H, V, GG, MODE><<<grid, 256, 0, ctx->stream>>>(g, kmers, n, out, slots, alive, hits, hit_index);
+        ++ctx->launches;
+        TRX_CUDA(cudaGetLastError());
+        return TRX_OK;
+    };
+    switch (G)
+    {
+    case 1: return go(std::integral_constant<int, 1>{});
+    case 2: return go(std::integral_constant<int, 2>{});
+    case 4: return go(std::integral_constant<int, 4>{});
+    case 8: return go(std::integral_constant<int, 8>{});
+    case 16: return go(std::integral_constant<int, 16>{});
+    default: return go(std::integral_constant<int, 32>{});
+    }
+}
+
+template <int MODE>
+static int launch_probe(trx_ctx * ctx, ibf_geom g, uint64_t const * kmers, uint64_t n, uint64_t * out,
+                        uint32_t const * slots, uint8_t * alive, uint64_t const * hits = nullptr,
+                        uint32_t const * hit_index = nullptr)
+{
+    if (n == 0)
+        return TRX_OK;
+    bool const vec2 = (g.shard_words % 2 == 0);
+    int const G = pow2_ceil(vec2 ? g.shard_words / 2 : g.shard_words);
+#define TRX_PROBE_H(HH)                                                                                                \
+    return vec2 ? launch_probe_g<HH, 2, MODE>(ctx, g, G, kmers, n, out, slots, alive, hits, hit_index)                 \
+                : launch_probe_g<HH, 1, MODE>(ctx, g, G, kmers, n, out, slots, alive, hits, hit_index)
+    if constexpr (MODE == 2)
+    {
+        TRX_PROBE_H(1);
+    }
+    else
+    {
+        switch (g.hash_funs)
+        {
+        case 1: TRX_PROBE_H(1);
+        case 2: TRX_PROBE_H(2);
+        case 3: TRX_PROBE_H(3);
+        case 4: TRX_PROBE_H(4);
+        default: TRX_PROBE_H(5);
+        }
+    }
+#undef TRX_PROBE_H
+}
+
+// exposed to hibf.cu
+int paths_and_hits_launch(trx_ctx * ctx, uint64_t * slot_words, uint64_t W, uint64_t const * d_hits,
+                          uint32_t const * d_hit_index, uint32_t const * d_slots, uint64_t n, uint8_t * d_alive)
+{
+    ibf_geom g{nullptr, 0, W, 0, 0, 1};
+    return launch_probe<2>(ctx, g, nullptr, n, slot_words, d_slots, d_alive, d_hits, d_hit_index);
+}
+
+} // namespace trx
+
+using namespace trx;
+
+extern "C"
+{
+
+int trx_ibf_create(trx_ctx_t * ctx, uint64_t bins, uint64_t bin_size, uint32_t hash_funs, uint32_t shard_index,
+                   uint32_t shard_count, trx_ibf_t ** out)
+{
+    if (!ctx || !out)
+        return set_error(TRX_EINVAL, "trx_ibf_create: NULL argument");
+    *out = nullptr;
+    // messages follow lib/hibf/src/interleaved_bloom_filter.cpp:41-46
+    if (bins == 0)
+        return set_error(TRX_EINVAL, "The number of bins must be > 0.");
+    if (hash_funs == 0 || hash_funs > 5)
+        return set_error(TRX_EINVAL, "The number of hash functions must be > 0 and <= 5.");
+    if (bin_size == 0)
+        return set_error(TRX_EINVAL, "The size of a bin must be > 0.");
+    if (shard_count == 0)
+        shard_count = 1;
+    auto * f = new (std::nothrow) trx_ibf;
+    if (!f)
+        return set_error(TRX_ENOMEM, "out of host memory");
+    f->ctx = ctx;
+    f->bins = bins;
+    f->bin_size = bin_size;
+    f->hash_funs = hash_funs;
+    f->hash_shift = static_cast<uint64_t>(__builtin_clzll(bin_size));
+    f->bin_words = (bins + 63) / 64;
+    f->technical_bins = f->bin_words * 64;
+    f->n_words = f->bin_words * bin_size; // technical_bins*bin_size bits / 64
+    if (shard_index >= shard_count || f->bin_words % shard_count != 0)
+    {
+        delete f;
+        return set_error(TRX_EINVAL, "shard %u/%u: shard_count must divide bin_words (%llu)", shard_index, shard_count,
+                         static_cast<unsigned long long>((bins + 63) / 64));
+    }
+    f->shard_words = f->bin_words / shard_count;
+    f->shard_word_begin = f->shard_words * shard_index;
+    f->shard_n_words = f->shard_words * bin_size;
+    if (ctx->use() != TRX_OK)
+    {
+        delete f;
+        return TRX_ECUDA;
+    }
+    cudaError_t e = cudaMalloc(&f->d_words, f->shard_n_words * sizeof(uint64_t));
+    if (e != cudaSuccess)
+    {
+        delete f;
+        return set_error(TRX_ENOMEM, "cudaMalloc of %llu matrix bytes: %s",
+                         static_cast<unsigned long long>(f->shard_n_words * 8), cudaGetErrorString(e));
+    }
+    e = cudaMemsetAsync(f->d_words, 0, f->shard_n_words * sizeof(uint64_t), ctx->stream);
+    if (e != cudaSuccess)
+    {
+        cudaFree(f->d_words);
+        delete f;
+        return set_error(TRX_ECUDA, "cudaMemsetAsync: %s", cudaGetErrorString(e));
+    }
+    *out = f;
+    return TRX_OK;
+}
+
+void trx_ibf_destroy(trx_ibf_t * f)
+{
+    if (!f)
+        return;
+    cudaSetDevice(f->ctx->device);
+    cudaStreamSynchronize(f->ctx->stream);
+    if (f->owns_words)
+        cudaFree(f->d_words);
+    delete f;
+}
+
+int trx_ibf_geometry(const trx_ibf_t * f, uint64_t out[10])
+{
+    if (!f || !out)
+        return set_error(TRX_EINVAL, "NULL argument");
+    out[0] = f->bins;
+    out[1] = f->technical_bins;
+    out[2] = f->bin_size;
+    out[3] = f->hash_shift;
+    out[4] = f->bin_words;
+    out[5] = f->hash_funs;
+    out[6] = f->n_words;
+    out[7] = f->shard_word_begin;
+    out[8] = f->shard_words;
+    out[9] = f->shard_n_words;
+    return TRX_OK;
+}
+
+void * trx_ibf_device_words(trx_ibf_t * f)
+{
+    return f ? f->d_words : nullptr;
+}
+
+int trx_ibf_clear(trx_ibf_t * f)
+{
+    if (!f)
+        return set_error(TRX_EINVAL, "NULL argument");
+    TRX_TRY(f->ctx->use());
+    TRX_CUDA(cudaMemsetAsync(f->d_words, 0, f->shard_n_words * sizeof(uint64_t), f->ctx->stream));
+    return TRX_OK;
+}
+
+int trx_ibf_upload(trx_ibf_t * f, const uint64_t * words, uint64_t n_words)
+{
+    if (!f || !words)
+        return set_error(TRX_EINVAL, "NULL argument");
+    if (n_words != f->n_words)
+        return set_error(TRX_EINVAL, "trx_ibf_upload: expected %llu words, got %llu",
+                         static_cast<unsigned long long>(f->n_words), static_cast<unsigned long long>(n_words));
+    TRX_TRY(f->ctx->use());
+    // strided 2-D copy picks this shard's columns out of every row
+    TRX_CUDA(cudaMemcpy2DAsync(f->d_words, f->shard_words * 8, words + f->shard_word_begin, f->bin_words * 8,
+                               f->shard_words * 8, f->bin_size, cudaMemcpyHostToDevice, f->ctx->stream));
+    TRX_CUDA(cudaStreamSynchronize(f->ctx->stream));
+    return TRX_OK;
+}
+
+int trx_ibf_download(trx_ibf_t * f, uint64_t * words, uint64_t n_words)
+{
+    if (!f || !words)
+        return set_error(TRX_EINVAL, "NULL argument");
+    if (n_words != f->n_words)
+        return set_error(TRX_EINVAL, "trx_ibf_download: expected %llu words, got %llu",
+                         static_cast<unsigned long long>(f->n_words), static_cast<unsigned long long>(n_words));
+    TRX_TRY(f->ctx->use());
+    TRX_CUDA(cudaMemcpy2DAsync(words + f->shard_word_begin, f->bin_words * 8, f->d_words, f->shard_words * 8,
+                               f->shard_words * 8, f->bin_size, cudaMemcpyDeviceToHost, f->ctx->stream));
+    TRX_CUDA(cudaStreamSynchronize(f->ctx->stream));
+    return TRX_OK;
+}
+
+// ------------------------------------------------------------------------------------------- K1
+int trx_emplace_values_dev(trx_ibf_t * f, const uint64_t * d_values, const uint32_t * d_bins, uint64_t n)
+{
+    if (!f)
+        return set_error(TRX_EINVAL, "NULL argument");
+    if (n == 0)
+        return TRX_OK;
+    TRX_TRY(f->ctx->use());
+    unsigned grid = grid_for(n, 256, f->ctx->sm_count, 8);
+    emplace_values_kernel<<<grid, 256, 0, f->ctx->stream>>>(geom_of(f), d_values, d_bins, n);
+    ++f->ctx->launches;
+    TRX_CUDA(cudaGetLastError());
+    return TRX_OK;
+}
+
+int trx_emplace_values(trx_ibf_t * f, const uint64_t * values, const uint32_t * bins, uint64_t n)
+{
+    if (!f || (n && (!values || !bins)))
+        return set_error(TRX_EINVAL, "NULL argument");
+    for (uint64_t i = 0; i < n; ++i)
+        if (bins[i] >= f->bins)
+            return set_error(TRX_ERANGE, "bin %u >= bin count %llu", bins[i], static_cast<unsigned long long>(f->bins));
+    trx_ctx * c = f->ctx;
+    TRX_TRY(c->use());
+    TRX_TRY(c->d_in[0].reserve(n * 8));
+    TRX_TRY(c->d_in[1].reserve(n * 4));
+    TRX_CUDA(cudaMemcpyAsync(c->d_in[0].ptr, values, n * 8, cudaMemcpyHostToDevice, c->stream));
+    TRX_CUDA(cudaMemcpyAsync(c->d_in[1].ptr, bins, n * 4, cudaMemcpyHostToDevice, c->stream));
+    TRX_TRY(trx_emplace_values_dev(f, static_cast<uint64_t *>(c->d_in[0].ptr), static_cast<uint32_t *>(c->d_in[1].ptr), n));
+    TRX_CUDA(cudaStreamSynchronize(c->stream));
+    return TRX_OK;
+}
+
+static int check_kmer_args(int molecule, uint32_t k)
+{
+    if (molecule != TRX_MOL_NA && molecule != TRX_MOL_AA)
+        return set_error(TRX_EINVAL, "molecule must be TRX_MOL_NA or TRX_MOL_AA");
+    if (k == 0 || (molecule == TRX_MOL_NA && k > 32) || (molecule == TRX_MOL_AA && k > 12))
+        return set_error(TRX_EINVAL, "k=%u out of range (DNA 1..32, peptide 1..12, src/main.cpp:28-32)", k);
+    return TRX_OK;
+}
+
+// aamap lives in the context's 4th input scratch (256 bytes)
+static int upload_aamap(trx_ctx * c, int reduction, uint8_t ** d_map)
+{
+    uint8_t aamap[256], redmap[256];
+    trx_peptide_maps(reduction, aamap, redmap);
+    TRX_TRY(c->d_in[3].reserve(256));
+    TRX_CUDA(cudaMemcpyAsync(c->d_in[3].ptr, aamap, 256, cudaMemcpyHostToDevice, c->stream));
+    TRX_CUDA(cudaStreamSynchronize(c->stream)); // aamap is a stack buffer
+    *d_map = static_cast<uint8_t *>(c->d_in[3].ptr);
+    return TRX_OK;
+}
+
+int trx_emplace_records_dev(trx_ibf_t * f, int molecule, uint32_t k, int reduction, const uint8_t * d_residues,
+                            uint64_t n_residues, const uint64_t * d_rec_offsets, const uint32_t * d_rec_bin,
+                            uint64_t n_records)
+{
+    if (!f)
+        return set_error(TRX_EINVAL, "NULL argument");
+    TRX_TRY(check_kmer_args(molecule, k));
+    if (n_records == 0 || n_residues == 0)
+        return TRX_OK;
+    trx_ctx * c = f->ctx;
+    TRX_TRY(c->use());
+    uint64_t n_runs = (n_residues + kRun - 1) / kRun;
+    unsigned grid = grid_for(n_runs, 256, c->sm_count, 8);
+    if (molecule == TRX_MOL_NA)
+    {
+        emplace_records_kernel<TRX_MOL_NA><<<grid, 256, 0, c->stream>>>(geom_of(f), d_residues, n_residues,
+                                                                        d_rec_offsets, d_rec_bin, n_records, k, nullptr);
+    }
+    else
+    {
+        uint8_t * d_map = nullptr;
+        TRX_TRY(upload_aamap(c, reduction, &d_map));
+        emplace_records_kernel<TRX_MOL_AA><<<grid, 256, 0, c->stream>>>(geom_of(f), d_residues, n_residues,
+                                                                        d_rec_offsets, d_rec_bin, n_records, k, d_map);
+    }
+    ++c->launches;
+    TRX_CUDA(cudaGetLastError());
+    return TRX_OK;
+}
+
+int trx_emplace_records(trx_ibf_t * f, int molecule, uint32_t k, int reduction, const uint8_t * residues,
+                        const uint64_t * rec_offsets, const uint32_t * rec_bin, uint64_t n_records)
+{
+    if (!f || (n_records && (!residues || !rec_offsets || !rec_bin)))
+        return set_error(TRX_EINVAL, "NULL argument");
+    TRX_TRY(check_kmer_args(molecule, k));
+    if (n_records == 0)
+        return TRX_OK;
+    if (rec_offsets[0] != 0)
+        return set_error(TRX_EINVAL, "rec_offsets[0] must be 0");
+    for (uint64_t i = 0; i < n_records; ++i)
+    {
+        if (rec_offsets[i + 1] < rec_offsets[i])
+            return set_error(TRX_EINVAL, "rec_offsets must be non-decreasing");
+        if (rec_bin[i] >= f->bins)
+            return set_error(TRX_ERANGE, "record %llu: bin %u >= bin count %llu", static_cast<unsigned long long>(i),
+                             rec_bin[i], static_cast<unsigned long long>(f->bins));
+    }
+    uint64_t const n_res = rec_offsets[n_records];
+    trx_ctx * c = f->ctx;
+    TRX_TRY(c->use());
+    TRX_TRY(c->d_in[0].reserve(n_res + 64));
+    TRX_TRY(c->d_in[1].reserve((n_records + 1) * 8));
+    TRX_TRY(c->d_in[2].reserve(n_records * 4));
+    TRX_CUDA(cudaMemcpyAsync(c->d_in[0].ptr, residues, n_res, cudaMemcpyHostToDevice, c->stream));
+    TRX_CUDA(cudaMemcpyAsync(c->d_in[1].ptr, rec_offsets, (n_records + 1) * 8, cudaMemcpyHostToDevice, c->stream));
+    TRX_CUDA(cudaMemcpyAsync(c->d_in[2].ptr, rec_bin, n_records * 4, cudaMemcpyHostToDevice, c->stream));
+    TRX_TRY(trx_emplace_records_dev(f, molecule, k, reduction, static_cast<uint8_t *>(c->d_in[0].ptr), n_res,
+                                    static_cast<uint64_t *>(c->d_in[1].ptr), static_cast<uint32_t *>(c->d_in[2].ptr),
+                                    n_records));
+    TRX_CUDA(cudaStreamSynchronize(c->stream));
+    return TRX_OK;
+}
+
+int trx_decompose_records(trx_ctx_t * c, int molecule, uint32_t k, int reduction, const uint8_t * residues,
+                          const uint64_t * rec_offsets, uint64_t n_records, uint64_t * out_values,
+                          uint64_t out_capacity, uint64_t * out_offsets)
+{
+    if (!c || !rec_offsets || !out_offsets)
+        return set_error(TRX_EINVAL, "NULL argument");
+    TRX_TRY(check_kmer_args(molecule, k));
+    out_offsets[0] = 0;
+    for (uint64_t i = 0; i < n_records; ++i)
+        out_offsets[i + 1] = out_offsets[i] + trx_emit_count(molecule, k, rec_offsets[i + 1] - rec_offsets[i]);
+    uint64_t const n_out = out_offsets[n_records];
+    if (n_out > out_capacity)
+        return set_error(TRX_ECAPACITY, "trx_decompose_records: need room for %llu values, got %llu",
+                         static_cast<unsigned long long>(n_out), static_cast<unsigned long long>(out_capacity));
+    if (n_out == 0)
+        return TRX_OK;
+    if (!residues || !out_values)
+        return set_error(TRX_EINVAL, "NULL argument");
+    uint64_t const n_res = rec_offsets[n_records];
+    TRX_TRY(c->use());
+    TRX_TRY(c->d_in[0].reserve(n_res + 64));
+    TRX_TRY(c->d_in[1].reserve((n_records + 1) * 8));
+    TRX_TRY(c->d_in[2].reserve((n_records + 1) * 8));
+    TRX_TRY(c->d_out[0].reserve(n_out * 8));
+    TRX_CUDA(cudaMemcpyAsync(c->d_in[0].ptr, residues, n_res, cudaMemcpyHostToDevice, c->stream));
+    TRX_CUDA(cudaMemcpyAsync(c->d_in[1].ptr, rec_offsets, (n_records + 1) * 8, cudaMemcpyHostToDevice, c->stream));
+    TRX_CUDA(cudaMemcpyAsync(c->d_in[2].ptr, out_offsets, (n_records + 1) * 8, cudaMemcpyHostToDevice, c->stream));
+    unsigned grid = grid_for(n_out, 256, c->sm_count, 8);
+    auto * d_text = static_cast<uint8_t *>(c->d_in[0].ptr);
+    auto * d_ro = static_cast<uint64_t *>(c->d_in[1].ptr);
+    auto * d_oo = static_cast<uint64_t *>(c->d_in[2].ptr);
+    auto * d_out = static_cast<uint64_t *>(c->d_out[0].ptr);
+    if (molecule == TRX_MOL_NA)
+    {
+        decompose_kernel<TRX_MOL_NA><<<grid, 256, 0, c->stream>>>(d_text, d_ro, d_oo, n_records, k, nullptr, d_out, n_out);
+    }
+    else
+    {
+        uint8_t * d_map = nullptr;
+        TRX_TRY(upload_aamap(c, reduction, &d_map));
+        decompose_kernel<TRX_MOL_AA><<<grid, 256, 0, c->stream>>>(d_text, d_ro, d_oo, n_records, k, d_map, d_out, n_out);
+    }
+    ++c->launches;
+    TRX_CUDA(cudaGetLastError());
+    TRX_CUDA(cudaMemcpyAsync(out_values, d_out, n_out * 8, cudaMemcpyDeviceToHost, c->stream));
+    TRX_CUDA(cudaStreamSynchronize(c->stream));
+    return TRX_OK;
+}
+
+// ------------------------------------------------------------------------------------------- K2
+int trx_bulk_contains_dev(trx_ibf_t * f, const uint64_t * d_kmers, uint64_t n, uint64_t * d_out_words)
+{
+    if (!f)
+        return set_error(TRX_EINVAL, "NULL argument");
+    TRX_TRY(f->ctx->use());
+    return launch_probe<0>(f->ctx, geom_of(f), d_kmers, n, d_out_words, nullptr, nullptr);
+}
+
+int trx_bulk_contains(trx_ibf_t * f, const uint64_t * kmers, uint64_t n, uint64_t * out_words)
+{
+    if (!f || (n && (!kmers || !out_words)))
+        return set_error(TRX_EINVAL, "NULL argument");
+    if (n == 0)
+        return TRX_OK;
+    trx_ctx * c = f->ctx;
+    TRX_TRY(c->use());
+    uint64_t const out_bytes = n * f->shard_words * 8;
+    TRX_TRY(c->d_in[0].reserve(n * 8));
+    TRX_TRY(c->d_out[0].reserve(out_bytes));
+    TRX_CUDA(cudaMemcpyAsync(c->d_in[0].ptr, kmers, n * 8, cudaMemcpyHostToDevice, c->stream));
+    TRX_TRY(trx_bulk_contains_dev(f, static_cast<uint64_t *>(c->d_in[0].ptr), n, static_cast<uint64_t *>(c->d_out[0].ptr)));
+    TRX_CUDA(cudaMemcpyAsync(out_words, c->d_out[0].ptr, out_bytes, cudaMemcpyDeviceToHost, c->stream));
+    TRX_CUDA(cudaStreamSynchronize(c->stream));
+    return TRX_OK;
+}
+
+// --------------------------------------------------------------------------------- path algebra
+int trx_paths_create(trx_ctx_t * ctx, uint64_t words_per_slot, uint64_t capacity, trx_paths_t ** out)
+{
+    if (!ctx || !out || words_per_slot == 0 || capacity == 0)
+        return set_error(TRX_EINVAL, "trx_paths_create: bad argument");
+    TRX_TRY(ctx->use());
+    auto * p = new (std::nothrow) trx_paths;
+    if (!p)
+        return set_error(TRX_ENOMEM, "out of host memory");
+    p->ctx = ctx;
+    p->words_per_slot = words_per_slot;
+    p->capacity = capacity;
+    cudaError_t e = cudaMalloc(&p->d_words, words_per_slot * capacity * 8);
+    if (e != cudaSuccess)
+    {
+        delete p;
+        return set_error(TRX_ENOMEM, "cudaMalloc paths: %s", cudaGetErrorString(e));
+    }
+    cudaMemsetAsync(p->d_words, 0, words_per_slot * capacity * 8, ctx->stream);
+    *out = p;
+    return TRX_OK;
+}
+
+void trx_paths_destroy(trx_paths_t * p)
+{
+    if (!p)
+        return;
+    cudaSetDevice(p->ctx->device);
+    cudaStreamSynchronize(p->ctx->stream);
+    cudaFree(p->d_words);
+    delete p;
+}
+
+void * trx_paths_device_words(trx_paths_t * p)
+{
+    return p ? p->d_words : nullptr;
+}
+
+int trx_paths_fill(trx_paths_t * p, uint64_t first, uint64_t n, uint64_t bins)
+{
+    if (!p)
+        return set_error(TRX_EINVAL, "NULL argument");
+    if (first + n > p->capacity)
+        return set_error(TRX_ERANGE, "slots [%llu,%llu) exceed capacity %llu", (unsigned long long)first,
+                         (unsigned long long)(first + n), (unsigned long long)p->capacity);
+    if (bins > p->words_per_slot * 64)
+        return set_error(TRX_EINVAL, "bins exceed slot width");
+    if (n == 0)
+        return TRX_OK;
+    TRX_TRY(p->ctx->use());
+    unsigned grid = grid_for(n * p->words_per_slot, 256, p->ctx->sm_count, 8);
+    paths_fill_kernel<<<grid, 256, 0, p->ctx->stream>>>(p->d_words, p->words_per_slot, first, n, bins);
+    ++p->ctx->launches;
+    TRX_CUDA(cudaGetLastError());
+    return TRX_OK;
+}
+
+static int stage_u32(trx_ctx * c, int which, uint32_t const * host, uint64_t n, uint32_t ** dev)
+{
+    TRX_TRY(c->d_in[which].reserve(n * 4));
+    TRX_CUDA(cudaMemcpyAsync(c->d_in[which].ptr, host, n * 4, cudaMemcpyHostToDevice, c->stream));
+    *dev = static_cast<uint32_t *>(c->d_in[which].ptr);
+    return TRX_OK;
+}
+
+static int check_slots(trx_paths const * p, uint32_t const * slots, uint64_t n)
+{
+    for (uint64_t i = 0; i < n; ++i)
+        if (slots[i] >= p->capacity)
+            return set_error(TRX_ERANGE, "slot %u >= capacity %llu", slots[i], (unsigned long long)p->capacity);
+    return TRX_OK;
+}
+
+int trx_paths_step(trx_ibf_t * f, trx_paths_t * p, const uint64_t * kmers, const uint32_t * slots, uint64_t n,
+                   uint8_t * alive)
+{
+    if (!f || !p || (n && (!kmers || !slots || !alive)))
+        return set_error(TRX_EINVAL, "NULL argument");
+    if (p->words_per_slot != f->shard_words || p->ctx != f->ctx)
+        return set_error(TRX_EINVAL, "path slots (%llu words) do not match the IBF shard (%llu words)",
+                         (unsigned long long)p->words_per_slot, (unsigned long long)f->shard_words);
+    if (n == 0)
+        return TRX_OK;
+    TRX_TRY(check_slots(p, slots, n));
+    trx_ctx * c = f->ctx;
+    TRX_TRY(c->use());
+    TRX_TRY(c->d_in[0].reserve(n * 8));
+    TRX_TRY(c->d_out[1].reserve(n));
+    TRX_CUDA(cudaMemcpyAsync(c->d_in[0].ptr, kmers, n * 8, cudaMemcpyHostToDevice, c->stream));
+    uint32_t * d_slots = nullptr;
+    TRX_TRY(stage_u32(c, 1, slots, n, &d_slots));
+    TRX_TRY(launch_probe<1>(c, geom_of(f), static_cast<uint64_t *>(c->d_in[0].ptr), n, p->d_words, d_slots,
+                            static_cast<uint8_t *>(c->d_out[1].ptr)));
+    TRX_CUDA(cudaMemcpyAsync(alive, c->d_out[1].ptr, n, cudaMemcpyDeviceToHost, c->stream));
+    TRX_CUDA(cudaStreamSynchronize(c->stream));
+    return TRX_OK;
+}
+
+int trx_paths_and_hits(trx_paths_t * p, const uint64_t * d_hits, const uint32_t * hit_index, const uint32_t * slots,
+                       uint64_t n, uint8_t * alive)
+{
+    if (!p || (n && (!d_hits || !hit_index || !slots || !alive)))
+        return set_error(TRX_EINVAL, "NULL argument");
+    if (n == 0)
+        return TRX_OK;
+    TRX_TRY(check_slots(p, slots, n));
+    trx_ctx * c = p->ctx;
+    TRX_TRY(c->use());
+    uint32_t *d_idx = nullptr, *d_slots = nullptr;
+    TRX_TRY(stage_u32(c, 0, hit_index, n, &d_idx));
+    TRX_TRY(stage_u32(c, 1, slots, n, &d_slots));
+    TRX_TRY(c->d_out[1].reserve(n));
+    TRX_TRY(paths_and_hits_launch(c, p->d_words, p->words_per_slot, d_hits, d_idx, d_slots, n,
+                                  static_cast<uint8_t *>(c->d_out[1].ptr)));
+    TRX_CUDA(cudaMemcpyAsync(alive, c->d_out[1].ptr, n, cudaMemcpyDeviceToHost, c->stream));
+    TRX_CUDA(cudaStreamSynchronize(c->stream));
+    return TRX_OK;
+}
+
+int trx_paths_or(trx_paths_t * p, const uint32_t * dst, const uint32_t * src, uint64_t n)
+{
+    if (!p || (n && (!dst || !src)))
+        return set_error(TRX_EINVAL, "NULL argument");
+    if (n == 0)
+        return TRX_OK;
+    TRX_TRY(check_slots(p, dst, n));
+    TRX_TRY(check_slots(p, src, n));
+    trx_ctx * c = p->ctx;
+    TRX_TRY(c->use());
+    uint32_t *d_dst = nullptr, *d_src = nullptr;
+    TRX_TRY(stage_u32(c, 0, dst, n, &d_dst));
+    TRX_TRY(stage_u32(c, 1, src, n, &d_src));
+    uint64_t const W = p->words_per_slot;
+    int const G = pow2_ceil(W);
+    auto go = [&](auto gtag) -> int
+    {
+        constexpr int GG = decltype(gtag)::value;
+        unsigned grid = grid_for(n, 256 / GG, c->sm_count, 8);
+        paths_or_kernel<GG><<<grid, 256, 0, c->stream>>>(p->d_words, W, d_dst, d_src, n);
+        ++c->launches;
+        TRX_CUDA(cudaGetLastError());
+        return TRX_OK;
+    };
+    int rc;
+    switch (G)
+    {
+    case 1: rc = go(std::integral_constant<int, 1>{}); break;
+    case 2: rc = go(std::integral_constant<int, 2>{}); break;
+    case 4: rc = go(std::integral_constant<int, 4>{}); break;
+    case 8: rc = go(std::integral_constant<int, 8>{}); break;
+    case 16: rc = go(std::integral_constant<int, 16>{}); break;
+    default: rc = go(std::integral_constant<int, 32>{}); break;
+    }
+    TRX_TRY(rc);
+    // the staged index arrays may be overwritten by the next call: finish before returning
+    TRX_CUDA(cudaStreamSynchronize(c->stream));
+    return TRX_OK;
+}
+
+int trx_paths_read(trx_paths_t * p, uint64_t first, uint64_t n, uint64_t * out_words)
+{
+    if (!p || !out_words)
+        return set_error(TRX_EINVAL, "NULL argument");
+    if (first + n > p->capacity)
+        return set_error(TRX_ERANGE, "slots out of range");
+    TRX_TRY(p->ctx->use());
+    TRX_CUDA(cudaMemcpyAsync(out_words, p->d_words + first * p->words_per_slot, n * p->words_per_slot * 8,
+                             cudaMemcpyDeviceToHost, p->ctx->stream));
+    TRX_CUDA(cudaStreamSynchronize(p->ctx->stream));
+    return TRX_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,407 @@
+// ibf_kernels.cuh — K1 (hash + emplace) and K2 (bulk_contains / path AND) device code.
+//
+// Reference arithmetic: lib/hibf/include/hibf/interleaved_bloom_filter.hpp:164-187 (hash_and_fit),
+// lib/hibf/src/interleaved_bloom_filter.cpp:119-140 (emplace), :203-290 (bulk_contains),
+// include/nucleotide_decomposer.h:81-121, include/peptide_decomposer.h:261-299 (k-mer packing).
+#pragma once
+
+#include "common.cuh"
+
+namespace trx
+{
+
+struct ibf_geom
+{
+    uint64_t * words;       // this shard's matrix, row r at r*shard_words
+    uint64_t bin_size;      // rows
+    uint64_t shard_words;   // words per row held here
+    uint64_t word_begin;    // first global word column held here
+    uint32_t hash_shift;
+    uint32_t hash_funs;
+};
+
+// ------------------------------------------------------------------------------------------- K2
+// One group of G lanes per k-mer; a lane owns V consecutive words (V=2 → 16-byte LDG.128) of every
+// row, striding by G*V.  All H row loads of a lane are issued before the first use so that every
+// thread has H independent random sector requests in flight; with 2048 resident threads per SM that
+// is the memory-level parallelism the random-probe roofline needs.  Nothing is staged in shared
+// memory: a row word is used exactly once, so registers are the right home for it.
+//
+// MODE 0: out[i*shard_words + w] = AND_h row_h[w]                       (bulk_contains)
+// MODE 1: slot[slots[i]][w] &= AND_h row_h[w]; alive[i] = any(slot)     (update_path + none())
+// MODE 2: slot[slots[i]][w] &= hits[hit_index[i]][w]; alive[i] = any    (HIBF route)
+template <int H, int V, int G, int MODE>
+__global__ void __launch_bounds__(256)
+    probe_kernel(ibf_geom g, uint64_t const * __restrict__ kmers, uint64_t n, uint64_t * __restrict__ out,
+                 uint32_t const * __restrict__ slots, uint8_t * __restrict__ alive,
+                 uint64_t const * __restrict__ hits, uint32_t const * __restrict__ hit_index)
+{
+    using vec_t = typename std::conditional<V == 2, ulonglong2, uint64_t>::type;
+    constexpr int groups_per_block = 256 / G;
+    unsigned const lane_in_group = threadIdx.x % G;
+    uint64_t const group0 = static_cast<uint64_t>(blockIdx.x) * groups_per_block + threadIdx.x / G;
+    uint64_t const stride = static_cast<uint64_t>(gridDim.x) * groups_per_block;
+    uint64_t const W = g.shard_words;
+
+    for (uint64_t i = group0; i < n; i += stride)
+    {
+        uint64_t rowbase[H > 0 ? H : 1];
+        if constexpr (MODE != 2)
+        {
+            uint64_t const v = __ldg(kmers + i);
+#pragma unroll
+            for (int h = 0; h < H; ++h)
+                rowbase[h] = hash_row(v, h, g.hash_shift, g.bin_size) * W;
+        }
+        else
+        {
+            rowbase[0] = static_cast<uint64_t>(__ldg(hit_index + i)) * W;
+        }
+        uint64_t * dst;
+        if constexpr (MODE == 0)
+            dst = out + i * W;
+        else
+            dst = out + static_cast<uint64_t>(__ldg(slots + i)) * W;
+
+        uint64_t any = 0;
+        for (uint64_t w = static_cast<uint64_t>(lane_in_group) * V; w < W; w += static_cast<uint64_t>(G) * V)
+        {
+            vec_t r[H > 0 ? H : 1];
+            if constexpr (MODE != 2)
+            {
+#pragma unroll
+                for (int h = 0; h < H; ++h)
+                    r[h] = *reinterpret_cast<vec_t const *>(g.words + rowbase[h] + w);
+            }
+            else
+            {
+                r[0] = *reinterpret_cast<vec_t const *>(hits + rowbase[0] + w);
+            }
+            vec_t acc = r[0];
+            if constexpr (MODE != 2)
+            {
+#pragma unroll
+                for (int h = 1; h < H; ++h)
+                {
+                    if constexpr (V == 2)
+                    {
+                        acc.x &= r[h].x;
+                        acc.y &= r[h].y;
+                    }
+                    else
+                        acc &= r[h];
+                }
+            }
+            if constexpr (MODE != 0)
+            {
+                vec_t cur = *reinterpret_cast<vec_t *>(dst + w);
+                if constexpr (V == 2)
+                {
+                    acc.x &= cur.x;
+                    acc.y &= cur.y;
+                    any |= acc.x | acc.y;
+                }
+                else
+                {
+                    acc &= cur;
+                    any |= acc;
+                }
+            }
+            *reinterpret_cast<vec_t *>(dst + w) = acc;
+        }
+        if constexpr (MODE != 0)
+        {
+            // group-wide none(): OR-reduce over the G lanes of this k-mer with shuffles
+            unsigned flag = any != 0;
+#pragma unroll
+            for (int off = G / 2; off > 0; off >>= 1)
+                flag |= __shfl_xor_sync(0xffffffffu, flag, off, G);
+            if (lane_in_group == 0)
+                alive[i] = static_cast<uint8_t>(flag);
+        }
+    }
+}
+
+// slot[dst[i]] |= slot[src[i]] — push/absorb/split and `path_matrix |= path` of the collector.
+template <int G>
+__global__ void __launch_bounds__(256)
+    paths_or_kernel(uint64_t * __restrict__ words, uint64_t W, uint32_t const * __restrict__ dst,
+                    uint32_t const * __restrict__ src, uint64_t n)
+{
+    constexpr int groups_per_block = 256 / G;
+    unsigned const lane_in_group = threadIdx.x % G;
+    uint64_t const group0 = static_cast<uint64_t>(blockIdx.x) * groups_per_block + threadIdx.x / G;
+    uint64_t const stride = static_cast<uint64_t>(gridDim.x) * groups_per_block;
+    for (uint64_t i = group0; i < n; i += stride)
+    {
+        uint64_t const * s = words + static_cast<uint64_t>(src[i]) * W;
+        unsigned long long * d = reinterpret_cast<unsigned long long *>(words + static_cast<uint64_t>(dst[i]) * W);
+        for (uint64_t w = lane_in_group; w < W; w += G)
+        {
+            uint64_t v = s[w];
+            if (v)
+                atomicOr(d + w, static_cast<unsigned long long>(v));
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256)
+    paths_fill_kernel(uint64_t * __restrict__ words, uint64_t W, uint64_t first, uint64_t n, uint64_t bins)
+{
+    uint64_t const total = n * W;
+    for (uint64_t t = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; t < total;
+         t += static_cast<uint64_t>(gridDim.x) * blockDim.x)
+    {
+        uint64_t const w = t % W;
+        uint64_t v;
+        if (bins >= (w + 1) * 64)
+            v = ~0ULL;
+        else if (bins <= w * 64)
+            v = 0;
+        else
+            v = (1ULL << (bins - w * 64)) - 1;
+        words[first * W + t] = v;
+    }
+}
+
+// ------------------------------------------------------------------------------------------- K1a
+// emplace for explicit (value, bin) pairs: H hashes, H 64-bit atomic ORs (RED.OR, no return value).
+__global__ void __launch_bounds__(256)
+    emplace_values_kernel(ibf_geom g, uint64_t const * __restrict__ values, uint32_t const * __restrict__ bins,
+                          uint64_t n)
+{
+    for (uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+         i += static_cast<uint64_t>(gridDim.x) * blockDim.x)
+    {
+        uint64_t const v = __ldg(values + i);
+        uint32_t const b = __ldg(bins + i);
+        uint64_t const col = (b >> 6);
+        if (col < g.word_begin || col >= g.word_begin + g.shard_words)
+            continue; // another shard owns this 64-bin block
+        unsigned long long const bit = 1ULL << (b & 63);
+        for (uint32_t h = 0; h < g.hash_funs; ++h)
+        {
+            uint64_t const row = hash_row(v, static_cast<int>(h), g.hash_shift, g.bin_size);
+            atomicOr(reinterpret_cast<unsigned long long *>(g.words + row * g.shard_words + (col - g.word_begin)), bit);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------- K1b
+__device__ __forceinline__ uint64_t dna_code(uint8_t c)
+{
+    return (c >> 1) & 3u; // nucleotide_decomposer.h:83-89
+}
+
+// reverse complement of a packed 2-bit k-mer: complement = code^2, reverse the 2-bit groups.
+__device__ __forceinline__ uint64_t dna_revcomp(uint64_t fwd, uint32_t k)
+{
+    uint64_t x = fwd ^ 0xAAAAAAAAAAAAAAAAULL;
+    x = __brevll(x);                                                            // reverses single bits …
+    x = ((x & 0x5555555555555555ULL) << 1) | ((x >> 1) & 0x5555555555555555ULL); // … so swap each pair back
+    return x >> (64 - 2 * k);
+}
+
+struct emplace_sink
+{
+    ibf_geom g;
+    uint64_t col;
+    unsigned long long bit;
+    bool mine;
+    __device__ __forceinline__ void set_bin(uint32_t b)
+    {
+        uint64_t c = b >> 6;
+        mine = c >= g.word_begin && c < g.word_begin + g.shard_words;
+        col = c - g.word_begin;
+        bit = 1ULL << (b & 63);
+    }
+    __device__ __forceinline__ void operator()(uint64_t v) const
+    {
+        if (!mine)
+            return;
+        for (uint32_t h = 0; h < g.hash_funs; ++h)
+        {
+            uint64_t const row = hash_row(v, static_cast<int>(h), g.hash_shift, g.bin_size);
+            atomicOr(reinterpret_cast<unsigned long long *>(g.words + row * g.shard_words + col), bit);
+        }
+    }
+};
+
+constexpr int kRun = 16;          // residues per thread = one LDG.128
+constexpr int kWindowBytes = 48;  // run + halo (k-1 <= 31) rounded up to 3 × 16 B
+
+// Residue-parallel decomposition + emplace.  Thread t owns the windows that START in
+// [16t, 16t+16); it reads those 16 bytes plus k-1 halo bytes (three 16-byte loads, the second and
+// third hit L1 because the neighbouring lanes load them as their own run), rolls the packed k-mer
+// across its run and fires H atomic ORs per window.  Record boundaries come from rec_offsets; the
+// record of the first byte is found by binary search, later boundaries by walking forward.
+template <int MOL>
+__global__ void __launch_bounds__(256)
+    emplace_records_kernel(ibf_geom g, uint8_t const * __restrict__ text, uint64_t n_residues,
+                           uint64_t const * __restrict__ rec_offsets, uint32_t const * __restrict__ rec_bin,
+                           uint64_t n_records, uint32_t k, uint8_t const * __restrict__ aamap)
+{
+    __shared__ uint8_t s_map[256];
+    if constexpr (MOL == TRX_MOL_AA)
+    {
+        s_map[threadIdx.x] = aamap[threadIdx.x];
+        __syncthreads();
+    }
+    constexpr uint32_t bits = MOL == TRX_MOL_NA ? 2 : 5;
+    uint64_t const mask = (bits * k >= 64) ? ~0ULL : ((1ULL << (bits * k)) - 1);
+    uint64_t const n_runs = (n_residues + kRun - 1) / kRun;
+
+    for (uint64_t run = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; run < n_runs;
+         run += static_cast<uint64_t>(gridDim.x) * blockDim.x)
+    {
+        uint64_t const p0 = run * kRun;
+        uint64_t const run_end = min(p0 + kRun, n_residues);
+        uint64_t const last = min(run_end + k - 1, n_residues); // exclusive: bytes this thread may consume
+
+        // 48 bytes into registers
+        uint8_t buf[kWindowBytes];
+        if (p0 + kWindowBytes <= n_residues && (reinterpret_cast<uintptr_t>(text) & 15) == 0)
+        {
+            uint4 const * src = reinterpret_cast<uint4 const *>(text + p0);
+            uint4 * dstv = reinterpret_cast<uint4 *>(buf);
+            dstv[0] = __ldg(src);
+            dstv[1] = __ldg(src + 1);
+            dstv[2] = __ldg(src + 2);
+        }
+        else
+        {
+#pragma unroll
+            for (int j = 0; j < kWindowBytes; ++j)
+                buf[j] = (p0 + j < n_residues) ? text[p0 + j] : 0;
+        }
+
+        // record containing p0: largest r with rec_offsets[r] <= p0
+        uint64_t lo = 0, hi = n_records;
+        while (hi - lo > 1)
+        {
+            uint64_t mid = (lo + hi) >> 1;
+            if (__ldg(rec_offsets + mid) <= p0)
+                lo = mid;
+            else
+                hi = mid;
+        }
+        uint64_t r = lo;
+        uint64_t rec_begin = __ldg(rec_offsets + r);
+        uint64_t rec_end = __ldg(rec_offsets + r + 1);
+        while (rec_end <= p0 && r + 1 < n_records) // empty records sharing the offset
+        {
+            ++r;
+            rec_begin = rec_end;
+            rec_end = __ldg(rec_offsets + r + 1);
+        }
+        emplace_sink sink{g, 0, 0, false};
+        sink.set_bin(__ldg(rec_bin + r));
+
+        uint64_t fwd = 0, rev = 0;
+        uint32_t cnt = 0;
+#pragma unroll 1
+        for (uint64_t p = p0; p < last; ++p)
+        {
+            if (p >= rec_end)
+            {
+                if (p >= run_end)
+                    break; // windows starting in the next record belong to another thread
+                do
+                {
+                    ++r;
+                    rec_begin = rec_end;
+                    rec_end = __ldg(rec_offsets + r + 1);
+                } while (rec_end <= p);
+                sink.set_bin(__ldg(rec_bin + r));
+                cnt = 0;
+                fwd = rev = 0;
+            }
+            uint8_t const c = buf[p - p0];
+            if constexpr (MOL == TRX_MOL_NA)
+            {
+                uint64_t const f = dna_code(c);
+                fwd = ((fwd << 2) & mask) | f;
+                rev = ((rev >> 2) & mask) | ((f ^ 2) << (2 * k - 2));
+            }
+            else
+            {
+                fwd = ((fwd << 5) & mask) | s_map[c];
+            }
+            if (cnt < k)
+                ++cnt;
+            if (cnt == k)
+            {
+                if constexpr (MOL == TRX_MOL_NA)
+                    sink(fwd <= rev ? fwd : rev);
+                else
+                    sink(fwd);
+                // DNA wrap-around k-mers (nucleotide_decomposer.h:104-111 rolls the WHOLE record in after the
+                // first k-mer): rec[j+1..k) ++ rec[0..j] for j = 0..k-2, emitted by the thread that owns the
+                // record's first window.
+                if constexpr (MOL == TRX_MOL_NA)
+                {
+                    if (p + 1 - k == rec_begin)
+                    {
+                        uint64_t wf = fwd, wr = rev;
+                        for (uint32_t j = 0; j + 1 < k; ++j)
+                        {
+                            uint64_t const f = dna_code(buf[rec_begin + j - p0]);
+                            wf = ((wf << 2) & mask) | f;
+                            wr = ((wr >> 2) & mask) | ((f ^ 2) << (2 * k - 2));
+                            sink(wf <= wr ? wf : wr);
+                        }
+                    }
+                }
+            }
+        }
+    }
+}
+
+// Ordered emission (decompose_record's exact call sequence) for hand-off to HIBF construction and for
+// parity tests of rows a1/a2.  One thread per emitted value; packs its k symbols directly.
+template <int MOL>
+__global__ void __launch_bounds__(256)
+    decompose_kernel(uint8_t const * __restrict__ text, uint64_t const * __restrict__ rec_offsets,
+                     uint64_t const * __restrict__ out_offsets, uint64_t n_records, uint32_t k,
+                     uint8_t const * __restrict__ aamap, uint64_t * __restrict__ out, uint64_t n_out)
+{
+    for (uint64_t e = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; e < n_out;
+         e += static_cast<uint64_t>(gridDim.x) * blockDim.x)
+    {
+        uint64_t lo = 0, hi = n_records;
+        while (hi - lo > 1)
+        {
+            uint64_t mid = (lo + hi) >> 1;
+            if (out_offsets[mid] <= e)
+                lo = mid;
+            else
+                hi = mid;
+        }
+        // skip records with zero emits that share the offset: pick the one that actually contains e
+        while (out_offsets[lo + 1] <= e)
+            ++lo;
+        uint8_t const * rec = text + rec_offsets[lo];
+        uint64_t const j = e - out_offsets[lo];
+        uint64_t v = 0;
+        if constexpr (MOL == TRX_MOL_NA)
+        {
+            // virtual string V = rec[0..k) ++ rec[0..L); emit j = window V[j..j+k)
+            for (uint32_t s = 0; s < k; ++s)
+            {
+                uint64_t idx = j + s;
+                uint8_t c = rec[idx < k ? idx : idx - k];
+                v = (v << 2) | dna_code(c);
+            }
+            uint64_t rc = dna_revcomp(v, k);
+            out[e] = v <= rc ? v : rc;
+        }
+        else
+        {
+            for (uint32_t s = 0; s < k; ++s)
+                v = (v << 5) | aamap[rec[j + s]];
+            out[e] = v;
+        }
+    }
+}
+
+} // namespace trx

@@ -1,0 +1,563 @@
+// regex_kernels.cuh — K4 device code: streaming Glushkov scan (phase 1) and exact match resolution
+// (phase 2).  Reference semantics: src/query.cpp:167-315 (FindAndConsume loops), include/query.h:97-188.
+//
+// Phase 1 streams every residue of the candidate bins once.  The text is cut into 128-byte chunks on
+// a fixed global grid; a CTA of 256 threads takes a 32 KB tile (256 chunks) that one elected thread
+// fetches with a single 2-D TMA tensor copy (SWIZZLE_128B, so that thread t reading 16-byte piece i of
+// row t touches bank group i^(t&7): conflict-free LDS.128) into a 2-stage shared-memory ring guarded
+// by mbarriers.  Thread t runs the position automaton over chunk t, injecting the start state only
+// inside its own chunk and running on past the chunk end (no injection) until the state dies, so every
+// match is seen by exactly the thread whose chunk holds its START.  Output: one flag bit per chunk and
+// one byte per record ("a match starts here").
+//
+// Phase 2 runs only on flagged records (rare) and reproduces the reference's non-overlapping
+// leftmost-longest (POSIX) or leftmost-first (Perl) match sequence exactly.
+#pragma once
+
+#include <cuda.h>
+
+#include "common.cuh"
+#include "regex.cuh"
+
+namespace trx
+{
+
+constexpr int kChunkBytes = 128;
+constexpr int kScanThreads = 256;
+constexpr int kTileBytes = kChunkBytes * kScanThreads; // 32 KB
+constexpr int kStages = 2;
+
+// device copy of the automaton; B already has the per-scan byte map (redmap / comp_tab) folded in
+struct regex_dev
+{
+    uint64_t first[kRegexWords];
+    uint64_t last[kRegexWords];
+    uint64_t B[256][kRegexWords];
+    uint64_t follow[64 * kRegexWords][kRegexWords];
+    // ordered lists for leftmost-first
+    uint16_t first_len;
+    uint16_t follow_off[64 * kRegexWords + 1];
+    uint8_t first_list[64 * kRegexWords];
+    uint8_t follow_list[4096]; // flattened; compile rejects patterns whose lists do not fit
+    int32_t positions;
+    int32_t posix_longest;
+    int32_t anchor_begin;
+    int32_t anchor_end;
+};
+
+struct scan_params
+{
+    uint8_t const * text;         // padded to a tile multiple, zero filled
+    uint64_t n_text;              // real bytes
+    uint64_t const * rec_offsets; // n_records + 1
+    uint32_t const * rec_bin;     // n_records
+    uint64_t n_records;
+    uint64_t const * cand_words;  // candidate bin bitmap (device)
+    uint32_t const * tiles;       // tile ids to scan
+    uint32_t n_tiles;
+    uint32_t * chunk_flags;       // bitmap over global chunk ids
+    uint8_t * rec_flags;          // per record
+    regex_dev const * re;
+};
+
+template <int W>
+struct state
+{
+    uint64_t w[W];
+    __device__ __forceinline__ bool any() const
+    {
+        if constexpr (W == 1)
+            return w[0] != 0;
+        else
+            return (w[0] | w[1]) != 0;
+    }
+};
+
+// shared-memory image of the tables phase 1 needs
+template <int W>
+struct scan_tables
+{
+    uint64_t Bf[256][W]; // B & first: the whole step when the state is empty
+    uint64_t B[256][W];
+    uint64_t follow[64 * W][W];
+    uint64_t first[W];
+    uint64_t last[W];
+};
+
+template <int W>
+__device__ __forceinline__ void step(state<W> & S, scan_tables<W> const & T, uint8_t c, bool inject)
+{
+    if (!S.any())
+    {
+        if (inject)
+        {
+#pragma unroll
+            for (int k = 0; k < W; ++k)
+                S.w[k] = T.Bf[c][k];
+        }
+        return;
+    }
+    uint64_t F[W];
+#pragma unroll
+    for (int k = 0; k < W; ++k)
+        F[k] = inject ? T.first[k] : 0;
+#pragma unroll
+    for (int k = 0; k < W; ++k)
+    {
+        uint64_t s = S.w[k];
+        while (s)
+        {
+            int i = __ffsll(static_cast<long long>(s)) - 1;
+            s &= s - 1;
+#pragma unroll
+            for (int q = 0; q < W; ++q)
+                F[q] |= T.follow[k * 64 + i][q];
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < W; ++k)
+        S.w[k] = F[k] & T.B[c][k];
+}
+
+template <int W>
+__device__ __forceinline__ bool accepts(state<W> const & S, scan_tables<W> const & T)
+{
+    if constexpr (W == 1)
+        return (S.w[0] & T.last[0]) != 0;
+    else
+        return ((S.w[0] & T.last[0]) | (S.w[1] & T.last[1])) != 0;
+}
+
+__device__ __forceinline__ uint32_t smem_u32(void const * p)
+{
+    return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+
+__device__ __forceinline__ void mbar_init(uint64_t * bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+
+__device__ __forceinline__ void mbar_wait(uint64_t * bar, uint32_t parity)
+{
+    uint32_t ok;
+    do
+    {
+        asm volatile("{\n\t.reg .pred p;\n\t"
+                     "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                     "selp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok)
+                     : "r"(smem_u32(bar)), "r"(parity)
+                     : "memory");
+    } while (!ok);
+}
+
+// one elected thread: arm the barrier with the byte count, then launch the 2-D tensor copy of one tile
+__device__ __forceinline__ void tma_load_tile(CUtensorMap const * tmap, void * dst, uint64_t * bar, int32_t row)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(kTileBytes) : "memory");
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                 :
+                 : "r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(0), "r"(row), "r"(smem_u32(bar))
+                 : "memory");
+}
+
+__device__ __forceinline__ bool is_candidate(uint64_t const * cand, uint32_t bin)
+{
+    return (cand[bin >> 6] >> (bin & 63)) & 1;
+}
+
+// largest r in [0, n) with off[r] <= g, skipping forward over empty records so that off[r+1] > g
+__device__ __forceinline__ uint64_t record_of(uint64_t const * __restrict__ off, uint64_t n, uint64_t g)
+{
+    uint64_t lo = 0, hi = n;
+    while (hi - lo > 1)
+    {
+        uint64_t mid = (lo + hi) >> 1;
+        if (__ldg(off + mid) <= g)
+            lo = mid;
+        else
+            hi = mid;
+    }
+    return lo;
+}
+
+// DIR = +1: forward strand.  DIR = -1: the record is read back to front (reverse strand; the
+// complement is folded into B).  "Position" below always means position in reading direction.
+template <int W, int DIR, bool USE_TMA>
+__global__ void __launch_bounds__(kScanThreads)
+    regex_scan_phase1(scan_params p, const __grid_constant__ CUtensorMap tmap)
+{
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    // layout: [tile stage 0][tile stage 1][tables][barriers]   (tiles first: SWIZZLE_128B wants 1024-B alignment)
+    uint8_t * tiles = smem_raw;
+    auto & T = *reinterpret_cast<scan_tables<W> *>(smem_raw + (USE_TMA ? kStages * kTileBytes : 0));
+    uint64_t * bars = reinterpret_cast<uint64_t *>(reinterpret_cast<uint8_t *>(&T) + sizeof(scan_tables<W>));
+
+    int const tid = threadIdx.x;
+    regex_dev const & re = *p.re;
+    for (int c = tid; c < 256; c += kScanThreads)
+#pragma unroll
+        for (int k = 0; k < W; ++k)
+        {
+            T.B[c][k] = re.B[c][k];
+            T.Bf[c][k] = re.B[c][k] & re.first[k];
+        }
+    for (int i = tid; i < 64 * W; i += kScanThreads)
+#pragma unroll
+        for (int k = 0; k < W; ++k)
+            T.follow[i][k] = re.follow[i][k];
+    if (tid < W)
+    {
+        T.first[tid] = re.first[tid];
+        T.last[tid] = re.last[tid];
+    }
+    bool const anchor_begin = re.anchor_begin != 0;
+    bool const anchor_end = re.anchor_end != 0;
+    if constexpr (USE_TMA)
+    {
+        if (tid == 0)
+        {
+            mbar_init(&bars[0], 1);
+            mbar_init(&bars[1], 1);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+    }
+    __syncthreads();
+
+    uint32_t const first_tile = blockIdx.x;
+    if constexpr (USE_TMA)
+    {
+        if (tid == 0 && first_tile < p.n_tiles)
+            tma_load_tile(&tmap, tiles, &bars[0], static_cast<int32_t>(p.tiles[first_tile]) * kScanThreads);
+    }
+
+    uint32_t it = 0;
+    for (uint32_t t = first_tile; t < p.n_tiles; t += gridDim.x, ++it)
+    {
+        uint32_t const stage = it & 1;
+        if constexpr (USE_TMA)
+        {
+            // prefetch the next tile into the other stage; every thread left it at the previous __syncthreads
+            uint32_t const tn = t + gridDim.x;
+            if (tid == 0 && tn < p.n_tiles)
+            {
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                tma_load_tile(&tmap, tiles + (stage ^ 1) * kTileBytes, &bars[stage ^ 1],
+                              static_cast<int32_t>(p.tiles[tn]) * kScanThreads);
+            }
+            mbar_wait(&bars[stage], (it >> 1) & 1);
+        }
+        uint64_t const chunk_id = static_cast<uint64_t>(p.tiles[t]) * kScanThreads + tid;
+        uint64_t const g_lo = chunk_id * kChunkBytes;
+        if (g_lo < p.n_text)
+        {
+            uint64_t const g_hi = min(g_lo + kChunkBytes, p.n_text); // exclusive
+            // first byte in reading direction
+            int64_t g = DIR > 0 ? static_cast<int64_t>(g_lo) : static_cast<int64_t>(g_hi) - 1;
+            uint64_t r = record_of(p.rec_offsets, p.n_records, static_cast<uint64_t>(g));
+            uint64_t rec_begin = __ldg(p.rec_offsets + r), rec_end = __ldg(p.rec_offsets + r + 1);
+            while (rec_end <= static_cast<uint64_t>(g)) // empty records sharing this offset
+            {
+                ++r;
+                rec_begin = rec_end;
+                rec_end = __ldg(p.rec_offsets + r + 1);
+            }
+            bool cand = is_candidate(p.cand_words, __ldg(p.rec_bin + r));
+            state<W> S;
+#pragma unroll
+            for (int k = 0; k < W; ++k)
+                S.w[k] = 0;
+            bool chunk_hit = false, rec_hit = false;
+
+            auto flush_record = [&]()
+            {
+                if (rec_hit)
+                    p.rec_flags[r] = 1;
+                rec_hit = false;
+            };
+            // one byte of the automaton; returns nothing, updates S / flags
+            auto feed = [&](uint8_t c, bool inject)
+            {
+                bool const at_first = DIR > 0 ? (static_cast<uint64_t>(g) == rec_begin) : (static_cast<uint64_t>(g) + 1 == rec_end);
+                bool const at_last = DIR > 0 ? (static_cast<uint64_t>(g) + 1 == rec_end) : (static_cast<uint64_t>(g) == rec_begin);
+                step<W>(S, T, c, inject && (!anchor_begin || at_first));
+                if (S.any() && accepts<W>(S, T) && (!anchor_end || at_last))
+                {
+                    chunk_hit = true;
+                    rec_hit = true;
+                }
+            };
+
+            uint8_t const * row = tiles + stage * kTileBytes + tid * kChunkBytes;
+#pragma unroll 1
+            for (int piece = 0; piece < kChunkBytes / 16; ++piece)
+            {
+                int const pi = DIR > 0 ? piece : (kChunkBytes / 16 - 1 - piece);
+                uint64_t const piece_lo = g_lo + static_cast<uint64_t>(pi) * 16;
+                if (piece_lo >= g_hi)
+                    continue; // beyond the end of the text (only in the last chunk)
+                uint4 v;
+                if constexpr (USE_TMA)
+                    v = *reinterpret_cast<uint4 const *>(row + ((pi ^ (tid & 7)) << 4));
+                else
+                    v = __ldg(reinterpret_cast<uint4 const *>(p.text + piece_lo));
+                uint32_t const words[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                for (int b = 0; b < 16; ++b)
+                {
+                    int const bi = DIR > 0 ? b : 15 - b;
+                    uint64_t const gb = piece_lo + bi;
+                    if (gb >= g_hi)
+                        continue;
+                    g = static_cast<int64_t>(gb);
+                    // record boundary in reading direction
+                    if (DIR > 0 ? (gb >= rec_end) : (gb < rec_begin))
+                    {
+                        flush_record();
+                        if constexpr (DIR > 0)
+                        {
+                            do
+                            {
+                                ++r;
+                                rec_begin = rec_end;
+                                rec_end = __ldg(p.rec_offsets + r + 1);
+                            } while (rec_end <= gb);
+                        }
+                        else
+                        {
+                            do
+                            {
+                                --r;
+                                rec_end = rec_begin;
+                                rec_begin = __ldg(p.rec_offsets + r);
+                            } while (rec_begin > gb);
+                        }
+                        cand = is_candidate(p.cand_words, __ldg(p.rec_bin + r));
+#pragma unroll
+                        for (int k = 0; k < W; ++k)
+                            S.w[k] = 0;
+                    }
+                    if (!cand)
+                        continue;
+                    uint8_t const c = static_cast<uint8_t>(words[bi >> 2] >> ((bi & 3) * 8));
+                    feed(c, true);
+                }
+            }
+            // run on past the chunk while a match that started inside it is still alive
+            if (cand && S.any())
+            {
+                if constexpr (DIR > 0)
+                {
+                    for (uint64_t gb = g_hi; gb < rec_end && S.any(); ++gb)
+                    {
+                        g = static_cast<int64_t>(gb);
+                        feed(__ldg(p.text + gb), false);
+                    }
+                }
+                else
+                {
+                    for (int64_t gb = static_cast<int64_t>(g_lo) - 1; gb >= static_cast<int64_t>(rec_begin) && S.any(); --gb)
+                    {
+                        g = gb;
+                        feed(__ldg(p.text + gb), false);
+                    }
+                }
+            }
+            flush_record();
+            if (chunk_hit)
+                atomicOr(p.chunk_flags + (chunk_id >> 5), 1u << (chunk_id & 31));
+        }
+        __syncthreads(); // everyone is done with this stage before it is refilled
+    }
+}
+
+} // namespace trx
+
+namespace trx
+{
+
+struct resolve_params
+{
+    uint8_t const * text;
+    uint64_t const * rec_offsets;
+    uint32_t const * cand_bins;        // candidate bin ids
+    uint64_t const * cand_rec_prefix;  // prefix sums of records per candidate bin (n_cand + 1)
+    uint64_t const * bin_rec_begin;    // first record of every bin (n_bins + 1)
+    uint32_t n_cand;
+    uint64_t n_cand_records;
+    uint32_t const * chunk_flags;
+    uint8_t const * rec_flags;
+    regex_dev const * re;
+    unsigned long long * hit_count;
+    uint64_t * hit_keys;               // record << 32 | start
+    uint32_t * hit_ends;
+    uint64_t cap;
+};
+
+// Anchored leftmost-longest match starting at position s of a record read through `at`: the automaton
+// runs without re-injection; the last position at which an accepting state was live wins.
+template <int W, class At>
+__device__ int64_t match_longest(regex_dev const & re, At at, int64_t s, int64_t L)
+{
+    uint64_t S[W];
+    uint8_t c = at(s);
+#pragma unroll
+    for (int k = 0; k < W; ++k)
+        S[k] = re.first[k] & re.B[c][k];
+    int64_t best = -1;
+    int64_t pos = s + 1; // exclusive end of what has been consumed
+    while (true)
+    {
+        uint64_t any = 0, acc = 0;
+#pragma unroll
+        for (int k = 0; k < W; ++k)
+        {
+            any |= S[k];
+            acc |= S[k] & re.last[k];
+        }
+        if (!any)
+            break;
+        if (acc && (!re.anchor_end || pos == L))
+            best = pos;
+        if (pos >= L)
+            break;
+        c = at(pos);
+        uint64_t F[W];
+#pragma unroll
+        for (int k = 0; k < W; ++k)
+            F[k] = 0;
+#pragma unroll
+        for (int k = 0; k < W; ++k)
+        {
+            uint64_t sbits = S[k];
+            while (sbits)
+            {
+                int i = __ffsll(static_cast<long long>(sbits)) - 1;
+                sbits &= sbits - 1;
+#pragma unroll
+                for (int q = 0; q < W; ++q)
+                    F[q] |= re.follow[k * 64 + i][q];
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < W; ++k)
+            S[k] = F[k] & re.B[c][k];
+        ++pos;
+    }
+    return best;
+}
+
+// Anchored leftmost-first match (Perl / default RE2): Pike VM over the priority-ordered position lists.
+// A thread = a position waiting to consume the next byte; list order = priority.  Reaching ACCEPT
+// records the end and cuts every lower-priority thread; higher-priority threads run on and may
+// still override it.
+template <class At>
+__device__ int64_t match_first(regex_dev const & re, At at, int64_t s, int64_t L)
+{
+    uint8_t cur[64 * kRegexWords], nxt[64 * kRegexWords];
+    int ncur = re.first_len;
+    for (int i = 0; i < ncur; ++i)
+        cur[i] = re.first_list[i];
+    int64_t best = -1;
+    for (int64_t pos = s; pos < L && ncur > 0; ++pos)
+    {
+        uint8_t const c = at(pos);
+        uint64_t in_next[kRegexWords] = {0, 0};
+        int nn = 0;
+        bool cut = false;
+        for (int t = 0; t < ncur && !cut; ++t)
+        {
+            int const q = cur[t];
+            if (!((re.B[c][q >> 6] >> (q & 63)) & 1))
+                continue;
+            for (int j = re.follow_off[q]; j < re.follow_off[q + 1]; ++j)
+            {
+                uint8_t const item = re.follow_list[j];
+                if (item == kAccept)
+                {
+                    if (!re.anchor_end || pos + 1 == L)
+                    {
+                        best = pos + 1;
+                        cut = true;
+                        break;
+                    }
+                    continue;
+                }
+                if (!((in_next[item >> 6] >> (item & 63)) & 1))
+                {
+                    in_next[item >> 6] |= 1ULL << (item & 63);
+                    nxt[nn++] = item;
+                }
+            }
+        }
+        for (int i = 0; i < nn; ++i)
+            cur[i] = nxt[i];
+        ncur = nn;
+    }
+    return best;
+}
+
+// One thread per record of the candidate bins; returns at once unless phase 1 flagged the record.
+template <int W, int DIR>
+__global__ void __launch_bounds__(128) regex_scan_phase2(resolve_params p)
+{
+    regex_dev const & re = *p.re;
+    for (uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < p.n_cand_records;
+         i += static_cast<uint64_t>(gridDim.x) * blockDim.x)
+    {
+        // which candidate bin does the i-th candidate record belong to
+        uint32_t lo = 0, hi = p.n_cand;
+        while (hi - lo > 1)
+        {
+            uint32_t mid = (lo + hi) >> 1;
+            if (p.cand_rec_prefix[mid] <= i)
+                lo = mid;
+            else
+                hi = mid;
+        }
+        uint64_t const r = p.bin_rec_begin[p.cand_bins[lo]] + (i - p.cand_rec_prefix[lo]);
+        if (!p.rec_flags[r])
+            continue;
+        uint64_t const rb = p.rec_offsets[r], re_off = p.rec_offsets[r + 1];
+        int64_t const L = static_cast<int64_t>(re_off - rb);
+        auto at = [&](int64_t pos) -> uint8_t
+        { return DIR > 0 ? p.text[rb + pos] : p.text[re_off - 1 - pos]; };
+        auto chunk_of = [&](int64_t pos) -> uint64_t
+        { return (DIR > 0 ? rb + pos : re_off - 1 - pos) / kChunkBytes; };
+
+        int64_t s = 0;
+        while (s < L)
+        {
+            uint64_t const ch = chunk_of(s);
+            if (!re.anchor_begin && !((p.chunk_flags[ch >> 5] >> (ch & 31)) & 1))
+            {
+                // no match starts anywhere in this chunk: jump to the first position of the next one
+                if constexpr (DIR > 0)
+                    s = static_cast<int64_t>((ch + 1) * kChunkBytes - rb);
+                else
+                    s = static_cast<int64_t>(re_off) - static_cast<int64_t>(ch * kChunkBytes); // ch == 0 ⇒ s >= L, loop ends
+                continue;
+            }
+            int64_t e = re.posix_longest ? match_longest<W>(re, at, s, L) : match_first(re, at, s, L);
+            if (e > s)
+            {
+                unsigned long long idx = atomicAdd(p.hit_count, 1ULL);
+                if (idx < p.cap)
+                {
+                    p.hit_keys[idx] = (r << 32) | static_cast<uint64_t>(s);
+                    p.hit_ends[idx] = static_cast<uint32_t>(e);
+                }
+                s = e; // FindAndConsume: the next search starts where this match ended
+            }
+            else
+            {
+                if (re.anchor_begin)
+                    break; // '^' can only match at the resume point
+                ++s;
+            }
+        }
+    }
+}
+
+} // namespace trx
