@@ -746,3 +746,75 @@ int64_t ref_re2_find_all(char const * regex, int posix_longest, char const * tex
 }
 
 } // extern "C"
+
+extern "C"
+{
+
+// Wraps caller-provided HIBF tables (e.g. a synthetic HIBF built on the GPU) in the reference's own
+// seqan::hibf::hierarchical_interleaved_bloom_filter so that its membership_agent can be timed /
+// compared on exactly the same structure.  All members touched are public in hibf
+// (hierarchical_interleaved_bloom_filter.hpp:209-238).
+void * ref_hibf_from_tables(uint64_t n_ibfs, uint64_t n_user_bins, uint64_t const * bins, uint64_t const * bin_size,
+                            uint64_t const * hash_funs, uint64_t const * const * words,
+                            uint64_t const * const * next_ibf, uint64_t const * const * user_bin,
+                            uint64_t const * table_len)
+{
+    try
+    {
+        auto * p = new ref_hibf{};
+        p->user_bins = n_user_bins;
+        auto & h = p->hibf;
+        for (uint64_t i = 0; i < n_ibfs; ++i)
+        {
+            h.ibf_vector.emplace_back(seqan::hibf::bin_count{bins[i]}, seqan::hibf::bin_size{bin_size[i]},
+                                      seqan::hibf::hash_function_count{hash_funs[i]});
+            auto & ibf = h.ibf_vector.back();
+            std::memcpy(const_cast<uint64_t *>(ibf.data()), words[i], ((ibf.bit_size() + 63) / 64) * sizeof(uint64_t));
+            h.next_ibf_id.emplace_back(next_ibf[i], next_ibf[i] + table_len[i]);
+            h.ibf_bin_to_user_bin_id.emplace_back(user_bin[i], user_bin[i] + table_len[i]);
+            h.prev_ibf_id.push_back({0, 0});
+        }
+        return p;
+    }
+    catch (std::exception const & e)
+    {
+        g_err = e.what();
+        return nullptr;
+    }
+}
+
+// The verify inner loop of src/query.cpp:194-237 over records held in memory (no gz / kseq), OpenMP over
+// records like the reference's `omp parallel for` over bins.  Returns the total number of matches.
+int64_t ref_re2_scan_records(char const * regex, int posix_longest, char const * text, uint64_t const * rec_offsets,
+                             uint64_t n_records, int threads)
+{
+    std::string wrapped = std::string("(") + regex + ")";
+    std::unique_ptr<re2::RE2> re;
+    if (posix_longest)
+        re = std::make_unique<re2::RE2>(wrapped, re2::RE2::POSIX);
+    else
+        re = std::make_unique<re2::RE2>(wrapped);
+    if (!re->ok())
+    {
+        g_err = re->error();
+        return -1;
+    }
+    int64_t total = 0;
+    if (threads < 1)
+        threads = 1;
+#pragma omp parallel for schedule(dynamic, 64) num_threads(threads) reduction(+ : total)
+    for (int64_t r = 0; r < static_cast<int64_t>(n_records); ++r)
+    {
+        re2::StringPiece content(text + rec_offsets[r], rec_offsets[r + 1] - rec_offsets[r]);
+        re2::StringPiece match;
+        while (RE2::FindAndConsume(&content, *re, &match))
+        {
+            ++total;
+            if (match.size() == 0)
+                break;
+        }
+    }
+    return total;
+}
+
+} // extern "C"

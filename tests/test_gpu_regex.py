@@ -1,0 +1,156 @@
+"""GPU parity tests for rows a9/a10: the verify scan against RE2 golden vectors (generated from the
+compiled reference), the Python restatement, and — where oracle/_ref travelled — RE2 itself."""
+import json
+import os
+import random
+
+import numpy as np
+import pytest
+
+import tetrex_b200 as t
+from oracle import bindings as ob
+
+pytestmark = pytest.mark.gpu
+
+COMP = bytes.maketrans(b"ACGTUMRWSYKVHDBNacgtumrwsykvhdbn", b"TGCAAKYWSRMBDHVNtgcaakywsrmbdhvn")
+
+
+def build_text(ctx, seqs, rec_bin, n_bins):
+    offs = np.zeros(len(seqs) + 1, dtype=np.uint64)
+    offs[1:] = np.cumsum([len(s) for s in seqs])
+    return t.Text(ctx, b"".join(seqs), offs, np.asarray(rec_bin, dtype=np.uint32), n_bins)
+
+
+def expected_hits(seqs, rec_bin, pattern, posix, finder, cand=None, transform=None):
+    out = []
+    for r, s in enumerate(seqs):
+        if cand is not None and rec_bin[r] not in cand:
+            continue
+        text = transform(s) if transform else s
+        for a, b in finder(pattern, posix, text):
+            out.append((rec_bin[r], r, a, b))
+    return np.array(out, dtype=np.uint32).reshape(-1, 4)
+
+
+def test_regex_golden_vectors(ctx, golden_dir):
+    """Every (pattern, text) case of tests/golden/regex.json, grouped by pattern into one multi-record text."""
+    cases = json.load(open(os.path.join(golden_dir, "regex.json")))
+    groups = {}
+    for c in cases:
+        groups.setdefault((c["pattern"], c["posix"]), []).append(c)
+    assert len(groups) >= 50
+    for (pat, posix), cs in groups.items():
+        seqs = [c["text"].encode() for c in cs]
+        if sum(len(s) for s in seqs) == 0:
+            continue
+        rec_bin = list(range(len(seqs)))
+        txt = build_text(ctx, seqs, rec_bin, len(seqs))
+        got = txt.scan(t.Regex(pat, posix))
+        want = [(rec_bin[r], r, a, b) for r, c in enumerate(cs) for a, b in c["matches"]]
+        assert got.tolist() == [list(x) for x in want], (pat, posix)
+        txt.close()
+
+
+PATTERNS_AA = ["LMA(E|Q)GLYN", "[ILV][ILV]K", "G.{2,4}K", "N[ST][^P]", "(AB|A)BC", "K+R?E", "C.{0,3}C", "W(A|C|D){1,3}W",
+               "^M", "K$", "(GA)+G", "A{3,5}", "[DE]{2}.[KR]{2}", "(A|AA)(A|AA)C"]
+PATTERNS_NA = ["A(C+|G+)T", "ACGT", "(A|AC)(CG|G)", "T+A", "G.{1,3}C", "(AC)*G", "CA?T", "[AG]C[CT]", "A{2,4}C", "(TA|T)A+",
+               "AC|ACG|ACGT", "^ACG", "TT$", "GATTACA", "(G|GG|GGG)T", "C(A|AT|ATG)G"]
+
+
+@pytest.mark.parametrize("posix,patterns,alpha", [(True, PATTERNS_AA, b"ACDEGKLMNPQRSTWILVY"), (False, PATTERNS_NA, b"ACGT"),
+                                                  (True, PATTERNS_NA, b"ACGT"), (False, PATTERNS_AA, b"ABCDEKLMQGWR")])
+def test_regex_random_multi_bin(ctx, posix, patterns, alpha):
+    """Ragged records (empty, 1 byte, chunk-straddling, multi-tile) in several bins, candidate subsets."""
+    rng = random.Random(sum(alpha) + len(patterns))
+    lengths = [0, 1, 2, 127, 128, 129, 255, 256, 257, 1000, 0, 5000, 40000, 33, 70000, 3, 0, 640, 128 * 256, 128 * 256 + 1, 90]
+    seqs = [bytes(rng.choice(alpha) for _ in range(L)) for L in lengths]
+    n_bins = 7
+    rec_bin = sorted(rng.randrange(n_bins) for _ in seqs)
+    txt = build_text(ctx, seqs, rec_bin, n_bins)
+    finder = ob.ref_find_all if ob.have_ref() else ob.find_all_python
+    for pat in patterns:
+        rx = t.Regex(pat, posix)
+        got, residues = txt.scan(rx, stats=True)
+        want = expected_hits(seqs, rec_bin, pat, posix, finder)
+        assert np.array_equal(got, want), (pat, posix, len(got), len(want))
+        assert residues == sum(lengths)
+        cand_bins = {1, 4, 6}
+        cand = np.zeros(1, dtype=np.uint64)
+        for b in cand_bins:
+            cand[0] |= np.uint64(1) << np.uint64(b)
+        got = txt.scan(rx, candidate_bins=cand)
+        assert np.array_equal(got, expected_hits(seqs, rec_bin, pat, posix, finder, cand=cand_bins)), (pat, "subset")
+    txt.close()
+
+
+def test_regex_staging_variants_agree(ctx, monkeypatch):
+    """The TMA-staged kernel and the direct-load variant (TRX_REGEX_STAGING=ldg) are the same algorithm."""
+    rng = random.Random(3)
+    seqs = [bytes(rng.choice(b"ACGT") for _ in range(L)) for L in [100000, 5, 300000, 77777]]
+    txt = build_text(ctx, seqs, [0, 0, 1, 2], 3)
+    rx = t.Regex("GATTA(C|G)A", False)
+    a = txt.scan(rx)
+    monkeypatch.setenv("TRX_REGEX_STAGING", "ldg")
+    b = txt.scan(rx)
+    assert len(a) > 0 and np.array_equal(a, b)
+    txt.close()
+
+
+def test_reverse_strand(ctx):
+    """reverse_verify_fasta_hit (src/query.cpp:167-191): the record is complemented through comp_tab and reversed."""
+    rng = random.Random(9)
+    seqs = [bytes(rng.choice(b"ACGTN") for _ in range(L)) for L in [16, 16, 500, 0, 1, 30000, 129]]
+    rec_bin = [0, 1, 1, 2, 2, 3, 4]
+    txt = build_text(ctx, seqs, rec_bin, 5)
+    finder = ob.ref_find_all if ob.have_ref() else ob.find_all_python
+    revcomp = lambda s: s.translate(COMP)[::-1]
+    for pat in ["A(C+|G+)T", "ACG", "T+A", "(A|AC)(CG|G)", "G.{1,3}C"]:
+        got = txt.scan(t.Regex(pat, False), reverse_strand=True)
+        want = expected_hits(seqs, rec_bin, pat, False, finder, transform=revcomp)
+        assert np.array_equal(got, want), pat
+    txt.close()
+
+
+def test_reduced_alphabet_map(ctx):
+    """verify_reduced_fasta_hit (src/query.cpp:240-315): text bytes go through redmap_ before matching."""
+    rng = random.Random(10)
+    aa = b"ACDEFGHIKLMNPQRSTVWY"
+    seqs = [bytes(rng.choice(aa) for _ in range(L)) for L in [50, 400, 3000, 129]]
+    rec_bin = [0, 0, 1, 2]
+    txt = build_text(ctx, seqs, rec_bin, 3)
+    finder = ob.ref_find_all if ob.have_ref() else ob.find_all_python
+    for red in (t.RED_MURPHY, t.RED_LI):
+        _, redmap = t.peptide_maps(red)
+        table = bytes(redmap.tolist())
+        for pat in ["IIK", "B[KS]B", "A(B|F)G", "S{2,3}P"]:
+            got = txt.scan(t.Regex(pat, True), map256=redmap)
+            want = expected_hits(seqs, rec_bin, pat, True, finder, transform=lambda s: s.translate(table))
+            assert np.array_equal(got, want), (red, pat)
+    txt.close()
+
+
+def test_many_hits_capacity(ctx):
+    seqs = [b"AC" * 5000]
+    txt = build_text(ctx, seqs, [0], 1)
+    rx = t.Regex("AC", False)
+    got = txt.scan(rx, cap=6000)
+    assert len(got) == 5000 and got[:, 2].tolist() == list(range(0, 10000, 2))
+    with pytest.raises(t.TetrexError) as e:
+        txt.scan(rx, cap=100)
+    assert e.value.code == -5
+    txt.close()
+
+
+def test_128_positions_two_word_state(ctx):
+    rng = random.Random(4)
+    motif = bytes(rng.choice(b"ACDEFGHIK") for _ in range(100))
+    seqs = [bytes(rng.choice(b"ACDEFGHIK") for _ in range(3000)) + motif + b"KK" + motif[:50], motif * 3]
+    txt = build_text(ctx, seqs, [0, 1], 2)
+    pat = motif.decode()
+    rx = t.Regex(pat, True)
+    assert rx.positions == 100
+    finder = ob.ref_find_all if ob.have_ref() else ob.find_all_python
+    assert np.array_equal(txt.scan(rx), expected_hits(seqs, [0, 1], pat, True, finder))
+    pat2 = motif[:70].decode() + ".{3,9}" + motif[79:90].decode()
+    assert np.array_equal(txt.scan(t.Regex(pat2, True)), expected_hits(seqs, [0, 1], pat2, True, finder))
+    txt.close()

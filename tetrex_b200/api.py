@@ -1,0 +1,317 @@
+"""Thin object layer over the C ABI — numpy in, numpy out.  Names follow the reference's domain
+(IBF, HIBF, bins, k-mers, paths, records).  Every method is one C-ABI call; nothing is computed in
+Python and nothing falls back to the CPU.
+
+Host-buffer methods take numpy arrays; ``*_dev`` methods take raw device pointers (ints), e.g.
+``tensor.data_ptr()`` of a torch CUDA tensor, and only enqueue work on the context's stream.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from ._abi import TrxHibfDesc, TrxHit, check, lib, u64p
+
+MOL_NA, MOL_AA = 0, 1
+RED_BASE, RED_MURPHY, RED_LI = 0, 1, 2
+
+
+def _np(a, dtype):
+    return np.ascontiguousarray(a, dtype=dtype)
+
+
+def _ptr(a):
+    return a.ctypes.data if a is not None else None
+
+
+class Context:
+    """One CUDA device + one stream (trx_ctx_t).  stream = raw cudaStream_t or None."""
+
+    def __init__(self, device: int = 0, stream: int | None = None):
+        self._h = C.c_void_p()
+        check(lib().trx_ctx_create(device, stream, C.byref(self._h)))
+        self.device = device
+
+    def close(self):
+        if self._h:
+            lib().trx_ctx_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def sync(self):
+        check(lib().trx_ctx_sync(self._h))
+
+    @property
+    def launches(self) -> int:
+        return lib().trx_ctx_launches(self._h)
+
+    def timer_start(self):
+        check(lib().trx_timer_start(self._h))
+
+    def timer_stop_ms(self) -> float:
+        ms = C.c_float()
+        check(lib().trx_timer_stop_ms(self._h, C.byref(ms)))
+        return ms.value
+
+    def decompose_records(self, molecule, k, reduction, residues: bytes | np.ndarray, rec_offsets):
+        """decompose_record for every record; returns (values, emit_offsets)."""
+        res = np.frombuffer(residues, dtype=np.uint8) if isinstance(residues, (bytes, bytearray)) else _np(residues, np.uint8)
+        offs = _np(rec_offsets, np.uint64)
+        n = len(offs) - 1
+        cap = int(sum(lib().trx_emit_count(molecule, k, int(offs[i + 1] - offs[i])) for i in range(n)))
+        out = np.zeros(max(cap, 1), dtype=np.uint64)
+        out_offs = np.zeros(n + 1, dtype=np.uint64)
+        check(lib().trx_decompose_records(self._h, molecule, k, reduction, _ptr(res), _ptr(offs), n, _ptr(out), cap,
+                                          _ptr(out_offs)))
+        return out[:cap], out_offs
+
+
+def emit_count(molecule, k, length) -> int:
+    return lib().trx_emit_count(molecule, k, length)
+
+
+def peptide_maps(reduction):
+    a = np.zeros(256, dtype=np.uint8)
+    r = np.zeros(256, dtype=np.uint8)
+    lib().trx_peptide_maps(reduction, a.ctypes.data_as(C.POINTER(C.c_uint8)), r.ctypes.data_as(C.POINTER(C.c_uint8)))
+    return a, r
+
+
+def compute_bitcount(n, fpr) -> int:
+    return lib().trx_compute_bitcount(n, fpr)
+
+
+class IBF:
+    """Flat interleaved Bloom filter resident in HBM (seqan::hibf::interleaved_bloom_filter)."""
+
+    def __init__(self, ctx: Context, bins: int, bin_size: int, hash_funs: int, shard_index: int = 0, shard_count: int = 1):
+        self.ctx = ctx
+        self._h = C.c_void_p()
+        check(lib().trx_ibf_create(ctx._h, bins, bin_size, hash_funs, shard_index, shard_count, C.byref(self._h)))
+        g = np.zeros(10, dtype=np.uint64)
+        check(lib().trx_ibf_geometry(self._h, g.ctypes.data_as(u64p)))
+        (self.bins, self.technical_bins, self.bin_size, self.hash_shift, self.bin_words, self.hash_funs, self.n_words,
+         self.shard_word_begin, self.shard_words, self.shard_n_words) = [int(x) for x in g]
+
+    def close(self):
+        if self._h:
+            lib().trx_ibf_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def device_words(self) -> int:
+        return lib().trx_ibf_device_words(self._h)
+
+    def clear(self):
+        check(lib().trx_ibf_clear(self._h))
+
+    def upload(self, words):
+        w = _np(words, np.uint64)
+        check(lib().trx_ibf_upload(self._h, _ptr(w), len(w)))
+
+    def download(self) -> np.ndarray:
+        w = np.zeros(self.n_words, dtype=np.uint64)
+        check(lib().trx_ibf_download(self._h, _ptr(w), len(w)))
+        return w
+
+    def emplace_values(self, values, bin_ids):
+        v = _np(values, np.uint64)
+        b = _np(bin_ids, np.uint32)
+        check(lib().trx_emplace_values(self._h, _ptr(v), _ptr(b), len(v)))
+
+    def emplace_values_dev(self, d_values: int, d_bins: int, n: int):
+        check(lib().trx_emplace_values_dev(self._h, d_values, d_bins, n))
+
+    def emplace_records(self, molecule, k, reduction, residues, rec_offsets, rec_bin):
+        res = np.frombuffer(residues, dtype=np.uint8) if isinstance(residues, (bytes, bytearray)) else _np(residues, np.uint8)
+        offs = _np(rec_offsets, np.uint64)
+        rb = _np(rec_bin, np.uint32)
+        check(lib().trx_emplace_records(self._h, molecule, k, reduction, _ptr(res), _ptr(offs), _ptr(rb), len(rb)))
+
+    def emplace_records_dev(self, molecule, k, reduction, d_residues: int, n_residues: int, d_rec_offsets: int,
+                            d_rec_bin: int, n_records: int):
+        check(lib().trx_emplace_records_dev(self._h, molecule, k, reduction, d_residues, n_residues, d_rec_offsets,
+                                            d_rec_bin, n_records))
+
+    def bulk_contains(self, kmers, out: np.ndarray | None = None) -> np.ndarray:
+        v = _np(kmers, np.uint64)
+        if out is None:
+            out = np.zeros((len(v), self.shard_words), dtype=np.uint64)
+        check(lib().trx_bulk_contains(self._h, _ptr(v), len(v), _ptr(out)))
+        return out
+
+    def bulk_contains_dev(self, d_kmers: int, n: int, d_out: int):
+        check(lib().trx_bulk_contains_dev(self._h, d_kmers, n, d_out))
+
+
+class Paths:
+    """Pool of path bitvectors (CollectorsItem::path_) in HBM."""
+
+    def __init__(self, ctx: Context, words_per_slot: int, capacity: int):
+        self.ctx = ctx
+        self.words_per_slot, self.capacity = words_per_slot, capacity
+        self._h = C.c_void_p()
+        check(lib().trx_paths_create(ctx._h, words_per_slot, capacity, C.byref(self._h)))
+
+    def close(self):
+        if self._h:
+            lib().trx_paths_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def fill(self, first, n, bins):
+        check(lib().trx_paths_fill(self._h, first, n, bins))
+
+    def step(self, ibf: IBF, kmers, slots) -> np.ndarray:
+        v = _np(kmers, np.uint64)
+        s = _np(slots, np.uint32)
+        alive = np.zeros(len(v), dtype=np.uint8)
+        check(lib().trx_paths_step(ibf._h, self._h, _ptr(v), _ptr(s), len(v), _ptr(alive)))
+        return alive
+
+    def and_hits(self, d_hits: int, hit_index, slots) -> np.ndarray:
+        hi = _np(hit_index, np.uint32)
+        s = _np(slots, np.uint32)
+        alive = np.zeros(len(s), dtype=np.uint8)
+        check(lib().trx_paths_and_hits(self._h, d_hits, _ptr(hi), _ptr(s), len(s), _ptr(alive)))
+        return alive
+
+    def or_(self, dst, src):
+        d = _np(dst, np.uint32)
+        s = _np(src, np.uint32)
+        check(lib().trx_paths_or(self._h, _ptr(d), _ptr(s), len(d)))
+
+    def read(self, first, n) -> np.ndarray:
+        out = np.zeros((n, self.words_per_slot), dtype=np.uint64)
+        check(lib().trx_paths_read(self._h, first, n, _ptr(out)))
+        return out
+
+
+class HIBF:
+    """Hierarchical IBF resident in HBM, built from flattened tables (oracle.bindings.HIBFTables-like)."""
+
+    def __init__(self, ctx: Context, n_user_bins, bins, bin_size, hash_funs, words, next_ibf, user_bin):
+        self.ctx = ctx
+        n = len(words)
+        self._keep = dict(bins=_np(bins, np.uint64), bin_size=_np(bin_size, np.uint64), hash_funs=_np(hash_funs, np.uint64),
+                          words=[_np(w, np.uint64) for w in words], next_ibf=[_np(w, np.uint64) for w in next_ibf],
+                          user_bin=[_np(w, np.uint64) for w in user_bin])
+        k = self._keep
+        table_len = np.array([len(t) for t in k["user_bin"]], dtype=np.uint64)
+        mk = lambda arrs: (u64p * n)(*[a.ctypes.data_as(u64p) for a in arrs])
+        desc = TrxHibfDesc(n, int(n_user_bins), k["bins"].ctypes.data_as(u64p), k["bin_size"].ctypes.data_as(u64p),
+                           k["hash_funs"].ctypes.data_as(u64p), mk(k["words"]), mk(k["next_ibf"]), mk(k["user_bin"]),
+                           table_len.ctypes.data_as(u64p))
+        self._h = C.c_void_p()
+        check(lib().trx_hibf_upload(ctx._h, C.byref(desc), C.byref(self._h)))
+        self.n_user_bins = int(n_user_bins)
+        self.out_words = int(lib().trx_hibf_user_bin_words(self._h))
+        self._keep = None  # the device copy is complete; host arrays are not referenced any more
+
+    @classmethod
+    def from_tables(cls, ctx, t):
+        return cls(ctx, t.n_user_bins, t.bins, t.bin_size, t.hash_funs, t.words, t.next_ibf, t.user_bin)
+
+    def close(self):
+        if self._h:
+            lib().trx_hibf_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def membership(self, kmers, out: np.ndarray | None = None, stats: bool = False):
+        v = _np(kmers, np.uint64)
+        if out is None:
+            out = np.zeros((len(v), self.out_words), dtype=np.uint64)
+        st = np.zeros(2, dtype=np.uint64)
+        check(lib().trx_hibf_membership(self._h, _ptr(v), len(v), _ptr(out), st.ctypes.data_as(u64p)))
+        return (out, st) if stats else out
+
+    def membership_dev(self, d_kmers: int, n: int, d_out: int):
+        st = np.zeros(2, dtype=np.uint64)
+        check(lib().trx_hibf_membership_dev(self._h, d_kmers, n, d_out, st.ctypes.data_as(u64p)))
+        return st
+
+
+class Regex:
+    def __init__(self, pattern: str, posix_longest: bool):
+        self._h = C.c_void_p()
+        check(lib().trx_regex_compile(pattern.encode("latin-1"), int(posix_longest), C.byref(self._h)))
+        self.pattern = pattern
+        self.positions = lib().trx_regex_positions(self._h)
+
+    def close(self):
+        if self._h:
+            lib().trx_regex_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Text:
+    """Residue store in HBM: records grouped by ascending bin."""
+
+    def __init__(self, ctx: Context, residues, rec_offsets, rec_bin, n_bins: int):
+        self.ctx = ctx
+        res = np.frombuffer(residues, dtype=np.uint8) if isinstance(residues, (bytes, bytearray)) else _np(residues, np.uint8)
+        self.rec_offsets = _np(rec_offsets, np.uint64)
+        self.rec_bin = _np(rec_bin, np.uint32)
+        self.n_bins = n_bins
+        self._h = C.c_void_p()
+        check(lib().trx_text_upload(ctx._h, _ptr(res), _ptr(self.rec_offsets), _ptr(self.rec_bin), len(self.rec_bin),
+                                    n_bins, C.byref(self._h)))
+
+    def close(self):
+        if self._h:
+            lib().trx_text_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def scan(self, regex: Regex, candidate_bins=None, reverse_strand=False, map256=None, cap=1 << 20, stats=False):
+        """Returns an (n,4) uint32 array of (bin, record, start, end) in reference print order."""
+        words = (self.n_bins + 63) // 64
+        if candidate_bins is None:
+            cand = np.zeros(words, dtype=np.uint64)
+            for b in range(self.n_bins):
+                cand[b >> 6] |= np.uint64(1) << np.uint64(b & 63)
+        else:
+            cand = _np(candidate_bins, np.uint64)
+            assert len(cand) == words
+        m = _np(map256, np.uint8) if map256 is not None else None
+        hits = (TrxHit * cap)()
+        n = C.c_uint64()
+        st = np.zeros(1, dtype=np.uint64)
+        check(lib().trx_regex_scan(self._h, regex._h, _ptr(cand), int(reverse_strand), _ptr(m) if m is not None else None,
+                                   C.addressof(hits), cap, C.byref(n), st.ctypes.data_as(u64p)))
+        arr = np.frombuffer(hits, dtype=np.uint32, count=4 * n.value).reshape(-1, 4).copy()
+        return (arr, int(st[0])) if stats else arr

@@ -288,8 +288,8 @@ int trx_emplace_records_dev(trx_ibf_t * f, int molecule, uint32_t k, int reducti
     unsigned grid = grid_for(n_runs, 256, c->sm_count, 8);
     if (molecule == TRX_MOL_NA)
     {
-        emplace_records_kernel<TRX_MOL_NA><<<grid, 256, 0, c->stream>>>(geom_of(f), d_residues, n_residues,
-                                                                        d_rec_offsets, d_rec_bin, n_records, k, nullptr);
+        emplace_dna_kernel<<<grid, 256, 0, c->stream>>>(geom_of(f), d_residues, n_residues, d_rec_offsets, d_rec_bin,
+                                                        n_records, k);
     }
     else
     {

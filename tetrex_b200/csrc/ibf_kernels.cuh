@@ -193,13 +193,70 @@ __device__ __forceinline__ uint64_t dna_code(uint8_t c)
     return (c >> 1) & 3u; // nucleotide_decomposer.h:83-89
 }
 
-// reverse complement of a packed 2-bit k-mer: complement = code^2, reverse the 2-bit groups.
+// NucleotideDecomposer::revComplement (nucleotide_decomposer.h:44-79): complement = code^2, reverse the
+// 2-bit groups.  Quirk kept for bit-exactness: the reference shifts a SIGNED 64-bit vector lane right by
+// 4 (`kmer2 >>= 4`), so when bit 63 is set (k = 32, first base T/G) the top byte's shuffle index has bit 7
+// set, pshufb yields 0 and the two leading bases drop out: the lowest nibble of the result is 0.
 __device__ __forceinline__ uint64_t dna_revcomp(uint64_t fwd, uint32_t k)
 {
     uint64_t x = fwd ^ 0xAAAAAAAAAAAAAAAAULL;
     x = __brevll(x);                                                            // reverses single bits …
     x = ((x & 0x5555555555555555ULL) << 1) | ((x >> 1) & 0x5555555555555555ULL); // … so swap each pair back
-    return x >> (64 - 2 * k);
+    x >>= (64 - 2 * k);
+    if (fwd >> 63)
+        x &= ~0xFULL;
+    return x;
+}
+
+// rollover_nuc_hash (nucleotide_decomposer.h:92-101): `(fb^0b10) << left_shift_` is evaluated on an int.
+// For k >= 16 (left_shift_ >= 30) that overflows; as compiled for x86 the count is taken mod 32 and the
+// int is sign-extended when ORed into the 64-bit reverse store.  The reference's INDEX side therefore
+// does not hold true reverse complements for k >= 16; the bits it sets are what we must reproduce.
+__device__ __forceinline__ uint64_t dna_comp_bits(uint64_t f, uint32_t left_shift)
+{
+    return static_cast<uint64_t>(static_cast<int64_t>(static_cast<int32_t>(static_cast<uint32_t>(f ^ 2) << (left_shift & 31))));
+}
+
+struct dna_state
+{
+    uint64_t fwd, rev;
+    __device__ __forceinline__ void roll(uint8_t c, uint64_t mask, uint32_t left_shift)
+    {
+        uint64_t const f = dna_code(c);
+        fwd = ((fwd << 2) & mask) | f;
+        rev = ((rev >> 2) & mask) | dna_comp_bits(f, left_shift);
+    }
+    __device__ __forceinline__ uint64_t canonical() const
+    {
+        return fwd <= rev ? fwd : rev;
+    }
+};
+
+// how many rolled symbols determine the (fwd, rev) stores completely: every contribution to `rev` enters at
+// bit <= 63 and moves down 2 bits per step, so 33 steps flush anything older; for k <= 15 the stores are the
+// exact k-mer and its reverse complement after k steps.
+__device__ __forceinline__ uint32_t dna_warmup(uint32_t k)
+{
+    return k >= 16 ? 33u : k;
+}
+
+// State of decompose_record (nucleotide_decomposer.h:103-111) BEFORE rolling rec[t] in, i.e. after the
+// initial k-mer and the symbols rec[0..t): replayed from at most dna_warmup(k) symbols back.
+__device__ __forceinline__ dna_state dna_state_before(uint8_t const * __restrict__ rec, uint64_t t, uint32_t k,
+                                                       uint64_t mask, uint32_t left_shift)
+{
+    dna_state s{0, 0};
+    uint32_t const warm = dna_warmup(k);
+    uint64_t t0 = t > warm ? t - warm : 0;
+    if (t0 == 0)
+    {
+        for (uint32_t i = 0; i < k; ++i)
+            s.fwd = (s.fwd << 2) | dna_code(__ldg(rec + i));
+        s.rev = dna_revcomp(s.fwd, k);
+    }
+    for (uint64_t j = t0; j < t; ++j)
+        s.roll(__ldg(rec + j), mask, left_shift);
+    return s;
 }
 
 struct emplace_sink
@@ -357,6 +414,73 @@ __global__ void __launch_bounds__(256)
     }
 }
 
+// DNA flavour.  One emit per rolled symbol (plus one per record for the initial k-mer), so a thread owns
+// the STEPS whose byte lies in its 16-byte run: it rebuilds the rolling stores from the preceding
+// dna_warmup(k) symbols (or from the record start) and then rolls through its run.  That reproduces the
+// reference's emits exactly, including the wrap-around k-mers of nucleotide_decomposer.h:110 (the whole
+// record is rolled in after the first k-mer) and the k >= 16 reverse-store quirk.
+__global__ void __launch_bounds__(256)
+    emplace_dna_kernel(ibf_geom g, uint8_t const * __restrict__ text, uint64_t n_residues,
+                       uint64_t const * __restrict__ rec_offsets, uint32_t const * __restrict__ rec_bin,
+                       uint64_t n_records, uint32_t k)
+{
+    uint64_t const mask = (2 * k >= 64) ? ~0ULL : ((1ULL << (2 * k)) - 1);
+    uint32_t const left_shift = 2 * k - 2;
+    uint64_t const n_runs = (n_residues + kRun - 1) / kRun;
+    for (uint64_t run = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; run < n_runs;
+         run += static_cast<uint64_t>(gridDim.x) * blockDim.x)
+    {
+        uint64_t const p0 = run * kRun;
+        uint64_t const run_end = min(p0 + kRun, n_residues);
+        uint64_t lo = 0, hi = n_records;
+        while (hi - lo > 1)
+        {
+            uint64_t mid = (lo + hi) >> 1;
+            if (__ldg(rec_offsets + mid) <= p0)
+                lo = mid;
+            else
+                hi = mid;
+        }
+        uint64_t r = lo;
+        uint64_t rec_begin = __ldg(rec_offsets + r);
+        uint64_t rec_end = __ldg(rec_offsets + r + 1);
+        emplace_sink sink{g, 0, 0, false};
+        sink.set_bin(__ldg(rec_bin + r));
+        bool usable = rec_end - rec_begin >= k; // shorter records are skipped (include/index_ibf.h:114-118)
+        dna_state s{0, 0};
+        if (usable)
+        {
+            s = dna_state_before(text + rec_begin, p0 - rec_begin, k, mask, left_shift);
+            if (p0 == rec_begin)
+                sink(s.canonical()); // the initial k-mer
+        }
+#pragma unroll 1
+        for (uint64_t p = p0; p < run_end; ++p)
+        {
+            if (p >= rec_end)
+            {
+                do
+                {
+                    ++r;
+                    rec_begin = rec_end;
+                    rec_end = __ldg(rec_offsets + r + 1);
+                } while (rec_end <= p);
+                sink.set_bin(__ldg(rec_bin + r));
+                usable = rec_end - rec_begin >= k;
+                if (usable)
+                {
+                    s = dna_state_before(text + rec_begin, 0, k, mask, left_shift);
+                    sink(s.canonical());
+                }
+            }
+            if (!usable)
+                continue;
+            s.roll(__ldg(text + p), mask, left_shift);
+            sink(s.canonical());
+        }
+    }
+}
+
 // Ordered emission (decompose_record's exact call sequence) for hand-off to HIBF construction and for
 // parity tests of rows a1/a2.  One thread per emitted value; packs its k symbols directly.
 template <int MOL>
@@ -385,15 +509,13 @@ __global__ void __launch_bounds__(256)
         uint64_t v = 0;
         if constexpr (MOL == TRX_MOL_NA)
         {
-            // virtual string V = rec[0..k) ++ rec[0..L); emit j = window V[j..j+k)
-            for (uint32_t s = 0; s < k; ++s)
-            {
-                uint64_t idx = j + s;
-                uint8_t c = rec[idx < k ? idx : idx - k];
-                v = (v << 2) | dna_code(c);
-            }
-            uint64_t rc = dna_revcomp(v, k);
-            out[e] = v <= rc ? v : rc;
+            // emit 0 = initial k-mer; emit j >= 1 = state after rolling rec[j-1]
+            uint64_t const mask = (2 * k >= 64) ? ~0ULL : ((1ULL << (2 * k)) - 1);
+            dna_state st = dna_state_before(rec, j == 0 ? 0 : j - 1, k, mask, 2 * k - 2);
+            if (j > 0)
+                st.roll(rec[j - 1], mask, 2 * k - 2);
+            out[e] = st.canonical();
+            (void)v;
         }
         else
         {

@@ -1,0 +1,394 @@
+// regex_scan.cu — C ABI for the HBM-resident residue store and the K4 verify scan.
+// Reference: iter_disk_search + verify_* (include/query.h:97-188, src/query.cpp:167-315).
+#include <algorithm>
+#include <cstdlib>
+
+#include <cub/device/device_radix_sort.cuh>
+
+#include "regex_kernels.cuh"
+
+struct trx_text
+{
+    trx_ctx * ctx{nullptr};
+    uint64_t n_text{}, n_text_padded{}, n_records{}, n_bins{};
+    uint8_t * d_text{nullptr};
+    uint64_t * d_rec_offsets{nullptr};
+    uint32_t * d_rec_bin{nullptr};
+    uint64_t * d_bin_rec_begin{nullptr};
+    uint32_t * d_chunk_flags{nullptr};
+    uint64_t n_chunk_flag_words{};
+    uint8_t * d_rec_flags{nullptr};
+    std::vector<uint64_t> h_rec_offsets;   // host copies: tile planning and hit formatting
+    std::vector<uint32_t> h_rec_bin;
+    std::vector<uint64_t> h_bin_rec_begin; // n_bins + 1
+    CUtensorMap tmap{};
+    bool has_tmap{false};
+    // per-scan scratch
+    trx::scratch d_cand, d_tiles, d_cand_bins, d_cand_prefix, d_regex, d_counter, d_keys, d_ends, d_keys2, d_ends2, d_sort_tmp;
+};
+
+using namespace trx;
+
+namespace
+{
+
+using encode_fn_t = CUresult (*)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, cuuint64_t const *,
+                                 cuuint64_t const *, cuuint32_t const *, cuuint32_t const *, CUtensorMapInterleave,
+                                 CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+// libcuda is reached through the runtime (no link-time dependency on the driver library)
+int make_tensor_map(trx_text * t)
+{
+    void * fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    TRX_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+    if (!fn || qres != cudaDriverEntryPointSuccess)
+        return set_error(TRX_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
+    auto encode = reinterpret_cast<encode_fn_t>(fn);
+    // the text as a 2-D byte tensor: [rows][128]; one TMA box = 256 rows × 128 B = one 32 KB tile
+    cuuint64_t dims[2] = {static_cast<cuuint64_t>(kChunkBytes), static_cast<cuuint64_t>(t->n_text_padded / kChunkBytes)};
+    cuuint64_t strides[1] = {static_cast<cuuint64_t>(kChunkBytes)};
+    cuuint32_t box[2] = {static_cast<cuuint32_t>(kChunkBytes), static_cast<cuuint32_t>(kScanThreads)};
+    cuuint32_t elem_strides[2] = {1, 1};
+    CUresult r = encode(&t->tmap, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, t->d_text, dims, strides, box, elem_strides,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS)
+        return set_error(TRX_ECUDA, "cuTensorMapEncodeTiled failed with CUresult %d", static_cast<int>(r));
+    t->has_tmap = true;
+    return TRX_OK;
+}
+
+} // namespace
+
+extern "C"
+{
+
+int trx_text_upload(trx_ctx_t * ctx, const uint8_t * residues, const uint64_t * rec_offsets, const uint32_t * rec_bin,
+                    uint64_t n_records, uint64_t n_bins, trx_text_t ** out)
+{
+    if (!ctx || !out || !rec_offsets || !rec_bin || n_records == 0 || n_bins == 0)
+        return set_error(TRX_EINVAL, "trx_text_upload: bad argument");
+    *out = nullptr;
+    if (rec_offsets[0] != 0)
+        return set_error(TRX_EINVAL, "rec_offsets[0] must be 0");
+    if (n_records >= (1ull << 32))
+        return set_error(TRX_EINVAL, "more than 2^32 records");
+    for (uint64_t i = 0; i < n_records; ++i)
+    {
+        if (rec_offsets[i + 1] < rec_offsets[i])
+            return set_error(TRX_EINVAL, "rec_offsets must be non-decreasing");
+        if (rec_offsets[i + 1] - rec_offsets[i] >= (1ull << 32))
+            return set_error(TRX_EINVAL, "record %llu longer than 2^32 bytes", (unsigned long long)i);
+        if (rec_bin[i] >= n_bins)
+            return set_error(TRX_ERANGE, "record %llu: bin %u >= %llu", (unsigned long long)i, rec_bin[i],
+                             (unsigned long long)n_bins);
+        if (i && rec_bin[i] < rec_bin[i - 1])
+            return set_error(TRX_EINVAL, "records must be grouped by ascending bin");
+    }
+    uint64_t const n_text = rec_offsets[n_records];
+    if (n_text && !residues)
+        return set_error(TRX_EINVAL, "residues is NULL");
+    if (n_text / kTileBytes >= (1ull << 31) / kScanThreads)
+        return set_error(TRX_EINVAL, "text too large for 32-bit TMA row coordinates");
+    TRX_TRY(ctx->use());
+    auto * t = new (std::nothrow) trx_text;
+    if (!t)
+        return set_error(TRX_ENOMEM, "out of host memory");
+    t->ctx = ctx;
+    t->n_text = n_text;
+    t->n_text_padded = (n_text / kTileBytes + 1) * kTileBytes;
+    t->n_records = n_records;
+    t->n_bins = n_bins;
+    t->h_rec_offsets.assign(rec_offsets, rec_offsets + n_records + 1);
+    t->h_rec_bin.assign(rec_bin, rec_bin + n_records);
+    t->h_bin_rec_begin.assign(n_bins + 1, 0);
+    {
+        uint64_t r = 0;
+        for (uint64_t b = 0; b <= n_bins; ++b)
+        {
+            while (r < n_records && rec_bin[r] < b)
+                ++r;
+            t->h_bin_rec_begin[b] = r;
+        }
+    }
+    t->n_chunk_flag_words = (t->n_text_padded / kChunkBytes + 31) / 32;
+    auto fail = [&](cudaError_t e)
+    {
+        trx_text_destroy(t);
+        return set_error(e == cudaErrorMemoryAllocation ? TRX_ENOMEM : TRX_ECUDA, "trx_text_upload: %s",
+                         cudaGetErrorString(e));
+    };
+    cudaError_t e;
+    if ((e = cudaMalloc(&t->d_text, t->n_text_padded)) != cudaSuccess) return fail(e);
+    if ((e = cudaMalloc(&t->d_rec_offsets, (n_records + 1) * 8)) != cudaSuccess) return fail(e);
+    if ((e = cudaMalloc(&t->d_rec_bin, n_records * 4)) != cudaSuccess) return fail(e);
+    if ((e = cudaMalloc(&t->d_bin_rec_begin, (n_bins + 1) * 8)) != cudaSuccess) return fail(e);
+    if ((e = cudaMalloc(&t->d_chunk_flags, t->n_chunk_flag_words * 4)) != cudaSuccess) return fail(e);
+    if ((e = cudaMalloc(&t->d_rec_flags, n_records)) != cudaSuccess) return fail(e);
+    if ((e = cudaMemsetAsync(t->d_text + (t->n_text_padded - kTileBytes), 0, kTileBytes, ctx->stream)) != cudaSuccess) return fail(e);
+    if (n_text && (e = cudaMemcpyAsync(t->d_text, residues, n_text, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess) return fail(e);
+    if ((e = cudaMemcpyAsync(t->d_rec_offsets, rec_offsets, (n_records + 1) * 8, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess) return fail(e);
+    if ((e = cudaMemcpyAsync(t->d_rec_bin, rec_bin, n_records * 4, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess) return fail(e);
+    if ((e = cudaMemcpyAsync(t->d_bin_rec_begin, t->h_bin_rec_begin.data(), (n_bins + 1) * 8, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess) return fail(e);
+    if ((e = cudaStreamSynchronize(ctx->stream)) != cudaSuccess) return fail(e);
+    int rc = make_tensor_map(t);
+    if (rc != TRX_OK)
+    {
+        trx_text_destroy(t);
+        return rc;
+    }
+    *out = t;
+    return TRX_OK;
+}
+
+void trx_text_destroy(trx_text_t * t)
+{
+    if (!t)
+        return;
+    cudaSetDevice(t->ctx->device);
+    cudaStreamSynchronize(t->ctx->stream);
+    cudaFree(t->d_text);
+    cudaFree(t->d_rec_offsets);
+    cudaFree(t->d_rec_bin);
+    cudaFree(t->d_bin_rec_begin);
+    cudaFree(t->d_chunk_flags);
+    cudaFree(t->d_rec_flags);
+    for (trx::scratch * s : {&t->d_cand, &t->d_tiles, &t->d_cand_bins, &t->d_cand_prefix, &t->d_regex, &t->d_counter,
+                             &t->d_keys, &t->d_ends, &t->d_keys2, &t->d_ends2, &t->d_sort_tmp})
+        s->release();
+    delete t;
+}
+
+} // extern "C"
+
+namespace
+{
+
+template <int W, int DIR, bool USE_TMA>
+int launch_phase1(trx_ctx * c, scan_params const & sp, CUtensorMap const & tmap)
+{
+    size_t smem = (USE_TMA ? kStages * kTileBytes : 0) + sizeof(scan_tables<W>) + 2 * sizeof(uint64_t);
+    auto kern = regex_scan_phase1<W, DIR, USE_TMA>;
+    TRX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    int per_sm = 0;
+    TRX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kScanThreads, smem));
+    if (per_sm < 1)
+        per_sm = 1;
+    unsigned grid = static_cast<unsigned>(std::min<uint64_t>(sp.n_tiles, static_cast<uint64_t>(c->sm_count) * per_sm));
+    kern<<<grid, kScanThreads, smem, c->stream>>>(sp, tmap);
+    ++c->launches;
+    TRX_CUDA(cudaGetLastError());
+    return TRX_OK;
+}
+
+template <int W>
+int launch_phase1_w(trx_ctx * c, scan_params const & sp, CUtensorMap const & tmap, bool reverse, bool use_tma)
+{
+    if (reverse)
+        return use_tma ? launch_phase1<W, -1, true>(c, sp, tmap) : launch_phase1<W, -1, false>(c, sp, tmap);
+    return use_tma ? launch_phase1<W, 1, true>(c, sp, tmap) : launch_phase1<W, 1, false>(c, sp, tmap);
+}
+
+template <int W>
+int launch_phase2_w(trx_ctx * c, resolve_params const & rp, bool reverse)
+{
+    unsigned grid = grid_for(rp.n_cand_records, 128, c->sm_count, 16);
+    if (reverse)
+        regex_scan_phase2<W, -1><<<grid, 128, 0, c->stream>>>(rp);
+    else
+        regex_scan_phase2<W, 1><<<grid, 128, 0, c->stream>>>(rp);
+    ++c->launches;
+    TRX_CUDA(cudaGetLastError());
+    return TRX_OK;
+}
+
+// comp_tab of src/query.cpp:7-16 as a byte map: IUPAC complement, everything else maps to itself.
+void complement_table(uint8_t tab[256])
+{
+    for (int i = 0; i < 256; ++i)
+        tab[i] = static_cast<uint8_t>(i);
+    char const * from = "ACGTUMRWSYKVHDBNacgtumrwsykvhdbn";
+    char const * to = "TGCAAKYWSRMBDHVNtgcaakywsrmbdhvn";
+    for (int i = 0; from[i]; ++i)
+        tab[static_cast<uint8_t>(from[i])] = static_cast<uint8_t>(to[i]);
+}
+
+} // namespace
+
+extern "C"
+{
+
+int trx_regex_scan(trx_text_t * t, trx_regex_t * re, const uint64_t * candidate_bin_words, int reverse_strand,
+                   const uint8_t * map256, trx_hit * hits, uint64_t cap, uint64_t * n_hits, uint64_t * stats)
+{
+    if (!t || !re || !candidate_bin_words || !n_hits || (cap && !hits))
+        return set_error(TRX_EINVAL, "trx_regex_scan: NULL argument");
+    *n_hits = 0;
+    if (stats)
+        stats[0] = 0;
+    trx_ctx * c = t->ctx;
+    TRX_TRY(c->use());
+    if (re->follow_list.size() > sizeof(regex_dev::follow_list))
+        return set_error(TRX_EREGEX, "pattern '%s': ordered follow lists need %zu bytes (max %zu)", re->pattern.c_str(),
+                         re->follow_list.size(), sizeof(regex_dev::follow_list));
+
+    // ---- plan: candidate bins → tiles (phase 1) and record ranges (phase 2)
+    uint64_t const cand_words = (t->n_bins + 63) / 64;
+    std::vector<uint32_t> cand_bins;
+    std::vector<uint64_t> cand_prefix{0};
+    std::vector<uint32_t> tiles;
+    uint64_t residues = 0;
+    for (uint64_t b = 0; b < t->n_bins; ++b)
+    {
+        if (!((candidate_bin_words[b >> 6] >> (b & 63)) & 1))
+            continue;
+        uint64_t r0 = t->h_bin_rec_begin[b], r1 = t->h_bin_rec_begin[b + 1];
+        if (r0 == r1)
+            continue;
+        uint64_t g0 = t->h_rec_offsets[r0], g1 = t->h_rec_offsets[r1];
+        cand_bins.push_back(static_cast<uint32_t>(b));
+        cand_prefix.push_back(cand_prefix.back() + (r1 - r0));
+        if (g1 == g0)
+            continue;
+        residues += g1 - g0;
+        for (uint64_t tile = g0 / kTileBytes; tile <= (g1 - 1) / kTileBytes; ++tile)
+            if (tiles.empty() || tiles.back() != tile)
+                tiles.push_back(static_cast<uint32_t>(tile));
+    }
+    if (stats)
+        stats[0] = residues;
+    if (cand_bins.empty() || tiles.empty())
+        return TRX_OK;
+
+    // ---- automaton image with the byte map folded into B
+    static_assert(sizeof(regex_dev) < 16384, "regex_dev grew unexpectedly");
+    auto img = std::make_unique<regex_dev>();
+    memset(img.get(), 0, sizeof(regex_dev));
+    uint8_t comp[256];
+    if (reverse_strand)
+        complement_table(comp);
+    for (int k = 0; k < kRegexWords; ++k)
+    {
+        img->first[k] = re->masks.first[k];
+        img->last[k] = re->masks.last[k];
+    }
+    for (int ch = 0; ch < 256; ++ch)
+    {
+        uint8_t seen = static_cast<uint8_t>(ch);
+        if (reverse_strand)
+            seen = comp[seen];
+        if (map256)
+            seen = map256[seen];
+        for (int k = 0; k < kRegexWords; ++k)
+            img->B[ch][k] = re->masks.B[seen][k];
+    }
+    memcpy(img->follow, re->masks.follow, sizeof(img->follow));
+    img->first_len = static_cast<uint16_t>(re->first_list.size());
+    memcpy(img->first_list, re->first_list.data(), re->first_list.size());
+    memcpy(img->follow_off, re->follow_off.data(), re->follow_off.size() * sizeof(uint16_t));
+    memcpy(img->follow_list, re->follow_list.data(), re->follow_list.size());
+    img->positions = re->positions;
+    img->posix_longest = re->posix_longest;
+    img->anchor_begin = re->anchor_begin;
+    img->anchor_end = re->anchor_end;
+
+    // ---- upload plan + automaton, clear flags
+    if (cap > (1ull << 31))
+        cap = 1ull << 31;
+    uint64_t const dev_cap = cap ? cap : 1;
+    TRX_TRY(t->d_cand.reserve(cand_words * 8));
+    TRX_TRY(t->d_tiles.reserve(tiles.size() * 4));
+    TRX_TRY(t->d_cand_bins.reserve(cand_bins.size() * 4));
+    TRX_TRY(t->d_cand_prefix.reserve(cand_prefix.size() * 8));
+    TRX_TRY(t->d_regex.reserve(sizeof(regex_dev)));
+    TRX_TRY(t->d_counter.reserve(8));
+    TRX_TRY(t->d_keys.reserve(dev_cap * 8));
+    TRX_TRY(t->d_ends.reserve(dev_cap * 4));
+    TRX_CUDA(cudaMemcpyAsync(t->d_cand.ptr, candidate_bin_words, cand_words * 8, cudaMemcpyHostToDevice, c->stream));
+    TRX_CUDA(cudaMemcpyAsync(t->d_tiles.ptr, tiles.data(), tiles.size() * 4, cudaMemcpyHostToDevice, c->stream));
+    TRX_CUDA(cudaMemcpyAsync(t->d_cand_bins.ptr, cand_bins.data(), cand_bins.size() * 4, cudaMemcpyHostToDevice, c->stream));
+    TRX_CUDA(cudaMemcpyAsync(t->d_cand_prefix.ptr, cand_prefix.data(), cand_prefix.size() * 8, cudaMemcpyHostToDevice, c->stream));
+    TRX_CUDA(cudaMemcpyAsync(t->d_regex.ptr, img.get(), sizeof(regex_dev), cudaMemcpyHostToDevice, c->stream));
+    TRX_CUDA(cudaMemsetAsync(t->d_counter.ptr, 0, 8, c->stream));
+    TRX_CUDA(cudaMemsetAsync(t->d_chunk_flags, 0, t->n_chunk_flag_words * 4, c->stream));
+    TRX_CUDA(cudaMemsetAsync(t->d_rec_flags, 0, t->n_records, c->stream));
+
+    scan_params sp{};
+    sp.text = t->d_text;
+    sp.n_text = t->n_text;
+    sp.rec_offsets = t->d_rec_offsets;
+    sp.rec_bin = t->d_rec_bin;
+    sp.n_records = t->n_records;
+    sp.cand_words = static_cast<uint64_t *>(t->d_cand.ptr);
+    sp.tiles = static_cast<uint32_t *>(t->d_tiles.ptr);
+    sp.n_tiles = static_cast<uint32_t>(tiles.size());
+    sp.chunk_flags = t->d_chunk_flags;
+    sp.rec_flags = t->d_rec_flags;
+    sp.re = static_cast<regex_dev *>(t->d_regex.ptr);
+
+    // TRX_REGEX_STAGING=ldg selects the direct-load variant of the same kernel (A/B evidence for the TMA staging)
+    char const * staging = getenv("TRX_REGEX_STAGING");
+    bool const use_tma = !(staging && strcmp(staging, "ldg") == 0);
+    bool const reverse = reverse_strand != 0;
+    if (re->words == 1)
+        TRX_TRY(launch_phase1_w<1>(c, sp, t->tmap, reverse, use_tma));
+    else
+        TRX_TRY(launch_phase1_w<2>(c, sp, t->tmap, reverse, use_tma));
+
+    resolve_params rp{};
+    rp.text = t->d_text;
+    rp.rec_offsets = t->d_rec_offsets;
+    rp.cand_bins = static_cast<uint32_t *>(t->d_cand_bins.ptr);
+    rp.cand_rec_prefix = static_cast<uint64_t *>(t->d_cand_prefix.ptr);
+    rp.bin_rec_begin = t->d_bin_rec_begin;
+    rp.n_cand = static_cast<uint32_t>(cand_bins.size());
+    rp.n_cand_records = cand_prefix.back();
+    rp.chunk_flags = t->d_chunk_flags;
+    rp.rec_flags = t->d_rec_flags;
+    rp.re = sp.re;
+    rp.hit_count = static_cast<unsigned long long *>(t->d_counter.ptr);
+    rp.hit_keys = static_cast<uint64_t *>(t->d_keys.ptr);
+    rp.hit_ends = static_cast<uint32_t *>(t->d_ends.ptr);
+    rp.cap = cap;
+    if (re->words == 1)
+        TRX_TRY(launch_phase2_w<1>(c, rp, reverse));
+    else
+        TRX_TRY(launch_phase2_w<2>(c, rp, reverse));
+
+    unsigned long long total = 0;
+    TRX_CUDA(cudaMemcpyAsync(&total, t->d_counter.ptr, 8, cudaMemcpyDeviceToHost, c->stream));
+    TRX_CUDA(cudaStreamSynchronize(c->stream));
+    *n_hits = total;
+    if (total > cap)
+        return set_error(TRX_ECAPACITY, "trx_regex_scan: %llu hits, room for %llu", total, (unsigned long long)cap);
+    if (total == 0)
+        return TRX_OK;
+
+    // ---- order = (bin, record, start): records are grouped by ascending bin, so (record, start) suffices
+    uint64_t const n = total;
+    TRX_TRY(t->d_keys2.reserve(n * 8));
+    TRX_TRY(t->d_ends2.reserve(n * 4));
+    size_t tmp_bytes = 0;
+    TRX_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, rp.hit_keys, static_cast<uint64_t *>(t->d_keys2.ptr),
+                                             rp.hit_ends, static_cast<uint32_t *>(t->d_ends2.ptr), static_cast<int>(n), 0, 64,
+                                             c->stream));
+    TRX_TRY(t->d_sort_tmp.reserve(tmp_bytes));
+    TRX_CUDA(cub::DeviceRadixSort::SortPairs(t->d_sort_tmp.ptr, tmp_bytes, rp.hit_keys,
+                                             static_cast<uint64_t *>(t->d_keys2.ptr), rp.hit_ends,
+                                             static_cast<uint32_t *>(t->d_ends2.ptr), static_cast<int>(n), 0, 64, c->stream));
+    c->launches += 3; // cub's histogram + onesweep passes
+    std::vector<uint64_t> keys(n);
+    std::vector<uint32_t> ends(n);
+    TRX_CUDA(cudaMemcpyAsync(keys.data(), t->d_keys2.ptr, n * 8, cudaMemcpyDeviceToHost, c->stream));
+    TRX_CUDA(cudaMemcpyAsync(ends.data(), t->d_ends2.ptr, n * 4, cudaMemcpyDeviceToHost, c->stream));
+    TRX_CUDA(cudaStreamSynchronize(c->stream));
+    for (uint64_t i = 0; i < n; ++i)
+    {
+        uint32_t rec = static_cast<uint32_t>(keys[i] >> 32);
+        hits[i] = trx_hit{t->h_rec_bin[rec], rec, static_cast<uint32_t>(keys[i]), ends[i]};
+    }
+    return TRX_OK;
+}
+
+} // extern "C"
