@@ -207,9 +207,10 @@ typedef struct trx_hit {
  * scanned with non-overlapping FindAndConsume semantics.  map256 (nullable, host): byte map applied
  * to the text before matching (redmap_ of a reduced index).  reverse_strand: scan comp_tab-
  * complemented, reversed records (src/query.cpp:7-16,167-191).  hits come back sorted by
- * (bin, record, start) = the reference's -t 1 print order.  If more than cap hits exist the first
- * cap are returned, *n_hits holds the total and the call returns TRX_ECAPACITY.
- * stats (nullable): [0] = residues scanned. */
+ * (bin, record, start) = the reference's -t 1 print order.  If more than cap hits exist, *n_hits holds the
+ * total, the call returns TRX_ECAPACITY and the contents of hits are unspecified (call again with room).
+ * stats (nullable, 2 entries): [0] = residues scanned, [1] = literals in the SIMD prefilter (0 = the exact
+ * automaton kernel ran as phase 1). */
 int trx_regex_scan(trx_text_t *text, trx_regex_t *re, const uint64_t *candidate_bin_words, int reverse_strand,
                    const uint8_t *map256, trx_hit *hits, uint64_t cap, uint64_t *n_hits, uint64_t *stats);
 

@@ -96,6 +96,45 @@ def test_regex_staging_variants_agree(ctx, monkeypatch):
     txt.close()
 
 
+def test_factor_filter_equals_exact_automaton(ctx, monkeypatch):
+    """Phase 1 has two variants (SIMD necessary-factor filter / exact automaton); both must lead to the same hits."""
+    rng = random.Random(12)
+    aa = b"ACDEFGHIKLMNPQRSTVWY"
+    seqs = [bytes(rng.choice(aa) for _ in range(L)) for L in [3000, 127, 128, 5, 0, 60000, 129, 4000]]
+    motif = b"LMAQGLYN"
+    for r, pos in [(0, 5), (0, 120), (0, 2992), (1, 119), (2, 0), (2, 120), (5, 127), (5, 128 * 256 - 3), (5, 59992), (6, 121)]:
+        b = bytearray(seqs[r])
+        b[pos:pos + 8] = motif
+        seqs[r] = bytes(b)
+    rec_bin = [0, 0, 1, 1, 2, 3, 3, 4]
+    txt = build_text(ctx, seqs, rec_bin, 5)
+    finder = ob.ref_find_all if ob.have_ref() else ob.find_all_python
+    dna = [bytes(rng.choice(b"ACGT") for _ in range(L)) for L in [50000, 130, 7]]
+    dtxt = build_text(ctx, dna, [0, 1, 1], 2)
+    revcomp = lambda s: s.translate(COMP)[::-1]
+    for pat, posix, used in [("LMA(E|Q)GLYN", True, True), ("MA[EQ]GLY", True, True), ("L.A.G", True, False), ("[LI]MAQ", True, True),
+                             ("(LMAQ|GLYN)", True, False), ("AQGL+YN", True, True), ("QGLYN$", True, True)]:
+        rx = t.Regex(pat, posix)
+        a = txt.scan(rx)
+        assert (txt.last_filter_literals >= 2) == used, (pat, txt.last_filter_literals)
+        monkeypatch.setenv("TRX_REGEX_FILTER", "off")
+        b = txt.scan(rx)
+        assert txt.last_filter_literals == 0
+        monkeypatch.delenv("TRX_REGEX_FILTER")
+        want = expected_hits(seqs, rec_bin, pat, posix, finder)
+        assert np.array_equal(a, want) and np.array_equal(b, want), pat
+        assert len(want) > 0, pat
+    for pat in ["GATTACAG", "ACGTAC(G|T)", "TTGACA.{3}T"]:
+        rx = t.Regex(pat, False)
+        for rev in (False, True):
+            a = dtxt.scan(rx, reverse_strand=rev)
+            assert dtxt.last_filter_literals >= 2, pat
+            want = expected_hits(dna, [0, 1, 1], pat, False, finder, transform=revcomp if rev else None)
+            assert np.array_equal(a, want), (pat, rev)
+    txt.close()
+    dtxt.close()
+
+
 def test_reverse_strand(ctx):
     """reverse_verify_fasta_hit (src/query.cpp:167-191): the record is complemented through comp_tab and reversed."""
     rng = random.Random(9)

@@ -310,8 +310,9 @@ class Text:
         m = _np(map256, np.uint8) if map256 is not None else None
         hits = (TrxHit * cap)()
         n = C.c_uint64()
-        st = np.zeros(1, dtype=np.uint64)
+        st = np.zeros(2, dtype=np.uint64)
         check(lib().trx_regex_scan(self._h, regex._h, _ptr(cand), int(reverse_strand), _ptr(m) if m is not None else None,
                                    C.addressof(hits), cap, C.byref(n), st.ctypes.data_as(u64p)))
         arr = np.frombuffer(hits, dtype=np.uint32, count=4 * n.value).reshape(-1, 4).copy()
+        self.last_filter_literals = int(st[1])
         return (arr, int(st[0])) if stats else arr

@@ -45,20 +45,43 @@ struct regex_dev
     int32_t anchor_end;
 };
 
+// necessary-factor prefilter: up to 4 literal bytes at fixed distances (span <= 4 bytes) that EVERY match
+// carries at a fixed offset from its first byte (derived on the host from the automaton's level sets)
+struct filter_spec
+{
+    int32_t n_literals;       // 0 = no usable factor: run the exact automaton kernel instead
+    int32_t start_delta;      // address of a match's first byte (reading direction) minus address of literal 0
+    uint32_t delta[4];        // byte distance of literal j from literal 0 (ascending addresses), delta[0] = 0, <= 3
+    uint32_t splat[4];        // literal byte replicated into all four lanes
+};
+
 struct scan_params
 {
     uint8_t const * text;         // padded to a tile multiple, zero filled
     uint64_t n_text;              // real bytes
+    uint64_t n_text_padded;
     uint64_t const * rec_offsets; // n_records + 1
     uint32_t const * rec_bin;     // n_records
     uint64_t n_records;
     uint64_t const * cand_words;  // candidate bin bitmap (device)
     uint32_t const * tiles;       // tile ids to scan
     uint32_t n_tiles;
-    uint32_t * chunk_flags;       // bitmap over global chunk ids
-    uint8_t * rec_flags;          // per record
+    uint32_t * chunk_flags;       // bitmap over global chunk ids: "a match may start in this chunk"
+    uint32_t * rec_flags;         // bitmap over records already listed
+    uint32_t * rec_list;          // records that may hold a match (each once), for phase 2
+    unsigned int * rec_count;
     regex_dev const * re;
+    filter_spec filter;
 };
+
+// first flagging of a record appends it to the phase-2 work list
+__device__ __forceinline__ void list_record(scan_params const & p, uint64_t r)
+{
+    uint32_t const bit = 1u << (r & 31);
+    uint32_t const old = atomicOr(p.rec_flags + (r >> 5), bit);
+    if (!(old & bit))
+        p.rec_list[atomicAdd(p.rec_count, 1u)] = static_cast<uint32_t>(r);
+}
 
 template <int W>
 struct state
@@ -273,7 +296,7 @@ __global__ void __launch_bounds__(kScanThreads)
             auto flush_record = [&]()
             {
                 if (rec_hit)
-                    p.rec_flags[r] = 1;
+                    list_record(p, r);
                 rec_hit = false;
             };
             // one byte of the automaton; returns nothing, updates S / flags
@@ -381,13 +404,9 @@ struct resolve_params
 {
     uint8_t const * text;
     uint64_t const * rec_offsets;
-    uint32_t const * cand_bins;        // candidate bin ids
-    uint64_t const * cand_rec_prefix;  // prefix sums of records per candidate bin (n_cand + 1)
-    uint64_t const * bin_rec_begin;    // first record of every bin (n_bins + 1)
-    uint32_t n_cand;
-    uint64_t n_cand_records;
+    uint32_t const * rec_list;         // records flagged by phase 1
+    unsigned int const * rec_count;
     uint32_t const * chunk_flags;
-    uint8_t const * rec_flags;
     regex_dev const * re;
     unsigned long long * hit_count;
     uint64_t * hit_keys;               // record << 32 | start
@@ -498,27 +517,17 @@ __device__ int64_t match_first(regex_dev const & re, At at, int64_t s, int64_t L
     return best;
 }
 
-// One thread per record of the candidate bins; returns at once unless phase 1 flagged the record.
+// One thread per record that phase 1 listed; the list length is read from device memory, so no host round
+// trip separates the two phases.
 template <int W, int DIR>
 __global__ void __launch_bounds__(128) regex_scan_phase2(resolve_params p)
 {
     regex_dev const & re = *p.re;
-    for (uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < p.n_cand_records;
+    uint64_t const n_listed = *p.rec_count;
+    for (uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n_listed;
          i += static_cast<uint64_t>(gridDim.x) * blockDim.x)
     {
-        // which candidate bin does the i-th candidate record belong to
-        uint32_t lo = 0, hi = p.n_cand;
-        while (hi - lo > 1)
-        {
-            uint32_t mid = (lo + hi) >> 1;
-            if (p.cand_rec_prefix[mid] <= i)
-                lo = mid;
-            else
-                hi = mid;
-        }
-        uint64_t const r = p.bin_rec_begin[p.cand_bins[lo]] + (i - p.cand_rec_prefix[lo]);
-        if (!p.rec_flags[r])
-            continue;
+        uint64_t const r = p.rec_list[i];
         uint64_t const rb = p.rec_offsets[r], re_off = p.rec_offsets[r + 1];
         int64_t const L = static_cast<int64_t>(re_off - rb);
         auto at = [&](int64_t pos) -> uint8_t
@@ -558,6 +567,160 @@ __global__ void __launch_bounds__(128) regex_scan_phase2(resolve_params p)
             }
         }
     }
+}
+
+} // namespace trx
+
+namespace trx
+{
+
+// ------------------------------------------------------------------------------------------------------
+// Phase 1, fast variant: SIMD-within-register necessary-factor filter.
+//
+// A byte-at-a-time automaton costs >= 9 thread instructions per residue, which caps a B200 at ~40 % of its
+// HBM bandwidth.  Phase 1 only has to produce a SUPERSET of the places where a match can start (phase 2 is
+// exact), so when every match carries NL literal bytes at fixed distances (filter_spec), the filter tests
+// four text positions per 32-bit operation:
+//      u  = (w ^ X0) | (shift(w, d1) ^ X1) | …        byte lane = 0  ⇔  all NL literals present there
+//      z  = (u - 0x01010101) & ~u & 0x80808080        ≠ 0  ⇔  some lane of u is 0
+// ≈ 2 instructions per residue for NL = 3.  Record boundaries, candidate bins and reading direction do not
+// matter here: a factor that straddles two records, or lies in a non-candidate bin that shares a tile, only
+// creates a false candidate that phase 2 never visits or rejects.
+template <int NL>
+__global__ void __launch_bounds__(kScanThreads)
+    regex_filter_simd(scan_params p, const __grid_constant__ CUtensorMap tmap)
+{
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t * tiles = smem_raw;
+    uint64_t * bars = reinterpret_cast<uint64_t *>(smem_raw + kStages * kTileBytes);
+    int const tid = threadIdx.x;
+    if (tid == 0)
+    {
+        mbar_init(&bars[0], 1);
+        mbar_init(&bars[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    uint32_t const first_tile = blockIdx.x;
+    if (tid == 0 && first_tile < p.n_tiles)
+        tma_load_tile(&tmap, tiles, &bars[0], static_cast<int32_t>(p.tiles[first_tile]) * kScanThreads);
+
+    uint32_t X[NL], D[NL];
+#pragma unroll
+    for (int j = 0; j < NL; ++j)
+    {
+        X[j] = p.filter.splat[j];
+        D[j] = p.filter.delta[j] * 8;
+    }
+
+    uint32_t it = 0;
+    for (uint32_t t = first_tile; t < p.n_tiles; t += gridDim.x, ++it)
+    {
+        uint32_t const stage = it & 1;
+        uint32_t const tn = t + gridDim.x;
+        if (tid == 0 && tn < p.n_tiles)
+        {
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            tma_load_tile(&tmap, tiles + (stage ^ 1) * kTileBytes, &bars[stage ^ 1],
+                          static_cast<int32_t>(p.tiles[tn]) * kScanThreads);
+        }
+        mbar_wait(&bars[stage], (it >> 1) & 1);
+
+        uint64_t const chunk_id = static_cast<uint64_t>(p.tiles[t]) * kScanThreads + tid;
+        uint64_t const g_lo = chunk_id * kChunkBytes;
+        uint8_t const * row = tiles + stage * kTileBytes + tid * kChunkBytes;
+        uint32_t w[kChunkBytes / 4 + 1];
+#pragma unroll
+        for (int piece = 0; piece < kChunkBytes / 16; ++piece)
+        {
+            uint4 v = *reinterpret_cast<uint4 const *>(row + ((piece ^ (tid & 7)) << 4));
+            w[4 * piece + 0] = v.x;
+            w[4 * piece + 1] = v.y;
+            w[4 * piece + 2] = v.z;
+            w[4 * piece + 3] = v.w;
+        }
+        // look-ahead word = first word of the next chunk: the neighbouring row of the tile, or global memory
+        if (tid + 1 < kScanThreads)
+            w[kChunkBytes / 4] = *reinterpret_cast<uint32_t const *>(row + kChunkBytes + ((0 ^ ((tid + 1) & 7)) << 4));
+        else
+            w[kChunkBytes / 4] = (g_lo + kChunkBytes + 4 <= p.n_text_padded)
+                                     ? __ldg(reinterpret_cast<uint32_t const *>(p.text + g_lo + kChunkBytes))
+                                     : 0u;
+        uint32_t piece_hits = 0; // bit i = piece i holds a candidate
+#pragma unroll
+        for (int piece = 0; piece < kChunkBytes / 16; ++piece)
+        {
+            uint32_t acc = 0;
+#pragma unroll
+            for (int q = 4 * piece; q < 4 * piece + 4; ++q)
+            {
+                uint32_t u = w[q] ^ X[0];
+#pragma unroll
+                for (int j = 1; j < NL; ++j)
+                    u |= __funnelshift_r(w[q], w[q + 1], D[j]) ^ X[j];
+                acc |= (u - 0x01010101u) & ~u & 0x80808080u;
+            }
+            if (acc)
+                piece_hits |= 1u << piece;
+        }
+        if (piece_hits && g_lo < p.n_text)
+        {
+            // rare path: translate candidate pieces into chunk flags and listed records
+            while (piece_hits)
+            {
+                int const piece = __ffs(piece_hits) - 1;
+                piece_hits &= piece_hits - 1;
+                int64_t lo = static_cast<int64_t>(g_lo) + piece * 16 + p.filter.start_delta;
+                int64_t hi = lo + 15;
+                if (hi < 0 || lo >= static_cast<int64_t>(p.n_text))
+                    continue;
+                if (lo < 0)
+                    lo = 0;
+                if (hi >= static_cast<int64_t>(p.n_text))
+                    hi = static_cast<int64_t>(p.n_text) - 1;
+                uint64_t const c0 = static_cast<uint64_t>(lo) / kChunkBytes, c1 = static_cast<uint64_t>(hi) / kChunkBytes;
+                atomicOr(p.chunk_flags + (c0 >> 5), 1u << (c0 & 31));
+                if (c1 != c0)
+                    atomicOr(p.chunk_flags + (c1 >> 5), 1u << (c1 & 31));
+                uint64_t r = record_of(p.rec_offsets, p.n_records, static_cast<uint64_t>(lo));
+                while (r < p.n_records && __ldg(p.rec_offsets + r) <= static_cast<uint64_t>(hi))
+                {
+                    if (__ldg(p.rec_offsets + r + 1) > static_cast<uint64_t>(lo) &&
+                        is_candidate(p.cand_words, __ldg(p.rec_bin + r)))
+                        list_record(p, r);
+                    ++r;
+                }
+            }
+        }
+        __syncthreads();
+    }
+}
+
+// byte histogram of the residue store (once per upload): the host uses it to pick the rarest literals
+__global__ void __launch_bounds__(256) byte_histogram_kernel(uint8_t const * __restrict__ text, uint64_t n,
+                                                             unsigned long long * __restrict__ hist)
+{
+    __shared__ unsigned int h[256];
+    h[threadIdx.x] = 0;
+    __syncthreads();
+    uint64_t const n16 = n / 16;
+    for (uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n16;
+         i += static_cast<uint64_t>(gridDim.x) * blockDim.x)
+    {
+        uint4 v = __ldg(reinterpret_cast<uint4 const *>(text) + i);
+        uint32_t const ws[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+#pragma unroll
+            for (int b = 0; b < 4; ++b)
+                atomicAdd(&h[(ws[k] >> (8 * b)) & 0xFF], 1u);
+    }
+    if (blockIdx.x == 0)
+        for (uint64_t i = n16 * 16 + threadIdx.x; i < n; i += blockDim.x)
+            atomicAdd(&h[text[i]], 1u);
+    __syncthreads();
+    if (h[threadIdx.x])
+        atomicAdd(hist + threadIdx.x, static_cast<unsigned long long>(h[threadIdx.x]));
 }
 
 } // namespace trx

@@ -17,14 +17,17 @@ struct trx_text
     uint64_t * d_bin_rec_begin{nullptr};
     uint32_t * d_chunk_flags{nullptr};
     uint64_t n_chunk_flag_words{};
-    uint8_t * d_rec_flags{nullptr};
+    uint32_t * d_rec_flags{nullptr};   // bitmap
+    uint64_t n_rec_flag_words{};
+    uint32_t * d_rec_list{nullptr};
+    double byte_freq[256]{};           // relative byte frequencies of the residue store
     std::vector<uint64_t> h_rec_offsets;   // host copies: tile planning and hit formatting
     std::vector<uint32_t> h_rec_bin;
     std::vector<uint64_t> h_bin_rec_begin; // n_bins + 1
     CUtensorMap tmap{};
     bool has_tmap{false};
     // per-scan scratch
-    trx::scratch d_cand, d_tiles, d_cand_bins, d_cand_prefix, d_regex, d_counter, d_keys, d_ends, d_keys2, d_ends2, d_sort_tmp;
+    trx::scratch d_stage, h_stage, d_counter, d_keys, d_ends, d_keys2, d_ends2, d_sort_tmp;
 };
 
 using namespace trx;
@@ -125,13 +128,30 @@ int trx_text_upload(trx_ctx_t * ctx, const uint8_t * residues, const uint64_t * 
     if ((e = cudaMalloc(&t->d_rec_bin, n_records * 4)) != cudaSuccess) return fail(e);
     if ((e = cudaMalloc(&t->d_bin_rec_begin, (n_bins + 1) * 8)) != cudaSuccess) return fail(e);
     if ((e = cudaMalloc(&t->d_chunk_flags, t->n_chunk_flag_words * 4)) != cudaSuccess) return fail(e);
-    if ((e = cudaMalloc(&t->d_rec_flags, n_records)) != cudaSuccess) return fail(e);
+    t->n_rec_flag_words = (n_records + 31) / 32;
+    if ((e = cudaMalloc(&t->d_rec_flags, t->n_rec_flag_words * 4)) != cudaSuccess) return fail(e);
+    if ((e = cudaMalloc(&t->d_rec_list, n_records * 4)) != cudaSuccess) return fail(e);
     if ((e = cudaMemsetAsync(t->d_text + (t->n_text_padded - kTileBytes), 0, kTileBytes, ctx->stream)) != cudaSuccess) return fail(e);
     if (n_text && (e = cudaMemcpyAsync(t->d_text, residues, n_text, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess) return fail(e);
     if ((e = cudaMemcpyAsync(t->d_rec_offsets, rec_offsets, (n_records + 1) * 8, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess) return fail(e);
     if ((e = cudaMemcpyAsync(t->d_rec_bin, rec_bin, n_records * 4, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess) return fail(e);
     if ((e = cudaMemcpyAsync(t->d_bin_rec_begin, t->h_bin_rec_begin.data(), (n_bins + 1) * 8, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess) return fail(e);
     if ((e = cudaStreamSynchronize(ctx->stream)) != cudaSuccess) return fail(e);
+    {
+        // byte histogram (one pass over the text on the device): lets the scan pick the rarest literals
+        unsigned long long * d_hist = nullptr;
+        unsigned long long h_hist[256];
+        if ((e = cudaMalloc(&d_hist, 256 * 8)) != cudaSuccess) return fail(e);
+        cudaMemsetAsync(d_hist, 0, 256 * 8, ctx->stream);
+        byte_histogram_kernel<<<ctx->sm_count * 4, 256, 0, ctx->stream>>>(t->d_text, n_text, d_hist);
+        ++ctx->launches;
+        cudaMemcpyAsync(h_hist, d_hist, sizeof h_hist, cudaMemcpyDeviceToHost, ctx->stream);
+        e = cudaStreamSynchronize(ctx->stream);
+        cudaFree(d_hist);
+        if (e != cudaSuccess) return fail(e);
+        for (int i = 0; i < 256; ++i)
+            t->byte_freq[i] = n_text ? static_cast<double>(h_hist[i]) / static_cast<double>(n_text) : 0.0;
+    }
     int rc = make_tensor_map(t);
     if (rc != TRX_OK)
     {
@@ -154,8 +174,9 @@ void trx_text_destroy(trx_text_t * t)
     cudaFree(t->d_bin_rec_begin);
     cudaFree(t->d_chunk_flags);
     cudaFree(t->d_rec_flags);
-    for (trx::scratch * s : {&t->d_cand, &t->d_tiles, &t->d_cand_bins, &t->d_cand_prefix, &t->d_regex, &t->d_counter,
-                             &t->d_keys, &t->d_ends, &t->d_keys2, &t->d_ends2, &t->d_sort_tmp})
+    cudaFree(t->d_rec_list);
+    for (trx::scratch * s : {&t->d_stage, &t->h_stage, &t->d_counter, &t->d_keys, &t->d_ends, &t->d_keys2, &t->d_ends2,
+                             &t->d_sort_tmp})
         s->release();
     delete t;
 }
@@ -190,10 +211,27 @@ int launch_phase1_w(trx_ctx * c, scan_params const & sp, CUtensorMap const & tma
     return use_tma ? launch_phase1<W, 1, true>(c, sp, tmap) : launch_phase1<W, 1, false>(c, sp, tmap);
 }
 
+template <int NL>
+int launch_filter(trx_ctx * c, scan_params const & sp, CUtensorMap const & tmap)
+{
+    size_t smem = kStages * kTileBytes + 2 * sizeof(uint64_t);
+    auto kern = regex_filter_simd<NL>;
+    TRX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    int per_sm = 0;
+    TRX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kScanThreads, smem));
+    if (per_sm < 1)
+        per_sm = 1;
+    unsigned grid = static_cast<unsigned>(std::min<uint64_t>(sp.n_tiles, static_cast<uint64_t>(c->sm_count) * per_sm));
+    kern<<<grid, kScanThreads, smem, c->stream>>>(sp, tmap);
+    ++c->launches;
+    TRX_CUDA(cudaGetLastError());
+    return TRX_OK;
+}
+
 template <int W>
 int launch_phase2_w(trx_ctx * c, resolve_params const & rp, bool reverse)
 {
-    unsigned grid = grid_for(rp.n_cand_records, 128, c->sm_count, 16);
+    unsigned grid = static_cast<unsigned>(c->sm_count) * 4;
     if (reverse)
         regex_scan_phase2<W, -1><<<grid, 128, 0, c->stream>>>(rp);
     else
@@ -212,6 +250,93 @@ void complement_table(uint8_t tab[256])
     char const * to = "TGCAAKYWSRMBDHVNtgcaakywsrmbdhvn";
     for (int i = 0; from[i]; ++i)
         tab[static_cast<uint8_t>(from[i])] = static_cast<uint8_t>(to[i]);
+}
+
+struct bits128
+{
+    uint64_t w[2]{0, 0};
+    bool any() const { return (w[0] | w[1]) != 0; }
+    bool intersects(uint64_t const * o) const { return ((w[0] & o[0]) | (w[1] & o[1])) != 0; }
+};
+
+// Derives the necessary factor of filter_spec from the automaton's level sets: L_0 = First,
+// L_{j+1} = Follow(L_j); every match has a byte of class(L_j) at offset j as long as no shorter match exists.
+// Offsets whose class is a single raw byte are literals; the best window of 4 consecutive offsets (by the
+// text's measured byte frequencies) becomes the filter.  n_literals = 0 if nothing selective enough exists.
+filter_spec derive_filter(regex_dev const & img, double const * freq, bool reverse)
+{
+    filter_spec fs{};
+    constexpr int kMaxDepth = 48;
+    int literal[kMaxDepth];
+    int depths = 0;
+    bits128 L;
+    L.w[0] = img.first[0];
+    L.w[1] = img.first[1];
+    for (; depths < kMaxDepth && L.any(); ++depths)
+    {
+        int count = 0, byte = -1;
+        for (int c = 0; c < 256 && count < 2; ++c)
+            if (L.intersects(img.B[c]))
+            {
+                ++count;
+                byte = c;
+            }
+        literal[depths] = count == 1 ? byte : -1;
+        if (L.intersects(img.last))
+        {
+            ++depths; // this offset is still necessary, deeper ones are not
+            break;
+        }
+        bits128 next;
+        for (int k = 0; k < 2; ++k)
+            for (uint64_t s = L.w[k]; s; s &= s - 1)
+            {
+                int pos = k * 64 + __builtin_ctzll(s);
+                next.w[0] |= img.follow[pos][0];
+                next.w[1] |= img.follow[pos][1];
+            }
+        L = next;
+    }
+    double best = 1.0;
+    int best_a = -1;
+    for (int a = 0; a < depths; ++a)
+    {
+        double prod = 1.0;
+        int n = 0;
+        for (int j = a; j < a + 4 && j < depths; ++j)
+            if (literal[j] >= 0)
+            {
+                prod *= std::max(freq[literal[j]], 1e-4);
+                ++n;
+            }
+        if (n >= 2 && prod < best)
+        {
+            best = prod;
+            best_a = a;
+        }
+    }
+    if (best_a < 0 || best > 1e-3) // weaker than ~1 candidate per 8 chunks: the exact automaton is the better filter
+        return fs;
+    int ds[4], n = 0;
+    for (int j = best_a; j < best_a + 4 && j < depths; ++j)
+        if (literal[j] >= 0)
+            ds[n++] = j;
+    fs.n_literals = n;
+    // literal 0 = lowest address: smallest depth when reading forward, largest when reading backwards
+    for (int j = 0; j < n; ++j)
+    {
+        int d = reverse ? ds[n - 1 - j] : ds[j];
+        int d0 = reverse ? ds[n - 1] : ds[0];
+        fs.delta[j] = static_cast<uint32_t>(reverse ? d0 - d : d - d0);
+        fs.splat[j] = 0x01010101u * static_cast<uint32_t>(literal[d]);
+    }
+    fs.start_delta = reverse ? ds[n - 1] : -ds[0];
+    return fs;
+}
+
+size_t align16(size_t x)
+{
+    return (x + 15) & ~size_t{15};
 }
 
 } // namespace
@@ -233,10 +358,8 @@ int trx_regex_scan(trx_text_t * t, trx_regex_t * re, const uint64_t * candidate_
         return set_error(TRX_EREGEX, "pattern '%s': ordered follow lists need %zu bytes (max %zu)", re->pattern.c_str(),
                          re->follow_list.size(), sizeof(regex_dev::follow_list));
 
-    // ---- plan: candidate bins → tiles (phase 1) and record ranges (phase 2)
+    // ---- plan: candidate bins → tiles of the text
     uint64_t const cand_words = (t->n_bins + 63) / 64;
-    std::vector<uint32_t> cand_bins;
-    std::vector<uint64_t> cand_prefix{0};
     std::vector<uint32_t> tiles;
     uint64_t residues = 0;
     for (uint64_t b = 0; b < t->n_bins; ++b)
@@ -247,8 +370,6 @@ int trx_regex_scan(trx_text_t * t, trx_regex_t * re, const uint64_t * candidate_
         if (r0 == r1)
             continue;
         uint64_t g0 = t->h_rec_offsets[r0], g1 = t->h_rec_offsets[r1];
-        cand_bins.push_back(static_cast<uint32_t>(b));
-        cand_prefix.push_back(cand_prefix.back() + (r1 - r0));
         if (g1 == g0)
             continue;
         residues += g1 - g0;
@@ -258,13 +379,23 @@ int trx_regex_scan(trx_text_t * t, trx_regex_t * re, const uint64_t * candidate_
     }
     if (stats)
         stats[0] = residues;
-    if (cand_bins.empty() || tiles.empty())
+    if (tiles.empty())
         return TRX_OK;
 
-    // ---- automaton image with the byte map folded into B
+    // ---- one pinned staging block: [candidate words | tile list | automaton image], one H2D copy
     static_assert(sizeof(regex_dev) < 16384, "regex_dev grew unexpectedly");
-    auto img = std::make_unique<regex_dev>();
-    memset(img.get(), 0, sizeof(regex_dev));
+    size_t const off_cand = 0;
+    size_t const off_tiles = align16(off_cand + cand_words * 8);
+    size_t const off_regex = align16(off_tiles + tiles.size() * 4);
+    size_t const stage_bytes = off_regex + sizeof(regex_dev);
+    t->h_stage.pinned_host = true;
+    TRX_TRY(t->h_stage.reserve(stage_bytes));
+    TRX_TRY(t->d_stage.reserve(stage_bytes));
+    auto * hs = static_cast<uint8_t *>(t->h_stage.ptr);
+    memcpy(hs + off_cand, candidate_bin_words, cand_words * 8);
+    memcpy(hs + off_tiles, tiles.data(), tiles.size() * 4);
+    auto * img = reinterpret_cast<regex_dev *>(hs + off_regex);
+    memset(img, 0, sizeof(regex_dev));
     uint8_t comp[256];
     if (reverse_strand)
         complement_table(comp);
@@ -293,45 +424,54 @@ int trx_regex_scan(trx_text_t * t, trx_regex_t * re, const uint64_t * candidate_
     img->anchor_begin = re->anchor_begin;
     img->anchor_end = re->anchor_end;
 
-    // ---- upload plan + automaton, clear flags
     if (cap > (1ull << 31))
         cap = 1ull << 31;
     uint64_t const dev_cap = cap ? cap : 1;
-    TRX_TRY(t->d_cand.reserve(cand_words * 8));
-    TRX_TRY(t->d_tiles.reserve(tiles.size() * 4));
-    TRX_TRY(t->d_cand_bins.reserve(cand_bins.size() * 4));
-    TRX_TRY(t->d_cand_prefix.reserve(cand_prefix.size() * 8));
-    TRX_TRY(t->d_regex.reserve(sizeof(regex_dev)));
-    TRX_TRY(t->d_counter.reserve(8));
+    TRX_TRY(t->d_counter.reserve(16));
     TRX_TRY(t->d_keys.reserve(dev_cap * 8));
     TRX_TRY(t->d_ends.reserve(dev_cap * 4));
-    TRX_CUDA(cudaMemcpyAsync(t->d_cand.ptr, candidate_bin_words, cand_words * 8, cudaMemcpyHostToDevice, c->stream));
-    TRX_CUDA(cudaMemcpyAsync(t->d_tiles.ptr, tiles.data(), tiles.size() * 4, cudaMemcpyHostToDevice, c->stream));
-    TRX_CUDA(cudaMemcpyAsync(t->d_cand_bins.ptr, cand_bins.data(), cand_bins.size() * 4, cudaMemcpyHostToDevice, c->stream));
-    TRX_CUDA(cudaMemcpyAsync(t->d_cand_prefix.ptr, cand_prefix.data(), cand_prefix.size() * 8, cudaMemcpyHostToDevice, c->stream));
-    TRX_CUDA(cudaMemcpyAsync(t->d_regex.ptr, img.get(), sizeof(regex_dev), cudaMemcpyHostToDevice, c->stream));
-    TRX_CUDA(cudaMemsetAsync(t->d_counter.ptr, 0, 8, c->stream));
+    auto * ds = static_cast<uint8_t *>(t->d_stage.ptr);
+    TRX_CUDA(cudaMemcpyAsync(ds, hs, stage_bytes, cudaMemcpyHostToDevice, c->stream));
+    TRX_CUDA(cudaMemsetAsync(t->d_counter.ptr, 0, 16, c->stream));
     TRX_CUDA(cudaMemsetAsync(t->d_chunk_flags, 0, t->n_chunk_flag_words * 4, c->stream));
-    TRX_CUDA(cudaMemsetAsync(t->d_rec_flags, 0, t->n_records, c->stream));
+    TRX_CUDA(cudaMemsetAsync(t->d_rec_flags, 0, t->n_rec_flag_words * 4, c->stream));
 
     scan_params sp{};
     sp.text = t->d_text;
     sp.n_text = t->n_text;
+    sp.n_text_padded = t->n_text_padded;
     sp.rec_offsets = t->d_rec_offsets;
     sp.rec_bin = t->d_rec_bin;
     sp.n_records = t->n_records;
-    sp.cand_words = static_cast<uint64_t *>(t->d_cand.ptr);
-    sp.tiles = static_cast<uint32_t *>(t->d_tiles.ptr);
+    sp.cand_words = reinterpret_cast<uint64_t *>(ds + off_cand);
+    sp.tiles = reinterpret_cast<uint32_t *>(ds + off_tiles);
     sp.n_tiles = static_cast<uint32_t>(tiles.size());
     sp.chunk_flags = t->d_chunk_flags;
     sp.rec_flags = t->d_rec_flags;
-    sp.re = static_cast<regex_dev *>(t->d_regex.ptr);
+    sp.rec_list = t->d_rec_list;
+    sp.rec_count = reinterpret_cast<unsigned int *>(static_cast<uint8_t *>(t->d_counter.ptr) + 8);
+    sp.re = reinterpret_cast<regex_dev *>(ds + off_regex);
 
-    // TRX_REGEX_STAGING=ldg selects the direct-load variant of the same kernel (A/B evidence for the TMA staging)
+    // TRX_REGEX_STAGING=ldg  → exact automaton kernel with direct loads (A/B evidence for the TMA staging)
+    // TRX_REGEX_FILTER=off   → never use the SIMD factor filter (A/B evidence for the filter)
     char const * staging = getenv("TRX_REGEX_STAGING");
+    char const * filt = getenv("TRX_REGEX_FILTER");
     bool const use_tma = !(staging && strcmp(staging, "ldg") == 0);
     bool const reverse = reverse_strand != 0;
-    if (re->words == 1)
+    if (use_tma && !(filt && strcmp(filt, "off") == 0))
+        sp.filter = derive_filter(*img, t->byte_freq, reverse);
+    if (stats)
+        stats[1] = static_cast<uint64_t>(sp.filter.n_literals);
+    if (sp.filter.n_literals >= 2)
+    {
+        switch (sp.filter.n_literals)
+        {
+        case 2: TRX_TRY(launch_filter<2>(c, sp, t->tmap)); break;
+        case 3: TRX_TRY(launch_filter<3>(c, sp, t->tmap)); break;
+        default: TRX_TRY(launch_filter<4>(c, sp, t->tmap)); break;
+        }
+    }
+    else if (re->words == 1)
         TRX_TRY(launch_phase1_w<1>(c, sp, t->tmap, reverse, use_tma));
     else
         TRX_TRY(launch_phase1_w<2>(c, sp, t->tmap, reverse, use_tma));
@@ -339,13 +479,9 @@ int trx_regex_scan(trx_text_t * t, trx_regex_t * re, const uint64_t * candidate_
     resolve_params rp{};
     rp.text = t->d_text;
     rp.rec_offsets = t->d_rec_offsets;
-    rp.cand_bins = static_cast<uint32_t *>(t->d_cand_bins.ptr);
-    rp.cand_rec_prefix = static_cast<uint64_t *>(t->d_cand_prefix.ptr);
-    rp.bin_rec_begin = t->d_bin_rec_begin;
-    rp.n_cand = static_cast<uint32_t>(cand_bins.size());
-    rp.n_cand_records = cand_prefix.back();
+    rp.rec_list = t->d_rec_list;
+    rp.rec_count = sp.rec_count;
     rp.chunk_flags = t->d_chunk_flags;
-    rp.rec_flags = t->d_rec_flags;
     rp.re = sp.re;
     rp.hit_count = static_cast<unsigned long long *>(t->d_counter.ptr);
     rp.hit_keys = static_cast<uint64_t *>(t->d_keys.ptr);
