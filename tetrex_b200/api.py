@@ -8,6 +8,7 @@ Host-buffer methods take numpy arrays; ``*_dev`` methods take raw device pointer
 from __future__ import annotations
 
 import ctypes as C
+import weakref
 
 import numpy as np
 
@@ -32,9 +33,12 @@ class Context:
         self._h = C.c_void_p()
         check(lib().trx_ctx_create(device, stream, C.byref(self._h)))
         self.device = device
+        self._children = weakref.WeakSet()  # handles that must be destroyed before the context
 
     def close(self):
         if self._h:
+            for child in list(self._children):
+                child.close()
             lib().trx_ctx_destroy(self._h)
             self._h = C.c_void_p()
 
@@ -98,6 +102,7 @@ class IBF:
         check(lib().trx_ibf_geometry(self._h, g.ctypes.data_as(u64p)))
         (self.bins, self.technical_bins, self.bin_size, self.hash_shift, self.bin_words, self.hash_funs, self.n_words,
          self.shard_word_begin, self.shard_words, self.shard_n_words) = [int(x) for x in g]
+        ctx._children.add(self)
 
     def close(self):
         if self._h:
@@ -164,6 +169,7 @@ class Paths:
         self.words_per_slot, self.capacity = words_per_slot, capacity
         self._h = C.c_void_p()
         check(lib().trx_paths_create(ctx._h, words_per_slot, capacity, C.byref(self._h)))
+        ctx._children.add(self)
 
     def close(self):
         if self._h:
@@ -224,6 +230,7 @@ class HIBF:
         self.n_user_bins = int(n_user_bins)
         self.out_words = int(lib().trx_hibf_user_bin_words(self._h))
         self._keep = None  # the device copy is complete; host arrays are not referenced any more
+        ctx._children.add(self)
 
     @classmethod
     def from_tables(cls, ctx, t):
@@ -285,6 +292,7 @@ class Text:
         self._h = C.c_void_p()
         check(lib().trx_text_upload(ctx._h, _ptr(res), _ptr(self.rec_offsets), _ptr(self.rec_bin), len(self.rec_bin),
                                     n_bins, C.byref(self._h)))
+        ctx._children.add(self)
 
     def close(self):
         if self._h:
@@ -308,7 +316,9 @@ class Text:
             cand = _np(candidate_bins, np.uint64)
             assert len(cand) == words
         m = _np(map256, np.uint8) if map256 is not None else None
-        hits = (TrxHit * cap)()
+        if getattr(self, "_hit_cap", 0) != cap:
+            self._hit_buf, self._hit_cap = (TrxHit * cap)(), cap
+        hits = self._hit_buf
         n = C.c_uint64()
         st = np.zeros(2, dtype=np.uint64)
         check(lib().trx_regex_scan(self._h, regex._h, _ptr(cand), int(reverse_strand), _ptr(m) if m is not None else None,

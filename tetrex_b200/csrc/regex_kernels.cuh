@@ -45,14 +45,15 @@ struct regex_dev
     int32_t anchor_end;
 };
 
-// necessary-factor prefilter: up to 4 literal bytes at fixed distances (span <= 4 bytes) that EVERY match
-// carries at a fixed offset from its first byte (derived on the host from the automaton's level sets)
+// necessary-factor prefilter: up to 8 literal bytes inside an 8-byte window that EVERY match carries at a
+// fixed offset from its first byte (derived on the host from the automaton's level sets).  Literals are
+// ordered by address; the first n_a lie in bytes 0..3 of the window, the following n_b in bytes 4..7.
 struct filter_spec
 {
-    int32_t n_literals;       // 0 = no usable factor: run the exact automaton kernel instead
-    int32_t start_delta;      // address of a match's first byte (reading direction) minus address of literal 0
-    uint32_t delta[4];        // byte distance of literal j from literal 0 (ascending addresses), delta[0] = 0, <= 3
-    uint32_t splat[4];        // literal byte replicated into all four lanes
+    int32_t n_a, n_b;         // n_a + n_b = 0: no usable factor, run the exact automaton kernel instead
+    int32_t start_delta;      // address of a match's first byte (reading direction) minus address of window byte 0
+    uint32_t delta[8];        // byte offset of literal j inside its 4-byte half (0..3)
+    uint32_t splat[8];        // literal byte replicated into all four lanes
 };
 
 struct scan_params
@@ -583,13 +584,14 @@ namespace trx
 // four text positions per 32-bit operation:
 //      u  = (w ^ X0) | (shift(w, d1) ^ X1) | …        byte lane = 0  ⇔  all NL literals present there
 //      z  = (u - 0x01010101) & ~u & 0x80808080        ≠ 0  ⇔  some lane of u is 0
-// ≈ 2 instructions per residue for NL = 3.  Record boundaries, candidate bins and reading direction do not
+// ≈ 2 instructions per residue for 3 literals, ≈ 5 for 8.  Record boundaries, candidate bins and reading direction do not
 // matter here: a factor that straddles two records, or lies in a non-candidate bin that shares a tile, only
 // creates a false candidate that phase 2 never visits or rejects.
-template <int NL>
+template <int NA, int NB>
 __global__ void __launch_bounds__(kScanThreads)
     regex_filter_simd(scan_params p, const __grid_constant__ CUtensorMap tmap)
 {
+    constexpr int NL = NA + NB;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t * tiles = smem_raw;
     uint64_t * bars = reinterpret_cast<uint64_t *>(smem_raw + kStages * kTileBytes);
@@ -605,7 +607,7 @@ __global__ void __launch_bounds__(kScanThreads)
     if (tid == 0 && first_tile < p.n_tiles)
         tma_load_tile(&tmap, tiles, &bars[0], static_cast<int32_t>(p.tiles[first_tile]) * kScanThreads);
 
-    uint32_t X[NL], D[NL];
+    uint32_t X[NL > 0 ? NL : 1], D[NL > 0 ? NL : 1];
 #pragma unroll
     for (int j = 0; j < NL; ++j)
     {
@@ -629,7 +631,7 @@ __global__ void __launch_bounds__(kScanThreads)
         uint64_t const chunk_id = static_cast<uint64_t>(p.tiles[t]) * kScanThreads + tid;
         uint64_t const g_lo = chunk_id * kChunkBytes;
         uint8_t const * row = tiles + stage * kTileBytes + tid * kChunkBytes;
-        uint32_t w[kChunkBytes / 4 + 1];
+        uint32_t w[kChunkBytes / 4 + 2];
 #pragma unroll
         for (int piece = 0; piece < kChunkBytes / 16; ++piece)
         {
@@ -639,13 +641,23 @@ __global__ void __launch_bounds__(kScanThreads)
             w[4 * piece + 2] = v.z;
             w[4 * piece + 3] = v.w;
         }
-        // look-ahead word = first word of the next chunk: the neighbouring row of the tile, or global memory
+        // look-ahead = first 8 bytes of the next chunk: the neighbouring row of the tile, or global memory
         if (tid + 1 < kScanThreads)
-            w[kChunkBytes / 4] = *reinterpret_cast<uint32_t const *>(row + kChunkBytes + ((0 ^ ((tid + 1) & 7)) << 4));
+        {
+            uint2 la = *reinterpret_cast<uint2 const *>(row + kChunkBytes + ((0 ^ ((tid + 1) & 7)) << 4));
+            w[kChunkBytes / 4] = la.x;
+            w[kChunkBytes / 4 + 1] = la.y;
+        }
+        else if (g_lo + kChunkBytes + 8 <= p.n_text_padded)
+        {
+            uint2 la = __ldg(reinterpret_cast<uint2 const *>(p.text + g_lo + kChunkBytes));
+            w[kChunkBytes / 4] = la.x;
+            w[kChunkBytes / 4 + 1] = la.y;
+        }
         else
-            w[kChunkBytes / 4] = (g_lo + kChunkBytes + 4 <= p.n_text_padded)
-                                     ? __ldg(reinterpret_cast<uint32_t const *>(p.text + g_lo + kChunkBytes))
-                                     : 0u;
+        {
+            w[kChunkBytes / 4] = w[kChunkBytes / 4 + 1] = 0;
+        }
         uint32_t piece_hits = 0; // bit i = piece i holds a candidate
 #pragma unroll
         for (int piece = 0; piece < kChunkBytes / 16; ++piece)
@@ -654,10 +666,14 @@ __global__ void __launch_bounds__(kScanThreads)
 #pragma unroll
             for (int q = 4 * piece; q < 4 * piece + 4; ++q)
             {
-                uint32_t u = w[q] ^ X[0];
+                uint32_t u = 0;
 #pragma unroll
-                for (int j = 1; j < NL; ++j)
-                    u |= __funnelshift_r(w[q], w[q + 1], D[j]) ^ X[j];
+                for (int j = 0; j < NL; ++j)
+                {
+                    constexpr int dummy = 0;
+                    int const base = q + (j >= NA ? 1 : 0) + dummy; // second half of the window = next word
+                    u |= __funnelshift_r(w[base], w[base + 1], D[j]) ^ X[j];
+                }
                 acc |= (u - 0x01010101u) & ~u & 0x80808080u;
             }
             if (acc)

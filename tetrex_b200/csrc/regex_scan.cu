@@ -211,11 +211,11 @@ int launch_phase1_w(trx_ctx * c, scan_params const & sp, CUtensorMap const & tma
     return use_tma ? launch_phase1<W, 1, true>(c, sp, tmap) : launch_phase1<W, 1, false>(c, sp, tmap);
 }
 
-template <int NL>
+template <int NA, int NB>
 int launch_filter(trx_ctx * c, scan_params const & sp, CUtensorMap const & tmap)
 {
     size_t smem = kStages * kTileBytes + 2 * sizeof(uint64_t);
-    auto kern = regex_filter_simd<NL>;
+    auto kern = regex_filter_simd<NA, NB>;
     TRX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
     int per_sm = 0;
     TRX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kScanThreads, smem));
@@ -226,6 +226,31 @@ int launch_filter(trx_ctx * c, scan_params const & sp, CUtensorMap const & tmap)
     ++c->launches;
     TRX_CUDA(cudaGetLastError());
     return TRX_OK;
+}
+
+template <int NA>
+int launch_filter_a(trx_ctx * c, scan_params const & sp, CUtensorMap const & tmap)
+{
+    switch (sp.filter.n_b)
+    {
+    case 0: return launch_filter<NA, 0>(c, sp, tmap);
+    case 1: return launch_filter<NA, 1>(c, sp, tmap);
+    case 2: return launch_filter<NA, 2>(c, sp, tmap);
+    case 3: return launch_filter<NA, 3>(c, sp, tmap);
+    default: return launch_filter<NA, 4>(c, sp, tmap);
+    }
+}
+
+int launch_filter_any(trx_ctx * c, scan_params const & sp, CUtensorMap const & tmap)
+{
+    switch (sp.filter.n_a)
+    {
+    case 0: return launch_filter_a<0>(c, sp, tmap);
+    case 1: return launch_filter_a<1>(c, sp, tmap);
+    case 2: return launch_filter_a<2>(c, sp, tmap);
+    case 3: return launch_filter_a<3>(c, sp, tmap);
+    default: return launch_filter_a<4>(c, sp, tmap);
+    }
 }
 
 template <int W>
@@ -262,7 +287,7 @@ struct bits128
 // Derives the necessary factor of filter_spec from the automaton's level sets: L_0 = First,
 // L_{j+1} = Follow(L_j); every match has a byte of class(L_j) at offset j as long as no shorter match exists.
 // Offsets whose class is a single raw byte are literals; the best window of 4 consecutive offsets (by the
-// text's measured byte frequencies) becomes the filter.  n_literals = 0 if nothing selective enough exists.
+// text's measured byte frequencies) becomes the filter.  n_a = n_b = 0 if nothing selective enough exists.
 filter_spec derive_filter(regex_dev const & img, double const * freq, bool reverse)
 {
     filter_spec fs{};
@@ -297,40 +322,51 @@ filter_spec derive_filter(regex_dev const & img, double const * freq, bool rever
             }
         L = next;
     }
+    // best window of 8 consecutive offsets: take literals rarest-first until the expected candidate rate is low
+    constexpr double kGoodEnough = 2e-5, kTooWeak = 1e-3;
     double best = 1.0;
     int best_a = -1;
+    uint32_t best_mask = 0;
     for (int a = 0; a < depths; ++a)
     {
-        double prod = 1.0;
-        int n = 0;
-        for (int j = a; j < a + 4 && j < depths; ++j)
+        int order[8], n = 0;
+        for (int j = a; j < a + 8 && j < depths; ++j)
             if (literal[j] >= 0)
-            {
-                prod *= std::max(freq[literal[j]], 1e-4);
-                ++n;
-            }
-        if (n >= 2 && prod < best)
+                order[n++] = j;
+        std::sort(order, order + n, [&](int x, int y) { return freq[literal[x]] < freq[literal[y]]; });
+        double prod = 1.0;
+        uint32_t mask = 0;
+        for (int i = 0; i < n && prod > kGoodEnough; ++i)
+        {
+            prod *= std::max(freq[literal[order[i]]], 1e-4);
+            mask |= 1u << (order[i] - a);
+        }
+        // prefer the cheaper filter among equally good ones
+        if (mask && (prod < best && (best > kGoodEnough || __builtin_popcount(mask) < __builtin_popcount(best_mask))))
         {
             best = prod;
             best_a = a;
+            best_mask = mask;
         }
     }
-    if (best_a < 0 || best > 1e-3) // weaker than ~1 candidate per 8 chunks: the exact automaton is the better filter
+    if (best_a < 0 || best > kTooWeak) // weaker than ~1 candidate per 8 chunks: the exact automaton is the better filter
         return fs;
-    int ds[4], n = 0;
-    for (int j = best_a; j < best_a + 4 && j < depths; ++j)
-        if (literal[j] >= 0)
-            ds[n++] = j;
-    fs.n_literals = n;
-    // literal 0 = lowest address: smallest depth when reading forward, largest when reading backwards
-    for (int j = 0; j < n; ++j)
+    // window byte 0 = lowest address: offset best_a when reading forward, best_a + 7 when reading backwards
+    int n = 0;
+    for (int off = 0; off < 8; ++off)
     {
-        int d = reverse ? ds[n - 1 - j] : ds[j];
-        int d0 = reverse ? ds[n - 1] : ds[0];
-        fs.delta[j] = static_cast<uint32_t>(reverse ? d0 - d : d - d0);
-        fs.splat[j] = 0x01010101u * static_cast<uint32_t>(literal[d]);
+        int const d = reverse ? best_a + 7 - off : best_a + off;
+        if (d < best_a || d >= best_a + 8 || !((best_mask >> (d - best_a)) & 1))
+            continue;
+        fs.delta[n] = static_cast<uint32_t>(off & 3);
+        fs.splat[n] = 0x01010101u * static_cast<uint32_t>(literal[d]);
+        if (off < 4)
+            ++fs.n_a;
+        else
+            ++fs.n_b;
+        ++n;
     }
-    fs.start_delta = reverse ? ds[n - 1] : -ds[0];
+    fs.start_delta = reverse ? best_a + 7 : -best_a;
     return fs;
 }
 
@@ -461,16 +497,9 @@ int trx_regex_scan(trx_text_t * t, trx_regex_t * re, const uint64_t * candidate_
     if (use_tma && !(filt && strcmp(filt, "off") == 0))
         sp.filter = derive_filter(*img, t->byte_freq, reverse);
     if (stats)
-        stats[1] = static_cast<uint64_t>(sp.filter.n_literals);
-    if (sp.filter.n_literals >= 2)
-    {
-        switch (sp.filter.n_literals)
-        {
-        case 2: TRX_TRY(launch_filter<2>(c, sp, t->tmap)); break;
-        case 3: TRX_TRY(launch_filter<3>(c, sp, t->tmap)); break;
-        default: TRX_TRY(launch_filter<4>(c, sp, t->tmap)); break;
-        }
-    }
+        stats[1] = static_cast<uint64_t>(sp.filter.n_a + sp.filter.n_b);
+    if (sp.filter.n_a + sp.filter.n_b >= 1)
+        TRX_TRY(launch_filter_any(c, sp, t->tmap));
     else if (re->words == 1)
         TRX_TRY(launch_phase1_w<1>(c, sp, t->tmap, reverse, use_tma));
     else
