@@ -309,9 +309,12 @@ class Text:
         """Returns an (n,4) uint32 array of (bin, record, start, end) in reference print order."""
         words = (self.n_bins + 63) // 64
         if candidate_bins is None:
-            cand = np.zeros(words, dtype=np.uint64)
-            for b in range(self.n_bins):
-                cand[b >> 6] |= np.uint64(1) << np.uint64(b & 63)
+            if getattr(self, "_all_bins", None) is None:
+                cand = np.full(words, np.uint64(2 ** 64 - 1), dtype=np.uint64)
+                if self.n_bins % 64:
+                    cand[-1] = np.uint64((1 << (self.n_bins % 64)) - 1)
+                self._all_bins = cand
+            cand = self._all_bins
         else:
             cand = _np(candidate_bins, np.uint64)
             assert len(cand) == words
