@@ -518,53 +518,82 @@ __device__ int64_t match_first(regex_dev const & re, At at, int64_t s, int64_t L
     return best;
 }
 
-// One thread per record that phase 1 listed; the list length is read from device memory, so no host round
-// trip separates the two phases.
+// One WARP per record that phase 1 listed (the list length is read from device memory, so no host round trip
+// separates the two phases).  The 32 lanes try 32 consecutive start positions at once — almost all die on the
+// first byte — and a ballot picks the leftmost start that really matches; the warp then jumps to the end of
+// that match (FindAndConsume) and goes on.  Chunks phase 1 did not flag are skipped whole.
 template <int W, int DIR>
 __global__ void __launch_bounds__(128) regex_scan_phase2(resolve_params p)
 {
-    regex_dev const & re = *p.re;
+    __shared__ regex_dev s_re; // the automaton, staged once per CTA: every attempt starts with a B[] lookup
+    {
+        uint32_t const * src = reinterpret_cast<uint32_t const *>(p.re);
+        uint32_t * dst = reinterpret_cast<uint32_t *>(&s_re);
+        for (unsigned i = threadIdx.x; i < sizeof(regex_dev) / 4; i += blockDim.x)
+            dst[i] = src[i];
+    }
+    __syncthreads();
+    regex_dev const & re = s_re;
+    unsigned const lane = threadIdx.x & 31;
     uint64_t const n_listed = *p.rec_count;
-    for (uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n_listed;
-         i += static_cast<uint64_t>(gridDim.x) * blockDim.x)
+    uint64_t const warp0 = (static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+    uint64_t const n_warps = (static_cast<uint64_t>(gridDim.x) * blockDim.x) >> 5;
+    for (uint64_t i = warp0; i < n_listed; i += n_warps)
     {
         uint64_t const r = p.rec_list[i];
         uint64_t const rb = p.rec_offsets[r], re_off = p.rec_offsets[r + 1];
         int64_t const L = static_cast<int64_t>(re_off - rb);
         auto at = [&](int64_t pos) -> uint8_t
         { return DIR > 0 ? p.text[rb + pos] : p.text[re_off - 1 - pos]; };
-        auto chunk_of = [&](int64_t pos) -> uint64_t
-        { return (DIR > 0 ? rb + pos : re_off - 1 - pos) / kChunkBytes; };
+        auto addr_of = [&](int64_t pos) -> uint64_t
+        { return DIR > 0 ? rb + pos : re_off - 1 - pos; };
 
-        int64_t s = 0;
+        int64_t s = 0; // warp-uniform
         while (s < L)
         {
-            uint64_t const ch = chunk_of(s);
+            uint64_t const ch = addr_of(s) / kChunkBytes;
+            // first position (reading direction) that lies in the next chunk
+            int64_t const next_chunk = DIR > 0 ? static_cast<int64_t>((ch + 1) * kChunkBytes - rb)
+                                               : static_cast<int64_t>(re_off) - static_cast<int64_t>(ch * kChunkBytes);
             if (!re.anchor_begin && !((p.chunk_flags[ch >> 5] >> (ch & 31)) & 1))
             {
-                // no match starts anywhere in this chunk: jump to the first position of the next one
-                if constexpr (DIR > 0)
-                    s = static_cast<int64_t>((ch + 1) * kChunkBytes - rb);
-                else
-                    s = static_cast<int64_t>(re_off) - static_cast<int64_t>(ch * kChunkBytes); // ch == 0 ⇒ s >= L, loop ends
+                s = next_chunk; // no match starts anywhere in this chunk
                 continue;
             }
-            int64_t e = re.posix_longest ? match_longest<W>(re, at, s, L) : match_first(re, at, s, L);
-            if (e > s)
+            int64_t const limit = next_chunk < L ? next_chunk : L;
+            int64_t const my_s = s + lane;
+            int64_t e = -1;
+            if (my_s < limit && (!re.anchor_begin || lane == 0))
             {
-                unsigned long long idx = atomicAdd(p.hit_count, 1ULL);
-                if (idx < p.cap)
+                uint8_t const c = at(my_s);
+                uint64_t quick = 0;
+#pragma unroll
+                for (int k = 0; k < W; ++k)
+                    quick |= re.first[k] & re.B[c][k];
+                if (quick)
+                    e = re.posix_longest ? match_longest<W>(re, at, my_s, L) : match_first(re, at, my_s, L);
+            }
+            unsigned const found = __ballot_sync(0xffffffffu, e > my_s);
+            if (found)
+            {
+                int const leader = __ffs(found) - 1;
+                int64_t const e_hit = __shfl_sync(0xffffffffu, e, leader);
+                if (lane == 0)
                 {
-                    p.hit_keys[idx] = (r << 32) | static_cast<uint64_t>(s);
-                    p.hit_ends[idx] = static_cast<uint32_t>(e);
+                    unsigned long long idx = atomicAdd(p.hit_count, 1ULL);
+                    if (idx < p.cap)
+                    {
+                        p.hit_keys[idx] = (r << 32) | static_cast<uint64_t>(s + leader);
+                        p.hit_ends[idx] = static_cast<uint32_t>(e_hit);
+                    }
                 }
-                s = e; // FindAndConsume: the next search starts where this match ended
+                s = e_hit; // FindAndConsume: the next search starts where this match ended
             }
             else
             {
                 if (re.anchor_begin)
                     break; // '^' can only match at the resume point
-                ++s;
+                s = (s + 32 < limit) ? s + 32 : limit;
             }
         }
     }

@@ -27,7 +27,7 @@ struct trx_text
     CUtensorMap tmap{};
     bool has_tmap{false};
     // per-scan scratch
-    trx::scratch d_stage, h_stage, d_counter, d_keys, d_ends, d_keys2, d_ends2, d_sort_tmp;
+    trx::scratch d_stage, h_stage, h_small, d_counter, d_keys, d_ends, d_keys2, d_ends2, d_sort_tmp;
 };
 
 using namespace trx;
@@ -175,7 +175,7 @@ void trx_text_destroy(trx_text_t * t)
     cudaFree(t->d_chunk_flags);
     cudaFree(t->d_rec_flags);
     cudaFree(t->d_rec_list);
-    for (trx::scratch * s : {&t->d_stage, &t->h_stage, &t->d_counter, &t->d_keys, &t->d_ends, &t->d_keys2, &t->d_ends2,
+    for (trx::scratch * s : {&t->d_stage, &t->h_stage, &t->h_small, &t->d_counter, &t->d_keys, &t->d_ends, &t->d_keys2, &t->d_ends2,
                              &t->d_sort_tmp})
         s->release();
     delete t;
@@ -191,11 +191,14 @@ int launch_phase1(trx_ctx * c, scan_params const & sp, CUtensorMap const & tmap)
 {
     size_t smem = (USE_TMA ? kStages * kTileBytes : 0) + sizeof(scan_tables<W>) + 2 * sizeof(uint64_t);
     auto kern = regex_scan_phase1<W, DIR, USE_TMA>;
-    TRX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-    int per_sm = 0;
-    TRX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kScanThreads, smem));
-    if (per_sm < 1)
-        per_sm = 1;
+    static int per_sm = 0; // per template instantiation: attribute + occupancy are queried once
+    if (per_sm == 0)
+    {
+        TRX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+        int q = 0;
+        TRX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&q, kern, kScanThreads, smem));
+        per_sm = q < 1 ? 1 : q;
+    }
     unsigned grid = static_cast<unsigned>(std::min<uint64_t>(sp.n_tiles, static_cast<uint64_t>(c->sm_count) * per_sm));
     kern<<<grid, kScanThreads, smem, c->stream>>>(sp, tmap);
     ++c->launches;
@@ -216,11 +219,14 @@ int launch_filter(trx_ctx * c, scan_params const & sp, CUtensorMap const & tmap)
 {
     size_t smem = kStages * kTileBytes + 2 * sizeof(uint64_t);
     auto kern = regex_filter_simd<NA, NB>;
-    TRX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-    int per_sm = 0;
-    TRX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kScanThreads, smem));
-    if (per_sm < 1)
-        per_sm = 1;
+    static int per_sm = 0;
+    if (per_sm == 0)
+    {
+        TRX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+        int q = 0;
+        TRX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&q, kern, kScanThreads, smem));
+        per_sm = q < 1 ? 1 : q;
+    }
     unsigned grid = static_cast<unsigned>(std::min<uint64_t>(sp.n_tiles, static_cast<uint64_t>(c->sm_count) * per_sm));
     kern<<<grid, kScanThreads, smem, c->stream>>>(sp, tmap);
     ++c->launches;
@@ -521,14 +527,41 @@ int trx_regex_scan(trx_text_t * t, trx_regex_t * re, const uint64_t * candidate_
     else
         TRX_TRY(launch_phase2_w<2>(c, rp, reverse));
 
-    unsigned long long total = 0;
-    TRX_CUDA(cudaMemcpyAsync(&total, t->d_counter.ptr, 8, cudaMemcpyDeviceToHost, c->stream));
+    // ---- read back: the hit count and, speculatively, the first kSmall hits in the same round trip
+    constexpr uint64_t kSmall = 1024;
+    uint64_t const spec = cap < kSmall ? cap : kSmall;
+    t->h_small.pinned_host = true;
+    TRX_TRY(t->h_small.reserve(16 + kSmall * 12));
+    auto * h_total = static_cast<unsigned long long *>(t->h_small.ptr);
+    auto * h_keys = reinterpret_cast<uint64_t *>(static_cast<uint8_t *>(t->h_small.ptr) + 16);
+    auto * h_ends = reinterpret_cast<uint32_t *>(static_cast<uint8_t *>(t->h_small.ptr) + 16 + kSmall * 8);
+    TRX_CUDA(cudaMemcpyAsync(h_total, t->d_counter.ptr, 8, cudaMemcpyDeviceToHost, c->stream));
+    if (spec)
+    {
+        TRX_CUDA(cudaMemcpyAsync(h_keys, rp.hit_keys, spec * 8, cudaMemcpyDeviceToHost, c->stream));
+        TRX_CUDA(cudaMemcpyAsync(h_ends, rp.hit_ends, spec * 4, cudaMemcpyDeviceToHost, c->stream));
+    }
     TRX_CUDA(cudaStreamSynchronize(c->stream));
+    unsigned long long const total = *h_total;
     *n_hits = total;
     if (total > cap)
         return set_error(TRX_ECAPACITY, "trx_regex_scan: %llu hits, room for %llu", total, (unsigned long long)cap);
     if (total == 0)
         return TRX_OK;
+    if (total <= spec)
+    {
+        // a handful of hits: put them into print order right here instead of launching a device sort
+        std::vector<std::pair<uint64_t, uint32_t>> v(total);
+        for (uint64_t i = 0; i < total; ++i)
+            v[i] = {h_keys[i], h_ends[i]};
+        std::sort(v.begin(), v.end());
+        for (uint64_t i = 0; i < total; ++i)
+        {
+            uint32_t rec = static_cast<uint32_t>(v[i].first >> 32);
+            hits[i] = trx_hit{t->h_rec_bin[rec], rec, static_cast<uint32_t>(v[i].first), v[i].second};
+        }
+        return TRX_OK;
+    }
 
     // ---- order = (bin, record, start): records are grouped by ascending bin, so (record, start) suffices
     uint64_t const n = total;
