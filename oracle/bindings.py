@@ -411,3 +411,45 @@ class RefHIBF:
         if n < 0:
             raise ValueError(ref().ref_last_error().decode())
         return out
+
+
+def ref_kgraph(regex: str, molecule: int, k: int, reduction: int = 0):
+    """The k-graph the reference builds (construct_kgraph / construct_reduced_kgraph + determine_top_sort):
+    (postfix, [(symbol, first, second, rank) per node id]) or None if the reference threw."""
+    cap = 1 << 17
+    sym = np.zeros(cap, dtype=np.int32)
+    fi = np.zeros(cap, dtype=np.int32)
+    se = np.zeros(cap, dtype=np.int32)
+    rk = np.zeros(cap, dtype=np.int32)
+    pf = C.create_string_buffer(1 << 16)
+    i32p = C.POINTER(C.c_int32)
+    n = ref().ref_kgraph(regex.encode(), molecule, k, reduction, 0, sym.ctypes.data_as(i32p), fi.ctypes.data_as(i32p),
+                         se.ctypes.data_as(i32p), rk.ctypes.data_as(i32p), cap, pf, 1 << 16)
+    if n < 0:
+        return None
+    return pf.value.decode(), [[int(sym[i]), int(fi[i]), int(se[i]), int(rk[i])] for i in range(n)]
+
+
+def ref_index_build(files, k, fpr, hash_count, molecule, flavor, reduction, out_path, threads=1):
+    """drive_index's work with the reference's own classes: flavor 0 = flat IBF, 1 = HIBF. Writes out_path."""
+    arr = (C.c_char_p * len(files))(*[f.encode() for f in files])
+    rc = ref().ref_index_build(arr, len(files), k, fpr, hash_count, molecule, flavor, reduction, threads, out_path.encode())
+    if rc != 0:
+        raise RuntimeError(ref().ref_last_error().decode())
+
+
+def ref_index_query(index_path, regex, verify=True, threads=1, stdout_path=None):
+    """process_query (+ iter_disk_search) of the reference on an index file: (hit words, captured stdout)."""
+    import tempfile
+    words = np.zeros(1 << 14, dtype=np.uint64)
+    tmp = stdout_path or tempfile.mktemp(prefix="ref_stdout_")
+    n = ref().ref_index_query(index_path.encode(), regex.encode(), 0, 1 if verify else 0, threads, _p(words, u64p), len(words),
+                              tmp.encode())
+    if n < 0:
+        raise RuntimeError(ref().ref_last_error().decode())
+    text = ""
+    if verify and os.path.exists(tmp):
+        text = open(tmp).read()
+        if stdout_path is None:
+            os.unlink(tmp)
+    return words[:n].copy(), text

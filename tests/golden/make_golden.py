@@ -98,10 +98,140 @@ def golden_regex():
     json.dump(cases, open(os.path.join(OUT, "regex.json"), "w"))
 
 
+def golden_kgraph():
+    """k-graphs of the reference (node symbols, two-slot arc map, ranks) for the host layer's construct_kgraph."""
+    cases = []
+    fixed = [("LMA(E|Q)GLYN", 1, 3, 0), ("LMA(E|Q)GLYN", 1, 6, 0), ("AC*GT", 1, 3, 0), ("A(CD)+EF", 1, 4, 0),
+             ("AC{2,4}DE", 1, 3, 0), ("(AC){3}DEF", 1, 3, 0), ("AC?D.EF", 1, 3, 0), ("A[CD]E[^FG]HIK", 1, 3, 0),
+             (".*ACDEF.{2}", 1, 4, 0), ("ACGT(A|C)T+G", 0, 4, 0), ("LMAEGLYN", 1, 3, 1), ("L.{0,2}MAC", 1, 3, 0),
+             ("AC{0,1}DEF", 1, 3, 0), ("A(C|D)*EFG", 1, 3, 0), ("(A|C)(D|E)(F|G)HIK", 1, 4, 2), ("AB{3}", 1, 3, 0),
+             ("A{2,3}(CD){1,2}EF", 1, 3, 0), ("^MK.*LL$", 1, 2, 0), ("C.{2,4}C.{3}[LIVMFYWC].{8}H.{3,5}H", 1, 3, 0),
+             ("TATA[AT]A[AT](A|G)", 0, 5, 0), ("GG(ACT)+CC", 0, 6, 0), ("LM[AG]EGLYN", 1, 4, 1), ("W(KR|DE)LY?N", 1, 3, 2)]
+    rng = random.Random(5)
+
+    def gen(alpha, depth):
+        r = rng.random()
+        if depth == 0 or r < 0.45:
+            return "".join(rng.choice(alpha) for _ in range(rng.randint(1, 4)))
+        if r < 0.6:
+            return "(" + gen(alpha, depth - 1) + "|" + gen(alpha, depth - 1) + ")"
+        if r < 0.72:
+            inner = "(" + gen(alpha, depth - 1) + ")" if rng.random() < 0.5 else rng.choice(alpha)
+            return inner + rng.choice(["*", "+", "?", "{2}", "{1,3}", "{0,2}", "{3}", "{2,4}", "{0,1}"])
+        if r < 0.82:
+            return "[" + "".join(rng.sample(alpha, rng.randint(1, 3))) + "]"
+        return gen(alpha, depth - 1) + gen(alpha, depth - 1)
+
+    for _ in range(60):
+        mol = rng.choice([0, 1])
+        alpha = "ACGT" if mol == 0 else AA.decode()
+        fixed.append(("".join(gen(alpha, 2) for _ in range(rng.randint(1, 3))), mol, rng.choice([2, 3, 4, 5, 6]), 0))
+    for rx, mol, k, red in fixed:
+        got = ob.ref_kgraph(rx, mol, k, red)
+        assert got is not None, rx
+        cases.append({"regex": rx, "molecule": mol, "k": k, "reduction": red, "postfix": got[0], "nodes": got[1]})
+    with open(os.path.join(OUT, "kgraph.json"), "w") as f:
+        json.dump(cases, f, separators=(",", ":"))
+    print("kgraph.json:", len(cases), "cases")
+
+
+CLI_QUERIES_AA = ["LMA(E|Q)GLYN", "WKC(DE)+FH", "MK[AG]PLW", "HHC.{2}CW", "AAAAAAA", "^MKTA", "C.{2,4}C.{3}[LIVMFYWC]", "G(LY|QP)NW?K",
+                  "KR{2}T", "PW(AC|DE|FG)HI*K"]
+CLI_QUERIES_NA = ["TATAAAAG", "GG(ACT)+CC", "ACGTAC(GG|TT)AC", "TTTTTTTTTT", "CAT[AC]GATTACA", "GAT{2,3}ACA"]
+
+
+def write_bins(rng, directory, prefix, alphabet, n_bins, n_records, length, motifs):
+    """Deterministic synthetic FASTA bins (committed under tests/data/): random residues with planted motifs."""
+    os.makedirs(directory, exist_ok=True)
+    files = []
+    for b in range(n_bins):
+        path = os.path.join(directory, f"{prefix}_{b}.fa")
+        with open(path, "w") as f:
+            for r in range(n_records):
+                n = rng.randint(length // 2, length)
+                seq = bytearray(rand_seq(rng, alphabet, n))
+                for m in motifs:
+                    if rng.random() < 0.08:
+                        at = rng.randint(0, max(0, n - len(m)))
+                        seq[at:at + len(m)] = m
+                if b == 2 and r == 1:
+                    seq = seq[:3]  # shorter than k: "RECORD TOO SHORT"
+                f.write(f">{prefix}{b}_{r} synthetic record {r} of bin {b}\n")
+                for i in range(0, len(seq), 60):
+                    f.write(seq[i:i + 60].decode() + "\n")
+        files.append(os.path.relpath(path, ROOT))
+    return files
+
+
+def guarded(fn, *args):
+    """Runs fn in a forked child: the reference aborts the process on some inputs (documented in DESIGN.md)."""
+    import pickle
+    r, w = os.pipe()
+    pid = os.fork()
+    if pid == 0:
+        os.close(r)
+        try:
+            os.write(w, pickle.dumps(fn(*args)))
+        finally:
+            os._exit(0)
+    os.close(w)
+    data = b""
+    while True:
+        chunk = os.read(r, 1 << 16)
+        if not chunk:
+            break
+        data += chunk
+    os.close(r)
+    _, status = os.waitpid(pid, 0)
+    return pickle.loads(data) if status == 0 and data else None
+
+
+def golden_cli():
+    """End-to-end fixtures for the host layer (tetrex index / query): the reference builds indexes over
+    tests/data/* and answers a list of queries; index files, candidate bins and printed lines are committed."""
+    rng = random.Random(2024)
+    data = os.path.join(ROOT, "tests", "data")
+    aa_motifs = [b"LMAEGLYN", b"LMAQGLYN", b"WKCDEDEFH", b"MKAPLW", b"HHCAKCW", b"AAAAAAAA", b"GLYNWK", b"GQPNK", b"KRRT",
+                 b"PWDEHIIK", b"CAACLLLV", b"MKTA"]
+    na_motifs = [b"TATAAAAG", b"GGACTACTCC", b"CTTTATA", b"ACGTACGGAC", b"GGAGTAGTCC", b"CATAGATTACA", b"TGTAATCGATG", b"GATTTACA"]
+    aa_files = write_bins(rng, data, "pep", AA, 12, 6, 240, aa_motifs)
+    na_files = write_bins(rng, data, "dna", b"ACGT", 9, 4, 400, na_motifs)
+    big_files = write_bins(rng, data, "wide", AA, 70, 2, 120, aa_motifs)  # > 64 user bins: two-level HIBF
+    cwd = os.getcwd()
+    os.chdir(ROOT)  # indexes store the paths relative to the repo root
+    out = []
+    try:
+        for name, files, mol, k, flavor, red, queries in [
+                ("pep_flat_k4", aa_files, 1, 4, 0, 0, CLI_QUERIES_AA), ("pep_hibf_k4", aa_files, 1, 4, 1, 0, CLI_QUERIES_AA),
+                ("pep_flat_k3_murphy", aa_files, 1, 3, 0, 1, ["LMAEGLYN", "MKAPLW", "WKCDEDEFH"]),
+                ("dna_flat_k6", na_files, 0, 6, 0, 0, CLI_QUERIES_NA), ("dna_hibf_k8", na_files, 0, 8, 1, 0, CLI_QUERIES_NA),
+                ("wide_hibf_k4", big_files, 1, 4, 1, 0, CLI_QUERIES_AA[:5])]:
+            idx = os.path.join("tests", "golden", "cli", name + ".ibf")
+            os.makedirs(os.path.dirname(idx), exist_ok=True)
+            ob.ref_index_build(files, k, 0.05, 3, mol, flavor, red, idx)
+            for q in queries:
+                got = guarded(ob.ref_index_query, idx, q, True)
+                if got is None:
+                    print("reference aborts on", name, q)
+                    out.append(dict(index=idx, files=files, molecule=mol, k=k, flavor=flavor, reduction=red, regex=q,
+                                    reference_aborts=True))
+                    continue
+                words, text = got
+                bins = [b for b in range(len(files)) if int(words[b // 64]) >> (b % 64) & 1]
+                out.append(dict(index=idx, files=files, molecule=mol, k=k, flavor=flavor, reduction=red, regex=q, bins=bins,
+                                stdout=text))
+    finally:
+        os.chdir(cwd)
+    json.dump(out, open(os.path.join(OUT, "cli.json"), "w"), indent=0)
+    print("cli.json:", len(out), "queries,", sum(len(c.get("stdout", "").splitlines()) for c in out), "lines")
+
+
 if __name__ == "__main__":
     assert ob.have_ref(), "build oracle/_ref first: make -C oracle ref"
     golden_decompose()
     golden_ibf()
     golden_hibf()
     golden_regex()
+    golden_kgraph()
+    golden_cli()
     print("golden vectors written to", OUT)

@@ -1,0 +1,120 @@
+"""Host C++ layer (tetrex_b200/host) on the CPU: regex front end + k-graph against the reference's k-graphs
+(tests/golden/kgraph.json, made by tests/golden/make_golden.py from oracle/_ref), index-file reader against the
+reference-written files in tests/golden/cli/.  No kernels run here; the `tetrex` binary is built by
+__graft_entry__.build()."""
+import json
+import os
+import random
+import subprocess
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+TETREX = os.path.join(ROOT, "tetrex_b200", "bin", "tetrex")
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+
+@pytest.fixture(scope="module")
+def tetrex():
+    if not os.path.exists(TETREX):
+        import __graft_entry__
+        __graft_entry__.build()
+    assert os.path.exists(TETREX), "host layer did not build"
+    return TETREX
+
+
+def run_kgraph(tetrex, regex, molecule, k, reduction):
+    args = [tetrex, "kgraph", "-k", str(k)]
+    if molecule == 0:
+        args.append("-n")
+    if reduction:
+        args += ["-r", ["", "murphy", "li"][reduction]]
+    args.append(regex)
+    out = subprocess.run(args, capture_output=True, text=True, timeout=60)
+    if out.returncode != 0:
+        return None
+    lines = out.stdout.split("\n")
+    postfix = lines[0].split("\t")[1]
+    n = int(lines[1].split("\t")[1])
+    return postfix, [[int(x) for x in line.split("\t")[1:]] for line in lines[2:2 + n]]
+
+
+def test_kgraph_matches_reference_golden(tetrex):
+    cases = json.load(open(os.path.join(GOLDEN, "kgraph.json")))
+    assert len(cases) >= 80
+    for c in cases:
+        got = run_kgraph(tetrex, c["regex"], c["molecule"], c["k"], c["reduction"])
+        assert got is not None, c["regex"]
+        assert got[0] == c["postfix"], c["regex"]
+        assert got[1] == c["nodes"], (c["regex"], c["k"])
+
+
+def test_kgraph_fuzz_against_compiled_reference(tetrex):
+    """Live comparison with oracle/_ref (present in the dev container and shipped to the GPU box as a built .so)."""
+    from oracle import bindings as ob
+    if not ob.have_ref():
+        pytest.skip("oracle/_ref not built")
+    rng = random.Random(99)
+
+    def gen(alpha, depth):
+        r = rng.random()
+        if depth == 0 or r < 0.45:
+            return "".join(rng.choice(alpha) for _ in range(rng.randint(1, 4)))
+        if r < 0.6:
+            return "(" + gen(alpha, depth - 1) + "|" + gen(alpha, depth - 1) + ")"
+        if r < 0.72:
+            inner = "(" + gen(alpha, depth - 1) + ")" if rng.random() < 0.5 else rng.choice(alpha)
+            return inner + rng.choice(["*", "+", "?", "{2}", "{1,3}", "{0,2}", "{3}", "{2,4}"])
+        if r < 0.8:
+            return "[" + "".join(rng.sample(alpha, rng.randint(1, 3))) + "]"
+        if r < 0.86 and len(alpha) > 4:
+            return rng.choice([".", "[^" + "".join(rng.sample(alpha, 2)) + "]", ".{2}"])
+        return gen(alpha, depth - 1) + gen(alpha, depth - 1)
+
+    for _ in range(60):
+        mol = rng.choice([0, 1])
+        alpha = "ACGT" if mol == 0 else "ACDEFGHIKLMNPQRSTVWY"
+        k = rng.choice([2, 3, 4, 5, 6])
+        rx = "".join(gen(alpha, 2) for _ in range(rng.randint(1, 3)))
+        want = ob.ref_kgraph(rx, mol, k, 0)
+        got = run_kgraph(tetrex, rx, mol, k, 0)
+        if want is None:
+            continue
+        assert got is not None, rx
+        assert got[0] == want[0] and got[1] == want[1], (rx, mol, k)
+
+
+def test_kgraph_rejects_what_the_reference_cannot_build(tetrex):
+    # stack underflow / uninitialised nodes in the reference's reduced builder: a clean error here
+    assert run_kgraph(tetrex, "A{3}CD", 1, 3, 1) is None
+    assert run_kgraph(tetrex, ".R", 1, 5, 2) is None
+    out = subprocess.run([tetrex, "kgraph", "-k", "3", "-r", "li", ".R"], capture_output=True, text=True)
+    assert out.returncode == 1 and "[Error]" in out.stderr
+
+
+def test_inspect_reads_reference_written_indexes(tetrex):
+    cases = json.load(open(os.path.join(GOLDEN, "cli.json")))
+    seen = {}
+    for c in cases:
+        seen[c["index"]] = c
+    assert len(seen) >= 6
+    for idx, c in seen.items():
+        out = subprocess.run([tetrex, "inspect", idx], capture_output=True, text=True, cwd=ROOT, timeout=60)
+        assert out.returncode == 0, out.stderr
+        text = out.stdout
+        assert ("INDEX TYPE: HIBF" if c["flavor"] else "INDEX TYPE: IBF") in text
+        assert f"KMER LENGTH ({'bases' if c['molecule'] == 0 else 'residues'}): {c['k']}" in text
+        assert f"[REDUCTION={c['reduction']}]" in text
+        listed = [line[3:] for line in text.splitlines() if line.startswith("\t- ")]
+        assert listed == c["files"]
+        if not c["flavor"]:
+            assert f"BIN COUNT (BFs): {len(c['files'])}" in text
+
+
+def test_query_reports_unreadable_index_like_the_reference(tetrex, tmp_path):
+    bad = tmp_path / "broken.ibf"
+    bad.write_bytes(b"\x04\x02\x00\x00")
+    out = subprocess.run([tetrex, "query", str(bad), "ACGT"], capture_output=True, text=True, timeout=60)
+    assert "Filepath to (H)IBF Index not valid" in out.stderr  # src/main.cpp:55
+    out = subprocess.run([tetrex, "index", "-k", "13", "x", "y.fa"], capture_output=True, text=True, timeout=60)
+    assert "Max kmer size for amino acids is 12" in out.stderr  # src/main.cpp:30

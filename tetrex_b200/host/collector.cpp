@@ -1,0 +1,252 @@
+// collector.cpp — OTFCollector::collect (include/otf_collector.h:341-393) as a level-synchronous batch producer.
+//
+// The reference walks the k-graph in topological rank order; all items of one rank sit on the same node, are
+// independent of each other and only write to higher ranks.  That is the batch boundary used here: per rank the
+// host decides WHAT happens (roll the k-mer, probe, push, absorb, split, match — identical rules: items are keyed
+// by (rank, kmer & submask), the first arrival's kmer/shift_count win, later arrivals only OR their path in) and
+// the device does it: one trx_paths_step launch probes every k-mer of the rank, ANDs the hit vectors into the
+// path slots and reports which paths died; one trx_paths_or launch performs every push-copy, absorb and match OR.
+// Path bitvectors never leave HBM; only the 1-byte alive flags travel.
+//
+// Known difference: inside one rank the reference pops items in robin_hood hash-table order, this code in
+// arrival order.  The order only matters when two items with DIFFERENT shift counts collide on the same
+// (rank, sub-k-mer) key (SURVEY.md §7 hard part 3); tests/test_collector_vs_ref.py fuzzes this against the
+// compiled reference.
+#include <algorithm>
+#include <unordered_map>
+
+#include "trx_host.hpp"
+
+namespace trxh
+{
+
+namespace
+{
+
+struct item
+{
+    uint8_t shift_count;
+    uint64_t kmer;
+    uint32_t slot;
+};
+
+struct bucket
+{
+    std::vector<item> items;
+    std::unordered_map<uint64_t, uint32_t> by_key; // kmer & submask → index into items
+};
+
+struct slot_pool
+{
+    trx_paths_t * paths{nullptr};
+    uint64_t words{}, capacity{}, next{};
+    ~slot_pool() { trx_paths_destroy(paths); }
+    uint32_t fresh()
+    {
+        if (next >= capacity)
+            throw error("regular expression too complex: more than " + std::to_string(capacity) +
+                        " live paths (try a more specific query)");
+        return static_cast<uint32_t>(next++);
+    }
+};
+
+// device scratch for the HIBF route (k-mers in, hit vectors out)
+struct dev_buffer
+{
+    trx_ctx_t * ctx;
+    void * ptr{nullptr};
+    uint64_t bytes{0};
+    explicit dev_buffer(trx_ctx_t * c) : ctx(c) {}
+    ~dev_buffer()
+    {
+        if (ptr)
+            trx_dev_free(ctx, ptr);
+    }
+    void reserve(uint64_t want)
+    {
+        if (want <= bytes)
+            return;
+        if (ptr)
+            check(trx_dev_free(ctx, ptr));
+        ptr = nullptr;
+        check(trx_dev_alloc(ctx, want + want / 2, &ptr));
+        bytes = want + want / 2;
+    }
+};
+
+} // namespace
+
+bitvector collect(kgraph const & g, DeviceIndex & index, collect_stats * stats)
+{
+    size_t const n_nodes = g.size();
+    uint64_t const bins = index.bin_count();
+    uint64_t const W = index.bin_words();
+    uint8_t const k = index.k();
+    unsigned const bits = index.is_dna() ? 2 : 5;
+    // create_selection_bitmask (otf_collector.h:168-182): the low (k-1) symbols
+    uint64_t submask = 0;
+    for (unsigned i = 0; i + 1 < k; ++i)
+        submask = (submask << bits) | ((1ull << bits) - 1);
+
+    slot_pool pool;
+    pool.words = W;
+    pool.capacity = std::max<uint64_t>(1ull << 12, std::min<uint64_t>(1ull << 20, (1ull << 28) / (W * 8)));
+    check(trx_paths_create(index.ctx(), W, pool.capacity, &pool.paths));
+    uint32_t const match_slot = pool.fresh(); // path_matrix = bitvector(bins): all clear (pool is zeroed)
+    uint32_t const start_slot = pool.fresh();
+    check(trx_paths_fill(pool.paths, start_slot, 1, bins)); // hit_vector = bitvector(bins, true)
+
+    std::vector<bucket> table(n_nodes);
+    std::vector<int> node_of_rank(n_nodes, -1);
+    for (size_t id = 0; id < n_nodes; ++id)
+        node_of_rank[g.rank[id]] = static_cast<int>(id);
+
+    std::vector<uint32_t> or_dst, or_src;
+    auto push = [&](int node, item it, bool may_hand_over) {
+        bucket & b = table[g.rank[node]];
+        uint64_t const key = it.kmer & submask;
+        auto found = b.by_key.find(key);
+        if (found != b.by_key.end())
+        {
+            // absorb (otf_collector.h:204-208): only the path is merged, kmer_/shift_count_ of the first arrival stay
+            or_dst.push_back(b.items[found->second].slot);
+            or_src.push_back(it.slot);
+            return;
+        }
+        if (!may_hand_over)
+        {
+            uint32_t copy = pool.fresh(); // zero → OR = copy
+            or_dst.push_back(copy);
+            or_src.push_back(it.slot);
+            it.slot = copy;
+        }
+        b.by_key.emplace(key, static_cast<uint32_t>(b.items.size()));
+        b.items.push_back(it);
+    };
+
+    push(0, item{0, 0, start_slot}, true);
+
+    dev_buffer d_kmers(index.ctx()), d_hits(index.ctx());
+    std::vector<uint64_t> probe_kmers;
+    std::vector<uint32_t> probe_slots, probe_item;
+    std::vector<uint8_t> alive;
+
+    for (size_t r = 0; r < n_nodes; ++r)
+    {
+        bucket & b = table[r];
+        if (b.items.empty())
+            continue;
+        int const node = node_of_rank[r];
+        int const sym = g.symbol[node];
+        or_dst.clear();
+        or_src.clear();
+        if (stats)
+        {
+            ++stats->ranks;
+            stats->items += b.items.size();
+        }
+        if (sym == Match)
+        {
+            for (item const & it : b.items)
+            {
+                or_dst.push_back(match_slot); // path_matrix |= top.path_
+                or_src.push_back(it.slot);
+            }
+        }
+        else if (sym == Ghost || sym == '$')
+        {
+            for (item const & it : b.items)
+                push(g.first[node], it, true);
+        }
+        else if (sym == Split)
+        {
+            for (item const & it : b.items)
+            {
+                push(g.first[node], it, false);
+                push(g.second[node], it, false);
+            }
+        }
+        else if (sym == Gap)
+        {
+            throw error("Gap nodes (-a augmentation) are not part of this build");
+        }
+        else
+        {
+            // update_path (otf_collector.h:247-279)
+            probe_kmers.clear();
+            probe_slots.clear();
+            probe_item.clear();
+            for (size_t i = 0; i < b.items.size(); ++i)
+            {
+                item & it = b.items[i];
+                if (it.shift_count + 1 < k)
+                {
+                    index.update_kmer(sym, it.kmer);
+                    ++it.shift_count;
+                    continue;
+                }
+                uint64_t const probe = index.update_kmer(sym, it.kmer);
+                if (it.shift_count + 1 == k)
+                    ++it.shift_count;
+                probe_kmers.push_back(probe);
+                probe_slots.push_back(it.slot);
+                probe_item.push_back(static_cast<uint32_t>(i));
+            }
+            alive.assign(b.items.size(), 1);
+            if (!probe_kmers.empty())
+            {
+                std::vector<uint8_t> res(probe_kmers.size());
+                if (!index.is_hibf())
+                {
+                    check(trx_paths_step(index.flat(), pool.paths, probe_kmers.data(), probe_slots.data(),
+                                         probe_kmers.size(), res.data()));
+                }
+                else
+                {
+                    uint64_t const n = probe_kmers.size();
+                    d_kmers.reserve(n * 8);
+                    d_hits.reserve(n * W * 8);
+                    check(trx_copy_h2d(index.ctx(), d_kmers.ptr, probe_kmers.data(), n * 8));
+                    check(trx_hibf_membership_dev(index.hibf(), static_cast<uint64_t *>(d_kmers.ptr), n,
+                                                  static_cast<uint64_t *>(d_hits.ptr), nullptr));
+                    std::vector<uint32_t> idx(n);
+                    for (uint64_t i = 0; i < n; ++i)
+                        idx[i] = static_cast<uint32_t>(i);
+                    check(trx_paths_and_hits(pool.paths, static_cast<uint64_t *>(d_hits.ptr), idx.data(),
+                                             probe_slots.data(), n, res.data()));
+                }
+                for (size_t j = 0; j < res.size(); ++j)
+                    alive[probe_item[j]] = res[j];
+                if (stats)
+                    stats->probes += probe_kmers.size();
+            }
+            for (size_t i = 0; i < b.items.size(); ++i)
+                if (alive[i]) // `if(top.path_.none()) break;` drops dead paths at once
+                    push(g.first[node], b.items[i], true);
+        }
+        if (!or_dst.empty())
+            check(trx_paths_or(pool.paths, or_dst.data(), or_src.data(), or_dst.size()));
+        b.items.clear();
+        b.by_key.clear();
+    }
+    bitvector out(W);
+    check(trx_paths_read(pool.paths, match_slot, 1, out.data()));
+    return out;
+}
+
+bitvector process_query(std::string const & regex, DeviceIndex & index, collect_stats * stats)
+{
+    // preprocess_query (include/query.h:80-94): peptides reduce (if the index is reduced) and trim, DNA only translates
+    std::string rx = regex;
+    if (!index.is_dna())
+    {
+        if (index.reduction() > 0)
+            rx = reduce_query_alphabet(rx, index.redmap());
+        rx = trim_regex(rx);
+    }
+    std::string postfix = translate(rx);
+    kgraph g = construct_kgraph(postfix, index.k(), index.reduction() != TRX_RED_BASE); // include/query.h:239-240
+    return collect(g, index, stats);
+}
+
+} // namespace trxh

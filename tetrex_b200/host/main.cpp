@@ -1,0 +1,255 @@
+// main.cpp — `tetrex` command line (src/main.cpp, include/arg_parse.h): index / query / inspect with the
+// reference's option letters.  Two extra developer sub-commands print intermediate results for the parity tests:
+//   tetrex kgraph [-n] [-r murphy|li] -k K REGEX      postfix string + every node of the k-graph
+//   tetrex bins IDX REGEX                             the candidate bins of process_query, one index per line
+// Unlike the reference (molecule_/ibf_ are frozen before parsing, so its -n and -i are dead) the
+// flags take effect here.
+#include <cstring>
+#include <iostream>
+
+#include "trx_host.hpp"
+
+using namespace trxh;
+
+namespace
+{
+
+struct arg_reader
+{
+    int argc;
+    char ** argv;
+    int pos;
+    bool done() const { return pos >= argc; }
+    std::string next(char const * what)
+    {
+        if (pos >= argc)
+            throw error(std::string("missing value for ") + what);
+        return argv[pos++];
+    }
+};
+
+bool is_flag(std::string const & a, char s, char const * l)
+{
+    return (a.size() == 2 && a[0] == '-' && a[1] == s) || a == std::string("--") + l;
+}
+
+unsigned to_uint(std::string const & s, char const * what)
+{
+    try
+    {
+        size_t used = 0;
+        unsigned long v = std::stoul(s, &used);
+        if (used != s.size())
+            throw 0;
+        return static_cast<unsigned>(v);
+    }
+    catch (...)
+    {
+        throw error(std::string("Value parse failed for ") + what + ": " + s);
+    }
+}
+
+int run_index(arg_reader a)
+{
+    index_arguments args;
+    std::vector<std::string> positional;
+    try
+    {
+        while (!a.done())
+        {
+            std::string s = a.next("argument");
+            if (is_flag(s, 'k', "ksize")) args.k = static_cast<uint8_t>(to_uint(a.next("-k"), "-k"));
+            else if (is_flag(s, 'p', "fpr")) args.fpr = std::stof(a.next("-p"));
+            else if (is_flag(s, 'c', "hash_count")) args.hash_count = static_cast<uint8_t>(to_uint(a.next("-c"), "-c"));
+            else if (is_flag(s, 't', "threads")) args.t = static_cast<uint8_t>(to_uint(a.next("-t"), "-t"));
+            else if (is_flag(s, 'n', "nucleic_acid")) args.dna = true;
+            else if (is_flag(s, 'i', "ibf")) args.idx = true;
+            else if (is_flag(s, 'r', "reduce"))
+            {
+                args.reduction = a.next("-r");
+                if (args.reduction != "murphy" && args.reduction != "li")
+                    throw error("Validation failed for option -r/--reduce: Value " + args.reduction + " is not one of [murphy, li].");
+            }
+            else if (s.size() > 1 && s[0] == '-') throw error("Unknown option " + s + ".");
+            else positional.push_back(s);
+        }
+        if (positional.size() < 2)
+            throw error("Not enough positional arguments provided (Need at least 2).");
+    }
+    catch (std::exception const & e)
+    {
+        std::cerr << "[Indexing Parser Error] " << e.what() << "\n"; // src/main.cpp:25
+        return 0;
+    }
+    if (!args.dna && args.k > 12)
+    {
+        std::cerr << "[Indexing Parser Error] Max kmer size for amino acids is 12" << "\n"; // src/main.cpp:30
+        return 0;
+    }
+    args.ofile = positional[0];
+    args.acid_libs.assign(positional.begin() + 1, positional.end());
+    drive_index(args);
+    return 0;
+}
+
+int run_query(arg_reader a)
+{
+    query_arguments args;
+    std::vector<std::string> positional;
+    bool read_file = false;
+    try
+    {
+        while (!a.done())
+        {
+            std::string s = a.next("argument");
+            if (is_flag(s, 'd', "draw")) args.draw = true;
+            else if (is_flag(s, 'v', "verbose")) args.verbose = true;
+            else if (is_flag(s, 'f', "file")) read_file = true;
+            else if (is_flag(s, 'c', "conj")) args.conjunction = "on";
+            else if (is_flag(s, 'a', "augment")) args.augment = true;
+            else if (is_flag(s, 't', "threads")) args.t = static_cast<uint8_t>(to_uint(a.next("-t"), "-t"));
+            else if (is_flag(s, 'o', "output")) args.ofile = a.next("-o");
+            else if (is_flag(s, 'g', "gibf")) args.dibf = a.next("-g");
+            else if (s.size() > 1 && s[0] == '-' && positional.size() < 1) throw error("Unknown option " + s + ".");
+            else positional.push_back(s);
+        }
+        if (positional.empty())
+            throw error("Not enough positional arguments provided (Need at least 1).");
+    }
+    catch (std::exception const & e)
+    {
+        std::cerr << "[Error TetRex Query module " << e.what() << "\n"; // src/main.cpp:47
+        return 0;
+    }
+    args.idx = positional[0];
+    args.regex = positional.size() > 1 ? positional[1] : "-";
+    if (read_file)
+    {
+        args.read_file = args.regex;
+        args.regex = "x"; // not read from stdin
+    }
+    try
+    {
+        drive_query(args);
+    }
+    catch (archive_error const & e)
+    {
+        std::cerr << "Filepath to (H)IBF Index not valid" << std::endl; // src/main.cpp:55-56
+        std::cerr << e.what() << '\n';
+    }
+    return 0;
+}
+
+int run_kgraph(arg_reader a)
+{
+    unsigned k = 3;
+    bool dna = false;
+    int reduction = TRX_RED_BASE;
+    std::string regex;
+    while (!a.done())
+    {
+        std::string s = a.next("argument");
+        if (s == "-k") k = to_uint(a.next("-k"), "-k");
+        else if (s == "-n") dna = true;
+        else if (s == "-r")
+        {
+            std::string r = a.next("-r");
+            reduction = r == "murphy" ? TRX_RED_MURPHY : r == "li" ? TRX_RED_LI : TRX_RED_BASE;
+        }
+        else regex = s;
+    }
+    std::string rx = regex;
+    if (!dna)
+    {
+        if (reduction != TRX_RED_BASE)
+        {
+            uint8_t aamap[256], redmap[256];
+            trx_peptide_maps(reduction, aamap, redmap);
+            rx = reduce_query_alphabet(rx, redmap);
+        }
+        rx = trim_regex(rx);
+    }
+    std::string postfix = translate(rx);
+    std::cout << "postfix\t" << postfix << "\n";
+    kgraph g = construct_kgraph(postfix, static_cast<uint8_t>(k), reduction != TRX_RED_BASE);
+    std::cout << "nodes\t" << g.size() << "\n";
+    for (size_t i = 0; i < g.size(); ++i)
+        std::cout << i << "\t" << g.symbol[i] << "\t" << g.first[i] << "\t" << g.second[i] << "\t" << g.rank[i] << "\n";
+    return 0;
+}
+
+int run_bins(arg_reader a)
+{
+    std::string idx = a.next("index"), regex = a.next("regex");
+    trx_ctx_t * ctx = nullptr;
+    check(trx_ctx_create(0, nullptr, &ctx));
+    int rc = 0;
+    try
+    {
+        DeviceIndex index(ctx);
+        index.load(idx);
+        collect_stats st;
+        bitvector v = process_query(regex, index, &st);
+        for (uint64_t b = 0; b < index.bin_count(); ++b)
+            if (v[b / 64] >> (b % 64) & 1)
+                std::cout << b << "\n";
+        std::cerr << "probes " << st.probes << " ranks " << st.ranks << " items " << st.items << std::endl;
+    }
+    catch (std::exception const & e)
+    {
+        std::cerr << e.what() << std::endl;
+        rc = 1;
+    }
+    trx_ctx_destroy(ctx);
+    return rc;
+}
+
+void usage()
+{
+    std::cerr << "tetrex - regular expression search over (H)IBF-indexed sequence libraries (B200 build)\n"
+                 "  tetrex index [-k K] [-p FPR] [-c HASHES] [-n] [-i] [-r murphy|li] OUT LIB...\n"
+                 "  tetrex query [-v] [-f] [-o FILE] IDX REGEX\n"
+                 "  tetrex inspect IDX\n";
+}
+
+} // namespace
+
+int main(int argc, char ** argv)
+{
+    if (argc < 2)
+    {
+        usage();
+        return 0;
+    }
+    std::string const cmd = argv[1];
+    arg_reader a{argc, argv, 2};
+    try
+    {
+        if (cmd == "index") return run_index(a);
+        if (cmd == "query") return run_query(a);
+        if (cmd == "inspect")
+        {
+            if (a.done())
+            {
+                std::cerr << "[Error TetRex Index Inspection module Not enough positional arguments provided (Need at least 1).\n";
+                return 0;
+            }
+            drive_inspection(a.next("index"));
+            return 0;
+        }
+        if (cmd == "kgraph") return run_kgraph(a);
+        if (cmd == "bins") return run_bins(a);
+        if (cmd == "model" || cmd == "dindex")
+        {
+            std::cerr << "[Error] sub-command '" << cmd << "' is outside this build (DESIGN.md, out of scope)\n";
+            return 1;
+        }
+        usage();
+        return cmd == "-h" || cmd == "--help" ? 0 : 1;
+    }
+    catch (std::exception const & e)
+    {
+        std::cerr << "[Error] " << e.what() << "\n"; // src/main.cpp:123
+        return 1;
+    }
+}

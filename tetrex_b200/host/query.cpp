@@ -1,0 +1,302 @@
+// query.cpp — the query side above the collector: iter_disk_search (include/query.h:97-188), run_collection
+// (include/query.h:250-291), run_multiple_queries (:330-340), drive_query (src/query.cpp:477-498), drive_index
+// (src/index_base.cpp:73-118) and drive_inspection (src/inspect_idx.cpp).  Same messages on the same streams
+// (seqan3::debug_stream is stderr), same output lines; every scan is one trx_regex_scan call (K4).
+#include <bit>
+#include <chrono>
+#include <fstream>
+#include <iomanip>
+#include <iostream>
+#include <sstream>
+
+#include "trx_host.hpp"
+
+namespace trxh
+{
+
+namespace
+{
+
+// comp_tab (src/query.cpp:7-16) restated: IUPAC complement for letters, identity elsewhere
+char complement(char c)
+{
+    static char const upper[] = "TVGHEFCDIJMLKNOPQYSAABWXRZ"; // complement of 'A'..'Z'
+    if (c >= 'A' && c <= 'Z')
+        return upper[c - 'A'];
+    if (c >= 'a' && c <= 'z')
+        return static_cast<char>(upper[c - 'a'] + ('a' - 'A'));
+    if (c == '`')
+        return '@'; // the table maps 96 to 64
+    return c;
+}
+
+uint64_t popcount(bitvector const & v)
+{
+    uint64_t n = 0;
+    for (uint64_t w : v)
+        n += std::popcount(w);
+    return n;
+}
+
+struct regex_handle
+{
+    trx_regex_t * re{nullptr};
+    regex_handle(std::string const & pattern, bool posix)
+    {
+        check(trx_regex_compile(pattern.c_str(), posix ? 1 : 0, &re));
+    }
+    ~regex_handle() { trx_regex_destroy(re); }
+};
+
+std::vector<trx_hit> scan(DeviceIndex::text_store const & store, regex_handle & rx, bitvector const & cand, bool reverse,
+                          uint8_t const * map)
+{
+    std::vector<trx_hit> hits(4096);
+    for (;;)
+    {
+        uint64_t n = 0;
+        int rc = trx_regex_scan(store.text, rx.re, cand.data(), reverse ? 1 : 0, map, hits.data(), hits.size(), &n, nullptr);
+        if (rc == TRX_ECAPACITY)
+        {
+            hits.resize(n + n / 8 + 16);
+            continue;
+        }
+        check(rc);
+        hits.resize(n);
+        return hits;
+    }
+}
+
+} // namespace
+
+uint64_t iter_disk_search(bitvector const & hits_in, std::string const & query_in, DeviceIndex & index, std::string const & dest)
+{
+    DeviceIndex::text_store const & store = index.text();
+    std::vector<std::string> const & libs = index.acid_libs();
+    // compute_set_bins (src/query.cpp:40-76): a one-bin library is always scanned
+    bitvector cand((libs.size() + 63) / 64, 0);
+    if (libs.size() == 1)
+        cand[0] = 1;
+    else
+        for (size_t w = 0; w < cand.size() && w < hits_in.size(); ++w)
+            cand[w] = hits_in[w];
+
+    std::string query = query_in;
+    bool const dna = index.is_dna();
+    if (!dna && index.reduction() > 0)
+        query = reduce_query_alphabet(query, index.redmap()); // include/query.h:144
+    regex_handle rx(query, /*posix=*/!dna);                    // RE2::POSIX for peptides, default options for DNA
+
+    std::ofstream file_out;
+    std::ostream * out = &std::cout;
+    if (dest != "-")
+    {
+        file_out.open(dest);
+        if (!file_out)
+            throw error("Failed to open output file: " + dest);
+        out = &file_out;
+    }
+
+    uint8_t const * map = (!dna && index.reduction() > 0) ? index.redmap() : nullptr;
+    std::vector<trx_hit> fwd = scan(store, rx, cand, false, map);
+    std::vector<trx_hit> rev;
+    if (dna)
+        rev = scan(store, rx, cand, true, nullptr);
+
+    uint64_t lines = 0;
+    std::string line, match;
+    auto emit_forward = [&](trx_hit const & h) {
+        char const * rec = store.residues.data() + store.offsets[h.record];
+        match.assign(rec + h.start, h.end - h.start);
+        if (map) // verify_reduced_fasta_hit prints the REDUCED residues (src/query.cpp:284-287)
+            for (char & c : match)
+                c = static_cast<char>(map[static_cast<uint8_t>(c)]);
+        *out << libs[h.bin] << '\t' << store.names[h.record] << '\t' << match << '\t' << h.start << ',' << h.end << '\n';
+        ++lines;
+    };
+    auto emit_reverse = [&](trx_hit const & h) {
+        // coordinates are in the reverse-complemented record (src/query.cpp:167-191)
+        uint64_t const len = store.offsets[h.record + 1] - store.offsets[h.record];
+        char const * rec = store.residues.data() + store.offsets[h.record];
+        match.clear();
+        for (uint32_t p = h.start; p < h.end; ++p)
+            match.push_back(complement(rec[len - 1 - p]));
+        // reverse hits always go to stdout, whatever -o says (std::osyncstream(std::cout), :186)
+        std::cout << libs[h.bin] << '\t' << store.names[h.record] << '\t' << match << '\t' << "REVERSE STRAND HIT" << std::endl;
+        ++lines;
+    };
+    // per bin: all forward lines, then all reverse lines (include/query.h:132-134); bins ascending (-t 1 order)
+    size_t i = 0, j = 0;
+    while (i < fwd.size() || j < rev.size())
+    {
+        uint32_t bin = UINT32_MAX;
+        if (i < fwd.size())
+            bin = fwd[i].bin;
+        if (j < rev.size())
+            bin = std::min(bin, rev[j].bin);
+        for (; i < fwd.size() && fwd[i].bin == bin; ++i)
+            emit_forward(fwd[i]);
+        if (j < rev.size() && rev[j].bin == bin)
+        {
+            out->flush();
+            for (; j < rev.size() && rev[j].bin == bin; ++j)
+                emit_reverse(rev[j]);
+        }
+    }
+    out->flush();
+    return lines;
+}
+
+namespace
+{
+
+double now()
+{
+    return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+// run_collection (include/query.h:250-291)
+void run_collection(query_arguments & args, bool read_file, DeviceIndex & index)
+{
+    bool const verbose = args.verbose && !read_file;
+    double const t1 = now();
+    bitvector hit_vector(index.bin_words(), 0);
+    for (uint64_t b = 0; b < index.bin_count(); ++b)
+        hit_vector[b / 64] |= 1ull << (b % 64);
+    if (index.bin_count() > 1)
+    {
+        bitvector got = process_query(args.regex, index);
+        for (size_t w = 0; w < hit_vector.size(); ++w)
+            hit_vector[w] &= got[w];
+    }
+    else
+        std::cerr << "[WARNING] Index contains only 1 bin. Unable to accelerate search using the TetRex algorithm. "
+                     "Performing Linear Scan"
+                  << std::endl;
+    if (verbose)
+        std::cerr << "Narrowed Search to " << popcount(hit_vector) << " possible bins" << std::endl;
+    if (read_file)
+        std::cerr << "Bin Count: " << popcount(hit_vector) << "\t";
+    if (popcount(hit_vector) != 0)
+    {
+        try
+        {
+            iter_disk_search(hit_vector, args.regex, index, args.ofile);
+        }
+        catch (std::exception const & e)
+        {
+            std::cerr << e.what() << '\n';
+        }
+    }
+    double const t2 = now();
+    if (verbose || read_file)
+        std::cerr << "Query Time: " << (t2 - t1) << std::endl;
+}
+
+} // namespace
+
+void drive_query(query_arguments & args)
+{
+    if (args.regex == "-")
+        std::cin >> args.regex; // src/query.cpp:479
+    if (args.augment || args.draw || args.dibf != "-" || args.conjunction != "-")
+        throw error("-a / -d / -g / -c (augmentation, graph drawing, DGram index, conjunction) are outside this build: "
+                    "see DESIGN.md \"out of scope\"");
+    {
+        // load_params comes first in the reference too (src/query.cpp:480-481): an unreadable file is reported before
+        // anything else happens
+        uint8_t k;
+        std::string molecule;
+        bool is_hibf;
+        read_index_params(args.idx, k, molecule, is_hibf);
+    }
+    trx_ctx_t * ctx = nullptr;
+    check(trx_ctx_create(0, nullptr, &ctx));
+    try
+    {
+        DeviceIndex index(ctx);
+        index.load(args.idx);
+        if (args.read_file != "-")
+        {
+            // read_regex_from_file + run_multiple_queries (src/query.cpp:372-395, include/query.h:330-340):
+            // "id<TAB>motif" per line, matches of each go to "<id>.tsv"
+            std::ifstream in(args.read_file);
+            if (!in.is_open())
+                throw error("Could not open file: " + args.read_file);
+            std::string line;
+            while (std::getline(in, line))
+            {
+                if (line.empty())
+                    continue;
+                std::istringstream iss(line);
+                std::string id, motif;
+                if (!std::getline(iss, id, '\t') || !std::getline(iss, motif, '\t'))
+                    continue;
+                args.regex = motif;
+                args.ofile = id + ".tsv";
+                std::cerr << id << "\t";
+                run_collection(args, true, index);
+            }
+        }
+        else
+            run_collection(args, false, index);
+    }
+    catch (...)
+    {
+        trx_ctx_destroy(ctx);
+        throw;
+    }
+    trx_ctx_destroy(ctx);
+}
+
+void drive_index(index_arguments const & args)
+{
+    trx_ctx_t * ctx = nullptr;
+    check(trx_ctx_create(0, nullptr, &ctx));
+    try
+    {
+        DeviceIndex index(ctx);
+        index.build(args);
+        std::cerr << "Writing to disk... ";
+        index.store(args.ofile + ".ibf");
+        std::cerr << "DONE" << std::endl;
+    }
+    catch (...)
+    {
+        trx_ctx_destroy(ctx);
+        throw;
+    }
+    trx_ctx_destroy(ctx);
+}
+
+void drive_inspection(std::string const & idx_path)
+{
+    // src/inspect_idx.cpp — reads the file only, no device needed
+    std::cerr << "Reading Index from Disk... ";
+    double const t1 = now();
+    index_image img = read_index(idx_path);
+    std::cerr << "DONE in " << now() - t1 << "s" << std::endl;
+    bool const dna = img.molecule == "na";
+    if (!img.is_hibf)
+    {
+        std::cout << "INDEX TYPE: IBF" << std::endl;
+        std::cout << "BIN COUNT (BFs): " << img.flat.bins << std::endl;
+        std::cout << "BIN SIZE (bits): " << img.flat.bin_size << std::endl;
+    }
+    else
+    {
+        std::cout << "INDEX TYPE: HIBF" << std::endl;
+        std::cout << "FALSE POSITIVE RATE: " << std::fixed << std::setprecision(2) << img.fpr << std::endl;
+    }
+    std::cout << "HASH COUNT (hash functions): " << unsigned(img.hash_count) << std::endl;
+    std::cout << "KMER LENGTH (" << (dna ? "bases" : "residues") << "): " << unsigned(img.k) << std::endl;
+    // the reference streams the uint8_t reduction_ as a raw character here; the number is printed instead
+    std::cout << "MOLECULE TYPE (alphabet): " << (dna ? "Nucleic Acid" : "Amino Acid") << " [REDUCTION=" << unsigned(img.reduction)
+              << "]" << std::endl;
+    std::cout << "ACID LIBRARY (filepaths):" << std::endl;
+    for (auto const & path : img.acid_libs)
+        std::cout << "\t- " << path << std::endl;
+    std::cerr << "DONE" << std::endl;
+}
+
+} // namespace trxh

@@ -1,0 +1,226 @@
+// trx_host.hpp — host C++ layer of tetrex_b200: the reference's C++ API for the index-probe + verify path
+// (TetrexIndex, process_query, iter_disk_search, drive_index, drive_query — /root/reference include/index_base.h,
+// include/query.h) re-implemented on top of the C ABI in include/tetrex_b200.h.  Every hot loop is a C-ABI call
+// into libtetrex_cuda.so; this layer only parses files and regexes, plans batches and formats output.
+#pragma once
+
+#include <cstdint>
+#include <map>
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <utility>
+#include <vector>
+
+#include "../../include/tetrex_b200.h"
+
+namespace trxh
+{
+
+struct error : std::runtime_error
+{
+    using std::runtime_error::runtime_error;
+};
+
+// thrown for unreadable / truncated index files; plays the role of cereal::Exception (src/main.cpp:54-58)
+struct archive_error : std::runtime_error
+{
+    using std::runtime_error::runtime_error;
+};
+
+void check(int rc); // throws trxh::error with trx_last_error() when rc != TRX_OK
+
+// ------------------------------------------------------------------------------------------ arguments
+// include/arg_parse.h:10-70 — same names and defaults; molecule / ibf are derived AFTER parsing here (the
+// reference freezes them before parsing, SURVEY.md F3, so its -n / -i flags are dead).
+struct index_arguments
+{
+    uint8_t k = 6;
+    float fpr = 0.05f;
+    uint8_t hash_count = 3;
+    uint8_t t = 1;
+    bool dna = false;  // -n
+    bool idx = false;  // -i : flat IBF instead of HIBF
+    std::string reduction = "None";
+    std::string ofile;
+    std::vector<std::string> acid_libs;
+};
+
+struct query_arguments
+{
+    uint8_t t = 1;
+    bool verbose = false;
+    bool draw = false;
+    bool augment = false;
+    std::string idx;
+    std::string regex;
+    std::string read_file = "-";
+    std::string conjunction = "-";
+    std::string dibf = "-";
+    std::string ofile = "-";
+};
+
+// --------------------------------------------------------------------------------------------- index file
+// One technical IBF as serialised by seqan::hibf::interleaved_bloom_filter.
+struct ibf_image
+{
+    uint64_t bins{}, technical_bins{}, bin_size{}, hash_shift{}, bin_words{}, hash_funs{};
+    std::vector<uint64_t> words;     // ceil(technical_bins*bin_size/64)
+    std::vector<uint64_t> occupancy; // technical_bins zeros on every TetRex path
+    bool track_occupancy{false};
+};
+
+struct hibf_image
+{
+    uint64_t number_of_user_bins{};
+    std::vector<ibf_image> ibf_vector;
+    std::vector<std::vector<uint64_t>> next_ibf_id;
+    std::vector<std::pair<uint64_t, uint64_t>> prev_ibf_id;
+    std::vector<std::vector<uint64_t>> ibf_bin_to_user_bin_id;
+};
+
+// TetrexIndex as it lies on disk (include/index_base.h:160-165 + index_ibf.h:152-156 / index_hibf.h:154-158
+// + the decomposer tail, molecule_decomposer.h:118-122)
+struct index_image
+{
+    uint8_t k{};
+    std::string molecule;          // "na" / "aa"
+    bool is_hibf{};
+    std::vector<std::string> acid_libs;
+    uint8_t reduction{};           // 0 none, 1 murphy, 2 li
+    uint64_t bin_count{};
+    uint64_t bin_size_member{};    // flat only; the reference always writes 0 here
+    float fpr{0.05f};              // HIBF only
+    uint8_t hash_count{};
+    std::vector<std::string> bin_names; // tech_bins_ / user_bins_
+    ibf_image flat;
+    hibf_image hibf;
+};
+
+void write_index(index_image const & img, std::string const & path);
+index_image read_index(std::string const & path);
+// index_params / load_params (include/index_base.h:5-16,197-202): only the three leading fields
+void read_index_params(std::string const & path, uint8_t & k, std::string & molecule, bool & is_hibf);
+
+// ------------------------------------------------------------------------------------------------- FASTA
+struct fasta_record
+{
+    std::string name;    // header up to the first whitespace (kseq name.s)
+    std::string comment; // rest of the header line
+    std::string seq;     // concatenated sequence lines
+};
+// kseq_read over gzopen (include/kseq.h): plain or gzip, FASTA or FASTQ. Throws trxh::error if unopenable.
+std::vector<fasta_record> read_fasta(std::string const & path);
+
+// ------------------------------------------------------------------------------------- regex front end
+// translate() / PostfixConverter (include/utils.h:96-468, src/utils.cpp:3-15): infix → postfix with '-' as the
+// explicit concatenation operator; '.' and [^..] expand over the 20 amino acids.
+std::string translate(std::string const & pattern);
+// trimRegEx / reduce_query_alphabet / preprocess_query (src/query.cpp:78-155, include/query.h:80-94)
+std::string trim_regex(std::string const & regex);
+std::string reduce_query_alphabet(std::string const & regex, uint8_t const redmap[256]);
+
+// --------------------------------------------------------------------------------------------- k-graph
+enum node_symbol : int { Match = 256, Ghost = 257, Split = 258, Gap = 259 };
+
+// Linearised acyclic NFA of construct_kgraph (src/construct_nfa.cpp:265-335): node ids, symbols and the
+// two-slot arc map exactly as the reference numbers them, plus the collector's ranks
+// (include/otf_collector.h:328-339).
+struct kgraph
+{
+    std::vector<int> symbol;
+    std::vector<int> first, second; // arc_map slots; -1 = none
+    std::vector<int> rank;
+    std::vector<std::pair<int, int>> arcs; // in creation order (source, target)
+    int add_node(int sym);
+    void add_arc(int source, int target); // update_arc_map (src/construction_tools.cpp:136-158)
+    void compute_ranks();
+    size_t size() const { return symbol.size(); }
+};
+// reduced = true → construct_reduced_kgraph (src/construct_reduced_nfa.cpp), used when the index alphabet is reduced
+kgraph construct_kgraph(std::string const & postfix, uint8_t k, bool reduced = false);
+
+// ------------------------------------------------------------------------------------------------ index
+// TetrexIndex<flavor, molecule> with its bit matrix in HBM.
+class DeviceIndex
+{
+public:
+    explicit DeviceIndex(trx_ctx_t * ctx) : ctx_(ctx) {}
+    ~DeviceIndex();
+    DeviceIndex(DeviceIndex const &) = delete;
+    DeviceIndex & operator=(DeviceIndex const &) = delete;
+
+    // create_{ibf,hibf}_{dna,aa}_index + populate_index (src/index_base.cpp:25-70): reads the FASTA bins,
+    // sizes the filter with the reference's rule and sets every bit on the GPU (K1).
+    void build(index_arguments const & args);
+    void store(std::string const & path) const; // store_ibf
+    void load(std::string const & path);        // load_ibf + upload to the device
+
+    uint8_t k() const { return img_.k; }
+    bool is_dna() const { return img_.molecule == "na"; }
+    bool is_hibf() const { return img_.is_hibf; }
+    uint8_t reduction() const { return img_.reduction; }
+    uint64_t bin_count() const { return img_.bin_count; }
+    uint64_t bin_words() const { return (img_.bin_count + 63) / 64; }
+    std::vector<std::string> const & acid_libs() const { return img_.acid_libs; }
+    index_image const & image() const { return img_; }
+    trx_ctx_t * ctx() const { return ctx_; }
+    trx_ibf_t * flat() const { return flat_; }
+    trx_hibf_t * hibf() const { return hibf_; }
+    uint8_t const * aamap() const { return aamap_; }
+    uint8_t const * redmap() const { return redmap_; }
+    uint64_t sequences_indexed() const { return seq_count_; }
+
+    // TetrexIndex::update_kmer (nucleotide_decomposer.h:113-121 / peptide_decomposer.h:293-299): rolls `symbol`
+    // into `kmer` (forward value) and returns the value that is probed.
+    uint64_t update_kmer(int symbol, uint64_t & kmer) const;
+
+    // residue store for verify: built on first use from acid_libs (the files iter_disk_search would re-read)
+    struct text_store
+    {
+        trx_text_t * text{nullptr};
+        std::vector<std::string> names;      // per record: ">" + name
+        std::vector<uint64_t> offsets;       // n_records + 1
+        std::vector<uint32_t> rec_bin;
+        std::string residues;
+    };
+    text_store const & text();
+
+private:
+    void upload();
+    void init_maps();
+    trx_ctx_t * ctx_;
+    index_image img_;
+    trx_ibf_t * flat_{nullptr};
+    trx_hibf_t * hibf_{nullptr};
+    uint8_t aamap_[256]{}, redmap_[256]{};
+    uint64_t seq_count_{};
+    std::unique_ptr<text_store> text_;
+};
+
+// ------------------------------------------------------------------------------------------ query path
+using bitvector = std::vector<uint64_t>; // ceil(bins/64) words, bit b = bin b (seqan::hibf::bit_vector words)
+
+struct collect_stats
+{
+    uint64_t probes{};   // k-mers probed on the device
+    uint64_t ranks{};    // level-synchronous rounds
+    uint64_t items{};    // collector items processed
+};
+
+// process_query (include/query.h:226-247): preprocess, k-graph, OTFCollector::collect with every probe, path
+// AND, none() test and path OR executed on the device.
+bitvector process_query(std::string const & regex, DeviceIndex & index, collect_stats * stats = nullptr);
+// the collector alone on a ready k-graph (OTFCollector::collect, include/otf_collector.h:341-393)
+bitvector collect(kgraph const & g, DeviceIndex & index, collect_stats * stats = nullptr);
+
+// iter_disk_search (include/query.h:97-188): verifies the candidate bins on the device (K4) and writes the
+// reference's lines "bin_path\t>name\tmatch\tstart,end\n" (+ "…\tREVERSE STRAND HIT" for DNA) to `dest`
+// ("-" = stdout).  Returns the number of lines written.
+uint64_t iter_disk_search(bitvector const & hits, std::string const & query, DeviceIndex & index, std::string const & dest);
+
+void drive_index(index_arguments const & args);
+void drive_query(query_arguments & args);
+void drive_inspection(std::string const & idx_path);
+
+} // namespace trxh
