@@ -453,3 +453,28 @@ def ref_index_query(index_path, regex, verify=True, threads=1, stdout_path=None)
         if stdout_path is None:
             os.unlink(tmp)
     return words[:n].copy(), text
+
+
+def guarded(fn, *args):
+    """Runs fn(*args) in a forked child and returns its (pickled) result, or the string "ABORTED" if the child died:
+    the reference terminates or segfaults on some inputs (empty regex after trimming, UB in its reduced k-graph
+    builder, short queries on a flat index), which must not take the test process with it."""
+    import pickle
+    r, w = os.pipe()
+    pid = os.fork()
+    if pid == 0:
+        os.close(r)
+        try:
+            os.write(w, pickle.dumps(fn(*args)))
+        finally:
+            os._exit(0)
+    os.close(w)
+    data = b""
+    while True:
+        chunk = os.read(r, 1 << 16)
+        if not chunk:
+            break
+        data += chunk
+    os.close(r)
+    _, status = os.waitpid(pid, 0)
+    return pickle.loads(data) if status == 0 and data else "ABORTED"
