@@ -170,24 +170,12 @@ def run_ours(args):
     pin_q = torch.from_numpy(q_host.view(np.int64)).pin_memory()
     pin_out = torch.empty(args.batch * W, dtype=torch.int64).pin_memory()
 
+    from tetrex_b200.dist import max_over_ranks, sum_over_ranks  # all-reduce over NCCL when world > 1
+
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
-
-    def max_over_ranks(x: float) -> float:
-        if world == 1:
-            return x
-        tt = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        return float(tt.item())
-
-    def sum_over_ranks(x: float) -> float:
-        if world == 1:
-            return x
-        tt = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(tt, op=dist.ReduceOp.SUM)
-        return float(tt.item())
 
     # ---------------- device-resident timing: K steps of K3 on the batch
     visited = 0
@@ -262,7 +250,7 @@ def run_ours(args):
         dist.barrier()
         dist.destroy_process_group()
     if line is not None:
-        print(json.dumps(line))
+        emit(line)
 
 
 def cpu_baseline(tables, q_host, budget_s: float = 12.0):
@@ -412,7 +400,7 @@ def run_reference(args):
     dt = time.perf_counter() - t0
     value = per_step * args.steps / dt
     sample = f"{per_step} k-mers per step (prefix of the same seeded batch), one membership agent per thread"
-    print(json.dumps({
+    emit({
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u64", "data": "synthetic",
@@ -421,11 +409,30 @@ def run_reference(args):
                    "index": "same layout as the GPU arm, bits set by the CPU oracle (no CUDA in this arm)"},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": kind, "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    }))
+    })
+
+
+_REAL_STDOUT = None
+
+
+def claim_stdout():
+    """stdout must carry exactly one JSON line: libraries that write to fd 1 (NCCL prints its version banner
+    there) are sent to stderr for the whole run; emit() writes to the saved descriptor."""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+
+
+def emit(line: dict):
+    out = _REAL_STDOUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
 
 
 if __name__ == "__main__":
     a = parse_args()
+    claim_stdout()
     if a.impl == "reference":
         run_reference(a)
     else:
