@@ -9,6 +9,8 @@
 // (the next level's item count stays in device memory).
 #include <cub/device/device_radix_sort.cuh>
 
+#include <algorithm>
+
 #include "common.cuh"
 
 namespace trx
@@ -137,6 +139,382 @@ __global__ void __launch_bounds__(256)
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Root + second level without a frontier: "windowed" schedule.
+//
+// The HIBF (0.37 GB at C2) does not fit the 126 MB L2, but a WINDOW of a few neighbouring second-level IBFs does.
+// hibf_root_kernel probes the root for every k-mer of the batch and keeps the merged-bin hits (one 64-bit word per
+// root word) in a scratch array.  Then one hibf_window_kernel launch per window walks ALL k-mers of the batch
+// against the children of that window only: the window's matrices are read from DRAM once per batch and stay in L2
+// (loads carry an evict_last policy) while millions of probes hit them.  Everything that merely streams through —
+// k-mers, root words, results — is read and written with evict_first so that it does not push the window out: a
+// scattered 8-byte atomic into the 512 MB result array allocates a whole 128-byte L2 line, and ~10 M of those per
+// pass were measured to flush L2 ten times over.  Results therefore never go to the result array directly: a
+// window's children report into a narrow run of user-bin words [word_lo, word_lo+span); the warp accumulates those
+// words in shared memory and stores them, coalesced, into a per-window strip; hibf_merge_kernel finally ORs the
+// strips into the caller's rows.  The frontier kernels above get their locality from a radix sort and pay 16 B of
+// frontier traffic per (k-mer, child) pair plus the sort; here a pair costs nothing but its probe.
+// Inside the window kernel a warp owns 32 k-mers (lane = k-mer); a k-mer reaches only about a third of the
+// children, so the warp gathers its (k-mer, child) pairs through ballots into a shared-memory queue and probes 32
+// pairs at a time with all lanes busy.  Merged bins hit on the second level (HIBFs with three or more levels) are
+// appended to the frontier and handled by hibf_level_kernel<false> after the merge.
+constexpr int kWinThreads = 256;
+constexpr uint32_t kMaxSpan = 24;    // user-bin words one window (or the root) may report into
+constexpr uint32_t kMaxWindowBins = 16; // root technical bins per window (shared-memory tables and pair queue)
+
+struct hibf_window
+{
+    uint32_t bin_begin, bin_end; // root technical bins of this window
+    uint32_t word_lo, span;      // user-bin words [word_lo, word_lo + span) its children report into
+    uint64_t strip_off;          // offset of the window's strip, in units of n words (Σ span of earlier windows)
+};
+
+__device__ __forceinline__ uint64_t policy_evict_last()
+{
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+__device__ __forceinline__ uint64_t policy_evict_first()
+{
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+__device__ __forceinline__ uint64_t ld_hint(uint64_t const * p, uint64_t policy)
+{
+    uint64_t v;
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.u64 %0, [%1], %2;" : "=l"(v) : "l"(p), "l"(policy));
+    return v;
+}
+__device__ __forceinline__ void st_hint(uint64_t * p, uint64_t v, uint64_t policy)
+{
+    asm volatile("st.global.L1::no_allocate.L2::cache_hint.u64 [%0], %1, %2;" ::"l"(p), "l"(v), "l"(policy) : "memory");
+}
+
+// FAST: every IBF has one word per row (≤ 64 technical bins) and fewer than 2^32 rows — the shape seqan's layout
+// produces for tmax = 64; the fastrange product then needs two 32x32 multiplies instead of a 64x64 high multiply
+// calls f(bit index) for every set bit, low half first: 32-bit find-first-set is one FLO, the 64-bit one a dozen instructions
+template <class F>
+__device__ __forceinline__ void for_each_bit(uint64_t x, F f)
+{
+    uint32_t lo = static_cast<uint32_t>(x), hi = static_cast<uint32_t>(x >> 32);
+    while (lo)
+    {
+        int b = __ffs(static_cast<int>(lo)) - 1;
+        lo &= lo - 1;
+        f(b);
+    }
+    while (hi)
+    {
+        int b = __ffs(static_cast<int>(hi)) - 1;
+        hi &= hi - 1;
+        f(b + 32);
+    }
+}
+
+template <int H, bool FAST>
+__device__ __forceinline__ uint64_t probe_word(hibf_dev const & h, hibf_ibf_desc const & d, uint64_t kmer, uint32_t w,
+                                               uint64_t policy)
+{
+    uint64_t hit = ~0ULL;
+#pragma unroll
+    for (int f = 0; f < 5; ++f)
+    {
+        if (H ? f < H : static_cast<uint32_t>(f) < d.hash_funs)
+        {
+            if constexpr (FAST)
+            {
+                uint64_t x = kmer * hash_seed(f);
+                x ^= x >> d.hash_shift;
+                x *= 11400714819323198485ULL;
+                uint64_t const bs = static_cast<uint32_t>(d.bin_size);
+                uint64_t const row = ((x >> 32) * bs + (((x & 0xffffffffULL) * bs) >> 32)) >> 32;
+                hit &= ld_hint(h.words + d.word_off + row, policy);
+            }
+            else
+                hit &= ld_hint(h.words + d.word_off + hash_row(kmer, f, d.hash_shift, d.bin_size) * d.bin_words + w, policy);
+        }
+    }
+    return hit;
+}
+
+// root_words[i * bin_words(root) + w] = merged-bin hits of k-mer i in root word w.  root_strip (n × root.span words,
+// zeroed) receives the user bins that sit directly on the root.
+template <int H, bool FAST>
+__global__ void __launch_bounds__(256)
+    hibf_root_kernel(hibf_dev h, uint64_t const * __restrict__ kmers, uint64_t n, uint64_t * __restrict__ root_words,
+                     hibf_window root, uint64_t * __restrict__ root_strip, unsigned long long * __restrict__ counters)
+{
+    hibf_ibf_desc const d0 = h.ibfs[0];
+    uint64_t const keep = policy_evict_last(), stream = policy_evict_first();
+    unsigned long long reached = 0;
+    uint64_t const stride = static_cast<uint64_t>(gridDim.x) * blockDim.x;
+    for (uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride)
+    {
+        uint64_t const v = ld_hint(kmers + i, stream);
+        for (uint32_t w = 0; w < d0.bin_words; ++w)
+        {
+            uint64_t const hit = probe_word<H, FAST>(h, d0, v, w, keep);
+            uint32_t const mask_idx = d0.table_off / 64 + w;
+            uint64_t users = hit & __ldg(h.user_mask + mask_idx);
+            uint64_t const children = hit & __ldg(h.merged_mask + mask_idx);
+            st_hint(root_words + i * d0.bin_words + w, children, stream);
+            reached += __popcll(children);
+            while (users)
+            {
+                int b = __ffsll(static_cast<long long>(users)) - 1;
+                users &= users - 1;
+                uint32_t ub = __ldg(h.user_bin + d0.table_off + w * 64 + b);
+                atomicOr(reinterpret_cast<unsigned long long *>(root_strip + i * root.span + ((ub >> 6) - root.word_lo)),
+                         1ULL << (ub & 63));
+            }
+        }
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1)
+        reached += __shfl_xor_sync(0xffffffffu, reached, off);
+    if ((threadIdx.x & 31) == 0 && reached)
+        atomicAdd(counters + 2, reached); // = number of level-1 items, what the frontier path counts there
+}
+
+// Everything a pair needs about its child, for the (at most kMaxWindowBins) root bins of the window, in shared
+// memory: with the tables in global memory every pair made three more L1 requests (masks, user-bin ids) that missed
+// L1 most of the time because the random row sectors stream through it.
+struct window_child
+{
+    uint64_t word_off;
+    uint64_t bin_size;
+    uint32_t bin_words, hash_shift, hash_funs, table_off;
+    uint64_t user_mask, merged_mask; // of word 0 (FAST shape: the only word)
+};
+
+template <int H, bool FAST>
+__global__ void __launch_bounds__(kWinThreads)
+    hibf_window_kernel(hibf_dev h, uint64_t const * __restrict__ kmers, uint64_t n, uint64_t const * __restrict__ root_words,
+                       hibf_window win, uint64_t * __restrict__ strip, uint64_t * __restrict__ frontier_out,
+                       unsigned long long * __restrict__ counters, uint64_t capacity)
+{
+    extern __shared__ uint64_t win_acc[]; // kWinThreads rows of (span + 1) words
+    __shared__ window_child s_child[kMaxWindowBins];
+    __shared__ uint16_t s_ub[FAST ? kMaxWindowBins : 1][64]; // user bin of (window bin, technical bin); FAST: ids < 65536
+    __shared__ uint16_t s_queue[kWinThreads / 32][32 * kMaxWindowBins];
+    hibf_ibf_desc const d0 = h.ibfs[0];
+    uint32_t const win_bins = min(win.bin_end - win.bin_begin, kMaxWindowBins);
+    if (threadIdx.x < win_bins)
+    {
+        uint32_t const bin = win.bin_begin + threadIdx.x;
+        uint32_t const idx = d0.table_off + bin;
+        window_child c{};
+        if (h.merged_mask[idx / 64] >> (idx % 64) & 1)
+        {
+            hibf_ibf_desc const d = h.ibfs[h.next_ibf[idx]];
+            c = window_child{d.word_off, d.bin_size, d.bin_words, d.hash_shift, d.hash_funs, d.table_off,
+                             h.user_mask[d.table_off / 64], h.merged_mask[d.table_off / 64]};
+        }
+        s_child[threadIdx.x] = c;
+    }
+    __syncthreads();
+    if constexpr (FAST)
+    {
+        for (uint32_t t = threadIdx.x; t < win_bins * 64; t += kWinThreads)
+            s_ub[t >> 6][t & 63] = static_cast<uint16_t>(h.user_bin[s_child[t >> 6].table_off + (t & 63)]);
+        __syncthreads();
+    }
+    uint64_t const keep = policy_evict_last(), stream = policy_evict_first();
+    unsigned const lane = threadIdx.x & 31;
+    unsigned const warp = threadIdx.x >> 5;
+    uint32_t const win_mask = win_bins >= 32 ? ~0u : ((1u << win_bins) - 1);
+    uint32_t const lt_mask = (1u << lane) - 1;
+    uint32_t const span = win.span, pitch = span + 1;
+    uint32_t const inv_span = span ? (65536 + span - 1) / span : 0;
+    uint16_t * const queue = s_queue[warp];
+    uint64_t * const warp_acc = win_acc + static_cast<size_t>(warp * 32) * pitch;
+    uint64_t const warps = static_cast<uint64_t>(gridDim.x) * (kWinThreads / 32);
+    uint64_t const n_groups = (n + 31) / 32;
+    for (uint64_t g = static_cast<uint64_t>(blockIdx.x) * (kWinThreads / 32) + warp; g < n_groups; g += warps)
+    {
+        uint64_t const base = g * 32;
+        uint64_t const i = base + lane;
+        bool const active = i < n;
+        uint64_t const v = active ? ld_hint(kmers + i, stream) : 0;
+        for (uint32_t w = 0; w < span; ++w)
+            warp_acc[lane * pitch + w] = 0;
+        __syncwarp();
+        // second level for one queued pair per lane; every lane takes part in the shuffle
+        auto process = [&](bool valid, uint32_t entry) {
+            unsigned const src = entry & 31;
+            uint32_t const wb = entry >> 5; // bin inside the window
+            uint64_t const kmer = __shfl_sync(0xffffffffu, v, src);
+            if (!valid)
+                return;
+            window_child const & c = s_child[wb];
+            hibf_ibf_desc const dc{c.word_off, c.bin_size, c.bin_words, c.hash_shift, c.hash_funs, c.table_off};
+            unsigned * const row32 = reinterpret_cast<unsigned *>(warp_acc + src * pitch) - 2 * win.word_lo;
+            for (uint32_t w2 = 0; w2 < (FAST ? 1u : dc.bin_words); ++w2)
+            {
+                uint64_t const hit2 = probe_word<H, FAST>(h, dc, kmer, w2, keep);
+                if (hit2 == 0)
+                    continue;
+                uint64_t const users2 = hit2 & (FAST ? c.user_mask : __ldg(h.user_mask + dc.table_off / 64 + w2));
+                uint64_t const deeper = hit2 & (FAST ? c.merged_mask : __ldg(h.merged_mask + dc.table_off / 64 + w2));
+                for_each_bit(users2, [&](int b2) {
+                    uint32_t ub;
+                    if constexpr (FAST)
+                        ub = s_ub[wb][b2];
+                    else
+                        ub = __ldg(h.user_bin + dc.table_off + w2 * 64 + b2);
+                    // two lanes may hold pairs of the same k-mer: shared-memory atomic, on the 32-bit half (64-bit
+                    // shared atomics other than CAS compile to a CAS loop)
+                    atomicOr(row32 + (ub >> 5), 1u << (ub & 31));
+                });
+                for_each_bit(deeper, [&](int b2) { // third level and below: hand over to the frontier kernels
+                    unsigned long long pos = atomicAdd(counters + 3, 1ULL);
+                    if (pos < capacity)
+                        frontier_out[pos] = (static_cast<uint64_t>(__ldg(h.next_ibf + dc.table_off + w2 * 64 + b2)) << 32) |
+                                            static_cast<uint32_t>(base + src);
+                    else
+                        counters[0] = 1;
+                });
+            }
+        };
+        // gather the warp's (k-mer, root bin) pairs, child-major: all lanes that reach bin b, then bin b + 1, …  A
+        // window never crosses a root word and has at most kMaxWindowBins bins.
+        uint64_t const root_word = active ? ld_hint(root_words + i * d0.bin_words + (win.bin_begin >> 6), stream) : 0;
+        uint32_t const children = static_cast<uint32_t>(root_word >> (win.bin_begin & 63)) & win_mask;
+        uint32_t total = 0;
+        for (uint32_t b = 0; b < win_bins; ++b)
+        {
+            bool const want = (children >> b) & 1;
+            unsigned const m = __ballot_sync(0xffffffffu, want);
+            if (want)
+                queue[total + __popc(m & lt_mask)] = static_cast<uint16_t>((b << 5) | lane);
+            total += __popc(m);
+        }
+        __syncwarp();
+        for (uint32_t r = 0; r < total; r += 32)
+        {
+            bool const valid = r + lane < total;
+            process(valid, valid ? queue[r + lane] : lane);
+        }
+        __syncwarp();
+        // the warp's 32 strip rows are contiguous: consecutive lanes store consecutive words
+        uint64_t const rows = base + 32 <= n ? 32 : n - base;
+        uint64_t * const dst = strip + base * span;
+        for (uint32_t idx = lane; idx < rows * span; idx += 32)
+        {
+            uint32_t const r = (idx * inv_span) >> 16; // idx / span for idx < 32 * kMaxSpan
+            st_hint(dst + idx, warp_acc[r * pitch + (idx - r * span)], stream);
+        }
+        __syncwarp();
+    }
+}
+
+// out[i][w] = OR of every strip that covers user-bin word w (windows[0] is the root's own strip, span 0 = none).
+// A thread keeps one word column w for all its rows, so the covering strips are looked up once.
+__global__ void __launch_bounds__(256)
+    hibf_merge_kernel(hibf_window const * __restrict__ windows, uint32_t n_windows, uint64_t const * __restrict__ strips,
+                      uint64_t n, uint32_t out_words, uint64_t * __restrict__ out)
+{
+    uint64_t const stream = policy_evict_first();
+    uint32_t const cols = out_words < 256 ? out_words : 256;
+    uint32_t const rows_per_block = 256 / cols;
+    uint32_t const r_in_block = threadIdx.x / cols;
+    if (r_in_block >= rows_per_block)
+        return;
+    for (uint32_t w = threadIdx.x % cols; w < out_words; w += cols)
+    {
+        constexpr int kMaxCover = 4;
+        uint64_t const * src[kMaxCover];
+        uint32_t span[kMaxCover];
+        int n_cover = 0;
+        bool overflow = false;
+        for (uint32_t g = 0; g < n_windows; ++g)
+        {
+            hibf_window const win = windows[g];
+            if (w - win.word_lo < win.span) // unsigned: also false for w < word_lo
+            {
+                if (n_cover < kMaxCover)
+                {
+                    src[n_cover] = strips + win.strip_off * n + (w - win.word_lo);
+                    span[n_cover] = win.span;
+                    ++n_cover;
+                }
+                else
+                    overflow = true;
+            }
+        }
+        for (uint64_t i = static_cast<uint64_t>(blockIdx.x) * rows_per_block + r_in_block; i < n;
+             i += static_cast<uint64_t>(gridDim.x) * rows_per_block)
+        {
+            uint64_t acc = 0;
+#pragma unroll
+            for (int c = 0; c < kMaxCover; ++c)
+                if (c < n_cover)
+                    acc |= ld_hint(src[c] + i * span[c], stream);
+            if (overflow) // more than kMaxCover strips cover this word: the general loop
+            {
+                acc = 0;
+                for (uint32_t g = 0; g < n_windows; ++g)
+                {
+                    hibf_window const win = windows[g];
+                    if (w - win.word_lo < win.span)
+                        acc |= ld_hint(strips + win.strip_off * n + i * win.span + (w - win.word_lo), stream);
+                }
+            }
+            st_hint(out + i * out_words + w, acc, stream);
+        }
+    }
+}
+
+// Same result through a shared-memory tile: a warp takes 32 rows, pulls every strip's 32 x span block in with
+// fully coalesced loads, ORs it into the tile and writes the 32 finished rows (contiguous in `out`) with
+// consecutive lanes on consecutive words.  Used when a 32-row tile fits (out_words <= kMergeTileWords).
+constexpr uint32_t kMergeWarps = 4;
+constexpr uint32_t kMergeTileWords = 64;
+
+__global__ void __launch_bounds__(kMergeWarps * 32)
+    hibf_merge_tile_kernel(hibf_window const * __restrict__ windows, uint32_t n_windows, uint64_t const * __restrict__ strips,
+                           uint64_t n, uint32_t out_words, uint64_t * __restrict__ out)
+{
+    extern __shared__ uint64_t merge_tile[];
+    uint64_t const stream = policy_evict_first();
+    unsigned const lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t const pitch = out_words + 1;
+    uint64_t * const tile = merge_tile + static_cast<size_t>(warp) * 32 * pitch;
+    uint32_t const inv_w = (65536 + out_words - 1) / out_words;
+    uint64_t const n_groups = (n + 31) / 32;
+    for (uint64_t g = static_cast<uint64_t>(blockIdx.x) * kMergeWarps + warp; g < n_groups; g += static_cast<uint64_t>(gridDim.x) * kMergeWarps)
+    {
+        uint64_t const base = g * 32;
+        uint32_t const rows = base + 32 <= n ? 32 : static_cast<uint32_t>(n - base);
+        for (uint32_t idx = lane; idx < 32 * pitch; idx += 32)
+            tile[idx] = 0;
+        __syncwarp();
+        for (uint32_t k = 0; k < n_windows; ++k)
+        {
+            hibf_window const win = windows[k];
+            if (win.span == 0)
+                continue;
+            uint32_t const inv = (65536 + win.span - 1) / win.span;
+            uint64_t const * const src = strips + win.strip_off * n + base * win.span;
+            for (uint32_t idx = lane; idx < rows * win.span; idx += 32)
+            {
+                uint32_t const r = (idx * inv) >> 16;
+                tile[r * pitch + win.word_lo + (idx - r * win.span)] |= ld_hint(src + idx, stream);
+            }
+            __syncwarp(); // strips may overlap in user-bin words: one at a time
+        }
+        uint64_t * const dst = out + base * out_words;
+        for (uint32_t idx = lane; idx < rows * out_words; idx += 32)
+        {
+            uint32_t const r = (idx * inv_w) >> 16;
+            st_hint(dst + idx, tile[r * pitch + (idx - r * out_words)], stream);
+        }
+        __syncwarp();
+    }
+}
+
 } // namespace trx
 
 struct trx_hibf
@@ -156,6 +534,17 @@ struct trx_hibf
     trx::scratch d_kmers, d_out, sort_tmp;
     int ibf_bits{1}; // bits needed for an IBF id (radix-sort range)
     bool sort_frontier{true};
+    bool fused{true};        // root + second level in one kernel (TRX_HIBF_FUSED=off → frontier kernels only)
+    int uniform_hash_funs{0}; // > 0 if every IBF uses the same number of hash functions
+    uint64_t root_bin_words{1};
+    trx::scratch root_words; // merged-bin hits of the root per k-mer
+    std::vector<trx::hibf_window> windows; // [0] = the root's own user bins, then root technical-bin ranges whose children share L2
+    trx::hibf_window * d_windows{nullptr};
+    uint64_t strip_words{0}; // Σ span
+    bool window_attr_set{false}, merge_attr_set{false};
+    unsigned window_ctas{6}; // resident CTAs per SM of the window kernel's persistent grid
+    bool fast_shape{false}; // every IBF: one word per row and fewer than 2^32 rows
+    trx::scratch strips;
     trx::hibf_dev dev() const
     {
         return trx::hibf_dev{d_words, d_ibfs, d_next, d_user, d_merged_mask, d_user_mask, static_cast<uint32_t>(out_words)};
@@ -167,6 +556,58 @@ using namespace trx;
 static constexpr uint64_t kChunk = 1ull << 20;   // k-mers per frontier pass
 static constexpr uint64_t kFanoutBudget = 32;    // frontier capacity = kFanoutBudget × chunk items
 static constexpr int kMaxLevels = 30;
+
+template <int H, bool FAST>
+static int launch_fused(trx_hibf * h, uint64_t const * d_kmers, uint64_t n, uint64_t * d_out, uint64_t * frontier,
+                        unsigned long long * ctr, uint64_t capacity)
+{
+    trx_ctx * c = h->ctx;
+    uint64_t const bw0 = h->root_bin_words;
+    TRX_TRY(h->root_words.reserve(n * bw0 * 8));
+    TRX_TRY(h->strips.reserve(n * h->strip_words * 8 + 8));
+    auto * rw = static_cast<uint64_t *>(h->root_words.ptr);
+    auto * strips = static_cast<uint64_t *>(h->strips.ptr);
+    hibf_window const & root = h->windows[0];
+    if (root.span)
+        TRX_CUDA(cudaMemsetAsync(strips, 0, n * root.span * 8, c->stream));
+    hibf_root_kernel<H, FAST><<<grid_for(n, 256, c->sm_count, 8), 256, 0, c->stream>>>(h->dev(), d_kmers, n, rw, root, strips, ctr);
+    ++c->launches;
+    if (!h->window_attr_set)
+    {
+        TRX_CUDA(cudaFuncSetAttribute(hibf_window_kernel<H, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      static_cast<int>(kWinThreads * (kMaxSpan + 1) * 8)));
+        h->window_attr_set = true;
+    }
+    unsigned const grid = grid_for((n + 31) / 32, kWinThreads / 32, c->sm_count, h->window_ctas);
+    for (size_t g = 1; g < h->windows.size(); ++g)
+    {
+        hibf_window const & win = h->windows[g];
+        size_t const smem = static_cast<size_t>(kWinThreads) * (win.span + 1) * 8;
+        hibf_window_kernel<H, FAST><<<grid, kWinThreads, smem, c->stream>>>(h->dev(), d_kmers, n, rw, win, strips + win.strip_off * n,
+                                                                     frontier, ctr, capacity);
+        ++c->launches;
+    }
+    if (h->out_words <= kMergeTileWords)
+    {
+        size_t const tile = static_cast<size_t>(kMergeWarps) * 32 * (h->out_words + 1) * 8;
+        if (!h->merge_attr_set)
+        {
+            TRX_CUDA(cudaFuncSetAttribute(hibf_merge_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          static_cast<int>(kMergeWarps * 32 * (kMergeTileWords + 1) * 8)));
+            h->merge_attr_set = true;
+        }
+        hibf_merge_tile_kernel<<<grid_for((n + 31) / 32, kMergeWarps, c->sm_count, 12), kMergeWarps * 32, tile, c->stream>>>(
+            h->d_windows, static_cast<uint32_t>(h->windows.size()), strips, n, static_cast<uint32_t>(h->out_words), d_out);
+    }
+    else
+    {
+        uint64_t const rows_per_block = 256 / (h->out_words < 256 ? h->out_words : 256);
+        hibf_merge_kernel<<<grid_for(n, static_cast<unsigned>(rows_per_block), c->sm_count, 8), 256, 0, c->stream>>>(
+            h->d_windows, static_cast<uint32_t>(h->windows.size()), strips, n, static_cast<uint32_t>(h->out_words), d_out);
+    }
+    ++c->launches;
+    return TRX_OK;
+}
 
 extern "C"
 {
@@ -274,6 +715,85 @@ int trx_hibf_upload(trx_ctx_t * ctx, const trx_hibf_desc * desc, trx_hibf_t ** o
     {
         char const * e = getenv("TRX_HIBF_SORT"); // TRX_HIBF_SORT=off: A/B evidence for the frontier sort
         h->sort_frontier = !(e && strcmp(e, "off") == 0);
+        e = getenv("TRX_HIBF_FUSED"); // TRX_HIBF_FUSED=off: frontier kernels for every level (A/B evidence)
+        h->fused = !(e && strcmp(e, "off") == 0) && depth >= 2;
+        if ((e = getenv("TRX_HIBF_CTAS")) && atoi(e) > 0)
+            h->window_ctas = static_cast<unsigned>(atoi(e));
+        h->fast_shape = true;
+        for (uint64_t i = 0; i < n; ++i)
+            if (ibfs[i].bin_words != 1 || ibfs[i].bin_size >= (1ull << 32))
+                h->fast_shape = false;
+        if (desc->n_user_bins >= 65536)
+            h->fast_shape = false; // 16-bit user-bin ids in the window kernel's shared-memory table
+        h->uniform_hash_funs = static_cast<int>(desc->hash_funs[0]);
+        for (uint64_t i = 1; i < n; ++i)
+            if (desc->hash_funs[i] != desc->hash_funs[0])
+                h->uniform_hash_funs = 0;
+        // windows: consecutive root technical bins whose children together stay below the L2 budget; for each the run of
+        // user-bin words its children report into (a window that would span more than kMaxSpan words is cut earlier)
+        h->root_bin_words = ibfs[0].bin_words;
+        uint64_t budget = 44ull << 20;
+        if ((e = getenv("TRX_HIBF_WINDOW_MB")) && atoll(e) > 0)
+            budget = static_cast<uint64_t>(atoll(e)) << 20;
+        auto word_range = [&](uint64_t ibf, uint32_t & lo, uint32_t & hi) {
+            for (uint64_t t = 0; t < static_cast<uint64_t>(ibfs[ibf].bin_words) * 64; ++t)
+            {
+                uint64_t idx = ibfs[ibf].table_off + t;
+                if (umask[idx / 64] >> (idx % 64) & 1)
+                {
+                    lo = std::min(lo, user[idx] >> 6);
+                    hi = std::max(hi, user[idx] >> 6);
+                }
+            }
+        };
+        {
+            uint32_t lo = UINT32_MAX, hi = 0;
+            word_range(0, lo, hi);
+            hibf_window root{0, 0, lo == UINT32_MAX ? 0 : lo, lo == UINT32_MAX ? 0 : hi - lo + 1, 0};
+            h->windows.push_back(root);
+            if (root.span > kMaxSpan)
+                h->fused = false;
+        }
+        uint32_t const root_bins = ibfs[0].bin_words * 64;
+        uint32_t begin = 0, lo = UINT32_MAX, hi = 0;
+        uint64_t bytes = 0;
+        auto close = [&](uint32_t end) {
+            if (lo != UINT32_MAX || bytes > 0)
+                h->windows.push_back(hibf_window{begin, end, lo == UINT32_MAX ? 0 : lo, lo == UINT32_MAX ? 0 : hi - lo + 1, 0});
+            begin = end;
+            lo = UINT32_MAX;
+            hi = 0;
+            bytes = 0;
+        };
+        for (uint32_t b = 0; b < root_bins && h->fused; ++b)
+        {
+            uint64_t const idx = ibfs[0].table_off + b;
+            if (!(mmask[idx / 64] >> (idx % 64) & 1))
+                continue;
+            uint64_t const child = next[idx];
+            uint64_t const child_bytes = ibfs[child].bin_size * ibfs[child].bin_words * 8;
+            uint32_t clo = UINT32_MAX, chi = 0;
+            word_range(child, clo, chi);
+            if (clo != UINT32_MAX && chi - clo + 1 > kMaxSpan)
+            {
+                h->fused = false; // one child alone reports into too wide a run: frontier kernels
+                break;
+            }
+            uint32_t const nlo = std::min(lo, clo), nhi = std::max(hi, chi);
+            bool const too_wide = nlo != UINT32_MAX && nhi - nlo + 1 > kMaxSpan;
+            if (b > begin && (bytes + child_bytes > budget || too_wide || b - begin >= kMaxWindowBins || (b >> 6) != (begin >> 6)))
+                close(b);
+            lo = std::min(lo, clo);
+            hi = std::max(hi, chi);
+            bytes += child_bytes;
+        }
+        close(root_bins);
+        h->strip_words = 0;
+        for (auto & win : h->windows)
+        {
+            win.strip_off = h->strip_words;
+            h->strip_words += win.span;
+        }
     }
     auto fail = [&](cudaError_t e)
     {
@@ -299,6 +819,8 @@ int trx_hibf_upload(trx_ctx_t * ctx, const trx_hibf_desc * desc, trx_hibf_t ** o
     if ((e = cudaMemcpyAsync(h->d_user, user.data(), table_total * 4, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess) return fail(e);
     if ((e = cudaMemcpyAsync(h->d_merged_mask, mmask.data(), table_total / 8, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess) return fail(e);
     if ((e = cudaMemcpyAsync(h->d_user_mask, umask.data(), table_total / 8, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess) return fail(e);
+    if ((e = cudaMalloc(&h->d_windows, h->windows.size() * sizeof(hibf_window))) != cudaSuccess) return fail(e);
+    if ((e = cudaMemcpyAsync(h->d_windows, h->windows.data(), h->windows.size() * sizeof(hibf_window), cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess) return fail(e);
     if ((e = cudaStreamSynchronize(ctx->stream)) != cudaSuccess) return fail(e);
     *out = h;
     return TRX_OK;
@@ -322,6 +844,9 @@ void trx_hibf_destroy(trx_hibf_t * h)
     h->d_kmers.release();
     h->d_out.release();
     h->sort_tmp.release();
+    h->root_words.release();
+    h->strips.release();
+    cudaFree(h->d_windows);
     delete h;
 }
 
@@ -334,21 +859,45 @@ uint64_t trx_hibf_user_bin_words(const trx_hibf_t * h)
 static int run_chunk(trx_hibf * h, uint64_t const * d_kmers, uint64_t n, uint64_t * d_out, uint64_t * visited)
 {
     trx_ctx * c = h->ctx;
-    uint64_t const capacity = kFanoutBudget * (n < 4096 ? 4096 : n);
-    TRX_TRY(h->frontier[0].reserve(capacity * 8));
-    TRX_TRY(h->frontier[1].reserve(capacity * 8));
+    bool const need_frontier = !h->fused || h->depth > 2;
+    uint64_t const capacity = need_frontier ? kFanoutBudget * (n < 4096 ? 4096 : n) : 0;
+    if (need_frontier)
+    {
+        TRX_TRY(h->frontier[0].reserve(capacity * 8));
+        TRX_TRY(h->frontier[1].reserve(capacity * 8));
+    }
     TRX_TRY(h->counters.reserve((kMaxLevels + 3) * 8));
     auto * ctr = static_cast<unsigned long long *>(h->counters.ptr);
     TRX_CUDA(cudaMemsetAsync(ctr, 0, (kMaxLevels + 3) * 8, c->stream));
-    TRX_CUDA(cudaMemsetAsync(d_out, 0, n * h->out_words * 8, c->stream));
-    unsigned const grid = grid_for(n, 256, c->sm_count, 8);
-    hibf_level_kernel<true><<<grid, 256, 0, c->stream>>>(h->dev(), d_kmers, n, nullptr,
-                                                         static_cast<uint64_t *>(h->frontier[0].ptr), ctr, 0, capacity, d_out);
-    ++c->launches;
+    int first_level = 1; // first level that still has to run through the frontier kernels
+    if (h->fused)
+    {
+        auto * fr = static_cast<uint64_t *>(h->frontier[0].ptr);
+        int const key = h->uniform_hash_funs * 2 + (h->fast_shape ? 1 : 0);
+        switch (key)
+        {
+        case 4: TRX_TRY((launch_fused<2, false>(h, d_kmers, n, d_out, fr, ctr, capacity))); break;
+        case 5: TRX_TRY((launch_fused<2, true>(h, d_kmers, n, d_out, fr, ctr, capacity))); break;
+        case 6: TRX_TRY((launch_fused<3, false>(h, d_kmers, n, d_out, fr, ctr, capacity))); break;
+        case 7: TRX_TRY((launch_fused<3, true>(h, d_kmers, n, d_out, fr, ctr, capacity))); break;
+        case 8: TRX_TRY((launch_fused<4, false>(h, d_kmers, n, d_out, fr, ctr, capacity))); break;
+        case 9: TRX_TRY((launch_fused<4, true>(h, d_kmers, n, d_out, fr, ctr, capacity))); break;
+        default: TRX_TRY((launch_fused<0, false>(h, d_kmers, n, d_out, fr, ctr, capacity))); break;
+        }
+        first_level = 2;
+    }
+    else
+    {
+        TRX_CUDA(cudaMemsetAsync(d_out, 0, n * h->out_words * 8, c->stream));
+        unsigned const grid = grid_for(n, 256, c->sm_count, 8);
+        hibf_level_kernel<true><<<grid, 256, 0, c->stream>>>(h->dev(), d_kmers, n, nullptr,
+                                                             static_cast<uint64_t *>(h->frontier[0].ptr), ctr, 0, capacity, d_out);
+        ++c->launches;
+    }
     unsigned const full_grid = static_cast<unsigned>(c->sm_count) * 8;
     // ping-pong: `cur` holds the items of the level about to run, `other` is free
     int cur = 0;
-    for (int level = 1; level < h->depth; ++level)
+    for (int level = first_level; level < h->depth; ++level)
     {
         if (h->sort_frontier)
         {
@@ -400,7 +949,8 @@ int trx_hibf_membership_dev(trx_hibf_t * h, const uint64_t * d_kmers, uint64_t n
     TRX_TRY(h->ctx->use());
     uint64_t visited = 0;
     uint64_t done = 0;
-    uint64_t chunk = kChunk;
+    // two-level HIBFs on the fused kernel need no frontier: the whole batch is one persistent launch
+    uint64_t chunk = (h->fused && h->depth <= 2) ? (n > kChunk ? n : kChunk) : kChunk;
     while (done < n)
     {
         uint64_t m = n - done < chunk ? n - done : chunk;
