@@ -542,7 +542,7 @@ struct trx_hibf
     trx::hibf_window * d_windows{nullptr};
     uint64_t strip_words{0}; // Σ span
     bool window_attr_set{false}, merge_attr_set{false};
-    unsigned window_ctas{6}; // resident CTAs per SM of the window kernel's persistent grid
+    unsigned window_ctas{8}; // resident CTAs per SM of the window kernel's persistent grid
     bool fast_shape{false}; // every IBF: one word per row and fewer than 2^32 rows
     trx::scratch strips;
     trx::hibf_dev dev() const
