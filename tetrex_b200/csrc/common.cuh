@@ -56,6 +56,9 @@ struct trx_ctx
     uint64_t launches{0};
     int sm_count{trx::kSMs};
     cudaEvent_t ev0{nullptr}, ev1{nullptr};
+    // second stream + events for the host-buffer entry points that overlap result copies with compute
+    cudaStream_t copy_stream{nullptr};
+    std::vector<cudaEvent_t> copy_events;
     // staging for the host-buffer entry points
     trx::scratch d_in[4];
     trx::scratch d_out[2];

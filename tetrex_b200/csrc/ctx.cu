@@ -127,6 +127,13 @@ void trx_ctx_destroy(trx_ctx_t * ctx)
         s.release();
     cudaEventDestroy(ctx->ev0);
     cudaEventDestroy(ctx->ev1);
+    for (cudaEvent_t e : ctx->copy_events)
+        cudaEventDestroy(e);
+    if (ctx->copy_stream)
+    {
+        cudaStreamSynchronize(ctx->copy_stream);
+        cudaStreamDestroy(ctx->copy_stream);
+    }
     if (ctx->owns_stream)
         cudaStreamDestroy(ctx->stream);
     delete ctx;

@@ -987,10 +987,40 @@ int trx_hibf_membership(trx_hibf_t * h, const uint64_t * kmers, uint64_t n, uint
     TRX_TRY(c->use());
     TRX_TRY(h->d_kmers.reserve(n * 8));
     TRX_TRY(h->d_out.reserve(n * h->out_words * 8));
-    TRX_CUDA(cudaMemcpyAsync(h->d_kmers.ptr, kmers, n * 8, cudaMemcpyHostToDevice, c->stream));
-    TRX_TRY(trx_hibf_membership_dev(h, static_cast<uint64_t *>(h->d_kmers.ptr), n, static_cast<uint64_t *>(h->d_out.ptr), stats));
-    TRX_CUDA(cudaMemcpyAsync(out_words, h->d_out.ptr, n * h->out_words * 8, cudaMemcpyDeviceToHost, c->stream));
+    auto * d_kmers = static_cast<uint64_t *>(h->d_kmers.ptr);
+    auto * d_out = static_cast<uint64_t *>(h->d_out.ptr);
+    TRX_CUDA(cudaMemcpyAsync(d_kmers, kmers, n * 8, cudaMemcpyHostToDevice, c->stream));
+    // The result (out_words x 8 B per k-mer, 128 B at C2) dwarfs the input: it leaves in pieces on a second stream
+    // while the next piece is being computed, so the call costs about max(compute, PCIe) instead of their sum.
+    uint64_t const piece = 1ull << 20;
+    if (!c->copy_stream)
+        TRX_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+    uint64_t visited = 0;
+    size_t k = 0;
+    for (uint64_t done = 0; done < n; done += piece, ++k)
+    {
+        uint64_t const m = n - done < piece ? n - done : piece;
+        uint64_t st[2] = {0, 0};
+        TRX_TRY(trx_hibf_membership_dev(h, d_kmers + done, m, d_out + done * h->out_words, st));
+        visited += st[0];
+        if (k >= c->copy_events.size())
+        {
+            cudaEvent_t e;
+            TRX_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            c->copy_events.push_back(e);
+        }
+        TRX_CUDA(cudaEventRecord(c->copy_events[k], c->stream));
+        TRX_CUDA(cudaStreamWaitEvent(c->copy_stream, c->copy_events[k], 0));
+        TRX_CUDA(cudaMemcpyAsync(out_words + done * h->out_words, d_out + done * h->out_words, m * h->out_words * 8,
+                                 cudaMemcpyDeviceToHost, c->copy_stream));
+    }
+    TRX_CUDA(cudaStreamSynchronize(c->copy_stream));
     TRX_CUDA(cudaStreamSynchronize(c->stream));
+    if (stats)
+    {
+        stats[0] = visited;
+        stats[1] = static_cast<uint64_t>(h->depth);
+    }
     return TRX_OK;
 }
 
