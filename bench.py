@@ -220,6 +220,10 @@ def run_ours(args):
     if rank == 0:
         peak, peak_src = peaks()
         algo_bytes = 32.0 * HASH_FUNS * visited_per_step
+        traffic = None  # DRAM bytes per step of the K3 kernels, from the committed ncu --set full capture
+        tpath = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1_traffic.json")
+        if os.path.exists(tpath):
+            traffic = json.load(open(tpath))["k3_dram_bytes_per_kmer"] * args.batch
         step_s = ms / 1e3 / args.steps
         achieved = algo_bytes / step_s / 1e9
         line = {
@@ -235,9 +239,12 @@ def run_ours(args):
                        "l2": "working set (HIBF + 512 MiB of result bitvectors per step) exceeds the 126 MB L2; no flush",
                        "visited_ibfs_per_kmer": visited_per_step / args.batch, "setup_s": round(setup_s, 1)},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "kernel": "hibf_level_kernel (root + lower level)", "peak_source": peak_src,
+                         "traffic": traffic, "kernel": "hibf_window_kernel (+ hibf_root_kernel, hibf_merge_tile_kernel: one step)",
+                         "peak_source": peak_src,
                          "algorithmic_bytes_per_step": algo_bytes,
-                         "note": "random 8-byte row reads counted as 32-byte sectors x h x visited IBFs"},
+                         "note": "algorithmic = 32-byte sector per 8-byte row read x h x visited IBFs (SURVEY 8(d)); achieved = that / "
+                                 "the step's device time (all K3 kernels); traffic = measured DRAM bytes per step (ncu), lower than "
+                                 "algorithmic because the child windows are served from L2"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": args.batch * 8,
                     "d2h_bytes_per_step": args.batch * W * 8, "steps": e_steps},
             "gpu_launches": int(launches), "clocks": clocks,
@@ -314,6 +321,15 @@ def extra_measurements(t, ctx, torch, residues, offs, rec_bin, planted, hibf, pe
         out["verify_cpu_residues_per_s"] = {"value": int(offs[n_rec]) / dt, "cores": os.cpu_count() or 1,
                                             "kind": "reference (RE2 FindAndConsume, records in memory, no gz/kseq)",
                                             "sample": f"first {n_rec} records"}
+
+    # ---- K4 on a PROSITE-style pattern (C2H2 zinc finger, PS00028): no selective literal factor exists, so phase 1 is
+    # the exact automaton kernel
+    prosite = "C.{2,4}C.{3}[LIVMFYWC].{8}H.{3,5}H"
+    rx2 = t.Regex(prosite, True)
+    h2 = txt.scan(rx2)
+    sec2 = timed(lambda: txt.scan(rx2), 3)
+    out["verify_prosite"] = {"pattern": prosite, "hits": int(len(h2)), "filter_literals": int(txt.last_filter_literals),
+                             "residues_per_s": n_res / sec2, "frac_of_hbm_peak": n_res / sec2 / 1e9 / peak}
 
     # ---- whole query: k-mers of the query -> K3 -> AND/OR on device -> K4 on the candidate bins
     aamap, _ = t.peptide_maps(t.RED_BASE)
