@@ -10,7 +10,7 @@ namespace trx
 static ibf_geom geom_of(trx_ibf const * f)
 {
     return ibf_geom{f->d_words, f->bin_size, f->shard_words, f->shard_word_begin,
-                    static_cast<uint32_t>(f->hash_shift), static_cast<uint32_t>(f->hash_funs)};
+                    static_cast<uint32_t>(f->hash_shift), static_cast<uint32_t>(f->hash_funs), 0, f->bin_size};
 }
 
 static int pow2_ceil(uint64_t x)
@@ -286,19 +286,37 @@ int trx_emplace_records_dev(trx_ibf_t * f, int molecule, uint32_t k, int reducti
     TRX_TRY(c->use());
     uint64_t n_runs = (n_residues + kRun - 1) / kRun;
     unsigned grid = grid_for(n_runs, 256, c->sm_count, 8);
-    if (molecule == TRX_MOL_NA)
-    {
-        emplace_dna_kernel<<<grid, 256, 0, c->stream>>>(geom_of(f), d_residues, n_residues, d_rec_offsets, d_rec_bin,
-                                                        n_records, k);
-    }
-    else
-    {
-        uint8_t * d_map = nullptr;
+    // A matrix that does not fit L2 is filled in row slices that do: every pass recomputes all hashes (cheap: the
+    // kernel is bound by the atomics, not the arithmetic) but only fires the atomics that fall into its slice, so the
+    // read-modify-writes stay in L2 instead of costing a 32-byte DRAM read and write-back each.  TRX_EMPLACE_WINDOW_MB
+    // sets the slice size (0 = one pass, the measured baseline).
+    uint64_t window = 64ull << 20;
+    if (char const * e = getenv("TRX_EMPLACE_WINDOW_MB"))
+        window = static_cast<uint64_t>(atoll(e)) << 20;
+    uint64_t const row_bytes = f->shard_words * 8;
+    uint64_t passes = window ? (f->bin_size * row_bytes + window - 1) / window : 1;
+    if (passes < 1)
+        passes = 1;
+    if (passes > 10)
+        passes = 1; // far beyond L2 (C4: 2.9 GB per GPU) re-hashing the text per slice costs more than the DRAM atomics
+    uint64_t const rows_per_pass = (f->bin_size + passes - 1) / passes;
+    uint8_t * d_map = nullptr;
+    if (molecule != TRX_MOL_NA)
         TRX_TRY(upload_aamap(c, reduction, &d_map));
-        emplace_records_kernel<TRX_MOL_AA><<<grid, 256, 0, c->stream>>>(geom_of(f), d_residues, n_residues,
-                                                                        d_rec_offsets, d_rec_bin, n_records, k, d_map);
+    for (uint64_t p = 0; p < passes; ++p)
+    {
+        ibf_geom g = geom_of(f);
+        g.row_lo = p * rows_per_pass;
+        g.row_hi = g.row_lo + rows_per_pass < f->bin_size ? g.row_lo + rows_per_pass : f->bin_size;
+        if (g.row_lo >= g.row_hi)
+            break;
+        if (molecule == TRX_MOL_NA)
+            emplace_dna_kernel<<<grid, 256, 0, c->stream>>>(g, d_residues, n_residues, d_rec_offsets, d_rec_bin, n_records, k);
+        else
+            emplace_records_kernel<TRX_MOL_AA><<<grid, 256, 0, c->stream>>>(g, d_residues, n_residues, d_rec_offsets, d_rec_bin,
+                                                                            n_records, k, d_map);
+        ++c->launches;
     }
-    ++c->launches;
     TRX_CUDA(cudaGetLastError());
     return TRX_OK;
 }

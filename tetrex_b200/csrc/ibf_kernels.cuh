@@ -18,6 +18,7 @@ struct ibf_geom
     uint64_t word_begin;    // first global word column held here
     uint32_t hash_shift;
     uint32_t hash_funs;
+    uint64_t row_lo, row_hi; // K1 only: rows this pass may touch (see trx_emplace_records_dev); [0, bin_size) otherwise
 };
 
 // ------------------------------------------------------------------------------------------- K2
@@ -279,7 +280,8 @@ struct emplace_sink
         for (uint32_t h = 0; h < g.hash_funs; ++h)
         {
             uint64_t const row = hash_row(v, static_cast<int>(h), g.hash_shift, g.bin_size);
-            atomicOr(reinterpret_cast<unsigned long long *>(g.words + row * g.shard_words + col), bit);
+            if (row - g.row_lo < g.row_hi - g.row_lo) // this pass's slice of the matrix (the L2-resident one)
+                atomicOr(reinterpret_cast<unsigned long long *>(g.words + row * g.shard_words + col), bit);
         }
     }
 };
