@@ -356,7 +356,7 @@ __global__ void __launch_bounds__(256)
         emplace_sink sink{g, 0, 0, false};
         sink.set_bin(__ldg(rec_bin + r));
 
-        uint64_t fwd = 0, rev = 0;
+        uint64_t fwd = 0;
         uint32_t cnt = 0;
 #pragma unroll 1
         for (uint64_t p = p0; p < last; ++p)
@@ -373,45 +373,13 @@ __global__ void __launch_bounds__(256)
                 } while (rec_end <= p);
                 sink.set_bin(__ldg(rec_bin + r));
                 cnt = 0;
-                fwd = rev = 0;
+                fwd = 0;
             }
-            uint8_t const c = buf[p - p0];
-            if constexpr (MOL == TRX_MOL_NA)
-            {
-                uint64_t const f = dna_code(c);
-                fwd = ((fwd << 2) & mask) | f;
-                rev = ((rev >> 2) & mask) | ((f ^ 2) << (2 * k - 2));
-            }
-            else
-            {
-                fwd = ((fwd << 5) & mask) | s_map[c];
-            }
+            fwd = ((fwd << 5) & mask) | s_map[buf[p - p0]]; // peptide_decomposer.h:261-291
             if (cnt < k)
                 ++cnt;
             if (cnt == k)
-            {
-                if constexpr (MOL == TRX_MOL_NA)
-                    sink(fwd <= rev ? fwd : rev);
-                else
-                    sink(fwd);
-                // DNA wrap-around k-mers (nucleotide_decomposer.h:104-111 rolls the WHOLE record in after the
-                // first k-mer): rec[j+1..k) ++ rec[0..j] for j = 0..k-2, emitted by the thread that owns the
-                // record's first window.
-                if constexpr (MOL == TRX_MOL_NA)
-                {
-                    if (p + 1 - k == rec_begin)
-                    {
-                        uint64_t wf = fwd, wr = rev;
-                        for (uint32_t j = 0; j + 1 < k; ++j)
-                        {
-                            uint64_t const f = dna_code(buf[rec_begin + j - p0]);
-                            wf = ((wf << 2) & mask) | f;
-                            wr = ((wr >> 2) & mask) | ((f ^ 2) << (2 * k - 2));
-                            sink(wf <= wr ? wf : wr);
-                        }
-                    }
-                }
-            }
+                sink(fwd);
         }
     }
 }
