@@ -246,3 +246,119 @@ def test_hibf_large_batch_matches_oracle(ctx, golden_dir):
     h = t.HIBF.from_tables(ctx, tb)
     assert np.array_equal(h.membership(q), tb.membership(q, threads=8))
     h.close()
+
+
+# ---- shapes seqan's layout does not produce at the golden sizes: three levels, IBFs wider than 64 technical bins,
+# per-IBF hash counts, user bins scattered over the whole result row, split bins — every kernel route of K3
+MERGED = np.uint64(0xFFFFFFFFFFFFFFFF)
+DELETED = np.uint64(0xFFFFFFFFFFFFFFFE)
+
+
+def synth_hibf(seed, n_user, root_tb, child_tb, grand_tb, hash_funs, scatter, values_per_bin=150):
+    """Random HIBF: root (root_tb technical bins) → children (child_tb) → grandchildren (grand_tb).  user bins are
+    dealt to the three levels; `scatter` permutes user-bin ids so that neighbouring technical bins report into
+    distant words of the result row.  Bits are set with the oracle's emplace."""
+    rng = np.random.default_rng(seed)
+    ids = rng.permutation(n_user) if scatter else np.arange(n_user)
+    vals = {int(u): rng.integers(0, 2 ** 40, values_per_bin, dtype=np.uint64) for u in range(n_user)}
+    it = iter(int(u) for u in ids)
+    ibfs = []  # dicts: tb, h, table[(kind, x)], filled later
+
+    def new_ibf(tb, h):
+        ibfs.append(dict(tb=tb, h=h, table=[("deleted", 0)] * tb))
+        return len(ibfs) - 1
+
+    def take(k):
+        out = []
+        for _ in range(k):
+            try:
+                out.append(next(it))
+            except StopIteration:
+                break
+        return out
+
+    root = new_ibf(root_tb, hash_funs[0])
+    n_children = min(6, root_tb // 4)
+    for c in range(n_children):
+        child = new_ibf(child_tb, hash_funs[1 % len(hash_funs)] if c % 2 else hash_funs[0])
+        ibfs[root]["table"][2 * c] = ("merged", child)
+        if c < 2:  # two children carry a third level
+            g = new_ibf(grand_tb, hash_funs[2 % len(hash_funs)])
+            ibfs[child]["table"][0] = ("merged", g)
+            for tb_i, u in enumerate(take(grand_tb // 2)):
+                ibfs[g]["table"][2 * tb_i] = ("user", u)
+                ibfs[g]["table"][2 * tb_i + 1] = ("user", u)  # split bin: two technical bins, one user bin
+        for tb_i, u in enumerate(take(child_tb // 2 - 1)):
+            ibfs[child]["table"][child_tb - 1 - tb_i] = ("user", u)
+    for tb_i, u in enumerate(take(root_tb // 4)):
+        ibfs[root]["table"][root_tb - 1 - tb_i] = ("user", u)
+    placed = {x for d in ibfs for kind, x in d["table"] if kind == "user"}
+
+    def subtree_users(i):
+        us = []
+        for kind, x in ibfs[i]["table"]:
+            if kind == "user":
+                us.append(x)
+            elif kind == "merged":
+                us += subtree_users(x)
+        return sorted(set(us))
+
+    words, nxt, ub, bins, bsz, hf = [], [], [], [], [], []
+    for i, d in enumerate(ibfs):
+        per_tb = []
+        for t_i, (kind, x) in enumerate(d["table"]):
+            if kind == "user":
+                v = vals[x]
+                # a split bin stores alternating halves in its technical bins
+                twins = [j for j, (k2, x2) in enumerate(d["table"]) if k2 == "user" and x2 == x]
+                per_tb.append(v[twins.index(t_i)::len(twins)])
+            elif kind == "merged":
+                per_tb.append(np.concatenate([vals[u] for u in subtree_users(x)]) if subtree_users(x) else np.zeros(0, np.uint64))
+            else:
+                per_tb.append(np.zeros(0, np.uint64))
+        size = max(64, int(max(len(v) for v in per_tb) * 5) | 1)
+        f = ob.OracleIBF(d["tb"], size, d["h"])
+        for t_i, v in enumerate(per_tb):
+            if len(v):
+                f.emplace(v, np.full(len(v), t_i, dtype=np.uint32))
+        words.append(f.words)
+        bins.append(d["tb"])
+        bsz.append(size)
+        hf.append(d["h"])
+        nxt.append(np.array([x if kind == "merged" else i for kind, x in d["table"]], dtype=np.uint64))
+        ub.append(np.array([MERGED if kind == "merged" else (np.uint64(x) if kind == "user" else DELETED) for kind, x in d["table"]],
+                           dtype=np.uint64))
+    tb = ob.HIBFTables(n_user, bins, bsz, hf, words, nxt, ub)
+    present = np.concatenate([vals[u][:40] for u in sorted(placed)])
+    query = np.concatenate([present, rng.integers(0, 2 ** 40, 3000, dtype=np.uint64)])
+    rng.shuffle(query)
+    return tb, query, vals, placed
+
+
+@pytest.mark.parametrize("case", [
+    dict(seed=1, n_user=400, root_tb=64, child_tb=64, grand_tb=64, hash_funs=[3], scatter=False),    # FAST shape, 3 levels
+    dict(seed=2, n_user=900, root_tb=128, child_tb=192, grand_tb=64, hash_funs=[3], scatter=False),  # multi-word IBFs
+    dict(seed=3, n_user=500, root_tb=64, child_tb=64, grand_tb=64, hash_funs=[2, 4, 3], scatter=False),  # per-IBF hash counts
+    dict(seed=4, n_user=4000, root_tb=64, child_tb=64, grand_tb=64, hash_funs=[3], scatter=True),    # spans too wide: frontier route
+    dict(seed=5, n_user=70000, root_tb=64, child_tb=128, grand_tb=64, hash_funs=[2], scatter=False),  # > 65535 user bins
+])
+def test_hibf_synthetic_shapes(ctx, case, monkeypatch):
+    tb, query, vals, placed = synth_hibf(**case)
+    want = tb.membership(query, threads=4)
+    # no false negatives by construction: every inserted value reports its user bin
+    some = sorted(placed)[:: max(1, len(placed) // 50)]
+    probe = np.array([vals[u][7] for u in some], dtype=np.uint64)
+    hits = tb.membership(probe)
+    assert all((int(hits[j][u >> 6]) >> (u & 63)) & 1 for j, u in enumerate(some))
+    if ob.have_ref() and case["n_user"] <= 4000:
+        assert np.array_equal(ob.RefHIBF.from_tables(tb).membership(query[:500], 1), want[:500])  # the reference's own recursion
+    for fused in ("on", "off"):
+        monkeypatch.setenv("TRX_HIBF_FUSED", fused)
+        h = t.HIBF.from_tables(ctx, tb)
+        got, st = h.membership(query, stats=True)
+        assert np.array_equal(got, want), (case, fused)
+        assert st[1] == 3
+        one = h.membership(query[:1])  # a single k-mer (collector batches are tiny)
+        assert np.array_equal(one, want[:1])
+        h.close()
+    monkeypatch.delenv("TRX_HIBF_FUSED")
