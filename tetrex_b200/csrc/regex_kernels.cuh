@@ -128,14 +128,19 @@ __device__ __forceinline__ void step(state<W> & S, scan_tables<W> const & T, uin
 #pragma unroll
     for (int k = 0; k < W; ++k)
     {
-        uint64_t s = S.w[k];
-        while (s)
-        {
-            int i = __ffsll(static_cast<long long>(s)) - 1;
-            s &= s - 1;
+        // 32-bit halves: find-first-set on 32 bits is one FLO, on 64 bits a dozen instructions
 #pragma unroll
-            for (int q = 0; q < W; ++q)
-                F[q] |= T.follow[k * 64 + i][q];
+        for (int half = 0; half < 2; ++half)
+        {
+            uint32_t s = static_cast<uint32_t>(S.w[k] >> (32 * half));
+            while (s)
+            {
+                int i = __ffs(static_cast<int>(s)) - 1 + 32 * half;
+                s &= s - 1;
+#pragma unroll
+                for (int q = 0; q < W; ++q)
+                    F[q] |= T.follow[k * 64 + i][q];
+            }
         }
     }
 #pragma unroll
@@ -277,11 +282,18 @@ __global__ void __launch_bounds__(kScanThreads)
         if (g_lo < p.n_text)
         {
             uint64_t const g_hi = min(g_lo + kChunkBytes, p.n_text); // exclusive
-            // first byte in reading direction
-            int64_t g = DIR > 0 ? static_cast<int64_t>(g_lo) : static_cast<int64_t>(g_hi) - 1;
-            uint64_t r = record_of(p.rec_offsets, p.n_records, static_cast<uint64_t>(g));
+            // Positions inside the chunk are counted as STEPS in reading direction — step j reads address g_lo + j
+            // forwards, g_lo + 127 - j backwards — so the per-byte bookkeeping is 32-bit: `boundary` = first step
+            // that no longer belongs to the current record, `first_step` = step of the record's first byte (negative
+            // if the record began before this chunk).  Only the last chunk of the text is short: forwards it ends at
+            // step n_here, backwards its first 128 - n_here steps are padding.
+            int32_t const n_here = static_cast<int32_t>(g_hi - g_lo);
+            int32_t const j_lo = DIR > 0 ? 0 : kChunkBytes - n_here;
+            int32_t const j_hi = DIR > 0 ? n_here : kChunkBytes;
+            uint64_t const g_first = DIR > 0 ? g_lo : g_hi - 1;
+            uint64_t r = record_of(p.rec_offsets, p.n_records, g_first);
             uint64_t rec_begin = __ldg(p.rec_offsets + r), rec_end = __ldg(p.rec_offsets + r + 1);
-            while (rec_end <= static_cast<uint64_t>(g)) // empty records sharing this offset
+            while (rec_end <= g_first) // empty records sharing this offset
             {
                 ++r;
                 rec_begin = rec_end;
@@ -293,18 +305,72 @@ __global__ void __launch_bounds__(kScanThreads)
             for (int k = 0; k < W; ++k)
                 S.w[k] = 0;
             bool chunk_hit = false, rec_hit = false;
-
+            int32_t boundary = 0, first_step = 0;
+            auto set_bounds = [&](int32_t j, uint64_t gb)
+            {
+                uint64_t const left = DIR > 0 ? rec_end - gb : gb - rec_begin + 1; // steps until the record is left
+                uint64_t const done = DIR > 0 ? gb - rec_begin : rec_end - 1 - gb; // steps since its first byte
+                boundary = j + static_cast<int32_t>(left < (1u << 20) ? left : (1u << 20));
+                first_step = done < (1u << 20) ? j - static_cast<int32_t>(done) : -(1 << 20);
+            };
+            set_bounds(j_lo, g_first);
+            bool pending_start = j_lo > 0; // backwards, short last chunk: nothing to read before step j_lo
+            bool const cand_at_start = cand;
+            if (pending_start)
+            {
+                cand = false;
+                boundary = j_lo;
+            }
             auto flush_record = [&]()
             {
                 if (rec_hit)
                     list_record(p, r);
                 rec_hit = false;
             };
-            // one byte of the automaton; returns nothing, updates S / flags
-            auto feed = [&](uint8_t c, bool inject)
+            // step j == boundary: the next record in reading direction begins, or the text ends
+            auto on_boundary = [&](int32_t j)
             {
-                bool const at_first = DIR > 0 ? (static_cast<uint64_t>(g) == rec_begin) : (static_cast<uint64_t>(g) + 1 == rec_end);
-                bool const at_last = DIR > 0 ? (static_cast<uint64_t>(g) + 1 == rec_end) : (static_cast<uint64_t>(g) == rec_begin);
+                if (pending_start)
+                {
+                    pending_start = false;
+                    cand = cand_at_start;
+                    set_bounds(j_lo, g_first);
+                    return;
+                }
+                flush_record();
+#pragma unroll
+                for (int k = 0; k < W; ++k)
+                    S.w[k] = 0;
+                if (j >= j_hi)
+                {
+                    cand = false; // padding behind the last residue
+                    boundary = 1 << 30;
+                    return;
+                }
+                uint64_t const gb = DIR > 0 ? g_lo + j : g_lo + (kChunkBytes - 1 - j);
+                if constexpr (DIR > 0)
+                {
+                    do
+                    {
+                        ++r;
+                        rec_begin = rec_end;
+                        rec_end = __ldg(p.rec_offsets + r + 1);
+                    } while (rec_end <= gb);
+                }
+                else
+                {
+                    do
+                    {
+                        --r;
+                        rec_end = rec_begin;
+                        rec_begin = __ldg(p.rec_offsets + r);
+                    } while (rec_begin > gb);
+                }
+                cand = is_candidate(p.cand_words, __ldg(p.rec_bin + r));
+                set_bounds(j, gb);
+            };
+            auto feed = [&](uint8_t c, bool inject, bool at_first, bool at_last)
+            {
                 step<W>(S, T, c, inject && (!anchor_begin || at_first));
                 if (S.any() && accepts<W>(S, T) && (!anchor_end || at_last))
                 {
@@ -317,75 +383,43 @@ __global__ void __launch_bounds__(kScanThreads)
 #pragma unroll 1
             for (int piece = 0; piece < kChunkBytes / 16; ++piece)
             {
-                int const pi = DIR > 0 ? piece : (kChunkBytes / 16 - 1 - piece);
-                uint64_t const piece_lo = g_lo + static_cast<uint64_t>(pi) * 16;
-                if (piece_lo >= g_hi)
-                    continue; // beyond the end of the text (only in the last chunk)
+                int32_t const j0 = piece * 16;
+                if (j0 >= j_hi)
+                    break; // beyond the end of the text (forwards, last chunk)
+                if (j0 + 16 <= j_lo)
+                    continue; // padding before the last residue (backwards, last chunk)
+                int const pi = DIR > 0 ? piece : kChunkBytes / 16 - 1 - piece;
                 uint4 v;
                 if constexpr (USE_TMA)
                     v = *reinterpret_cast<uint4 const *>(row + ((pi ^ (tid & 7)) << 4));
                 else
-                    v = __ldg(reinterpret_cast<uint4 const *>(p.text + piece_lo));
+                    v = __ldg(reinterpret_cast<uint4 const *>(p.text + g_lo + static_cast<uint64_t>(pi) * 16));
                 uint32_t const words[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
                 for (int b = 0; b < 16; ++b)
                 {
-                    int const bi = DIR > 0 ? b : 15 - b;
-                    uint64_t const gb = piece_lo + bi;
-                    if (gb >= g_hi)
-                        continue;
-                    g = static_cast<int64_t>(gb);
-                    // record boundary in reading direction
-                    if (DIR > 0 ? (gb >= rec_end) : (gb < rec_begin))
-                    {
-                        flush_record();
-                        if constexpr (DIR > 0)
-                        {
-                            do
-                            {
-                                ++r;
-                                rec_begin = rec_end;
-                                rec_end = __ldg(p.rec_offsets + r + 1);
-                            } while (rec_end <= gb);
-                        }
-                        else
-                        {
-                            do
-                            {
-                                --r;
-                                rec_end = rec_begin;
-                                rec_begin = __ldg(p.rec_offsets + r);
-                            } while (rec_begin > gb);
-                        }
-                        cand = is_candidate(p.cand_words, __ldg(p.rec_bin + r));
-#pragma unroll
-                        for (int k = 0; k < W; ++k)
-                            S.w[k] = 0;
-                    }
+                    int32_t const j = j0 + b;
+                    if (j == boundary)
+                        on_boundary(j);
                     if (!cand)
                         continue;
+                    int const bi = DIR > 0 ? b : 15 - b;
                     uint8_t const c = static_cast<uint8_t>(words[bi >> 2] >> ((bi & 3) * 8));
-                    feed(c, true);
+                    feed(c, true, j == first_step, j + 1 == boundary);
                 }
             }
             // run on past the chunk while a match that started inside it is still alive
-            if (cand && S.any())
+            if (cand && S.any() && (DIR < 0 || n_here == kChunkBytes))
             {
                 if constexpr (DIR > 0)
                 {
                     for (uint64_t gb = g_hi; gb < rec_end && S.any(); ++gb)
-                    {
-                        g = static_cast<int64_t>(gb);
-                        feed(__ldg(p.text + gb), false);
-                    }
+                        feed(__ldg(p.text + gb), false, false, gb + 1 == rec_end);
                 }
                 else
                 {
                     for (int64_t gb = static_cast<int64_t>(g_lo) - 1; gb >= static_cast<int64_t>(rec_begin) && S.any(); --gb)
-                    {
-                        g = gb;
-                        feed(__ldg(p.text + gb), false);
-                    }
+                        feed(__ldg(p.text + gb), false, false, static_cast<uint64_t>(gb) == rec_begin);
                 }
             }
             flush_record();
