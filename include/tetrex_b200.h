@@ -209,10 +209,22 @@ typedef struct trx_hit {
  * complemented, reversed records (src/query.cpp:7-16,167-191).  hits come back sorted by
  * (bin, record, start) = the reference's -t 1 print order.  If more than cap hits exist, *n_hits holds the
  * total, the call returns TRX_ECAPACITY and the contents of hits are unspecified (call again with room).
- * stats (nullable, 2 entries): [0] = residues scanned, [1] = literals in the SIMD prefilter (0 = the exact
- * automaton kernel ran as phase 1). */
+ * stats (nullable, 2 entries): [0] = residues scanned, [1] = literals (fixed window) or atoms (gapped factor) of the
+ * SIMD prefilter (0 = the exact automaton kernel ran as phase 1). */
 int trx_regex_scan(trx_text_t *text, trx_regex_t *re, const uint64_t *candidate_bin_words, int reverse_strand,
                    const uint8_t *map256, trx_hit *hits, uint64_t cap, uint64_t *n_hits, uint64_t *stats);
+
+/* Host only, no device needed: the phase-1 prefilter trx_regex_scan would pick for this regex on a text with the
+ * given relative byte frequencies (what RE2 does internally with its prefilter/memchr accelerations,
+ * lib/re2/re2/prog.h ConfigurePrefixAccel — here the plan is visible so that tests can check it is a NECESSARY
+ * condition of every match).  out[0] = 0 none (exact automaton), 1 fixed window, 2 gapped atoms.
+ * window: out[1] = literals in bytes 0..3, out[2] = in bytes 4..7, out[3] = address of the match's first byte minus
+ *         address of window byte 0, out[8+j] = byte offset of literal j in the window, out[16+j] = literal byte.
+ * atoms:  out[1] = distinct literals, out[2] = atoms, out[3], out[4] = the match's first byte lies at an address in
+ *         [anchor + out[3], anchor + out[4]]; atom a: literal byte out[8+a] at anchor + d for a d in
+ *         [out[16+a], out[24+a]]. */
+int trx_regex_filter_plan(const trx_regex_t *re, const double *byte_freq, int reverse_strand, const uint8_t *map256,
+                          int32_t out[48]);
 
 #ifdef __cplusplus
 }

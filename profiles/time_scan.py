@@ -8,7 +8,9 @@ from tetrex_b200 import synth
 ctx = t.Context(0)
 residues, offs, rec_bin, planted = synth.swissprot_like(570_000, 1024)
 txt = t.Text(ctx, residues, offs, rec_bin, 1024)
-for pat, posix in [("LMA(E|Q)GLYN", True), ("G.{2,4}K[ILV]", True), ("C.{2,4}C.{3}[LIVMFYWC].{8}H.{3,5}H", True)]:
+pats = sys.argv[1:] or ["LMA(E|Q)GLYN", "G.{2,4}K[ILV]", "C.{2,4}C.{3}[LIVMFYWC].{8}H.{3,5}H", "W.{2,4}C.{5,9}CW",
+                        "C.{2}C.{12}H.{3,5}H.{2}M", "D.{0,3}EW", "M.{2}(C|W)H.{3,4}(WK|WR)C"]
+for pat, posix in [(p, True) for p in pats]:
     rx = t.Regex(pat, posix)
     for env in ("", "off"):
         if env:

@@ -135,6 +135,78 @@ def test_factor_filter_equals_exact_automaton(ctx, monkeypatch):
     dtxt.close()
 
 
+def test_atom_filter_equals_exact_automaton(ctx, monkeypatch):
+    """Phase 1, gapped variant (literal masks + shifted mask algebra, regex_filter_atoms): PROSITE-style patterns with
+    x(m,n) gaps, instances planted across chunk (128 B) and tile (32 KB) borders, at record ends and back to back."""
+    from test_filter_plan_cpu import sample
+    rng = random.Random(77)
+    aa = "ACDEFGHIKLMNPQRSTVWY"
+    weights = [8.25, 1.37, 5.45, 6.75, 3.86, 7.07, 2.27, 5.96, 5.84, 9.66, 2.42, 4.06, 4.70, 3.93, 5.53, 6.56, 5.34, 6.87, 1.08, 2.92]
+    lengths = [70000, 127, 40, 0, 33000, 128 * 256, 128 * 256 + 5, 900, 66000]
+    rec_bin = [0, 0, 1, 1, 2, 2, 3, 3, 4]
+    finder = ob.ref_find_all if ob.have_ref() else ob.find_all_python
+    for pat in ["C.{2,4}C.{3}[LIVMFYWC].{8}H.{3,5}H", "W.{2,4}C.{5,9}CW", "D.{0,3}EW", "M.{2}(C|W)H.{3,4}(WK|WR)C",
+                "C.{12,16}W.{10,14}H.{2}M", "WM.{30,31}CH", "(C.{2,3}){2}WH", "C[ST]?W.{2,5}HM$"]:
+        body = pat.rstrip("$")
+        seqs = [bytearray("".join(rng.choices(aa, weights=weights, k=L)).encode()) for L in lengths]
+        planted = 0
+        for r, L in enumerate(lengths):
+            spots = [0, 60, 100, 120, 127, 128, 250, 32768 - 40, 32768 - 20, 32768 - 3, 32768, 65536 - 10, L - 60, L - 30]
+            for pos in spots:
+                inst = sample(body, aa, rng).encode()
+                if pos < 0 or pos + len(inst) > L:
+                    continue
+                seqs[r][pos:pos + len(inst)] = inst
+                planted += 1
+            inst = sample(body, aa, rng).encode()  # one flush with the record end
+            if len(inst) <= L:
+                seqs[r][L - len(inst):] = inst
+        seqs = [bytes(x) for x in seqs]
+        txt = build_text(ctx, seqs, rec_bin, 5)
+        rx = t.Regex(pat, True)
+        monkeypatch.setenv("TRX_REGEX_FILTER", "atoms")
+        a = txt.scan(rx)
+        assert txt.last_filter_literals >= 2, (pat, txt.last_filter_literals)
+        monkeypatch.setenv("TRX_REGEX_FILTER", "off")
+        b = txt.scan(rx)
+        assert txt.last_filter_literals == 0
+        monkeypatch.delenv("TRX_REGEX_FILTER")
+        c = txt.scan(rx)
+        want = expected_hits(seqs, rec_bin, pat, True, finder)
+        assert len(want) >= (5 if pat.endswith("$") else planted // 3), (pat, len(want), planted)
+        assert np.array_equal(a, want), (pat, "atoms", len(a), len(want))
+        assert np.array_equal(b, want) and np.array_equal(c, want), pat
+        cand = np.array([0b10101], dtype=np.uint64)
+        monkeypatch.setenv("TRX_REGEX_FILTER", "atoms")
+        got = txt.scan(rx, candidate_bins=cand)
+        monkeypatch.delenv("TRX_REGEX_FILTER")
+        assert np.array_equal(got, expected_hits(seqs, rec_bin, pat, True, finder, cand={0, 2, 4})), (pat, "subset")
+        txt.close()
+    # DNA, both strands (leftmost-first semantics, complement folded into the byte table)
+    revcomp = lambda s: s.translate(COMP)[::-1]
+    for pat in ["TATA.{2,4}CGCG", "GG.{1,6}CCATGG", "CG.{3}(AT|TA)GC.{0,2}GG"]:
+        dna = [bytearray(bytes(rng.choice(b"ACGT") for _ in range(L))) for L in [50000, 130, 7, 128 * 256 + 64]]
+        for r, L in enumerate([50000, 130, 7, 128 * 256 + 64]):
+            for pos in [0, 100, 125, 32768 - 8, 32768 - 1, L - 20]:
+                for rev in (False, True):
+                    inst = sample(pat, "ACGT", rng).encode()
+                    inst = revcomp(inst) if rev else inst
+                    q = pos + (40 if rev else 0)
+                    if q >= 0 and q + len(inst) <= L:
+                        dna[r][q:q + len(inst)] = inst
+        dna = [bytes(x) for x in dna]
+        dtxt = build_text(ctx, dna, [0, 1, 1, 1], 2)
+        rx = t.Regex(pat, False)
+        for rev in (False, True):
+            monkeypatch.setenv("TRX_REGEX_FILTER", "atoms")
+            a = dtxt.scan(rx, reverse_strand=rev)
+            assert dtxt.last_filter_literals >= 2, (pat, rev)
+            monkeypatch.delenv("TRX_REGEX_FILTER")
+            want = expected_hits(dna, [0, 1, 1, 1], pat, False, finder, transform=revcomp if rev else None)
+            assert len(want) >= 4 and np.array_equal(a, want), (pat, rev, len(a), len(want))
+        dtxt.close()
+
+
 def test_reverse_strand(ctx):
     """reverse_verify_fasta_hit (src/query.cpp:167-191): the record is complemented through comp_tab and reversed."""
     rng = random.Random(9)

@@ -77,6 +77,7 @@ PROTOTYPES = {
     "trx_regex_destroy": (None, [vp]),
     "trx_regex_positions": (C.c_int, [vp]),
     "trx_regex_scan": (C.c_int, [vp, vp, vp, C.c_int, vp, vp, C.c_uint64, u64p, u64p]),
+    "trx_regex_filter_plan": (C.c_int, [vp, vp, C.c_int, vp, vp]),
 }
 
 _lib = None

@@ -268,6 +268,23 @@ class Regex:
         self.pattern = pattern
         self.positions = lib().trx_regex_positions(self._h)
 
+    def filter_plan(self, byte_freq, reverse_strand=False, map256=None) -> dict:
+        """The phase-1 prefilter a scan would use on a text with these relative byte frequencies (host only)."""
+        f = _np(byte_freq, np.float64)
+        assert len(f) == 256
+        m = _np(map256, np.uint8) if map256 is not None else None
+        out = np.zeros(48, dtype=np.int32)
+        check(lib().trx_regex_filter_plan(self._h, _ptr(f), int(reverse_strand), _ptr(m) if m is not None else None, _ptr(out)))
+        kind = int(out[0])
+        if kind == 1:
+            n = int(out[1] + out[2])
+            return {"kind": "window", "start_delta": int(out[3]),
+                    "literals": [(int(out[8 + j]), int(out[16 + j])) for j in range(n)]}  # (window byte, literal)
+        if kind == 2:
+            return {"kind": "atoms", "n_lit": int(out[1]), "start_lo": int(out[3]), "start_hi": int(out[4]),
+                    "atoms": [(int(out[8 + a]), int(out[16 + a]), int(out[24 + a])) for a in range(int(out[2]))]}  # (literal, lo, hi)
+        return {"kind": "none"}
+
     def close(self):
         if self._h:
             lib().trx_regex_destroy(self._h)

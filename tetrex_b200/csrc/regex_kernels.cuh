@@ -25,7 +25,9 @@ namespace trx
 constexpr int kChunkBytes = 128;
 constexpr int kScanThreads = 256;
 constexpr int kTileBytes = kChunkBytes * kScanThreads; // 32 KB
-constexpr int kStages = 2;
+constexpr int kStages = 2;              // exact automaton kernel (phase 1)
+constexpr int kFilterStagesDefault = 2; // prefilter kernels; see filter_stages()
+constexpr unsigned long long kSmallHits = 1024;
 
 // device copy of the automaton; B already has the per-scan byte map (redmap / comp_tab) folded in
 struct regex_dev
@@ -56,6 +58,21 @@ struct filter_spec
     uint32_t splat[8];        // literal byte replicated into all four lanes
 };
 
+// gapped necessary-factor prefilter ("atoms"): up to 4 distinct literal bytes and up to 8 atoms, each saying
+// "literal `lit` occurs at address anchor + d for some d in [lo, hi]" (0 <= lo <= hi <= 31).  One atom is the
+// anchor itself (lo = hi = 0).  Atoms are grouped by literal: literal l owns atoms [atom_begin[l], atom_begin[l+1]).
+// Every match contains such a constellation, and its first byte (reading direction) lies at an address in
+// [anchor + start_lo, anchor + start_hi].  Derived on the host from the automaton's dominator chain.
+struct atom_spec
+{
+    int32_t n_lit;            // 0: unused
+    int32_t n_atoms;
+    int32_t start_lo, start_hi;
+    uint32_t splat[4];
+    uint8_t atom_begin[8];    // n_lit + 1 entries used
+    uint8_t lo[8], hi[8];
+};
+
 struct scan_params
 {
     uint8_t const * text;         // padded to a tile multiple, zero filled
@@ -73,6 +90,7 @@ struct scan_params
     unsigned int * rec_count;
     regex_dev const * re;
     filter_spec filter;
+    atom_spec atoms;
 };
 
 // first flagging of a record appends it to the phase-2 work list
@@ -446,6 +464,8 @@ struct resolve_params
     unsigned long long * hit_count;
     uint64_t * hit_keys;               // record << 32 | start
     uint32_t * hit_ends;
+    uint64_t * small_keys;             // the first kSmallHits hits go here: they sit next to the counters, so that
+    uint32_t * small_ends;             // one device-to-host copy brings the count and (almost always) every hit
     uint64_t cap;
 };
 
@@ -560,6 +580,9 @@ template <int W, int DIR>
 __global__ void __launch_bounds__(128) regex_scan_phase2(resolve_params p)
 {
     __shared__ regex_dev s_re; // the automaton, staged once per CTA: every attempt starts with a B[] lookup
+    // usually a handful of records are listed: CTAs without work leave before staging anything
+    if (static_cast<uint64_t>(blockIdx.x) * (blockDim.x >> 5) >= *p.rec_count)
+        return;
     {
         uint32_t const * src = reinterpret_cast<uint32_t const *>(p.re);
         uint32_t * dst = reinterpret_cast<uint32_t *>(&s_re);
@@ -617,8 +640,17 @@ __global__ void __launch_bounds__(128) regex_scan_phase2(resolve_params p)
                     unsigned long long idx = atomicAdd(p.hit_count, 1ULL);
                     if (idx < p.cap)
                     {
-                        p.hit_keys[idx] = (r << 32) | static_cast<uint64_t>(s + leader);
-                        p.hit_ends[idx] = static_cast<uint32_t>(e_hit);
+                        uint64_t const key = (r << 32) | static_cast<uint64_t>(s + leader);
+                        if (idx < kSmallHits)
+                        {
+                            p.small_keys[idx] = key;
+                            p.small_ends[idx] = static_cast<uint32_t>(e_hit);
+                        }
+                        else
+                        {
+                            p.hit_keys[idx] = key;
+                            p.hit_ends[idx] = static_cast<uint32_t>(e_hit);
+                        }
                     }
                 }
                 s = e_hit; // FindAndConsume: the next search starts where this match ended
@@ -650,25 +682,35 @@ namespace trx
 // ≈ 2 instructions per residue for 3 literals, ≈ 5 for 8.  Record boundaries, candidate bins and reading direction do not
 // matter here: a factor that straddles two records, or lies in a non-candidate bin that shares a tile, only
 // creates a false candidate that phase 2 never visits or rejects.
-template <int NA, int NB>
+template <int NA, int NB, int STAGES>
 __global__ void __launch_bounds__(kScanThreads)
     regex_filter_simd(scan_params p, const __grid_constant__ CUtensorMap tmap)
 {
     constexpr int NL = NA + NB;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t * tiles = smem_raw;
-    uint64_t * bars = reinterpret_cast<uint64_t *>(smem_raw + kStages * kTileBytes);
+    uint64_t * bars = reinterpret_cast<uint64_t *>(smem_raw + STAGES * kTileBytes);
     int const tid = threadIdx.x;
     if (tid == 0)
     {
-        mbar_init(&bars[0], 1);
-        mbar_init(&bars[1], 1);
+#pragma unroll
+        for (int st = 0; st < STAGES; ++st)
+            mbar_init(&bars[st], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
     uint32_t const first_tile = blockIdx.x;
-    if (tid == 0 && first_tile < p.n_tiles)
-        tma_load_tile(&tmap, tiles, &bars[0], static_cast<int32_t>(p.tiles[first_tile]) * kScanThreads);
+    // prologue: STAGES - 1 tiles in flight before the first wait
+    if (tid == 0)
+    {
+#pragma unroll
+        for (int st = 0; st < STAGES - 1; ++st)
+        {
+            uint32_t const tp = first_tile + st * gridDim.x;
+            if (tp < p.n_tiles)
+                tma_load_tile(&tmap, tiles + st * kTileBytes, &bars[st], static_cast<int32_t>(p.tiles[tp]) * kScanThreads);
+        }
+    }
 
     uint32_t X[NL > 0 ? NL : 1], D[NL > 0 ? NL : 1];
 #pragma unroll
@@ -678,18 +720,18 @@ __global__ void __launch_bounds__(kScanThreads)
         D[j] = p.filter.delta[j] * 8;
     }
 
-    uint32_t it = 0;
+    uint32_t it = 0, stage = 0, phase = 0;
     for (uint32_t t = first_tile; t < p.n_tiles; t += gridDim.x, ++it)
     {
-        uint32_t const stage = it & 1;
-        uint32_t const tn = t + gridDim.x;
+        // the stage freed by the previous iteration (all threads passed its closing barrier) takes tile it + STAGES - 1
+        uint32_t const tn = t + (STAGES - 1) * gridDim.x;
         if (tid == 0 && tn < p.n_tiles)
         {
+            uint32_t const fill = stage == 0 ? STAGES - 1 : stage - 1;
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-            tma_load_tile(&tmap, tiles + (stage ^ 1) * kTileBytes, &bars[stage ^ 1],
-                          static_cast<int32_t>(p.tiles[tn]) * kScanThreads);
+            tma_load_tile(&tmap, tiles + fill * kTileBytes, &bars[fill], static_cast<int32_t>(p.tiles[tn]) * kScanThreads);
         }
-        mbar_wait(&bars[stage], (it >> 1) & 1);
+        mbar_wait(&bars[stage], phase);
 
         uint64_t const chunk_id = static_cast<uint64_t>(p.tiles[t]) * kScanThreads + tid;
         uint64_t const g_lo = chunk_id * kChunkBytes;
@@ -772,6 +814,193 @@ __global__ void __launch_bounds__(kScanThreads)
             }
         }
         __syncthreads();
+        if (++stage == STAGES)
+        {
+            stage = 0;
+            phase ^= 1;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------
+// Phase 1, gapped variant: literal bit masks + shifted mask algebra.
+//
+// PROSITE-style patterns (C-x(2,4)-C-x(3)-[LIVMFYWC]-x(8)-H-x(3,5)-H) have no window of fixed-offset literals,
+// but they do have literals that EVERY match passes through, at distances that vary inside small ranges.  The
+// thread turns its 128-byte chunk into one 128-bit occurrence mask per literal — per 32-bit text word: XOR with
+// the splat, zero-byte test, and one multiply that gathers the four lane flags into a nibble — fetches the mask
+// of the following 32 bytes from its neighbour, and evaluates
+//      cand = AND over atoms ( OR over d in [lo, hi] ( mask[lit] >> d ) )
+// with funnel shifts on 32-bit pieces.  A surviving bit is the anchor of a possible match; the chunks that can
+// hold the match's first byte are flagged and the records they belong to are listed for phase 2, exactly like
+// the fixed-window filter does.  Cost ≈ 1.25 ALU instructions per residue and literal, independent of the
+// number of atoms and of the pattern's length.
+__device__ __forceinline__ uint32_t literal_nibble(uint32_t word, uint32_t splat)
+{
+    uint32_t const t = word ^ splat;
+    uint32_t z; // (t - 0x01010101) & ~t & 0x80808080: bit 7 of a lane set if the lane (or a lower one) is 0.  One LOP3
+                // with the mask as immediate — left to itself ptxas folds the XOR in again and spends a fourth LOP3.
+    asm("lop3.b32 %0, %1, %2, 0x80808080, 0x20;" : "=r"(z) : "r"(t - 0x01010101u), "r"(t));
+    return (z * 0x00204081u) >> 28; // lane flags 7,15,23,31 → bits 0..3
+}
+
+template <int NLIT, int STAGES>
+__global__ void __launch_bounds__(kScanThreads)
+    regex_filter_atoms(scan_params p, const __grid_constant__ CUtensorMap tmap)
+{
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t * tiles = smem_raw;
+    uint64_t * bars = reinterpret_cast<uint64_t *>(smem_raw + STAGES * kTileBytes);
+    uint32_t * halo = reinterpret_cast<uint32_t *>(bars + STAGES); // [NLIT][kScanThreads]: mask of each chunk's first 32 bytes
+    int const tid = threadIdx.x;
+    if (tid == 0)
+    {
+#pragma unroll
+        for (int st = 0; st < STAGES; ++st)
+            mbar_init(&bars[st], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    uint32_t const first_tile = blockIdx.x;
+    if (tid == 0)
+    {
+#pragma unroll
+        for (int st = 0; st < STAGES - 1; ++st)
+        {
+            uint32_t const tp = first_tile + st * gridDim.x;
+            if (tp < p.n_tiles)
+                tma_load_tile(&tmap, tiles + st * kTileBytes, &bars[st], static_cast<int32_t>(p.tiles[tp]) * kScanThreads);
+        }
+    }
+
+    uint32_t X[NLIT];
+#pragma unroll
+    for (int l = 0; l < NLIT; ++l)
+        X[l] = p.atoms.splat[l];
+
+    uint32_t it = 0, stage = 0, phase = 0;
+    for (uint32_t t = first_tile; t < p.n_tiles; t += gridDim.x, ++it)
+    {
+        // the stage freed by the previous iteration (all threads passed its closing barrier) takes tile it + STAGES - 1
+        uint32_t const tn = t + (STAGES - 1) * gridDim.x;
+        if (tid == 0 && tn < p.n_tiles)
+        {
+            uint32_t const fill = stage == 0 ? STAGES - 1 : stage - 1;
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            tma_load_tile(&tmap, tiles + fill * kTileBytes, &bars[fill], static_cast<int32_t>(p.tiles[tn]) * kScanThreads);
+        }
+        mbar_wait(&bars[stage], phase);
+
+        uint64_t const chunk_id = static_cast<uint64_t>(p.tiles[t]) * kScanThreads + tid;
+        uint64_t const g_lo = chunk_id * kChunkBytes;
+        uint8_t const * row = tiles + stage * kTileBytes + tid * kChunkBytes;
+        uint32_t m[NLIT][5];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) // 32 bytes of text → one mask word per literal
+        {
+            uint4 const v0 = *reinterpret_cast<uint4 const *>(row + (((2 * q) ^ (tid & 7)) << 4));
+            uint4 const v1 = *reinterpret_cast<uint4 const *>(row + (((2 * q + 1) ^ (tid & 7)) << 4));
+            uint32_t const w[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+#pragma unroll
+            for (int l = 0; l < NLIT; ++l)
+            {
+                uint32_t mm = 0;
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    mm |= literal_nibble(w[j], X[l]) << (4 * j);
+                m[l][q] = mm;
+            }
+        }
+#pragma unroll
+        for (int l = 0; l < NLIT; ++l)
+            halo[l * kScanThreads + tid] = m[l][0];
+        __syncthreads();
+        if (tid + 1 < kScanThreads)
+        {
+#pragma unroll
+            for (int l = 0; l < NLIT; ++l)
+                m[l][4] = halo[l * kScanThreads + tid + 1];
+        }
+        else if (g_lo + kChunkBytes + 32 <= p.n_text_padded)
+        {
+            // last chunk of the tile: the following 32 bytes belong to another tile — read them from global memory
+            uint4 const v0 = __ldg(reinterpret_cast<uint4 const *>(p.text + g_lo + kChunkBytes));
+            uint4 const v1 = __ldg(reinterpret_cast<uint4 const *>(p.text + g_lo + kChunkBytes + 16));
+            uint32_t const w[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+#pragma unroll
+            for (int l = 0; l < NLIT; ++l)
+            {
+                uint32_t mm = 0;
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    mm |= literal_nibble(w[j], X[l]) << (4 * j);
+                m[l][4] = mm;
+            }
+        }
+        else
+        {
+#pragma unroll
+            for (int l = 0; l < NLIT; ++l)
+                m[l][4] = 0;
+        }
+
+        uint32_t acc[4] = {~0u, ~0u, ~0u, ~0u};
+#pragma unroll
+        for (int l = 0; l < NLIT; ++l)
+        {
+            for (int a = p.atoms.atom_begin[l]; a < p.atoms.atom_begin[l + 1]; ++a)
+            {
+                uint32_t const d_hi = p.atoms.hi[a];
+                uint32_t r[4] = {0, 0, 0, 0};
+                for (uint32_t d = p.atoms.lo[a]; d <= d_hi; ++d)
+                {
+#pragma unroll
+                    for (int q = 0; q < 4; ++q)
+                        r[q] |= __funnelshift_r(m[l][q], m[l][q + 1], d);
+                }
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                    acc[q] &= r[q];
+            }
+        }
+        if ((acc[0] | acc[1] | acc[2] | acc[3]) && g_lo < p.n_text)
+        {
+            // rare path: every surviving bit is an anchor; flag the chunks its match can start in, list their records
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+            {
+                uint32_t bits = acc[q];
+                while (bits)
+                {
+                    int const b = __ffs(bits) - 1;
+                    bits &= bits - 1;
+                    int64_t const anchor = static_cast<int64_t>(g_lo) + 32 * q + b;
+                    int64_t lo = anchor + p.atoms.start_lo, hi = anchor + p.atoms.start_hi;
+                    if (hi < 0 || lo >= static_cast<int64_t>(p.n_text))
+                        continue;
+                    if (lo < 0)
+                        lo = 0;
+                    if (hi >= static_cast<int64_t>(p.n_text))
+                        hi = static_cast<int64_t>(p.n_text) - 1;
+                    for (uint64_t c = static_cast<uint64_t>(lo) / kChunkBytes; c <= static_cast<uint64_t>(hi) / kChunkBytes; ++c)
+                        atomicOr(p.chunk_flags + (c >> 5), 1u << (c & 31));
+                    uint64_t r = record_of(p.rec_offsets, p.n_records, static_cast<uint64_t>(lo));
+                    while (r < p.n_records && __ldg(p.rec_offsets + r) <= static_cast<uint64_t>(hi))
+                    {
+                        if (__ldg(p.rec_offsets + r + 1) > static_cast<uint64_t>(lo) &&
+                            is_candidate(p.cand_words, __ldg(p.rec_bin + r)))
+                            list_record(p, r);
+                        ++r;
+                    }
+                }
+            }
+        }
+        __syncthreads();
+        if (++stage == STAGES)
+        {
+            stage = 0;
+            phase ^= 1;
+        }
     }
 }
 

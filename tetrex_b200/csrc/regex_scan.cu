@@ -1,7 +1,11 @@
 // regex_scan.cu — C ABI for the HBM-resident residue store and the K4 verify scan.
 // Reference: iter_disk_search + verify_* (include/query.h:97-188, src/query.cpp:167-315).
 #include <algorithm>
+#include <cmath>
 #include <cstdlib>
+#include <functional>
+#include <memory>
+#include <vector>
 
 #include <cub/device/device_radix_sort.cuh>
 
@@ -15,10 +19,17 @@ struct trx_text
     uint64_t * d_rec_offsets{nullptr};
     uint32_t * d_rec_bin{nullptr};
     uint64_t * d_bin_rec_begin{nullptr};
+    // one allocation, so that a scan needs ONE memset and ONE read-back:
+    //   [chunk flags | record flags | counters (16 B) | first kSmallHits keys | first kSmallHits ends]
+    //    <------------- cleared per scan ------------->
+    //                                <------------------ copied to the host --------------------------->
+    uint8_t * d_scan_block{nullptr};
+    uint64_t clear_bytes{};            // chunk flags + record flags + counters
     uint32_t * d_chunk_flags{nullptr};
     uint64_t n_chunk_flag_words{};
     uint32_t * d_rec_flags{nullptr};   // bitmap
     uint64_t n_rec_flag_words{};
+    uint8_t * d_counters{nullptr};     // hit count (u64), listed-record count (u32)
     uint32_t * d_rec_list{nullptr};
     double byte_freq[256]{};           // relative byte frequencies of the residue store
     std::vector<uint64_t> h_rec_offsets;   // host copies: tile planning and hit formatting
@@ -27,7 +38,7 @@ struct trx_text
     CUtensorMap tmap{};
     bool has_tmap{false};
     // per-scan scratch
-    trx::scratch d_stage, h_stage, h_small, d_counter, d_keys, d_ends, d_keys2, d_ends2, d_sort_tmp;
+    trx::scratch d_stage, h_stage, h_small, d_keys, d_ends, d_keys2, d_ends2, d_sort_tmp;
 };
 
 using namespace trx;
@@ -127,9 +138,15 @@ int trx_text_upload(trx_ctx_t * ctx, const uint8_t * residues, const uint64_t * 
     if ((e = cudaMalloc(&t->d_rec_offsets, (n_records + 1) * 8)) != cudaSuccess) return fail(e);
     if ((e = cudaMalloc(&t->d_rec_bin, n_records * 4)) != cudaSuccess) return fail(e);
     if ((e = cudaMalloc(&t->d_bin_rec_begin, (n_bins + 1) * 8)) != cudaSuccess) return fail(e);
-    if ((e = cudaMalloc(&t->d_chunk_flags, t->n_chunk_flag_words * 4)) != cudaSuccess) return fail(e);
     t->n_rec_flag_words = (n_records + 31) / 32;
-    if ((e = cudaMalloc(&t->d_rec_flags, t->n_rec_flag_words * 4)) != cudaSuccess) return fail(e);
+    {
+        uint64_t const flag_bytes = (t->n_chunk_flag_words * 4 + t->n_rec_flag_words * 4 + 15) & ~uint64_t{15};
+        t->clear_bytes = flag_bytes + 16;
+        if ((e = cudaMalloc(&t->d_scan_block, t->clear_bytes + kSmallHits * 12)) != cudaSuccess) return fail(e);
+        t->d_chunk_flags = reinterpret_cast<uint32_t *>(t->d_scan_block);
+        t->d_rec_flags = t->d_chunk_flags + t->n_chunk_flag_words;
+        t->d_counters = t->d_scan_block + flag_bytes;
+    }
     if ((e = cudaMalloc(&t->d_rec_list, n_records * 4)) != cudaSuccess) return fail(e);
     if ((e = cudaMemsetAsync(t->d_text + (t->n_text_padded - kTileBytes), 0, kTileBytes, ctx->stream)) != cudaSuccess) return fail(e);
     if (n_text && (e = cudaMemcpyAsync(t->d_text, residues, n_text, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess) return fail(e);
@@ -172,10 +189,9 @@ void trx_text_destroy(trx_text_t * t)
     cudaFree(t->d_rec_offsets);
     cudaFree(t->d_rec_bin);
     cudaFree(t->d_bin_rec_begin);
-    cudaFree(t->d_chunk_flags);
-    cudaFree(t->d_rec_flags);
+    cudaFree(t->d_scan_block);
     cudaFree(t->d_rec_list);
-    for (trx::scratch * s : {&t->d_stage, &t->h_stage, &t->h_small, &t->d_counter, &t->d_keys, &t->d_ends, &t->d_keys2, &t->d_ends2,
+    for (trx::scratch * s : {&t->d_stage, &t->h_stage, &t->h_small, &t->d_keys, &t->d_ends, &t->d_keys2, &t->d_ends2,
                              &t->d_sort_tmp})
         s->release();
     delete t;
@@ -214,11 +230,23 @@ int launch_phase1_w(trx_ctx * c, scan_params const & sp, CUtensorMap const & tma
     return use_tma ? launch_phase1<W, 1, true>(c, sp, tmap) : launch_phase1<W, 1, false>(c, sp, tmap);
 }
 
-template <int NA, int NB>
-int launch_filter(trx_ctx * c, scan_params const & sp, CUtensorMap const & tmap)
+// depth of the TMA ring of the prefilter kernels (TRX_FILTER_STAGES = 2 | 3 | 4 overrides; measured default below)
+int filter_stages()
 {
-    size_t smem = kStages * kTileBytes + 2 * sizeof(uint64_t);
-    auto kern = regex_filter_simd<NA, NB>;
+    static int stages = []
+    {
+        char const * e = getenv("TRX_FILTER_STAGES");
+        int v = e ? atoi(e) : kFilterStagesDefault;
+        return v < 2 ? 2 : (v > 4 ? 4 : v);
+    }();
+    return stages;
+}
+
+template <int NA, int NB, int STAGES>
+int launch_filter_s(trx_ctx * c, scan_params const & sp, CUtensorMap const & tmap)
+{
+    size_t smem = STAGES * kTileBytes + STAGES * sizeof(uint64_t);
+    auto kern = regex_filter_simd<NA, NB, STAGES>;
     static int per_sm = 0;
     if (per_sm == 0)
     {
@@ -232,6 +260,17 @@ int launch_filter(trx_ctx * c, scan_params const & sp, CUtensorMap const & tmap)
     ++c->launches;
     TRX_CUDA(cudaGetLastError());
     return TRX_OK;
+}
+
+template <int NA, int NB>
+int launch_filter(trx_ctx * c, scan_params const & sp, CUtensorMap const & tmap)
+{
+    switch (filter_stages())
+    {
+    case 2: return launch_filter_s<NA, NB, 2>(c, sp, tmap);
+    case 3: return launch_filter_s<NA, NB, 3>(c, sp, tmap);
+    default: return launch_filter_s<NA, NB, 4>(c, sp, tmap);
+    }
 }
 
 template <int NA>
@@ -256,6 +295,48 @@ int launch_filter_any(trx_ctx * c, scan_params const & sp, CUtensorMap const & t
     case 2: return launch_filter_a<2>(c, sp, tmap);
     case 3: return launch_filter_a<3>(c, sp, tmap);
     default: return launch_filter_a<4>(c, sp, tmap);
+    }
+}
+
+template <int NLIT, int STAGES>
+int launch_atoms_s(trx_ctx * c, scan_params const & sp, CUtensorMap const & tmap)
+{
+    size_t smem = STAGES * kTileBytes + STAGES * sizeof(uint64_t) + NLIT * kScanThreads * sizeof(uint32_t);
+    auto kern = regex_filter_atoms<NLIT, STAGES>;
+    static int per_sm = 0;
+    if (per_sm == 0)
+    {
+        TRX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+        int q = 0;
+        TRX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&q, kern, kScanThreads, smem));
+        per_sm = q < 1 ? 1 : q;
+    }
+    unsigned grid = static_cast<unsigned>(std::min<uint64_t>(sp.n_tiles, static_cast<uint64_t>(c->sm_count) * per_sm));
+    kern<<<grid, kScanThreads, smem, c->stream>>>(sp, tmap);
+    ++c->launches;
+    TRX_CUDA(cudaGetLastError());
+    return TRX_OK;
+}
+
+template <int NLIT>
+int launch_atoms(trx_ctx * c, scan_params const & sp, CUtensorMap const & tmap)
+{
+    switch (filter_stages())
+    {
+    case 2: return launch_atoms_s<NLIT, 2>(c, sp, tmap);
+    case 3: return launch_atoms_s<NLIT, 3>(c, sp, tmap);
+    default: return launch_atoms_s<NLIT, 4>(c, sp, tmap);
+    }
+}
+
+int launch_atoms_any(trx_ctx * c, scan_params const & sp, CUtensorMap const & tmap)
+{
+    switch (sp.atoms.n_lit)
+    {
+    case 1: return launch_atoms<1>(c, sp, tmap);
+    case 2: return launch_atoms<2>(c, sp, tmap);
+    case 3: return launch_atoms<3>(c, sp, tmap);
+    default: return launch_atoms<4>(c, sp, tmap);
     }
 }
 
@@ -294,9 +375,10 @@ struct bits128
 // L_{j+1} = Follow(L_j); every match has a byte of class(L_j) at offset j as long as no shorter match exists.
 // Offsets whose class is a single raw byte are literals; the best window of 4 consecutive offsets (by the
 // text's measured byte frequencies) becomes the filter.  n_a = n_b = 0 if nothing selective enough exists.
-filter_spec derive_filter(regex_dev const & img, double const * freq, bool reverse)
+filter_spec derive_filter(regex_dev const & img, double const * freq, bool reverse, double * pass_out)
 {
     filter_spec fs{};
+    *pass_out = 1.0;
     constexpr int kMaxDepth = 48;
     int literal[kMaxDepth];
     int depths = 0;
@@ -373,7 +455,381 @@ filter_spec derive_filter(regex_dev const & img, double const * freq, bool rever
         ++n;
     }
     fs.start_delta = reverse ? best_a + 7 : -best_a;
+    *pass_out = best;
     return fs;
+}
+
+// ---- gapped factor ("atoms") derivation -----------------------------------------------------------------
+// Works on the position automaton as the scan sees it (byte maps already folded into B).  Nodes: positions
+// 0..P-1, S = P (before the first symbol), F = P + 1 (accept).  A position is *necessary* when F cannot be
+// reached from S without it; necessary positions form a chain every match walks through in the same order.
+// For neighbours on that chain the shortest and the longest walk between them bound their distance in the
+// text (the {m,n} expansions of the Glushkov construction are loop-free, so the bounds are finite there; a
+// '*' or '+' in between makes the distance unbounded and ends the usable part of the chain).
+struct atom_plan
+{
+    atom_spec spec{};
+    double pass{1.0}; // expected fraction of text positions that survive the filter
+};
+
+struct automaton_graph
+{
+    int P{0};
+    std::vector<std::vector<int>> succ; // P + 2 nodes
+    int S() const { return P; }
+    int F() const { return P + 1; }
+};
+
+automaton_graph build_graph(regex_dev const & img)
+{
+    automaton_graph g;
+    g.P = img.positions;
+    g.succ.assign(g.P + 2, {});
+    auto has = [](uint64_t const * w, int i) { return (w[i >> 6] >> (i & 63)) & 1; };
+    for (int q = 0; q < g.P; ++q)
+        if (has(img.first, q))
+            g.succ[g.S()].push_back(q);
+    for (int pos = 0; pos < g.P; ++pos)
+    {
+        for (int q = 0; q < g.P; ++q)
+            if (has(img.follow[pos], q))
+                g.succ[pos].push_back(q);
+        if (has(img.last, pos))
+            g.succ[pos].push_back(g.F());
+    }
+    return g;
+}
+
+// is `to` reachable from `from` when node `without` may not be entered?
+bool reachable_without(automaton_graph const & g, int from, int to, int without)
+{
+    std::vector<char> seen(g.succ.size(), 0);
+    std::vector<int> stack{from};
+    seen[from] = 1;
+    while (!stack.empty())
+    {
+        int u = stack.back();
+        stack.pop_back();
+        if (u == to)
+            return true;
+        for (int v : g.succ[u])
+            if (v != without && !seen[v])
+            {
+                seen[v] = 1;
+                stack.push_back(v);
+            }
+    }
+    return false;
+}
+
+constexpr int kUnbounded = 1 << 20;
+
+// Number of symbols strictly between leaving `src` and the first arrival at `dst`, minimum and maximum over all
+// walks (dst is not left again).  hi = kUnbounded if a walk can loop before reaching dst.
+bool walk_range(automaton_graph const & g, int src, int dst, int & lo, int & hi)
+{
+    size_t const n = g.succ.size();
+    // nodes that can reach dst without passing through dst
+    std::vector<char> co(n, 0);
+    co[dst] = 1;
+    for (bool grew = true; grew;)
+    {
+        grew = false;
+        for (size_t u = 0; u < n; ++u)
+            if (!co[u] && static_cast<int>(u) != dst)
+                for (int v : g.succ[u])
+                    if (co[v])
+                    {
+                        co[u] = 1;
+                        grew = true;
+                        break;
+                    }
+    }
+    if (!co[src])
+        return false;
+    // shortest: BFS over co-reachable nodes (edges = one symbol each; the edge into dst counts as its own symbol)
+    std::vector<int> dist(n, -1);
+    std::vector<int> queue;
+    for (int v : g.succ[src])
+        if (co[v] && dist[v] < 0)
+        {
+            dist[v] = 0;
+            queue.push_back(v);
+        }
+    for (size_t h = 0; h < queue.size(); ++h)
+    {
+        int u = queue[h];
+        if (u == dst)
+            continue;
+        for (int v : g.succ[u])
+            if (co[v] && dist[v] < 0)
+            {
+                dist[v] = dist[u] + 1;
+                queue.push_back(v);
+            }
+    }
+    if (dist[dst] < 0)
+        return false;
+    lo = dist[dst];
+    // longest: memoised DFS, a back edge among co-reachable nodes = unbounded
+    std::vector<int> best(n, -2); // -2 unvisited, -3 on stack
+    bool cyclic = false;
+    std::function<int(int)> longest = [&](int u) -> int
+    {
+        if (u == dst)
+            return 0;
+        if (best[u] == -3)
+        {
+            cyclic = true;
+            return 0;
+        }
+        if (best[u] >= 0)
+            return best[u];
+        best[u] = -3;
+        int b = 0;
+        for (int v : g.succ[u])
+            if (co[v])
+                b = std::max(b, 1 + longest(v));
+        best[u] = b;
+        return b;
+    };
+    int b = 0;
+    for (int v : g.succ[src])
+        if (co[v])
+            b = std::max(b, longest(v));
+    hi = cyclic ? kUnbounded : b;
+    return true;
+}
+
+atom_plan derive_atoms(regex_dev const & img, double const * freq, bool reverse)
+{
+    atom_plan none;
+    automaton_graph const g = build_graph(img);
+    int const P = g.P;
+    if (P <= 0)
+        return none;
+    // literal of a position: the single raw byte whose class holds it
+    std::vector<int> literal(P, -1);
+    {
+        std::vector<int> count(P, 0);
+        for (int c = 0; c < 256; ++c)
+            for (int pos = 0; pos < P; ++pos)
+                if ((img.B[c][pos >> 6] >> (pos & 63)) & 1)
+                {
+                    ++count[pos];
+                    literal[pos] = c;
+                }
+        for (int pos = 0; pos < P; ++pos)
+            if (count[pos] != 1)
+                literal[pos] = -1;
+    }
+    // chain of necessary literal positions, ordered by their shortest distance from S
+    struct link
+    {
+        int pos, lit;
+        int off_lo, off_hi; // offset of the symbol inside the match (first symbol = 0)
+    };
+    std::vector<link> chain;
+    {
+        std::vector<std::pair<int, int>> order; // (min offset, position)
+        for (int pos = 0; pos < P; ++pos)
+        {
+            if (literal[pos] < 0 || literal[pos] == 0 || reachable_without(g, g.S(), g.F(), pos))
+                continue;
+            int lo = 0, hi = 0;
+            if (!walk_range(g, g.S(), pos, lo, hi))
+                continue;
+            order.emplace_back(lo, pos);
+        }
+        std::sort(order.begin(), order.end());
+        int prev = g.S(), off_lo = 0, off_hi = 0;
+        for (auto const & [min_off, pos] : order)
+        {
+            (void)min_off;
+            int lo = 0, hi = 0;
+            if (!walk_range(g, prev, pos, lo, hi) || hi >= kUnbounded)
+                break; // distance unbounded from here on: later atoms cannot be tied to the match start
+            if (prev != g.S())
+            {
+                ++lo; // symbols strictly between the two + the step onto `pos`
+                ++hi;
+            }
+            off_lo += lo;
+            off_hi += hi;
+            chain.push_back(link{pos, literal[pos], off_lo, off_hi});
+            prev = pos;
+        }
+    }
+    if (chain.empty())
+        return none;
+
+    constexpr double kGoodEnough = 2e-5;
+    constexpr int kMaxStartSpread = 1024;
+    atom_plan best;
+    int best_lits = 99;
+    int const n = static_cast<int>(chain.size());
+    for (int anchor = 0; anchor < n; ++anchor)
+    {
+        if (chain[anchor].off_hi - chain[anchor].off_lo > kMaxStartSpread)
+            continue;
+        // address offsets of the other atoms relative to the anchor: forward scans look at later symbols (higher
+        // addresses), reverse scans read downwards, so EARLIER symbols lie at higher addresses
+        struct cand
+        {
+            int lit, lo, hi;
+            double factor;
+        };
+        std::vector<cand> cands;
+        for (int i = 0; i < n; ++i)
+        {
+            if (i == anchor || (reverse ? i > anchor : i < anchor))
+                continue;
+            int lo, hi;
+            if (!reverse)
+            {
+                // distance anchor → i: sum of the gaps in between = difference of cumulative offsets, taken gap-wise
+                lo = chain[i].off_lo - chain[anchor].off_lo;
+                hi = chain[i].off_hi - chain[anchor].off_hi;
+            }
+            else
+            {
+                lo = chain[anchor].off_lo - chain[i].off_lo;
+                hi = chain[anchor].off_hi - chain[i].off_hi;
+            }
+            if (lo < 1 || hi < lo || hi > 31)
+                continue;
+            double const f = 1.0 - std::pow(1.0 - std::max(freq[chain[i].lit], 1e-4), hi - lo + 1); // any of the offsets
+            if (f > 0.7)
+                continue;
+            cands.push_back(cand{chain[i].lit, lo, hi, f});
+        }
+        std::sort(cands.begin(), cands.end(), [](cand const & a, cand const & b) { return a.factor < b.factor; });
+        int lits[4], n_lit = 1;
+        lits[0] = chain[anchor].lit;
+        std::vector<cand> chosen{cand{chain[anchor].lit, 0, 0, std::max(freq[chain[anchor].lit], 1e-4)}};
+        double pass = chosen[0].factor;
+        for (cand const & cd : cands)
+        {
+            if (pass <= kGoodEnough || chosen.size() >= 8)
+                break;
+            int l = 0;
+            while (l < n_lit && lits[l] != cd.lit)
+                ++l;
+            if (l == n_lit)
+            {
+                if (n_lit == 4)
+                    continue;
+                lits[n_lit++] = cd.lit;
+            }
+            chosen.push_back(cd);
+            pass *= cd.factor;
+        }
+        // good enough is good enough: below the target rate prefer the cheaper kernel (fewer literals, fewer atoms)
+        bool better;
+        if (pass > kGoodEnough || best.pass > kGoodEnough)
+            better = pass < best.pass;
+        else
+            better = n_lit < best_lits || (n_lit == best_lits && static_cast<int>(chosen.size()) < best.spec.n_atoms);
+        if (!better)
+            continue;
+        atom_plan plan;
+        plan.pass = pass;
+        plan.spec.n_lit = n_lit;
+        plan.spec.n_atoms = static_cast<int32_t>(chosen.size());
+        int a = 0;
+        for (int l = 0; l < n_lit; ++l)
+        {
+            plan.spec.splat[l] = 0x01010101u * static_cast<uint32_t>(lits[l]);
+            plan.spec.atom_begin[l] = static_cast<uint8_t>(a);
+            for (cand const & cd : chosen)
+                if (cd.lit == lits[l])
+                {
+                    plan.spec.lo[a] = static_cast<uint8_t>(cd.lo);
+                    plan.spec.hi[a] = static_cast<uint8_t>(cd.hi);
+                    ++a;
+                }
+        }
+        for (int l = n_lit; l < 8; ++l)
+            plan.spec.atom_begin[l] = static_cast<uint8_t>(a);
+        if (!reverse)
+        {
+            plan.spec.start_lo = -chain[anchor].off_hi;
+            plan.spec.start_hi = -chain[anchor].off_lo;
+        }
+        else
+        {
+            plan.spec.start_lo = chain[anchor].off_lo;
+            plan.spec.start_hi = chain[anchor].off_hi;
+        }
+        best = plan;
+        best_lits = n_lit;
+    }
+    return best;
+}
+
+// the automaton as one scan sees it: comp_tab (reverse strand) and the reduced-alphabet map folded into B
+void fill_image(trx_regex const & rx, bool reverse_strand, uint8_t const * map256, regex_dev * img)
+{
+    trx_regex const * re = &rx;
+    memset(img, 0, sizeof(regex_dev));
+    uint8_t comp[256];
+    if (reverse_strand)
+        complement_table(comp);
+    for (int k = 0; k < kRegexWords; ++k)
+    {
+        img->first[k] = re->masks.first[k];
+        img->last[k] = re->masks.last[k];
+    }
+    for (int ch = 0; ch < 256; ++ch)
+    {
+        uint8_t seen = static_cast<uint8_t>(ch);
+        if (reverse_strand)
+            seen = comp[seen];
+        if (map256)
+            seen = map256[seen];
+        for (int k = 0; k < kRegexWords; ++k)
+            img->B[ch][k] = re->masks.B[seen][k];
+    }
+    memcpy(img->follow, re->masks.follow, sizeof(img->follow));
+    img->first_len = static_cast<uint16_t>(re->first_list.size());
+    memcpy(img->first_list, re->first_list.data(), re->first_list.size());
+    memcpy(img->follow_off, re->follow_off.data(), re->follow_off.size() * sizeof(uint16_t));
+    memcpy(img->follow_list, re->follow_list.data(), re->follow_list.size());
+    img->positions = re->positions;
+    img->posix_longest = re->posix_longest;
+    img->anchor_begin = re->anchor_begin;
+    img->anchor_end = re->anchor_end;
+}
+
+enum filter_kind : int { kFilterNone = 0, kFilterWindow = 1, kFilterAtoms = 2 };
+
+// Chooses phase 1 for one scan.  TRX_REGEX_FILTER = off | window | atoms restricts the choice (A/B evidence, tests).
+// The fixed window costs ~0.5 ALU instructions per residue and literal, the gapped atoms ~1.5: the window is kept
+// when it is selective enough on its own.
+filter_kind choose_filter(regex_dev const & img, double const * freq, bool reverse, filter_spec & window, atom_spec & atoms)
+{
+    char const * filt = getenv("TRX_REGEX_FILTER");
+    bool const filter_off = filt && strcmp(filt, "off") == 0;
+    bool const only_window = filt && strcmp(filt, "window") == 0;
+    bool const only_atoms = filt && strcmp(filt, "atoms") == 0;
+    window = filter_spec{};
+    atoms = atom_spec{};
+    if (filter_off)
+        return kFilterNone;
+    double window_pass = 1.0;
+    if (!only_atoms)
+        window = derive_filter(img, freq, reverse, &window_pass);
+    bool const have_window = window.n_a + window.n_b >= 1;
+    if (!only_window && !(have_window && window_pass <= 1e-4))
+    {
+        atom_plan plan = derive_atoms(img, freq, reverse);
+        if (plan.spec.n_lit >= 1 && (only_atoms || (plan.pass <= 1e-3 && (!have_window || plan.pass < 0.25 * window_pass))))
+        {
+            atoms = plan.spec;
+            return kFilterAtoms;
+        }
+    }
+    return have_window ? kFilterWindow : kFilterNone;
 }
 
 size_t align16(size_t x)
@@ -437,46 +893,16 @@ int trx_regex_scan(trx_text_t * t, trx_regex_t * re, const uint64_t * candidate_
     memcpy(hs + off_cand, candidate_bin_words, cand_words * 8);
     memcpy(hs + off_tiles, tiles.data(), tiles.size() * 4);
     auto * img = reinterpret_cast<regex_dev *>(hs + off_regex);
-    memset(img, 0, sizeof(regex_dev));
-    uint8_t comp[256];
-    if (reverse_strand)
-        complement_table(comp);
-    for (int k = 0; k < kRegexWords; ++k)
-    {
-        img->first[k] = re->masks.first[k];
-        img->last[k] = re->masks.last[k];
-    }
-    for (int ch = 0; ch < 256; ++ch)
-    {
-        uint8_t seen = static_cast<uint8_t>(ch);
-        if (reverse_strand)
-            seen = comp[seen];
-        if (map256)
-            seen = map256[seen];
-        for (int k = 0; k < kRegexWords; ++k)
-            img->B[ch][k] = re->masks.B[seen][k];
-    }
-    memcpy(img->follow, re->masks.follow, sizeof(img->follow));
-    img->first_len = static_cast<uint16_t>(re->first_list.size());
-    memcpy(img->first_list, re->first_list.data(), re->first_list.size());
-    memcpy(img->follow_off, re->follow_off.data(), re->follow_off.size() * sizeof(uint16_t));
-    memcpy(img->follow_list, re->follow_list.data(), re->follow_list.size());
-    img->positions = re->positions;
-    img->posix_longest = re->posix_longest;
-    img->anchor_begin = re->anchor_begin;
-    img->anchor_end = re->anchor_end;
+    fill_image(*re, reverse_strand != 0, map256, img);
 
     if (cap > (1ull << 31))
         cap = 1ull << 31;
     uint64_t const dev_cap = cap ? cap : 1;
-    TRX_TRY(t->d_counter.reserve(16));
     TRX_TRY(t->d_keys.reserve(dev_cap * 8));
     TRX_TRY(t->d_ends.reserve(dev_cap * 4));
     auto * ds = static_cast<uint8_t *>(t->d_stage.ptr);
     TRX_CUDA(cudaMemcpyAsync(ds, hs, stage_bytes, cudaMemcpyHostToDevice, c->stream));
-    TRX_CUDA(cudaMemsetAsync(t->d_counter.ptr, 0, 16, c->stream));
-    TRX_CUDA(cudaMemsetAsync(t->d_chunk_flags, 0, t->n_chunk_flag_words * 4, c->stream));
-    TRX_CUDA(cudaMemsetAsync(t->d_rec_flags, 0, t->n_rec_flag_words * 4, c->stream));
+    TRX_CUDA(cudaMemsetAsync(t->d_scan_block, 0, t->clear_bytes, c->stream));
 
     scan_params sp{};
     sp.text = t->d_text;
@@ -491,20 +917,24 @@ int trx_regex_scan(trx_text_t * t, trx_regex_t * re, const uint64_t * candidate_
     sp.chunk_flags = t->d_chunk_flags;
     sp.rec_flags = t->d_rec_flags;
     sp.rec_list = t->d_rec_list;
-    sp.rec_count = reinterpret_cast<unsigned int *>(static_cast<uint8_t *>(t->d_counter.ptr) + 8);
+    sp.rec_count = reinterpret_cast<unsigned int *>(t->d_counters + 8);
     sp.re = reinterpret_cast<regex_dev *>(ds + off_regex);
 
     // TRX_REGEX_STAGING=ldg  → exact automaton kernel with direct loads (A/B evidence for the TMA staging)
-    // TRX_REGEX_FILTER=off   → never use the SIMD factor filter (A/B evidence for the filter)
+    // TRX_REGEX_FILTER=off   → never use a SIMD prefilter (A/B evidence for the filters)
     char const * staging = getenv("TRX_REGEX_STAGING");
-    char const * filt = getenv("TRX_REGEX_FILTER");
     bool const use_tma = !(staging && strcmp(staging, "ldg") == 0);
     bool const reverse = reverse_strand != 0;
-    if (use_tma && !(filt && strcmp(filt, "off") == 0))
-        sp.filter = derive_filter(*img, t->byte_freq, reverse);
+    filter_kind kind = kFilterNone;
+    if (use_tma)
+        kind = choose_filter(*img, t->byte_freq, reverse, sp.filter, sp.atoms);
+    bool const use_atoms = kind == kFilterAtoms, use_window = kind == kFilterWindow;
     if (stats)
-        stats[1] = static_cast<uint64_t>(sp.filter.n_a + sp.filter.n_b);
-    if (sp.filter.n_a + sp.filter.n_b >= 1)
+        stats[1] = use_atoms ? static_cast<uint64_t>(sp.atoms.n_atoms)
+                             : (use_window ? static_cast<uint64_t>(sp.filter.n_a + sp.filter.n_b) : 0);
+    if (use_atoms)
+        TRX_TRY(launch_atoms_any(c, sp, t->tmap));
+    else if (use_window)
         TRX_TRY(launch_filter_any(c, sp, t->tmap));
     else if (re->words == 1)
         TRX_TRY(launch_phase1_w<1>(c, sp, t->tmap, reverse, use_tma));
@@ -518,29 +948,26 @@ int trx_regex_scan(trx_text_t * t, trx_regex_t * re, const uint64_t * candidate_
     rp.rec_count = sp.rec_count;
     rp.chunk_flags = t->d_chunk_flags;
     rp.re = sp.re;
-    rp.hit_count = static_cast<unsigned long long *>(t->d_counter.ptr);
+    rp.hit_count = reinterpret_cast<unsigned long long *>(t->d_counters);
     rp.hit_keys = static_cast<uint64_t *>(t->d_keys.ptr);
     rp.hit_ends = static_cast<uint32_t *>(t->d_ends.ptr);
+    rp.small_keys = reinterpret_cast<uint64_t *>(t->d_counters + 16);
+    rp.small_ends = reinterpret_cast<uint32_t *>(t->d_counters + 16 + kSmallHits * 8);
     rp.cap = cap;
     if (re->words == 1)
         TRX_TRY(launch_phase2_w<1>(c, rp, reverse));
     else
         TRX_TRY(launch_phase2_w<2>(c, rp, reverse));
 
-    // ---- read back: the hit count and, speculatively, the first kSmall hits in the same round trip
-    constexpr uint64_t kSmall = 1024;
+    // ---- read back: the counters and the first kSmallHits hits in ONE copy
+    constexpr uint64_t kSmall = kSmallHits;
     uint64_t const spec = cap < kSmall ? cap : kSmall;
     t->h_small.pinned_host = true;
     TRX_TRY(t->h_small.reserve(16 + kSmall * 12));
     auto * h_total = static_cast<unsigned long long *>(t->h_small.ptr);
     auto * h_keys = reinterpret_cast<uint64_t *>(static_cast<uint8_t *>(t->h_small.ptr) + 16);
     auto * h_ends = reinterpret_cast<uint32_t *>(static_cast<uint8_t *>(t->h_small.ptr) + 16 + kSmall * 8);
-    TRX_CUDA(cudaMemcpyAsync(h_total, t->d_counter.ptr, 8, cudaMemcpyDeviceToHost, c->stream));
-    if (spec)
-    {
-        TRX_CUDA(cudaMemcpyAsync(h_keys, rp.hit_keys, spec * 8, cudaMemcpyDeviceToHost, c->stream));
-        TRX_CUDA(cudaMemcpyAsync(h_ends, rp.hit_ends, spec * 4, cudaMemcpyDeviceToHost, c->stream));
-    }
+    TRX_CUDA(cudaMemcpyAsync(h_total, t->d_counters, 16 + kSmall * 12, cudaMemcpyDeviceToHost, c->stream));
     TRX_CUDA(cudaStreamSynchronize(c->stream));
     unsigned long long const total = *h_total;
     *n_hits = total;
@@ -565,6 +992,8 @@ int trx_regex_scan(trx_text_t * t, trx_regex_t * re, const uint64_t * candidate_
 
     // ---- order = (bin, record, start): records are grouped by ascending bin, so (record, start) suffices
     uint64_t const n = total;
+    TRX_CUDA(cudaMemcpyAsync(rp.hit_keys, rp.small_keys, kSmall * 8, cudaMemcpyDeviceToDevice, c->stream));
+    TRX_CUDA(cudaMemcpyAsync(rp.hit_ends, rp.small_ends, kSmall * 4, cudaMemcpyDeviceToDevice, c->stream));
     TRX_TRY(t->d_keys2.reserve(n * 8));
     TRX_TRY(t->d_ends2.reserve(n * 4));
     size_t tmp_bytes = 0;
@@ -585,6 +1014,46 @@ int trx_regex_scan(trx_text_t * t, trx_regex_t * re, const uint64_t * candidate_
     {
         uint32_t rec = static_cast<uint32_t>(keys[i] >> 32);
         hits[i] = trx_hit{t->h_rec_bin[rec], rec, static_cast<uint32_t>(keys[i]), ends[i]};
+    }
+    return TRX_OK;
+}
+
+int trx_regex_filter_plan(const trx_regex_t * re, const double * byte_freq, int reverse_strand, const uint8_t * map256,
+                          int32_t out[48])
+{
+    if (!re || !byte_freq || !out)
+        return set_error(TRX_EINVAL, "trx_regex_filter_plan: NULL argument");
+    auto img = std::make_unique<regex_dev>();
+    fill_image(*re, reverse_strand != 0, map256, img.get());
+    filter_spec window;
+    atom_spec atoms;
+    filter_kind const kind = choose_filter(*img, byte_freq, reverse_strand != 0, window, atoms);
+    memset(out, 0, 48 * sizeof(int32_t));
+    out[0] = kind;
+    if (kind == kFilterWindow)
+    {
+        out[1] = window.n_a;
+        out[2] = window.n_b;
+        out[3] = window.start_delta;
+        for (int j = 0; j < window.n_a + window.n_b; ++j)
+        {
+            out[8 + j] = static_cast<int32_t>(window.delta[j]) + (j >= window.n_a ? 4 : 0); // byte offset inside the window
+            out[16 + j] = static_cast<int32_t>(window.splat[j] & 0xFF);
+        }
+    }
+    else if (kind == kFilterAtoms)
+    {
+        out[1] = atoms.n_lit;
+        out[2] = atoms.n_atoms;
+        out[3] = atoms.start_lo;
+        out[4] = atoms.start_hi;
+        for (int l = 0; l < atoms.n_lit; ++l)
+            for (int a = atoms.atom_begin[l]; a < atoms.atom_begin[l + 1]; ++a)
+            {
+                out[8 + a] = static_cast<int32_t>(atoms.splat[l] & 0xFF);
+                out[16 + a] = atoms.lo[a];
+                out[24 + a] = atoms.hi[a];
+            }
     }
     return TRX_OK;
 }
