@@ -42,4 +42,5 @@ struct trx_regex
     std::vector<uint16_t> follow_off;
     std::vector<uint8_t> follow_list;
     std::string pattern;
+    uint64_t serial{0}; // unique per compiled regex: key of the per-text filter-plan cache
 };

@@ -5,6 +5,7 @@
 // Semantics to reproduce: RE2 as iter_disk_search uses it (include/query.h:101-104,146-149;
 // src/query.cpp:194-237; lib/re2/re2/re2.cc:428-437): the pattern is wrapped in one capture group,
 // searched unanchored, POSIX ⇒ leftmost-longest, default ⇒ leftmost-first with greedy quantifiers.
+#include <atomic>
 #include <memory>
 #include <stdexcept>
 
@@ -467,6 +468,8 @@ int trx_regex_compile(const char * pattern, int posix_longest, trx_regex_t ** ou
                                           "FindAndConsume loop never terminates on it)", pattern);
     auto re = std::make_unique<trx_regex>();
     re->pattern = pat;
+    static std::atomic<uint64_t> next_serial{1};
+    re->serial = next_serial.fetch_add(1);
     re->positions = m;
     re->words = m <= 64 ? 1 : 2;
     re->posix_longest = posix_longest != 0;

@@ -26,7 +26,7 @@ constexpr int kChunkBytes = 128;
 constexpr int kScanThreads = 256;
 constexpr int kTileBytes = kChunkBytes * kScanThreads; // 32 KB
 constexpr int kStages = 2;              // exact automaton kernel (phase 1)
-constexpr int kFilterStagesDefault = 2; // prefilter kernels; see filter_stages()
+constexpr int kFilterSplitDefault = 1;  // prefilter kernels: threads per text row; see filter_split()
 constexpr unsigned long long kSmallHits = 1024;
 
 // device copy of the automaton; B already has the per-scan byte map (redmap / comp_tab) folded in
@@ -88,6 +88,7 @@ struct scan_params
     uint32_t * rec_flags;         // bitmap over records already listed
     uint32_t * rec_list;          // records that may hold a match (each once), for phase 2
     unsigned int * rec_count;
+    unsigned int * tile_counter;  // next entry of `tiles` to hand out (prefilter kernels schedule tiles dynamically)
     regex_dev const * re;
     filter_spec filter;
     atom_spec atoms;
@@ -682,35 +683,109 @@ namespace trx
 // ≈ 2 instructions per residue for 3 literals, ≈ 5 for 8.  Record boundaries, candidate bins and reading direction do not
 // matter here: a factor that straddles two records, or lies in a non-candidate bin that shares a tile, only
 // creates a false candidate that phase 2 never visits or rejects.
-template <int NA, int NB, int STAGES>
-__global__ void __launch_bounds__(kScanThreads)
+// Shared skeleton of the two prefilter kernels: a warp-specialised ring of 32 KB tiles (256 rows x 128 B, one 2-D TMA
+// copy each).  The LAST warp of the CTA is the producer: one lane takes the next tile from a device-wide counter
+// (dynamic scheduling — with static striding the SMs were idle for 29 % of the kernel: ramp, 14-vs-15-tile imbalance
+// and drain), waits until every consumer warp has released the stage (`empty` mbarrier, one arrival per warp) and
+// issues the TMA copy, which completes on the stage's `full` mbarrier.  Consumer warps never meet at a CTA-wide
+// barrier: ncu showed 3.1 warps per issue slot parked at the closing __syncthreads of the previous design.
+// SPLIT threads share a 128-byte row, so a CTA has 256 * SPLIT consumer threads + 32.  Ring depth 2: three and four
+// stages with fewer CTAs per SM were measured 20-30 % slower.
+constexpr uint32_t kNoTile = 0xFFFFFFFFu;
+
+__device__ __forceinline__ void mbar_arrive(uint64_t * bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+template <int STAGES, int CONSUMERS>
+struct tile_ring
+{
+    static constexpr int kRingBytes = STAGES * kTileBytes + STAGES * (2 * sizeof(uint64_t) + sizeof(uint32_t));
+    uint8_t * tiles;
+    uint64_t * full;
+    uint64_t * empty;
+    uint32_t * slot; // tile id held by each stage (kNoTile = no more work)
+    uint32_t n{0};
+
+    __device__ __forceinline__ void init(uint8_t * smem)
+    {
+        tiles = smem;
+        full = reinterpret_cast<uint64_t *>(smem + STAGES * kTileBytes);
+        empty = full + STAGES;
+        slot = reinterpret_cast<uint32_t *>(empty + STAGES);
+        if (threadIdx.x == 0)
+        {
+#pragma unroll
+            for (int st = 0; st < STAGES; ++st)
+            {
+                mbar_init(&full[st], 1);
+                mbar_init(&empty[st], CONSUMERS / 32);
+            }
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        __syncthreads();
+    }
+    __device__ __forceinline__ bool is_producer() const { return threadIdx.x >= CONSUMERS; }
+
+    // producer warp, one lane: feeds the ring until the device-wide tile counter runs out
+    __device__ __forceinline__ void produce(scan_params const & p, CUtensorMap const * tmap)
+    {
+        if (threadIdx.x != CONSUMERS)
+            return;
+        for (uint32_t i = 0;; ++i)
+        {
+            uint32_t const stage = i % STAGES;
+            if (i >= STAGES)
+                mbar_wait(&empty[stage], ((i / STAGES) - 1) & 1);
+            uint32_t const idx = atomicAdd(p.tile_counter, 1u);
+            if (idx >= p.n_tiles)
+            {
+                slot[stage] = kNoTile;
+                mbar_arrive(&full[stage]); // release: the slot write is visible to whoever sees this phase complete
+                return;
+            }
+            uint32_t const tile = __ldg(p.tiles + idx);
+            slot[stage] = tile;
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            tma_load_tile(tmap, tiles + stage * kTileBytes, &full[stage], static_cast<int32_t>(tile) * kScanThreads);
+        }
+    }
+    // consumers: next tile (false = done).  release() hands the stage back, one arrival per warp.
+    __device__ __forceinline__ bool acquire(uint8_t const *& tile_ptr, uint32_t & tile_id)
+    {
+        uint32_t const stage = n % STAGES;
+        mbar_wait(&full[stage], (n / STAGES) & 1);
+        tile_id = slot[stage];
+        tile_ptr = tiles + stage * kTileBytes;
+        return tile_id != kNoTile;
+    }
+    __device__ __forceinline__ void release()
+    {
+        __syncwarp();
+        if ((threadIdx.x & 31) == 0)
+            mbar_arrive(&empty[n % STAGES]);
+        ++n;
+    }
+};
+
+template <int NA, int NB, int STAGES, int SPLIT>
+__global__ void __launch_bounds__(kScanThreads * SPLIT + 32)
     regex_filter_simd(scan_params p, const __grid_constant__ CUtensorMap tmap)
 {
     constexpr int NL = NA + NB;
+    constexpr int BYTES = kChunkBytes / SPLIT; // text bytes per thread
+    constexpr int WORDS = BYTES / 4, PIECES = BYTES / 16;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
-    uint8_t * tiles = smem_raw;
-    uint64_t * bars = reinterpret_cast<uint64_t *>(smem_raw + STAGES * kTileBytes);
+    tile_ring<STAGES, kScanThreads * SPLIT> ring;
+    ring.init(smem_raw);
+    if (ring.is_producer())
+    {
+        ring.produce(p, &tmap);
+        return;
+    }
     int const tid = threadIdx.x;
-    if (tid == 0)
-    {
-#pragma unroll
-        for (int st = 0; st < STAGES; ++st)
-            mbar_init(&bars[st], 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    __syncthreads();
-    uint32_t const first_tile = blockIdx.x;
-    // prologue: STAGES - 1 tiles in flight before the first wait
-    if (tid == 0)
-    {
-#pragma unroll
-        for (int st = 0; st < STAGES - 1; ++st)
-        {
-            uint32_t const tp = first_tile + st * gridDim.x;
-            if (tp < p.n_tiles)
-                tma_load_tile(&tmap, tiles + st * kTileBytes, &bars[st], static_cast<int32_t>(p.tiles[tp]) * kScanThreads);
-        }
-    }
+    int const row_i = tid / SPLIT, sub = tid % SPLIT;
 
     uint32_t X[NL > 0 ? NL : 1], D[NL > 0 ? NL : 1];
 #pragma unroll
@@ -720,52 +795,48 @@ __global__ void __launch_bounds__(kScanThreads)
         D[j] = p.filter.delta[j] * 8;
     }
 
-    uint32_t it = 0, stage = 0, phase = 0;
-    for (uint32_t t = first_tile; t < p.n_tiles; t += gridDim.x, ++it)
+    uint8_t const * tile;
+    uint32_t tile_id;
+    while (ring.acquire(tile, tile_id))
     {
-        // the stage freed by the previous iteration (all threads passed its closing barrier) takes tile it + STAGES - 1
-        uint32_t const tn = t + (STAGES - 1) * gridDim.x;
-        if (tid == 0 && tn < p.n_tiles)
-        {
-            uint32_t const fill = stage == 0 ? STAGES - 1 : stage - 1;
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-            tma_load_tile(&tmap, tiles + fill * kTileBytes, &bars[fill], static_cast<int32_t>(p.tiles[tn]) * kScanThreads);
-        }
-        mbar_wait(&bars[stage], phase);
-
-        uint64_t const chunk_id = static_cast<uint64_t>(p.tiles[t]) * kScanThreads + tid;
-        uint64_t const g_lo = chunk_id * kChunkBytes;
-        uint8_t const * row = tiles + stage * kTileBytes + tid * kChunkBytes;
-        uint32_t w[kChunkBytes / 4 + 2];
+        uint64_t const g_lo = (static_cast<uint64_t>(tile_id) * kScanThreads + row_i) * kChunkBytes + sub * BYTES;
+        uint8_t const * row = tile + row_i * kChunkBytes;
+        uint32_t w[WORDS + 2];
 #pragma unroll
-        for (int piece = 0; piece < kChunkBytes / 16; ++piece)
+        for (int piece = 0; piece < PIECES; ++piece)
         {
-            uint4 v = *reinterpret_cast<uint4 const *>(row + ((piece ^ (tid & 7)) << 4));
+            uint4 v = *reinterpret_cast<uint4 const *>(row + (((sub * PIECES + piece) ^ (row_i & 7)) << 4));
             w[4 * piece + 0] = v.x;
             w[4 * piece + 1] = v.y;
             w[4 * piece + 2] = v.z;
             w[4 * piece + 3] = v.w;
         }
-        // look-ahead = first 8 bytes of the next chunk: the neighbouring row of the tile, or global memory
-        if (tid + 1 < kScanThreads)
+        // look-ahead = the 8 bytes that follow: same row, the next row of the tile, or global memory
+        if (sub + 1 < SPLIT)
         {
-            uint2 la = *reinterpret_cast<uint2 const *>(row + kChunkBytes + ((0 ^ ((tid + 1) & 7)) << 4));
-            w[kChunkBytes / 4] = la.x;
-            w[kChunkBytes / 4 + 1] = la.y;
+            uint2 la = *reinterpret_cast<uint2 const *>(row + ((((sub + 1) * PIECES) ^ (row_i & 7)) << 4));
+            w[WORDS] = la.x;
+            w[WORDS + 1] = la.y;
         }
-        else if (g_lo + kChunkBytes + 8 <= p.n_text_padded)
+        else if (row_i + 1 < kScanThreads)
         {
-            uint2 la = __ldg(reinterpret_cast<uint2 const *>(p.text + g_lo + kChunkBytes));
-            w[kChunkBytes / 4] = la.x;
-            w[kChunkBytes / 4 + 1] = la.y;
+            uint2 la = *reinterpret_cast<uint2 const *>(row + kChunkBytes + ((0 ^ ((row_i + 1) & 7)) << 4));
+            w[WORDS] = la.x;
+            w[WORDS + 1] = la.y;
+        }
+        else if (g_lo + BYTES + 8 <= p.n_text_padded)
+        {
+            uint2 la = __ldg(reinterpret_cast<uint2 const *>(p.text + g_lo + BYTES));
+            w[WORDS] = la.x;
+            w[WORDS + 1] = la.y;
         }
         else
         {
-            w[kChunkBytes / 4] = w[kChunkBytes / 4 + 1] = 0;
+            w[WORDS] = w[WORDS + 1] = 0;
         }
         uint32_t piece_hits = 0; // bit i = piece i holds a candidate
 #pragma unroll
-        for (int piece = 0; piece < kChunkBytes / 16; ++piece)
+        for (int piece = 0; piece < PIECES; ++piece)
         {
             uint32_t acc = 0;
 #pragma unroll
@@ -775,8 +846,7 @@ __global__ void __launch_bounds__(kScanThreads)
 #pragma unroll
                 for (int j = 0; j < NL; ++j)
                 {
-                    constexpr int dummy = 0;
-                    int const base = q + (j >= NA ? 1 : 0) + dummy; // second half of the window = next word
+                    int const base = q + (j >= NA ? 1 : 0); // second half of the window = next word
                     u |= __funnelshift_r(w[base], w[base + 1], D[j]) ^ X[j];
                 }
                 acc |= (u - 0x01010101u) & ~u & 0x80808080u;
@@ -813,12 +883,7 @@ __global__ void __launch_bounds__(kScanThreads)
                 }
             }
         }
-        __syncthreads();
-        if (++stage == STAGES)
-        {
-            stage = 0;
-            phase ^= 1;
-        }
+        ring.release();
     }
 }
 
@@ -844,62 +909,47 @@ __device__ __forceinline__ uint32_t literal_nibble(uint32_t word, uint32_t splat
     return (z * 0x00204081u) >> 28; // lane flags 7,15,23,31 → bits 0..3
 }
 
-template <int NLIT, int STAGES>
-__global__ void __launch_bounds__(kScanThreads)
+template <int NLIT, int STAGES, int SPLIT>
+__global__ void __launch_bounds__(kScanThreads * SPLIT + 32)
     regex_filter_atoms(scan_params p, const __grid_constant__ CUtensorMap tmap)
 {
+    static_assert(SPLIT == 1 || SPLIT == 2, "a thread owns 128 or 64 bytes (256 * SPLIT + 32 threads per CTA)");
+    constexpr int THREADS = kScanThreads * SPLIT; // consumer threads
+    constexpr int BYTES = kChunkBytes / SPLIT;
+    constexpr int MW = BYTES / 32; // mask words per literal (one per 32 text bytes)
     extern __shared__ __align__(1024) uint8_t smem_raw[];
-    uint8_t * tiles = smem_raw;
-    uint64_t * bars = reinterpret_cast<uint64_t *>(smem_raw + STAGES * kTileBytes);
-    uint32_t * halo = reinterpret_cast<uint32_t *>(bars + STAGES); // [NLIT][kScanThreads]: mask of each chunk's first 32 bytes
+    using ring_t = tile_ring<STAGES, THREADS>;
+    ring_t ring;
+    ring.init(smem_raw);
+    if (ring.is_producer())
+    {
+        ring.produce(p, &tmap);
+        return;
+    }
+    // [2][NLIT][THREADS]: mask of each thread's first 32 bytes, double-buffered by tile parity (no closing barrier)
+    uint32_t * halo_base = reinterpret_cast<uint32_t *>(smem_raw + ((ring_t::kRingBytes + 15) & ~15));
     int const tid = threadIdx.x;
-    if (tid == 0)
-    {
-#pragma unroll
-        for (int st = 0; st < STAGES; ++st)
-            mbar_init(&bars[st], 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    __syncthreads();
-    uint32_t const first_tile = blockIdx.x;
-    if (tid == 0)
-    {
-#pragma unroll
-        for (int st = 0; st < STAGES - 1; ++st)
-        {
-            uint32_t const tp = first_tile + st * gridDim.x;
-            if (tp < p.n_tiles)
-                tma_load_tile(&tmap, tiles + st * kTileBytes, &bars[st], static_cast<int32_t>(p.tiles[tp]) * kScanThreads);
-        }
-    }
+    int const row_i = tid / SPLIT, sub = tid % SPLIT;
 
     uint32_t X[NLIT];
 #pragma unroll
     for (int l = 0; l < NLIT; ++l)
         X[l] = p.atoms.splat[l];
 
-    uint32_t it = 0, stage = 0, phase = 0;
-    for (uint32_t t = first_tile; t < p.n_tiles; t += gridDim.x, ++it)
+    uint8_t const * tile;
+    uint32_t tile_id;
+    while (ring.acquire(tile, tile_id))
     {
-        // the stage freed by the previous iteration (all threads passed its closing barrier) takes tile it + STAGES - 1
-        uint32_t const tn = t + (STAGES - 1) * gridDim.x;
-        if (tid == 0 && tn < p.n_tiles)
-        {
-            uint32_t const fill = stage == 0 ? STAGES - 1 : stage - 1;
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-            tma_load_tile(&tmap, tiles + fill * kTileBytes, &bars[fill], static_cast<int32_t>(p.tiles[tn]) * kScanThreads);
-        }
-        mbar_wait(&bars[stage], phase);
-
-        uint64_t const chunk_id = static_cast<uint64_t>(p.tiles[t]) * kScanThreads + tid;
-        uint64_t const g_lo = chunk_id * kChunkBytes;
-        uint8_t const * row = tiles + stage * kTileBytes + tid * kChunkBytes;
-        uint32_t m[NLIT][5];
+        uint32_t * halo = halo_base + (ring.n & 1) * (NLIT * THREADS);
+        uint64_t const g_lo = (static_cast<uint64_t>(tile_id) * kScanThreads + row_i) * kChunkBytes + sub * BYTES;
+        uint8_t const * row = tile + row_i * kChunkBytes;
+        uint32_t m[NLIT][MW + 1];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) // 32 bytes of text → one mask word per literal
+        for (int q = 0; q < MW; ++q) // 32 bytes of text → one mask word per literal
         {
-            uint4 const v0 = *reinterpret_cast<uint4 const *>(row + (((2 * q) ^ (tid & 7)) << 4));
-            uint4 const v1 = *reinterpret_cast<uint4 const *>(row + (((2 * q + 1) ^ (tid & 7)) << 4));
+            int const piece = sub * (BYTES / 16) + 2 * q;
+            uint4 const v0 = *reinterpret_cast<uint4 const *>(row + ((piece ^ (row_i & 7)) << 4));
+            uint4 const v1 = *reinterpret_cast<uint4 const *>(row + (((piece + 1) ^ (row_i & 7)) << 4));
             uint32_t const w[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
 #pragma unroll
             for (int l = 0; l < NLIT; ++l)
@@ -913,19 +963,19 @@ __global__ void __launch_bounds__(kScanThreads)
         }
 #pragma unroll
         for (int l = 0; l < NLIT; ++l)
-            halo[l * kScanThreads + tid] = m[l][0];
-        __syncthreads();
-        if (tid + 1 < kScanThreads)
+            halo[l * THREADS + tid] = m[l][0];
+        asm volatile("bar.sync 1, %0;" ::"n"(THREADS) : "memory"); // consumers only: the producer warp is elsewhere
+        if (tid + 1 < THREADS)
         {
 #pragma unroll
             for (int l = 0; l < NLIT; ++l)
-                m[l][4] = halo[l * kScanThreads + tid + 1];
+                m[l][MW] = halo[l * THREADS + tid + 1];
         }
-        else if (g_lo + kChunkBytes + 32 <= p.n_text_padded)
+        else if (g_lo + BYTES + 32 <= p.n_text_padded)
         {
-            // last chunk of the tile: the following 32 bytes belong to another tile — read them from global memory
-            uint4 const v0 = __ldg(reinterpret_cast<uint4 const *>(p.text + g_lo + kChunkBytes));
-            uint4 const v1 = __ldg(reinterpret_cast<uint4 const *>(p.text + g_lo + kChunkBytes + 16));
+            // last thread of the tile: the following 32 bytes belong to another tile — read them from global memory
+            uint4 const v0 = __ldg(reinterpret_cast<uint4 const *>(p.text + g_lo + BYTES));
+            uint4 const v1 = __ldg(reinterpret_cast<uint4 const *>(p.text + g_lo + BYTES + 16));
             uint32_t const w[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
 #pragma unroll
             for (int l = 0; l < NLIT; ++l)
@@ -934,40 +984,50 @@ __global__ void __launch_bounds__(kScanThreads)
 #pragma unroll
                 for (int j = 0; j < 8; ++j)
                     mm |= literal_nibble(w[j], X[l]) << (4 * j);
-                m[l][4] = mm;
+                m[l][MW] = mm;
             }
         }
         else
         {
 #pragma unroll
             for (int l = 0; l < NLIT; ++l)
-                m[l][4] = 0;
+                m[l][MW] = 0;
         }
 
-        uint32_t acc[4] = {~0u, ~0u, ~0u, ~0u};
+        uint32_t acc[MW];
+#pragma unroll
+        for (int q = 0; q < MW; ++q)
+            acc[q] = ~0u;
 #pragma unroll
         for (int l = 0; l < NLIT; ++l)
         {
             for (int a = p.atoms.atom_begin[l]; a < p.atoms.atom_begin[l + 1]; ++a)
             {
                 uint32_t const d_hi = p.atoms.hi[a];
-                uint32_t r[4] = {0, 0, 0, 0};
+                uint32_t r[MW];
+#pragma unroll
+                for (int q = 0; q < MW; ++q)
+                    r[q] = 0;
                 for (uint32_t d = p.atoms.lo[a]; d <= d_hi; ++d)
                 {
 #pragma unroll
-                    for (int q = 0; q < 4; ++q)
+                    for (int q = 0; q < MW; ++q)
                         r[q] |= __funnelshift_r(m[l][q], m[l][q + 1], d);
                 }
 #pragma unroll
-                for (int q = 0; q < 4; ++q)
+                for (int q = 0; q < MW; ++q)
                     acc[q] &= r[q];
             }
         }
-        if ((acc[0] | acc[1] | acc[2] | acc[3]) && g_lo < p.n_text)
+        uint32_t any = 0;
+#pragma unroll
+        for (int q = 0; q < MW; ++q)
+            any |= acc[q];
+        if (any && g_lo < p.n_text)
         {
             // rare path: every surviving bit is an anchor; flag the chunks its match can start in, list their records
 #pragma unroll
-            for (int q = 0; q < 4; ++q)
+            for (int q = 0; q < MW; ++q)
             {
                 uint32_t bits = acc[q];
                 while (bits)
@@ -995,12 +1055,7 @@ __global__ void __launch_bounds__(kScanThreads)
                 }
             }
         }
-        __syncthreads();
-        if (++stage == STAGES)
-        {
-            stage = 0;
-            phase ^= 1;
-        }
+        ring.release();
     }
 }
 

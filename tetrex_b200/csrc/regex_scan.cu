@@ -1,7 +1,9 @@
 // regex_scan.cu — C ABI for the HBM-resident residue store and the K4 verify scan.
 // Reference: iter_disk_search + verify_* (include/query.h:97-188, src/query.cpp:167-315).
 #include <algorithm>
+#include <chrono>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <functional>
 #include <memory>
@@ -37,8 +39,23 @@ struct trx_text
     std::vector<uint64_t> h_bin_rec_begin; // n_bins + 1
     CUtensorMap tmap{};
     bool has_tmap{false};
+    // the last tile plan (candidate bins → 32 KB tiles) stays on the device: queries that verify the same candidate set
+    // (bench loops, strand pairs, -c conjunctions) skip the planning loop and the upload of the tile list
+    std::vector<uint64_t> plan_cand;
+    std::vector<uint32_t> plan_tiles;
+    uint64_t plan_residues{};
+    bool plan_valid{false};
+    // phase-1 choice per (regex, strand, byte map, TRX_REGEX_FILTER): derived from the automaton once, not per scan
+    struct cached_choice
+    {
+        uint64_t serial, map_hash;
+        int reverse, mode, kind;
+        trx::filter_spec window;
+        trx::atom_spec atoms;
+    };
+    std::vector<cached_choice> choices;
     // per-scan scratch
-    trx::scratch d_stage, h_stage, h_small, d_keys, d_ends, d_keys2, d_ends2, d_sort_tmp;
+    trx::scratch d_stage, h_stage, h_small, d_tiles, d_keys, d_ends, d_keys2, d_ends2, d_sort_tmp;
 };
 
 using namespace trx;
@@ -191,7 +208,7 @@ void trx_text_destroy(trx_text_t * t)
     cudaFree(t->d_bin_rec_begin);
     cudaFree(t->d_scan_block);
     cudaFree(t->d_rec_list);
-    for (trx::scratch * s : {&t->d_stage, &t->h_stage, &t->h_small, &t->d_keys, &t->d_ends, &t->d_keys2, &t->d_ends2,
+    for (trx::scratch * s : {&t->d_stage, &t->h_stage, &t->h_small, &t->d_tiles, &t->d_keys, &t->d_ends, &t->d_keys2, &t->d_ends2,
                              &t->d_sort_tmp})
         s->release();
     delete t;
@@ -230,33 +247,35 @@ int launch_phase1_w(trx_ctx * c, scan_params const & sp, CUtensorMap const & tma
     return use_tma ? launch_phase1<W, 1, true>(c, sp, tmap) : launch_phase1<W, 1, false>(c, sp, tmap);
 }
 
-// depth of the TMA ring of the prefilter kernels (TRX_FILTER_STAGES = 2 | 3 | 4 overrides; measured default below)
-int filter_stages()
+// threads per 128-byte text row in the prefilter kernels (TRX_FILTER_SPLIT = 1 | 2; 1 was measured 2-8 % faster).
+// The ring depth is fixed at 2: 3 and 4 stages were measured 20-30 % slower (fewer resident CTAs per SM).
+int filter_split()
 {
-    static int stages = []
+    static int split = []
     {
-        char const * e = getenv("TRX_FILTER_STAGES");
-        int v = e ? atoi(e) : kFilterStagesDefault;
-        return v < 2 ? 2 : (v > 4 ? 4 : v);
+        char const * e = getenv("TRX_FILTER_SPLIT");
+        int v = e ? atoi(e) : kFilterSplitDefault;
+        return v <= 1 ? 1 : 2;
     }();
-    return stages;
+    return split;
 }
 
-template <int NA, int NB, int STAGES>
+template <int NA, int NB, int STAGES, int SPLIT>
 int launch_filter_s(trx_ctx * c, scan_params const & sp, CUtensorMap const & tmap)
 {
-    size_t smem = STAGES * kTileBytes + STAGES * sizeof(uint64_t);
-    auto kern = regex_filter_simd<NA, NB, STAGES>;
+    constexpr int kThreads = kScanThreads * SPLIT + 32; // + the producer warp
+    size_t smem = tile_ring<STAGES, kScanThreads * SPLIT>::kRingBytes;
+    auto kern = regex_filter_simd<NA, NB, STAGES, SPLIT>;
     static int per_sm = 0;
     if (per_sm == 0)
     {
         TRX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
         int q = 0;
-        TRX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&q, kern, kScanThreads, smem));
+        TRX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&q, kern, kThreads, smem));
         per_sm = q < 1 ? 1 : q;
     }
     unsigned grid = static_cast<unsigned>(std::min<uint64_t>(sp.n_tiles, static_cast<uint64_t>(c->sm_count) * per_sm));
-    kern<<<grid, kScanThreads, smem, c->stream>>>(sp, tmap);
+    kern<<<grid, kThreads, smem, c->stream>>>(sp, tmap);
     ++c->launches;
     TRX_CUDA(cudaGetLastError());
     return TRX_OK;
@@ -265,12 +284,7 @@ int launch_filter_s(trx_ctx * c, scan_params const & sp, CUtensorMap const & tma
 template <int NA, int NB>
 int launch_filter(trx_ctx * c, scan_params const & sp, CUtensorMap const & tmap)
 {
-    switch (filter_stages())
-    {
-    case 2: return launch_filter_s<NA, NB, 2>(c, sp, tmap);
-    case 3: return launch_filter_s<NA, NB, 3>(c, sp, tmap);
-    default: return launch_filter_s<NA, NB, 4>(c, sp, tmap);
-    }
+    return filter_split() == 1 ? launch_filter_s<NA, NB, 2, 1>(c, sp, tmap) : launch_filter_s<NA, NB, 2, 2>(c, sp, tmap);
 }
 
 template <int NA>
@@ -298,21 +312,23 @@ int launch_filter_any(trx_ctx * c, scan_params const & sp, CUtensorMap const & t
     }
 }
 
-template <int NLIT, int STAGES>
+template <int NLIT, int STAGES, int SPLIT>
 int launch_atoms_s(trx_ctx * c, scan_params const & sp, CUtensorMap const & tmap)
 {
-    size_t smem = STAGES * kTileBytes + STAGES * sizeof(uint64_t) + NLIT * kScanThreads * sizeof(uint32_t);
-    auto kern = regex_filter_atoms<NLIT, STAGES>;
+    constexpr int kThreads = kScanThreads * SPLIT + 32; // + the producer warp
+    size_t smem = ((tile_ring<STAGES, kScanThreads * SPLIT>::kRingBytes + 15) & ~15) +
+                  2 * NLIT * kScanThreads * SPLIT * sizeof(uint32_t);
+    auto kern = regex_filter_atoms<NLIT, STAGES, SPLIT>;
     static int per_sm = 0;
     if (per_sm == 0)
     {
         TRX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
         int q = 0;
-        TRX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&q, kern, kScanThreads, smem));
+        TRX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&q, kern, kThreads, smem));
         per_sm = q < 1 ? 1 : q;
     }
     unsigned grid = static_cast<unsigned>(std::min<uint64_t>(sp.n_tiles, static_cast<uint64_t>(c->sm_count) * per_sm));
-    kern<<<grid, kScanThreads, smem, c->stream>>>(sp, tmap);
+    kern<<<grid, kThreads, smem, c->stream>>>(sp, tmap);
     ++c->launches;
     TRX_CUDA(cudaGetLastError());
     return TRX_OK;
@@ -321,12 +337,7 @@ int launch_atoms_s(trx_ctx * c, scan_params const & sp, CUtensorMap const & tmap
 template <int NLIT>
 int launch_atoms(trx_ctx * c, scan_params const & sp, CUtensorMap const & tmap)
 {
-    switch (filter_stages())
-    {
-    case 2: return launch_atoms_s<NLIT, 2>(c, sp, tmap);
-    case 3: return launch_atoms_s<NLIT, 3>(c, sp, tmap);
-    default: return launch_atoms_s<NLIT, 4>(c, sp, tmap);
-    }
+    return filter_split() == 1 ? launch_atoms_s<NLIT, 2, 1>(c, sp, tmap) : launch_atoms_s<NLIT, 2, 2>(c, sp, tmap);
 }
 
 int launch_atoms_any(trx_ctx * c, scan_params const & sp, CUtensorMap const & tmap)
@@ -852,48 +863,72 @@ int trx_regex_scan(trx_text_t * t, trx_regex_t * re, const uint64_t * candidate_
         stats[0] = 0;
     trx_ctx * c = t->ctx;
     TRX_TRY(c->use());
+    // TRX_SCAN_TRACE=1: host-clock breakdown of this call on stderr (diagnostic)
+    static bool const trace = getenv("TRX_SCAN_TRACE") != nullptr;
+    auto const now = [] { return std::chrono::steady_clock::now(); };
+    auto const t_begin = now();
+    auto t_plan = t_begin, t_image = t_begin, t_choice = t_begin, t_enqueued = t_begin;
     if (re->follow_list.size() > sizeof(regex_dev::follow_list))
         return set_error(TRX_EREGEX, "pattern '%s': ordered follow lists need %zu bytes (max %zu)", re->pattern.c_str(),
                          re->follow_list.size(), sizeof(regex_dev::follow_list));
 
+    // the clear of flags and counters does not depend on anything below: let it run while the host plans
+    TRX_CUDA(cudaMemsetAsync(t->d_scan_block, 0, t->clear_bytes, c->stream));
+
     // ---- plan: candidate bins → tiles of the text
     uint64_t const cand_words = (t->n_bins + 63) / 64;
-    std::vector<uint32_t> tiles;
-    uint64_t residues = 0;
-    for (uint64_t b = 0; b < t->n_bins; ++b)
+    bool const same_plan = t->plan_valid && memcmp(t->plan_cand.data(), candidate_bin_words, cand_words * 8) == 0;
+    if (!same_plan)
     {
-        if (!((candidate_bin_words[b >> 6] >> (b & 63)) & 1))
-            continue;
-        uint64_t r0 = t->h_bin_rec_begin[b], r1 = t->h_bin_rec_begin[b + 1];
-        if (r0 == r1)
-            continue;
-        uint64_t g0 = t->h_rec_offsets[r0], g1 = t->h_rec_offsets[r1];
-        if (g1 == g0)
-            continue;
-        residues += g1 - g0;
-        for (uint64_t tile = g0 / kTileBytes; tile <= (g1 - 1) / kTileBytes; ++tile)
-            if (tiles.empty() || tiles.back() != tile)
-                tiles.push_back(static_cast<uint32_t>(tile));
+        t->plan_valid = false;
+        t->plan_cand.assign(candidate_bin_words, candidate_bin_words + cand_words);
+        std::vector<uint32_t> & tl = t->plan_tiles;
+        tl.clear();
+        uint64_t residues = 0;
+        for (uint64_t b = 0; b < t->n_bins; ++b)
+        {
+            if (!((candidate_bin_words[b >> 6] >> (b & 63)) & 1))
+                continue;
+            uint64_t r0 = t->h_bin_rec_begin[b], r1 = t->h_bin_rec_begin[b + 1];
+            if (r0 == r1)
+                continue;
+            uint64_t g0 = t->h_rec_offsets[r0], g1 = t->h_rec_offsets[r1];
+            if (g1 == g0)
+                continue;
+            residues += g1 - g0;
+            for (uint64_t tile = g0 / kTileBytes; tile <= (g1 - 1) / kTileBytes; ++tile)
+                if (tl.empty() || tl.back() != tile)
+                    tl.push_back(static_cast<uint32_t>(tile));
+        }
+        t->plan_residues = residues;
+        if (!tl.empty())
+        {
+            // pageable source: the copy is staged by the driver before the call returns, the vector may change afterwards
+            TRX_TRY(t->d_tiles.reserve(tl.size() * 4));
+            TRX_CUDA(cudaMemcpyAsync(t->d_tiles.ptr, tl.data(), tl.size() * 4, cudaMemcpyHostToDevice, c->stream));
+        }
+        t->plan_valid = true;
     }
+    std::vector<uint32_t> const & tiles = t->plan_tiles;
     if (stats)
-        stats[0] = residues;
+        stats[0] = t->plan_residues;
     if (tiles.empty())
         return TRX_OK;
 
-    // ---- one pinned staging block: [candidate words | tile list | automaton image], one H2D copy
+    t_plan = now();
+    // ---- one pinned staging block: [candidate words | automaton image], one H2D copy
     static_assert(sizeof(regex_dev) < 16384, "regex_dev grew unexpectedly");
     size_t const off_cand = 0;
-    size_t const off_tiles = align16(off_cand + cand_words * 8);
-    size_t const off_regex = align16(off_tiles + tiles.size() * 4);
+    size_t const off_regex = align16(off_cand + cand_words * 8);
     size_t const stage_bytes = off_regex + sizeof(regex_dev);
     t->h_stage.pinned_host = true;
     TRX_TRY(t->h_stage.reserve(stage_bytes));
     TRX_TRY(t->d_stage.reserve(stage_bytes));
     auto * hs = static_cast<uint8_t *>(t->h_stage.ptr);
     memcpy(hs + off_cand, candidate_bin_words, cand_words * 8);
-    memcpy(hs + off_tiles, tiles.data(), tiles.size() * 4);
     auto * img = reinterpret_cast<regex_dev *>(hs + off_regex);
     fill_image(*re, reverse_strand != 0, map256, img);
+    t_image = now();
 
     if (cap > (1ull << 31))
         cap = 1ull << 31;
@@ -902,8 +937,6 @@ int trx_regex_scan(trx_text_t * t, trx_regex_t * re, const uint64_t * candidate_
     TRX_TRY(t->d_ends.reserve(dev_cap * 4));
     auto * ds = static_cast<uint8_t *>(t->d_stage.ptr);
     TRX_CUDA(cudaMemcpyAsync(ds, hs, stage_bytes, cudaMemcpyHostToDevice, c->stream));
-    TRX_CUDA(cudaMemsetAsync(t->d_scan_block, 0, t->clear_bytes, c->stream));
-
     scan_params sp{};
     sp.text = t->d_text;
     sp.n_text = t->n_text;
@@ -912,12 +945,13 @@ int trx_regex_scan(trx_text_t * t, trx_regex_t * re, const uint64_t * candidate_
     sp.rec_bin = t->d_rec_bin;
     sp.n_records = t->n_records;
     sp.cand_words = reinterpret_cast<uint64_t *>(ds + off_cand);
-    sp.tiles = reinterpret_cast<uint32_t *>(ds + off_tiles);
+    sp.tiles = static_cast<uint32_t *>(t->d_tiles.ptr);
     sp.n_tiles = static_cast<uint32_t>(tiles.size());
     sp.chunk_flags = t->d_chunk_flags;
     sp.rec_flags = t->d_rec_flags;
     sp.rec_list = t->d_rec_list;
     sp.rec_count = reinterpret_cast<unsigned int *>(t->d_counters + 8);
+    sp.tile_counter = reinterpret_cast<unsigned int *>(t->d_counters + 12);
     sp.re = reinterpret_cast<regex_dev *>(ds + off_regex);
 
     // TRX_REGEX_STAGING=ldg  → exact automaton kernel with direct loads (A/B evidence for the TMA staging)
@@ -927,8 +961,39 @@ int trx_regex_scan(trx_text_t * t, trx_regex_t * re, const uint64_t * candidate_
     bool const reverse = reverse_strand != 0;
     filter_kind kind = kFilterNone;
     if (use_tma)
-        kind = choose_filter(*img, t->byte_freq, reverse, sp.filter, sp.atoms);
+    {
+        char const * filt = getenv("TRX_REGEX_FILTER");
+        int const mode = !filt ? 0 : (filt[0] == 'o' ? 1 : (filt[0] == 'w' ? 2 : (filt[0] == 'a' ? 3 : 4)));
+        uint64_t map_hash = 0;
+        if (map256)
+        {
+            map_hash = 1469598103934665603ull; // FNV-1a
+            for (int i = 0; i < 256; ++i)
+                map_hash = (map_hash ^ map256[i]) * 1099511628211ull;
+        }
+        trx_text::cached_choice const * found = nullptr;
+        for (auto const & cc : t->choices)
+            if (cc.serial == re->serial && cc.reverse == reverse_strand && cc.mode == mode && cc.map_hash == map_hash)
+                found = &cc;
+        if (!found)
+        {
+            trx_text::cached_choice cc{};
+            cc.serial = re->serial;
+            cc.map_hash = map_hash;
+            cc.reverse = reverse_strand;
+            cc.mode = mode;
+            cc.kind = choose_filter(*img, t->byte_freq, reverse, cc.window, cc.atoms);
+            if (t->choices.size() >= 256)
+                t->choices.clear();
+            t->choices.push_back(cc);
+            found = &t->choices.back();
+        }
+        kind = static_cast<filter_kind>(found->kind);
+        sp.filter = found->window;
+        sp.atoms = found->atoms;
+    }
     bool const use_atoms = kind == kFilterAtoms, use_window = kind == kFilterWindow;
+    t_choice = now();
     if (stats)
         stats[1] = use_atoms ? static_cast<uint64_t>(sp.atoms.n_atoms)
                              : (use_window ? static_cast<uint64_t>(sp.filter.n_a + sp.filter.n_b) : 0);
@@ -968,7 +1033,15 @@ int trx_regex_scan(trx_text_t * t, trx_regex_t * re, const uint64_t * candidate_
     auto * h_keys = reinterpret_cast<uint64_t *>(static_cast<uint8_t *>(t->h_small.ptr) + 16);
     auto * h_ends = reinterpret_cast<uint32_t *>(static_cast<uint8_t *>(t->h_small.ptr) + 16 + kSmall * 8);
     TRX_CUDA(cudaMemcpyAsync(h_total, t->d_counters, 16 + kSmall * 12, cudaMemcpyDeviceToHost, c->stream));
+    t_enqueued = now();
     TRX_CUDA(cudaStreamSynchronize(c->stream));
+    if (trace)
+    {
+        auto us = [](auto a, auto b) { return std::chrono::duration<double, std::micro>(b - a).count(); };
+        fprintf(stderr, "trx_regex_scan: plan %.1f  image %.1f  filter choice %.1f  enqueue %.1f  wait %.1f us (%zu tiles)\n",
+                us(t_begin, t_plan), us(t_plan, t_image), us(t_image, t_choice), us(t_choice, t_enqueued),
+                us(t_enqueued, now()), tiles.size());
+    }
     unsigned long long const total = *h_total;
     *n_hits = total;
     if (total > cap)
