@@ -322,14 +322,43 @@ def extra_measurements(t, ctx, torch, residues, offs, rec_bin, planted, hibf, pe
                                             "kind": "reference (RE2 FindAndConsume, records in memory, no gz/kseq)",
                                             "sample": f"first {n_rec} records"}
 
-    # ---- K4 on a PROSITE-style pattern (C2H2 zinc finger, PS00028): no selective literal factor exists, so phase 1 is
-    # the exact automaton kernel
+    # ---- K4 on a PROSITE-style pattern (C2H2 zinc finger, PS00028): no fixed-offset literal window exists; phase 1 is
+    # the gapped-atom prefilter (literal masks + shifted mask algebra), TRX_REGEX_FILTER=off = the exact automaton kernel
     prosite = "C.{2,4}C.{3}[LIVMFYWC].{8}H.{3,5}H"
     rx2 = t.Regex(prosite, True)
     h2 = txt.scan(rx2)
-    sec2 = timed(lambda: txt.scan(rx2), 3)
-    out["verify_prosite"] = {"pattern": prosite, "hits": int(len(h2)), "filter_literals": int(txt.last_filter_literals),
+    sec2 = timed(lambda: txt.scan(rx2), 5)
+    out["verify_prosite"] = {"pattern": prosite, "hits": int(len(h2)), "filter_atoms": int(txt.last_filter_literals),
                              "residues_per_s": n_res / sec2, "frac_of_hbm_peak": n_res / sec2 / 1e9 / peak}
+    os.environ["TRX_REGEX_FILTER"] = "off"
+    h2x = txt.scan(rx2)
+    sec2x = timed(lambda: txt.scan(rx2), 2)
+    os.environ.pop("TRX_REGEX_FILTER")
+    out["verify_prosite"]["exact_automaton_residues_per_s"] = n_res / sec2x
+    out["verify_prosite"]["hits_equal_exact_automaton"] = bool(np.array_equal(h2, h2x))
+    txt.close()
+
+    # ---- K4 at a size where the per-call latencies (one H2D, one memset, two launches, one D2H, one sync ~ 50 us) no longer
+    # dominate: the same collection 8 times over (1.6 G residues, 8192 bins) — the streaming rate of the kernels
+    reps8 = 8
+    big_res = np.tile(np.asarray(residues, dtype=np.uint8), reps8)
+    n_rec = len(offs) - 1
+    big_offs = np.concatenate([np.asarray(offs[:-1], dtype=np.uint64) + np.uint64(i * n_res) for i in range(reps8)] +
+                              [np.array([reps8 * n_res], dtype=np.uint64)])
+    big_bin = np.concatenate([np.asarray(rec_bin, dtype=np.uint32) + np.uint32(i * N_BINS) for i in range(reps8)])
+    big = t.Text(ctx, big_res, big_offs, big_bin, N_BINS * reps8)
+    del big_res
+    large = {}
+    for name, rxx in (("window", rx), ("atoms", rx2)):
+        hb = big.scan(rxx)
+        secb = timed(lambda: big.scan(rxx), 3)
+        large[name] = {"pattern": rxx.pattern, "hits": int(len(hb)), "residues_per_s": reps8 * n_res / secb,
+                       "frac_of_hbm_peak": reps8 * n_res / secb / 1e9 / peak, "us_per_scan": secb * 1e6}
+    large["residues"] = reps8 * n_res
+    large["records"] = reps8 * n_rec
+    out["verify_large"] = large
+    big.close()
+    txt = t.Text(ctx, residues, offs, rec_bin, N_BINS)
 
     # ---- whole query: k-mers of the query -> K3 -> AND/OR on device -> K4 on the candidate bins
     aamap, _ = t.peptide_maps(t.RED_BASE)

@@ -1,0 +1,127 @@
+// capi.cpp — C facade of the host layer (libtrxhost.so) for drivers that are not C++: one process per GPU under
+// torchrun opens its shard of an index file, runs process_query with the global pruning decision delegated to a
+// callback (torch.distributed all-reduce in tetrex_b200/sharded.py) and verifies its own bins.  Plain pointers and
+// sizes only; every call returns 0 or -1 with the message in trxh_last_error().
+#include <cstring>
+#include <sstream>
+
+#include "trx_host.hpp"
+
+namespace
+{
+thread_local std::string g_error;
+
+struct handle
+{
+    trx_ctx_t * ctx;
+    trxh::DeviceIndex index;
+    explicit handle(trx_ctx_t * c) : ctx(c), index(c) {}
+};
+
+template <class F>
+int guarded(F && f)
+{
+    try
+    {
+        f();
+        return 0;
+    }
+    catch (std::exception const & e)
+    {
+        g_error = e.what();
+        return -1;
+    }
+}
+} // namespace
+
+extern "C"
+{
+
+typedef void (*trxh_alive_fn)(uint8_t * alive, uint64_t n, void * user);
+
+const char * trxh_last_error(void)
+{
+    return g_error.c_str();
+}
+
+// load_ibf (include/index_base.h:189-195) of shard `shard_index` of `shard_count` onto the device of `ctx`
+int trxh_open(trx_ctx_t * ctx, const char * path, uint32_t shard_index, uint32_t shard_count, void ** out)
+{
+    return guarded([&] {
+        auto h = std::make_unique<handle>(ctx);
+        h->index.set_shard(shard_index, shard_count);
+        h->index.load(path);
+        *out = h.release();
+    });
+}
+
+void trxh_close(void * h)
+{
+    delete static_cast<handle *>(h);
+}
+
+// out[0..8) = bin_count, bin_words, is_hibf, is_dna, k, shard_word_begin, shard_words, reduction
+int trxh_info(void * hv, uint64_t out[8])
+{
+    return guarded([&] {
+        auto & ix = static_cast<handle *>(hv)->index;
+        out[0] = ix.bin_count();
+        out[1] = ix.bin_words();
+        out[2] = ix.is_hibf();
+        out[3] = ix.is_dna();
+        out[4] = ix.k();
+        out[5] = ix.shard_word_begin();
+        out[6] = ix.shard_words();
+        out[7] = ix.reduction();
+    });
+}
+
+// process_query (include/query.h:226-247).  out_words: bin_words entries; a column shard fills only its own words.
+// alive (nullable when unsharded): ORs n bytes over all shards in place.  stats (nullable): probes, ranks, items.
+int trxh_process_query(void * hv, const char * regex, trxh_alive_fn alive, void * user, uint64_t * out_words, uint64_t * stats)
+{
+    return guarded([&] {
+        auto & ix = static_cast<handle *>(hv)->index;
+        trxh::shard_hooks hooks;
+        if (alive)
+            hooks.any_alive = [alive, user](uint8_t * a, size_t n) { alive(a, n, user); };
+        trxh::collect_stats st;
+        trxh::bitvector got = trxh::process_query(regex, ix, &st, alive ? &hooks : nullptr);
+        // run_collection (include/query.h:256-262): the answer is ANDed into a vector of the real bins
+        for (uint64_t w = 0; w < got.size(); ++w)
+        {
+            uint64_t const first = w * 64, bins = ix.bin_count();
+            uint64_t const mask = bins >= first + 64 ? ~0ull : (bins > first ? (1ull << (bins - first)) - 1 : 0);
+            out_words[w] = got[w] & mask;
+        }
+        if (stats)
+        {
+            stats[0] = st.probes;
+            stats[1] = st.ranks;
+            stats[2] = st.items;
+        }
+    });
+}
+
+// iter_disk_search (include/query.h:97-188) over this shard's bins; the lines come back as one malloc'ed buffer
+// (free with trxh_free).
+int trxh_verify(void * hv, const uint64_t * cand_words, const char * regex, char ** out_text, uint64_t * out_len, uint64_t * n_lines)
+{
+    return guarded([&] {
+        auto & ix = static_cast<handle *>(hv)->index;
+        trxh::bitvector cand(cand_words, cand_words + ix.bin_words());
+        std::ostringstream os;
+        *n_lines = trxh::iter_disk_search(cand, regex, ix, os);
+        std::string const text = os.str();
+        *out_text = static_cast<char *>(malloc(text.size() + 1));
+        memcpy(*out_text, text.c_str(), text.size() + 1);
+        *out_len = text.size();
+    });
+}
+
+void trxh_free(void * p)
+{
+    free(p);
+}
+
+} // extern "C"

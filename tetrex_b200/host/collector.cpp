@@ -76,11 +76,18 @@ struct dev_buffer
 
 } // namespace
 
-bitvector collect(kgraph const & g, DeviceIndex & index, collect_stats * stats)
+bitvector collect(kgraph const & g, DeviceIndex & index, collect_stats * stats, shard_hooks const * hooks)
 {
     size_t const n_nodes = g.size();
-    uint64_t const bins = index.bin_count();
-    uint64_t const W = index.bin_words();
+    // a column shard of a flat index walks the same graph over its own bins only: paths are shard_words() wide and the
+    // pruning decision is made global through hooks->any_alive
+    bool const sharded = !index.is_hibf() && index.shard_count() > 1;
+    uint64_t const word_begin = sharded ? index.shard_word_begin() : 0;
+    uint64_t const W = index.path_words();
+    uint64_t const bins = sharded ? std::min<uint64_t>(W * 64, index.bin_count() > word_begin * 64 ? index.bin_count() - word_begin * 64 : 0)
+                                  : index.bin_count();
+    if (sharded && !(hooks && hooks->any_alive))
+        throw error("a column-sharded index needs shard_hooks::any_alive (the pruning decision spans all shards)");
     uint8_t const k = index.k();
     unsigned const bits = index.is_dna() ? 2 : 5;
     // create_selection_bitmask (otf_collector.h:168-182): the low (k-1) symbols
@@ -215,6 +222,8 @@ bitvector collect(kgraph const & g, DeviceIndex & index, collect_stats * stats)
                     check(trx_paths_and_hits(pool.paths, static_cast<uint64_t *>(d_hits.ptr), idx.data(),
                                              probe_slots.data(), n, res.data()));
                 }
+                if (sharded)
+                    hooks->any_alive(res.data(), res.size());
                 for (size_t j = 0; j < res.size(); ++j)
                     alive[probe_item[j]] = res[j];
                 if (stats)
@@ -229,12 +238,12 @@ bitvector collect(kgraph const & g, DeviceIndex & index, collect_stats * stats)
         b.items.clear();
         b.by_key.clear();
     }
-    bitvector out(W);
-    check(trx_paths_read(pool.paths, match_slot, 1, out.data()));
+    bitvector out(index.bin_words(), 0);
+    check(trx_paths_read(pool.paths, match_slot, 1, out.data() + word_begin));
     return out;
 }
 
-bitvector process_query(std::string const & regex, DeviceIndex & index, collect_stats * stats)
+bitvector process_query(std::string const & regex, DeviceIndex & index, collect_stats * stats, shard_hooks const * hooks)
 {
     // preprocess_query (include/query.h:80-94): peptides reduce (if the index is reduced) and trim, DNA only translates
     std::string rx = regex;
@@ -246,7 +255,7 @@ bitvector process_query(std::string const & regex, DeviceIndex & index, collect_
     }
     std::string postfix = translate(rx);
     kgraph g = construct_kgraph(postfix, index.k(), index.reduction() != TRX_RED_BASE); // include/query.h:239-240
-    return collect(g, index, stats);
+    return collect(g, index, stats, hooks);
 }
 
 } // namespace trxh

@@ -81,12 +81,14 @@ struct library
     uint64_t indexed{};             // records of length >= k
 };
 
-library read_library(std::vector<std::string> const & files, int molecule, unsigned k, bool announce_short)
+// bins outside [first_bin, last_bin) are skipped (they keep their ids and simply have no records): a verify shard
+library read_library(std::vector<std::string> const & files, int molecule, unsigned k, bool announce_short,
+                     size_t first_bin = 0, size_t last_bin = SIZE_MAX)
 {
     library lib;
     lib.offsets.push_back(0);
     lib.bin_emits.assign(files.size(), 0);
-    for (size_t b = 0; b < files.size(); ++b)
+    for (size_t b = first_bin; b < files.size() && b < last_bin; ++b)
     {
         for (fasta_record & rec : read_fasta(files[b]))
         {
@@ -320,7 +322,10 @@ void DeviceIndex::upload()
         ibf_image const & f = img_.flat;
         if (flat_)
             trx_ibf_destroy(flat_), flat_ = nullptr;
-        check(trx_ibf_create(ctx_, f.bins, f.bin_size, static_cast<uint32_t>(f.hash_funs), 0, 1, &flat_));
+        if (shard_count_ > 1 && f.bin_words % shard_count_ != 0)
+            throw error("cannot split " + std::to_string(f.bin_words) + " 64-bin columns over " + std::to_string(shard_count_) +
+                        " shards (the shard count must divide the column count)");
+        check(trx_ibf_create(ctx_, f.bins, f.bin_size, static_cast<uint32_t>(f.hash_funs), shard_index_, shard_count_, &flat_));
         check(trx_ibf_upload(flat_, f.words.data(), f.words.size()));
         return;
     }
@@ -367,15 +372,40 @@ void DeviceIndex::load(std::string const & path)
     upload();
 }
 
+void DeviceIndex::set_shard(uint32_t index, uint32_t count)
+{
+    if (count == 0 || index >= count)
+        throw error("shard " + std::to_string(index) + " of " + std::to_string(count) + " does not exist");
+    if (flat_ || hibf_ || text_)
+        throw error("set_shard must be called before load()");
+    shard_index_ = index;
+    shard_count_ = count;
+}
+
+uint64_t DeviceIndex::shard_word_begin() const
+{
+    // balanced contiguous split of the 64-bin words (equal parts whenever count divides, which a flat IBF requires)
+    uint64_t const words = bin_words(), base = words / shard_count_, extra = words % shard_count_;
+    return shard_index_ * base + std::min<uint64_t>(shard_index_, extra);
+}
+
+uint64_t DeviceIndex::shard_words() const
+{
+    uint64_t const words = bin_words(), base = words / shard_count_, extra = words % shard_count_;
+    return base + (shard_index_ < extra ? 1 : 0);
+}
+
 DeviceIndex::text_store const & DeviceIndex::text()
 {
     if (!text_)
     {
         // iter_disk_search re-opens acid_libs_[bin] per query (include/query.h:126-131,171-177)
-        for (std::string const & f : img_.acid_libs)
-            if (!std::filesystem::exists(f))
+        size_t const first_bin = shard_count_ > 1 ? shard_word_begin() * 64 : 0;
+        size_t const last_bin = shard_count_ > 1 ? (shard_word_begin() + shard_words()) * 64 : SIZE_MAX;
+        for (size_t b = first_bin; b < img_.acid_libs.size() && b < last_bin; ++b)
+            if (!std::filesystem::exists(img_.acid_libs[b]))
                 throw error("File not found. Did you move/rename an indexed file?");
-        library lib = read_library(img_.acid_libs, is_dna() ? TRX_MOL_NA : TRX_MOL_AA, img_.k, false);
+        library lib = read_library(img_.acid_libs, is_dna() ? TRX_MOL_NA : TRX_MOL_AA, img_.k, false, first_bin, last_bin);
         text_ = std::make_unique<text_store>();
         text_->names = std::move(lib.names);
         text_->offsets = std::move(lib.offsets);

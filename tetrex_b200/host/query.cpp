@@ -69,7 +69,37 @@ std::vector<trx_hit> scan(DeviceIndex::text_store const & store, regex_handle & 
 
 } // namespace
 
+namespace
+{
+uint64_t search_impl(bitvector const & hits_in, std::string const & query_in, DeviceIndex & index, std::ostream * out,
+                     std::ostream * rev_out);
+}
+
 uint64_t iter_disk_search(bitvector const & hits_in, std::string const & query_in, DeviceIndex & index, std::string const & dest)
+{
+    std::ofstream file_out;
+    std::ostream * out = &std::cout;
+    if (dest != "-")
+    {
+        file_out.open(dest);
+        if (!file_out)
+            throw error("Failed to open output file: " + dest);
+        out = &file_out;
+    }
+    // reverse hits always go to stdout, whatever -o says (std::osyncstream(std::cout), src/query.cpp:186)
+    return search_impl(hits_in, query_in, index, out, &std::cout);
+}
+
+uint64_t iter_disk_search(bitvector const & hits_in, std::string const & query_in, DeviceIndex & index, std::ostream & out)
+{
+    return search_impl(hits_in, query_in, index, &out, &out);
+}
+
+namespace
+{
+
+uint64_t search_impl(bitvector const & hits_in, std::string const & query_in, DeviceIndex & index, std::ostream * out,
+                     std::ostream * rev_out)
 {
     DeviceIndex::text_store const & store = index.text();
     std::vector<std::string> const & libs = index.acid_libs();
@@ -80,22 +110,16 @@ uint64_t iter_disk_search(bitvector const & hits_in, std::string const & query_i
     else
         for (size_t w = 0; w < cand.size() && w < hits_in.size(); ++w)
             cand[w] = hits_in[w];
+    if (index.shard_count() > 1) // a shard verifies its own bins only (its text store holds nothing else)
+        for (size_t w = 0; w < cand.size(); ++w)
+            if (w < index.shard_word_begin() || w >= index.shard_word_begin() + index.shard_words())
+                cand[w] = 0;
 
     std::string query = query_in;
     bool const dna = index.is_dna();
     if (!dna && index.reduction() > 0)
         query = reduce_query_alphabet(query, index.redmap()); // include/query.h:144
     regex_handle rx(query, /*posix=*/!dna);                    // RE2::POSIX for peptides, default options for DNA
-
-    std::ofstream file_out;
-    std::ostream * out = &std::cout;
-    if (dest != "-")
-    {
-        file_out.open(dest);
-        if (!file_out)
-            throw error("Failed to open output file: " + dest);
-        out = &file_out;
-    }
 
     uint8_t const * map = (!dna && index.reduction() > 0) ? index.redmap() : nullptr;
     std::vector<trx_hit> fwd = scan(store, rx, cand, false, map);
@@ -121,8 +145,7 @@ uint64_t iter_disk_search(bitvector const & hits_in, std::string const & query_i
         match.clear();
         for (uint32_t p = h.start; p < h.end; ++p)
             match.push_back(complement(rec[len - 1 - p]));
-        // reverse hits always go to stdout, whatever -o says (std::osyncstream(std::cout), :186)
-        std::cout << libs[h.bin] << '\t' << store.names[h.record] << '\t' << match << '\t' << "REVERSE STRAND HIT" << std::endl;
+        *rev_out << libs[h.bin] << '\t' << store.names[h.record] << '\t' << match << '\t' << "REVERSE STRAND HIT" << std::endl;
         ++lines;
     };
     // per bin: all forward lines, then all reverse lines (include/query.h:132-134); bins ascending (-t 1 order)
@@ -146,9 +169,6 @@ uint64_t iter_disk_search(bitvector const & hits_in, std::string const & query_i
     out->flush();
     return lines;
 }
-
-namespace
-{
 
 double now()
 {

@@ -5,6 +5,8 @@
 #pragma once
 
 #include <cstdint>
+#include <functional>
+#include <iosfwd>
 #include <map>
 #include <memory>
 #include <stdexcept>
@@ -146,6 +148,17 @@ class DeviceIndex
 {
 public:
     explicit DeviceIndex(trx_ctx_t * ctx) : ctx_(ctx) {}
+    // One process per GPU: this handle is shard `index` of `count`.  Call before load().
+    //  * flat IBF: the handle holds the 64-bin column block [word_begin, word_begin + words) of EVERY row
+    //    (trx_ibf_create(..., shard_index, shard_count); count must divide bin_words), path bitvectors are that wide;
+    //  * HIBF: the (small) filter is replicated, every shard computes the whole candidate vector;
+    //  * verify text: only the FASTA files of the shard's bins are read and uploaded, bins keep their global ids.
+    void set_shard(uint32_t index, uint32_t count);
+    uint32_t shard_index() const { return shard_index_; }
+    uint32_t shard_count() const { return shard_count_; }
+    uint64_t shard_word_begin() const;  // first 64-bin word this shard owns
+    uint64_t shard_words() const;       // number of 64-bin words this shard owns
+    uint64_t path_words() const { return is_hibf() ? bin_words() : shard_words(); } // width of a collector path slot
     ~DeviceIndex();
     DeviceIndex(DeviceIndex const &) = delete;
     DeviceIndex & operator=(DeviceIndex const &) = delete;
@@ -190,6 +203,7 @@ private:
     void upload();
     void init_maps();
     trx_ctx_t * ctx_;
+    uint32_t shard_index_{0}, shard_count_{1};
     index_image img_;
     trx_ibf_t * flat_{nullptr};
     trx_hibf_t * hibf_{nullptr};
@@ -201,6 +215,15 @@ private:
 // ------------------------------------------------------------------------------------------ query path
 using bitvector = std::vector<uint64_t>; // ceil(bins/64) words, bit b = bin b (seqan::hibf::bit_vector words)
 
+// Hooks for the column-sharded collector.  any_alive: called once per probe step with one byte per probed item
+// (1 = some bin of THIS shard is still set on the item's path); it must OR the bytes over all shards in place
+// (an all-reduce(MAX) of n bytes) so that every shard prunes the same items — `path_.none()` is a statement about
+// ALL bins (include/otf_collector.h:383).  Unset = single device.
+struct shard_hooks
+{
+    std::function<void(uint8_t * alive, size_t n)> any_alive;
+};
+
 struct collect_stats
 {
     uint64_t probes{};   // k-mers probed on the device
@@ -210,14 +233,19 @@ struct collect_stats
 
 // process_query (include/query.h:226-247): preprocess, k-graph, OTFCollector::collect with every probe, path
 // AND, none() test and path OR executed on the device.
-bitvector process_query(std::string const & regex, DeviceIndex & index, collect_stats * stats = nullptr);
+// A sharded flat index returns the whole-width vector with only its own words filled in (the caller ORs / gathers).
+bitvector process_query(std::string const & regex, DeviceIndex & index, collect_stats * stats = nullptr,
+                        shard_hooks const * hooks = nullptr);
 // the collector alone on a ready k-graph (OTFCollector::collect, include/otf_collector.h:341-393)
-bitvector collect(kgraph const & g, DeviceIndex & index, collect_stats * stats = nullptr);
+bitvector collect(kgraph const & g, DeviceIndex & index, collect_stats * stats = nullptr, shard_hooks const * hooks = nullptr);
 
 // iter_disk_search (include/query.h:97-188): verifies the candidate bins on the device (K4) and writes the
 // reference's lines "bin_path\t>name\tmatch\tstart,end\n" (+ "…\tREVERSE STRAND HIT" for DNA) to `dest`
 // ("-" = stdout).  Returns the number of lines written.
 uint64_t iter_disk_search(bitvector const & hits, std::string const & query, DeviceIndex & index, std::string const & dest);
+// the same into a stream (forward and reverse-strand lines alike); a sharded index prints the lines of its own bins —
+// shards own ascending bin ranges, so concatenating the shards' outputs in shard order is the -t 1 print order
+uint64_t iter_disk_search(bitvector const & hits, std::string const & query, DeviceIndex & index, std::ostream & out);
 
 void drive_index(index_arguments const & args);
 void drive_query(query_arguments & args);
