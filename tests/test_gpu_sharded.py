@@ -2,8 +2,8 @@
 (one thread and one CUDA context handle per shard), the collector's pruning flags are OR-ed over the shards at every probe
 step, each shard verifies its own bins.  Candidate vector and printed lines must equal the unsharded `tetrex query`."""
 import os
-import random
 import subprocess
+import sys
 import threading
 
 import numpy as np
@@ -15,8 +15,8 @@ from tetrex_b200 import sharded
 pytestmark = pytest.mark.gpu
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-TETREX = os.path.join(ROOT, "tetrex_b200", "bin", "tetrex")
-AA = "ACDEFGHIKLMNPQRSTVWY"
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+from sharded_collection import QUERIES, TETREX  # noqa: E402
 
 
 def run(args):
@@ -43,31 +43,8 @@ class ThreadAllReduce:
 
 @pytest.fixture(scope="module")
 def collection(tmp_path_factory):
-    """256 peptide bins (4 words of 64 bins): motif instances planted in a few bins of every 64-bin column block."""
-    d = tmp_path_factory.mktemp("sharded")
-    rng = random.Random(5)
-    motifs = {3: "LMAQGLYN", 70: "LMAEGLYN", 130: "LMAQGLYN", 200: "LMAEGLYN", 255: "LMAQGLYN", 64: "CAHCWKKH"}
-    files = []
-    for b in range(256):
-        path = d / f"bin_{b:04d}.fa"
-        with open(path, "w") as f:
-            for r in range(3):
-                seq = "".join(rng.choice(AA) for _ in range(rng.randint(60, 400)))
-                if b in motifs and r == 1:
-                    seq = seq[:20] + motifs[b] + seq[20:]
-                f.write(f">b{b}_r{r} synthetic\n{seq}\n")
-        files.append(str(path))
-    lst = d / "bins.lst"
-    lst.write_text("\n".join(files) + "\n")
-    flat, hibf = str(d / "flat"), str(d / "hibf")
-    out = run(["index", "-i", "-k", "5", flat, str(lst)])
-    assert out.returncode == 0, out.stderr
-    out = run(["index", "-k", "5", hibf, str(lst)])
-    assert out.returncode == 0, out.stderr
-    return {"flat": flat + ".ibf", "hibf": hibf + ".ibf", "files": files}
-
-
-QUERIES = ["LMA(E|Q)GLYN", "CAHCWKKH", "LMAQGL", "MA(E|Q)GL(Y|F)N", "WWWWWWW", "L.AQGLYN"]
+    from sharded_collection import build
+    return build(str(tmp_path_factory.mktemp("sharded")))
 
 
 @pytest.mark.parametrize("kind,shards", [("flat", 2), ("flat", 4), ("hibf", 2), ("hibf", 3)])

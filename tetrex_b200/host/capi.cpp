@@ -2,8 +2,12 @@
 // torchrun opens its shard of an index file, runs process_query with the global pruning decision delegated to a
 // callback (torch.distributed all-reduce in tetrex_b200/sharded.py) and verifies its own bins.  Plain pointers and
 // sizes only; every call returns 0 or -1 with the message in trxh_last_error().
+#include <csignal>
 #include <cstring>
 #include <sstream>
+
+#include <execinfo.h>
+#include <unistd.h>
 
 #include "trx_host.hpp"
 
@@ -34,8 +38,25 @@ int guarded(F && f)
 }
 } // namespace
 
+namespace
+{
+void segv_backtrace(int)
+{
+    void * frames[64];
+    int const n = backtrace(frames, 64);
+    backtrace_symbols_fd(frames, n, 2);
+    _exit(139);
+}
+} // namespace
+
 extern "C"
 {
+
+// diagnostic: native backtrace (module + offset, for addr2line) on SIGSEGV instead of a silent death of the driver
+void trxh_debug_backtrace_on_segv(void)
+{
+    signal(SIGSEGV, segv_backtrace);
+}
 
 typedef void (*trxh_alive_fn)(uint8_t * alive, uint64_t n, void * user);
 
