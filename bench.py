@@ -360,6 +360,38 @@ def extra_measurements(t, ctx, torch, residues, offs, rec_bin, planted, hibf, pe
     big.close()
     txt = t.Text(ctx, residues, offs, rec_bin, N_BINS)
 
+    # ---- K4 over BASELINE config 2's pattern population: 1000 PROSITE-style patterns, every bin scanned for each
+    from tetrex_b200 import synth
+    pats = synth.prosite_patterns(1000, 1000)
+    kinds = {"window": 0, "atoms": 0, "exact": 0}
+    freq = np.bincount(residues[:1 << 24], minlength=256).astype(np.float64)
+    freq /= freq.sum()
+    compiled = []
+    for pat in pats:
+        rxp = t.Regex(pat, True)
+        kind = rxp.filter_plan(freq)["kind"]
+        kinds["exact" if kind == "none" else kind] += 1
+        compiled.append((rxp, kind))
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    total_hits, overflow, per_kind_s = 0, 0, {"window": 0.0, "atoms": 0.0, "none": 0.0}
+    for rxp, kind in compiled:
+        t1 = time.perf_counter()
+        try:
+            total_hits += len(txt.scan(rxp))
+        except t.TetrexError:
+            overflow += 1
+        per_kind_s[kind] += time.perf_counter() - t1
+    dt = time.perf_counter() - t0
+    out["verify_pattern_batch"] = {
+        "patterns": len(pats), "grammar": "SURVEY 8(d) C3: 6-14 elements, 60 % literal / 25 % class / 10 % x / 5 % (2,4) gaps",
+        "phase1_kernel": kinds, "scans_per_s": len(pats) / dt, "residues_per_s": len(pats) * n_res / dt,
+        "frac_of_hbm_peak": len(pats) * n_res / dt / 1e9 / peak, "hits": int(total_hits), "over_capacity": overflow,
+        "mean_us_per_scan": {("exact" if k == "none" else k): (per_kind_s[k] / max(kinds["exact" if k == "none" else k], 1)) * 1e6
+                             for k in per_kind_s}}
+    for rxp, _ in compiled:
+        rxp.close()
+
     # ---- whole query: k-mers of the query -> K3 -> AND/OR on device -> K4 on the candidate bins
     aamap, _ = t.peptide_maps(t.RED_BASE)
 

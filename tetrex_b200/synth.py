@@ -53,6 +53,32 @@ def swissprot_like(n_seqs: int = 570_000, n_bins: int = 1024, seed: int = 202503
     return residues, offs, rec_bin, planted
 
 
+def prosite_patterns(n: int = 1000, seed: int = 1000, planted_fraction: float = 0.0):
+    """PROSITE-style patterns as regexes (SURVEY.md §8(d) "C3 patterns", grammar of utils/tetrex_tools:130-153):
+    6-14 elements, each a literal (60 %), a class of 2-5 letters (25 %), x (10 %), x(2,4) or class(2,4) (5 %)."""
+    import random
+    rng = random.Random(seed)
+    aa = "ACDEFGHIKLMNPQRSTVWY"
+    pats = []
+    for _ in range(n):
+        parts = []
+        for _e in range(rng.randint(6, 14)):
+            u = rng.random()
+            if u < 0.60:
+                parts.append(rng.choice(aa))
+            elif u < 0.85:
+                parts.append("[" + "".join(sorted(rng.sample(aa, rng.randint(2, 5)))) + "]")
+            elif u < 0.95:
+                parts.append(".")
+            elif rng.random() < 0.5:
+                parts.append(".{2,4}")
+            else:
+                parts.append("[" + "".join(sorted(rng.sample(aa, rng.randint(2, 5)))) + "]{2,4}")
+        # the reference trims leading/trailing wildcards before building the k-graph; a verify regex may keep them
+        pats.append("".join(parts))
+    return pats
+
+
 def dna_like(n_bins: int, records_per_bin: int, record_len: int, seed: int = 8192):
     rng = np.random.default_rng(seed)
     n = n_bins * records_per_bin
