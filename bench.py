@@ -383,6 +383,17 @@ def extra_measurements(t, ctx, torch, residues, offs, rec_bin, planted, hibf, pe
             overflow += 1
         per_kind_s[kind] += time.perf_counter() - t1
     dt = time.perf_counter() - t0
+    # the same batch with three scans in flight (trx_regex_scan_begin/_end): kernels back to back, host latency hidden
+    only_rx = [rxp for rxp, _ in compiled]
+    txt.scan_many(only_rx[:8], cap=1 << 20)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    piped = txt.scan_many(only_rx, cap=1 << 20, depth=3)
+    dt_piped = time.perf_counter() - t0
+    out["verify_pattern_batch_pipelined"] = {"depth": 3, "scans_per_s": len(pats) / dt_piped,
+                                             "residues_per_s": len(pats) * n_res / dt_piped,
+                                             "frac_of_hbm_peak": len(pats) * n_res / dt_piped / 1e9 / peak,
+                                             "hits": int(sum(len(h) for h in piped))}
     out["verify_pattern_batch"] = {
         "patterns": len(pats), "grammar": "SURVEY 8(d) C3: 6-14 elements, 60 % literal / 25 % class / 10 % x / 5 % (2,4) gaps",
         "phase1_kernel": kinds, "scans_per_s": len(pats) / dt, "residues_per_s": len(pats) * n_res / dt,

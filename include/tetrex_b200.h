@@ -214,17 +214,30 @@ typedef struct trx_hit {
 int trx_regex_scan(trx_text_t *text, trx_regex_t *re, const uint64_t *candidate_bin_words, int reverse_strand,
                    const uint8_t *map256, trx_hit *hits, uint64_t cap, uint64_t *n_hits, uint64_t *stats);
 
+/* The same scan in two halves, for batches of queries (run_multiple_queries, include/query.h:330-340, loops over a
+ * file of regexes): _begin plans and enqueues everything on the context's stream and returns a ticket at once, _end
+ * waits for that scan and delivers its hits exactly as trx_regex_scan does (which is _begin + _end).  Up to
+ * TRX_SCAN_SLOTS scans of one text may be in flight; their kernels run back to back on the device while the host is
+ * already planning the next one — the ~50 us of per-call latency (plan, launches, read-back, sync) is paid once per
+ * batch instead of once per regex.  A further _begin with every slot taken returns TRX_ECAPACITY.  The regex handle and
+ * the candidate / map arrays are only read during _begin.  Tickets may be ended in any order. */
+#define TRX_SCAN_SLOTS 4
+int trx_regex_scan_begin(trx_text_t *text, trx_regex_t *re, const uint64_t *candidate_bin_words, int reverse_strand,
+                         const uint8_t *map256, uint64_t cap, int *ticket);
+int trx_regex_scan_end(trx_text_t *text, int ticket, trx_hit *hits, uint64_t *n_hits, uint64_t *stats);
+
 /* Host only, no device needed: the phase-1 prefilter trx_regex_scan would pick for this regex on a text with the
  * given relative byte frequencies (what RE2 does internally with its prefilter/memchr accelerations,
  * lib/re2/re2/prog.h ConfigurePrefixAccel — here the plan is visible so that tests can check it is a NECESSARY
  * condition of every match).  out[0] = 0 none (exact automaton), 1 fixed window, 2 gapped atoms.
  * window: out[1] = literals in bytes 0..3, out[2] = in bytes 4..7, out[3] = address of the match's first byte minus
  *         address of window byte 0, out[8+j] = byte offset of literal j in the window, out[16+j] = literal byte.
- * atoms:  out[1] = distinct literals, out[2] = atoms, out[3], out[4] = the match's first byte lies at an address in
- *         [anchor + out[3], anchor + out[4]]; atom a: literal byte out[8+a] at anchor + d for a d in
- *         [out[16+a], out[24+a]]. */
+ * atoms:  out[1] = distinct literal bytes, out[2] = terms, out[5] = atoms, out[3], out[4] = the match's first byte
+ *         lies at an address in [anchor + out[3], anchor + out[4]]; term i: byte out[8+i] at anchor + d for a d in
+ *         [out[24+i], out[40+i]], belonging to atom out[56+i] — an atom holds if ANY of its terms does (a class of up
+ *         to 3 bytes), the filter passes where ALL atoms hold. */
 int trx_regex_filter_plan(const trx_regex_t *re, const double *byte_freq, int reverse_strand, const uint8_t *map256,
-                          int32_t out[48]);
+                          int32_t out[72]);
 
 #ifdef __cplusplus
 }

@@ -71,12 +71,15 @@ def flagged_starts(plan: dict, text: np.ndarray) -> np.ndarray:
         return ok
     assert plan["kind"] == "atoms"
     hit = np.ones(n, dtype=bool)
-    for lit, lo, hi in plan["atoms"]:
-        assert 0 <= lo <= hi <= 31
+    lits = set()
+    for byts, lo, hi in plan["atoms"]:
+        assert 0 <= lo <= hi <= 31 and 1 <= len(byts) <= 3
+        lits |= set(byts)
         m = np.zeros(n, dtype=bool)
         for d in range(lo, hi + 1):
-            m[:n - d] |= text[d:] == lit
+            m[:n - d] |= np.isin(text[d:], byts)
         hit &= m
+    assert len(lits) == plan["n_lit"] <= 4
     assert any(lo == 0 and hi == 0 for _, lo, hi in plan["atoms"]), "one atom is the anchor"
     for a in np.flatnonzero(hit):
         lo, hi = max(0, a + plan["start_lo"]), min(n - 1, a + plan["start_hi"])
@@ -99,6 +102,8 @@ PEPTIDE = [
     "D.{0,3}EW", "C.{2}C.*H.{3}H", "W.{2,4}C.{5,9}CW", "(AB|CD)W.{1,2}M(K|R)H", "C(A|.{2,3})W.{0,2}M",
     "M.{2}(C|W)H.{3,4}(WK|WR)C", "HC+W.{3}M", "(C.{2,3}){2}WH", "C.{12,16}W.{10,14}H.{2}M", "W{2,3}.{4}C",
     "C[ST]?W.{2,5}HM", "WM.{30,31}CH", "C.{3}C.{3}C.{3}W", "N[^P][ST][^P]", "[RK].{2,3}[DE].{2,3}Y",
+    "[DM]D[KR]K[HLMY][EFS][CI]", "[HI]{2,4}[CSV]{2,4}R[NP].E", "[EMVWY]F[FR]Y[CST]{2,4}.", "H[IMPTV]G.[GHNPT].",
+    "[FHI][AGS].S.M", "R..[AV][MQW][DW]", "[CW][HM].{1,3}[CW]K", "GF[DMN].[CG].[INPSY]{2,4}.{2,4}[GQT][KR]",
 ]
 DNA = ["GATTACAG", "ACGTAC(G|T)", "TTGACA.{3}T", "TATA.{2,4}CGCG", "GG.{1,6}CCATGG", "A(C+|G+)T", "CG.{3}(AT|TA)GC.{0,2}GG"]
 
@@ -159,7 +164,10 @@ def test_plan_kinds():
     assert t.Regex("LMA(E|Q)GLYN", True).filter_plan(freq)["kind"] == "window"
     zf = t.Regex("C.{2,4}C.{3}[LIVMFYWC].{8}H.{3,5}H", True).filter_plan(freq)
     assert zf["kind"] == "atoms" and zf["n_lit"] == 2
-    assert sorted(zf["atoms"]) == [(67, 0, 0), (67, 3, 5), (72, 16, 18), (72, 20, 24)] and (zf["start_lo"], zf["start_hi"]) == (0, 0)
+    assert sorted(zf["atoms"]) == [((67,), 0, 0), ((67,), 3, 5), ((72,), 16, 18), ((72,), 20, 24)]
+    assert (zf["start_lo"], zf["start_hi"]) == (0, 0)
+    cl = t.Regex("[DM]D[KR]K[HLMY][EFS][CI]", True).filter_plan(freq)  # no literal window is selective enough; small classes are
+    assert cl["kind"] == "atoms" and any(len(b) > 1 for b, _, _ in cl["atoms"])
     assert t.Regex("(LMAQ|GLYN)", True).filter_plan(freq)["kind"] == "none"   # no necessary literal
     assert t.Regex("[ST].[RK]", True).filter_plan(freq)["kind"] == "none"
     # a reduced alphabet turns every literal into a class of raw bytes: no literal factor survives the byte map

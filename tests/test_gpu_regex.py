@@ -207,6 +207,46 @@ def test_atom_filter_equals_exact_automaton(ctx, monkeypatch):
         dtxt.close()
 
 
+def test_pipelined_scans_equal_sequential(ctx):
+    """trx_regex_scan_begin/_end: several scans in flight on one text give what one scan at a time gives, tickets can be
+    ended in any order, and the fifth begin is refused."""
+    rng = random.Random(21)
+    aa = b"ACDEFGHIKLMNPQRSTVWY"
+    seqs = [bytes(rng.choice(aa) for _ in range(L)) for L in [50000, 300, 0, 70000, 128 * 256 + 7, 5]]
+    rec_bin = [0, 0, 1, 2, 2, 3]
+    txt = build_text(ctx, seqs, rec_bin, 4)
+    pats = ["LMA(E|Q)GLYN", "C.{2,4}C", "[ILV][ILV]K", "W.{2,4}C.{5,9}CW", "N[ST][^P]", "KK+", "MA[EQ]G", "D.{0,3}EW", "HH", "^M", "W$"]
+    regs = [t.Regex(p, True) for p in pats]
+    want = [txt.scan(rx) for rx in regs]
+    assert sum(len(w) for w in want) > 100
+    for depth in (1, 2, 4):
+        got = txt.scan_many(regs, depth=depth)
+        for p, a, b in zip(pats, got, want):
+            assert np.array_equal(a, b), (p, depth)
+    cand = np.array([0b0101], dtype=np.uint64)
+    got = txt.scan_many(regs, candidate_bins=cand, depth=3)
+    for p, a, rx in zip(pats, got, regs):
+        assert np.array_equal(a, txt.scan(rx, candidate_bins=cand)), p
+    # out-of-order end, slot exhaustion, bad tickets
+    tickets = [txt.scan_begin(rx) for rx in regs[:4]]
+    with pytest.raises(t.TetrexError) as e:
+        txt.scan_begin(regs[4])
+    assert e.value.code == -5  # TRX_ECAPACITY
+    for i in (2, 0, 3, 1):
+        assert np.array_equal(txt.scan_end(tickets[i]), want[i]), pats[i]
+    with pytest.raises(t.TetrexError):
+        txt.scan_end(tickets[0])  # already ended
+    with pytest.raises(t.TetrexError):
+        txt.scan_end((17, 16))
+    # a scan that overflows its capacity reports it at _end and frees the slot
+    tk = txt.scan_begin(regs[2], cap=3)
+    with pytest.raises(t.TetrexError) as e:
+        txt.scan_end(tk)
+    assert e.value.code == -5
+    assert np.array_equal(txt.scan(regs[2]), want[2])
+    txt.close()
+
+
 def test_reverse_strand(ctx):
     """reverse_verify_fasta_hit (src/query.cpp:167-191): the record is complemented through comp_tab and reversed."""
     rng = random.Random(9)

@@ -77,6 +77,8 @@ PROTOTYPES = {
     "trx_regex_destroy": (None, [vp]),
     "trx_regex_positions": (C.c_int, [vp]),
     "trx_regex_scan": (C.c_int, [vp, vp, vp, C.c_int, vp, vp, C.c_uint64, u64p, u64p]),
+    "trx_regex_scan_begin": (C.c_int, [vp, vp, vp, C.c_int, vp, C.c_uint64, C.POINTER(C.c_int)]),
+    "trx_regex_scan_end": (C.c_int, [vp, C.c_int, vp, u64p, u64p]),
     "trx_regex_filter_plan": (C.c_int, [vp, vp, C.c_int, vp, vp]),
 }
 

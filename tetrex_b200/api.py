@@ -273,7 +273,7 @@ class Regex:
         f = _np(byte_freq, np.float64)
         assert len(f) == 256
         m = _np(map256, np.uint8) if map256 is not None else None
-        out = np.zeros(48, dtype=np.int32)
+        out = np.zeros(72, dtype=np.int32)
         check(lib().trx_regex_filter_plan(self._h, _ptr(f), int(reverse_strand), _ptr(m) if m is not None else None, _ptr(out)))
         kind = int(out[0])
         if kind == 1:
@@ -281,8 +281,12 @@ class Regex:
             return {"kind": "window", "start_delta": int(out[3]),
                     "literals": [(int(out[8 + j]), int(out[16 + j])) for j in range(n)]}  # (window byte, literal)
         if kind == 2:
+            atoms = {}
+            for i in range(int(out[2])):
+                a = atoms.setdefault(int(out[56 + i]), [[], int(out[24 + i]), int(out[40 + i])])
+                a[0].append(int(out[8 + i]))
             return {"kind": "atoms", "n_lit": int(out[1]), "start_lo": int(out[3]), "start_hi": int(out[4]),
-                    "atoms": [(int(out[8 + a]), int(out[16 + a]), int(out[24 + a])) for a in range(int(out[2]))]}  # (literal, lo, hi)
+                    "atoms": [(tuple(sorted(b)), lo, hi) for b, lo, hi in atoms.values()]}  # (bytes of the class, lo, hi)
         return {"kind": "none"}
 
     def close(self):
@@ -321,6 +325,61 @@ class Text:
             self.close()
         except Exception:
             pass
+
+    SCAN_SLOTS = 4  # TRX_SCAN_SLOTS
+
+    def _candidates(self, candidate_bins):
+        words = (self.n_bins + 63) // 64
+        if candidate_bins is None:
+            if getattr(self, "_all_bins", None) is None:
+                cand = np.full(words, np.uint64(2 ** 64 - 1), dtype=np.uint64)
+                if self.n_bins % 64:
+                    cand[-1] = np.uint64((1 << (self.n_bins % 64)) - 1)
+                self._all_bins = cand
+            return self._all_bins
+        cand = _np(candidate_bins, np.uint64)
+        assert len(cand) == words
+        return cand
+
+    def scan_begin(self, regex: Regex, candidate_bins=None, reverse_strand=False, map256=None, cap=1 << 16) -> tuple:
+        """First half of scan(): returns a ticket at once; up to SCAN_SLOTS scans may be in flight."""
+        cand = self._candidates(candidate_bins)
+        m = _np(map256, np.uint8) if map256 is not None else None
+        ticket = C.c_int(-1)
+        check(lib().trx_regex_scan_begin(self._h, regex._h, _ptr(cand), int(reverse_strand), _ptr(m) if m is not None else None,
+                                         cap, C.byref(ticket)))
+        return ticket.value, cap
+
+    def scan_end(self, ticket: tuple) -> np.ndarray:
+        """Second half: waits for that scan; (n,4) uint32 rows (bin, record, start, end) in reference print order."""
+        tk, cap = ticket
+        bufs = self.__dict__.setdefault("_slot_bufs", {})
+        if tk not in bufs or len(bufs[tk]) < cap:
+            bufs[tk] = (TrxHit * cap)()
+        n = C.c_uint64()
+        st = np.zeros(2, dtype=np.uint64)
+        check(lib().trx_regex_scan_end(self._h, tk, C.addressof(bufs[tk]), C.byref(n), st.ctypes.data_as(u64p)))
+        self.last_filter_literals = int(st[1])
+        return np.frombuffer(bufs[tk], dtype=np.uint32, count=4 * n.value).reshape(-1, 4).copy()
+
+    def scan_many(self, regexes, candidate_bins=None, reverse_strand=False, map256=None, cap=1 << 16, depth=3):
+        """A batch of regexes over the same candidate bins, `depth` scans in flight; returns one hit array per regex."""
+        assert 1 <= depth <= self.SCAN_SLOTS
+        out, pending = [], []
+        try:
+            for rx in regexes:
+                if len(pending) == depth:
+                    out.append(self.scan_end(pending.pop(0)))
+                pending.append(self.scan_begin(rx, candidate_bins, reverse_strand, map256, cap))
+            while pending:
+                out.append(self.scan_end(pending.pop(0)))
+        finally:
+            for tk in pending:  # an error above must not leave slots taken
+                try:
+                    self.scan_end(tk)
+                except Exception:
+                    pass
+        return out
 
     def scan(self, regex: Regex, candidate_bins=None, reverse_strand=False, map256=None, cap=1 << 20, stats=False):
         """Returns an (n,4) uint32 array of (bin, record, start, end) in reference print order."""

@@ -58,19 +58,23 @@ struct filter_spec
     uint32_t splat[8];        // literal byte replicated into all four lanes
 };
 
-// gapped necessary-factor prefilter ("atoms"): up to 4 distinct literal bytes and up to 8 atoms, each saying
-// "literal `lit` occurs at address anchor + d for some d in [lo, hi]" (0 <= lo <= hi <= 31).  One atom is the
-// anchor itself (lo = hi = 0).  Atoms are grouped by literal: literal l owns atoms [atom_begin[l], atom_begin[l+1]).
-// Every match contains such a constellation, and its first byte (reading direction) lies at an address in
-// [anchor + start_lo, anchor + start_hi].  Derived on the host from the automaton's dominator chain.
+// gapped necessary-factor prefilter ("atoms"): up to 4 distinct literal bytes and up to 8 atoms.  An atom says "one of
+// the atom's bytes occurs at address anchor + d for some d in [lo, hi]" (0 <= lo <= hi <= 31); it is stored as one TERM
+// per byte of its class (1-3 bytes), the terms of an atom are consecutive and the last one carries end_group.  One atom
+// is the anchor itself (lo = hi = 0).  Every match contains such a constellation, and its first byte (reading
+// direction) lies at an address in [anchor + start_lo, anchor + start_hi].  Derived on the host from the automaton's
+// dominator chain.
+constexpr int kMaxAtomTerms = 16;
 struct atom_spec
 {
     int32_t n_lit;            // 0: unused
     int32_t n_atoms;
+    int32_t n_terms;
     int32_t start_lo, start_hi;
     uint32_t splat[4];
-    uint8_t atom_begin[8];    // n_lit + 1 entries used
-    uint8_t lo[8], hi[8];
+    uint8_t term_lit[kMaxAtomTerms]; // index into splat
+    uint8_t term_lo[kMaxAtomTerms], term_hi[kMaxAtomTerms];
+    uint8_t term_end[kMaxAtomTerms]; // 1 = last term of its atom
 };
 
 struct scan_params
@@ -994,29 +998,39 @@ __global__ void __launch_bounds__(kScanThreads * SPLIT + 32)
                 m[l][MW] = 0;
         }
 
-        uint32_t acc[MW];
+        // cand = AND over atoms ( OR over the atom's bytes and offsets ( mask[byte] >> d ) ).  The term loop is uniform
+        // across the CTA; the literal index picks a register array, hence the if-chain instead of an indexed access.
+        uint32_t acc[MW], r[MW];
 #pragma unroll
         for (int q = 0; q < MW; ++q)
-            acc[q] = ~0u;
-#pragma unroll
-        for (int l = 0; l < NLIT; ++l)
         {
-            for (int a = p.atoms.atom_begin[l]; a < p.atoms.atom_begin[l + 1]; ++a)
+            acc[q] = ~0u;
+            r[q] = 0;
+        }
+        for (int i = 0; i < p.atoms.n_terms; ++i)
+        {
+            uint32_t const lit = p.atoms.term_lit[i], d_lo = p.atoms.term_lo[i], d_hi = p.atoms.term_hi[i];
+#pragma unroll
+            for (int l = 0; l < NLIT; ++l)
             {
-                uint32_t const d_hi = p.atoms.hi[a];
-                uint32_t r[MW];
-#pragma unroll
-                for (int q = 0; q < MW; ++q)
-                    r[q] = 0;
-                for (uint32_t d = p.atoms.lo[a]; d <= d_hi; ++d)
+                if (lit == static_cast<uint32_t>(l))
                 {
+                    for (uint32_t d = d_lo; d <= d_hi; ++d)
+                    {
 #pragma unroll
-                    for (int q = 0; q < MW; ++q)
-                        r[q] |= __funnelshift_r(m[l][q], m[l][q + 1], d);
+                        for (int q = 0; q < MW; ++q)
+                            r[q] |= __funnelshift_r(m[l][q], m[l][q + 1], d);
+                    }
                 }
+            }
+            if (p.atoms.term_end[i])
+            {
 #pragma unroll
                 for (int q = 0; q < MW; ++q)
+                {
                     acc[q] &= r[q];
+                    r[q] = 0;
+                }
             }
         }
         uint32_t any = 0;

@@ -21,18 +21,29 @@ struct trx_text
     uint64_t * d_rec_offsets{nullptr};
     uint32_t * d_rec_bin{nullptr};
     uint64_t * d_bin_rec_begin{nullptr};
-    // one allocation, so that a scan needs ONE memset and ONE read-back:
+    // Per-scan state lives in SLOTS so that several scans can be in flight on the context's stream (trx_regex_scan_begin /
+    // _end): the kernels of consecutive scans then run back to back, without the host round trip (plan, enqueue, sync,
+    // read-back — ~50 us) between them.  One allocation per slot, so that a scan needs ONE memset and ONE read-back:
     //   [chunk flags | record flags | counters (16 B) | first kSmallHits keys | first kSmallHits ends]
     //    <------------- cleared per scan ------------->
     //                                <------------------ copied to the host --------------------------->
-    uint8_t * d_scan_block{nullptr};
+    struct scan_slot
+    {
+        uint8_t * d_block{nullptr};
+        uint32_t * d_chunk_flags{nullptr};
+        uint32_t * d_rec_flags{nullptr};   // bitmap
+        uint8_t * d_counters{nullptr};     // hit count (u64), listed-record count (u32), next tile (u32)
+        uint32_t * d_rec_list{nullptr};
+        trx::scratch d_stage, h_stage, h_small, d_keys, d_ends;
+        cudaEvent_t done{nullptr};
+        bool busy{false};
+        uint64_t cap{}, residues{}, filter_units{};
+    };
+    static constexpr int kScanSlots = 4;
+    scan_slot slots[kScanSlots];
     uint64_t clear_bytes{};            // chunk flags + record flags + counters
-    uint32_t * d_chunk_flags{nullptr};
     uint64_t n_chunk_flag_words{};
-    uint32_t * d_rec_flags{nullptr};   // bitmap
     uint64_t n_rec_flag_words{};
-    uint8_t * d_counters{nullptr};     // hit count (u64), listed-record count (u32)
-    uint32_t * d_rec_list{nullptr};
     double byte_freq[256]{};           // relative byte frequencies of the residue store
     std::vector<uint64_t> h_rec_offsets;   // host copies: tile planning and hit formatting
     std::vector<uint32_t> h_rec_bin;
@@ -55,7 +66,7 @@ struct trx_text
     };
     std::vector<cached_choice> choices;
     // per-scan scratch
-    trx::scratch d_stage, h_stage, h_small, d_tiles, d_keys, d_ends, d_keys2, d_ends2, d_sort_tmp;
+    trx::scratch d_tiles, d_keys2, d_ends2, d_sort_tmp;
 };
 
 using namespace trx;
@@ -159,12 +170,16 @@ int trx_text_upload(trx_ctx_t * ctx, const uint8_t * residues, const uint64_t * 
     {
         uint64_t const flag_bytes = (t->n_chunk_flag_words * 4 + t->n_rec_flag_words * 4 + 15) & ~uint64_t{15};
         t->clear_bytes = flag_bytes + 16;
-        if ((e = cudaMalloc(&t->d_scan_block, t->clear_bytes + kSmallHits * 12)) != cudaSuccess) return fail(e);
-        t->d_chunk_flags = reinterpret_cast<uint32_t *>(t->d_scan_block);
-        t->d_rec_flags = t->d_chunk_flags + t->n_chunk_flag_words;
-        t->d_counters = t->d_scan_block + flag_bytes;
+        for (trx_text::scan_slot & sl : t->slots)
+        {
+            if ((e = cudaMalloc(&sl.d_block, t->clear_bytes + kSmallHits * 12)) != cudaSuccess) return fail(e);
+            sl.d_chunk_flags = reinterpret_cast<uint32_t *>(sl.d_block);
+            sl.d_rec_flags = sl.d_chunk_flags + t->n_chunk_flag_words;
+            sl.d_counters = sl.d_block + flag_bytes;
+            if ((e = cudaMalloc(&sl.d_rec_list, n_records * 4)) != cudaSuccess) return fail(e);
+            if ((e = cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming)) != cudaSuccess) return fail(e);
+        }
     }
-    if ((e = cudaMalloc(&t->d_rec_list, n_records * 4)) != cudaSuccess) return fail(e);
     if ((e = cudaMemsetAsync(t->d_text + (t->n_text_padded - kTileBytes), 0, kTileBytes, ctx->stream)) != cudaSuccess) return fail(e);
     if (n_text && (e = cudaMemcpyAsync(t->d_text, residues, n_text, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess) return fail(e);
     if ((e = cudaMemcpyAsync(t->d_rec_offsets, rec_offsets, (n_records + 1) * 8, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess) return fail(e);
@@ -206,10 +221,16 @@ void trx_text_destroy(trx_text_t * t)
     cudaFree(t->d_rec_offsets);
     cudaFree(t->d_rec_bin);
     cudaFree(t->d_bin_rec_begin);
-    cudaFree(t->d_scan_block);
-    cudaFree(t->d_rec_list);
-    for (trx::scratch * s : {&t->d_stage, &t->h_stage, &t->h_small, &t->d_tiles, &t->d_keys, &t->d_ends, &t->d_keys2, &t->d_ends2,
-                             &t->d_sort_tmp})
+    for (trx_text::scan_slot & sl : t->slots)
+    {
+        cudaFree(sl.d_block);
+        cudaFree(sl.d_rec_list);
+        if (sl.done)
+            cudaEventDestroy(sl.done);
+        for (trx::scratch * s : {&sl.d_stage, &sl.h_stage, &sl.h_small, &sl.d_keys, &sl.d_ends})
+            s->release();
+    }
+    for (trx::scratch * s : {&t->d_tiles, &t->d_keys2, &t->d_ends2, &t->d_sort_tmp})
         s->release();
     delete t;
 }
@@ -619,25 +640,41 @@ atom_plan derive_atoms(regex_dev const & img, double const * freq, bool reverse)
     int const P = g.P;
     if (P <= 0)
         return none;
-    // literal of a position: the single raw byte whose class holds it
-    std::vector<int> literal(P, -1);
+    // class of a position = the raw bytes it accepts; usable as an atom when there are at most 3 of them
+    constexpr int kMaxClass = 3;
+    struct small_class
+    {
+        int n{0};
+        int byte[kMaxClass]{};
+        double freq{0.0};
+    };
+    std::vector<small_class> cls(P);
     {
         std::vector<int> count(P, 0);
         for (int c = 0; c < 256; ++c)
             for (int pos = 0; pos < P; ++pos)
                 if ((img.B[c][pos >> 6] >> (pos & 63)) & 1)
                 {
+                    if (count[pos] < kMaxClass)
+                        cls[pos].byte[count[pos]] = c;
                     ++count[pos];
-                    literal[pos] = c;
                 }
         for (int pos = 0; pos < P; ++pos)
-            if (count[pos] != 1)
-                literal[pos] = -1;
+        {
+            cls[pos].n = count[pos] <= kMaxClass ? count[pos] : 0;
+            for (int j = 0; j < cls[pos].n; ++j)
+            {
+                if (cls[pos].byte[j] == 0) // the text is zero padded: a NUL literal would match the padding
+                    cls[pos].n = 0;
+                else
+                    cls[pos].freq += std::max(freq[cls[pos].byte[j]], 1e-4);
+            }
+        }
     }
-    // chain of necessary literal positions, ordered by their shortest distance from S
+    // chain of necessary small-class positions, ordered by their shortest distance from S
     struct link
     {
-        int pos, lit;
+        int pos;
         int off_lo, off_hi; // offset of the symbol inside the match (first symbol = 0)
     };
     std::vector<link> chain;
@@ -645,7 +682,7 @@ atom_plan derive_atoms(regex_dev const & img, double const * freq, bool reverse)
         std::vector<std::pair<int, int>> order; // (min offset, position)
         for (int pos = 0; pos < P; ++pos)
         {
-            if (literal[pos] < 0 || literal[pos] == 0 || reachable_without(g, g.S(), g.F(), pos))
+            if (cls[pos].n == 0 || reachable_without(g, g.S(), g.F(), pos))
                 continue;
             int lo = 0, hi = 0;
             if (!walk_range(g, g.S(), pos, lo, hi))
@@ -667,7 +704,7 @@ atom_plan derive_atoms(regex_dev const & img, double const * freq, bool reverse)
             }
             off_lo += lo;
             off_hi += hi;
-            chain.push_back(link{pos, literal[pos], off_lo, off_hi});
+            chain.push_back(link{pos, off_lo, off_hi});
             prev = pos;
         }
     }
@@ -675,21 +712,21 @@ atom_plan derive_atoms(regex_dev const & img, double const * freq, bool reverse)
         return none;
 
     constexpr double kGoodEnough = 2e-5;
-    constexpr int kMaxStartSpread = 1024;
+    constexpr int kMaxStartSpread = 1024, kMaxAtoms = 8;
     atom_plan best;
     int best_lits = 99;
     int const n = static_cast<int>(chain.size());
+    struct cand
+    {
+        int pos, lo, hi;
+        double factor;
+    };
     for (int anchor = 0; anchor < n; ++anchor)
     {
         if (chain[anchor].off_hi - chain[anchor].off_lo > kMaxStartSpread)
             continue;
         // address offsets of the other atoms relative to the anchor: forward scans look at later symbols (higher
         // addresses), reverse scans read downwards, so EARLIER symbols lie at higher addresses
-        struct cand
-        {
-            int lit, lo, hi;
-            double factor;
-        };
         std::vector<cand> cands;
         for (int i = 0; i < n; ++i)
         {
@@ -698,8 +735,7 @@ atom_plan derive_atoms(regex_dev const & img, double const * freq, bool reverse)
             int lo, hi;
             if (!reverse)
             {
-                // distance anchor → i: sum of the gaps in between = difference of cumulative offsets, taken gap-wise
-                lo = chain[i].off_lo - chain[anchor].off_lo;
+                lo = chain[i].off_lo - chain[anchor].off_lo; // sum of the gaps in between, gap-wise minimum / maximum
                 hi = chain[i].off_hi - chain[anchor].off_hi;
             }
             else
@@ -709,59 +745,82 @@ atom_plan derive_atoms(regex_dev const & img, double const * freq, bool reverse)
             }
             if (lo < 1 || hi < lo || hi > 31)
                 continue;
-            double const f = 1.0 - std::pow(1.0 - std::max(freq[chain[i].lit], 1e-4), hi - lo + 1); // any of the offsets
+            double const f = 1.0 - std::pow(1.0 - std::min(cls[chain[i].pos].freq, 1.0), hi - lo + 1); // any of the offsets
             if (f > 0.7)
                 continue;
-            cands.push_back(cand{chain[i].lit, lo, hi, f});
+            cands.push_back(cand{chain[i].pos, lo, hi, f});
         }
         std::sort(cands.begin(), cands.end(), [](cand const & a, cand const & b) { return a.factor < b.factor; });
-        int lits[4], n_lit = 1;
-        lits[0] = chain[anchor].lit;
-        std::vector<cand> chosen{cand{chain[anchor].lit, 0, 0, std::max(freq[chain[anchor].lit], 1e-4)}};
-        double pass = chosen[0].factor;
+        int lits[4], n_lit = 0, n_terms = 0;
+        auto lits_after = [&](small_class const & c)
+        {
+            int extra = 0;
+            for (int j = 0; j < c.n; ++j)
+            {
+                bool known = false;
+                for (int l = 0; l < n_lit; ++l)
+                    known |= lits[l] == c.byte[j];
+                extra += known ? 0 : 1;
+            }
+            return n_lit + extra;
+        };
+        auto take = [&](small_class const & c)
+        {
+            for (int j = 0; j < c.n; ++j)
+            {
+                bool known = false;
+                for (int l = 0; l < n_lit; ++l)
+                    known |= lits[l] == c.byte[j];
+                if (!known)
+                    lits[n_lit++] = c.byte[j];
+            }
+            n_terms += c.n;
+        };
+        small_class const & ac = cls[chain[anchor].pos];
+        take(ac);
+        std::vector<cand> chosen{cand{chain[anchor].pos, 0, 0, ac.freq}};
+        double pass = ac.freq;
         for (cand const & cd : cands)
         {
-            if (pass <= kGoodEnough || chosen.size() >= 8)
+            if (pass <= kGoodEnough || static_cast<int>(chosen.size()) >= kMaxAtoms)
                 break;
-            int l = 0;
-            while (l < n_lit && lits[l] != cd.lit)
-                ++l;
-            if (l == n_lit)
-            {
-                if (n_lit == 4)
-                    continue;
-                lits[n_lit++] = cd.lit;
-            }
+            small_class const & c = cls[cd.pos];
+            if (lits_after(c) > 4 || n_terms + c.n > kMaxAtomTerms)
+                continue;
+            take(c);
             chosen.push_back(cd);
             pass *= cd.factor;
         }
-        // good enough is good enough: below the target rate prefer the cheaper kernel (fewer literals, fewer atoms)
+        // good enough is good enough: below the target rate prefer the cheaper kernel (fewer literals, fewer terms)
         bool better;
         if (pass > kGoodEnough || best.pass > kGoodEnough)
             better = pass < best.pass;
         else
-            better = n_lit < best_lits || (n_lit == best_lits && static_cast<int>(chosen.size()) < best.spec.n_atoms);
+            better = n_lit < best_lits || (n_lit == best_lits && n_terms < best.spec.n_terms);
         if (!better)
             continue;
         atom_plan plan;
         plan.pass = pass;
         plan.spec.n_lit = n_lit;
         plan.spec.n_atoms = static_cast<int32_t>(chosen.size());
-        int a = 0;
         for (int l = 0; l < n_lit; ++l)
-        {
             plan.spec.splat[l] = 0x01010101u * static_cast<uint32_t>(lits[l]);
-            plan.spec.atom_begin[l] = static_cast<uint8_t>(a);
-            for (cand const & cd : chosen)
-                if (cd.lit == lits[l])
-                {
-                    plan.spec.lo[a] = static_cast<uint8_t>(cd.lo);
-                    plan.spec.hi[a] = static_cast<uint8_t>(cd.hi);
-                    ++a;
-                }
+        int a = 0;
+        for (cand const & cd : chosen)
+        {
+            small_class const & c = cls[cd.pos];
+            for (int j = 0; j < c.n; ++j, ++a)
+            {
+                int l = 0;
+                while (lits[l] != c.byte[j])
+                    ++l;
+                plan.spec.term_lit[a] = static_cast<uint8_t>(l);
+                plan.spec.term_lo[a] = static_cast<uint8_t>(cd.lo);
+                plan.spec.term_hi[a] = static_cast<uint8_t>(cd.hi);
+                plan.spec.term_end[a] = j + 1 == c.n ? 1 : 0;
+            }
         }
-        for (int l = n_lit; l < 8; ++l)
-            plan.spec.atom_begin[l] = static_cast<uint8_t>(a);
+        plan.spec.n_terms = a;
         if (!reverse)
         {
             plan.spec.start_lo = -chain[anchor].off_hi;
@@ -853,27 +912,36 @@ size_t align16(size_t x)
 extern "C"
 {
 
-int trx_regex_scan(trx_text_t * t, trx_regex_t * re, const uint64_t * candidate_bin_words, int reverse_strand,
-                   const uint8_t * map256, trx_hit * hits, uint64_t cap, uint64_t * n_hits, uint64_t * stats)
+int trx_regex_scan_begin(trx_text_t * t, trx_regex_t * re, const uint64_t * candidate_bin_words, int reverse_strand,
+                         const uint8_t * map256, uint64_t cap, int * ticket)
 {
-    if (!t || !re || !candidate_bin_words || !n_hits || (cap && !hits))
-        return set_error(TRX_EINVAL, "trx_regex_scan: NULL argument");
-    *n_hits = 0;
-    if (stats)
-        stats[0] = 0;
+    if (!t || !re || !candidate_bin_words || !ticket)
+        return set_error(TRX_EINVAL, "trx_regex_scan_begin: NULL argument");
+    *ticket = -1;
     trx_ctx * c = t->ctx;
     TRX_TRY(c->use());
+    int slot_index = -1;
+    for (int i = 0; i < trx_text::kScanSlots && slot_index < 0; ++i)
+        if (!t->slots[i].busy)
+            slot_index = i;
+    if (slot_index < 0)
+        return set_error(TRX_ECAPACITY, "trx_regex_scan_begin: %d scans already in flight on this text (call trx_regex_scan_end)",
+                         trx_text::kScanSlots);
+    trx_text::scan_slot & sl = t->slots[slot_index];
+    sl.cap = cap;
+    sl.residues = 0;
+    sl.filter_units = 0;
     // TRX_SCAN_TRACE=1: host-clock breakdown of this call on stderr (diagnostic)
     static bool const trace = getenv("TRX_SCAN_TRACE") != nullptr;
     auto const now = [] { return std::chrono::steady_clock::now(); };
     auto const t_begin = now();
-    auto t_plan = t_begin, t_image = t_begin, t_choice = t_begin, t_enqueued = t_begin;
+    auto t_plan = t_begin, t_image = t_begin, t_choice = t_begin;
     if (re->follow_list.size() > sizeof(regex_dev::follow_list))
         return set_error(TRX_EREGEX, "pattern '%s': ordered follow lists need %zu bytes (max %zu)", re->pattern.c_str(),
                          re->follow_list.size(), sizeof(regex_dev::follow_list));
 
     // the clear of flags and counters does not depend on anything below: let it run while the host plans
-    TRX_CUDA(cudaMemsetAsync(t->d_scan_block, 0, t->clear_bytes, c->stream));
+    TRX_CUDA(cudaMemsetAsync(sl.d_block, 0, t->clear_bytes, c->stream));
 
     // ---- plan: candidate bins → tiles of the text
     uint64_t const cand_words = (t->n_bins + 63) / 64;
@@ -910,10 +978,8 @@ int trx_regex_scan(trx_text_t * t, trx_regex_t * re, const uint64_t * candidate_
         t->plan_valid = true;
     }
     std::vector<uint32_t> const & tiles = t->plan_tiles;
-    if (stats)
-        stats[0] = t->plan_residues;
-    if (tiles.empty())
-        return TRX_OK;
+    sl.residues = t->plan_residues;
+    // even an empty plan goes through the whole protocol (the memset above left the slot's counters at zero)
 
     t_plan = now();
     // ---- one pinned staging block: [candidate words | automaton image], one H2D copy
@@ -921,10 +987,10 @@ int trx_regex_scan(trx_text_t * t, trx_regex_t * re, const uint64_t * candidate_
     size_t const off_cand = 0;
     size_t const off_regex = align16(off_cand + cand_words * 8);
     size_t const stage_bytes = off_regex + sizeof(regex_dev);
-    t->h_stage.pinned_host = true;
-    TRX_TRY(t->h_stage.reserve(stage_bytes));
-    TRX_TRY(t->d_stage.reserve(stage_bytes));
-    auto * hs = static_cast<uint8_t *>(t->h_stage.ptr);
+    sl.h_stage.pinned_host = true;
+    TRX_TRY(sl.h_stage.reserve(stage_bytes));
+    TRX_TRY(sl.d_stage.reserve(stage_bytes));
+    auto * hs = static_cast<uint8_t *>(sl.h_stage.ptr);
     memcpy(hs + off_cand, candidate_bin_words, cand_words * 8);
     auto * img = reinterpret_cast<regex_dev *>(hs + off_regex);
     fill_image(*re, reverse_strand != 0, map256, img);
@@ -933,9 +999,9 @@ int trx_regex_scan(trx_text_t * t, trx_regex_t * re, const uint64_t * candidate_
     if (cap > (1ull << 31))
         cap = 1ull << 31;
     uint64_t const dev_cap = cap ? cap : 1;
-    TRX_TRY(t->d_keys.reserve(dev_cap * 8));
-    TRX_TRY(t->d_ends.reserve(dev_cap * 4));
-    auto * ds = static_cast<uint8_t *>(t->d_stage.ptr);
+    TRX_TRY(sl.d_keys.reserve(dev_cap * 8));
+    TRX_TRY(sl.d_ends.reserve(dev_cap * 4));
+    auto * ds = static_cast<uint8_t *>(sl.d_stage.ptr);
     TRX_CUDA(cudaMemcpyAsync(ds, hs, stage_bytes, cudaMemcpyHostToDevice, c->stream));
     scan_params sp{};
     sp.text = t->d_text;
@@ -947,11 +1013,11 @@ int trx_regex_scan(trx_text_t * t, trx_regex_t * re, const uint64_t * candidate_
     sp.cand_words = reinterpret_cast<uint64_t *>(ds + off_cand);
     sp.tiles = static_cast<uint32_t *>(t->d_tiles.ptr);
     sp.n_tiles = static_cast<uint32_t>(tiles.size());
-    sp.chunk_flags = t->d_chunk_flags;
-    sp.rec_flags = t->d_rec_flags;
-    sp.rec_list = t->d_rec_list;
-    sp.rec_count = reinterpret_cast<unsigned int *>(t->d_counters + 8);
-    sp.tile_counter = reinterpret_cast<unsigned int *>(t->d_counters + 12);
+    sp.chunk_flags = sl.d_chunk_flags;
+    sp.rec_flags = sl.d_rec_flags;
+    sp.rec_list = sl.d_rec_list;
+    sp.rec_count = reinterpret_cast<unsigned int *>(sl.d_counters + 8);
+    sp.tile_counter = reinterpret_cast<unsigned int *>(sl.d_counters + 12);
     sp.re = reinterpret_cast<regex_dev *>(ds + off_regex);
 
     // TRX_REGEX_STAGING=ldg  → exact automaton kernel with direct loads (A/B evidence for the TMA staging)
@@ -994,10 +1060,11 @@ int trx_regex_scan(trx_text_t * t, trx_regex_t * re, const uint64_t * candidate_
     }
     bool const use_atoms = kind == kFilterAtoms, use_window = kind == kFilterWindow;
     t_choice = now();
-    if (stats)
-        stats[1] = use_atoms ? static_cast<uint64_t>(sp.atoms.n_atoms)
-                             : (use_window ? static_cast<uint64_t>(sp.filter.n_a + sp.filter.n_b) : 0);
-    if (use_atoms)
+    sl.filter_units = use_atoms ? static_cast<uint64_t>(sp.atoms.n_atoms)
+                                : (use_window ? static_cast<uint64_t>(sp.filter.n_a + sp.filter.n_b) : 0);
+    if (tiles.empty())
+        ; // nothing to scan: no kernel, the read-back below returns the zeroed counters
+    else if (use_atoms)
         TRX_TRY(launch_atoms_any(c, sp, t->tmap));
     else if (use_window)
         TRX_TRY(launch_filter_any(c, sp, t->tmap));
@@ -1009,39 +1076,69 @@ int trx_regex_scan(trx_text_t * t, trx_regex_t * re, const uint64_t * candidate_
     resolve_params rp{};
     rp.text = t->d_text;
     rp.rec_offsets = t->d_rec_offsets;
-    rp.rec_list = t->d_rec_list;
+    rp.rec_list = sl.d_rec_list;
     rp.rec_count = sp.rec_count;
-    rp.chunk_flags = t->d_chunk_flags;
+    rp.chunk_flags = sl.d_chunk_flags;
     rp.re = sp.re;
-    rp.hit_count = reinterpret_cast<unsigned long long *>(t->d_counters);
-    rp.hit_keys = static_cast<uint64_t *>(t->d_keys.ptr);
-    rp.hit_ends = static_cast<uint32_t *>(t->d_ends.ptr);
-    rp.small_keys = reinterpret_cast<uint64_t *>(t->d_counters + 16);
-    rp.small_ends = reinterpret_cast<uint32_t *>(t->d_counters + 16 + kSmallHits * 8);
+    rp.hit_count = reinterpret_cast<unsigned long long *>(sl.d_counters);
+    rp.hit_keys = static_cast<uint64_t *>(sl.d_keys.ptr);
+    rp.hit_ends = static_cast<uint32_t *>(sl.d_ends.ptr);
+    rp.small_keys = reinterpret_cast<uint64_t *>(sl.d_counters + 16);
+    rp.small_ends = reinterpret_cast<uint32_t *>(sl.d_counters + 16 + kSmallHits * 8);
     rp.cap = cap;
-    if (re->words == 1)
+    if (tiles.empty())
+        ;
+    else if (re->words == 1)
         TRX_TRY(launch_phase2_w<1>(c, rp, reverse));
     else
         TRX_TRY(launch_phase2_w<2>(c, rp, reverse));
 
     // ---- read back: the counters and the first kSmallHits hits in ONE copy
     constexpr uint64_t kSmall = kSmallHits;
-    uint64_t const spec = cap < kSmall ? cap : kSmall;
-    t->h_small.pinned_host = true;
-    TRX_TRY(t->h_small.reserve(16 + kSmall * 12));
-    auto * h_total = static_cast<unsigned long long *>(t->h_small.ptr);
-    auto * h_keys = reinterpret_cast<uint64_t *>(static_cast<uint8_t *>(t->h_small.ptr) + 16);
-    auto * h_ends = reinterpret_cast<uint32_t *>(static_cast<uint8_t *>(t->h_small.ptr) + 16 + kSmall * 8);
-    TRX_CUDA(cudaMemcpyAsync(h_total, t->d_counters, 16 + kSmall * 12, cudaMemcpyDeviceToHost, c->stream));
-    t_enqueued = now();
-    TRX_CUDA(cudaStreamSynchronize(c->stream));
+    sl.h_small.pinned_host = true;
+    TRX_TRY(sl.h_small.reserve(16 + kSmall * 12));
+    auto * h_total = static_cast<unsigned long long *>(sl.h_small.ptr);
+    TRX_CUDA(cudaMemcpyAsync(h_total, sl.d_counters, 16 + kSmall * 12, cudaMemcpyDeviceToHost, c->stream));
+    TRX_CUDA(cudaEventRecord(sl.done, c->stream));
+    sl.busy = true;
+    *ticket = slot_index;
     if (trace)
     {
         auto us = [](auto a, auto b) { return std::chrono::duration<double, std::micro>(b - a).count(); };
-        fprintf(stderr, "trx_regex_scan: plan %.1f  image %.1f  filter choice %.1f  enqueue %.1f  wait %.1f us (%zu tiles)\n",
-                us(t_begin, t_plan), us(t_plan, t_image), us(t_image, t_choice), us(t_choice, t_enqueued),
-                us(t_enqueued, now()), tiles.size());
+        fprintf(stderr, "trx_regex_scan_begin: plan %.1f  image %.1f  filter choice %.1f  enqueue %.1f us (%zu tiles, slot %d)\n",
+                us(t_begin, t_plan), us(t_plan, t_image), us(t_image, t_choice), us(t_choice, now()), tiles.size(), slot_index);
     }
+    return TRX_OK;
+}
+
+int trx_regex_scan_end(trx_text_t * t, int ticket, trx_hit * hits, uint64_t * n_hits, uint64_t * stats)
+{
+    if (!t || !n_hits || ticket < 0 || ticket >= trx_text::kScanSlots || !t->slots[ticket].busy)
+        return set_error(TRX_EINVAL, "trx_regex_scan_end: bad ticket");
+    trx_text::scan_slot & sl = t->slots[ticket];
+    uint64_t const cap = sl.cap;
+    if (cap && !hits)
+        return set_error(TRX_EINVAL, "trx_regex_scan_end: hits is NULL");
+    trx_ctx * c = t->ctx;
+    TRX_TRY(c->use());
+    *n_hits = 0;
+    if (stats)
+    {
+        stats[0] = sl.residues;
+        stats[1] = sl.filter_units;
+    }
+    cudaError_t const waited = cudaEventSynchronize(sl.done);
+    sl.busy = false; // whatever happens below, the slot is free again
+    TRX_CUDA(waited);
+    constexpr uint64_t kSmall = kSmallHits;
+    uint64_t const spec = cap < kSmall ? cap : kSmall;
+    auto * h_total = static_cast<unsigned long long *>(sl.h_small.ptr);
+    auto * h_keys = reinterpret_cast<uint64_t *>(static_cast<uint8_t *>(sl.h_small.ptr) + 16);
+    auto * h_ends = reinterpret_cast<uint32_t *>(static_cast<uint8_t *>(sl.h_small.ptr) + 16 + kSmall * 8);
+    uint64_t * const d_hit_keys = static_cast<uint64_t *>(sl.d_keys.ptr);
+    uint32_t * const d_hit_ends = static_cast<uint32_t *>(sl.d_ends.ptr);
+    uint64_t * const d_small_keys = reinterpret_cast<uint64_t *>(sl.d_counters + 16);
+    uint32_t * const d_small_ends = reinterpret_cast<uint32_t *>(sl.d_counters + 16 + kSmallHits * 8);
     unsigned long long const total = *h_total;
     *n_hits = total;
     if (total > cap)
@@ -1065,17 +1162,17 @@ int trx_regex_scan(trx_text_t * t, trx_regex_t * re, const uint64_t * candidate_
 
     // ---- order = (bin, record, start): records are grouped by ascending bin, so (record, start) suffices
     uint64_t const n = total;
-    TRX_CUDA(cudaMemcpyAsync(rp.hit_keys, rp.small_keys, kSmall * 8, cudaMemcpyDeviceToDevice, c->stream));
-    TRX_CUDA(cudaMemcpyAsync(rp.hit_ends, rp.small_ends, kSmall * 4, cudaMemcpyDeviceToDevice, c->stream));
+    TRX_CUDA(cudaMemcpyAsync(d_hit_keys, d_small_keys, kSmall * 8, cudaMemcpyDeviceToDevice, c->stream));
+    TRX_CUDA(cudaMemcpyAsync(d_hit_ends, d_small_ends, kSmall * 4, cudaMemcpyDeviceToDevice, c->stream));
     TRX_TRY(t->d_keys2.reserve(n * 8));
     TRX_TRY(t->d_ends2.reserve(n * 4));
     size_t tmp_bytes = 0;
-    TRX_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, rp.hit_keys, static_cast<uint64_t *>(t->d_keys2.ptr),
-                                             rp.hit_ends, static_cast<uint32_t *>(t->d_ends2.ptr), static_cast<int>(n), 0, 64,
+    TRX_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, d_hit_keys, static_cast<uint64_t *>(t->d_keys2.ptr),
+                                             d_hit_ends, static_cast<uint32_t *>(t->d_ends2.ptr), static_cast<int>(n), 0, 64,
                                              c->stream));
     TRX_TRY(t->d_sort_tmp.reserve(tmp_bytes));
-    TRX_CUDA(cub::DeviceRadixSort::SortPairs(t->d_sort_tmp.ptr, tmp_bytes, rp.hit_keys,
-                                             static_cast<uint64_t *>(t->d_keys2.ptr), rp.hit_ends,
+    TRX_CUDA(cub::DeviceRadixSort::SortPairs(t->d_sort_tmp.ptr, tmp_bytes, d_hit_keys,
+                                             static_cast<uint64_t *>(t->d_keys2.ptr), d_hit_ends,
                                              static_cast<uint32_t *>(t->d_ends2.ptr), static_cast<int>(n), 0, 64, c->stream));
     c->launches += 3; // cub's histogram + onesweep passes
     std::vector<uint64_t> keys(n);
@@ -1091,8 +1188,19 @@ int trx_regex_scan(trx_text_t * t, trx_regex_t * re, const uint64_t * candidate_
     return TRX_OK;
 }
 
+int trx_regex_scan(trx_text_t * t, trx_regex_t * re, const uint64_t * candidate_bin_words, int reverse_strand,
+                   const uint8_t * map256, trx_hit * hits, uint64_t cap, uint64_t * n_hits, uint64_t * stats)
+{
+    if (!t || !re || !candidate_bin_words || !n_hits || (cap && !hits))
+        return set_error(TRX_EINVAL, "trx_regex_scan: NULL argument");
+    *n_hits = 0;
+    int ticket = -1;
+    TRX_TRY(trx_regex_scan_begin(t, re, candidate_bin_words, reverse_strand, map256, cap, &ticket));
+    return trx_regex_scan_end(t, ticket, hits, n_hits, stats);
+}
+
 int trx_regex_filter_plan(const trx_regex_t * re, const double * byte_freq, int reverse_strand, const uint8_t * map256,
-                          int32_t out[48])
+                          int32_t out[72])
 {
     if (!re || !byte_freq || !out)
         return set_error(TRX_EINVAL, "trx_regex_filter_plan: NULL argument");
@@ -1101,7 +1209,7 @@ int trx_regex_filter_plan(const trx_regex_t * re, const double * byte_freq, int 
     filter_spec window;
     atom_spec atoms;
     filter_kind const kind = choose_filter(*img, byte_freq, reverse_strand != 0, window, atoms);
-    memset(out, 0, 48 * sizeof(int32_t));
+    memset(out, 0, 72 * sizeof(int32_t));
     out[0] = kind;
     if (kind == kFilterWindow)
     {
@@ -1117,16 +1225,19 @@ int trx_regex_filter_plan(const trx_regex_t * re, const double * byte_freq, int 
     else if (kind == kFilterAtoms)
     {
         out[1] = atoms.n_lit;
-        out[2] = atoms.n_atoms;
+        out[2] = atoms.n_terms;
         out[3] = atoms.start_lo;
         out[4] = atoms.start_hi;
-        for (int l = 0; l < atoms.n_lit; ++l)
-            for (int a = atoms.atom_begin[l]; a < atoms.atom_begin[l + 1]; ++a)
-            {
-                out[8 + a] = static_cast<int32_t>(atoms.splat[l] & 0xFF);
-                out[16 + a] = atoms.lo[a];
-                out[24 + a] = atoms.hi[a];
-            }
+        out[5] = atoms.n_atoms;
+        int group = 0;
+        for (int a = 0; a < atoms.n_terms; ++a)
+        {
+            out[8 + a] = static_cast<int32_t>(atoms.splat[atoms.term_lit[a]] & 0xFF);
+            out[24 + a] = atoms.term_lo[a];
+            out[40 + a] = atoms.term_hi[a];
+            out[56 + a] = group;
+            group += atoms.term_end[a];
+        }
     }
     return TRX_OK;
 }
