@@ -270,6 +270,62 @@ def run_ours(args):
         emit(line)
 
 
+def host_path_queries(t, ctx, residues, offs, rec_bin, reps=100):
+    """Writes the synthetic collection as 1024 FASTA files, builds a HIBF and a flat index with tetrex_b200/bin/tetrex
+    (K1), loads them through libtrxhost.so and times whole queries: regex -> k-graph -> collector (K2/K3 + path algebra on
+    the device, one host decision per rank of the graph) -> candidate bins -> K4 verify -> formatted lines."""
+    import shutil
+    import subprocess
+    import tempfile
+    from tetrex_b200 import sharded
+    tetrex = os.path.join(ROOT, "tetrex_b200", "bin", "tetrex")
+    d = tempfile.mkdtemp(prefix="trx_bench_")
+    res = {}
+    try:
+        raw = np.asarray(residues, dtype=np.uint8).tobytes()
+        o = [int(x) for x in offs]
+        files, r = [], 0
+        for b in range(N_BINS):
+            path = os.path.join(d, f"bin_{b:04d}.fa")
+            parts = []
+            while r < len(rec_bin) and rec_bin[r] == b:
+                parts.append(b">sp|S%07d|SYN_%d\n" % (r, b))
+                parts.append(raw[o[r]:o[r + 1]])
+                parts.append(b"\n")
+                r += 1
+            with open(path, "wb") as f:
+                f.write(b"".join(parts))
+            files.append(path)
+        lst = os.path.join(d, "bins.lst")
+        with open(lst, "w") as f:
+            f.write("\n".join(files) + "\n")
+        for name, flags in (("hibf", []), ("flat", ["-i"])):
+            t0 = time.perf_counter()
+            p = subprocess.run([tetrex, "index"] + flags + ["-k", str(K), os.path.join(d, name), lst], capture_output=True,
+                               text=True, timeout=600)
+            if p.returncode != 0:
+                raise RuntimeError(p.stderr[-300:])
+            build_s = time.perf_counter() - t0
+            ix = sharded.ShardedIndex(ctx, os.path.join(d, name + ".ibf"), 0, 1)
+            words, text = ix.query(QUERY)
+            lines = text.count("\n")
+            t0 = time.perf_counter()
+            for _ in range(reps):
+                w, st = ix.local_candidates(QUERY)
+            t1 = time.perf_counter()
+            for _ in range(reps):
+                ix.verify_local(w, QUERY)
+            t2 = time.perf_counter()
+            res[name] = {"queries_per_s": reps / (t2 - t0), "process_query_us": (t1 - t0) / reps * 1e6,
+                         "iter_disk_search_us": (t2 - t1) / reps * 1e6, "candidate_bins": int(np.bitwise_count(words).sum()),
+                         "lines": lines, "collector": st, "index_build_s_incl_process_start_and_fasta_parse": round(build_s, 2)}
+            ix.close()
+        res["query"] = QUERY
+        return res
+    finally:
+        shutil.rmtree(d, ignore_errors=True)
+
+
 def measure_c4_sharded_probe(t, ctx, torch, rank, world, barrier, max_over_ranks, n=1 << 21, steps=5):
     """K2 at the C4 shape (8192 bins x 22.83 M rows = 23.4 GB, h = 3, 3072 B read per k-mer): rank r holds the
     column block r of `world` (128/world words of every row), every rank probes the same n k-mers, so one k-mer is
@@ -480,6 +536,13 @@ def extra_measurements(t, ctx, torch, residues, offs, rec_bin, planted, hibf, pe
     out["regex_queries_per_s"] = reps / (time.perf_counter() - t0)
     out["regex_query"] = QUERY + " (filter on GPU via K3 + path AND/OR of its 6 k-mers on host words, verify via K4)"
     txt.close()
+
+    # ---- the same query through the reference-shaped host path (C++: process_query = k-graph + collector with the path
+    # algebra on the device, iter_disk_search = K4 + line formatting) on index files built by this repo's `tetrex index`
+    try:
+        out["host_path_queries"] = host_path_queries(t, ctx, residues, offs, rec_bin)
+    except Exception as e:  # never lose the bench line over a side measurement
+        out["host_path_queries"] = {"error": f"{type(e).__name__}: {e}"[:300]}
 
     # ---- K2 / K1 on the flat C3 shape: 1024 bins, bin_size from the reference's sizing rule
     lens = (offs[1:] - offs[:-1]).astype(np.int64)

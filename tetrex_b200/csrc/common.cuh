@@ -63,6 +63,9 @@ struct trx_ctx
     trx::scratch d_in[4];
     trx::scratch d_out[2];
     trx::scratch h_pin[2];
+    // h_pin[1] doubles as an arena for small index lists that kernels read straight from pinned host memory without a
+    // sync of their own (trx_paths_or); the offset goes back to 0 at every stream synchronisation of the path algebra
+    size_t pin_arena_off{0};
     int use() const; // cudaSetDevice
 };
 

@@ -13,6 +13,9 @@ static ibf_geom geom_of(trx_ibf const * f)
                     static_cast<uint32_t>(f->hash_shift), static_cast<uint32_t>(f->hash_funs), 0, f->bin_size};
 }
 
+// host-buffer entry points of the path algebra go zero-copy (pinned host memory read by the kernel) up to this many items
+constexpr uint64_t kZeroCopyItems = 4096;
+
 static int pow2_ceil(uint64_t x)
 {
     int g = 1;
@@ -517,6 +520,25 @@ int trx_paths_step(trx_ibf_t * f, trx_paths_t * p, const uint64_t * kmers, const
     TRX_TRY(check_slots(p, slots, n));
     trx_ctx * c = f->ctx;
     TRX_TRY(c->use());
+    if (n <= kZeroCopyItems)
+    {
+        // the collector's usual case — a handful of items per rank of the k-graph: the kernel reads k-mers and slots
+        // straight from pinned host memory and writes the alive bytes there; one launch + one sync instead of two
+        // staged uploads, a launch, a staged download and a sync (~35 us -> ~10 us per step)
+        c->h_pin[0].pinned_host = true;
+        TRX_TRY(c->h_pin[0].reserve(kZeroCopyItems * 13 + 64));
+        auto * base = static_cast<uint8_t *>(c->h_pin[0].ptr);
+        auto * h_kmers = reinterpret_cast<uint64_t *>(base);
+        auto * h_slots = reinterpret_cast<uint32_t *>(base + kZeroCopyItems * 8);
+        uint8_t * h_alive = base + kZeroCopyItems * 12;
+        memcpy(h_kmers, kmers, n * 8);
+        memcpy(h_slots, slots, n * 4);
+        TRX_TRY(launch_probe<1>(c, geom_of(f), h_kmers, n, p->d_words, h_slots, h_alive));
+        TRX_CUDA(cudaStreamSynchronize(c->stream));
+        c->pin_arena_off = 0;
+        memcpy(alive, h_alive, n);
+        return TRX_OK;
+    }
     TRX_TRY(c->d_in[0].reserve(n * 8));
     TRX_TRY(c->d_out[1].reserve(n));
     TRX_CUDA(cudaMemcpyAsync(c->d_in[0].ptr, kmers, n * 8, cudaMemcpyHostToDevice, c->stream));
@@ -539,6 +561,22 @@ int trx_paths_and_hits(trx_paths_t * p, const uint64_t * d_hits, const uint32_t 
     TRX_TRY(check_slots(p, slots, n));
     trx_ctx * c = p->ctx;
     TRX_TRY(c->use());
+    if (n <= kZeroCopyItems)
+    {
+        c->h_pin[0].pinned_host = true;
+        TRX_TRY(c->h_pin[0].reserve(kZeroCopyItems * 13 + 64));
+        auto * base = static_cast<uint8_t *>(c->h_pin[0].ptr);
+        auto * h_idx = reinterpret_cast<uint32_t *>(base);
+        auto * h_slots = reinterpret_cast<uint32_t *>(base + kZeroCopyItems * 8);
+        uint8_t * h_alive = base + kZeroCopyItems * 12;
+        memcpy(h_idx, hit_index, n * 4);
+        memcpy(h_slots, slots, n * 4);
+        TRX_TRY(paths_and_hits_launch(c, p->d_words, p->words_per_slot, d_hits, h_idx, h_slots, n, h_alive));
+        TRX_CUDA(cudaStreamSynchronize(c->stream));
+        c->pin_arena_off = 0;
+        memcpy(alive, h_alive, n);
+        return TRX_OK;
+    }
     uint32_t *d_idx = nullptr, *d_slots = nullptr;
     TRX_TRY(stage_u32(c, 0, hit_index, n, &d_idx));
     TRX_TRY(stage_u32(c, 1, slots, n, &d_slots));
@@ -561,8 +599,28 @@ int trx_paths_or(trx_paths_t * p, const uint32_t * dst, const uint32_t * src, ui
     trx_ctx * c = p->ctx;
     TRX_TRY(c->use());
     uint32_t *d_dst = nullptr, *d_src = nullptr;
-    TRX_TRY(stage_u32(c, 0, dst, n, &d_dst));
-    TRX_TRY(stage_u32(c, 1, src, n, &d_src));
+    if (n <= kZeroCopyItems)
+    {
+        // fire and forget: the lists go into the pinned arena and the kernel reads them from there whenever it runs
+        constexpr size_t kArenaBytes = 64 * kZeroCopyItems * 8;
+        c->h_pin[1].pinned_host = true;
+        TRX_TRY(c->h_pin[1].reserve(kArenaBytes));
+        if (c->pin_arena_off + n * 8 > kArenaBytes)
+        {
+            TRX_CUDA(cudaStreamSynchronize(c->stream)); // every earlier reader is done
+            c->pin_arena_off = 0;
+        }
+        d_dst = reinterpret_cast<uint32_t *>(static_cast<uint8_t *>(c->h_pin[1].ptr) + c->pin_arena_off);
+        d_src = d_dst + n;
+        memcpy(d_dst, dst, n * 4);
+        memcpy(d_src, src, n * 4);
+        c->pin_arena_off += (n * 8 + 15) & ~size_t{15};
+    }
+    else
+    {
+        TRX_TRY(stage_u32(c, 0, dst, n, &d_dst));
+        TRX_TRY(stage_u32(c, 1, src, n, &d_src));
+    }
     uint64_t const W = p->words_per_slot;
     int const G = pow2_ceil(W);
     auto go = [&](auto gtag) -> int
@@ -600,6 +658,7 @@ int trx_paths_read(trx_paths_t * p, uint64_t first, uint64_t n, uint64_t * out_w
     TRX_CUDA(cudaMemcpyAsync(out_words, p->d_words + first * p->words_per_slot, n * p->words_per_slot * 8,
                              cudaMemcpyDeviceToHost, p->ctx->stream));
     TRX_CUDA(cudaStreamSynchronize(p->ctx->stream));
+    p->ctx->pin_arena_off = 0;
     return TRX_OK;
 }
 

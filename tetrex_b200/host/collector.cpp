@@ -36,43 +36,51 @@ struct bucket
     std::unordered_map<uint64_t, uint32_t> by_key; // kmer & submask → index into items
 };
 
+// view of the index's persistent slot pool for one query
 struct slot_pool
 {
-    trx_paths_t * paths{nullptr};
-    uint64_t words{}, capacity{}, next{};
-    ~slot_pool() { trx_paths_destroy(paths); }
+    DeviceIndex::collector_scratch & sc;
+    explicit slot_pool(DeviceIndex::collector_scratch & s) : sc(s) {}
+    trx_paths_t * paths() const { return sc.paths; }
     uint32_t fresh()
     {
-        if (next >= capacity)
-            throw error("regular expression too complex: more than " + std::to_string(capacity) +
+        if (sc.used >= sc.capacity)
+            throw error("regular expression too complex: more than " + std::to_string(sc.capacity) +
                         " live paths (try a more specific query)");
-        return static_cast<uint32_t>(next++);
+        return static_cast<uint32_t>(sc.used++);
     }
 };
 
-// device scratch for the HIBF route (k-mers in, hit vectors out)
-struct dev_buffer
+// (re)creates the pool for slots of W words and hands it out all-zero
+void prepare_pool(DeviceIndex & index, uint64_t W)
 {
-    trx_ctx_t * ctx;
-    void * ptr{nullptr};
-    uint64_t bytes{0};
-    explicit dev_buffer(trx_ctx_t * c) : ctx(c) {}
-    ~dev_buffer()
+    DeviceIndex::collector_scratch & sc = index.scratch();
+    uint64_t const capacity = std::max<uint64_t>(1ull << 12, std::min<uint64_t>(1ull << 20, (1ull << 28) / (W * 8)));
+    if (!sc.paths || sc.words != W || sc.capacity != capacity)
     {
-        if (ptr)
-            trx_dev_free(ctx, ptr);
+        if (sc.paths)
+            trx_paths_destroy(sc.paths);
+        sc.paths = nullptr;
+        check(trx_paths_create(index.ctx(), W, capacity, &sc.paths)); // zeroed
+        sc.words = W;
+        sc.capacity = capacity;
     }
-    void reserve(uint64_t want)
-    {
-        if (want <= bytes)
-            return;
-        if (ptr)
-            check(trx_dev_free(ctx, ptr));
-        ptr = nullptr;
-        check(trx_dev_alloc(ctx, want + want / 2, &ptr));
-        bytes = want + want / 2;
-    }
-};
+    else if (sc.used)
+        check(trx_dev_memset(index.ctx(), trx_paths_device_words(sc.paths), 0, sc.used * W * 8));
+    sc.used = 0;
+}
+
+void reserve_dev(trx_ctx_t * ctx, void *& ptr, uint64_t & have, uint64_t want)
+{
+    if (want <= have)
+        return;
+    if (ptr)
+        check(trx_dev_free(ctx, ptr));
+    ptr = nullptr;
+    have = 0;
+    check(trx_dev_alloc(ctx, want + want / 2, &ptr));
+    have = want + want / 2;
+}
 
 } // namespace
 
@@ -95,13 +103,11 @@ bitvector collect(kgraph const & g, DeviceIndex & index, collect_stats * stats, 
     for (unsigned i = 0; i + 1 < k; ++i)
         submask = (submask << bits) | ((1ull << bits) - 1);
 
-    slot_pool pool;
-    pool.words = W;
-    pool.capacity = std::max<uint64_t>(1ull << 12, std::min<uint64_t>(1ull << 20, (1ull << 28) / (W * 8)));
-    check(trx_paths_create(index.ctx(), W, pool.capacity, &pool.paths));
+    prepare_pool(index, W);
+    slot_pool pool(index.scratch());
     uint32_t const match_slot = pool.fresh(); // path_matrix = bitvector(bins): all clear (pool is zeroed)
     uint32_t const start_slot = pool.fresh();
-    check(trx_paths_fill(pool.paths, start_slot, 1, bins)); // hit_vector = bitvector(bins, true)
+    check(trx_paths_fill(pool.paths(), start_slot, 1, bins)); // hit_vector = bitvector(bins, true)
 
     std::vector<bucket> table(n_nodes);
     std::vector<int> node_of_rank(n_nodes, -1);
@@ -133,7 +139,7 @@ bitvector collect(kgraph const & g, DeviceIndex & index, collect_stats * stats, 
 
     push(0, item{0, 0, start_slot}, true);
 
-    dev_buffer d_kmers(index.ctx()), d_hits(index.ctx());
+    DeviceIndex::collector_scratch & sc = index.scratch();
     std::vector<uint64_t> probe_kmers;
     std::vector<uint32_t> probe_slots, probe_item;
     std::vector<uint8_t> alive;
@@ -205,21 +211,21 @@ bitvector collect(kgraph const & g, DeviceIndex & index, collect_stats * stats, 
                 std::vector<uint8_t> res(probe_kmers.size());
                 if (!index.is_hibf())
                 {
-                    check(trx_paths_step(index.flat(), pool.paths, probe_kmers.data(), probe_slots.data(),
+                    check(trx_paths_step(index.flat(), pool.paths(), probe_kmers.data(), probe_slots.data(),
                                          probe_kmers.size(), res.data()));
                 }
                 else
                 {
                     uint64_t const n = probe_kmers.size();
-                    d_kmers.reserve(n * 8);
-                    d_hits.reserve(n * W * 8);
-                    check(trx_copy_h2d(index.ctx(), d_kmers.ptr, probe_kmers.data(), n * 8));
-                    check(trx_hibf_membership_dev(index.hibf(), static_cast<uint64_t *>(d_kmers.ptr), n,
-                                                  static_cast<uint64_t *>(d_hits.ptr), nullptr));
+                    reserve_dev(index.ctx(), sc.d_kmers, sc.kmers_bytes, n * 8);
+                    reserve_dev(index.ctx(), sc.d_hits, sc.hits_bytes, n * W * 8);
+                    check(trx_copy_h2d(index.ctx(), sc.d_kmers, probe_kmers.data(), n * 8));
+                    check(trx_hibf_membership_dev(index.hibf(), static_cast<uint64_t *>(sc.d_kmers), n,
+                                                  static_cast<uint64_t *>(sc.d_hits), nullptr));
                     std::vector<uint32_t> idx(n);
                     for (uint64_t i = 0; i < n; ++i)
                         idx[i] = static_cast<uint32_t>(i);
-                    check(trx_paths_and_hits(pool.paths, static_cast<uint64_t *>(d_hits.ptr), idx.data(),
+                    check(trx_paths_and_hits(pool.paths(), static_cast<uint64_t *>(sc.d_hits), idx.data(),
                                              probe_slots.data(), n, res.data()));
                 }
                 if (sharded)
@@ -234,12 +240,12 @@ bitvector collect(kgraph const & g, DeviceIndex & index, collect_stats * stats, 
                     push(g.first[node], b.items[i], true);
         }
         if (!or_dst.empty())
-            check(trx_paths_or(pool.paths, or_dst.data(), or_src.data(), or_dst.size()));
+            check(trx_paths_or(pool.paths(), or_dst.data(), or_src.data(), or_dst.size()));
         b.items.clear();
         b.by_key.clear();
     }
     bitvector out(index.bin_words(), 0);
-    check(trx_paths_read(pool.paths, match_slot, 1, out.data() + word_begin));
+    check(trx_paths_read(pool.paths(), match_slot, 1, out.data() + word_begin));
     return out;
 }
 

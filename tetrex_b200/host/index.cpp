@@ -27,6 +27,12 @@ DeviceIndex::~DeviceIndex()
 {
     if (text_ && text_->text)
         trx_text_destroy(text_->text);
+    if (scratch_.paths)
+        trx_paths_destroy(scratch_.paths);
+    if (scratch_.d_kmers)
+        trx_dev_free(ctx_, scratch_.d_kmers);
+    if (scratch_.d_hits)
+        trx_dev_free(ctx_, scratch_.d_hits);
     if (flat_)
         trx_ibf_destroy(flat_);
     if (hibf_)

@@ -199,6 +199,19 @@ public:
     };
     text_store const & text();
 
+    // Device scratch of the collector, kept between queries: the path-slot pool (cudaMalloc + cudaFree of up to
+    // 128 MB per query cost 0.6 ms — more than the whole walk) and the k-mer / hit-vector buffers of the HIBF route.
+    // `used` slots of the previous query are zeroed when the next one starts.
+    struct collector_scratch
+    {
+        trx_paths_t * paths{nullptr};
+        uint64_t words{}, capacity{}, used{};
+        void * d_kmers{nullptr};
+        void * d_hits{nullptr};
+        uint64_t kmers_bytes{}, hits_bytes{};
+    };
+    collector_scratch & scratch() { return scratch_; }
+
 private:
     void upload();
     void init_maps();
@@ -210,6 +223,7 @@ private:
     uint8_t aamap_[256]{}, redmap_[256]{};
     uint64_t seq_count_{};
     std::unique_ptr<text_store> text_;
+    collector_scratch scratch_;
 };
 
 // ------------------------------------------------------------------------------------------ query path
