@@ -352,13 +352,17 @@ def test_hibf_synthetic_shapes(ctx, case, monkeypatch):
     assert all((int(hits[j][u >> 6]) >> (u & 63)) & 1 for j, u in enumerate(some))
     if ob.have_ref() and case["n_user"] <= 4000:
         assert np.array_equal(ob.RefHIBF.from_tables(tb).membership(query[:500], 1), want[:500])  # the reference's own recursion
-    for fused in ("on", "off"):
-        monkeypatch.setenv("TRX_HIBF_FUSED", fused)
+    for fused in ("on", "off", "auto"):
+        if fused == "auto":  # default: batches of <= 2048 k-mers take the unsorted frontier route, larger ones the windowed one
+            monkeypatch.delenv("TRX_HIBF_FUSED")
+        else:
+            monkeypatch.setenv("TRX_HIBF_FUSED", fused)
         h = t.HIBF.from_tables(ctx, tb)
         got, st = h.membership(query, stats=True)
         assert np.array_equal(got, want), (case, fused)
         assert st[1] == 3
         one = h.membership(query[:1])  # a single k-mer (collector batches are tiny)
         assert np.array_equal(one, want[:1])
+        for m in (7, 2048, 2049):
+            assert np.array_equal(h.membership(query[:m]), want[:m]), (case, fused, m)
         h.close()
-    monkeypatch.delenv("TRX_HIBF_FUSED")

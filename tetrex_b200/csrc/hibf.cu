@@ -535,6 +535,8 @@ struct trx_hibf
     int ibf_bits{1}; // bits needed for an IBF id (radix-sort range)
     bool sort_frontier{true};
     bool fused{true};        // root + second level in one kernel (TRX_HIBF_FUSED=off → frontier kernels only)
+    uint64_t small_batch{2048}; // up to this many k-mers a pass takes the unsorted frontier route: 3 launches instead of the
+                                // windowed schedule's ~12 (collector batches are a handful of k-mers); 0 when TRX_HIBF_FUSED is set
     int uniform_hash_funs{0}; // > 0 if every IBF uses the same number of hash functions
     uint64_t root_bin_words{1};
     trx::scratch root_words; // merged-bin hits of the root per k-mer
@@ -717,6 +719,8 @@ int trx_hibf_upload(trx_ctx_t * ctx, const trx_hibf_desc * desc, trx_hibf_t ** o
         h->sort_frontier = !(e && strcmp(e, "off") == 0);
         e = getenv("TRX_HIBF_FUSED"); // TRX_HIBF_FUSED=off: frontier kernels for every level (A/B evidence)
         h->fused = !(e && strcmp(e, "off") == 0) && depth >= 2;
+        if (e)
+            h->small_batch = 0; // an explicit route request is honoured for every batch size
         if ((e = getenv("TRX_HIBF_CTAS")) && atoi(e) > 0)
             h->window_ctas = static_cast<unsigned>(atoi(e));
         h->fast_shape = true;
@@ -859,7 +863,9 @@ uint64_t trx_hibf_user_bin_words(const trx_hibf_t * h)
 static int run_chunk(trx_hibf * h, uint64_t const * d_kmers, uint64_t n, uint64_t * d_out, uint64_t * visited)
 {
     trx_ctx * c = h->ctx;
-    bool const need_frontier = !h->fused || h->depth > 2;
+    bool const small = n <= h->small_batch;
+    bool const fused = h->fused && !small, sort_frontier = h->sort_frontier && !small;
+    bool const need_frontier = !fused || h->depth > 2;
     uint64_t const capacity = need_frontier ? kFanoutBudget * (n < 4096 ? 4096 : n) : 0;
     if (need_frontier)
     {
@@ -870,7 +876,7 @@ static int run_chunk(trx_hibf * h, uint64_t const * d_kmers, uint64_t n, uint64_
     auto * ctr = static_cast<unsigned long long *>(h->counters.ptr);
     TRX_CUDA(cudaMemsetAsync(ctr, 0, (kMaxLevels + 3) * 8, c->stream));
     int first_level = 1; // first level that still has to run through the frontier kernels
-    if (h->fused)
+    if (fused)
     {
         auto * fr = static_cast<uint64_t *>(h->frontier[0].ptr);
         int const key = h->uniform_hash_funs * 2 + (h->fast_shape ? 1 : 0);
@@ -899,7 +905,7 @@ static int run_chunk(trx_hibf * h, uint64_t const * d_kmers, uint64_t n, uint64_
     int cur = 0;
     for (int level = first_level; level < h->depth; ++level)
     {
-        if (h->sort_frontier)
+        if (sort_frontier)
         {
             // Group the frontier by IBF id (high word of an item) so that the probes of one lower-level IBF
             // (a few MB) run together and hit L2 instead of spreading 3 random 64-byte DRAM fetches per item
