@@ -396,6 +396,8 @@ void complement_table(uint8_t tab[256])
         tab[static_cast<uint8_t>(from[i])] = static_cast<uint8_t>(to[i]);
 }
 
+constexpr double kDefaultMaxPass = 1e-3;
+
 struct bits128
 {
     uint64_t w[2]{0, 0};
@@ -407,6 +409,20 @@ struct bits128
 // L_{j+1} = Follow(L_j); every match has a byte of class(L_j) at offset j as long as no shorter match exists.
 // Offsets whose class is a single raw byte are literals; the best window of 4 consecutive offsets (by the
 // text's measured byte frequencies) becomes the filter.  n_a = n_b = 0 if nothing selective enough exists.
+// A prefilter whose expected pass rate (fraction of text positions it lets through) exceeds this is not used: phase 2
+// would then visit most chunks anyway and the exact automaton kernel is the better phase 1.  TRX_FILTER_MAX_PASS
+// overrides the measured default.
+double max_pass_rate()
+{
+    static double const v = []
+    {
+        char const * e = getenv("TRX_FILTER_MAX_PASS");
+        double x = e ? atof(e) : kDefaultMaxPass;
+        return x > 0 ? x : kDefaultMaxPass;
+    }();
+    return v;
+}
+
 filter_spec derive_filter(regex_dev const & img, double const * freq, bool reverse, double * pass_out)
 {
     filter_spec fs{};
@@ -443,7 +459,8 @@ filter_spec derive_filter(regex_dev const & img, double const * freq, bool rever
         L = next;
     }
     // best window of 8 consecutive offsets: take literals rarest-first until the expected candidate rate is low
-    constexpr double kGoodEnough = 2e-5, kTooWeak = 1e-3;
+    constexpr double kGoodEnough = 2e-5;
+    double const kTooWeak = max_pass_rate();
     double best = 1.0;
     int best_a = -1;
     uint32_t best_mask = 0;
@@ -893,7 +910,7 @@ filter_kind choose_filter(regex_dev const & img, double const * freq, bool rever
     if (!only_window && !(have_window && window_pass <= 1e-4))
     {
         atom_plan plan = derive_atoms(img, freq, reverse);
-        if (plan.spec.n_lit >= 1 && (only_atoms || (plan.pass <= 1e-3 && (!have_window || plan.pass < 0.25 * window_pass))))
+        if (plan.spec.n_lit >= 1 && (only_atoms || (plan.pass <= max_pass_rate() && (!have_window || plan.pass < 0.25 * window_pass))))
         {
             atoms = plan.spec;
             return kFilterAtoms;
