@@ -217,8 +217,9 @@ int trx_regex_scan(trx_text_t *text, trx_regex_t *re, const uint64_t *candidate_
 /* The same scan in two halves, for batches of queries (run_multiple_queries, include/query.h:330-340, loops over a
  * file of regexes): _begin plans and enqueues everything on the context's stream and returns a ticket at once, _end
  * waits for that scan and delivers its hits exactly as trx_regex_scan does (which is _begin + _end).  Up to
- * TRX_SCAN_SLOTS scans of one text may be in flight; their kernels run back to back on the device while the host is
- * already planning the next one — the ~50 us of per-call latency (plan, launches, read-back, sync) is paid once per
+ * TRX_SCAN_SLOTS scans of one text may be in flight, each on a stream of its own (NOT the context's stream: order
+ * other work against a scan through _end); their kernels run back to back on the device while the host is already
+ * planning the next one — the ~50 us of per-call latency (plan, launches, read-back, sync) is paid once per
  * batch instead of once per regex.  A further _begin with every slot taken returns TRX_ECAPACITY.  The regex handle and
  * the candidate / map arrays are only read during _begin.  Tickets may be ended in any order. */
 #define TRX_SCAN_SLOTS 4

@@ -20,7 +20,7 @@ hits = 0
 for r, k in zip(regs, kinds):
     t1 = time.perf_counter(); hits += len(txt.scan(r)); per[k] += time.perf_counter() - t1
 dt = time.perf_counter() - t0
-t0 = time.perf_counter(); piped = txt.scan_many(regs, cap=1 << 20, depth=3); dtp = time.perf_counter() - t0
+t0 = time.perf_counter(); piped = txt.scan_many(regs, cap=1 << 20, depth=int(os.environ.get("DEPTH", 3))); dtp = time.perf_counter() - t0
 cnt = {k: kinds.count(k) for k in per}
 print(f"max_pass={os.environ.get('TRX_FILTER_MAX_PASS', 'default')}: census {cnt}  sequential {len(pats)/dt:7.0f} scans/s  pipelined {len(pats)/dtp:7.0f} scans/s  "
       f"mean us: " + ", ".join(f"{k} {per[k]/max(cnt[k],1)*1e6:.0f}" for k in per) + f"  hits {hits} / {sum(len(h) for h in piped)}")

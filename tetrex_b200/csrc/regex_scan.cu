@@ -34,7 +34,9 @@ struct trx_text
         uint32_t * d_rec_flags{nullptr};   // bitmap
         uint8_t * d_counters{nullptr};     // hit count (u64), listed-record count (u32), next tile (u32)
         uint32_t * d_rec_list{nullptr};
-        trx::scratch d_stage, h_stage, h_small, d_keys, d_ends;
+        trx::scratch d_stage, h_stage, h_small, d_keys, d_ends, d_tiles;
+        uint64_t tiles_serial{0};          // plan_serial of the tile list in d_tiles
+        cudaStream_t stream{nullptr};      // a stream per slot: the copies and the clear of one scan overlap the kernels of another
         cudaEvent_t done{nullptr};
         bool busy{false};
         uint64_t cap{}, residues{}, filter_units{};
@@ -56,6 +58,7 @@ struct trx_text
     std::vector<uint32_t> plan_tiles;
     uint64_t plan_residues{};
     bool plan_valid{false};
+    uint64_t plan_serial{0};           // bumped whenever plan_tiles changes
     // phase-1 choice per (regex, strand, byte map, TRX_REGEX_FILTER): derived from the automaton once, not per scan
     struct cached_choice
     {
@@ -66,7 +69,7 @@ struct trx_text
     };
     std::vector<cached_choice> choices;
     // per-scan scratch
-    trx::scratch d_tiles, d_keys2, d_ends2, d_sort_tmp;
+    trx::scratch d_keys2, d_ends2, d_sort_tmp;
 };
 
 using namespace trx;
@@ -178,6 +181,7 @@ int trx_text_upload(trx_ctx_t * ctx, const uint8_t * residues, const uint64_t * 
             sl.d_counters = sl.d_block + flag_bytes;
             if ((e = cudaMalloc(&sl.d_rec_list, n_records * 4)) != cudaSuccess) return fail(e);
             if ((e = cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming)) != cudaSuccess) return fail(e);
+            if ((e = cudaStreamCreateWithFlags(&sl.stream, cudaStreamNonBlocking)) != cudaSuccess) return fail(e);
         }
     }
     if ((e = cudaMemsetAsync(t->d_text + (t->n_text_padded - kTileBytes), 0, kTileBytes, ctx->stream)) != cudaSuccess) return fail(e);
@@ -225,12 +229,17 @@ void trx_text_destroy(trx_text_t * t)
     {
         cudaFree(sl.d_block);
         cudaFree(sl.d_rec_list);
+        if (sl.stream)
+        {
+            cudaStreamSynchronize(sl.stream);
+            cudaStreamDestroy(sl.stream);
+        }
         if (sl.done)
             cudaEventDestroy(sl.done);
-        for (trx::scratch * s : {&sl.d_stage, &sl.h_stage, &sl.h_small, &sl.d_keys, &sl.d_ends})
+        for (trx::scratch * s : {&sl.d_stage, &sl.h_stage, &sl.h_small, &sl.d_keys, &sl.d_ends, &sl.d_tiles})
             s->release();
     }
-    for (trx::scratch * s : {&t->d_tiles, &t->d_keys2, &t->d_ends2, &t->d_sort_tmp})
+    for (trx::scratch * s : {&t->d_keys2, &t->d_ends2, &t->d_sort_tmp})
         s->release();
     delete t;
 }
@@ -241,7 +250,7 @@ namespace
 {
 
 template <int W, int DIR, bool USE_TMA>
-int launch_phase1(trx_ctx * c, scan_params const & sp, CUtensorMap const & tmap)
+int launch_phase1(trx_ctx * c, cudaStream_t st, scan_params const & sp, CUtensorMap const & tmap)
 {
     size_t smem = (USE_TMA ? kStages * kTileBytes : 0) + sizeof(scan_tables<W>) + 2 * sizeof(uint64_t);
     auto kern = regex_scan_phase1<W, DIR, USE_TMA>;
@@ -254,18 +263,18 @@ int launch_phase1(trx_ctx * c, scan_params const & sp, CUtensorMap const & tmap)
         per_sm = q < 1 ? 1 : q;
     }
     unsigned grid = static_cast<unsigned>(std::min<uint64_t>(sp.n_tiles, static_cast<uint64_t>(c->sm_count) * per_sm));
-    kern<<<grid, kScanThreads, smem, c->stream>>>(sp, tmap);
+    kern<<<grid, kScanThreads, smem, st>>>(sp, tmap);
     ++c->launches;
     TRX_CUDA(cudaGetLastError());
     return TRX_OK;
 }
 
 template <int W>
-int launch_phase1_w(trx_ctx * c, scan_params const & sp, CUtensorMap const & tmap, bool reverse, bool use_tma)
+int launch_phase1_w(trx_ctx * c, cudaStream_t st, scan_params const & sp, CUtensorMap const & tmap, bool reverse, bool use_tma)
 {
     if (reverse)
-        return use_tma ? launch_phase1<W, -1, true>(c, sp, tmap) : launch_phase1<W, -1, false>(c, sp, tmap);
-    return use_tma ? launch_phase1<W, 1, true>(c, sp, tmap) : launch_phase1<W, 1, false>(c, sp, tmap);
+        return use_tma ? launch_phase1<W, -1, true>(c, st, sp, tmap) : launch_phase1<W, -1, false>(c, st, sp, tmap);
+    return use_tma ? launch_phase1<W, 1, true>(c, st, sp, tmap) : launch_phase1<W, 1, false>(c, st, sp, tmap);
 }
 
 // threads per 128-byte text row in the prefilter kernels (TRX_FILTER_SPLIT = 1 | 2; 1 was measured 2-8 % faster).
@@ -282,7 +291,7 @@ int filter_split()
 }
 
 template <int NA, int NB, int STAGES, int SPLIT>
-int launch_filter_s(trx_ctx * c, scan_params const & sp, CUtensorMap const & tmap)
+int launch_filter_s(trx_ctx * c, cudaStream_t st, scan_params const & sp, CUtensorMap const & tmap)
 {
     constexpr int kThreads = kScanThreads * SPLIT + 32; // + the producer warp
     size_t smem = tile_ring<STAGES, kScanThreads * SPLIT>::kRingBytes;
@@ -296,45 +305,45 @@ int launch_filter_s(trx_ctx * c, scan_params const & sp, CUtensorMap const & tma
         per_sm = q < 1 ? 1 : q;
     }
     unsigned grid = static_cast<unsigned>(std::min<uint64_t>(sp.n_tiles, static_cast<uint64_t>(c->sm_count) * per_sm));
-    kern<<<grid, kThreads, smem, c->stream>>>(sp, tmap);
+    kern<<<grid, kThreads, smem, st>>>(sp, tmap);
     ++c->launches;
     TRX_CUDA(cudaGetLastError());
     return TRX_OK;
 }
 
 template <int NA, int NB>
-int launch_filter(trx_ctx * c, scan_params const & sp, CUtensorMap const & tmap)
+int launch_filter(trx_ctx * c, cudaStream_t st, scan_params const & sp, CUtensorMap const & tmap)
 {
-    return filter_split() == 1 ? launch_filter_s<NA, NB, 2, 1>(c, sp, tmap) : launch_filter_s<NA, NB, 2, 2>(c, sp, tmap);
+    return filter_split() == 1 ? launch_filter_s<NA, NB, 2, 1>(c, st, sp, tmap) : launch_filter_s<NA, NB, 2, 2>(c, st, sp, tmap);
 }
 
 template <int NA>
-int launch_filter_a(trx_ctx * c, scan_params const & sp, CUtensorMap const & tmap)
+int launch_filter_a(trx_ctx * c, cudaStream_t st, scan_params const & sp, CUtensorMap const & tmap)
 {
     switch (sp.filter.n_b)
     {
-    case 0: return launch_filter<NA, 0>(c, sp, tmap);
-    case 1: return launch_filter<NA, 1>(c, sp, tmap);
-    case 2: return launch_filter<NA, 2>(c, sp, tmap);
-    case 3: return launch_filter<NA, 3>(c, sp, tmap);
-    default: return launch_filter<NA, 4>(c, sp, tmap);
+    case 0: return launch_filter<NA, 0>(c, st, sp, tmap);
+    case 1: return launch_filter<NA, 1>(c, st, sp, tmap);
+    case 2: return launch_filter<NA, 2>(c, st, sp, tmap);
+    case 3: return launch_filter<NA, 3>(c, st, sp, tmap);
+    default: return launch_filter<NA, 4>(c, st, sp, tmap);
     }
 }
 
-int launch_filter_any(trx_ctx * c, scan_params const & sp, CUtensorMap const & tmap)
+int launch_filter_any(trx_ctx * c, cudaStream_t st, scan_params const & sp, CUtensorMap const & tmap)
 {
     switch (sp.filter.n_a)
     {
-    case 0: return launch_filter_a<0>(c, sp, tmap);
-    case 1: return launch_filter_a<1>(c, sp, tmap);
-    case 2: return launch_filter_a<2>(c, sp, tmap);
-    case 3: return launch_filter_a<3>(c, sp, tmap);
-    default: return launch_filter_a<4>(c, sp, tmap);
+    case 0: return launch_filter_a<0>(c, st, sp, tmap);
+    case 1: return launch_filter_a<1>(c, st, sp, tmap);
+    case 2: return launch_filter_a<2>(c, st, sp, tmap);
+    case 3: return launch_filter_a<3>(c, st, sp, tmap);
+    default: return launch_filter_a<4>(c, st, sp, tmap);
     }
 }
 
 template <int NLIT, int STAGES, int SPLIT>
-int launch_atoms_s(trx_ctx * c, scan_params const & sp, CUtensorMap const & tmap)
+int launch_atoms_s(trx_ctx * c, cudaStream_t st, scan_params const & sp, CUtensorMap const & tmap)
 {
     constexpr int kThreads = kScanThreads * SPLIT + 32; // + the producer warp
     size_t smem = ((tile_ring<STAGES, kScanThreads * SPLIT>::kRingBytes + 15) & ~15) +
@@ -349,37 +358,37 @@ int launch_atoms_s(trx_ctx * c, scan_params const & sp, CUtensorMap const & tmap
         per_sm = q < 1 ? 1 : q;
     }
     unsigned grid = static_cast<unsigned>(std::min<uint64_t>(sp.n_tiles, static_cast<uint64_t>(c->sm_count) * per_sm));
-    kern<<<grid, kThreads, smem, c->stream>>>(sp, tmap);
+    kern<<<grid, kThreads, smem, st>>>(sp, tmap);
     ++c->launches;
     TRX_CUDA(cudaGetLastError());
     return TRX_OK;
 }
 
 template <int NLIT>
-int launch_atoms(trx_ctx * c, scan_params const & sp, CUtensorMap const & tmap)
+int launch_atoms(trx_ctx * c, cudaStream_t st, scan_params const & sp, CUtensorMap const & tmap)
 {
-    return filter_split() == 1 ? launch_atoms_s<NLIT, 2, 1>(c, sp, tmap) : launch_atoms_s<NLIT, 2, 2>(c, sp, tmap);
+    return filter_split() == 1 ? launch_atoms_s<NLIT, 2, 1>(c, st, sp, tmap) : launch_atoms_s<NLIT, 2, 2>(c, st, sp, tmap);
 }
 
-int launch_atoms_any(trx_ctx * c, scan_params const & sp, CUtensorMap const & tmap)
+int launch_atoms_any(trx_ctx * c, cudaStream_t st, scan_params const & sp, CUtensorMap const & tmap)
 {
     switch (sp.atoms.n_lit)
     {
-    case 1: return launch_atoms<1>(c, sp, tmap);
-    case 2: return launch_atoms<2>(c, sp, tmap);
-    case 3: return launch_atoms<3>(c, sp, tmap);
-    default: return launch_atoms<4>(c, sp, tmap);
+    case 1: return launch_atoms<1>(c, st, sp, tmap);
+    case 2: return launch_atoms<2>(c, st, sp, tmap);
+    case 3: return launch_atoms<3>(c, st, sp, tmap);
+    default: return launch_atoms<4>(c, st, sp, tmap);
     }
 }
 
 template <int W>
-int launch_phase2_w(trx_ctx * c, resolve_params const & rp, bool reverse)
+int launch_phase2_w(trx_ctx * c, cudaStream_t st, resolve_params const & rp, bool reverse)
 {
     unsigned grid = static_cast<unsigned>(c->sm_count) * 4;
     if (reverse)
-        regex_scan_phase2<W, -1><<<grid, 128, 0, c->stream>>>(rp);
+        regex_scan_phase2<W, -1><<<grid, 128, 0, st>>>(rp);
     else
-        regex_scan_phase2<W, 1><<<grid, 128, 0, c->stream>>>(rp);
+        regex_scan_phase2<W, 1><<<grid, 128, 0, st>>>(rp);
     ++c->launches;
     TRX_CUDA(cudaGetLastError());
     return TRX_OK;
@@ -945,6 +954,7 @@ int trx_regex_scan_begin(trx_text_t * t, trx_regex_t * re, const uint64_t * cand
         return set_error(TRX_ECAPACITY, "trx_regex_scan_begin: %d scans already in flight on this text (call trx_regex_scan_end)",
                          trx_text::kScanSlots);
     trx_text::scan_slot & sl = t->slots[slot_index];
+    cudaStream_t const st = sl.stream;
     sl.cap = cap;
     sl.residues = 0;
     sl.filter_units = 0;
@@ -958,7 +968,7 @@ int trx_regex_scan_begin(trx_text_t * t, trx_regex_t * re, const uint64_t * cand
                          re->follow_list.size(), sizeof(regex_dev::follow_list));
 
     // the clear of flags and counters does not depend on anything below: let it run while the host plans
-    TRX_CUDA(cudaMemsetAsync(sl.d_block, 0, t->clear_bytes, c->stream));
+    TRX_CUDA(cudaMemsetAsync(sl.d_block, 0, t->clear_bytes, st));
 
     // ---- plan: candidate bins → tiles of the text
     uint64_t const cand_words = (t->n_bins + 63) / 64;
@@ -986,14 +996,17 @@ int trx_regex_scan_begin(trx_text_t * t, trx_regex_t * re, const uint64_t * cand
                     tl.push_back(static_cast<uint32_t>(tile));
         }
         t->plan_residues = residues;
-        if (!tl.empty())
-        {
-            // pageable source: the copy is staged by the driver before the call returns, the vector may change afterwards
-            TRX_TRY(t->d_tiles.reserve(tl.size() * 4));
-            TRX_CUDA(cudaMemcpyAsync(t->d_tiles.ptr, tl.data(), tl.size() * 4, cudaMemcpyHostToDevice, c->stream));
-        }
+        ++t->plan_serial;
         t->plan_valid = true;
     }
+    if (sl.tiles_serial != t->plan_serial && !t->plan_tiles.empty())
+    {
+        // every slot keeps its own device copy of the tile list (a scan in flight on another slot may still read the old one);
+        // pageable source: the copy is staged by the driver before the call returns
+        TRX_TRY(sl.d_tiles.reserve(t->plan_tiles.size() * 4));
+        TRX_CUDA(cudaMemcpyAsync(sl.d_tiles.ptr, t->plan_tiles.data(), t->plan_tiles.size() * 4, cudaMemcpyHostToDevice, st));
+    }
+    sl.tiles_serial = t->plan_serial;
     std::vector<uint32_t> const & tiles = t->plan_tiles;
     sl.residues = t->plan_residues;
     // even an empty plan goes through the whole protocol (the memset above left the slot's counters at zero)
@@ -1019,7 +1032,7 @@ int trx_regex_scan_begin(trx_text_t * t, trx_regex_t * re, const uint64_t * cand
     TRX_TRY(sl.d_keys.reserve(dev_cap * 8));
     TRX_TRY(sl.d_ends.reserve(dev_cap * 4));
     auto * ds = static_cast<uint8_t *>(sl.d_stage.ptr);
-    TRX_CUDA(cudaMemcpyAsync(ds, hs, stage_bytes, cudaMemcpyHostToDevice, c->stream));
+    TRX_CUDA(cudaMemcpyAsync(ds, hs, stage_bytes, cudaMemcpyHostToDevice, st));
     scan_params sp{};
     sp.text = t->d_text;
     sp.n_text = t->n_text;
@@ -1028,7 +1041,7 @@ int trx_regex_scan_begin(trx_text_t * t, trx_regex_t * re, const uint64_t * cand
     sp.rec_bin = t->d_rec_bin;
     sp.n_records = t->n_records;
     sp.cand_words = reinterpret_cast<uint64_t *>(ds + off_cand);
-    sp.tiles = static_cast<uint32_t *>(t->d_tiles.ptr);
+    sp.tiles = static_cast<uint32_t *>(sl.d_tiles.ptr);
     sp.n_tiles = static_cast<uint32_t>(tiles.size());
     sp.chunk_flags = sl.d_chunk_flags;
     sp.rec_flags = sl.d_rec_flags;
@@ -1082,13 +1095,13 @@ int trx_regex_scan_begin(trx_text_t * t, trx_regex_t * re, const uint64_t * cand
     if (tiles.empty())
         ; // nothing to scan: no kernel, the read-back below returns the zeroed counters
     else if (use_atoms)
-        TRX_TRY(launch_atoms_any(c, sp, t->tmap));
+        TRX_TRY(launch_atoms_any(c, st, sp, t->tmap));
     else if (use_window)
-        TRX_TRY(launch_filter_any(c, sp, t->tmap));
+        TRX_TRY(launch_filter_any(c, st, sp, t->tmap));
     else if (re->words == 1)
-        TRX_TRY(launch_phase1_w<1>(c, sp, t->tmap, reverse, use_tma));
+        TRX_TRY(launch_phase1_w<1>(c, st, sp, t->tmap, reverse, use_tma));
     else
-        TRX_TRY(launch_phase1_w<2>(c, sp, t->tmap, reverse, use_tma));
+        TRX_TRY(launch_phase1_w<2>(c, st, sp, t->tmap, reverse, use_tma));
 
     resolve_params rp{};
     rp.text = t->d_text;
@@ -1106,17 +1119,17 @@ int trx_regex_scan_begin(trx_text_t * t, trx_regex_t * re, const uint64_t * cand
     if (tiles.empty())
         ;
     else if (re->words == 1)
-        TRX_TRY(launch_phase2_w<1>(c, rp, reverse));
+        TRX_TRY(launch_phase2_w<1>(c, st, rp, reverse));
     else
-        TRX_TRY(launch_phase2_w<2>(c, rp, reverse));
+        TRX_TRY(launch_phase2_w<2>(c, st, rp, reverse));
 
     // ---- read back: the counters and the first kSmallHits hits in ONE copy
     constexpr uint64_t kSmall = kSmallHits;
     sl.h_small.pinned_host = true;
     TRX_TRY(sl.h_small.reserve(16 + kSmall * 12));
     auto * h_total = static_cast<unsigned long long *>(sl.h_small.ptr);
-    TRX_CUDA(cudaMemcpyAsync(h_total, sl.d_counters, 16 + kSmall * 12, cudaMemcpyDeviceToHost, c->stream));
-    TRX_CUDA(cudaEventRecord(sl.done, c->stream));
+    TRX_CUDA(cudaMemcpyAsync(h_total, sl.d_counters, 16 + kSmall * 12, cudaMemcpyDeviceToHost, st));
+    TRX_CUDA(cudaEventRecord(sl.done, st));
     sl.busy = true;
     *ticket = slot_index;
     if (trace)
@@ -1138,6 +1151,7 @@ int trx_regex_scan_end(trx_text_t * t, int ticket, trx_hit * hits, uint64_t * n_
         return set_error(TRX_EINVAL, "trx_regex_scan_end: hits is NULL");
     trx_ctx * c = t->ctx;
     TRX_TRY(c->use());
+    cudaStream_t const st = sl.stream;
     *n_hits = 0;
     if (stats)
     {
@@ -1179,24 +1193,24 @@ int trx_regex_scan_end(trx_text_t * t, int ticket, trx_hit * hits, uint64_t * n_
 
     // ---- order = (bin, record, start): records are grouped by ascending bin, so (record, start) suffices
     uint64_t const n = total;
-    TRX_CUDA(cudaMemcpyAsync(d_hit_keys, d_small_keys, kSmall * 8, cudaMemcpyDeviceToDevice, c->stream));
-    TRX_CUDA(cudaMemcpyAsync(d_hit_ends, d_small_ends, kSmall * 4, cudaMemcpyDeviceToDevice, c->stream));
+    TRX_CUDA(cudaMemcpyAsync(d_hit_keys, d_small_keys, kSmall * 8, cudaMemcpyDeviceToDevice, st));
+    TRX_CUDA(cudaMemcpyAsync(d_hit_ends, d_small_ends, kSmall * 4, cudaMemcpyDeviceToDevice, st));
     TRX_TRY(t->d_keys2.reserve(n * 8));
     TRX_TRY(t->d_ends2.reserve(n * 4));
     size_t tmp_bytes = 0;
     TRX_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, d_hit_keys, static_cast<uint64_t *>(t->d_keys2.ptr),
                                              d_hit_ends, static_cast<uint32_t *>(t->d_ends2.ptr), static_cast<int>(n), 0, 64,
-                                             c->stream));
+                                             st));
     TRX_TRY(t->d_sort_tmp.reserve(tmp_bytes));
     TRX_CUDA(cub::DeviceRadixSort::SortPairs(t->d_sort_tmp.ptr, tmp_bytes, d_hit_keys,
                                              static_cast<uint64_t *>(t->d_keys2.ptr), d_hit_ends,
-                                             static_cast<uint32_t *>(t->d_ends2.ptr), static_cast<int>(n), 0, 64, c->stream));
+                                             static_cast<uint32_t *>(t->d_ends2.ptr), static_cast<int>(n), 0, 64, st));
     c->launches += 3; // cub's histogram + onesweep passes
     std::vector<uint64_t> keys(n);
     std::vector<uint32_t> ends(n);
-    TRX_CUDA(cudaMemcpyAsync(keys.data(), t->d_keys2.ptr, n * 8, cudaMemcpyDeviceToHost, c->stream));
-    TRX_CUDA(cudaMemcpyAsync(ends.data(), t->d_ends2.ptr, n * 4, cudaMemcpyDeviceToHost, c->stream));
-    TRX_CUDA(cudaStreamSynchronize(c->stream));
+    TRX_CUDA(cudaMemcpyAsync(keys.data(), t->d_keys2.ptr, n * 8, cudaMemcpyDeviceToHost, st));
+    TRX_CUDA(cudaMemcpyAsync(ends.data(), t->d_ends2.ptr, n * 4, cudaMemcpyDeviceToHost, st));
+    TRX_CUDA(cudaStreamSynchronize(st));
     for (uint64_t i = 0; i < n; ++i)
     {
         uint32_t rec = static_cast<uint32_t>(keys[i] >> 32);
