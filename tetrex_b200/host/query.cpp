@@ -122,10 +122,32 @@ uint64_t search_impl(bitvector const & hits_in, std::string const & query_in, De
     regex_handle rx(query, /*posix=*/!dna);                    // RE2::POSIX for peptides, default options for DNA
 
     uint8_t const * map = (!dna && index.reduction() > 0) ? index.redmap() : nullptr;
-    std::vector<trx_hit> fwd = scan(store, rx, cand, false, map);
-    std::vector<trx_hit> rev;
-    if (dna)
-        rev = scan(store, rx, cand, true, nullptr);
+    std::vector<trx_hit> fwd, rev;
+    if (!dna)
+        fwd = scan(store, rx, cand, false, map);
+    else
+    {
+        // both strands in flight at once (trx_regex_scan_begin/_end): the second scan's kernels follow the first one's
+        // without a host round trip in between
+        int t_fwd = -1, t_rev = -1;
+        uint64_t const cap = 4096;
+        check(trx_regex_scan_begin(store.text, rx.re, cand.data(), 0, map, cap, &t_fwd));
+        int const rc_begin = trx_regex_scan_begin(store.text, rx.re, cand.data(), 1, nullptr, cap, &t_rev);
+        auto finish = [&](int ticket, bool reverse, uint8_t const * m) {
+            std::vector<trx_hit> hits(cap);
+            uint64_t n = 0;
+            int const rc = trx_regex_scan_end(store.text, ticket, hits.data(), &n, nullptr);
+            if (rc == TRX_ECAPACITY)
+                return scan(store, rx, cand, reverse, m); // more hits than the speculative buffer: once more, with room
+            check(rc);
+            hits.resize(n);
+            return hits;
+        };
+        fwd = finish(t_fwd, false, map);
+        if (rc_begin != TRX_OK)
+            check(rc_begin);
+        rev = finish(t_rev, true, nullptr);
+    }
 
     uint64_t lines = 0;
     std::string line, match;
