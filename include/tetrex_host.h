@@ -1,0 +1,53 @@
+/* tetrex_host.h — C facade of the host layer (tetrex_b200/host/capi.cpp → tetrex_b200/lib/libtrxhost.so).
+ *
+ * include/tetrex_b200.h is the boundary of the CUDA library; this header is the boundary of the C++ layer that mirrors
+ * the reference's query API on top of it, for drivers that are not C++ (one process per GPU under torchrun:
+ * tetrex_b200/sharded.py).  Reference interfaces, relative to /root/reference:
+ *   load_ibf                      include/index_base.h:189-195
+ *   process_query                 include/query.h:226-247   (preprocess, construct_kgraph, OTFCollector::collect)
+ *   iter_disk_search              include/query.h:97-188    (verify_fasta_hit & co., src/query.cpp:167-315)
+ * Every function returns 0, or -1 with the message in trxh_last_error() (thread-local): the messages are the ones the
+ * C++ layer throws (trxh::error / trxh::archive_error), i.e. what src/main.cpp prints for std::runtime_error /
+ * cereal::Exception.  There is no CPU fallback underneath: the handle lives on the device of the trx_ctx_t. */
+#ifndef TETREX_HOST_H
+#define TETREX_HOST_H
+
+#include <stdint.h>
+
+#include "tetrex_b200.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char *trxh_last_error(void);
+
+/* Loads shard `shard_index` of `shard_count` of an index file onto ctx's device (1 shard = the whole index).  Flat IBF:
+ * the 64-bin column block of every row (shard_count must divide bin_words); HIBF: a replica; in both cases verify reads
+ * only the FASTA files of the shard's bins. */
+int trxh_open(trx_ctx_t *ctx, const char *path, uint32_t shard_index, uint32_t shard_count, void **out);
+void trxh_close(void *handle);
+/* out[0..8) = bin_count, bin_words, is_hibf, is_dna, k, shard_word_begin, shard_words, reduction */
+int trxh_info(void *handle, uint64_t out[8]);
+
+/* ORs n bytes over all shards in place (all-reduce MAX): the collector's `path_.none()` (include/otf_collector.h:383) is
+ * a statement about all bins.  Called once per probing rank of the k-graph, on the calling thread. */
+typedef void (*trxh_alive_fn)(uint8_t *alive, uint64_t n, void *user);
+
+/* process_query: candidate bins of `regex` as bin_words words (bit b = bin b, ANDed with the real bins like
+ * run_collection does).  A column shard fills only its own words and REQUIRES `alive`; otherwise alive may be NULL.
+ * stats (nullable, 3 entries): k-mers probed, ranks visited, collector items. */
+int trxh_process_query(void *handle, const char *regex, trxh_alive_fn alive, void *user, uint64_t *out_words, uint64_t *stats);
+
+/* iter_disk_search over the shard's own bins: the reference's output lines, in its -t 1 order, as one malloc'ed buffer
+ * (trxh_free).  cand_words: bin_words words (bits of other shards' bins are ignored). */
+int trxh_verify(void *handle, const uint64_t *cand_words, const char *regex, char **out_text, uint64_t *out_len, uint64_t *n_lines);
+void trxh_free(void *p);
+
+/* diagnostic: print a native backtrace on SIGSEGV */
+void trxh_debug_backtrace_on_segv(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TETREX_HOST_H */

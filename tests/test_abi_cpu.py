@@ -31,6 +31,18 @@ def test_library_exports_every_declared_symbol():
     assert sorted(_abi.PROTOTYPES) == names
 
 
+def test_host_facade_exports_every_declared_symbol():
+    """include/tetrex_host.h ↔ tetrex_b200/lib/libtrxhost.so (the C facade of the C++ host layer)."""
+    from tetrex_b200 import sharded
+    hdr = open(os.path.join(ROOT, "include", "tetrex_host.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    names = sorted(set(re.findall(r"\b(trxh_[a-z0-9_]+)\s*\(", hdr)))
+    assert len(names) >= 8
+    handle = sharded.host_lib()
+    for n in names:
+        assert hasattr(handle, n), f"{n} declared in include/tetrex_host.h but not exported by libtrxhost.so"
+
+
 def test_abi_version():
     assert t.lib().trx_abi_version() == 1
 

@@ -82,6 +82,15 @@ def _worker(rank, world, port, out_dir):
             assert keys == sorted(keys)
         else:
             assert merged is None
+        # output lines: every rank formats the lines of its own (ascending) bins, rank 0 gets them in rank = bin order
+        from tetrex_b200 import sharded
+        text = sharded.gather_text("".join(f"bin{b}\t>r\tLMA\t0,3\n" for b in my_bins[:3]))
+        if rank == 0:
+            want_lines = [f"bin{b}\t>r\tLMA\t0,3" for r in range(world) for b in
+                          np.arange(td.column_shard(bin_words, r, world)[0] * 64, td.column_shard(bin_words, r, world)[0] * 64 + 3)]
+            assert text.splitlines() == want_lines
+        else:
+            assert text is None
         assert td.max_over_ranks(float(rank + 1)) == float(world)
         assert td.sum_over_ranks(1.5) == 1.5 * world
         sl = td.unit_slice(values.size, rank, world)

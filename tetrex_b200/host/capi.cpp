@@ -9,6 +9,7 @@
 #include <execinfo.h>
 #include <unistd.h>
 
+#include "../../include/tetrex_host.h"
 #include "trx_host.hpp"
 
 namespace
@@ -57,8 +58,6 @@ void trxh_debug_backtrace_on_segv(void)
 {
     signal(SIGSEGV, segv_backtrace);
 }
-
-typedef void (*trxh_alive_fn)(uint8_t * alive, uint64_t n, void * user);
 
 const char * trxh_last_error(void)
 {
