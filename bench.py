@@ -216,6 +216,39 @@ def run_ours(args):
     e2e_value = sum_over_ranks(float(args.batch * e_steps)) / (e_ms / 1e3)
     assert int(out_np.view(np.int64).sum()) == checksum_dev, "host-buffer path and device path disagree"
 
+    # ---------------- end to end the way the collector uses the device (OTFCollector::update_path, include/otf_collector.h:
+    # 247-279): k-mers and their path slots go in from pinned host memory, the hit vectors are ANDed into HBM-resident
+    # path bitvectors, ONE alive byte per k-mer comes back — the per-k-mer bitvectors never cross PCIe
+    collector_e2e = None
+    if not args.no_extra:
+        paths = t.Paths(ctx, W, args.batch)
+        paths.fill(0, args.batch, N_BINS)
+        ident = torch.arange(args.batch, dtype=torch.int32).pin_memory().numpy().view(np.uint32)  # pinned like the k-mers
+        alive = torch.zeros(args.batch, dtype=torch.uint8).pin_memory().numpy()
+        from tetrex_b200._abi import check, u64p  # noqa: F401
+        import ctypes as C
+
+        def collector_step():
+            d_q.copy_(pin_q, non_blocking=True)  # 8 B per k-mer over PCIe, on the context's stream
+            hibf.membership_dev(d_q.data_ptr(), args.batch, d_out.data_ptr())
+            check(t.lib().trx_paths_and_hits(paths._h, d_out.data_ptr(), ident.ctypes.data_as(C.c_void_p),
+                                             ident.ctypes.data_as(C.c_void_p), args.batch, alive.ctypes.data_as(C.c_void_p)))
+        for _ in range(2):
+            collector_step()
+        barrier()
+        tw = time.perf_counter()
+        for _ in range(e_steps):
+            collector_step()
+        torch.cuda.synchronize()
+        c_ms = max_over_ranks((time.perf_counter() - tw) * 1e3)
+        barrier()
+        collector_e2e = {"value": sum_over_ranks(float(args.batch * e_steps)) / (c_ms / 1e3), "unit": UNIT,
+                         "h2d_bytes_per_step": args.batch * 16, "d2h_bytes_per_step": args.batch,
+                         "what": "k-mers + slot ids in (pinned host), membership on the device, AND into HBM-resident path "
+                                 "slots (trx_paths_and_hits), one alive byte per k-mer out",
+                         "alive_fraction_after_steps": float(alive.mean())}
+        paths.close()
+
     # ---------------- BASELINE config 4 (8192-bin DNA IBF, k = 20, 23.4 GB), bins sharded over the ranks in 64-bin column
     # blocks, the SAME k-mer batch on every rank (= broadcast): K2 bulk_contains of every k-mer against all 8192 bins
     flat_c4 = None
@@ -255,6 +288,8 @@ def run_ours(args):
                     "d2h_bytes_per_step": args.batch * W * 8, "steps": e_steps},
             "gpu_launches": int(launches), "clocks": clocks,
         }
+        if collector_e2e is not None:
+            line["e2e"]["collector_step"] = collector_e2e
         if flat_c4 is not None:
             flat_c4["roofline"]["peak"] = peak
             flat_c4["roofline"]["frac"] = flat_c4["roofline"]["achieved"] / peak
