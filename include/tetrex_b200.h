@@ -236,9 +236,12 @@ int trx_regex_scan_end(trx_text_t *text, int ticket, trx_hit *hits, uint64_t *n_
  * atoms:  out[1] = distinct literal bytes, out[2] = terms, out[5] = atoms, out[3], out[4] = the match's first byte
  *         lies at an address in [anchor + out[3], anchor + out[4]]; term i: byte out[8+i] at anchor + d for a d in
  *         [out[24+i], out[40+i]], belonging to atom out[56+i] — an atom holds if ANY of its terms does (a class of up
- *         to 3 bytes), the filter passes where ALL atoms hold. */
+ *         to 3 bytes), the SIMD stage passes where ALL atoms hold.  out[6] = confirm checks, evaluated only at the
+ *         anchors that pass: check c holds if the byte at anchor + d is in its class for a d in
+ *         [out[72+10c], out[73+10c]] (signed), class = 256-bit mask in out[74+10c .. 82+10c) (bit b of word w = byte
+ *         32w + b). */
 int trx_regex_filter_plan(const trx_regex_t *re, const double *byte_freq, int reverse_strand, const uint8_t *map256,
-                          int32_t out[72]);
+                          int32_t out[136]);
 
 #ifdef __cplusplus
 }

@@ -80,6 +80,16 @@ def flagged_starts(plan: dict, text: np.ndarray) -> np.ndarray:
             m[:n - d] |= np.isin(text[d:], byts)
         hit &= m
     assert len(lits) == plan["n_lit"] <= 4
+    for byts, lo, hi in plan.get("confirm", []):  # second stage: evaluated at the surviving anchors, offsets signed
+        assert -128 <= lo <= hi <= 127 and hi - lo <= 7 and len(byts) >= 1
+        m = np.zeros(n, dtype=bool)
+        member = np.isin(text, byts)
+        for d in range(lo, hi + 1):
+            if d >= 0:
+                m[:n - d] |= member[d:]
+            else:
+                m[-d:] |= member[:n + d]
+        hit &= m
     assert any(lo == 0 and hi == 0 for _, lo, hi in plan["atoms"]), "one atom is the anchor"
     for a in np.flatnonzero(hit):
         lo, hi = max(0, a + plan["start_lo"]), min(n - 1, a + plan["start_hi"])
@@ -104,6 +114,8 @@ PEPTIDE = [
     "C[ST]?W.{2,5}HM", "WM.{30,31}CH", "C.{3}C.{3}C.{3}W", "N[^P][ST][^P]", "[RK].{2,3}[DE].{2,3}Y",
     "[DM]D[KR]K[HLMY][EFS][CI]", "[HI]{2,4}[CSV]{2,4}R[NP].E", "[EMVWY]F[FR]Y[CST]{2,4}.", "H[IMPTV]G.[GHNPT].",
     "[FHI][AGS].S.M", "R..[AV][MQW][DW]", "[CW][HM].{1,3}[CW]K", "GF[DMN].[CG].[INPSY]{2,4}.{2,4}[GQT][KR]",
+    ".N.I.[GRS]", "...[GPST][NRSWY]F", ".[GRWY].I[DGNQR]E.", "[LQTY]E.{2,4}V.{2,4}.F[IKMRY]", "Y[GIMR]{2,4}.F..",
+    "[AIQVY][DILRY][INRW][AEGKQ]{2,4}[ADFKM].M", "..[MV]{2,4}[EHLMW][FGLS][LV][DHPTY][PQTW]", "[ILV]{2}.K[DE]{1,3}[FYW].N",
 ]
 DNA = ["GATTACAG", "ACGTAC(G|T)", "TTGACA.{3}T", "TATA.{2,4}CGCG", "GG.{1,6}CCATGG", "A(C+|G+)T", "CG.{3}(AT|TA)GC.{0,2}GG"]
 
@@ -168,9 +180,40 @@ def test_plan_kinds():
     assert (zf["start_lo"], zf["start_hi"]) == (0, 0)
     cl = t.Regex("[DM]D[KR]K[HLMY][EFS][CI]", True).filter_plan(freq)  # no literal window is selective enough; small classes are
     assert cl["kind"] == "atoms" and any(len(b) > 1 for b, _, _ in cl["atoms"])
+    weak = t.Regex(".N.I.[GRS]", True).filter_plan(freq)  # two weak literals + a class that does not fit the byte budget
+    assert weak["kind"] == "atoms" and weak["confirm"] and sorted(weak["confirm"][0][0]) == [ord(c) for c in "GRS"]
     assert t.Regex("(LMAQ|GLYN)", True).filter_plan(freq)["kind"] == "none"   # no necessary literal
     assert t.Regex("[ST].[RK]", True).filter_plan(freq)["kind"] == "none"
-    # a reduced alphabet turns every literal into a class of raw bytes: no literal factor survives the byte map
+    # a reduced alphabet turns every literal into a class of raw bytes: no fixed literal window survives the byte map,
+    # classes of up to three raw bytes can still be atoms (and wider ones confirm checks)
     _, redmap = t.peptide_maps(1)
     reduced = "".join(chr(redmap[ord(c)]) for c in "LMAQGLYN")
-    assert t.Regex(reduced, True).filter_plan(freq, map256=redmap)["kind"] == "none"
+    assert t.Regex(reduced, True).filter_plan(freq, map256=redmap)["kind"] in ("none", "atoms")
+
+
+@pytest.mark.parametrize("reduction", [1, 2])
+@pytest.mark.parametrize("motif", ["LMAQGLYNCW", "CWHKDEPGCC", "HP.{2,3}WCM"])
+def test_reduced_alphabet_plan_is_necessary(reduction, motif):
+    """verify_reduced_fasta_hit (src/query.cpp:239-291): the RECORD is mapped through redmap_ and the reduced regex runs on
+    that; the prefilter works on the raw text with the map folded into the byte classes."""
+    rng = random.Random(zlib.crc32(motif.encode()) + reduction)
+    _, redmap = t.peptide_maps(reduction)
+    table = bytes(int(x) for x in redmap)
+    pattern = "".join(chr(redmap[ord(c)]) if c.isalpha() else c for c in motif)  # reduce_query_alphabet on the literals
+    freq = frequencies(AA_FREQ)
+    plan = t.Regex(pattern, True).filter_plan(freq, map256=redmap)
+    parts = []
+    for _ in range(300):
+        parts.append("".join(rng.choices(AA, weights=[AA_FREQ[c] for c in AA], k=rng.randint(0, 90))))
+        inst = sample(pattern, "".join(sorted(set(chr(b) for b in table[65:91]))), rng)
+        # a raw preimage of the reduced instance: any residue that maps to the wanted reduced letter
+        parts.append("".join(rng.choice([a for a in AA if chr(redmap[ord(a)]) == ch] or [ch]) for ch in inst))
+    raw = "".join(parts)
+    mapped = raw.encode().translate(table).decode()
+    starts = [m.start() for m in re.finditer("(?=(" + pattern + "))", mapped)]
+    assert len(starts) >= 300
+    if plan["kind"] == "none":
+        return
+    ok = flagged_starts(plan, np.frombuffer(raw.encode(), dtype=np.uint8))
+    missed = [s for s in starts if not ok[s]]
+    assert not missed, (pattern, plan, missed[:5])

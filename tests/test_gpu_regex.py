@@ -146,7 +146,9 @@ def test_atom_filter_equals_exact_automaton(ctx, monkeypatch):
     rec_bin = [0, 0, 1, 1, 2, 2, 3, 3, 4]
     finder = ob.ref_find_all if ob.have_ref() else ob.find_all_python
     for pat in ["C.{2,4}C.{3}[LIVMFYWC].{8}H.{3,5}H", "W.{2,4}C.{5,9}CW", "D.{0,3}EW", "M.{2}(C|W)H.{3,4}(WK|WR)C",
-                "C.{12,16}W.{10,14}H.{2}M", "WM.{30,31}CH", "(C.{2,3}){2}WH", "C[ST]?W.{2,5}HM$"]:
+                "C.{12,16}W.{10,14}H.{2}M", "WM.{30,31}CH", "(C.{2,3}){2}WH", "C[ST]?W.{2,5}HM$",
+                # weak literals + classes that only fit the confirm stage (evaluated at the surviving anchors)
+                ".N.I.[GRS]", "R..[AV][MQW][DW]", "[LQTY]E.{2,4}V.{2,4}.F[IKMRY]", "H[IMPTV]G.[GHNPT]."]:
         body = pat.rstrip("$")
         seqs = [bytearray("".join(rng.choices(aa, weights=weights, k=L)).encode()) for L in lengths]
         planted = 0
@@ -200,7 +202,7 @@ def test_atom_filter_equals_exact_automaton(ctx, monkeypatch):
         for rev in (False, True):
             monkeypatch.setenv("TRX_REGEX_FILTER", "atoms")
             a = dtxt.scan(rx, reverse_strand=rev)
-            assert dtxt.last_filter_literals >= 2, (pat, rev)
+            assert dtxt.last_filter_literals >= 1, (pat, rev)  # SIMD atoms; further positions may sit in the confirm stage
             monkeypatch.delenv("TRX_REGEX_FILTER")
             want = expected_hits(dna, [0, 1, 1, 1], pat, False, finder, transform=revcomp if rev else None)
             assert len(want) >= 4 and np.array_equal(a, want), (pat, rev, len(a), len(want))

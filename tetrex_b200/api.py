@@ -273,7 +273,7 @@ class Regex:
         f = _np(byte_freq, np.float64)
         assert len(f) == 256
         m = _np(map256, np.uint8) if map256 is not None else None
-        out = np.zeros(72, dtype=np.int32)
+        out = np.zeros(136, dtype=np.int32)
         check(lib().trx_regex_filter_plan(self._h, _ptr(f), int(reverse_strand), _ptr(m) if m is not None else None, _ptr(out)))
         kind = int(out[0])
         if kind == 1:
@@ -285,8 +285,14 @@ class Regex:
             for i in range(int(out[2])):
                 a = atoms.setdefault(int(out[56 + i]), [[], int(out[24 + i]), int(out[40 + i])])
                 a[0].append(int(out[8 + i]))
+            confirm = []
+            for c in range(int(out[6])):
+                words = out[74 + 10 * c:82 + 10 * c].view(np.uint32)
+                byts = tuple(32 * w + b for w in range(8) for b in range(32) if (int(words[w]) >> b) & 1)
+                confirm.append((byts, int(out[72 + 10 * c]), int(out[73 + 10 * c])))
             return {"kind": "atoms", "n_lit": int(out[1]), "start_lo": int(out[3]), "start_hi": int(out[4]),
-                    "atoms": [(tuple(sorted(b)), lo, hi) for b, lo, hi in atoms.values()]}  # (bytes of the class, lo, hi)
+                    "atoms": [(tuple(sorted(b)), lo, hi) for b, lo, hi in atoms.values()],  # (bytes of the class, lo, hi)
+                    "confirm": confirm}  # second stage, same triples, offsets signed
         return {"kind": "none"}
 
     def close(self):

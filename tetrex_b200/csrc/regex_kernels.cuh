@@ -65,6 +65,16 @@ struct filter_spec
 // direction) lies at an address in [anchor + start_lo, anchor + start_hi].  Derived on the host from the automaton's
 // dominator chain.
 constexpr int kMaxAtomTerms = 16;
+constexpr int kMaxConfirm = 6;
+// Second stage of the gapped prefilter, evaluated only at the anchors the SIMD stage lets through: "the byte at address
+// anchor + d belongs to `mask` for some d in [lo, hi]" (offsets may be negative; classes of any size).  These are the
+// necessary positions that do not fit the SIMD stage's budget of 4 distinct bytes.
+struct confirm_check
+{
+    int8_t lo, hi;
+    uint8_t pad[2];
+    uint32_t mask[8]; // bit c set: byte c is in the class
+};
 struct atom_spec
 {
     int32_t n_lit;            // 0: unused
@@ -75,6 +85,8 @@ struct atom_spec
     uint8_t term_lit[kMaxAtomTerms]; // index into splat
     uint8_t term_lo[kMaxAtomTerms], term_hi[kMaxAtomTerms];
     uint8_t term_end[kMaxAtomTerms]; // 1 = last term of its atom
+    int32_t n_confirm;
+    confirm_check confirm[kMaxConfirm]; // most selective first
 };
 
 struct scan_params
@@ -1049,6 +1061,24 @@ __global__ void __launch_bounds__(kScanThreads * SPLIT + 32)
                     int const b = __ffs(bits) - 1;
                     bits &= bits - 1;
                     int64_t const anchor = static_cast<int64_t>(g_lo) + 32 * q + b;
+                    // second stage: the remaining necessary positions, straight from the text (L2: the tile just went by)
+                    bool confirmed = true;
+                    for (int c = 0; c < p.atoms.n_confirm && confirmed; ++c)
+                    {
+                        bool found = false;
+                        for (int d = p.atoms.confirm[c].lo; d <= p.atoms.confirm[c].hi && !found; ++d)
+                        {
+                            int64_t const a = anchor + d;
+                            if (a >= 0 && a < static_cast<int64_t>(p.n_text))
+                            {
+                                uint32_t const byte = __ldg(p.text + a);
+                                found = (p.atoms.confirm[c].mask[byte >> 5] >> (byte & 31)) & 1;
+                            }
+                        }
+                        confirmed = found;
+                    }
+                    if (!confirmed)
+                        continue;
                     int64_t lo = anchor + p.atoms.start_lo, hi = anchor + p.atoms.start_hi;
                     if (hi < 0 || lo >= static_cast<int64_t>(p.n_text))
                         continue;

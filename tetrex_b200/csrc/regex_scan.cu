@@ -406,6 +406,7 @@ void complement_table(uint8_t tab[256])
 }
 
 constexpr double kDefaultMaxPass = 1e-3;
+constexpr double kMaxSimdPass = 2e-2; // admission of the gapped prefilter's SIMD stage when confirm checks follow
 
 struct bits128
 {
@@ -527,7 +528,8 @@ filter_spec derive_filter(regex_dev const & img, double const * freq, bool rever
 struct atom_plan
 {
     atom_spec spec{};
-    double pass{1.0}; // expected fraction of text positions that survive the filter
+    double pass{1.0};      // expected fraction of text positions that survive the SIMD stage
+    double confirmed{1.0}; // … and the confirm checks: what phase 2 gets to see
 };
 
 struct automaton_graph
@@ -666,13 +668,16 @@ atom_plan derive_atoms(regex_dev const & img, double const * freq, bool reverse)
     int const P = g.P;
     if (P <= 0)
         return none;
-    // class of a position = the raw bytes it accepts; usable as an atom when there are at most 3 of them
+    // class of a position = the raw bytes it accepts.  At most 3 of them: usable as a SIMD atom; any other class that
+    // is not nearly everything: usable as a confirm check at the anchors the SIMD stage lets through.
     constexpr int kMaxClass = 3;
     struct small_class
     {
-        int n{0};
+        int n{0};          // 1..3: SIMD-capable; 0: not
         int byte[kMaxClass]{};
-        double freq{0.0};
+        double freq{0.0};  // expected fraction of text bytes in the class
+        uint32_t mask[8]{};
+        bool usable{false}; // as a confirm check
     };
     std::vector<small_class> cls(P);
     {
@@ -684,20 +689,16 @@ atom_plan derive_atoms(regex_dev const & img, double const * freq, bool reverse)
                     if (count[pos] < kMaxClass)
                         cls[pos].byte[count[pos]] = c;
                     ++count[pos];
+                    cls[pos].mask[c >> 5] |= 1u << (c & 31);
+                    cls[pos].freq += c == 0 ? 1.0 : std::max(freq[c], 1e-4); // the text is zero padded: NUL is "everywhere"
                 }
         for (int pos = 0; pos < P; ++pos)
         {
-            cls[pos].n = count[pos] <= kMaxClass ? count[pos] : 0;
-            for (int j = 0; j < cls[pos].n; ++j)
-            {
-                if (cls[pos].byte[j] == 0) // the text is zero padded: a NUL literal would match the padding
-                    cls[pos].n = 0;
-                else
-                    cls[pos].freq += std::max(freq[cls[pos].byte[j]], 1e-4);
-            }
+            cls[pos].n = (count[pos] <= kMaxClass && !(cls[pos].mask[0] & 1u)) ? count[pos] : 0;
+            cls[pos].usable = count[pos] > 0 && cls[pos].freq <= 0.6;
         }
     }
-    // chain of necessary small-class positions, ordered by their shortest distance from S
+    // chain of necessary positions with a usable class, ordered by their shortest distance from S
     struct link
     {
         int pos;
@@ -708,7 +709,7 @@ atom_plan derive_atoms(regex_dev const & img, double const * freq, bool reverse)
         std::vector<std::pair<int, int>> order; // (min offset, position)
         for (int pos = 0; pos < P; ++pos)
         {
-            if (cls[pos].n == 0 || reachable_without(g, g.S(), g.F(), pos))
+            if (!cls[pos].usable || reachable_without(g, g.S(), g.F(), pos))
                 continue;
             int lo = 0, hi = 0;
             if (!walk_range(g, g.S(), pos, lo, hi))
@@ -749,14 +750,14 @@ atom_plan derive_atoms(regex_dev const & img, double const * freq, bool reverse)
     };
     for (int anchor = 0; anchor < n; ++anchor)
     {
-        if (chain[anchor].off_hi - chain[anchor].off_lo > kMaxStartSpread)
+        if (chain[anchor].off_hi - chain[anchor].off_lo > kMaxStartSpread || cls[chain[anchor].pos].n == 0)
             continue;
         // address offsets of the other atoms relative to the anchor: forward scans look at later symbols (higher
         // addresses), reverse scans read downwards, so EARLIER symbols lie at higher addresses
         std::vector<cand> cands;
         for (int i = 0; i < n; ++i)
         {
-            if (i == anchor || (reverse ? i > anchor : i < anchor))
+            if (i == anchor || (reverse ? i > anchor : i < anchor) || cls[chain[i].pos].n == 0)
                 continue;
             int lo, hi;
             if (!reverse)
@@ -817,9 +818,54 @@ atom_plan derive_atoms(regex_dev const & img, double const * freq, bool reverse)
             chosen.push_back(cd);
             pass *= cd.factor;
         }
-        // good enough is good enough: below the target rate prefer the cheaper kernel (fewer literals, fewer terms)
+        // second stage: every other necessary position within reach of the anchor, most selective first
+        struct check
+        {
+            int pos, lo, hi;
+            double factor;
+        };
+        std::vector<check> checks;
+        if (pass > kGoodEnough)
+            for (int i = 0; i < n; ++i)
+            {
+                bool used = false;
+                for (cand const & cd : chosen)
+                    used |= cd.pos == chain[i].pos;
+                if (used)
+                    continue;
+                // signed offset (in reading direction) of symbol i relative to the anchor's symbol
+                int lo = chain[i].off_lo - chain[anchor].off_lo, hi = chain[i].off_hi - chain[anchor].off_hi;
+                if (i < anchor)
+                    std::swap(lo, hi); // before the anchor the gap-wise bounds come out reversed
+                if (lo > hi)
+                    continue;
+                if (reverse) // reading direction = descending addresses
+                {
+                    int const t_lo = -hi, t_hi = -lo;
+                    lo = t_lo;
+                    hi = t_hi;
+                }
+                if (lo < -120 || hi > 120 || hi - lo > 7)
+                    continue;
+                double const f = 1.0 - std::pow(1.0 - std::min(cls[chain[i].pos].freq, 1.0), hi - lo + 1);
+                if (f > 0.7)
+                    continue;
+                checks.push_back(check{chain[i].pos, lo, hi, f});
+            }
+        std::sort(checks.begin(), checks.end(), [](check const & a, check const & b) { return a.factor < b.factor; });
+        double confirmed = pass;
+        size_t n_checks = 0;
+        while (n_checks < checks.size() && n_checks < static_cast<size_t>(kMaxConfirm) && confirmed > kGoodEnough)
+            confirmed *= checks[n_checks++].factor;
+        // The cost of a plan is its SIMD stage plus a few dependent L2 reads per surviving anchor: a usable plan first of
+        // all, then the more selective SIMD stage, then — good enough is good enough — the cheaper one.
+        auto usable = [](double simd, double conf) { return simd <= kMaxSimdPass && conf <= max_pass_rate(); };
         bool better;
-        if (pass > kGoodEnough || best.pass > kGoodEnough)
+        if (usable(pass, confirmed) != usable(best.pass, best.confirmed))
+            better = usable(pass, confirmed);
+        else if (!usable(pass, confirmed))
+            better = confirmed < best.confirmed;
+        else if (pass > kGoodEnough || best.pass > kGoodEnough)
             better = pass < best.pass;
         else
             better = n_lit < best_lits || (n_lit == best_lits && n_terms < best.spec.n_terms);
@@ -827,6 +873,14 @@ atom_plan derive_atoms(regex_dev const & img, double const * freq, bool reverse)
             continue;
         atom_plan plan;
         plan.pass = pass;
+        plan.confirmed = confirmed;
+        plan.spec.n_confirm = static_cast<int32_t>(n_checks);
+        for (size_t ci = 0; ci < n_checks; ++ci)
+        {
+            plan.spec.confirm[ci].lo = static_cast<int8_t>(checks[ci].lo);
+            plan.spec.confirm[ci].hi = static_cast<int8_t>(checks[ci].hi);
+            memcpy(plan.spec.confirm[ci].mask, cls[checks[ci].pos].mask, sizeof plan.spec.confirm[ci].mask);
+        }
         plan.spec.n_lit = n_lit;
         plan.spec.n_atoms = static_cast<int32_t>(chosen.size());
         for (int l = 0; l < n_lit; ++l)
@@ -919,7 +973,11 @@ filter_kind choose_filter(regex_dev const & img, double const * freq, bool rever
     if (!only_window && !(have_window && window_pass <= 1e-4))
     {
         atom_plan plan = derive_atoms(img, freq, reverse);
-        if (plan.spec.n_lit >= 1 && (only_atoms || (plan.pass <= max_pass_rate() && (!have_window || plan.pass < 0.25 * window_pass))))
+        // the SIMD stage alone may be weak (every surviving anchor costs a few dependent L2 reads in the confirm stage),
+        // what phase 2 gets to see must not be
+        if (plan.spec.n_lit >= 1 &&
+            (only_atoms || (plan.pass <= kMaxSimdPass && plan.confirmed <= max_pass_rate() &&
+                            (!have_window || plan.confirmed < 0.25 * window_pass))))
         {
             atoms = plan.spec;
             return kFilterAtoms;
@@ -1231,7 +1289,7 @@ int trx_regex_scan(trx_text_t * t, trx_regex_t * re, const uint64_t * candidate_
 }
 
 int trx_regex_filter_plan(const trx_regex_t * re, const double * byte_freq, int reverse_strand, const uint8_t * map256,
-                          int32_t out[72])
+                          int32_t out[136])
 {
     if (!re || !byte_freq || !out)
         return set_error(TRX_EINVAL, "trx_regex_filter_plan: NULL argument");
@@ -1240,7 +1298,7 @@ int trx_regex_filter_plan(const trx_regex_t * re, const double * byte_freq, int 
     filter_spec window;
     atom_spec atoms;
     filter_kind const kind = choose_filter(*img, byte_freq, reverse_strand != 0, window, atoms);
-    memset(out, 0, 72 * sizeof(int32_t));
+    memset(out, 0, 136 * sizeof(int32_t));
     out[0] = kind;
     if (kind == kFilterWindow)
     {
@@ -1268,6 +1326,14 @@ int trx_regex_filter_plan(const trx_regex_t * re, const double * byte_freq, int 
             out[40 + a] = atoms.term_hi[a];
             out[56 + a] = group;
             group += atoms.term_end[a];
+        }
+        out[6] = atoms.n_confirm;
+        for (int c = 0; c < atoms.n_confirm; ++c)
+        {
+            out[72 + 10 * c] = atoms.confirm[c].lo;
+            out[73 + 10 * c] = atoms.confirm[c].hi;
+            for (int w = 0; w < 8; ++w)
+                out[74 + 10 * c + w] = static_cast<int32_t>(atoms.confirm[c].mask[w]);
         }
     }
     return TRX_OK;
