@@ -44,6 +44,12 @@ int trxh_process_query(void *handle, const char *regex, trxh_alive_fn alive, voi
 int trxh_verify(void *handle, const uint64_t *cand_words, const char *regex, char **out_text, uint64_t *out_len, uint64_t *n_lines);
 void trxh_free(void *p);
 
+/* Host only (no device): the order in which the collector drains one rank whose items arrived with these keys
+ * (`kmer_ & submask_`), i.e. robin_hood::unordered_map slot order as OTFCollector::collect sees it through
+ * `comp_table_[i].begin()` (include/otf_collector.h:355-357, include/robin_hood.h).  Duplicate keys are absorbed.
+ * out[j] = index into keys of the j-th item popped; returns the number of items. */
+uint64_t trxh_rank_pop_order(const uint64_t *keys, uint64_t n, uint32_t *out);
+
 /* diagnostic: print a native backtrace on SIGSEGV */
 void trxh_debug_backtrace_on_segv(void);
 

@@ -129,6 +129,8 @@ def ref():
                                              C.POINTER(u64p), u64p]
         lib.ref_re2_scan_records.restype = C.c_int64
         lib.ref_re2_scan_records.argtypes = [C.c_char_p, C.c_int, C.c_void_p, u64p, C.c_uint64, C.c_int]
+        lib.ref_rh_pop_order.restype = C.c_uint64
+        lib.ref_rh_pop_order.argtypes = [u64p, C.c_uint64, u32p]
         _ref = lib
     return _ref
 
@@ -453,6 +455,14 @@ def ref_index_query(index_path, regex, verify=True, threads=1, stdout_path=None)
         if stdout_path is None:
             os.unlink(tmp)
     return words[:n].copy(), text
+
+
+def ref_rh_pop_order(keys) -> np.ndarray:
+    """Pop order of a robin_hood::unordered_map<uint64_t, ...> filled like OTFCollector::push fills a rank."""
+    k = np.ascontiguousarray(keys, dtype=np.uint64)
+    out = np.zeros(len(k), dtype=np.uint32)
+    n = ref().ref_rh_pop_order(_p(k, u64p), len(k), _p(out, u32p))
+    return out[:n].copy()
 
 
 def guarded(fn, *args):

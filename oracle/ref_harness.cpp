@@ -818,3 +818,27 @@ int64_t ref_re2_scan_records(char const * regex, int posix_longest, char const *
 }
 
 } // extern "C"
+
+extern "C"
+{
+
+// The order in which OTFCollector::collect drains one rank (include/otf_collector.h:355-357: `comp_table_[i].begin()`
+// + scrub): keys are inserted like push() does (find, then operator[]), then begin() is erased until the map is empty.
+// out[j] = index (into keys) of the j-th popped entry; duplicates of a key are absorbed (not inserted).  Returns the
+// number of entries popped.  Checks the host layer's restatement of the container's slot placement (rh_order.hpp).
+uint64_t ref_rh_pop_order(uint64_t const * keys, uint64_t n, uint32_t * out)
+{
+    robin_hood::unordered_map<uint64_t, uint32_t> m;
+    for (uint64_t i = 0; i < n; ++i)
+        if (m.find(keys[i]) == m.end())
+            m[keys[i]] = static_cast<uint32_t>(i);
+    uint64_t j = 0;
+    while (!m.empty())
+    {
+        out[j++] = m.begin()->second;
+        m.erase(m.begin());
+    }
+    return j;
+}
+
+} // extern "C"

@@ -226,12 +226,185 @@ def golden_cli():
     print("cli.json:", len(out), "queries,", sum(len(c.get("stdout", "").splitlines()) for c in out), "lines")
 
 
+def golden_c1():
+    """BASELINE config 1 on the reference's own five files (data/dna_example_split/sequence{1..5}.fa, 27 bytes each,
+    copied verbatim as test DATA to tests/data/dna_example_split/): the flat DNA IBF (k=3, h=3, FPR 0.05: 106 rows x 64
+    technical bins = 848 bytes), the nucleotide HIBF, and the PEPTIDE HIBF the reference's CLI really builds for
+    `tetrex index -n -k 3`, each queried with README.md:45-51's A(C+|G+)T."""
+    import shutil
+    src = "/root/reference/data/dna_example_split"
+    dst = os.path.join(ROOT, "tests", "data", "dna_example_split")
+    os.makedirs(dst, exist_ok=True)
+    files = []
+    for i in range(1, 6):
+        shutil.copyfile(os.path.join(src, f"sequence{i}.fa"), os.path.join(dst, f"sequence{i}.fa"))
+        files.append(os.path.relpath(os.path.join(dst, f"sequence{i}.fa"), ROOT))
+    cwd = os.getcwd()
+    os.chdir(ROOT)
+    out = []
+    try:
+        for name, mol, flavor in [("c1_dna_flat_k3", 0, 0), ("c1_dna_hibf_k3", 0, 1), ("c1_pep_hibf_k3", 1, 1)]:
+            idx = os.path.join("tests", "golden", "cli", name + ".ibf")
+            ob.ref_index_build(files, 3, 0.05, 3, mol, flavor, 0, idx)
+            for q in ["A(C+|G+)T", "ACT", "CCC(T|G)", "GA+TC"]:
+                got = guarded(ob.ref_index_query, idx, q, True)
+                if got is None:
+                    out.append(dict(index=idx, files=files, molecule=mol, k=3, flavor=flavor, reduction=0, regex=q,
+                                    reference_aborts=True))
+                    continue
+                words, text = got
+                bins = [b for b in range(len(files)) if int(words[b // 64]) >> (b % 64) & 1]
+                out.append(dict(index=idx, files=files, molecule=mol, k=3, flavor=flavor, reduction=0, regex=q, bins=bins,
+                                stdout=text))
+    finally:
+        os.chdir(cwd)
+    json.dump(out, open(os.path.join(OUT, "cli_c1.json"), "w"), indent=0)
+    print("cli_c1.json:", len(out), "queries,", sum(len(c.get("stdout", "").splitlines()) for c in out), "lines")
+
+
+def read_records(path):
+    recs, cur = [], []
+    for line in open(os.path.join(ROOT, path)):
+        if line.startswith(">"):
+            if cur:
+                recs.append("".join(cur))
+            cur = []
+        else:
+            cur.append(line.strip())
+    if cur:
+        recs.append("".join(cur))
+    return recs
+
+
+def fuzz_regexes(rng, records, alphabet, k, n):
+    """Regexes grown around true substrings of the indexed records, so that paths survive the filter and the collector's
+    split / absorb / prune rules all fire; one family is built to make items with different shift counts collide on the
+    same sub-k-mer key (the symbol that packs to 0 — 'A' — in front of a shared suffix: `(XAC|C)DEF`)."""
+    out = []
+    zero = "A"
+    while len(out) < n:
+        rec = rng.choice(records)
+        L = rng.randint(k + 1, k + 8)
+        if len(rec) < L + 2:
+            continue
+        at = rng.randint(0, len(rec) - L)
+        s = rec[at:at + L]
+        fam = rng.random()
+        if fam < 0.22:
+            # colliding-prefix family
+            m = rng.randint(1, 2)
+            j = rng.randint(1, max(1, k - 2))
+            r = "".join(rng.choice(alphabet) for _ in range(rng.randint(1, 2)))
+            alt = [r + zero * j + s[:m], s[:m]]
+            if rng.random() < 0.5:
+                alt.reverse()
+            if rng.random() < 0.3:
+                alt.append("".join(rng.choice(alphabet) for _ in range(rng.randint(1, 3))) + s[:m])
+            out.append("(" + "|".join(alt) + ")" + s[m:])
+            continue
+        if fam < 0.30:
+            # two joins in a row: paths of three different lengths meet
+            a, b = rng.randint(1, 2), rng.randint(1, 2)
+            x = "".join(rng.choice(alphabet) for _ in range(rng.randint(1, 3)))
+            out.append("(" + x + s[:a] + "|" + s[:a] + ")(" + zero + s[a:a + b] + "|" + s[a:a + b] + ")" + s[a + b:])
+            continue
+        parts, i = [], 0
+        dots = 0
+        while i < len(s):
+            u = rng.random()
+            c = s[i]
+            if u < 0.52:
+                parts.append(c)
+            elif u < 0.64:
+                extra = rng.sample(alphabet, rng.randint(1, 3))
+                cls = sorted(set(extra + [c]))
+                rng.shuffle(cls)
+                parts.append("[" + "".join(cls) + "]")
+            elif u < 0.76:
+                w = rng.randint(1, min(3, len(s) - i))
+                true = s[i:i + w]
+                other = "".join(rng.choice(alphabet) for _ in range(rng.randint(1, 3)))
+                if rng.random() < 0.3:
+                    other = other[:1] + zero * rng.randint(1, 2) + true[-1:]
+                alts = [true, other]
+                rng.shuffle(alts)
+                parts.append("(" + "|".join(alts) + ")")
+                i += w - 1
+            elif u < 0.81:
+                parts.append(c + rng.choice(alphabet) + "?")
+            elif u < 0.87:
+                parts.append(c + rng.choice(["+", "*", "{1,2}", "{1,3}", "{1}"]))
+                if parts[-1].endswith("*"):
+                    parts[-1] = c + c + "*"
+            elif u < 0.91 and i + 1 < len(s) and s[i + 1] == c:
+                parts.append(c + rng.choice(["{2}", "{2,3}", "{1,2}", "+"]))
+                i += 1
+            elif u < 0.96 and dots < 2 and alphabet != "ACGT":
+                parts.append(".")
+                dots += 1
+            elif dots < 1 and alphabet != "ACGT" and i + 2 < len(s):
+                parts.append(".{1,2}")
+                i += rng.randint(0, 1)
+                dots += 2
+            else:
+                parts.append(c)
+            i += 1
+        out.append("".join(parts))
+    return out
+
+
+def golden_collector_fuzz():
+    """>= 500 seeded regexes through the reference's process_query (preprocess, k-graph, OTFCollector::collect with its
+    robin_hood pop order) on the reference-written index files of tests/golden/cli: the candidate-bin sets the host
+    collector must reproduce bit for bit (tests/test_collector_vs_ref.py)."""
+    rng = random.Random(20251105)
+    cli = json.load(open(os.path.join(OUT, "cli.json"))) + json.load(open(os.path.join(OUT, "cli_c1.json")))
+    seen, out = set(), []
+    cwd = os.getcwd()
+    os.chdir(ROOT)
+    try:
+        for c in cli:
+            if c["index"] in seen:
+                continue
+            seen.add(c["index"])
+            records = [r for f in c["files"] for r in read_records(f)]
+            alphabet = "ACGT" if c["molecule"] == 0 else AA.decode()
+            n = 30 if "c1_" in c["index"] else (40 if c["reduction"] else 90)
+            aborted = 0
+            for q in fuzz_regexes(rng, records, alphabet, c["k"], n):
+                got = guarded(ob.ref_index_query, c["index"], q, False)
+                if got is None:
+                    aborted += 1
+                    continue
+                words = got[0]
+                bins = [b for b in range(len(c["files"])) if int(words[b // 64]) >> (b % 64) & 1]
+                out.append(dict(index=c["index"], regex=q, bins=bins))
+            print(c["index"], n, "regexes,", aborted, "aborted in the reference")
+    finally:
+        os.chdir(cwd)
+    with open(os.path.join(OUT, "collector_fuzz.json"), "w") as f:
+        json.dump(out, f, indent=0)
+    nonempty = sum(1 for c in out if c["bins"])
+    print("collector_fuzz.json:", len(out), "cases,", nonempty, "with candidate bins")
+
+
+def golden_rh_order():
+    """Pop orders of the real robin_hood::unordered_map for key lists shaped like a rank's sub-k-mer keys."""
+    rng = random.Random(99)
+    cases = []
+    for n in [1, 2, 3, 5, 7, 8, 9, 13, 20, 33, 64, 100, 257, 1000]:
+        for bits in [6, 15, 25, 60]:
+            keys = [rng.getrandbits(bits) for _ in range(n)]
+            cases.append(dict(keys=[str(k) for k in keys], order=[int(x) for x in ob.ref_rh_pop_order(keys)]))
+    json.dump(cases, open(os.path.join(OUT, "rh_order.json"), "w"))
+    print("rh_order.json:", len(cases), "cases")
+
+
+STEPS = {"decompose": golden_decompose, "ibf": golden_ibf, "hibf": golden_hibf, "regex": golden_regex,
+         "kgraph": golden_kgraph, "cli": golden_cli, "c1": golden_c1, "collector_fuzz": golden_collector_fuzz, "rh_order": golden_rh_order}
+
 if __name__ == "__main__":
     assert ob.have_ref(), "build oracle/_ref first: make -C oracle ref"
-    golden_decompose()
-    golden_ibf()
-    golden_hibf()
-    golden_regex()
-    golden_kgraph()
-    golden_cli()
+    for step in (sys.argv[1:] or list(STEPS)):
+        STEPS[step]()
     print("golden vectors written to", OUT)

@@ -121,3 +121,44 @@ def test_query_reports_unreadable_index_like_the_reference(tetrex, tmp_path):
     assert "Filepath to (H)IBF Index not valid" in out.stderr  # src/main.cpp:55
     out = subprocess.run([tetrex, "index", "-k", "13", "x", "y.fa"], capture_output=True, text=True, timeout=60)
     assert "Max kmer size for amino acids is 12" in out.stderr  # src/main.cpp:30
+
+
+# ------------------------------------------------------------------------------------- collector pop order
+def _pop_order(keys):
+    import ctypes as C
+    import numpy as np
+    h = C.CDLL(os.path.join(ROOT, "tetrex_b200", "lib", "libtrxhost.so"))
+    h.trxh_rank_pop_order.restype = C.c_uint64
+    h.trxh_rank_pop_order.argtypes = [C.POINTER(C.c_uint64), C.c_uint64, C.POINTER(C.c_uint32)]
+    k = np.ascontiguousarray(keys, dtype=np.uint64)
+    out = np.zeros(len(k), dtype=np.uint32)
+    n = h.trxh_rank_pop_order(k.ctypes.data_as(C.POINTER(C.c_uint64)), len(k), out.ctypes.data_as(C.POINTER(C.c_uint32)))
+    return out[:n].tolist()
+
+
+def test_rank_pop_order_equals_robin_hood_golden(tetrex):
+    """rh_order.hpp places keys exactly like the reference's robin_hood::unordered_map does (the collector drains a rank
+    in slot order, include/otf_collector.h:355-357): orders recorded from the real container, 1 … 1000 keys."""
+    cases = json.load(open(os.path.join(GOLDEN, "rh_order.json")))
+    assert len(cases) >= 50
+    for c in cases:
+        assert _pop_order([int(k) for k in c["keys"]]) == c["order"]
+
+
+def test_rank_pop_order_live_against_reference(tetrex):
+    from oracle import bindings as ob
+    if not ob.have_ref():
+        pytest.skip("oracle/_ref not built on this machine")
+    rng = random.Random(3)
+    for _ in range(400):
+        n = rng.choice([1, 2, 3, 7, 8, 9, 13, 50, 100, 400, 3000])
+        kind = rng.random()
+        if kind < 0.3:
+            keys = [rng.getrandbits(64) for _ in range(n)]
+        elif kind < 0.6:
+            keys = [rng.getrandbits(rng.choice([4, 10, 15, 25])) for _ in range(n)]
+        elif kind < 0.8:
+            keys = [rng.getrandbits(8) << 5 for _ in range(n)]  # same info bits, clustered homes
+        else:
+            keys = [rng.randrange(0, 40) * 32 ** rng.randrange(0, 5) for _ in range(n)]
+        assert _pop_order(keys) == ob.ref_rh_pop_order(keys).tolist()

@@ -10,6 +10,7 @@
 #include <unistd.h>
 
 #include "../../include/tetrex_host.h"
+#include "rh_order.hpp"
 #include "trx_host.hpp"
 
 namespace
@@ -142,6 +143,19 @@ int trxh_verify(void * hv, const uint64_t * cand_words, const char * regex, char
 void trxh_free(void * p)
 {
     free(p);
+}
+
+// host only: the order in which the collector drains a rank whose items arrived with these keys (duplicates are
+// absorbed).  out[j] = index of the j-th item popped; returns how many.
+uint64_t trxh_rank_pop_order(const uint64_t * keys, uint64_t n, uint32_t * out)
+{
+    trxh::rh_slots t;
+    for (uint64_t i = 0; i < n; ++i)
+        if (t.find(keys[i]) == trxh::rh_slots::npos)
+            t.insert_new(keys[i], static_cast<uint32_t>(i));
+    uint64_t j = 0;
+    t.for_each([&](uint32_t v) { out[j++] = v; });
+    return j;
 }
 
 } // extern "C"

@@ -8,13 +8,15 @@
 // path slots and reports which paths died; one trx_paths_or launch performs every push-copy, absorb and match OR.
 // Path bitvectors never leave HBM; only the 1-byte alive flags travel.
 //
-// Known difference: inside one rank the reference pops items in robin_hood hash-table order, this code in
-// arrival order.  The order only matters when two items with DIFFERENT shift counts collide on the same
-// (rank, sub-k-mer) key (SURVEY.md §7 hard part 3); tests/test_collector_vs_ref.py fuzzes this against the
-// compiled reference.
+// Order inside a rank: the reference drains a rank through `comp_table_[i].begin()` of a robin_hood map, i.e. in the
+// SLOT order of that table, and the order is observable — when two items of one rank collide on a later key
+// (e.g. `(XAC|C)DEF`, k = 4: "XACD" and "CD" both key as "ACD" because A packs to 0) the first one pushed keeps its
+// kmer_/shift_count_ (absorb, otf_collector.h:204-208) and decides whether the next symbol is probed.  rh_order.hpp
+// restates the container's slot placement, every rank is processed in exactly that order, and
+// tests/test_collector_vs_ref.py fuzzes the resulting candidate sets against the compiled reference's process_query.
 #include <algorithm>
-#include <unordered_map>
 
+#include "rh_order.hpp"
 #include "trx_host.hpp"
 
 namespace trxh
@@ -32,8 +34,16 @@ struct item
 
 struct bucket
 {
-    std::vector<item> items;
-    std::unordered_map<uint64_t, uint32_t> by_key; // kmer & submask → index into items
+    std::vector<item> items; // in arrival order; drained in the slot order of by_key
+    rh_slots by_key;         // kmer & submask → index into items, placed like comp_table_[rank] places it
+    // the items in the order OTFCollector::collect pops them (include/otf_collector.h:355-357)
+    void sort_into_pop_order()
+    {
+        std::vector<item> ordered;
+        ordered.reserve(items.size());
+        by_key.for_each([&](uint32_t i) { ordered.push_back(items[i]); });
+        items.swap(ordered);
+    }
 };
 
 // view of the index's persistent slot pool for one query
@@ -118,11 +128,11 @@ bitvector collect(kgraph const & g, DeviceIndex & index, collect_stats * stats, 
     auto push = [&](int node, item it, bool may_hand_over) {
         bucket & b = table[g.rank[node]];
         uint64_t const key = it.kmer & submask;
-        auto found = b.by_key.find(key);
-        if (found != b.by_key.end())
+        uint32_t const found = b.by_key.find(key);
+        if (found != rh_slots::npos)
         {
             // absorb (otf_collector.h:204-208): only the path is merged, kmer_/shift_count_ of the first arrival stay
-            or_dst.push_back(b.items[found->second].slot);
+            or_dst.push_back(b.items[found].slot);
             or_src.push_back(it.slot);
             return;
         }
@@ -133,7 +143,7 @@ bitvector collect(kgraph const & g, DeviceIndex & index, collect_stats * stats, 
             or_src.push_back(it.slot);
             it.slot = copy;
         }
-        b.by_key.emplace(key, static_cast<uint32_t>(b.items.size()));
+        b.by_key.insert_new(key, static_cast<uint32_t>(b.items.size()));
         b.items.push_back(it);
     };
 
@@ -149,6 +159,7 @@ bitvector collect(kgraph const & g, DeviceIndex & index, collect_stats * stats, 
         bucket & b = table[r];
         if (b.items.empty())
             continue;
+        b.sort_into_pop_order();
         int const node = node_of_rank[r];
         int const sym = g.symbol[node];
         or_dst.clear();

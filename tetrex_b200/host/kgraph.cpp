@@ -3,7 +3,7 @@
 // Behavioural restatement of construct_kgraph (src/construct_nfa.cpp:1-335) + update_arc_map
 // (src/construction_tools.cpp:136-158) + OTFCollector::determine_top_sort (include/otf_collector.h:328-339).
 // Which k-mers a query probes is decided here, so node numbering, arc order and the two-slot arc map follow
-// the reference step for step (tests/test_kgraph_vs_ref.py compares the result with the compiled reference
+// the reference step for step (tests/test_host_cpu.py compares the result with the compiled reference
 // node by node):  nodes are numbered in creation order; an arc from a non-split node overwrites both slots;
 // a split node fills slot 1 then slot 2; '*' and '+' are unrolled to at most k-1 repetitions; {m,n} copies the
 // operand; a quantifier whose operand is not the first thing on the stack concatenates immediately and eats the

@@ -1,7 +1,11 @@
 // regex_front.cpp — the per-query host work that decides which k-mers exist: query pre-processing
 // (src/query.cpp:78-155) and infix → postfix translation (include/utils.h:96-468, src/utils.cpp:3-15).
-// Behavioural restatement: same token classes, same precedences (| = 1 < concat = 2 < * + ? {} = 3), '-' as the
-// explicit concatenation operator, '.' and [^…] expanded over the 20 amino acids in the reference's orders.
+// Out-of-perf-scope host code kept for CLI parity, and deliberately the CLOSEST thing to the reference in this
+// repository: the tokenizer's control flow follows PostfixConverter's and the error strings are the reference's word
+// for word, because `tetrex query` must accept, reject and report exactly what the reference does; only the
+// representation (one function, own token types) is this repo's.  Same token classes, same precedences
+// (| = 1 < concat = 2 < * + ? {} = 3), '-' as the explicit concatenation operator, '.' and [^…] expanded over the
+// 20 amino acids in the reference's orders (a required constant).
 #include <algorithm>
 #include <iostream>
 
