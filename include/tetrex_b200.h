@@ -221,7 +221,8 @@ int trx_regex_scan(trx_text_t *text, trx_regex_t *re, const uint64_t *candidate_
  * other work against a scan through _end); their kernels run back to back on the device while the host is already
  * planning the next one — the ~50 us of per-call latency (plan, launches, read-back, sync) is paid once per
  * batch instead of once per regex.  A further _begin with every slot taken returns TRX_ECAPACITY.  The regex handle and
- * the candidate / map arrays are only read during _begin.  Tickets may be ended in any order. */
+ * the candidate / map arrays are only read during _begin.  Tickets may be ended in any order.  _end with hits == NULL
+ * and n_hits == NULL abandons the scan: it waits for it and frees the slot without delivering anything. */
 #define TRX_SCAN_SLOTS 4
 int trx_regex_scan_begin(trx_text_t *text, trx_regex_t *re, const uint64_t *candidate_bin_words, int reverse_strand,
                          const uint8_t *map256, uint64_t cap, int *ticket);

@@ -129,6 +129,8 @@ def ref():
                                              C.POINTER(u64p), u64p]
         lib.ref_re2_scan_records.restype = C.c_int64
         lib.ref_re2_scan_records.argtypes = [C.c_char_p, C.c_int, C.c_void_p, u64p, C.c_uint64, C.c_int]
+        lib.ref_re2_scan_records_hits.restype = C.c_int64
+        lib.ref_re2_scan_records_hits.argtypes = [C.c_char_p, C.c_int, C.c_void_p, u64p, C.c_uint64, C.c_int, u32p, C.c_uint64]
         lib.ref_rh_pop_order.restype = C.c_uint64
         lib.ref_rh_pop_order.argtypes = [u64p, C.c_uint64, u32p]
         _ref = lib
@@ -455,6 +457,21 @@ def ref_index_query(index_path, regex, verify=True, threads=1, stdout_path=None)
         if stdout_path is None:
             os.unlink(tmp)
     return words[:n].copy(), text
+
+
+def ref_scan_records_hits(pattern: str, posix_longest: bool, text: np.ndarray, rec_offsets: np.ndarray, threads: int,
+                          cap: int = 1 << 20) -> np.ndarray:
+    """RE2 FindAndConsume over in-memory records: (n, 3) uint32 rows (record, start, end) in print order."""
+    text = np.ascontiguousarray(text, dtype=np.uint8)
+    offs = np.ascontiguousarray(rec_offsets, dtype=np.uint64)
+    out = np.zeros((cap, 3), dtype=np.uint32)
+    n = ref().ref_re2_scan_records_hits(pattern.encode(), int(posix_longest), text.ctypes.data, _p(offs, u64p), len(offs) - 1,
+                                        threads, _p(out, u32p), cap)
+    if n < 0:
+        raise ValueError(ref().ref_last_error().decode())
+    if n > cap:
+        return ref_scan_records_hits(pattern, posix_longest, text, rec_offsets, threads, cap=int(n))
+    return out[:n].copy()
 
 
 def ref_rh_pop_order(keys) -> np.ndarray:

@@ -842,3 +842,57 @@ uint64_t ref_rh_pop_order(uint64_t const * keys, uint64_t n, uint32_t * out)
 }
 
 } // extern "C"
+
+extern "C"
+{
+
+// ref_re2_scan_records with the matches returned: (record, start, end) triples in (record, start) order — the order
+// iter_disk_search prints them with -t 1.  Returns the total number of matches (may exceed cap; then only the first
+// cap triples are written).
+int64_t ref_re2_scan_records_hits(char const * regex, int posix_longest, char const * text, uint64_t const * rec_offsets,
+                                  uint64_t n_records, int threads, uint32_t * out_triples, uint64_t cap)
+{
+    std::string wrapped = std::string("(") + regex + ")";
+    std::unique_ptr<re2::RE2> re;
+    if (posix_longest)
+        re = std::make_unique<re2::RE2>(wrapped, re2::RE2::POSIX);
+    else
+        re = std::make_unique<re2::RE2>(wrapped);
+    if (!re->ok())
+    {
+        g_err = re->error();
+        return -1;
+    }
+    if (threads < 1)
+        threads = 1;
+    std::vector<std::vector<uint32_t>> per(n_records);
+#pragma omp parallel for schedule(dynamic, 64) num_threads(threads)
+    for (int64_t r = 0; r < static_cast<int64_t>(n_records); ++r)
+    {
+        char const * base = text + rec_offsets[r];
+        re2::StringPiece content(base, rec_offsets[r + 1] - rec_offsets[r]);
+        re2::StringPiece match;
+        while (RE2::FindAndConsume(&content, *re, &match))
+        {
+            if (match.size() == 0)
+                break;
+            per[r].push_back(static_cast<uint32_t>(match.data() - base));
+            per[r].push_back(static_cast<uint32_t>(match.data() - base + match.size()));
+        }
+    }
+    int64_t total = 0;
+    for (uint64_t r = 0; r < n_records; ++r)
+        for (size_t i = 0; i + 1 < per[r].size(); i += 2)
+        {
+            if (static_cast<uint64_t>(total) < cap)
+            {
+                out_triples[3 * total] = static_cast<uint32_t>(r);
+                out_triples[3 * total + 1] = per[r][i];
+                out_triples[3 * total + 2] = per[r][i + 1];
+            }
+            ++total;
+        }
+    return total;
+}
+
+} // extern "C"

@@ -388,6 +388,90 @@ def golden_collector_fuzz():
     print("collector_fuzz.json:", len(out), "cases,", nonempty, "with candidate bins")
 
 
+def golden_prosite_batch():
+    """BASELINE config 3's pattern population (synth.prosite_patterns(1000, 1000)) through RE2 exactly as
+    iter_disk_search uses it (POSIX longest, FindAndConsume) over the /100 twin of the Swissprot-shaped collection
+    (5700 records, 2.0 M residues) with 10 % of the patterns planted: every hit of every pattern."""
+    from tetrex_b200 import synth
+    residues, offs, rec_bin, _ = synth.swissprot_like(5700, 1024)
+    pats = synth.prosite_patterns(1000, 1000)
+    planted = synth.plant_patterns(residues, offs, pats)
+    rows = []
+    for pi, pat in enumerate(pats):
+        h = ob.ref_scan_records_hits(pat, True, residues, offs, 8)
+        rows.append(np.concatenate([np.full((len(h), 1), pi, dtype=np.uint32), h], axis=1))
+    hits = np.concatenate(rows)
+    np.savez_compressed(os.path.join(OUT, "prosite_batch.npz"), hits=hits, planted=np.array(planted, dtype=np.uint32),
+                        text_crc=np.uint64(int(np.bitwise_xor.reduce(residues.astype(np.uint64) * np.arange(1, len(residues) + 1, dtype=np.uint64)))))
+    per = np.bincount(hits[:, 0], minlength=len(pats))
+    print("prosite_batch.npz:", len(hits), "hits,", int((per > 0).sum()), "patterns with hits,", len(planted), "planted")
+
+
+def per_bin_kmers(residues, offs, rec_bin, n_bins, k=6):
+    """What HIBFIndex::populate_index hands to seqan::hibf::config::input_fn (include/index_hibf.h:110-122): every
+    peptide k-mer of every record of a bin, duplicates included, through the reference's decomposer."""
+    per = [[] for _ in range(n_bins)]
+    raw = residues.tobytes()
+    for r in range(len(offs) - 1):
+        per[int(rec_bin[r])].append(ob.ref_decompose(1, k, 0, raw[int(offs[r]):int(offs[r + 1])]))
+    return [np.concatenate(p) if p else np.zeros(0, dtype=np.uint64) for p in per]
+
+
+def golden_c2_twin_hibf():
+    """The /100 twin of BASELINE config 2 (5700 Swissprot-shaped records in 1024 user bins, k = 6, h = 3, FPR 0.05) laid
+    out and built by seqan::hibf itself (sketches, DP layout, split + merged bins) exactly as HIBFIndex::populate_index
+    calls it; tables + the reference's membership answers for present and absent 6-mers."""
+    from tetrex_b200 import synth
+    residues, offs, rec_bin, _ = synth.swissprot_like(5700, 1024)
+    per = per_bin_kmers(residues, offs, rec_bin, 1024)
+    rh = ob.RefHIBF(per, 3, 0.05, 1)
+    tb = rh.tables()
+    rng = np.random.default_rng(1024)
+    allk = np.concatenate(per)
+    q = np.concatenate([rng.choice(allk, 6000), rng.integers(0, 1 << 30, 6000, dtype=np.uint64)])
+    tb.save(os.path.join(OUT, "hibf_c2twin_tables.npz"))
+    np.savez_compressed(os.path.join(OUT, "hibf_c2twin_query.npz"), query=q, hits=rh.membership(q, 8))
+    split = sum(int((np.bincount(u[u < 2 ** 63].astype(np.int64)) > 1).sum()) for u in tb.user_bin)
+    print("hibf_c2twin:", tb.n_ibfs, "IBFs,", sum(w.nbytes for w in tb.words) / 1e6, "MB,", split, "split user bins")
+
+
+def golden_cli_ws():
+    """kseq's raw-line semantics (include/kseq.h:198-202): sequence lines keep embedded / trailing blanks and tabs, only
+    one trailing \\r goes, a line starting with '@' or '+' ends a FASTA record too.  Three small peptide bins written
+    with such lines; the reference's record lengths, k-mers and printed start,end coordinates all depend on it."""
+    data = os.path.join(ROOT, "tests", "data")
+    bodies = [
+        b">ws0_a first record\r\nMKTAYIAKQR \r\nQISFVKSHFS\t\r\nRQLEERLGLI\r\n>ws0_b\nLMAEGLYN  WKCDEDEFH\nGLYNWK\n",
+        b">ws1_a\tcomment with tab\nHHCAKCW \n\n \nPWDEHIIK\n@ws1_b in the middle\nMKAPLWLMAQGLYN\nKRRT\n",
+        b">ws2_a\nCAACLLLV\r\n\r\nGQPNK\t\tMKTA\n>ws2_b\nAAAAAAAA \nLMAEGLYN",
+    ]
+    files = []
+    for b, body in enumerate(bodies):
+        path = os.path.join(data, f"ws_{b}.fa")
+        open(path, "wb").write(body)
+        files.append(os.path.relpath(path, ROOT))
+    cwd = os.getcwd()
+    os.chdir(ROOT)
+    out = []
+    try:
+        idx = os.path.join("tests", "golden", "cli", "ws_flat_k3.ibf")
+        ob.ref_index_build(files, 3, 0.05, 3, 1, 0, 0, idx)
+        for q in ["LMA(E|Q)GLYN", "GLYNWK", "MKTA", "KRRT", "W.PWDE", "LLLVGQ", "HFS.RQL", "PNK..MK", "AAAA"]:
+            got = guarded(ob.ref_index_query, idx, q, True)
+            if got is None:
+                print("reference aborts on", q)
+                continue
+            words, text = got
+            bins = [b for b in range(len(files)) if int(words[b // 64]) >> (b % 64) & 1]
+            out.append(dict(index=idx, files=files, molecule=1, k=3, flavor=0, reduction=0, regex=q, bins=bins, stdout=text))
+    finally:
+        os.chdir(cwd)
+    json.dump(out, open(os.path.join(OUT, "cli_ws.json"), "w"), indent=0)
+    print("cli_ws.json:", len(out), "queries,", sum(len(c["stdout"].splitlines()) for c in out), "lines")
+    for c in out:
+        print(c["regex"], c["bins"], repr(c["stdout"]))
+
+
 def golden_rh_order():
     """Pop orders of the real robin_hood::unordered_map for key lists shaped like a rank's sub-k-mer keys."""
     rng = random.Random(99)
@@ -401,7 +485,8 @@ def golden_rh_order():
 
 
 STEPS = {"decompose": golden_decompose, "ibf": golden_ibf, "hibf": golden_hibf, "regex": golden_regex,
-         "kgraph": golden_kgraph, "cli": golden_cli, "c1": golden_c1, "collector_fuzz": golden_collector_fuzz, "rh_order": golden_rh_order}
+         "kgraph": golden_kgraph, "cli": golden_cli, "c1": golden_c1, "collector_fuzz": golden_collector_fuzz, "rh_order": golden_rh_order,
+         "prosite_batch": golden_prosite_batch, "c2_twin_hibf": golden_c2_twin_hibf, "cli_ws": golden_cli_ws}
 
 if __name__ == "__main__":
     assert ob.have_ref(), "build oracle/_ref first: make -C oracle ref"

@@ -210,8 +210,10 @@ def test_path_algebra(ctx, bins):
 
 
 # ------------------------------------------------------------------------------------------------ a8
-@pytest.mark.parametrize("name", ["hibf_small", "hibf_100", "hibf_300"])
+@pytest.mark.parametrize("name", ["hibf_small", "hibf_100", "hibf_300", "hibf_c2twin"])
 def test_hibf_membership_golden(ctx, golden_dir, name):
+    """hibf_c2twin = the /100 twin of BASELINE config 2 (1024 user bins, peptide 6-mers) laid out by seqan::hibf itself:
+    65 IBFs, 1007 of the 1024 user bins split over several technical bins."""
     tb = ob.HIBFTables.load(os.path.join(golden_dir, name + "_tables.npz"))
     q = np.load(os.path.join(golden_dir, name + "_query.npz"))
     h = t.HIBF.from_tables(ctx, tb)
@@ -245,6 +247,26 @@ def test_hibf_large_batch_matches_oracle(ctx, golden_dir):
     q = rng.integers(0, 2 ** 40, 300000, dtype=np.uint64)
     h = t.HIBF.from_tables(ctx, tb)
     assert np.array_equal(h.membership(q), tb.membership(q, threads=8))
+    h.close()
+
+
+@pytest.mark.parametrize("route", ["windows", "frontier"])
+def test_hibf_seqan_layout_c2_twin_large_batch(ctx, golden_dir, route, monkeypatch):
+    """K3's bench route (root + L2 windows + merge: batches > 2048 k-mers) and the frontier route on the seqan-built
+    1024-user-bin layout, 400 000 k-mers (half present), against the C port — which the golden file pins to seqan's own
+    membership_for on this very layout (test_oracle_golden / hibf_c2twin_query.npz)."""
+    if route == "frontier":
+        monkeypatch.setenv("TRX_HIBF_FUSED", "off")
+    tb = ob.HIBFTables.load(os.path.join(golden_dir, "hibf_c2twin_tables.npz"))
+    gq = np.load(os.path.join(golden_dir, "hibf_c2twin_query.npz"))
+    assert np.array_equal(tb.membership(gq["query"], threads=8), gq["hits"])  # the port agrees with seqan here
+    rng = np.random.default_rng(5)
+    q = np.concatenate([rng.choice(gq["query"][:6000], 200000), rng.integers(0, 1 << 30, 200000, dtype=np.uint64)])
+    rng.shuffle(q)
+    h = t.HIBF.from_tables(ctx, tb)
+    got, st = h.membership(q, stats=True)
+    assert np.array_equal(got, tb.membership(q, threads=8))
+    assert st[0] > len(q)  # merged bins were entered
     h.close()
 
 

@@ -307,3 +307,58 @@ def test_128_positions_two_word_state(ctx):
     pat2 = motif[:70].decode() + ".{3,9}" + motif[79:90].decode()
     assert np.array_equal(txt.scan(t.Regex(pat2, True)), expected_hits(seqs, [0, 1], pat2, True, finder))
     txt.close()
+
+
+def test_prosite_pattern_batch_equals_re2(ctx, golden_dir, monkeypatch):
+    """BASELINE config 3's pattern population — synth.prosite_patterns(1000, 1000), 10 % planted — over the /100 twin of
+    the Swissprot-shaped collection: EVERY hit of EVERY pattern equals what RE2 (POSIX longest, FindAndConsume, as
+    include/query.h:146-149 + src/query.cpp:194-237 use it) returned for the same text (tests/golden/prosite_batch.npz,
+    made by tests/golden/make_golden.py from oracle/_ref).  Run pipelined with the planner's own choice of phase 1, and
+    again with each phase-1 kind forced, so window, atoms and the exact automaton all face the whole population."""
+    from tetrex_b200 import synth
+    z = np.load(os.path.join(golden_dir, "prosite_batch.npz"))
+    residues, offs, rec_bin, _ = synth.swissprot_like(5700, 1024)
+    pats = synth.prosite_patterns(1000, 1000)
+    planted = synth.plant_patterns(residues, offs, pats)
+    assert planted == z["planted"].tolist()
+    crc = int(np.bitwise_xor.reduce(residues.astype(np.uint64) * np.arange(1, len(residues) + 1, dtype=np.uint64)))
+    assert crc == int(z["text_crc"]), "the seeded twin is not the text the golden hits were made on"
+    want_all = z["hits"]
+    assert len(want_all) >= 10000
+    bounds = np.searchsorted(want_all[:, 0], np.arange(len(pats) + 1))
+    txt = t.Text(ctx, residues, offs, rec_bin, 1024)
+    regexes = [t.Regex(p, True) for p in pats]
+
+    def check(results, label):
+        kinds_wrong = []
+        for pi, got in enumerate(results):
+            want = want_all[bounds[pi]:bounds[pi + 1], 1:]
+            g = got[:, 1:]  # (record, start, end); bin = rec_bin[record]
+            if not (np.array_equal(g, want) and np.array_equal(got[:, 0], rec_bin[got[:, 1]])):
+                kinds_wrong.append((pi, pats[pi], len(g), len(want)))
+        assert not kinds_wrong, f"{label}: {len(kinds_wrong)} patterns differ from RE2, first {kinds_wrong[:3]}"
+
+    freq = np.bincount(residues, minlength=256).astype(np.float64)
+    freq /= freq.sum()
+    kinds = {"window": 0, "atoms": 0, "none": 0}
+    for rx in regexes:
+        kinds[rx.filter_plan(freq)["kind"]] += 1
+    assert kinds["window"] > 100 and kinds["atoms"] > 50, kinds
+    check(txt.scan_many(regexes, cap=1 << 16, depth=3), "planner's choice, 3 scans in flight")
+    for forced in ("off", "atoms", "window"):
+        monkeypatch.setenv("TRX_REGEX_FILTER", forced)
+        sub = regexes if forced == "off" else regexes[::3]
+        res = [txt.scan(rx, cap=1 << 16) for rx in sub]
+        if forced != "off":
+            full = [np.zeros((0, 4), dtype=np.uint32)] * len(regexes)
+            for i, r in zip(range(0, len(regexes), 3), res):
+                full[i] = r
+            wrong = [i for i in range(0, len(regexes), 3)
+                     if not np.array_equal(full[i][:, 1:], want_all[bounds[i]:bounds[i + 1], 1:])]
+            assert not wrong, (forced, wrong[:5])
+        else:
+            check(res, "exact automaton for every pattern")
+        monkeypatch.delenv("TRX_REGEX_FILTER")
+    for rx in regexes:
+        rx.close()
+    txt.close()

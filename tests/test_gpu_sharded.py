@@ -47,7 +47,9 @@ def collection(tmp_path_factory):
     return build(str(tmp_path_factory.mktemp("sharded")))
 
 
-@pytest.mark.parametrize("kind,shards", [("flat", 2), ("flat", 4), ("hibf", 2), ("hibf", 3)])
+# ("hibf", 8): more shards than 64-bin words (256 bins = 4 words) — four of the eight shards own no bins at all and must
+# answer "no lines" instead of failing to upload an empty text (a 256-bin replicated HIBF on an 8-GPU box)
+@pytest.mark.parametrize("kind,shards", [("flat", 2), ("flat", 4), ("hibf", 2), ("hibf", 3), ("hibf", 8)])
 def test_sharded_query_equals_unsharded(ctx, collection, kind, shards):
     path = collection[kind]
     reduce_ = ThreadAllReduce(shards)

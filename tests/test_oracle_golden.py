@@ -58,7 +58,7 @@ def test_ibf_golden(golden_dir):
         assert np.array_equal(o.bulk_contains(z[f"query_{i}"], threads=2), z[f"hits_{i}"])
 
 
-@pytest.mark.parametrize("name", ["hibf_small", "hibf_100", "hibf_300"])
+@pytest.mark.parametrize("name", ["hibf_small", "hibf_100", "hibf_300", "hibf_c2twin"])
 def test_hibf_golden(golden_dir, name):
     tb = ob.HIBFTables.load(os.path.join(golden_dir, name + "_tables.npz"))
     q = np.load(os.path.join(golden_dir, name + "_query.npz"))

@@ -1201,9 +1201,18 @@ int trx_regex_scan_begin(trx_text_t * t, trx_regex_t * re, const uint64_t * cand
 
 int trx_regex_scan_end(trx_text_t * t, int ticket, trx_hit * hits, uint64_t * n_hits, uint64_t * stats)
 {
-    if (!t || !n_hits || ticket < 0 || ticket >= trx_text::kScanSlots || !t->slots[ticket].busy)
+    if (!t || ticket < 0 || ticket >= trx_text::kScanSlots || !t->slots[ticket].busy)
         return set_error(TRX_EINVAL, "trx_regex_scan_end: bad ticket");
     trx_text::scan_slot & sl = t->slots[ticket];
+    if (!hits && !n_hits)
+    {
+        // abandon: the caller gave up on this scan (error path); wait it out and free the slot
+        cudaEventSynchronize(sl.done);
+        sl.busy = false;
+        return TRX_OK;
+    }
+    if (!n_hits)
+        return set_error(TRX_EINVAL, "trx_regex_scan_end: n_hits is NULL");
     uint64_t const cap = sl.cap;
     if (cap && !hits)
         return set_error(TRX_EINVAL, "trx_regex_scan_end: hits is NULL");

@@ -24,58 +24,85 @@ std::vector<fasta_record> read_fasta(std::string const & path)
         if (n < 0)
             throw error("read error in " + path);
     }
+    // kseq_read (include/kseq.h:181-226) over the whole buffer, byte for byte:
+    //  * a record starts at the next '>' or '@' — ANYWHERE in the stream when no header character is pending (file start,
+    //    after a FASTQ record), else at the header character that ended the previous record's sequence;
+    //  * name = up to the first isspace(); comment = rest of that line unless the name ended at '\n';
+    //  * sequence: a line starting with '>', '+' or '@' ends it (whatever the record's own marker); empty lines are
+    //    skipped; every other line is appended RAW (spaces, tabs and all) minus one trailing '\r' when the sequence is
+    //    longer than one byte (ks_getuntil2's rule looks at the accumulated string, :145);
+    //  * '+' starts a FASTQ quality block: the rest of that line is dropped, quality lines are read until they are as
+    //    long as the sequence; a length mismatch (-2) ends the reading of the file, as the callers' `>= 0` loops do.
     std::vector<fasta_record> out;
     size_t i = 0, n = data.size();
-    auto line_end = [&](size_t p) {
-        size_t e = data.find('\n', p);
-        return e == std::string::npos ? n : e;
+    auto append_line = [&](std::string & str, size_t & pos) { // ks_getuntil2(KS_SEP_LINE, append)
+        size_t e = data.find('\n', pos);
+        if (e == std::string::npos)
+            e = n;
+        str.append(data, pos, e - pos);
+        pos = e < n ? e + 1 : n;
+        if (str.size() > 1 && str.back() == '\r')
+            str.pop_back();
     };
-    // skip to the first header
-    while (i < n && data[i] != '>' && data[i] != '@')
-        i = line_end(i) + 1;
-    while (i < n)
+    int last_char = 0;
+    for (;;)
     {
-        char const marker = data[i];
-        size_t e = line_end(i);
-        size_t he = e;
-        if (he > i && data[he - 1] == '\r')
-            --he;
+        if (last_char == 0)
+        {
+            while (i < n && data[i] != '>' && data[i] != '@')
+                ++i;
+            if (i >= n)
+                break;
+            last_char = data[i++];
+        }
         fasta_record rec;
-        size_t p = i + 1;
-        size_t ws = p;
-        while (ws < he && !isspace(static_cast<unsigned char>(data[ws])))
+        if (i >= n)
+            break; // ks_getuntil on an exhausted stream: -1, normal exit
+        size_t ws = i;
+        while (ws < n && !isspace(static_cast<unsigned char>(data[ws])))
             ++ws;
-        rec.name.assign(data, p, ws - p);
-        if (ws < he)
-            rec.comment.assign(data, ws + 1, he - ws - 1);
-        i = e + 1;
-        // sequence lines until the next header ('>' / '@' at line start) or, for FASTQ, the '+' line
-        while (i < n && data[i] != '>' && data[i] != '+' && !(marker == '@' && data[i] == '@'))
+        rec.name.assign(data, i, ws - i);
+        int const delim = ws < n ? data[ws] : 0;
+        i = ws < n ? ws + 1 : n;
+        if (delim != '\n' && ws < n)
+            append_line(rec.comment, i);
+        int c = -1;
+        while (i < n)
         {
-            e = line_end(i);
-            for (size_t q = i; q < e; ++q)
+            c = static_cast<unsigned char>(data[i++]);
+            if (c == '>' || c == '+' || c == '@')
+                break;
+            if (c == '\n')
             {
-                unsigned char c = static_cast<unsigned char>(data[q]);
-                if (isgraph(c)) // kseq keeps graphical characters only
-                    rec.seq.push_back(static_cast<char>(c));
+                c = -1;
+                continue;
             }
-            i = e + 1;
+            rec.seq.push_back(static_cast<char>(c));
+            append_line(rec.seq, i);
+            c = -1;
         }
-        if (i < n && data[i] == '+')
+        last_char = (c == '>' || c == '@') ? c : last_char;
+        if (c != '+')
         {
-            // FASTQ: skip the '+' line and as many quality characters as there are bases
-            i = line_end(i) + 1;
-            size_t q = 0;
-            while (i < n && q < rec.seq.size())
-            {
-                e = line_end(i);
-                size_t le = e;
-                if (le > i && data[le - 1] == '\r')
-                    --le;
-                q += le - i;
-                i = e + 1;
-            }
+            if (c != '>' && c != '@')
+                last_char = -1; // end of stream: this was the last record
+            out.push_back(std::move(rec));
+            if (last_char == -1)
+                break;
+            continue;
         }
+        // FASTQ
+        while (i < n && data[i] != '\n')
+            ++i;
+        if (i >= n)
+            break; // -2: no quality string
+        ++i;
+        std::string qual;
+        while (i < n && qual.size() < rec.seq.size())
+            append_line(qual, i);
+        last_char = 0;
+        if (qual.size() != rec.seq.size())
+            break; // -2: the callers stop reading this file here, the record is not delivered
         out.push_back(std::move(rec));
     }
     return out;

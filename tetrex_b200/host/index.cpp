@@ -87,15 +87,18 @@ struct library
     uint64_t indexed{};             // records of length >= k
 };
 
-// bins outside [first_bin, last_bin) are skipped (they keep their ids and simply have no records): a verify shard
+// bins that are not wanted are skipped (they keep their ids and simply have no records): a verify shard, or a
+// one-shot query that only needs its candidate bins
 library read_library(std::vector<std::string> const & files, int molecule, unsigned k, bool announce_short,
-                     size_t first_bin = 0, size_t last_bin = SIZE_MAX)
+                     std::vector<bool> const * want = nullptr)
 {
     library lib;
     lib.offsets.push_back(0);
     lib.bin_emits.assign(files.size(), 0);
-    for (size_t b = first_bin; b < files.size() && b < last_bin; ++b)
+    for (size_t b = 0; b < files.size(); ++b)
     {
+        if (want && !(*want)[b])
+            continue;
         for (fasta_record & rec : read_fasta(files[b]))
         {
             if (rec.seq.size() < k)
@@ -314,6 +317,7 @@ void DeviceIndex::build(index_arguments const & args)
     text_->offsets = std::move(lib.offsets);
     text_->rec_bin = std::move(lib.rec_bin);
     text_->residues = std::move(lib.residues);
+    text_->loaded.assign(files.size(), true);
     std::cerr << "Indexed " << seq_count_ << " sequences across " << img_.bin_count << " bins." << std::endl;
     if (img_.bin_count == 1)
         std::cerr << "[WARNING] The indexed reference library was not split into bins. The TetRex runtime will be "
@@ -401,22 +405,48 @@ uint64_t DeviceIndex::shard_words() const
     return base + (shard_index_ < extra ? 1 : 0);
 }
 
-DeviceIndex::text_store const & DeviceIndex::text()
+DeviceIndex::text_store const & DeviceIndex::text(bitvector const & cand)
 {
-    if (!text_)
+    // iter_disk_search opens acid_libs_[bin] of the CANDIDATE bins only, per query (include/query.h:126-131,171-177):
+    // a moved file of a bin that is not a candidate is not an error, and a one-shot `tetrex query` must not pay for
+    // parsing and uploading the whole collection.  The store keeps what it has loaded; it grows to the union when a
+    // later query needs more, and takes every bin of the shard once a query asks for more than a quarter of them (a
+    // resident process ends up with the whole text in HBM, where K4 wants it).
+    size_t const n_bins = img_.acid_libs.size();
+    size_t const first_bin = shard_count_ > 1 ? shard_word_begin() * 64 : 0;
+    size_t const last_bin = std::min<size_t>(n_bins, shard_count_ > 1 ? (shard_word_begin() + shard_words()) * 64 : n_bins);
+    auto wanted = [&](size_t b) { return b / 64 < cand.size() && ((cand[b / 64] >> (b % 64)) & 1); };
+    bool missing = !text_;
+    size_t n_wanted = 0;
+    for (size_t b = first_bin; b < last_bin; ++b)
+        if (wanted(b))
+        {
+            ++n_wanted;
+            if (text_ && !text_->loaded[b])
+                missing = true;
+        }
+    if (missing)
     {
-        // iter_disk_search re-opens acid_libs_[bin] per query (include/query.h:126-131,171-177)
-        size_t const first_bin = shard_count_ > 1 ? shard_word_begin() * 64 : 0;
-        size_t const last_bin = shard_count_ > 1 ? (shard_word_begin() + shard_words()) * 64 : SIZE_MAX;
-        for (size_t b = first_bin; b < img_.acid_libs.size() && b < last_bin; ++b)
-            if (!std::filesystem::exists(img_.acid_libs[b]))
+        std::vector<bool> load(n_bins, false);
+        bool const everything = preload_all_ || n_wanted * 4 > last_bin - first_bin;
+        for (size_t b = first_bin; b < last_bin; ++b)
+            load[b] = everything || wanted(b) || (text_ && text_->loaded[b]);
+        for (size_t b = first_bin; b < last_bin; ++b)
+            if (load[b] && (everything ? wanted(b) : true) && !std::filesystem::exists(img_.acid_libs[b]))
                 throw error("File not found. Did you move/rename an indexed file?");
-        library lib = read_library(img_.acid_libs, is_dna() ? TRX_MOL_NA : TRX_MOL_AA, img_.k, false, first_bin, last_bin);
+        if (everything) // bins nobody asked for: a missing file only means that bin has no text yet
+            for (size_t b = first_bin; b < last_bin; ++b)
+                if (load[b] && !wanted(b) && !std::filesystem::exists(img_.acid_libs[b]))
+                    load[b] = false;
+        library lib = read_library(img_.acid_libs, is_dna() ? TRX_MOL_NA : TRX_MOL_AA, img_.k, false, &load);
+        if (text_ && text_->text)
+            trx_text_destroy(text_->text);
         text_ = std::make_unique<text_store>();
         text_->names = std::move(lib.names);
         text_->offsets = std::move(lib.offsets);
         text_->rec_bin = std::move(lib.rec_bin);
         text_->residues = std::move(lib.residues);
+        text_->loaded = std::move(load);
     }
     if (!text_->text)
         check(trx_text_upload(ctx_, reinterpret_cast<uint8_t const *>(text_->residues.data()), text_->offsets.data(),

@@ -101,7 +101,6 @@ namespace
 uint64_t search_impl(bitvector const & hits_in, std::string const & query_in, DeviceIndex & index, std::ostream * out,
                      std::ostream * rev_out)
 {
-    DeviceIndex::text_store const & store = index.text();
     std::vector<std::string> const & libs = index.acid_libs();
     // compute_set_bins (src/query.cpp:40-76): a one-bin library is always scanned
     bitvector cand((libs.size() + 63) / 64, 0);
@@ -114,6 +113,13 @@ uint64_t search_impl(bitvector const & hits_in, std::string const & query_in, De
         for (size_t w = 0; w < cand.size(); ++w)
             if (w < index.shard_word_begin() || w >= index.shard_word_begin() + index.shard_words())
                 cand[w] = 0;
+    if (libs.size() % 64) // bits past the last bin never name a file
+        cand.back() &= (1ull << (libs.size() % 64)) - 1;
+    // nothing to verify here — no candidate among this shard's bins, or a shard that owns no bins at all (more shards
+    // than 64-bin words): the reference's loop over set bins simply does not execute (include/query.h:120-139)
+    if (popcount(cand) == 0)
+        return 0;
+    DeviceIndex::text_store const & store = index.text(cand);
 
     std::string query = query_in;
     bool const dna = index.is_dna();
@@ -133,10 +139,23 @@ uint64_t search_impl(bitvector const & hits_in, std::string const & query_in, De
         uint64_t const cap = 4096;
         check(trx_regex_scan_begin(store.text, rx.re, cand.data(), 0, map, cap, &t_fwd));
         int const rc_begin = trx_regex_scan_begin(store.text, rx.re, cand.data(), 1, nullptr, cap, &t_rev);
-        auto finish = [&](int ticket, bool reverse, uint8_t const * m) {
+        // a ticket that is not ended keeps its slot busy on the persistent text handle: whatever happens below, both
+        // are ended before this scope is left
+        struct ticket_guard
+        {
+            trx_text_t * text;
+            int * ticket;
+            ~ticket_guard()
+            {
+                if (*ticket >= 0)
+                    trx_regex_scan_end(text, *ticket, nullptr, nullptr, nullptr);
+            }
+        } guard_fwd{store.text, &t_fwd}, guard_rev{store.text, &t_rev};
+        auto finish = [&](int & ticket, bool reverse, uint8_t const * m) {
             std::vector<trx_hit> hits(cap);
             uint64_t n = 0;
             int const rc = trx_regex_scan_end(store.text, ticket, hits.data(), &n, nullptr);
+            ticket = -1;
             if (rc == TRX_ECAPACITY)
                 return scan(store, rx, cand, reverse, m); // more hits than the speculative buffer: once more, with room
             check(rc);

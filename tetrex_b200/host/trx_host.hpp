@@ -196,8 +196,12 @@ public:
         std::vector<uint64_t> offsets;       // n_records + 1
         std::vector<uint32_t> rec_bin;
         std::string residues;
+        std::vector<bool> loaded;            // per bin: its FASTA file has been read into this store
     };
-    text_store const & text();
+    // the store with (at least) the candidate bins' records loaded and uploaded; `cand` = ceil(bins/64) words
+    text_store const & text(std::vector<uint64_t> const & cand);
+    // resident processes (servers, benchmarks) load every bin on first use instead of growing query by query
+    void preload_all_text(bool on) { preload_all_ = on; }
 
     // Device scratch of the collector, kept between queries: the path-slot pool (cudaMalloc + cudaFree of up to
     // 128 MB per query cost 0.6 ms — more than the whole walk) and the k-mer / hit-vector buffers of the HIBF route.
@@ -222,6 +226,7 @@ private:
     trx_hibf_t * hibf_{nullptr};
     uint8_t aamap_[256]{}, redmap_[256]{};
     uint64_t seq_count_{};
+    bool preload_all_{false};
     std::unique_ptr<text_store> text_;
     collector_scratch scratch_;
 };

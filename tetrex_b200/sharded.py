@@ -126,8 +126,22 @@ class ShardedIndex:
             words = (gather_words or tdist.gather_words)(local)
         if not verify:
             return words, None
-        text, _ = self.verify_local(words, regex) if words.any() else ("", 0)
-        return words, (gather_lines or gather_text)(text)
+        # an error on ONE rank (a moved FASTA file of its bins, …) must not leave the others waiting in the gather:
+        # every rank enters the collective, the failure travels with it and is raised everywhere
+        failure = None
+        try:
+            text, _ = self.verify_local(words, regex) if words.any() else ("", 0)
+        except HostError as e:
+            text, failure = "", f"shard {self.shard_index}: {e}"
+        gathered = (gather_lines or gather_text)(text if failure is None else _FAILED + failure)
+        if failure is not None:
+            raise HostError(failure)
+        if gathered is not None and _FAILED in gathered:
+            raise HostError(gathered.split(_FAILED, 1)[1].split("\n", 1)[0])
+        return words, gathered
+
+
+_FAILED = "\x00trx-shard-failed\x00"
 
 
 def gather_text(text: str):

@@ -79,6 +79,52 @@ def prosite_patterns(n: int = 1000, seed: int = 1000, planted_fraction: float = 
     return pats
 
 
+def pattern_instance(pattern: str, rng) -> bytes:
+    """One string the PROSITE-style pattern (grammar of prosite_patterns) matches: a letter per literal, a member per
+    class, a random residue per '.', the lower or upper count for a {m,n} repeat."""
+    aa = "ACDEFGHIKLMNPQRSTVWY"
+    out, i = [], 0
+    while i < len(pattern):
+        c = pattern[i]
+        if c == "[":
+            j = pattern.index("]", i)
+            choices, i = pattern[i + 1:j], j + 1
+        elif c == ".":
+            choices, i = aa, i + 1
+        else:
+            choices, i = c, i + 1
+        reps = 1
+        if i < len(pattern) and pattern[i] == "{":
+            j = pattern.index("}", i)
+            lo, _, hi = pattern[i + 1:j].partition(",")
+            reps = rng.randint(int(lo), int(hi or lo))
+            i = j + 1
+        out.extend(rng.choice(choices) for _ in range(reps))
+    return "".join(out).encode()
+
+
+def plant_patterns(residues, rec_offsets, patterns, seed: int = 1000, fraction: float = 0.10, max_records: int = 50):
+    """SURVEY.md 8(d) "C3 patterns": 10 % of the patterns are planted into 1-50 random records each (in place, at a random
+    offset inside the record).  Returns the indices of the planted patterns."""
+    import random
+    rng = random.Random(seed + 1)
+    n_rec = len(rec_offsets) - 1
+    planted = []
+    for pi, pat in enumerate(patterns):
+        if rng.random() >= fraction:
+            continue
+        planted.append(pi)
+        for _ in range(rng.randint(1, max_records)):
+            inst = np.frombuffer(pattern_instance(pat, rng), dtype=np.uint8)
+            r = rng.randrange(n_rec)
+            lo, hi = int(rec_offsets[r]), int(rec_offsets[r + 1])
+            if hi - lo < len(inst):
+                continue
+            at = rng.randint(lo, hi - len(inst))
+            residues[at:at + len(inst)] = inst
+    return planted
+
+
 def dna_like(n_bins: int, records_per_bin: int, record_len: int, seed: int = 8192):
     rng = np.random.default_rng(seed)
     n = n_bins * records_per_bin
