@@ -645,8 +645,11 @@ int trx_paths_or(trx_paths_t * p, const uint32_t * dst, const uint32_t * src, ui
     default: rc = go(std::integral_constant<int, 32>{}); break;
     }
     TRX_TRY(rc);
-    // the staged index arrays may be overwritten by the next call: finish before returning
-    TRX_CUDA(cudaStreamSynchronize(c->stream));
+    // arena path: nothing to wait for — the lists stay where they are until the arena wraps (which synchronises) or a
+    // later call that reads results back has synchronised and reset it.  Staged path: the caller's arrays may have been
+    // pinned (then the copies above are truly asynchronous) and may be rewritten as soon as this returns.
+    if (n > kZeroCopyItems)
+        TRX_CUDA(cudaStreamSynchronize(c->stream));
     return TRX_OK;
 }
 

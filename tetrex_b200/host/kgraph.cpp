@@ -395,7 +395,12 @@ kgraph construct_kgraph(std::string const & postfix, uint8_t k, bool reduced)
         default: b.symbol(sym); break;
         }
     }
-    if (b.stack.size() != 1)
+    // The reference caps whatever is on TOP of the stack (src/construct_nfa.cpp:316-333, construct_reduced_nfa.cpp:
+    // 374-391; its `assert(stack.size() == 0)` is compiled out).  The reduced builder really gets there with operands
+    // left over: `S{1}` after a prefix concatenates, pushes the symbol again and swallows the next '-' (:284-291), so
+    // for "NLS{1}G" the graph that is walked is only "SG" — deterministic, and reproduced here node for node (the
+    // orphaned prefix nodes stay in the graph and in the rank order, nothing points to them).
+    if (b.stack.empty() || (!reduced && b.stack.size() != 1))
         throw error("malformed regular expression (operands left on the stack)");
     subgraph whole = b.stack.top();
     if (whole.start < 0)
