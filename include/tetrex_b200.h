@@ -51,6 +51,7 @@ typedef struct trx_hibf trx_hibf_t;
 typedef struct trx_paths trx_paths_t;
 typedef struct trx_text trx_text_t;
 typedef struct trx_regex trx_regex_t;
+typedef struct trx_comm trx_comm_t;
 
 /* ------------------------------------------------------------------------------------------ context */
 const char *trx_last_error(void);
@@ -142,6 +143,14 @@ int trx_paths_fill(trx_paths_t *p, uint64_t first, uint64_t n, uint64_t bins);
  * appear once per call.  Host arrays in, alive (n bytes) out. */
 int trx_paths_step(trx_ibf_t *ibf, trx_paths_t *p, const uint64_t *kmers, const uint32_t *slots, uint64_t n,
                    uint8_t *alive);
+/* the same launch on device arrays: enqueues on the context's stream and returns (alive bytes land in d_alive). */
+int trx_paths_step_dev(trx_ibf_t *ibf, trx_paths_t *p, const uint64_t *d_kmers, const uint32_t *d_slots, uint64_t n,
+                       uint8_t *d_alive);
+/* trx_paths_step for a 64-bin column shard: `path_.none()` is a statement about ALL bins, so the
+ * alive bytes are OR-ed over the shards (trx_comm_any_alive_dev, on the device, same stream) before they are copied
+ * out; every rank must make the same call with the same k-mers and slots. */
+int trx_paths_step_sharded(trx_ibf_t *ibf, trx_paths_t *p, trx_comm_t *comm, const uint64_t *kmers, const uint32_t *slots,
+                           uint64_t n, uint8_t *alive);
 /* same, against precomputed hit vectors resident on the device (HIBF route: trx_hibf_membership_dev
  * wrote d_hits[hit_index[i]*words_per_slot ...]) */
 int trx_paths_and_hits(trx_paths_t *p, const uint64_t *d_hits, const uint32_t *hit_index, const uint32_t *slots,
@@ -243,6 +252,31 @@ int trx_regex_scan_end(trx_text_t *text, int ticket, trx_hit *hits, uint64_t *n_
  *         32w + b). */
 int trx_regex_filter_plan(const trx_regex_t *re, const double *byte_freq, int reverse_strand, const uint8_t *map256,
                           int32_t out[136]);
+
+/* ------------------------------------------------------------------- multi-GPU: collectives (8(e)) */
+/* One communicator per context = per GPU (NCCL over NVLink/NVSwitch, bound at run time: no link dependency, single-GPU
+ * use never loads it).  The reference has nothing of the kind (single process, OpenMP over bins, include/query.h:113);
+ * what it replaces is the implicit "all bins are in this address space" of OTFCollector::collect.
+ *   one process per GPU:  rank 0 calls trx_comm_unique_id, the caller ships the 128 bytes to every rank by any
+ *                         channel (torch.distributed, a file, MPI), every rank calls trx_comm_create;
+ *   one process, N GPUs:  trx_comm_create_all(ctxs, n, comms) (ncclCommInitAll).
+ * All _dev calls enqueue on the context's stream (ordered after the kernels already queued there) and return. */
+#define TRX_COMM_ID_BYTES 128
+int trx_comm_unique_id(uint8_t id[TRX_COMM_ID_BYTES]);
+int trx_comm_create(trx_ctx_t *ctx, int rank, int world, const uint8_t id[TRX_COMM_ID_BYTES], trx_comm_t **out);
+int trx_comm_create_all(trx_ctx_t *const *ctxs, int n, trx_comm_t **out);
+void trx_comm_destroy(trx_comm_t *comm);
+int trx_comm_rank(const trx_comm_t *comm);
+int trx_comm_world(const trx_comm_t *comm);
+uint64_t trx_comm_collectives(const trx_comm_t *comm); /* collectives issued so far (bench: what crossed NVLink) */
+int trx_comm_version(void);                            /* NCCL version code, -1 if NCCL cannot be loaded */
+/* in-place OR of n alive bytes over all ranks (all-reduce MAX): otf_collector.h:383's none() made global */
+int trx_comm_any_alive_dev(trx_comm_t *comm, uint8_t *d_alive, uint64_t n);
+/* d_recv[r*bytes_per_rank ...] = rank r's d_send: final candidate words, hit counts, hit tuples */
+int trx_comm_allgather_dev(trx_comm_t *comm, const void *d_send, void *d_recv, uint64_t bytes_per_rank);
+int trx_comm_bcast_dev(trx_comm_t *comm, void *d_buf, uint64_t bytes, int root);
+/* host buffers (small control messages): stages, gathers, reads back, synchronises */
+int trx_comm_allgather(trx_comm_t *comm, const void *send, void *recv, uint64_t bytes_per_rank);
 
 #ifdef __cplusplus
 }

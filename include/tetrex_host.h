@@ -30,6 +30,14 @@ void trxh_close(void *handle);
 /* out[0..8) = bin_count, bin_words, is_hibf, is_dna, k, shard_word_begin, shard_words, reduction */
 int trxh_info(void *handle, uint64_t out[8]);
 
+/* A communicator of the CUDA library (trx_comm_create, include/tetrex_b200.h) for this handle: a column-sharded
+ * trxh_process_query then needs no callback — alive bytes are all-reduced on the device, on the probe kernel's stream, and
+ * the candidate words are all-gathered, so out_words is complete on every rank.  NULL detaches.  Not owned. */
+int trxh_attach_comm(void *handle, trx_comm_t *comm);
+/* resident processes (servers, benchmarks): load every bin of the shard into HBM on the first verify; the default reads
+ * the candidate bins' FASTA files only, like iter_disk_search (include/query.h:126-131) */
+int trxh_preload_text(void *handle, int on);
+
 /* ORs n bytes over all shards in place (all-reduce MAX): the collector's `path_.none()` (include/otf_collector.h:383) is
  * a statement about all bins.  Called once per probing rank of the k-graph, on the calling thread. */
 typedef void (*trxh_alive_fn)(uint8_t *alive, uint64_t n, void *user);

@@ -24,7 +24,10 @@ def main():
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     ctx = t.Context(local)
-    index = sharded.ShardedIndex(ctx, sys.argv[1])
+    # default: the C++ layer reduces its pruning flags and gathers its candidate words over NCCL itself (trx_comm_*, on the
+    # device); TRX_SHARD_CALLBACK=1 = the older route through a Python callback and torch.distributed
+    comm = None if os.environ.get("TRX_SHARD_CALLBACK") else t.Comm.from_torch_dist(ctx)
+    index = sharded.ShardedIndex(ctx, sys.argv[1], comm=comm)
     ok = True
     for regex in sys.argv[2:]:
         words, text = index.query(regex)
@@ -38,7 +41,25 @@ def main():
                 same = want.stdout == text
                 print(f"   equals single-GPU tetrex query: {same}")
                 ok &= same
+    # throughput of the filter phase over the shards, collectives included (every rank runs the same walk)
+    import time
+    reps = int(os.environ.get("TRX_REPS", "200"))
+    for regex in sys.argv[2:3]:
+        for _ in range(10):
+            index.local_candidates(regex)
+        dist.barrier()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            _, st = index.local_candidates(regex)
+        dt = time.perf_counter() - t0
+        if rank == 0:
+            how = "trx_comm (NCCL inside libtrxhost)" if comm is not None else "python callback + torch.distributed"
+            coll = f", {comm.collectives} NCCL collectives so far" if comm is not None else ""
+            print(f"== process_query x{reps} over {world} shards via {how}: {reps / dt:.0f} queries/s, "
+                  f"{dt / reps * 1e6:.0f} us/query, {st}{coll}")
     index.close()
+    if comm is not None:
+        comm.close()
     dist.barrier()
     dist.destroy_process_group()
     sys.exit(0 if ok else 1)

@@ -63,6 +63,8 @@ PROTOTYPES = {
     "trx_paths_device_words": (vp, [vp]),
     "trx_paths_fill": (C.c_int, [vp, C.c_uint64, C.c_uint64, C.c_uint64]),
     "trx_paths_step": (C.c_int, [vp, vp, vp, vp, C.c_uint64, vp]),
+    "trx_paths_step_dev": (C.c_int, [vp, vp, vp, vp, C.c_uint64, vp]),
+    "trx_paths_step_sharded": (C.c_int, [vp, vp, vp, vp, vp, C.c_uint64, vp]),
     "trx_paths_and_hits": (C.c_int, [vp, vp, vp, vp, C.c_uint64, vp]),
     "trx_paths_or": (C.c_int, [vp, vp, vp, C.c_uint64]),
     "trx_paths_read": (C.c_int, [vp, C.c_uint64, C.c_uint64, vp]),
@@ -80,6 +82,18 @@ PROTOTYPES = {
     "trx_regex_scan_begin": (C.c_int, [vp, vp, vp, C.c_int, vp, C.c_uint64, C.POINTER(C.c_int)]),
     "trx_regex_scan_end": (C.c_int, [vp, C.c_int, vp, u64p, u64p]),
     "trx_regex_filter_plan": (C.c_int, [vp, vp, C.c_int, vp, vp]),
+    "trx_comm_unique_id": (C.c_int, [vp]),
+    "trx_comm_create": (C.c_int, [vp, C.c_int, C.c_int, vp, vpp]),
+    "trx_comm_create_all": (C.c_int, [vpp, C.c_int, vpp]),
+    "trx_comm_destroy": (None, [vp]),
+    "trx_comm_rank": (C.c_int, [vp]),
+    "trx_comm_world": (C.c_int, [vp]),
+    "trx_comm_collectives": (C.c_uint64, [vp]),
+    "trx_comm_version": (C.c_int, []),
+    "trx_comm_any_alive_dev": (C.c_int, [vp, vp, C.c_uint64]),
+    "trx_comm_allgather_dev": (C.c_int, [vp, vp, vp, C.c_uint64]),
+    "trx_comm_bcast_dev": (C.c_int, [vp, vp, C.c_uint64, C.c_int]),
+    "trx_comm_allgather": (C.c_int, [vp, vp, vp, C.c_uint64]),
 }
 
 _lib = None

@@ -76,6 +76,57 @@ class Context:
         return out[:cap], out_offs
 
 
+class Comm:
+    """NCCL communicator of the CUDA library for one context = one GPU (trx_comm_t)."""
+
+    def __init__(self, ctx: Context, rank: int, world: int, unique_id: bytes):
+        assert len(unique_id) == 128
+        self.ctx, self.rank, self.world = ctx, rank, world
+        self._h = C.c_void_p()
+        buf = (C.c_uint8 * 128).from_buffer_copy(unique_id)
+        check(lib().trx_comm_create(ctx._h, rank, world, C.addressof(buf), C.byref(self._h)))
+        ctx._children.add(self)
+
+    @staticmethod
+    def unique_id() -> bytes:
+        buf = (C.c_uint8 * 128)()
+        check(lib().trx_comm_unique_id(C.addressof(buf)))
+        return bytes(buf)
+
+    @classmethod
+    def from_torch_dist(cls, ctx: Context):
+        """One rank per GPU under torchrun: rank 0 draws the id, torch.distributed ships the 128 bytes."""
+        import torch.distributed as dist
+        rank, world = dist.get_rank(), dist.get_world_size()
+        box = [cls.unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(box, src=0)
+        return cls(ctx, rank, world, box[0])
+
+    @property
+    def collectives(self) -> int:
+        return lib().trx_comm_collectives(self._h)
+
+    def any_alive_dev(self, d_alive: int, n: int):
+        check(lib().trx_comm_any_alive_dev(self._h, d_alive, n))
+
+    def allgather_dev(self, d_send: int, d_recv: int, bytes_per_rank: int):
+        check(lib().trx_comm_allgather_dev(self._h, d_send, d_recv, bytes_per_rank))
+
+    def bcast_dev(self, d_buf: int, nbytes: int, root: int = 0):
+        check(lib().trx_comm_bcast_dev(self._h, d_buf, nbytes, root))
+
+    def close(self):
+        if self._h:
+            lib().trx_comm_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 def emit_count(molecule, k, length) -> int:
     return lib().trx_emit_count(molecule, k, length)
 
@@ -191,6 +242,9 @@ class Paths:
         alive = np.zeros(len(v), dtype=np.uint8)
         check(lib().trx_paths_step(ibf._h, self._h, _ptr(v), _ptr(s), len(v), _ptr(alive)))
         return alive
+
+    def step_dev(self, ibf: IBF, d_kmers: int, d_slots: int, n: int, d_alive: int):
+        check(lib().trx_paths_step_dev(ibf._h, self._h, d_kmers, d_slots, n, d_alive))
 
     def and_hits(self, d_hits: int, hit_index, slots) -> np.ndarray:
         hi = _np(hit_index, np.uint32)

@@ -553,6 +553,63 @@ int trx_paths_step(trx_ibf_t * f, trx_paths_t * p, const uint64_t * kmers, const
     return TRX_OK;
 }
 
+int trx_paths_step_dev(trx_ibf_t * f, trx_paths_t * p, const uint64_t * d_kmers, const uint32_t * d_slots, uint64_t n,
+                       uint8_t * d_alive)
+{
+    if (!f || !p || (n && (!d_kmers || !d_slots || !d_alive)))
+        return set_error(TRX_EINVAL, "NULL argument");
+    if (p->words_per_slot != f->shard_words || p->ctx != f->ctx)
+        return set_error(TRX_EINVAL, "path slots (%llu words) do not match the IBF shard (%llu words)",
+                         (unsigned long long)p->words_per_slot, (unsigned long long)f->shard_words);
+    if (n == 0)
+        return TRX_OK;
+    TRX_TRY(f->ctx->use());
+    return launch_probe<1>(f->ctx, geom_of(f), d_kmers, n, p->d_words, d_slots, d_alive);
+}
+
+int trx_paths_step_sharded(trx_ibf_t * f, trx_paths_t * p, trx_comm_t * comm, const uint64_t * kmers,
+                           const uint32_t * slots, uint64_t n, uint8_t * alive)
+{
+    if (!f || !p || !comm || (n && (!kmers || !slots || !alive)))
+        return set_error(TRX_EINVAL, "NULL argument");
+    if (n == 0)
+        return TRX_OK;
+    TRX_TRY(check_slots(p, slots, n));
+    trx_ctx * c = f->ctx;
+    TRX_TRY(c->use());
+    // k-mers and slots are read from pinned host memory (small steps) or staged; the alive bytes are written to
+    // DEVICE memory, OR-ed over the shards there (NCCL, same stream) and only then copied out: one sync per step
+    uint64_t const * src_kmers = nullptr;
+    uint32_t const * src_slots = nullptr;
+    if (n <= kZeroCopyItems)
+    {
+        c->h_pin[0].pinned_host = true;
+        TRX_TRY(c->h_pin[0].reserve(kZeroCopyItems * 13 + 64));
+        auto * base = static_cast<uint8_t *>(c->h_pin[0].ptr);
+        memcpy(base, kmers, n * 8);
+        memcpy(base + kZeroCopyItems * 8, slots, n * 4);
+        src_kmers = reinterpret_cast<uint64_t *>(base);
+        src_slots = reinterpret_cast<uint32_t *>(base + kZeroCopyItems * 8);
+    }
+    else
+    {
+        TRX_TRY(c->d_in[0].reserve(n * 8));
+        TRX_CUDA(cudaMemcpyAsync(c->d_in[0].ptr, kmers, n * 8, cudaMemcpyHostToDevice, c->stream));
+        uint32_t * d_slots = nullptr;
+        TRX_TRY(stage_u32(c, 1, slots, n, &d_slots));
+        src_kmers = static_cast<uint64_t *>(c->d_in[0].ptr);
+        src_slots = d_slots;
+    }
+    TRX_TRY(c->d_out[1].reserve(n));
+    auto * d_alive = static_cast<uint8_t *>(c->d_out[1].ptr);
+    TRX_TRY(trx_paths_step_dev(f, p, src_kmers, src_slots, n, d_alive));
+    TRX_TRY(trx_comm_any_alive_dev(comm, d_alive, n));
+    TRX_CUDA(cudaMemcpyAsync(alive, d_alive, n, cudaMemcpyDeviceToHost, c->stream));
+    TRX_CUDA(cudaStreamSynchronize(c->stream));
+    c->pin_arena_off = 0;
+    return TRX_OK;
+}
+
 int trx_paths_and_hits(trx_paths_t * p, const uint64_t * d_hits, const uint32_t * hit_index, const uint32_t * slots,
                        uint64_t n, uint8_t * alive)
 {

@@ -21,6 +21,7 @@ struct handle
 {
     trx_ctx_t * ctx;
     trxh::DeviceIndex index;
+    trx_comm_t * comm{nullptr}; // not owned
     explicit handle(trx_ctx_t * c) : ctx(c), index(c) {}
 };
 
@@ -81,6 +82,19 @@ void trxh_close(void * h)
     delete static_cast<handle *>(h);
 }
 
+// From now on a column-sharded trxh_process_query reduces its pruning flags and gathers its candidate words through this
+// communicator (NCCL, on the device); pass NULL to detach.  The communicator stays the caller's.
+int trxh_attach_comm(void * hv, trx_comm_t * comm)
+{
+    return guarded([&] { static_cast<handle *>(hv)->comm = comm; });
+}
+
+// resident processes: read and upload every bin's text on the first verify instead of growing query by query
+int trxh_preload_text(void * hv, int on)
+{
+    return guarded([&] { static_cast<handle *>(hv)->index.preload_all_text(on != 0); });
+}
+
 // out[0..8) = bin_count, bin_words, is_hibf, is_dna, k, shard_word_begin, shard_words, reduction
 int trxh_info(void * hv, uint64_t out[8])
 {
@@ -106,8 +120,9 @@ int trxh_process_query(void * hv, const char * regex, trxh_alive_fn alive, void 
         trxh::shard_hooks hooks;
         if (alive)
             hooks.any_alive = [alive, user](uint8_t * a, size_t n) { alive(a, n, user); };
+        hooks.comm = static_cast<handle *>(hv)->comm;
         trxh::collect_stats st;
-        trxh::bitvector got = trxh::process_query(regex, ix, &st, alive ? &hooks : nullptr);
+        trxh::bitvector got = trxh::process_query(regex, ix, &st, (alive || hooks.comm) ? &hooks : nullptr);
         // run_collection (include/query.h:256-262): the answer is ANDed into a vector of the real bins
         for (uint64_t w = 0; w < got.size(); ++w)
         {

@@ -104,8 +104,9 @@ bitvector collect(kgraph const & g, DeviceIndex & index, collect_stats * stats, 
     uint64_t const W = index.path_words();
     uint64_t const bins = sharded ? std::min<uint64_t>(W * 64, index.bin_count() > word_begin * 64 ? index.bin_count() - word_begin * 64 : 0)
                                   : index.bin_count();
-    if (sharded && !(hooks && hooks->any_alive))
-        throw error("a column-sharded index needs shard_hooks::any_alive (the pruning decision spans all shards)");
+    if (sharded && !(hooks && (hooks->any_alive || hooks->comm)))
+        throw error("a column-sharded index needs shard_hooks::any_alive or ::comm (the pruning decision spans all shards)");
+    trx_comm_t * const comm = sharded && hooks ? hooks->comm : nullptr;
     uint8_t const k = index.k();
     unsigned const bits = index.is_dna() ? 2 : 5;
     // create_selection_bitmask (otf_collector.h:168-182): the low (k-1) symbols
@@ -220,7 +221,10 @@ bitvector collect(kgraph const & g, DeviceIndex & index, collect_stats * stats, 
             if (!probe_kmers.empty())
             {
                 std::vector<uint8_t> res(probe_kmers.size());
-                if (!index.is_hibf())
+                if (comm) // probe + all-reduce(MAX) of the alive bytes on the device + one read-back
+                    check(trx_paths_step_sharded(index.flat(), pool.paths(), comm, probe_kmers.data(), probe_slots.data(),
+                                                 probe_kmers.size(), res.data()));
+                else if (!index.is_hibf())
                 {
                     check(trx_paths_step(index.flat(), pool.paths(), probe_kmers.data(), probe_slots.data(),
                                          probe_kmers.size(), res.data()));
@@ -239,7 +243,7 @@ bitvector collect(kgraph const & g, DeviceIndex & index, collect_stats * stats, 
                     check(trx_paths_and_hits(pool.paths(), static_cast<uint64_t *>(sc.d_hits), idx.data(),
                                              probe_slots.data(), n, res.data()));
                 }
-                if (sharded)
+                if (sharded && !comm)
                     hooks->any_alive(res.data(), res.size());
                 for (size_t j = 0; j < res.size(); ++j)
                     alive[probe_item[j]] = res[j];
@@ -257,6 +261,11 @@ bitvector collect(kgraph const & g, DeviceIndex & index, collect_stats * stats, 
     }
     bitvector out(index.bin_words(), 0);
     check(trx_paths_read(pool.paths(), match_slot, 1, out.data() + word_begin));
+    if (comm) // every rank contributes its column block (equal sizes: the shard count divides bin_words) and gets all
+    {
+        bitvector mine(out.begin() + word_begin, out.begin() + word_begin + W);
+        check(trx_comm_allgather(comm, mine.data(), out.data(), W * 8));
+    }
     return out;
 }
 

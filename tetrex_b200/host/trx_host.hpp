@@ -241,6 +241,10 @@ using bitvector = std::vector<uint64_t>; // ceil(bins/64) words, bit b = bin b (
 struct shard_hooks
 {
     std::function<void(uint8_t * alive, size_t n)> any_alive;
+    // preferred: a communicator of the CUDA library (NCCL over NVLink).  The alive bytes are then reduced ON THE DEVICE,
+    // on the stream of the probe kernel that wrote them (trx_paths_step_sharded) — no callback, no host hop — and the
+    // final candidate words are all-gathered the same way, so every rank returns the whole vector.
+    trx_comm_t * comm{nullptr};
 };
 
 struct collect_stats

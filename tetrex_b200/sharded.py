@@ -48,6 +48,8 @@ def host_lib():
         h.trxh_verify.argtypes = [vp, u64p, C.c_char_p, C.POINTER(C.c_void_p), u64p, u64p]
         h.trxh_free.argtypes = [vp]
         h.trxh_free.restype = None
+        h.trxh_attach_comm.argtypes = [vp, vp]
+        h.trxh_preload_text.argtypes = [vp, C.c_int]
         _host = h
     return _host
 
@@ -63,7 +65,8 @@ class ShardedIndex:
     any_alive(alive: np.ndarray[uint8]) -> np.ndarray[uint8] must return the element-wise OR over all shards; the
     default is the process group's all-reduce (`tetrex_b200.dist.any_alive`)."""
 
-    def __init__(self, ctx, path: str, shard_index: int | None = None, shard_count: int | None = None, any_alive=None):
+    def __init__(self, ctx, path: str, shard_index: int | None = None, shard_count: int | None = None, any_alive=None,
+                 comm=None, preload_text: bool = False):
         rank, world, _ = tdist.rank_world()
         self.shard_index = rank if shard_index is None else shard_index
         self.shard_count = world if shard_count is None else shard_count
@@ -76,6 +79,11 @@ class ShardedIndex:
         (self.bin_count, self.bin_words, hibf, dna, self.k, self.word_begin, self.words, self.reduction) = map(int, info)
         self.is_hibf, self.is_dna = bool(hibf), bool(dna)
         self.column_sharded = (not self.is_hibf) and self.shard_count > 1
+        self.comm = comm  # tetrex_b200.api.Comm: pruning flags and candidate words travel over NCCL inside the C++ layer
+        if comm is not None:
+            _check(host_lib().trxh_attach_comm(self._h, comm._h))
+        if preload_text:
+            _check(host_lib().trxh_preload_text(self._h, 1))
 
         def _cb(ptr, n, _user):
             a = np.ctypeslib.as_array(ptr, shape=(int(n),))
@@ -99,7 +107,7 @@ class ShardedIndex:
         column-sharded, {probes, ranks, items})."""
         words = np.zeros(self.bin_words, dtype=np.uint64)
         stats = np.zeros(3, dtype=np.uint64)
-        cb = self._cb if self.column_sharded else C.cast(None, _ALIVE_FN)
+        cb = self._cb if (self.column_sharded and self.comm is None) else C.cast(None, _ALIVE_FN)
         _check(host_lib().trxh_process_query(self._h, regex.encode(), cb, None, words.ctypes.data_as(C.POINTER(C.c_uint64)),
                                              stats.ctypes.data_as(C.POINTER(C.c_uint64))))
         return words, dict(zip(("probes", "ranks", "items"), map(int, stats)))
@@ -121,7 +129,7 @@ class ShardedIndex:
         """The whole query on all shards (collective: every rank calls it with the same regex).  Returns
         (candidate words of ALL bins, the output text on rank 0 / None elsewhere)."""
         words, _ = self.local_candidates(regex)
-        if self.column_sharded:
+        if self.column_sharded and self.comm is None:
             local = words[self.word_begin:self.word_begin + self.words]
             words = (gather_words or tdist.gather_words)(local)
         if not verify:
