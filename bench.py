@@ -43,6 +43,7 @@ def parse_args():
     ap.add_argument("--seqs", type=int, default=570_000, help="sequences in the synthetic collection (570000 = C2)")
     ap.add_argument("--batch", type=int, default=1 << 22, help="k-mers per rank per step")
     ap.add_argument("--no-extra", action="store_true", help="skip the K2/K4 side measurements")
+    ap.add_argument("--c4-bins", type=int, default=8192, help="bins of the C4 build (8192 = the config; smaller for smoke runs)")
     return ap.parse_args()
 
 
@@ -251,9 +252,29 @@ def run_ours(args):
 
     # ---------------- BASELINE config 4 (8192-bin DNA IBF, k = 20, 23.4 GB), bins sharded over the ranks in 64-bin column
     # blocks, the SAME k-mer batch on every rank (= broadcast): K2 bulk_contains of every k-mer against all 8192 bins
-    flat_c4 = None
+    # and the real thing: the matrix BUILT by K1 from streamed text, probed with canonical 20-mers, checked against the
+    # oracle at full size, and the column-sharded collector step with its NCCL collectives (bench_configs.py)
+    flat_c4, c4 = None, None
+    comm = None
     if not args.no_extra and 128 % world == 0:
+        import bench_configs as bc
+        peak_now, _ = peaks()
+        if world > 1:
+            comm = t.Comm.from_torch_dist(ctx)
         flat_c4 = measure_c4_sharded_probe(t, ctx, torch, rank, world, barrier, max_over_ranks)
+        try:
+            c4, f4, keep4, bs4 = bc.measure_c4(t, ctx, torch, rank, world, barrier, max_over_ranks, sum_over_ranks, peak_now, comm,
+                                               bins=args.c4_bins)
+            more, d_q4 = bc.c4_probe_and_check(t, ctx, torch, f4, keep4, bs4, rank, world, barrier, max_over_ranks, peak_now, comm)
+            c4.update(more)
+            c4["sharded_query_step"] = bc.c4_sharded_query_step(t, ctx, torch, f4, d_q4, rank, world, barrier, max_over_ranks,
+                                                                peak_now, comm)
+            del d_q4
+            f4.close()
+            torch.cuda.empty_cache()
+        except Exception as e:  # a side measurement never costs the headline line; on N > 1 every rank fails alike
+            import traceback
+            c4 = {"error": f"{type(e).__name__}: {e}"[:400], "trace": traceback.format_exc()[-600:]}
 
     line = None
     if rank == 0:
@@ -294,10 +315,26 @@ def run_ours(args):
             flat_c4["roofline"]["peak"] = peak
             flat_c4["roofline"]["frac"] = flat_c4["roofline"]["achieved"] / peak
             line["flat_c4_sharded"] = flat_c4
+        line["configs"] = {"C2": "the headline above (value / e2e / roofline / cpu_baseline)"}
+        if c4 is not None:
+            line["configs"]["C4"] = c4
         if world == 1:
             line["cpu_baseline"] = cpu_baseline(tables, q_host)
             if not args.no_extra:
                 line["extra"] = extra_measurements(t, ctx, torch, residues, offs, rec_bin, planted, hibf, peak)
+                import bench_configs as bc
+                for key, fn in (("C1", lambda: bc.measure_c1(t, ctx)),
+                                ("C5", lambda: bc.measure_c5(t, ctx, torch, residues, offs, peak)),
+                                ("C2_seqan_layout", lambda: bc.measure_c2_seqan_layout(t, ctx, torch, residues, offs, rec_bin,
+                                                                                       N_BINS, q_host, peak))):
+                    try:
+                        line["configs"][key] = fn()
+                    except Exception as e:
+                        import traceback
+                        line["configs"][key] = {"error": f"{type(e).__name__}: {e}"[:400], "trace": traceback.format_exc()[-600:]}
+                line["configs"]["C3"] = line["extra"].pop("C3", None)
+    if comm is not None:
+        comm.close()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -305,7 +342,7 @@ def run_ours(args):
         emit(line)
 
 
-def host_path_queries(t, ctx, residues, offs, rec_bin, reps=100):
+def host_path_queries(t, ctx, residues, offs, rec_bin, reps=100, on_index=None):
     """Writes the synthetic collection as 1024 FASTA files, builds a HIBF and a flat index with tetrex_b200/bin/tetrex
     (K1), loads them through libtrxhost.so and times whole queries: regex -> k-graph -> collector (K2/K3 + path algebra on
     the device, one host decision per rank of the graph) -> candidate bins -> K4 verify -> formatted lines."""
@@ -341,7 +378,7 @@ def host_path_queries(t, ctx, residues, offs, rec_bin, reps=100):
             if p.returncode != 0:
                 raise RuntimeError(p.stderr[-300:])
             build_s = time.perf_counter() - t0
-            ix = sharded.ShardedIndex(ctx, os.path.join(d, name + ".ibf"), 0, 1)
+            ix = sharded.ShardedIndex(ctx, os.path.join(d, name + ".ibf"), 0, 1, preload_text=True)
             words, text = ix.query(QUERY)
             lines = text.count("\n")
             t0 = time.perf_counter()
@@ -354,6 +391,8 @@ def host_path_queries(t, ctx, residues, offs, rec_bin, reps=100):
             res[name] = {"queries_per_s": reps / (t2 - t0), "process_query_us": (t1 - t0) / reps * 1e6,
                          "iter_disk_search_us": (t2 - t1) / reps * 1e6, "candidate_bins": int(np.bitwise_count(words).sum()),
                          "lines": lines, "collector": st, "index_build_s_incl_process_start_and_fasta_parse": round(build_s, 2)}
+            if on_index is not None:
+                on_index(name, ix)
             ix.close()
         res["query"] = QUERY
         return res
@@ -542,6 +581,7 @@ def extra_measurements(t, ctx, torch, residues, offs, rec_bin, planted, hibf, pe
         "frac_of_hbm_peak": len(pats) * n_res / dt / 1e9 / peak, "hits": int(total_hits), "over_capacity": overflow,
         "mean_us_per_scan": {("exact" if k == "none" else k): (per_kind_s[k] / max(kinds["exact" if k == "none" else k], 1)) * 1e6
                              for k in per_kind_s}}
+    pattern_hits = {pat: int(len(h)) for pat, h in zip(pats, piped)}
     for rxp, _ in compiled:
         rxp.close()
 
@@ -575,7 +615,14 @@ def extra_measurements(t, ctx, torch, residues, offs, rec_bin, planted, hibf, pe
     # ---- the same query through the reference-shaped host path (C++: process_query = k-graph + collector with the path
     # algebra on the device, iter_disk_search = K4 + line formatting) on index files built by this repo's `tetrex index`
     try:
-        out["host_path_queries"] = host_path_queries(t, ctx, residues, offs, rec_bin)
+        import bench_configs as bc
+        c3 = {}
+
+        def on_index(name, ix):
+            if name == "flat":
+                c3["pattern_batch_filter_and_verify"] = bc.measure_c3_patterns(ix, pats, lambda p: pattern_hits[p])
+        out["host_path_queries"] = host_path_queries(t, ctx, residues, offs, rec_bin, on_index=on_index)
+        out["C3"] = c3
     except Exception as e:  # never lose the bench line over a side measurement
         out["host_path_queries"] = {"error": f"{type(e).__name__}: {e}"[:300]}
 
@@ -601,6 +648,20 @@ def extra_measurements(t, ctx, torch, residues, offs, rec_bin, planted, hibf, pe
     out["flat_roofline"] = {"bound": "hbm", "achieved": algo / sec / 1e9, "peak": peak, "unit": "GB/s",
                             "frac": algo / sec / 1e9 / peak, "note": "h x bin_words x 8 B read per k-mer (384 B); the "
                             "154 MB matrix is mostly L2-resident, result write (128 B/k-mer) not counted"}
+    c3 = out.setdefault("C3", {})
+    c3["workload"] = (f"peptide flat IBF, 1024 bins x {bin_size} rows ({flat.n_words * 8 / 1e6:.0f} MB), k=6, h=3; "
+                      "1000 PROSITE-style patterns")
+    c3["k2_probes_per_s"] = n / sec
+    c3["roofline"] = dict(out["flat_roofline"], traffic=None, kernel="probe_kernel<3,2,8,0>")
+    c3["k1_kmers_per_s"] = out["emplace_kmers_per_s"]
+    c3["verify_batch_all_bins"] = {"scans_per_s_pipelined": out["verify_pattern_batch_pipelined"]["scans_per_s"],
+                                   "scans_per_s_one_at_a_time": out["verify_pattern_batch"]["scans_per_s"],
+                                   "hits": out["verify_pattern_batch"]["hits"]}
+    try:
+        import bench_configs as bc
+        c3["cpu_baseline"] = bc.cpu_baseline_flat_probe(N_BINS, bin_size, HASH_FUNS, q.cpu().numpy().view(np.uint64))
+    except Exception as e:
+        c3["cpu_baseline"] = {"error": f"{type(e).__name__}: {e}"[:200]}
     flat.close()
     return out
 

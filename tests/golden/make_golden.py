@@ -472,6 +472,82 @@ def golden_cli_ws():
         print(c["regex"], c["bins"], repr(c["stdout"]))
 
 
+def write_twin_fasta(directory, residues, offs, rec_bin, n_bins):
+    """The /100 twin as n_bins FASTA files (one record per line pair), names as bench.py writes them."""
+    os.makedirs(directory, exist_ok=True)
+    raw = residues.tobytes()
+    files, r = [], 0
+    for b in range(n_bins):
+        path = os.path.join(directory, f"bin_{b:04d}.fa")
+        with open(path, "wb") as f:
+            while r < len(rec_bin) and rec_bin[r] == b:
+                f.write(b">sp|S%07d|SYN_%d\n" % (r, b))
+                f.write(raw[int(offs[r]):int(offs[r + 1])])
+                f.write(b"\n")
+                r += 1
+        files.append(path)
+    return files
+
+
+def guarded_timed(fn, seconds, *args):
+    """guarded() with a CPU-time limit in the child: the reference's enumeration explodes on wildcard-rich patterns."""
+    import pickle
+    import resource
+    r, w = os.pipe()
+    pid = os.fork()
+    if pid == 0:
+        os.close(r)
+        try:
+            resource.setrlimit(resource.RLIMIT_CPU, (seconds, seconds))
+            resource.setrlimit(resource.RLIMIT_AS, (6 << 30, 6 << 30))
+            os.dup2(os.open(os.devnull, os.O_WRONLY), 2)
+            os.write(w, pickle.dumps(fn(*args)))
+        finally:
+            os._exit(0)
+    os.close(w)
+    data = b""
+    while True:
+        chunk = os.read(r, 1 << 16)
+        if not chunk:
+            break
+        data += chunk
+    os.close(r)
+    _, status = os.waitpid(pid, 0)
+    return pickle.loads(data) if status == 0 and data else None
+
+
+def golden_prosite_filter():
+    """BASELINE config 3's FILTER phase: the reference's process_query (k-graph + OTFCollector over a flat peptide IBF,
+    k = 6) for the PROSITE-style patterns on the /100 twin, 1024 bins.  The index is built by the reference from FASTA files
+    in a scratch directory; only the candidate-bin lists are committed — the GPU test rebuilds the (byte-identical) index
+    with `tetrex index -i`.  Patterns whose enumeration does not finish in 3 CPU-seconds in the reference are skipped."""
+    import tempfile
+    from tetrex_b200 import synth
+    residues, offs, rec_bin, _ = synth.swissprot_like(5700, 1024)
+    pats = synth.prosite_patterns(1000, 1000)
+    synth.plant_patterns(residues, offs, pats)
+    d = tempfile.mkdtemp(prefix="trx_twin_")
+    files = write_twin_fasta(d, residues, offs, rec_bin, 1024)
+    idx = os.path.join(d, "twin_flat.ibf")
+    ob.ref_index_build(files, 6, 0.05, 3, 1, 0, 0, idx)
+    out, skipped = [], 0
+    for pi, pat in enumerate(pats):
+        got = guarded_timed(ob.ref_index_query, 3, idx, pat, False)
+        if got is None:
+            skipped += 1
+            continue
+        words = got[0]
+        out.append(dict(pattern=pi, bins=[b for b in range(1024) if int(words[b // 64]) >> (b % 64) & 1]))
+        if len(out) >= 400:
+            break
+    import shutil
+    shutil.rmtree(d, ignore_errors=True)
+    with open(os.path.join(OUT, "prosite_filter.json"), "w") as f:
+        json.dump(out, f, separators=(",", ":"))
+    print("prosite_filter.json:", len(out), "patterns,", skipped, "skipped (reference > 3 s or aborted),",
+          sum(1 for c in out if c["bins"]), "with candidates, mean", sum(len(c["bins"]) for c in out) / len(out), "bins")
+
+
 def golden_rh_order():
     """Pop orders of the real robin_hood::unordered_map for key lists shaped like a rank's sub-k-mer keys."""
     rng = random.Random(99)
@@ -486,7 +562,7 @@ def golden_rh_order():
 
 STEPS = {"decompose": golden_decompose, "ibf": golden_ibf, "hibf": golden_hibf, "regex": golden_regex,
          "kgraph": golden_kgraph, "cli": golden_cli, "c1": golden_c1, "collector_fuzz": golden_collector_fuzz, "rh_order": golden_rh_order,
-         "prosite_batch": golden_prosite_batch, "c2_twin_hibf": golden_c2_twin_hibf, "cli_ws": golden_cli_ws}
+         "prosite_batch": golden_prosite_batch, "c2_twin_hibf": golden_c2_twin_hibf, "cli_ws": golden_cli_ws, "prosite_filter": golden_prosite_filter}
 
 if __name__ == "__main__":
     assert ob.have_ref(), "build oracle/_ref first: make -C oracle ref"
