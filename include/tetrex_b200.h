@@ -129,6 +129,22 @@ int trx_emplace_records_dev(trx_ibf_t *ibf, int molecule, uint32_t k, int reduct
 int trx_bulk_contains(trx_ibf_t *ibf, const uint64_t *kmers, uint64_t n, uint64_t *out_words);
 int trx_bulk_contains_dev(trx_ibf_t *ibf, const uint64_t *d_kmers, uint64_t n, uint64_t *d_out_words);
 
+/* K2 without any allocation.  NO COUNTERPART IN THE REFERENCE: added for callers
+ * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same
+ * arguments and result as trx_bulk_contains (host k-mers in, host hit vectors out, returns when they are there), but the
+ * device staging of k-mers and hit vectors is a fixed file-scope `static __device__` array of TRX_NOALLOC_SCRATCH_BYTES
+ * instead of the context's grow-on-demand buffers; the call makes no cudaMalloc / cudaFree / allocating library call.
+ *   - limit: n*8 (rounded up to 256) + n*shard_words*8 bytes must fit the array; beyond that TRX_ECAPACITY with the
+ *     numbers in trx_last_error().  trx_bulk_contains_noalloc_max_kmers(ibf) = the largest n for this filter
+ *     (C3, 16 words per k-mer: 30 840; C4 whole, 128 words: 4 064).
+ *   - every GPU that loads the library holds the array until the process exits.
+ *   - ALL calls on one device share the array, and it keeps the last call's contents (nothing needs clearing: every byte a
+ *     call reads was written by that call).  Calls that overlap on the GPU — two contexts / streams / host threads on the
+ *     same device — RACE on it: serialise them.  The call itself synchronises its stream before it returns. */
+#define TRX_NOALLOC_SCRATCH_BYTES (4u << 20)
+int trx_bulk_contains_noalloc(trx_ibf_t *ibf, const uint64_t *kmers, uint64_t n, uint64_t *out_words);
+uint64_t trx_bulk_contains_noalloc_max_kmers(const trx_ibf_t *ibf);
+
 /* ------------------------------------------------------ a6: collector path algebra in HBM */
 /* A pool of `capacity` path bitvectors ("slots") of words_per_slot uint64 each — the path_ member
  * of every live CollectorsItem (include/otf_collector.h:19-37) — resident in HBM. */

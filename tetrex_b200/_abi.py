@@ -58,6 +58,8 @@ PROTOTYPES = {
     "trx_emplace_records_dev": (C.c_int, [vp, C.c_int, C.c_uint32, C.c_int, vp, C.c_uint64, vp, vp, C.c_uint64]),
     "trx_bulk_contains": (C.c_int, [vp, vp, C.c_uint64, vp]),
     "trx_bulk_contains_dev": (C.c_int, [vp, vp, C.c_uint64, vp]),
+    "trx_bulk_contains_noalloc": (C.c_int, [vp, vp, C.c_uint64, vp]),
+    "trx_bulk_contains_noalloc_max_kmers": (C.c_uint64, [vp]),
     "trx_paths_create": (C.c_int, [vp, C.c_uint64, C.c_uint64, vpp]),
     "trx_paths_destroy": (None, [vp]),
     "trx_paths_device_words": (vp, [vp]),

@@ -208,6 +208,18 @@ class IBF:
         check(lib().trx_bulk_contains(self._h, _ptr(v), len(v), _ptr(out)))
         return out
 
+    def bulk_contains_noalloc(self, kmers, out: np.ndarray | None = None) -> np.ndarray:
+        """bulk_contains through the library's fixed device scratch: no allocation on the device side at all."""
+        v = _np(kmers, np.uint64)
+        if out is None:
+            out = np.zeros((len(v), self.shard_words), dtype=np.uint64)
+        check(lib().trx_bulk_contains_noalloc(self._h, _ptr(v), len(v), _ptr(out)))
+        return out
+
+    @property
+    def noalloc_max_kmers(self) -> int:
+        return lib().trx_bulk_contains_noalloc_max_kmers(self._h)
+
     def bulk_contains_dev(self, d_kmers: int, n: int, d_out: int):
         check(lib().trx_bulk_contains_dev(self._h, d_kmers, n, d_out))
 

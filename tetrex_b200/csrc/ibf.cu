@@ -1,5 +1,6 @@
 // ibf.cu — C ABI for the flat IBF (rows a1–a7 of SURVEY.md §8): create/upload/download, K1 emplace,
 // K2 bulk_contains and the collector's path algebra.
+#include <mutex>
 #include <type_traits>
 
 #include "ibf_kernels.cuh"
@@ -721,6 +722,84 @@ int trx_paths_read(trx_paths_t * p, uint64_t first, uint64_t n, uint64_t * out_w
                              cudaMemcpyDeviceToHost, p->ctx->stream));
     TRX_CUDA(cudaStreamSynchronize(p->ctx->stream));
     p->ctx->pin_arena_off = 0;
+    return TRX_OK;
+}
+
+// ------------------------------------------------------------------------------- no-allocation probe
+// trx_bulk_contains for callers that must not allocate (CUDA graph capture around them, tight serving loops, harnesses
+// that forbid cudaMalloc): the staging that trx_bulk_contains keeps in grow-on-demand cudaMalloc'ed buffers (k-mers in,
+// hit vectors out) lives in ONE file-scope device array of fixed size instead.  Every GPU that loads this library holds
+// the array (TRX_NOALLOC_SCRATCH_BYTES) until the process exits; the
+// reference has nothing of the kind.
+}  // extern "C" (the array and its address cache are file-local)
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[TRX_NOALLOC_SCRATCH_BYTES];
+
+namespace
+{
+constexpr int kNoallocMaxDevices = 64;
+std::mutex g_noalloc_mutex;
+void * g_noalloc_ptr[kNoallocMaxDevices] = {}; // per device: the DEVICE address of g_noalloc_scratch on that device
+
+// In host code `g_noalloc_scratch` is only a stand-in symbol, not a device address: the address a kernel may use comes
+// from cudaGetSymbolAddress, asked once per device with that device current.
+int noalloc_scratch_for(int device, unsigned char ** out)
+{
+    if (device < 0 || device >= kNoallocMaxDevices)
+        return set_error(TRX_EINVAL, "device %d: the no-allocation scratch is kept for devices 0..%d", device,
+                         kNoallocMaxDevices - 1);
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (!g_noalloc_ptr[device])
+    {
+        TRX_CUDA(cudaSetDevice(device));
+        void * ptr = nullptr;
+        TRX_CUDA(cudaGetSymbolAddress(&ptr, g_noalloc_scratch));
+        if (!ptr)
+            return set_error(TRX_ECUDA, "cudaGetSymbolAddress returned a null address for the no-allocation scratch");
+        g_noalloc_ptr[device] = ptr;
+    }
+    *out = static_cast<unsigned char *>(g_noalloc_ptr[device]);
+    return TRX_OK;
+}
+} // namespace
+
+extern "C"
+{
+
+uint64_t trx_bulk_contains_noalloc_max_kmers(const trx_ibf_t * f)
+{
+    if (!f)
+        return 0;
+    return TRX_NOALLOC_SCRATCH_BYTES / (8 + f->shard_words * 8);
+}
+
+int trx_bulk_contains_noalloc(trx_ibf_t * f, const uint64_t * kmers, uint64_t n, uint64_t * out_words)
+{
+    if (!f || (n && (!kmers || !out_words)))
+        return set_error(TRX_EINVAL, "NULL argument");
+    if (n == 0)
+        return TRX_OK;
+    uint64_t const out_bytes = n * f->shard_words * 8;
+    uint64_t const in_bytes = (n * 8 + 255) & ~uint64_t{255}; // the hit vectors start 256-byte aligned
+    if (n > trx_bulk_contains_noalloc_max_kmers(f) || in_bytes + out_bytes > TRX_NOALLOC_SCRATCH_BYTES)
+        return set_error(TRX_ECAPACITY,
+                         "trx_bulk_contains_noalloc: %llu k-mers x %llu words need %llu bytes of staging, the fixed scratch "
+                         "holds %llu (at most %llu k-mers per call for this filter); split the batch or use trx_bulk_contains",
+                         (unsigned long long)n, (unsigned long long)f->shard_words,
+                         (unsigned long long)(in_bytes + out_bytes), (unsigned long long)TRX_NOALLOC_SCRATCH_BYTES,
+                         (unsigned long long)trx_bulk_contains_noalloc_max_kmers(f));
+    trx_ctx * c = f->ctx;
+    unsigned char * scratch = nullptr;
+    TRX_TRY(noalloc_scratch_for(c->device, &scratch));
+    TRX_TRY(c->use());
+    auto * d_kmers = reinterpret_cast<uint64_t *>(scratch);
+    auto * d_out = reinterpret_cast<uint64_t *>(scratch + in_bytes);
+    // nothing here has to start at zero: the k-mers are copied in, and the probe STORES every word of every hit vector
+    // (MODE 0 writes the AND, it never accumulates), so whatever the previous call left in the array is overwritten
+    TRX_CUDA(cudaMemcpyAsync(d_kmers, kmers, n * 8, cudaMemcpyHostToDevice, c->stream));
+    TRX_TRY(launch_probe<0>(c, geom_of(f), d_kmers, n, d_out, nullptr, nullptr));
+    TRX_CUDA(cudaMemcpyAsync(out_words, d_out, out_bytes, cudaMemcpyDeviceToHost, c->stream));
+    TRX_CUDA(cudaStreamSynchronize(c->stream));
     return TRX_OK;
 }
 
