@@ -90,7 +90,8 @@ def measure_c4(t, ctx, torch, rank, world, barrier, max_over_ranks, sum_over_ran
         gen_s += time.perf_counter() - tg
         e0, e1 = events(torch)
         e0.record()
-        f.emplace_records_dev(t.MOL_NA, C4_K, 0, text.data_ptr(), text.numel(), d_offs.data_ptr(), d_bin.data_ptr(), recs)
+        f.emplace_records_slab_dev(t.MOL_NA, C4_K, 0, text.data_ptr(), text.numel(), d_offs.data_ptr(), d_bin.data_ptr(), recs,
+                                   slab * C4_SLAB_BINS, C4_SLAB_BINS)
         e1.record()
         torch.cuda.synchronize()
         k1_ms += e0.elapsed_time(e1)
@@ -106,7 +107,8 @@ def measure_c4(t, ctx, torch, rank, world, barrier, max_over_ranks, sum_over_ran
         "wall_s_incl_text_generation": wall, "text_generation_s_per_rank": gen_s,
         "matrix_gb": bins / 8 * bin_size / 1e9, "matrix_gb_per_gpu": f.shard_n_words * 8 / 1e9, "bin_size": bin_size,
         "streaming": f"{n_slabs} slabs of {C4_SLAB_BINS} bins ({recs * C4_RECORD_LEN / 1e6:.0f} MB of text each), one "
-                     "emplace launch per slab, no slab outlives its launch",
+                     "trx_emplace_records_slab_dev call per slab (bits collected in a dense 183 MB copy of the slab's word "
+                     "column in L2-sized row slices, then folded into the interleaved matrix), no slab outlives its call",
         "roofline": roofline(n_kmers * (1 + 64 * C4_H) / (k1_ms / 1e3) / 1e9 / world, peak,
                              "per GPU; algorithmic = 1 B text + h x 64 B (32 B sector fill + 32 B write-back per atomicOr into "
                              "a matrix >> L2) = 193 B per emitted k-mer (SURVEY 8(d))", bytes_per_kmer=1 + 64 * C4_H,
@@ -227,13 +229,16 @@ def c4_sharded_query_step(t, ctx, torch, f, d_q, rank, world, barrier, max_over_
     """The column-sharded QUERY path of SURVEY.md 8(e) on the C4 matrix, collectives included: the same batch of path
     items on every rank; per step one fused probe + AND into the rank's HBM-resident path slots (K2 MODE 1, 128/S words
     per slot) and one all-reduce(MAX) of the alive bytes over NCCL — `path_.none()` is global (include/otf_collector.h:383);
-    after the last step the slots' words are all-gathered (the final candidate vector of every item).  Whole-job items/s,
-    device time, max over ranks."""
+    after the last step the candidate vectors are all-gathered: ONE vector per query (the match accumulator, `path_matrix`
+    of otf_collector.h:343,363), a query being 256 items of the batch here (config 3's patterns average 22 k probes per
+    query, so this is generous).  Whole-job items/s, device time, max over ranks."""
     W = f.shard_words
     paths = t.Paths(ctx, W, n)
     d_slots = torch.arange(n, dtype=torch.int32, device="cuda")
     d_alive = torch.zeros(n, dtype=torch.uint8, device="cuda")
-    d_all = torch.empty(n * W * world, dtype=torch.int64, device="cuda") if world > 1 else None
+    items_per_query = 256
+    n_queries = n // items_per_query
+    d_all = torch.empty(n_queries * W * world, dtype=torch.int64, device="cuda") if world > 1 else None
     words_ptr = t.lib().trx_paths_device_words(paths._h)
     use_comm = comm is not None and world > 1
 
@@ -244,7 +249,7 @@ def c4_sharded_query_step(t, ctx, torch, f, d_q, rank, world, barrier, max_over_
             if use_comm:
                 comm.any_alive_dev(d_alive.data_ptr(), n)
         if use_comm:
-            comm.allgather_dev(words_ptr, d_all.data_ptr(), n * W * 8)
+            comm.allgather_dev(words_ptr, d_all.data_ptr(), n_queries * W * 8)
     one_round()
     barrier()
     c0 = comm.collectives if comm is not None else 0
@@ -258,10 +263,11 @@ def c4_sharded_query_step(t, ctx, torch, f, d_q, rank, world, barrier, max_over_
     read_b = C4_H * W * 8 + 2 * W * 8  # rows + path slot read-modify-write
     out = {"items_per_s": items / (ms / 1e3), "ms": ms, "items_per_step": n, "steps": steps, "shards": world,
            "collectives_in_region": (comm.collectives - c0) if comm is not None else 0,
-           "bytes_over_nvlink_per_rank": (steps * n + n * W * 8 * (world - 1)) if world > 1 else 0,
+           "bytes_over_nvlink_per_rank": (steps * n + n_queries * W * 8 * (world - 1)) if world > 1 else 0,
+           "queries": n_queries, "items_per_query": items_per_query,
            "alive_after_last_step": float(d_alive.float().mean().item()),
-           "what": "fused probe + path AND (trx_paths_step_dev) + ncclAllReduce(MAX, 1 B/item) per step, ncclAllGather of the "
-                   "final path words; k-mer batch identical on all ranks",
+           "what": "fused probe + path AND (trx_paths_step_dev) + ncclAllReduce(MAX, 1 B/item) per step, ncclAllGather of one "
+                   "candidate vector per query at the end; k-mer batch identical on all ranks",
            "roofline": roofline(items * read_b / (ms / 1e3) / 1e9, peak,
                                 f"per GPU: (h + 2) x {W * 8} B per item and step (rows + slot read + slot write); the "
                                 "collectives ride on the same stream and are inside the timed region",

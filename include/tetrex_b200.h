@@ -124,6 +124,17 @@ int trx_emplace_records_dev(trx_ibf_t *ibf, int molecule, uint32_t k, int reduct
                             uint64_t n_residues, const uint64_t *d_rec_offsets, const uint32_t *d_rec_bin,
                             uint64_t n_records);
 
+/* K1b for a SLAB of neighbouring bins: the same fused loop, with the promise-free hint that the records of this call
+ * belong to bins [first_bin, first_bin + n_bins) — what IBFIndex::populate_index's outer loop over files
+ * (include/index_ibf.h:105-112: one FASTA file = one bin) gives for free when files are streamed in order.  When the matrix
+ * is far larger than L2 the bits of those bins are collected in a dense copy of their word columns (L2-sliced passes)
+ * and folded into the interleaved matrix in one strided pass, instead of one DRAM read-modify-write per bit.  Records
+ * whose bin lies outside the range are still emplaced correctly (straight into the matrix).  trx_emplace_records (host
+ * buffers) derives the range from rec_bin itself. */
+int trx_emplace_records_slab_dev(trx_ibf_t *ibf, int molecule, uint32_t k, int reduction, const uint8_t *d_residues,
+                                 uint64_t n_residues, const uint64_t *d_rec_offsets, const uint32_t *d_rec_bin,
+                                 uint64_t n_records, uint64_t first_bin, uint64_t n_bins);
+
 /* K2 — containment_agent_type::bulk_contains (…cpp:203-290) / IBFIndex::query (index_ibf.h:146-150)
  * for a batch: out_words[i*shard_words + w] = AND_h row_h(kmers[i])[w]. */
 int trx_bulk_contains(trx_ibf_t *ibf, const uint64_t *kmers, uint64_t n, uint64_t *out_words);

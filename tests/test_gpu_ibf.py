@@ -119,6 +119,50 @@ def test_dna_example_split_c1(ctx):
     f.close()
 
 
+@pytest.mark.parametrize("mol,k,alpha", [(0, 20, b"ACGT"), (1, 6, AA)])
+def test_emplace_slab_route_equals_oracle(ctx, mol, k, alpha, monkeypatch):
+    """K1's slab route (dense copy of the slab's word columns, L2-sliced passes, strided fold into the matrix): forced on
+    a small matrix with a 1 MB slice size; records of bins inside the named range, a few OUTSIDE it (those must still land,
+    straight in the matrix), a second slab into the same matrix, and the host-buffer entry point which derives the range
+    itself — all bit-equal to the oracle's emplace."""
+    import torch
+    monkeypatch.setenv("TRX_EMPLACE_WINDOW_MB", "1")
+    rng = random.Random(k)
+    bins, bin_size = 2048, 60013  # 32 words x 60013 rows = 15 MB: more than ten 1 MB slices -> the whole-matrix route gives up
+    f = t.IBF(ctx, bins, bin_size, 3)
+    want = ob.OracleIBF(bins, bin_size, 3)
+    for first, n_bins, strays in [(128, 64, [5, 2047]), (700, 30, []), (0, 64, [64])]:
+        seqs, text, offs = make_records(rng, alpha, [rng.randint(k, 400) for _ in range(60)])
+        rec_bin = np.array([first + rng.randrange(n_bins) for _ in seqs], dtype=np.uint32)
+        for j, b in enumerate(strays):
+            rec_bin[j] = b
+        d_text = torch.frombuffer(bytearray(text), dtype=torch.uint8).cuda()
+        d_offs = torch.from_numpy(offs.view(np.int64)).cuda()
+        d_bin = torch.from_numpy(rec_bin.view(np.int32)).cuda()
+        launches = ctx.launches
+        f.emplace_records_slab_dev(mol, k, 0, d_text.data_ptr(), len(text), d_offs.data_ptr(), d_bin.data_ptr(), len(seqs),
+                                   first, n_bins)
+        ctx.sync()
+        assert ctx.launches - launches == 2, "one sliced pass into the 480 KB slab + the fold"
+        want.emplace_records(mol, k, 0, text, offs, rec_bin)
+        assert np.array_equal(f.download(), want.words), (first, n_bins)
+    # host-buffer entry point: range taken from rec_bin
+    seqs, text, offs = make_records(rng, alpha, [rng.randint(k, 300) for _ in range(40)])
+    rec_bin = np.array([1000 + rng.randrange(20) for _ in seqs], dtype=np.uint32)
+    f.emplace_records(mol, k, 0, text, offs, rec_bin)
+    want.emplace_records(mol, k, 0, text, offs, rec_bin)
+    assert np.array_equal(f.download(), want.words)
+    # and with the route switched off the same bits
+    monkeypatch.setenv("TRX_EMPLACE_SLAB", "off")
+    g = t.IBF(ctx, bins, bin_size, 3)
+    g.emplace_records(mol, k, 0, text, offs, rec_bin)
+    only = ob.OracleIBF(bins, bin_size, 3)
+    only.emplace_records(mol, k, 0, text, offs, rec_bin)
+    assert np.array_equal(g.download(), only.words)
+    g.close()
+    f.close()
+
+
 # ------------------------------------------------------------------------------------------------ a5
 @pytest.mark.parametrize("bins,bs,h", [(5, 106, 3), (64, 5000, 1), (128, 5000, 2), (320, 3001, 3), (1024, 20011, 3),
                                        (1000, 999, 4), (8192, 4099, 3), (8192 + 64, 1031, 5), (2048, 1 << 16, 3)])

@@ -201,6 +201,11 @@ class IBF:
         check(lib().trx_emplace_records_dev(self._h, molecule, k, reduction, d_residues, n_residues, d_rec_offsets,
                                             d_rec_bin, n_records))
 
+    def emplace_records_slab_dev(self, molecule, k, reduction, d_residues: int, n_residues: int, d_rec_offsets: int,
+                                 d_rec_bin: int, n_records: int, first_bin: int, n_bins: int):
+        check(lib().trx_emplace_records_slab_dev(self._h, molecule, k, reduction, d_residues, n_residues, d_rec_offsets,
+                                                 d_rec_bin, n_records, first_bin, n_bins))
+
     def bulk_contains(self, kmers, out: np.ndarray | None = None) -> np.ndarray:
         v = _np(kmers, np.uint64)
         if out is None:

@@ -76,6 +76,7 @@ struct trx_ibf
     uint64_t shard_word_begin{}, shard_words{}, shard_n_words{};
     uint64_t * d_words{nullptr}; // shard_n_words words, row r at r*shard_words
     bool owns_words{true};
+    trx::scratch slab;           // K1: dense copy of a few word columns while a slab of bins is being emplaced
 };
 
 struct trx_paths

@@ -475,14 +475,16 @@ constexpr uint32_t kMergeTileWords = 64;
 
 __global__ void __launch_bounds__(kMergeWarps * 32)
     hibf_merge_tile_kernel(hibf_window const * __restrict__ windows, uint32_t n_windows, uint64_t const * __restrict__ strips,
-                           uint64_t n, uint32_t out_words, uint64_t * __restrict__ out)
+                           uint64_t n, uint32_t out_words, uint64_t * __restrict__ out, uint32_t const * __restrict__ inv_perm)
 {
     extern __shared__ uint64_t merge_tile[];
     uint64_t const stream = policy_evict_first();
     unsigned const lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint32_t const pitch = out_words + 1;
     uint64_t * const tile = merge_tile + static_cast<size_t>(warp) * 32 * pitch;
-    uint32_t const inv_w = (65536 + out_words - 1) / out_words;
+    // idx / out_words for idx < 32 * kMergeTileWords = 2048: a 20-bit reciprocal is exact there (error < 2048 / 2^20 <
+    // 1 / 64); the 16-bit one the window kernel uses for its narrow spans is not (63 words: 2015 * 1041 >> 16 = 32)
+    uint32_t const inv_w = ((1u << 20) + out_words - 1) / out_words;
     uint64_t const n_groups = (n + 31) / 32;
     for (uint64_t g = static_cast<uint64_t>(blockIdx.x) * kMergeWarps + warp; g < n_groups; g += static_cast<uint64_t>(gridDim.x) * kMergeWarps)
     {
@@ -498,17 +500,39 @@ __global__ void __launch_bounds__(kMergeWarps * 32)
                 continue;
             uint32_t const inv = (65536 + win.span - 1) / win.span;
             uint64_t const * const src = strips + win.strip_off * n + base * win.span;
-            for (uint32_t idx = lane; idx < rows * win.span; idx += 32)
+            if (!inv_perm)
             {
-                uint32_t const r = (idx * inv) >> 16;
-                tile[r * pitch + win.word_lo + (idx - r * win.span)] |= ld_hint(src + idx, stream);
+                for (uint32_t idx = lane; idx < rows * win.span; idx += 32)
+                {
+                    uint32_t const r = (idx * inv) >> 16;
+                    tile[r * pitch + win.word_lo + (idx - r * win.span)] |= ld_hint(src + idx, stream);
+                }
+            }
+            else
+            {
+                // strips live in the PERMUTED user-bin order (layout order: the bins of one child are neighbours, so a
+                // window's strip is a few words wide whatever ids the layout gave them); hits are sparse — a few dozen
+                // of the row's bits — so every set bit is moved to its real id on the way into the tile
+                for (uint32_t idx = lane; idx < rows * win.span; idx += 32)
+                {
+                    uint64_t const v = ld_hint(src + idx, stream);
+                    if (v == 0)
+                        continue;
+                    uint32_t const r = (idx * inv) >> 16;
+                    uint32_t const pos0 = (win.word_lo + (idx - r * win.span)) * 64;
+                    unsigned * const row32 = reinterpret_cast<unsigned *>(tile + r * pitch);
+                    for_each_bit(v, [&](int b) {
+                        uint32_t const ub = __ldg(inv_perm + pos0 + b);
+                        atomicOr(row32 + (ub >> 5), 1u << (ub & 31)); // two lanes may hold words of the same row
+                    });
+                }
             }
             __syncwarp(); // strips may overlap in user-bin words: one at a time
         }
         uint64_t * const dst = out + base * out_words;
         for (uint32_t idx = lane; idx < rows * out_words; idx += 32)
         {
-            uint32_t const r = (idx * inv_w) >> 16;
+            uint32_t const r = (idx * inv_w) >> 20;
             st_hint(dst + idx, tile[r * pitch + (idx - r * out_words)], stream);
         }
         __syncwarp();
@@ -542,6 +566,10 @@ struct trx_hibf
     trx::scratch root_words; // merged-bin hits of the root per k-mer
     std::vector<trx::hibf_window> windows; // [0] = the root's own user bins, then root technical-bin ranges whose children share L2
     trx::hibf_window * d_windows{nullptr};
+    // user-bin ids in layout (DFS) order for the root / window kernels' strips, and the way back for the merge;
+    // nullptr = the ids already are in that order (or the permuted route does not apply): strips hold real ids
+    uint32_t * d_user_perm{nullptr};
+    uint32_t * d_inv_perm{nullptr};
     uint64_t strip_words{0}; // Σ span
     bool window_attr_set{false}, merge_attr_set{false};
     unsigned window_ctas{8}; // resident CTAs per SM of the window kernel's persistent grid
@@ -550,6 +578,13 @@ struct trx_hibf
     trx::hibf_dev dev() const
     {
         return trx::hibf_dev{d_words, d_ibfs, d_next, d_user, d_merged_mask, d_user_mask, static_cast<uint32_t>(out_words)};
+    }
+    trx::hibf_dev dev_strips() const // what the kernels that write strips see
+    {
+        trx::hibf_dev d = dev();
+        if (d_user_perm)
+            d.user_bin = d_user_perm;
+        return d;
     }
 };
 
@@ -572,7 +607,7 @@ static int launch_fused(trx_hibf * h, uint64_t const * d_kmers, uint64_t n, uint
     hibf_window const & root = h->windows[0];
     if (root.span)
         TRX_CUDA(cudaMemsetAsync(strips, 0, n * root.span * 8, c->stream));
-    hibf_root_kernel<H, FAST><<<grid_for(n, 256, c->sm_count, 8), 256, 0, c->stream>>>(h->dev(), d_kmers, n, rw, root, strips, ctr);
+    hibf_root_kernel<H, FAST><<<grid_for(n, 256, c->sm_count, 8), 256, 0, c->stream>>>(h->dev_strips(), d_kmers, n, rw, root, strips, ctr);
     ++c->launches;
     if (!h->window_attr_set)
     {
@@ -585,7 +620,7 @@ static int launch_fused(trx_hibf * h, uint64_t const * d_kmers, uint64_t n, uint
     {
         hibf_window const & win = h->windows[g];
         size_t const smem = static_cast<size_t>(kWinThreads) * (win.span + 1) * 8;
-        hibf_window_kernel<H, FAST><<<grid, kWinThreads, smem, c->stream>>>(h->dev(), d_kmers, n, rw, win, strips + win.strip_off * n,
+        hibf_window_kernel<H, FAST><<<grid, kWinThreads, smem, c->stream>>>(h->dev_strips(), d_kmers, n, rw, win, strips + win.strip_off * n,
                                                                      frontier, ctr, capacity);
         ++c->launches;
     }
@@ -599,7 +634,8 @@ static int launch_fused(trx_hibf * h, uint64_t const * d_kmers, uint64_t n, uint
             h->merge_attr_set = true;
         }
         hibf_merge_tile_kernel<<<grid_for((n + 31) / 32, kMergeWarps, c->sm_count, 12), kMergeWarps * 32, tile, c->stream>>>(
-            h->d_windows, static_cast<uint32_t>(h->windows.size()), strips, n, static_cast<uint32_t>(h->out_words), d_out);
+            h->d_windows, static_cast<uint32_t>(h->windows.size()), strips, n, static_cast<uint32_t>(h->out_words), d_out,
+            h->d_inv_perm);
     }
     else
     {
@@ -714,6 +750,8 @@ int trx_hibf_upload(trx_ctx_t * ctx, const trx_hibf_desc * desc, trx_hibf_t ** o
     h->depth = depth;
     while ((1ull << h->ibf_bits) < n)
         ++h->ibf_bits;
+    std::vector<uint32_t> user_strip, inv_perm; // strip-order ids per technical bin / the way back (see below)
+    bool use_perm = false;
     {
         char const * e = getenv("TRX_HIBF_SORT"); // TRX_HIBF_SORT=off: A/B evidence for the frontier sort
         h->sort_frontier = !(e && strcmp(e, "off") == 0);
@@ -733,6 +771,54 @@ int trx_hibf_upload(trx_ctx_t * ctx, const trx_hibf_desc * desc, trx_hibf_t ** o
         for (uint64_t i = 1; i < n; ++i)
             if (desc->hash_funs[i] != desc->hash_funs[0])
                 h->uniform_hash_funs = 0;
+        // Strip order of the user bins = the order in which a walk of the layout meets them (an IBF's own user bins, then
+        // its children's, recursively).  seqan's layout deals user bins to merged bins by size, so the ids inside one
+        // child are scattered over the whole range: in id order every window would report into ALL result words and the
+        // strips would be as large as the result (measured on the seqan-built C2 index: 16 words per k-mer and window,
+        // 10 GB of strip traffic per 4 Mi k-mers, 1.17 instead of 2.4 G probes/s); in walk order a child's bins are
+        // neighbours and a window reports into 2-3 words.  The merge kernel moves the (sparse) hit bits back to real ids.
+        std::vector<uint32_t> perm(desc->n_user_bins, UINT32_MAX);
+        inv_perm.assign(h->out_words * 64, 0);
+        {
+            uint32_t pos = 0;
+            std::vector<char> walked(n, 0);
+            std::vector<uint64_t> stack{0};
+            walked[0] = 1;
+            while (!stack.empty())
+            {
+                uint64_t const i = stack.back();
+                stack.pop_back();
+                uint64_t const tbs = static_cast<uint64_t>(ibfs[i].bin_words) * 64;
+                for (uint64_t t = 0; t < tbs; ++t)
+                {
+                    uint32_t const ub = user[ibfs[i].table_off + t];
+                    if (ub < kDeleted && ub != kMerged && perm[ub] == UINT32_MAX)
+                        perm[ub] = pos++;
+                }
+                for (uint64_t t = tbs; t-- > 0;) // pushed in reverse: children are walked in technical-bin order
+                    if (user[ibfs[i].table_off + t] == kMerged && !walked[next[ibfs[i].table_off + t]])
+                    {
+                        walked[next[ibfs[i].table_off + t]] = 1;
+                        stack.push_back(next[ibfs[i].table_off + t]);
+                    }
+            }
+            for (uint64_t ub = 0; ub < desc->n_user_bins; ++ub) // bins the layout never placed
+                if (perm[ub] == UINT32_MAX)
+                    perm[ub] = pos++;
+        }
+        bool identity = true;
+        for (uint64_t ub = 0; ub < desc->n_user_bins; ++ub)
+        {
+            identity = identity && perm[ub] == ub;
+            inv_perm[perm[ub]] = static_cast<uint32_t>(ub);
+        }
+        char const * pe = getenv("TRX_HIBF_PERMUTE"); // TRX_HIBF_PERMUTE=off: strips in id order (A/B evidence)
+        use_perm = !identity && h->fused && h->out_words <= kMergeTileWords && !(pe && strcmp(pe, "off") == 0);
+        user_strip = user;
+        if (use_perm)
+            for (auto & ub : user_strip)
+                if (ub < kDeleted && ub != kMerged)
+                    ub = perm[ub];
         // windows: consecutive root technical bins whose children together stay below the L2 budget; for each the run of
         // user-bin words its children report into (a window that would span more than kMaxSpan words is cut earlier)
         h->root_bin_words = ibfs[0].bin_words;
@@ -745,8 +831,8 @@ int trx_hibf_upload(trx_ctx_t * ctx, const trx_hibf_desc * desc, trx_hibf_t ** o
                 uint64_t idx = ibfs[ibf].table_off + t;
                 if (umask[idx / 64] >> (idx % 64) & 1)
                 {
-                    lo = std::min(lo, user[idx] >> 6);
-                    hi = std::max(hi, user[idx] >> 6);
+                    lo = std::min(lo, user_strip[idx] >> 6);
+                    hi = std::max(hi, user_strip[idx] >> 6);
                 }
             }
         };
@@ -823,6 +909,13 @@ int trx_hibf_upload(trx_ctx_t * ctx, const trx_hibf_desc * desc, trx_hibf_t ** o
     if ((e = cudaMemcpyAsync(h->d_user, user.data(), table_total * 4, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess) return fail(e);
     if ((e = cudaMemcpyAsync(h->d_merged_mask, mmask.data(), table_total / 8, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess) return fail(e);
     if ((e = cudaMemcpyAsync(h->d_user_mask, umask.data(), table_total / 8, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess) return fail(e);
+    if (use_perm && h->fused)
+    {
+        if ((e = cudaMalloc(&h->d_user_perm, table_total * 4)) != cudaSuccess) return fail(e);
+        if ((e = cudaMalloc(&h->d_inv_perm, inv_perm.size() * 4)) != cudaSuccess) return fail(e);
+        if ((e = cudaMemcpyAsync(h->d_user_perm, user_strip.data(), table_total * 4, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess) return fail(e);
+        if ((e = cudaMemcpyAsync(h->d_inv_perm, inv_perm.data(), inv_perm.size() * 4, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess) return fail(e);
+    }
     if ((e = cudaMalloc(&h->d_windows, h->windows.size() * sizeof(hibf_window))) != cudaSuccess) return fail(e);
     if ((e = cudaMemcpyAsync(h->d_windows, h->windows.data(), h->windows.size() * sizeof(hibf_window), cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess) return fail(e);
     if ((e = cudaStreamSynchronize(ctx->stream)) != cudaSuccess) return fail(e);
@@ -851,6 +944,8 @@ void trx_hibf_destroy(trx_hibf_t * h)
     h->root_words.release();
     h->strips.release();
     cudaFree(h->d_windows);
+    cudaFree(h->d_user_perm);
+    cudaFree(h->d_inv_perm);
     delete h;
 }
 

@@ -11,7 +11,7 @@ namespace trx
 static ibf_geom geom_of(trx_ibf const * f)
 {
     return ibf_geom{f->d_words, f->bin_size, f->shard_words, f->shard_word_begin,
-                    static_cast<uint32_t>(f->hash_shift), static_cast<uint32_t>(f->hash_funs), 0, f->bin_size};
+                    static_cast<uint32_t>(f->hash_shift), static_cast<uint32_t>(f->hash_funs), 0, f->bin_size, nullptr, 0, 0};
 }
 
 // host-buffer entry points of the path algebra go zero-copy (pinned host memory read by the kernel) up to this many items
@@ -160,6 +160,7 @@ void trx_ibf_destroy(trx_ibf_t * f)
     cudaStreamSynchronize(f->ctx->stream);
     if (f->owns_words)
         cudaFree(f->d_words);
+    f->slab.release();
     delete f;
 }
 
@@ -277,9 +278,31 @@ static int upload_aamap(trx_ctx * c, int reduction, uint8_t ** d_map)
     return TRX_OK;
 }
 
+static int emplace_records_impl(trx_ibf_t * f, int molecule, uint32_t k, int reduction, const uint8_t * d_residues,
+                                uint64_t n_residues, const uint64_t * d_rec_offsets, const uint32_t * d_rec_bin,
+                                uint64_t n_records, uint64_t hint_first_bin, uint64_t hint_n_bins);
+
 int trx_emplace_records_dev(trx_ibf_t * f, int molecule, uint32_t k, int reduction, const uint8_t * d_residues,
                             uint64_t n_residues, const uint64_t * d_rec_offsets, const uint32_t * d_rec_bin,
                             uint64_t n_records)
+{
+    return emplace_records_impl(f, molecule, k, reduction, d_residues, n_residues, d_rec_offsets, d_rec_bin, n_records, 0, 0);
+}
+
+int trx_emplace_records_slab_dev(trx_ibf_t * f, int molecule, uint32_t k, int reduction, const uint8_t * d_residues,
+                                 uint64_t n_residues, const uint64_t * d_rec_offsets, const uint32_t * d_rec_bin,
+                                 uint64_t n_records, uint64_t first_bin, uint64_t n_bins)
+{
+    if (f && (n_bins == 0 || first_bin + n_bins > f->bins))
+        return set_error(TRX_ERANGE, "bins [%llu, %llu) are not bins of this filter (%llu)", (unsigned long long)first_bin,
+                         (unsigned long long)(first_bin + n_bins), (unsigned long long)f->bins);
+    return emplace_records_impl(f, molecule, k, reduction, d_residues, n_residues, d_rec_offsets, d_rec_bin, n_records,
+                                first_bin, n_bins);
+}
+
+static int emplace_records_impl(trx_ibf_t * f, int molecule, uint32_t k, int reduction, const uint8_t * d_residues,
+                                uint64_t n_residues, const uint64_t * d_rec_offsets, const uint32_t * d_rec_bin,
+                                uint64_t n_records, uint64_t hint_first_bin, uint64_t hint_n_bins)
 {
     if (!f)
         return set_error(TRX_EINVAL, "NULL argument");
@@ -301,8 +324,39 @@ int trx_emplace_records_dev(trx_ibf_t * f, int molecule, uint32_t k, int reducti
     uint64_t passes = window ? (f->bin_size * row_bytes + window - 1) / window : 1;
     if (passes < 1)
         passes = 1;
+    // Far beyond L2 (C4: 23 GB, 2.9 GB per GPU at 8 shards) slicing the whole matrix would mean re-hashing the text dozens
+    // of times.  But the records of one call usually belong to a few neighbouring bins (one FASTA file = one bin, a slab of
+    // files = one 64-bin word column): when the caller names that bin range, the bits go into a DENSE copy of just those
+    // word columns (C4, 64 bins: 22.8 M rows x 8 B = 183 MB instead of one 8-byte word every 1 KiB), which IS sliceable
+    // into L2-sized passes, and one strided OR pass folds it into the interleaved matrix.  Bins outside the named range
+    // still go straight to the matrix, so the hint is about speed only.
+    uint64_t slab_words = 0, slab_begin = 0;
     if (passes > 10)
-        passes = 1; // far beyond L2 (C4: 2.9 GB per GPU) re-hashing the text per slice costs more than the DRAM atomics
+    {
+        passes = 1;
+        if (hint_n_bins)
+        {
+            uint64_t w0 = hint_first_bin / 64, w1 = (hint_first_bin + hint_n_bins + 63) / 64;
+            w0 = w0 < f->shard_word_begin ? f->shard_word_begin : w0;
+            w1 = w1 > f->shard_word_begin + f->shard_words ? f->shard_word_begin + f->shard_words : w1;
+            uint64_t const slab_bytes = w1 > w0 ? (w1 - w0) * 8 * f->bin_size : 0;
+            char const * off = getenv("TRX_EMPLACE_SLAB"); // TRX_EMPLACE_SLAB=off: A/B evidence
+            if (slab_bytes && slab_bytes <= (1ull << 30) && (w1 - w0) * 4 <= f->shard_words && window &&
+                !(off && strcmp(off, "off") == 0))
+            {
+                slab_words = w1 - w0;
+                slab_begin = w0;
+                passes = (slab_bytes + window - 1) / window;
+            }
+        }
+    }
+    uint64_t * d_slab = nullptr;
+    if (slab_words)
+    {
+        TRX_TRY(f->slab.reserve(slab_words * 8 * f->bin_size));
+        d_slab = static_cast<uint64_t *>(f->slab.ptr);
+        TRX_CUDA(cudaMemsetAsync(d_slab, 0, slab_words * 8 * f->bin_size, c->stream));
+    }
     uint64_t const rows_per_pass = (f->bin_size + passes - 1) / passes;
     uint8_t * d_map = nullptr;
     if (molecule != TRX_MOL_NA)
@@ -310,6 +364,9 @@ int trx_emplace_records_dev(trx_ibf_t * f, int molecule, uint32_t k, int reducti
     for (uint64_t p = 0; p < passes; ++p)
     {
         ibf_geom g = geom_of(f);
+        g.slab = d_slab;
+        g.slab_words = slab_words;
+        g.slab_begin = slab_begin;
         g.row_lo = p * rows_per_pass;
         g.row_hi = g.row_lo + rows_per_pass < f->bin_size ? g.row_lo + rows_per_pass : f->bin_size;
         if (g.row_lo >= g.row_hi)
@@ -319,6 +376,13 @@ int trx_emplace_records_dev(trx_ibf_t * f, int molecule, uint32_t k, int reducti
         else
             emplace_records_kernel<TRX_MOL_AA><<<grid, 256, 0, c->stream>>>(g, d_residues, n_residues, d_rec_offsets, d_rec_bin,
                                                                             n_records, k, d_map);
+        ++c->launches;
+    }
+    if (slab_words)
+    {
+        uint64_t const total = slab_words * f->bin_size;
+        slab_merge_kernel<<<grid_for(total, 256, c->sm_count, 16), 256, 0, c->stream>>>(
+            f->d_words, f->shard_words, slab_begin - f->shard_word_begin, d_slab, slab_words, f->bin_size);
         ++c->launches;
     }
     TRX_CUDA(cudaGetLastError());
@@ -343,6 +407,12 @@ int trx_emplace_records(trx_ibf_t * f, int molecule, uint32_t k, int reduction, 
             return set_error(TRX_ERANGE, "record %llu: bin %u >= bin count %llu", static_cast<unsigned long long>(i),
                              rec_bin[i], static_cast<unsigned long long>(f->bins));
     }
+    uint32_t bin_lo = rec_bin[0], bin_hi = rec_bin[0];
+    for (uint64_t i = 1; i < n_records; ++i)
+    {
+        bin_lo = rec_bin[i] < bin_lo ? rec_bin[i] : bin_lo;
+        bin_hi = rec_bin[i] > bin_hi ? rec_bin[i] : bin_hi;
+    }
     uint64_t const n_res = rec_offsets[n_records];
     trx_ctx * c = f->ctx;
     TRX_TRY(c->use());
@@ -352,9 +422,9 @@ int trx_emplace_records(trx_ibf_t * f, int molecule, uint32_t k, int reduction, 
     TRX_CUDA(cudaMemcpyAsync(c->d_in[0].ptr, residues, n_res, cudaMemcpyHostToDevice, c->stream));
     TRX_CUDA(cudaMemcpyAsync(c->d_in[1].ptr, rec_offsets, (n_records + 1) * 8, cudaMemcpyHostToDevice, c->stream));
     TRX_CUDA(cudaMemcpyAsync(c->d_in[2].ptr, rec_bin, n_records * 4, cudaMemcpyHostToDevice, c->stream));
-    TRX_TRY(trx_emplace_records_dev(f, molecule, k, reduction, static_cast<uint8_t *>(c->d_in[0].ptr), n_res,
-                                    static_cast<uint64_t *>(c->d_in[1].ptr), static_cast<uint32_t *>(c->d_in[2].ptr),
-                                    n_records));
+    TRX_TRY(emplace_records_impl(f, molecule, k, reduction, static_cast<uint8_t *>(c->d_in[0].ptr), n_res,
+                                 static_cast<uint64_t *>(c->d_in[1].ptr), static_cast<uint32_t *>(c->d_in[2].ptr), n_records,
+                                 bin_lo, static_cast<uint64_t>(bin_hi) - bin_lo + 1));
     TRX_CUDA(cudaStreamSynchronize(c->stream));
     return TRX_OK;
 }

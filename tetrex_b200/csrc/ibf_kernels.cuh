@@ -19,6 +19,11 @@ struct ibf_geom
     uint32_t hash_shift;
     uint32_t hash_funs;
     uint64_t row_lo, row_hi; // K1 only: rows this pass may touch (see trx_emplace_records_dev); [0, bin_size) otherwise
+    // K1 only, optional: a dense stand-in for the word columns [slab_begin, slab_begin + slab_words) of every row
+    // (row r at r*slab_words).  Bits of bins in those columns are set there instead of in `words`; the caller ORs the
+    // slab into the matrix afterwards (slab_merge_kernel).  nullptr = everything goes to `words`.
+    uint64_t * slab;
+    uint64_t slab_words, slab_begin;
 };
 
 // ------------------------------------------------------------------------------------------- K2
@@ -266,11 +271,21 @@ struct emplace_sink
     uint64_t col;
     unsigned long long bit;
     bool mine;
+    uint64_t * base;
+    uint64_t stride;
     __device__ __forceinline__ void set_bin(uint32_t b)
     {
         uint64_t c = b >> 6;
         mine = c >= g.word_begin && c < g.word_begin + g.shard_words;
         col = c - g.word_begin;
+        base = g.words;
+        stride = g.shard_words;
+        if (g.slab && c - g.slab_begin < g.slab_words) // unsigned: also false below slab_begin
+        {
+            base = g.slab;
+            stride = g.slab_words;
+            col = c - g.slab_begin;
+        }
         bit = 1ULL << (b & 63);
     }
     __device__ __forceinline__ void operator()(uint64_t v) const
@@ -281,10 +296,30 @@ struct emplace_sink
         {
             uint64_t const row = hash_row(v, static_cast<int>(h), g.hash_shift, g.bin_size);
             if (row - g.row_lo < g.row_hi - g.row_lo) // this pass's slice of the matrix (the L2-resident one)
-                atomicOr(reinterpret_cast<unsigned long long *>(g.words + row * g.shard_words + col), bit);
+                atomicOr(reinterpret_cast<unsigned long long *>(base + row * stride + col), bit);
         }
     }
 };
+
+// matrix[r][col0 + j] |= slab[r][j] for the rows of the slab: plain read-modify-write (stream order keeps emplaces apart),
+// untouched words are skipped.  One 32-byte sector is read and written back per touched word: what is left of the
+// 64 B per atomic that K1 pays when it sets bits in a matrix far larger than L2 one at a time.
+__global__ void __launch_bounds__(256)
+    slab_merge_kernel(uint64_t * __restrict__ matrix, uint64_t shard_words, uint64_t col0, uint64_t const * __restrict__ slab,
+                      uint64_t slab_words, uint64_t rows)
+{
+    uint64_t const total = rows * slab_words;
+    uint64_t const stride = static_cast<uint64_t>(gridDim.x) * blockDim.x;
+    for (uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride)
+    {
+        uint64_t const v = __ldcs(slab + i);
+        if (v == 0)
+            continue;
+        uint64_t const r = i / slab_words, j = i - r * slab_words;
+        uint64_t * const dst = matrix + r * shard_words + col0 + j;
+        *dst |= v;
+    }
+}
 
 constexpr int kRun = 16;          // residues per thread = one LDG.128
 constexpr int kWindowBytes = 48;  // run + halo (k-1 <= 31) rounded up to 3 × 16 B
