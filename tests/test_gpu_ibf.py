@@ -143,7 +143,7 @@ def test_emplace_slab_route_equals_oracle(ctx, mol, k, alpha, monkeypatch):
         f.emplace_records_slab_dev(mol, k, 0, d_text.data_ptr(), len(text), d_offs.data_ptr(), d_bin.data_ptr(), len(seqs),
                                    first, n_bins)
         ctx.sync()
-        assert ctx.launches - launches == 2, "one sliced pass into the 480 KB slab + the fold"
+        assert ctx.launches - launches == 2, "one pass into the 480 KB slab + the fold"
         want.emplace_records(mol, k, 0, text, offs, rec_bin)
         assert np.array_equal(f.download(), want.words), (first, n_bins)
     # host-buffer entry point: range taken from rec_bin

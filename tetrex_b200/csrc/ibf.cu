@@ -311,7 +311,11 @@ static int emplace_records_impl(trx_ibf_t * f, int molecule, uint32_t k, int red
         return TRX_OK;
     trx_ctx * c = f->ctx;
     TRX_TRY(c->use());
-    uint64_t n_runs = (n_residues + kRun - 1) / kRun;
+    uint32_t dna_run = 64; // steps per DNA thread (TRX_DNA_RUN: A/B evidence)
+    if (char const * e = getenv("TRX_DNA_RUN"))
+        dna_run = atoi(e) > 0 ? static_cast<uint32_t>(atoi(e)) : dna_run;
+    uint64_t const per_thread = molecule == TRX_MOL_NA ? dna_run : static_cast<uint32_t>(kRun);
+    uint64_t n_runs = (n_residues + per_thread - 1) / per_thread;
     unsigned grid = grid_for(n_runs, 256, c->sm_count, 8);
     // A matrix that does not fit L2 is filled in row slices that do: every pass recomputes all hashes (cheap: the
     // kernel is bound by the atomics, not the arithmetic) but only fires the atomics that fall into its slice, so the
@@ -346,7 +350,10 @@ static int emplace_records_impl(trx_ibf_t * f, int molecule, uint32_t k, int red
             {
                 slab_words = w1 - w0;
                 slab_begin = w0;
-                passes = (slab_bytes + window - 1) / window;
+                // a dense slab is hit by ~100 atomics per 32-byte sector, so even at 1.5x the L2 size nearly all of them
+                // find their sector in L2: one pass (8.7 ms per 64-bin C4 slab) beats three L2-sized slices (11.3 ms),
+                // whose extra text + hashing passes cost more than the few misses; slice only slabs far beyond L2
+                passes = slab_bytes <= (256ull << 20) ? 1 : (slab_bytes + window - 1) / window;
             }
         }
     }
@@ -372,7 +379,8 @@ static int emplace_records_impl(trx_ibf_t * f, int molecule, uint32_t k, int red
         if (g.row_lo >= g.row_hi)
             break;
         if (molecule == TRX_MOL_NA)
-            emplace_dna_kernel<<<grid, 256, 0, c->stream>>>(g, d_residues, n_residues, d_rec_offsets, d_rec_bin, n_records, k);
+            emplace_dna_kernel<<<grid, 256, 0, c->stream>>>(g, d_residues, n_residues, d_rec_offsets, d_rec_bin, n_records, k,
+                                                            dna_run);
         else
             emplace_records_kernel<TRX_MOL_AA><<<grid, 256, 0, c->stream>>>(g, d_residues, n_residues, d_rec_offsets, d_rec_bin,
                                                                             n_records, k, d_map);

@@ -288,15 +288,44 @@ struct emplace_sink
         }
         bit = 1ULL << (b & 63);
     }
+    // What bounds K1 (measured on the C4 slab route, profiles/README.md): a pass costs 1.2 ms of text + hashing per 234 M
+    // k-mers plus 10.7 ps per atomic that fires — about 94 G red.or per second at L2, the same for 64- and 32-bit operands
+    // and whether or not the target is L2 resident; a target far larger than L2 with one bit per sector (the interleaved
+    // matrix itself) pays 21 ps, the DRAM read-modify-write.  The hash loop is unrolled so that the seeds are immediates,
+    // and for filters with fewer than 2^32 rows (every configuration of BASELINE.json) the 64x64 high multiply of the
+    // fastrange step is two 32x32 wide multiplies: mulhi64(x, bs) = (hi(x)*bs + (lo(x)*bs >> 32)) >> 32 exactly.
     __device__ __forceinline__ void operator()(uint64_t v) const
     {
         if (!mine)
             return;
-        for (uint32_t h = 0; h < g.hash_funs; ++h)
+        if (g.bin_size >> 32 == 0)
         {
-            uint64_t const row = hash_row(v, static_cast<int>(h), g.hash_shift, g.bin_size);
-            if (row - g.row_lo < g.row_hi - g.row_lo) // this pass's slice of the matrix (the L2-resident one)
-                atomicOr(reinterpret_cast<unsigned long long *>(base + row * stride + col), bit);
+            uint64_t const bs = static_cast<uint32_t>(g.bin_size);
+            uint32_t const lo = static_cast<uint32_t>(g.row_lo), n_rows = static_cast<uint32_t>(g.row_hi - g.row_lo);
+#pragma unroll
+            for (int h = 0; h < 5; ++h)
+            {
+                if (static_cast<uint32_t>(h) < g.hash_funs)
+                {
+                    uint64_t x = v * hash_seed(h);
+                    x ^= x >> g.hash_shift;
+                    x *= 11400714819323198485ULL;
+                    uint32_t const row = static_cast<uint32_t>(((x >> 32) * bs + (((x & 0xffffffffULL) * bs) >> 32)) >> 32);
+                    if (row - lo < n_rows) // this pass's slice of the matrix (the L2-resident one)
+                        atomicOr(reinterpret_cast<unsigned long long *>(base + static_cast<uint64_t>(row) * stride + col), bit);
+                }
+            }
+            return;
+        }
+#pragma unroll
+        for (int h = 0; h < 5; ++h)
+        {
+            if (static_cast<uint32_t>(h) < g.hash_funs)
+            {
+                uint64_t const row = hash_row(v, h, g.hash_shift, g.bin_size);
+                if (row - g.row_lo < g.row_hi - g.row_lo)
+                    atomicOr(reinterpret_cast<unsigned long long *>(base + row * stride + col), bit);
+            }
         }
     }
 };
@@ -419,7 +448,8 @@ __global__ void __launch_bounds__(256)
     }
 }
 
-// DNA flavour.  One emit per rolled symbol (plus one per record for the initial k-mer), so a thread owns
+// DNA flavour (run_len steps per thread: the warm-up below costs up to 33 rolls per thread whatever the run length, so DNA
+// threads take longer runs than the peptide kernel's 16).  One emit per rolled symbol (plus one per record for the initial k-mer), so a thread owns
 // the STEPS whose byte lies in its 16-byte run: it rebuilds the rolling stores from the preceding
 // dna_warmup(k) symbols (or from the record start) and then rolls through its run.  That reproduces the
 // reference's emits exactly, including the wrap-around k-mers of nucleotide_decomposer.h:110 (the whole
@@ -427,16 +457,16 @@ __global__ void __launch_bounds__(256)
 __global__ void __launch_bounds__(256)
     emplace_dna_kernel(ibf_geom g, uint8_t const * __restrict__ text, uint64_t n_residues,
                        uint64_t const * __restrict__ rec_offsets, uint32_t const * __restrict__ rec_bin,
-                       uint64_t n_records, uint32_t k)
+                       uint64_t n_records, uint32_t k, uint32_t run_len)
 {
     uint64_t const mask = (2 * k >= 64) ? ~0ULL : ((1ULL << (2 * k)) - 1);
     uint32_t const left_shift = 2 * k - 2;
-    uint64_t const n_runs = (n_residues + kRun - 1) / kRun;
+    uint64_t const n_runs = (n_residues + run_len - 1) / run_len;
     for (uint64_t run = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; run < n_runs;
          run += static_cast<uint64_t>(gridDim.x) * blockDim.x)
     {
-        uint64_t const p0 = run * kRun;
-        uint64_t const run_end = min(p0 + kRun, n_residues);
+        uint64_t const p0 = run * run_len;
+        uint64_t const run_end = min(p0 + run_len, n_residues);
         uint64_t lo = 0, hi = n_records;
         while (hi - lo > 1)
         {
