@@ -264,6 +264,21 @@ int trx_regex_scan_begin(trx_text_t *text, trx_regex_t *re, const uint64_t *cand
                          const uint8_t *map256, uint64_t cap, int *ticket);
 int trx_regex_scan_end(trx_text_t *text, int ticket, trx_hit *hits, uint64_t *n_hits, uint64_t *stats);
 
+/* K4 for a BATCH of patterns in one pass over the text — run_multiple_queries (include/query.h:330-340: a file of motifs,
+ * each verified against its own candidate bins) and the Set-based verify of the conjunction path (include/query.h:191-224,
+ * src/query.cpp:318-339) without re-reading the text per pattern.  Pattern i is scanned over the bins set in
+ * candidate_bin_words[i * cand_stride_words ...] (cand_stride_words = 0: all patterns share one bitmap); forward strand,
+ * no byte map.  hits come back grouped by pattern, each group in trx_regex_scan's order; hit_pattern[j] = pattern of
+ * hits[j]; per_pattern_hits (nullable) = group sizes.  More than cap hits: TRX_ECAPACITY, *n_hits = a lower bound.
+ * Every tile of the union of candidate bins is read ONCE per launch of up to 128 patterns: occurrence bitmasks of the
+ * batch's alphabet are built per tile and every pattern's necessary-factor plan is evaluated on them; patterns without
+ * such a plan, or with more than 8192 candidate records, go through trx_regex_scan internally (same results).
+ * stats (nullable, 4 entries): residues read by the shared passes, patterns answered by them, patterns answered one at a
+ * time, shared passes launched. */
+int trx_regex_scan_multi(trx_text_t *text, trx_regex_t *const *regexes, uint32_t n_patterns,
+                         const uint64_t *candidate_bin_words, uint64_t cand_stride_words, trx_hit *hits,
+                         uint32_t *hit_pattern, uint64_t cap, uint64_t *n_hits, uint64_t *per_pattern_hits, uint64_t *stats);
+
 /* Host only, no device needed: the phase-1 prefilter trx_regex_scan would pick for this regex on a text with the
  * given relative byte frequencies (what RE2 does internally with its prefilter/memchr accelerations,
  * lib/re2/re2/prog.h ConfigurePrefixAccel — here the plan is visible so that tests can check it is a NECESSARY

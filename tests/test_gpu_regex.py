@@ -362,3 +362,79 @@ def test_prosite_pattern_batch_equals_re2(ctx, golden_dir, monkeypatch):
     for rx in regexes:
         rx.close()
     txt.close()
+
+
+def test_multi_pattern_scan_equals_re2_and_single_scans(ctx, golden_dir, monkeypatch):
+    """trx_regex_scan_multi (one pass over the text per batch of <= 128 patterns: shared occurrence masks + per-pattern
+    necessary-factor terms + one phase-2 launch) on BASELINE config 3's 1000 patterns over the /100 twin: every hit of
+    every pattern equals RE2's (tests/golden/prosite_batch.npz); most patterns really take the shared pass; with
+    per-pattern candidate bitmaps the answer equals trx_regex_scan's for each; TRX_REGEX_MULTI=off gives the same lists."""
+    from tetrex_b200 import synth
+    z = np.load(os.path.join(golden_dir, "prosite_batch.npz"))
+    residues, offs, rec_bin, _ = synth.swissprot_like(5700, 1024)
+    pats = synth.prosite_patterns(1000, 1000)
+    synth.plant_patterns(residues, offs, pats)
+    want_all = z["hits"]
+    bounds = np.searchsorted(want_all[:, 0], np.arange(len(pats) + 1))
+    txt = t.Text(ctx, residues, offs, rec_bin, 1024)
+    regexes = [t.Regex(p, True) for p in pats]
+    got, st = txt.scan_multi(regexes, cap=1 << 17, stats=True)
+    assert st["shared"] >= 900 and st["shared"] + st["single"] == 1000 and st["passes"] >= 8, st
+    wrong = [i for i in range(len(pats))
+             if not (np.array_equal(got[i][:, 1:], want_all[bounds[i]:bounds[i + 1], 1:]) and
+                     np.array_equal(got[i][:, 0], rec_bin[got[i][:, 1]]))]
+    assert not wrong, f"{len(wrong)} patterns differ from RE2, first {[(i, pats[i]) for i in wrong[:3]]}"
+    assert sum(len(g) for g in got) == len(want_all)
+    # per-pattern candidate bins: pattern i may only be verified in its own bins
+    rng = np.random.default_rng(3)
+    sub = list(range(0, 1000, 7))
+    cand = rng.integers(0, 2 ** 63, (len(sub), 16), dtype=np.uint64) | (rng.integers(0, 2 ** 63, (len(sub), 16), dtype=np.uint64) << np.uint64(1))
+    multi = txt.scan_multi([regexes[i] for i in sub], candidate_bins=cand, cap=1 << 17)
+    for k, i in enumerate(sub):
+        assert np.array_equal(multi[k], txt.scan(regexes[i], candidate_bins=cand[k], cap=1 << 16)), pats[i]
+    # the same batch with the shared pass switched off
+    monkeypatch.setenv("TRX_REGEX_MULTI", "off")
+    off, st_off = txt.scan_multi(regexes[:200], cap=1 << 17, stats=True)
+    assert st_off["shared"] == 0 and st_off["single"] == 200
+    assert all(np.array_equal(a, b) for a, b in zip(off, got[:200]))
+    monkeypatch.delenv("TRX_REGEX_MULTI")
+    # capacity: too small a buffer is reported, not truncated
+    with pytest.raises(t.TetrexError) as e:
+        txt.scan_multi(regexes, cap=100)
+    assert e.value.code == -5
+    # an empty batch and a batch of one
+    assert txt.scan_multi([]) == []
+    assert np.array_equal(txt.scan_multi([regexes[0]])[0], got[0])
+    for rx in regexes:
+        rx.close()
+    txt.close()
+
+
+def test_multi_pattern_scan_dna_and_edge_shapes(ctx):
+    """Other alphabets and shapes through the shared pass: DNA literals, a pattern repeated in one batch, patterns that share
+    no letters, matches straddling chunk / tile boundaries (records of 40 000 residues), anchored and unfilterable patterns
+    (single path inside the same call)."""
+    rng = random.Random(11)
+    seqs, rec_bin = [], []
+    for b in range(6):
+        for r in range(3):
+            n = rng.choice([50, 4000, 40000])
+            s = bytearray(rng.choice(b"ACGT") for _ in range(n))
+            for at in (0, 120, 125, n - 9, n // 2, 32760 if n > 33000 else 7):
+                if 0 <= at <= n - 8:
+                    s[at:at + 8] = rng.choice([b"GATTACAG", b"TTGACGTA", b"GGGCCCAT"])
+            seqs.append(bytes(s))
+            rec_bin.append(b)
+    txt = build_text(ctx, seqs, rec_bin, 6)
+    pats = ["GATTACAG", "TTGACGTA", "GAT{2}ACA", "GG(G|A)CCCAT", "GATTACAG", "TTGAC.TA", "^ACGT", "[AC]+GATTA", "T+", "GGGCCC(AT|TA)"]
+    regexes = [t.Regex(p, False) for p in pats]
+    got, st = txt.scan_multi(regexes, cap=1 << 20, stats=True)
+    assert st["shared"] >= 5, st
+    for p, rx, g in zip(pats, regexes, got):
+        assert np.array_equal(g, txt.scan(rx, cap=1 << 20)), p
+    cand = np.array([0b010110], dtype=np.uint64)
+    for g, rx in zip(txt.scan_multi(regexes, candidate_bins=cand, cap=1 << 20), regexes):
+        assert np.array_equal(g, txt.scan(rx, candidate_bins=cand, cap=1 << 20))
+    for rx in regexes:
+        rx.close()
+    txt.close()

@@ -458,6 +458,28 @@ class Text:
                     pass
         return out
 
+    def scan_multi(self, regexes, candidate_bins=None, cap=1 << 20, stats=False):
+        """A batch of patterns in shared passes over the text (trx_regex_scan_multi).  candidate_bins: None (all bins),
+        one bitmap for all patterns, or an (n_patterns, words) array.  Returns one (n,4) hit array per regex."""
+        n = len(regexes)
+        words = (self.n_bins + 63) // 64
+        cand = self._candidates(None) if candidate_bins is None else _np(candidate_bins, np.uint64)
+        stride = 0 if cand.ndim == 1 else words
+        assert cand.shape[-1] == words and (cand.ndim == 1 or cand.shape[0] == n)
+        handles = (C.c_void_p * max(n, 1))(*[rx._h for rx in regexes])
+        if getattr(self, "_mhit_cap", 0) != cap:
+            self._mhit_buf, self._mpat_buf, self._mhit_cap = (TrxHit * cap)(), np.zeros(cap, dtype=np.uint32), cap
+        total = C.c_uint64()
+        per = np.zeros(max(n, 1), dtype=np.uint64)
+        st = np.zeros(4, dtype=np.uint64)
+        check(lib().trx_regex_scan_multi(self._h, handles, n, _ptr(cand), stride, C.addressof(self._mhit_buf), _ptr(self._mpat_buf),
+                                         cap, C.byref(total), _ptr(per), _ptr(st)))
+        arr = np.frombuffer(self._mhit_buf, dtype=np.uint32, count=4 * total.value).reshape(-1, 4)
+        bounds = np.concatenate([[0], np.cumsum(per[:n])]).astype(np.int64)
+        out = [arr[bounds[i]:bounds[i + 1]].copy() for i in range(n)]
+        self.last_multi_stats = dict(zip(("residues", "shared", "single", "passes"), map(int, st)))
+        return (out, self.last_multi_stats) if stats else out
+
     def scan(self, regex: Regex, candidate_bins=None, reverse_strand=False, map256=None, cap=1 << 20, stats=False):
         """Returns an (n,4) uint32 array of (bin, record, start, end) in reference print order."""
         words = (self.n_bins + 63) // 64

@@ -484,6 +484,12 @@ struct resolve_params
     uint64_t * small_keys;             // the first kSmallHits hits go here: they sit next to the counters, so that
     uint32_t * small_ends;             // one device-to-host copy brings the count and (almost always) every hit
     uint64_t cap;
+    // multi-pattern scans (regex_scan_phase2_multi): hits of all patterns share one list, tagged with the pattern;
+    // nullptr = single-pattern scan.  rec_cap bounds the listed records (0 = no bound); chunk_flags may be nullptr
+    // (no chunk is skipped).
+    uint32_t * hit_pats;
+    uint32_t pattern_id;
+    uint32_t rec_cap;
 };
 
 // Anchored leftmost-longest match starting at position s of a record read through `at`: the automaton
@@ -594,9 +600,8 @@ __device__ int64_t match_first(regex_dev const & re, At at, int64_t s, int64_t L
 // first byte — and a ballot picks the leftmost start that really matches; the warp then jumps to the end of
 // that match (FindAndConsume) and goes on.  Chunks phase 1 did not flag are skipped whole.
 template <int W, int DIR>
-__global__ void __launch_bounds__(128) regex_scan_phase2(resolve_params p)
+__device__ __forceinline__ void phase2_body(resolve_params const & p, regex_dev & s_re)
 {
-    __shared__ regex_dev s_re; // the automaton, staged once per CTA: every attempt starts with a B[] lookup
     // usually a handful of records are listed: CTAs without work leave before staging anything
     if (static_cast<uint64_t>(blockIdx.x) * (blockDim.x >> 5) >= *p.rec_count)
         return;
@@ -609,7 +614,9 @@ __global__ void __launch_bounds__(128) regex_scan_phase2(resolve_params p)
     __syncthreads();
     regex_dev const & re = s_re;
     unsigned const lane = threadIdx.x & 31;
-    uint64_t const n_listed = *p.rec_count;
+    uint64_t n_listed = *p.rec_count;
+    if (p.rec_cap && n_listed > p.rec_cap)
+        n_listed = p.rec_cap; // the list overflowed: the host repeats this pattern on the single-pattern path
     uint64_t const warp0 = (static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
     uint64_t const n_warps = (static_cast<uint64_t>(gridDim.x) * blockDim.x) >> 5;
     for (uint64_t i = warp0; i < n_listed; i += n_warps)
@@ -629,7 +636,7 @@ __global__ void __launch_bounds__(128) regex_scan_phase2(resolve_params p)
             // first position (reading direction) that lies in the next chunk
             int64_t const next_chunk = DIR > 0 ? static_cast<int64_t>((ch + 1) * kChunkBytes - rb)
                                                : static_cast<int64_t>(re_off) - static_cast<int64_t>(ch * kChunkBytes);
-            if (!re.anchor_begin && !((p.chunk_flags[ch >> 5] >> (ch & 31)) & 1))
+            if (!re.anchor_begin && p.chunk_flags && !((p.chunk_flags[ch >> 5] >> (ch & 31)) & 1))
             {
                 s = next_chunk; // no match starts anywhere in this chunk
                 continue;
@@ -658,7 +665,13 @@ __global__ void __launch_bounds__(128) regex_scan_phase2(resolve_params p)
                     if (idx < p.cap)
                     {
                         uint64_t const key = (r << 32) | static_cast<uint64_t>(s + leader);
-                        if (idx < kSmallHits)
+                        if (p.hit_pats)
+                        {
+                            p.hit_keys[idx] = key;
+                            p.hit_ends[idx] = static_cast<uint32_t>(e_hit);
+                            p.hit_pats[idx] = p.pattern_id;
+                        }
+                        else if (idx < kSmallHits)
                         {
                             p.small_keys[idx] = key;
                             p.small_ends[idx] = static_cast<uint32_t>(e_hit);
@@ -680,6 +693,25 @@ __global__ void __launch_bounds__(128) regex_scan_phase2(resolve_params p)
             }
         }
     }
+}
+
+template <int W, int DIR>
+__global__ void __launch_bounds__(128) regex_scan_phase2(resolve_params p)
+{
+    __shared__ regex_dev s_re; // the automaton, staged once per CTA: every attempt starts with a B[] lookup
+    phase2_body<W, DIR>(p, s_re);
+}
+
+// one launch for a batch of patterns: blockIdx.y = pattern; its CTAs take that pattern's automaton and work list
+template <int W, int DIR>
+__global__ void __launch_bounds__(128) regex_scan_phase2_multi(resolve_params const * __restrict__ params)
+{
+    __shared__ regex_dev s_re;
+    __shared__ resolve_params s_p;
+    if (threadIdx.x == 0)
+        s_p = params[blockIdx.y];
+    __syncthreads();
+    phase2_body<W, DIR>(s_p, s_re);
 }
 
 } // namespace trx
@@ -1128,6 +1160,207 @@ __global__ void __launch_bounds__(256) byte_histogram_kernel(uint8_t const * __r
     __syncthreads();
     if (h[threadIdx.x])
         atomicAdd(hist + threadIdx.x, static_cast<unsigned long long>(h[threadIdx.x]));
+}
+
+// ------------------------------------------------------------------------------------------------------
+// Phase 1 for a BATCH of patterns: one pass over the text for all of them (run_multiple_queries,
+// include/query.h:330-340, loops over a file of motifs and re-reads every candidate bin per motif; the pattern-at-a-time
+// kernels above do the same with HBM).
+//
+// What is shared between patterns is everything that depends on the text only: the TMA tile, and the OCCURRENCE MASKS —
+// for every byte of the batch's alphabet (the union of the literals its prefilters test, <= kMultiLetters) one bit per
+// text position.  A thread owns a 128-byte row, builds its 4 mask words per letter once per tile and parks them in
+// shared memory, plane-wise (conflict-free).  After that a pattern's necessary condition — the same window / gapped-atom
+// plans the single-pattern kernels use, as one list of terms "letter l at anchor + d, d in [lo, hi]", atoms ANDed, terms
+// of an atom ORed — costs 5 LDS + a few funnel shifts per term and 128 anchors: ~0.5 instructions per residue and
+// pattern instead of 2.75-3.75, and no HBM traffic at all after the first pattern.  Survivors are confirmed (classes,
+// signed offsets: the plan's second stage) and listed per pattern for regex_scan_phase2_multi.
+constexpr int kMultiLetters = 24;
+constexpr int kMultiPatterns = 128; // per launch
+constexpr uint32_t kMultiListCap = 8192; // listed records per pattern; more = a pattern for the single-pattern path
+
+struct multi_terms // the part every thread walks for every tile: kept in shared memory
+{
+    int32_t n_terms;
+    uint8_t letter[kMaxAtomTerms], lo[kMaxAtomTerms], hi[kMaxAtomTerms], end[kMaxAtomTerms];
+};
+
+struct multi_program // per pattern, in global memory; the rest is only touched where an anchor survives
+{
+    multi_terms terms;
+    int32_t start_lo, start_hi; // a match's first byte lies in [anchor + start_lo, anchor + start_hi]
+    int32_t n_confirm;
+    confirm_check confirm[kMaxConfirm];
+    uint64_t const * cand_words; // candidate bins of THIS pattern
+    uint32_t * rec_flags;        // bitmap over records already listed for this pattern
+    uint32_t * rec_list;         // kMultiListCap entries
+    unsigned int * rec_count;
+};
+
+struct multi_params
+{
+    multi_program const * programs;
+    uint32_t n_patterns;
+    uint32_t n_letters;
+    uint32_t splat[kMultiLetters]; // letter byte replicated into the four lanes
+};
+
+template <int STAGES>
+__global__ void __launch_bounds__(kScanThreads + 32)
+    regex_filter_multi(scan_params p, multi_params mp, const __grid_constant__ CUtensorMap tmap)
+{
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    using ring_t = tile_ring<STAGES, kScanThreads>;
+    ring_t ring;
+    ring.init(smem_raw);
+    // [letter][word 0..3][row]: masks of the tile in flight; lookahead[letter]: first word of the row after the tile
+    uint32_t * const masks = reinterpret_cast<uint32_t *>(smem_raw + ((ring_t::kRingBytes + 15) & ~15));
+    uint32_t * const lookahead = masks + kMultiLetters * 4 * kScanThreads;
+    multi_terms * const s_terms = reinterpret_cast<multi_terms *>(lookahead + kMultiLetters);
+    for (uint32_t i = threadIdx.x; i < mp.n_patterns * (sizeof(multi_terms) / 4); i += blockDim.x)
+    {
+        uint32_t const pat = i / (sizeof(multi_terms) / 4), w = i % (sizeof(multi_terms) / 4);
+        reinterpret_cast<uint32_t *>(s_terms + pat)[w] = reinterpret_cast<uint32_t const *>(&mp.programs[pat].terms)[w];
+    }
+    __syncthreads();
+    if (ring.is_producer())
+    {
+        ring.produce(p, &tmap);
+        return;
+    }
+    int const tid = threadIdx.x;
+    uint8_t const * tile;
+    uint32_t tile_id;
+    while (ring.acquire(tile, tile_id))
+    {
+        uint64_t const g_lo = (static_cast<uint64_t>(tile_id) * kScanThreads + tid) * kChunkBytes;
+        uint32_t w[32];
+        {
+            uint8_t const * row = tile + tid * kChunkBytes;
+#pragma unroll
+            for (int piece = 0; piece < 8; ++piece)
+            {
+                uint4 const v = *reinterpret_cast<uint4 const *>(row + ((piece ^ (tid & 7)) << 4));
+                w[4 * piece + 0] = v.x;
+                w[4 * piece + 1] = v.y;
+                w[4 * piece + 2] = v.z;
+                w[4 * piece + 3] = v.w;
+            }
+        }
+        ring.release(); // the row is in registers: the producer may refill the stage while the batch is evaluated
+        for (uint32_t l = 0; l < mp.n_letters; ++l)
+        {
+            uint32_t const x = mp.splat[l];
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+            {
+                uint32_t mm = 0;
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    mm |= literal_nibble(w[8 * q + j], x) << (4 * j);
+                masks[(l * 4 + q) * kScanThreads + tid] = mm;
+            }
+        }
+        if (tid == kScanThreads - 1)
+        {
+            // the 32 bytes after the tile belong to another tile: straight from global memory
+            uint32_t la[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+            if (g_lo + kChunkBytes + 32 <= p.n_text_padded)
+            {
+                uint4 const v0 = __ldg(reinterpret_cast<uint4 const *>(p.text + g_lo + kChunkBytes));
+                uint4 const v1 = __ldg(reinterpret_cast<uint4 const *>(p.text + g_lo + kChunkBytes + 16));
+                la[0] = v0.x, la[1] = v0.y, la[2] = v0.z, la[3] = v0.w, la[4] = v1.x, la[5] = v1.y, la[6] = v1.z, la[7] = v1.w;
+            }
+            for (uint32_t l = 0; l < mp.n_letters; ++l)
+            {
+                uint32_t mm = 0;
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    mm |= literal_nibble(la[j], mp.splat[l]) << (4 * j);
+                // zero padding compares equal to a letter only if that letter is byte 0, which no pattern literal is
+                lookahead[l] = mm;
+            }
+        }
+        asm volatile("bar.sync 1, %0;" ::"n"(kScanThreads) : "memory"); // consumers only; once per tile and BATCH
+        bool const real = g_lo < p.n_text;
+        for (uint32_t pat = 0; pat < mp.n_patterns; ++pat)
+        {
+            multi_terms const & T = s_terms[pat];
+            uint32_t acc0 = ~0u, acc1 = ~0u, acc2 = ~0u, acc3 = ~0u, r0 = 0, r1 = 0, r2 = 0, r3 = 0;
+            for (int i = 0; i < T.n_terms; ++i)
+            {
+                uint32_t const * const m = masks + static_cast<uint32_t>(T.letter[i]) * 4 * kScanThreads + tid;
+                uint32_t const m0 = m[0], m1 = m[kScanThreads], m2 = m[2 * kScanThreads], m3 = m[3 * kScanThreads];
+                uint32_t const m4 = tid + 1 < kScanThreads ? m[1] : lookahead[T.letter[i]];
+                for (uint32_t d = T.lo[i]; d <= T.hi[i]; ++d)
+                {
+                    r0 |= __funnelshift_r(m0, m1, d);
+                    r1 |= __funnelshift_r(m1, m2, d);
+                    r2 |= __funnelshift_r(m2, m3, d);
+                    r3 |= __funnelshift_r(m3, m4, d);
+                }
+                if (T.end[i])
+                {
+                    acc0 &= r0, acc1 &= r1, acc2 &= r2, acc3 &= r3;
+                    r0 = r1 = r2 = r3 = 0;
+                }
+            }
+            if (!((acc0 | acc1 | acc2 | acc3) && real))
+                continue;
+            // rare path: every surviving bit is an anchor of pattern `pat`
+            multi_program const & P = mp.programs[pat];
+            uint32_t const acc[4] = {acc0, acc1, acc2, acc3};
+            for (int q = 0; q < 4; ++q)
+            {
+                uint32_t bits = acc[q];
+                while (bits)
+                {
+                    int const b = __ffs(bits) - 1;
+                    bits &= bits - 1;
+                    int64_t const anchor = static_cast<int64_t>(g_lo) + 32 * q + b;
+                    bool confirmed = true;
+                    for (int c = 0; c < P.n_confirm && confirmed; ++c)
+                    {
+                        bool found = false;
+                        for (int d = P.confirm[c].lo; d <= P.confirm[c].hi && !found; ++d)
+                        {
+                            int64_t const a = anchor + d;
+                            if (a >= 0 && a < static_cast<int64_t>(p.n_text))
+                            {
+                                uint32_t const byte = __ldg(p.text + a);
+                                found = (P.confirm[c].mask[byte >> 5] >> (byte & 31)) & 1;
+                            }
+                        }
+                        confirmed = found;
+                    }
+                    if (!confirmed)
+                        continue;
+                    int64_t lo = anchor + P.start_lo, hi = anchor + P.start_hi;
+                    if (hi < 0 || lo >= static_cast<int64_t>(p.n_text))
+                        continue;
+                    lo = lo < 0 ? 0 : lo;
+                    hi = hi >= static_cast<int64_t>(p.n_text) ? static_cast<int64_t>(p.n_text) - 1 : hi;
+                    uint64_t r = record_of(p.rec_offsets, p.n_records, static_cast<uint64_t>(lo));
+                    while (r < p.n_records && __ldg(p.rec_offsets + r) <= static_cast<uint64_t>(hi))
+                    {
+                        if (__ldg(p.rec_offsets + r + 1) > static_cast<uint64_t>(lo) && is_candidate(P.cand_words, __ldg(p.rec_bin + r)))
+                        {
+                            uint32_t const bit = 1u << (r & 31);
+                            uint32_t const old = atomicOr(P.rec_flags + (r >> 5), bit);
+                            if (!(old & bit))
+                            {
+                                unsigned const at = atomicAdd(P.rec_count, 1u);
+                                if (at < kMultiListCap)
+                                    P.rec_list[at] = static_cast<uint32_t>(r);
+                            }
+                        }
+                        ++r;
+                    }
+                }
+            }
+        }
+        asm volatile("bar.sync 1, %0;" ::"n"(kScanThreads) : "memory"); // nobody still reads the masks of this tile
+    }
 }
 
 } // namespace trx

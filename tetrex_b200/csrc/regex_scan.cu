@@ -70,6 +70,11 @@ struct trx_text
     std::vector<cached_choice> choices;
     // per-scan scratch
     trx::scratch d_keys2, d_ends2, d_sort_tmp;
+    // multi-pattern scans (trx_regex_scan_multi): one staging block up (programs, automata, candidate words, phase-2
+    // parameters), one block of flags / lists / counters, one hit list
+    trx::scratch m_h_stage, m_d_stage, m_d_flags, m_d_lists, m_d_counters, m_d_tiles, m_d_hit_keys, m_d_hit_ends, m_d_hit_pats,
+        m_h_back;
+    bool multi_attr_set{false};
 };
 
 using namespace trx;
@@ -239,7 +244,8 @@ void trx_text_destroy(trx_text_t * t)
         for (trx::scratch * s : {&sl.d_stage, &sl.h_stage, &sl.h_small, &sl.d_keys, &sl.d_ends, &sl.d_tiles})
             s->release();
     }
-    for (trx::scratch * s : {&t->d_keys2, &t->d_ends2, &t->d_sort_tmp})
+    for (trx::scratch * s : {&t->d_keys2, &t->d_ends2, &t->d_sort_tmp, &t->m_h_stage, &t->m_d_stage, &t->m_d_flags, &t->m_d_lists,
+                             &t->m_d_counters, &t->m_d_tiles, &t->m_d_hit_keys, &t->m_d_hit_ends, &t->m_d_hit_pats, &t->m_h_back})
         s->release();
     delete t;
 }
@@ -1344,6 +1350,410 @@ int trx_regex_filter_plan(const trx_regex_t * re, const double * byte_freq, int 
             for (int w = 0; w < 8; ++w)
                 out[74 + 10 * c + w] = static_cast<int32_t>(atoms.confirm[c].mask[w]);
         }
+    }
+    return TRX_OK;
+}
+
+} // extern "C"
+
+
+// ------------------------------------------------------------------------------------------------ multi-pattern scan
+namespace
+{
+
+struct multi_plan
+{
+    multi_program prog{};           // terms / start range / confirm checks filled in, pointers not yet
+    bool usable{false};
+};
+
+// One pattern's phase-1 plan (the cached window / atoms choice of the single-pattern path) as a term list over the
+// batch's alphabet.  `letter_of[byte]` = index into the alphabet, growing as new bytes appear; false = the alphabet is
+// full, or the pattern has no prefilter at all (exact automaton only): such patterns take the single-pattern path.
+bool plan_for_multi(filter_kind kind, filter_spec const & window, atom_spec const & atoms, int letter_of[256],
+                    uint32_t splat[kMultiLetters], uint32_t & n_letters, multi_plan & out)
+{
+    int local_of[256];
+    memcpy(local_of, letter_of, sizeof local_of);
+    uint32_t local_n = n_letters;
+    uint32_t local_splat[kMultiLetters];
+    memcpy(local_splat, splat, sizeof local_splat);
+    auto letter = [&](uint32_t byte) -> int {
+        if (local_of[byte] < 0)
+        {
+            if (local_n >= static_cast<uint32_t>(kMultiLetters) || byte == 0)
+                return -1;
+            local_of[byte] = static_cast<int>(local_n);
+            local_splat[local_n++] = byte * 0x01010101u;
+        }
+        return local_of[byte];
+    };
+    multi_program & P = out.prog;
+    P = multi_program{};
+    if (kind == kFilterWindow)
+    {
+        int const n = window.n_a + window.n_b;
+        for (int j = 0; j < n; ++j)
+        {
+            int const l = letter(window.splat[j] & 0xFF);
+            if (l < 0)
+                return false;
+            uint32_t const off = window.delta[j] + (j >= window.n_a ? 4 : 0); // byte offset inside the 8-byte window
+            P.terms.letter[j] = static_cast<uint8_t>(l);
+            P.terms.lo[j] = P.terms.hi[j] = static_cast<uint8_t>(off);
+            P.terms.end[j] = 1;
+        }
+        P.terms.n_terms = n;
+        P.start_lo = P.start_hi = window.start_delta;
+        P.n_confirm = 0;
+    }
+    else if (kind == kFilterAtoms)
+    {
+        for (int i = 0; i < atoms.n_terms; ++i)
+        {
+            int const l = letter(atoms.splat[atoms.term_lit[i]] & 0xFF);
+            if (l < 0)
+                return false;
+            P.terms.letter[i] = static_cast<uint8_t>(l);
+            P.terms.lo[i] = atoms.term_lo[i];
+            P.terms.hi[i] = atoms.term_hi[i];
+            P.terms.end[i] = atoms.term_end[i];
+        }
+        P.terms.n_terms = atoms.n_terms;
+        P.start_lo = atoms.start_lo;
+        P.start_hi = atoms.start_hi;
+        P.n_confirm = atoms.n_confirm;
+        memcpy(P.confirm, atoms.confirm, sizeof P.confirm);
+    }
+    else
+        return false;
+    if (P.terms.n_terms <= 0)
+        return false;
+    memcpy(letter_of, local_of, sizeof local_of);
+    memcpy(splat, local_splat, sizeof local_splat);
+    n_letters = local_n;
+    out.usable = true;
+    return true;
+}
+
+} // namespace
+
+extern "C"
+{
+
+int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t n_patterns,
+                         const uint64_t * candidate_bin_words, uint64_t cand_stride_words, trx_hit * hits,
+                         uint32_t * hit_pattern, uint64_t cap, uint64_t * n_hits, uint64_t * per_pattern_hits,
+                         uint64_t * stats)
+{
+    if (!t || !regexes || !candidate_bin_words || !n_hits || (cap && (!hits || !hit_pattern)))
+        return set_error(TRX_EINVAL, "trx_regex_scan_multi: NULL argument");
+    *n_hits = 0;
+    for (uint32_t i = 0; i < n_patterns; ++i)
+        if (!regexes[i])
+            return set_error(TRX_EINVAL, "trx_regex_scan_multi: pattern %u is NULL", i);
+    uint64_t const cand_words = (t->n_bins + 63) / 64;
+    if (cand_stride_words != 0 && cand_stride_words < cand_words)
+        return set_error(TRX_EINVAL, "trx_regex_scan_multi: candidate stride %llu < %llu words per pattern",
+                         (unsigned long long)cand_stride_words, (unsigned long long)cand_words);
+    if (per_pattern_hits)
+        memset(per_pattern_hits, 0, n_patterns * sizeof(uint64_t));
+    if (stats)
+        stats[0] = stats[1] = stats[2] = stats[3] = 0;
+    if (n_patterns == 0)
+        return TRX_OK;
+    trx_ctx * c = t->ctx;
+    TRX_TRY(c->use());
+    cudaStream_t const st = c->stream;
+    auto cand_of = [&](uint32_t i) { return candidate_bin_words + static_cast<uint64_t>(i) * cand_stride_words; };
+
+    struct tagged_hit
+    {
+        uint32_t pat, rec, start, end;
+    };
+    std::vector<tagged_hit> all;
+    std::vector<uint32_t> single; // patterns for the pattern-at-a-time path
+
+    // ---- every pattern's phase-1 plan (cached per text like the single-pattern path does)
+    char const * filt = getenv("TRX_REGEX_FILTER");
+    char const * multi_off = getenv("TRX_REGEX_MULTI"); // TRX_REGEX_MULTI=off: every pattern on the single path (A/B, tests)
+    bool const shared_pass = t->has_tmap && !filt && !(multi_off && strcmp(multi_off, "off") == 0);
+    auto img = std::make_unique<regex_dev>();
+    uint32_t next = 0;
+    while (shared_pass && next < n_patterns)
+    {
+        // ---- a batch: up to kMultiPatterns patterns whose prefilter literals fit one alphabet of kMultiLetters bytes
+        int letter_of[256];
+        for (int & x : letter_of)
+            x = -1;
+        multi_params mp{};
+        std::vector<multi_plan> plans;
+        std::vector<uint32_t> ids;
+        while (next < n_patterns && ids.size() < static_cast<size_t>(kMultiPatterns))
+        {
+            trx_regex_t * re = regexes[next];
+            trx_text::cached_choice const * found = nullptr;
+            for (auto const & cc : t->choices)
+                if (cc.serial == re->serial && cc.reverse == 0 && cc.mode == 0 && cc.map_hash == 0)
+                    found = &cc;
+            if (!found)
+            {
+                fill_image(*re, false, nullptr, img.get());
+                trx_text::cached_choice cc{};
+                cc.serial = re->serial;
+                cc.kind = choose_filter(*img, t->byte_freq, false, cc.window, cc.atoms);
+                if (t->choices.size() >= 4096)
+                    t->choices.clear();
+                t->choices.push_back(cc);
+                found = &t->choices.back();
+            }
+            multi_plan plan;
+            uint32_t const letters_before = mp.n_letters;
+            bool const ok = re->follow_list.size() <= sizeof(regex_dev::follow_list) &&
+                            plan_for_multi(static_cast<filter_kind>(found->kind), found->window, found->atoms, letter_of, mp.splat,
+                                           mp.n_letters, plan);
+            if (!ok)
+            {
+                bool const alphabet_full = found->kind != kFilterNone && letters_before > 0 && !ids.empty() &&
+                                           re->follow_list.size() <= sizeof(regex_dev::follow_list);
+                if (alphabet_full)
+                {
+                    // does it fit an empty alphabet?  then it opens the next batch; otherwise it is a single-path pattern
+                    int fresh_of[256];
+                    for (int & x : fresh_of)
+                        x = -1;
+                    uint32_t fresh_splat[kMultiLetters], fresh_n = 0;
+                    multi_plan probe;
+                    if (plan_for_multi(static_cast<filter_kind>(found->kind), found->window, found->atoms, fresh_of, fresh_splat,
+                                       fresh_n, probe))
+                        break; // close this batch, the pattern is retried as the first of the next one
+                }
+                single.push_back(next++);
+                continue;
+            }
+            plans.push_back(plan);
+            ids.push_back(next++);
+        }
+        if (ids.empty())
+            continue;
+        uint32_t const nb = static_cast<uint32_t>(ids.size());
+        mp.n_patterns = nb;
+
+        // ---- tiles: the union of the batch's candidate bins
+        std::vector<uint64_t> uni(cand_words, 0);
+        for (uint32_t k = 0; k < nb; ++k)
+            for (uint64_t w = 0; w < cand_words; ++w)
+                uni[w] |= cand_of(ids[k])[w];
+        std::vector<uint32_t> tiles;
+        uint64_t residues = 0;
+        for (uint64_t b = 0; b < t->n_bins; ++b)
+        {
+            if (!((uni[b >> 6] >> (b & 63)) & 1))
+                continue;
+            uint64_t const r0 = t->h_bin_rec_begin[b], r1 = t->h_bin_rec_begin[b + 1];
+            if (r0 == r1)
+                continue;
+            uint64_t const g0 = t->h_rec_offsets[r0], g1 = t->h_rec_offsets[r1];
+            if (g1 == g0)
+                continue;
+            residues += g1 - g0;
+            for (uint64_t tile = g0 / kTileBytes; tile <= (g1 - 1) / kTileBytes; ++tile)
+                if (tiles.empty() || tiles.back() != tile)
+                    tiles.push_back(static_cast<uint32_t>(tile));
+        }
+        if (stats)
+        {
+            stats[0] += residues;
+            stats[1] += nb;
+            stats[3] += 1;
+        }
+        if (tiles.empty())
+            continue; // no candidate bin holds a residue: no hits for this batch
+
+        // ---- device blocks.  staging (one H2D): [programs | automata | candidate words | phase-2 parameters]
+        uint64_t const rfw = t->n_rec_flag_words;
+        size_t const off_prog = 0;
+        size_t const off_img = align16(off_prog + nb * sizeof(multi_program));
+        size_t const off_cand = align16(off_img + nb * sizeof(regex_dev));
+        size_t const off_rp = align16(off_cand + static_cast<size_t>(nb) * cand_words * 8);
+        size_t const stage_bytes = off_rp + nb * sizeof(resolve_params);
+        t->m_h_stage.pinned_host = true;
+        TRX_TRY(t->m_h_stage.reserve(stage_bytes));
+        TRX_TRY(t->m_d_stage.reserve(stage_bytes));
+        TRX_TRY(t->m_d_flags.reserve(static_cast<size_t>(nb) * rfw * 4));
+        TRX_TRY(t->m_d_lists.reserve(static_cast<size_t>(nb) * kMultiListCap * 4));
+        size_t const counter_bytes = 16 + static_cast<size_t>(nb) * 4; // hit count (u64), tile counter (u32), pad, listed records per pattern
+        TRX_TRY(t->m_d_counters.reserve(counter_bytes));
+        TRX_TRY(t->m_d_tiles.reserve(tiles.size() * 4));
+        uint64_t const dev_cap = cap ? cap : 1;
+        TRX_TRY(t->m_d_hit_keys.reserve(dev_cap * 8));
+        TRX_TRY(t->m_d_hit_ends.reserve(dev_cap * 4));
+        TRX_TRY(t->m_d_hit_pats.reserve(dev_cap * 4));
+        auto * hs = static_cast<uint8_t *>(t->m_h_stage.ptr);
+        auto * ds = static_cast<uint8_t *>(t->m_d_stage.ptr);
+        auto * d_counters = static_cast<uint8_t *>(t->m_d_counters.ptr);
+        auto * h_prog = reinterpret_cast<multi_program *>(hs + off_prog);
+        auto * h_rp = reinterpret_cast<resolve_params *>(hs + off_rp);
+        for (uint32_t k = 0; k < nb; ++k)
+        {
+            fill_image(*regexes[ids[k]], false, nullptr, reinterpret_cast<regex_dev *>(hs + off_img) + k);
+            memcpy(hs + off_cand + static_cast<size_t>(k) * cand_words * 8, cand_of(ids[k]), cand_words * 8);
+            multi_program & P = h_prog[k];
+            P = plans[k].prog;
+            P.cand_words = reinterpret_cast<uint64_t const *>(ds + off_cand) + static_cast<size_t>(k) * cand_words;
+            P.rec_flags = static_cast<uint32_t *>(t->m_d_flags.ptr) + static_cast<size_t>(k) * rfw;
+            P.rec_list = static_cast<uint32_t *>(t->m_d_lists.ptr) + static_cast<size_t>(k) * kMultiListCap;
+            P.rec_count = reinterpret_cast<unsigned int *>(d_counters + 16) + k;
+            resolve_params & rp = h_rp[k];
+            rp = resolve_params{};
+            rp.text = t->d_text;
+            rp.rec_offsets = t->d_rec_offsets;
+            rp.rec_list = P.rec_list;
+            rp.rec_count = P.rec_count;
+            rp.chunk_flags = nullptr; // per-pattern chunk bitmaps would cost 200 KB each: phase 2 tests every start
+            rp.re = reinterpret_cast<regex_dev const *>(ds + off_img) + k;
+            rp.hit_count = reinterpret_cast<unsigned long long *>(d_counters);
+            rp.hit_keys = static_cast<uint64_t *>(t->m_d_hit_keys.ptr);
+            rp.hit_ends = static_cast<uint32_t *>(t->m_d_hit_ends.ptr);
+            rp.hit_pats = static_cast<uint32_t *>(t->m_d_hit_pats.ptr);
+            rp.pattern_id = k;
+            rp.rec_cap = kMultiListCap;
+            rp.cap = cap;
+        }
+        TRX_CUDA(cudaMemsetAsync(t->m_d_flags.ptr, 0, static_cast<size_t>(nb) * rfw * 4, st));
+        TRX_CUDA(cudaMemsetAsync(d_counters, 0, counter_bytes, st));
+        TRX_CUDA(cudaMemcpyAsync(ds, hs, stage_bytes, cudaMemcpyHostToDevice, st));
+        TRX_CUDA(cudaMemcpyAsync(t->m_d_tiles.ptr, tiles.data(), tiles.size() * 4, cudaMemcpyHostToDevice, st));
+        mp.programs = reinterpret_cast<multi_program const *>(ds + off_prog);
+        scan_params sp{};
+        sp.text = t->d_text;
+        sp.n_text = t->n_text;
+        sp.n_text_padded = t->n_text_padded;
+        sp.rec_offsets = t->d_rec_offsets;
+        sp.rec_bin = t->d_rec_bin;
+        sp.n_records = t->n_records;
+        sp.tiles = static_cast<uint32_t *>(t->m_d_tiles.ptr);
+        sp.n_tiles = static_cast<uint32_t>(tiles.size());
+        sp.tile_counter = reinterpret_cast<unsigned int *>(d_counters + 8);
+        {
+            constexpr int STAGES = 2;
+            size_t const smem = ((tile_ring<STAGES, kScanThreads>::kRingBytes + 15) & ~size_t{15}) +
+                                (static_cast<size_t>(kMultiLetters) * 4 * kScanThreads + kMultiLetters) * 4 +
+                                static_cast<size_t>(kMultiPatterns) * sizeof(multi_terms) + 1024;
+            if (!t->multi_attr_set)
+            {
+                TRX_CUDA(cudaFuncSetAttribute(regex_filter_multi<STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              static_cast<int>(smem)));
+                t->multi_attr_set = true;
+            }
+            unsigned const grid = std::min<unsigned>(static_cast<unsigned>(c->sm_count), sp.n_tiles);
+            regex_filter_multi<STAGES><<<grid, kScanThreads + 32, smem, st>>>(sp, mp, t->tmap);
+            ++c->launches;
+            TRX_CUDA(cudaGetLastError());
+        }
+        regex_scan_phase2_multi<2, 1><<<dim3(16, nb), 128, 0, st>>>(reinterpret_cast<resolve_params const *>(ds + off_rp));
+        ++c->launches;
+        TRX_CUDA(cudaGetLastError());
+
+        // ---- read back: counters first (how many hits, which lists overflowed), then the hit triples
+        t->m_h_back.pinned_host = true;
+        TRX_TRY(t->m_h_back.reserve(counter_bytes));
+        TRX_CUDA(cudaMemcpyAsync(t->m_h_back.ptr, d_counters, counter_bytes, cudaMemcpyDeviceToHost, st));
+        TRX_CUDA(cudaStreamSynchronize(st));
+        auto const * h_back = static_cast<uint8_t const *>(t->m_h_back.ptr);
+        unsigned long long const batch_hits = *reinterpret_cast<unsigned long long const *>(h_back);
+        auto const * listed = reinterpret_cast<uint32_t const *>(h_back + 16);
+        if (batch_hits > cap)
+        {
+            *n_hits = all.size() + batch_hits;
+            return set_error(TRX_ECAPACITY, "trx_regex_scan_multi: at least %llu hits, room for %llu",
+                             (unsigned long long)(all.size() + batch_hits), (unsigned long long)cap);
+        }
+        std::vector<char> overflowed(nb, 0);
+        for (uint32_t k = 0; k < nb; ++k)
+            if (listed[k] > kMultiListCap)
+            {
+                overflowed[k] = 1; // more candidate records than the shared pass lists: the single-pattern path takes it
+                single.push_back(ids[k]);
+                if (stats)
+                    --stats[1];
+            }
+        if (batch_hits)
+        {
+            std::vector<uint64_t> keys(batch_hits);
+            std::vector<uint32_t> ends(batch_hits), pats(batch_hits);
+            TRX_CUDA(cudaMemcpyAsync(keys.data(), t->m_d_hit_keys.ptr, batch_hits * 8, cudaMemcpyDeviceToHost, st));
+            TRX_CUDA(cudaMemcpyAsync(ends.data(), t->m_d_hit_ends.ptr, batch_hits * 4, cudaMemcpyDeviceToHost, st));
+            TRX_CUDA(cudaMemcpyAsync(pats.data(), t->m_d_hit_pats.ptr, batch_hits * 4, cudaMemcpyDeviceToHost, st));
+            TRX_CUDA(cudaStreamSynchronize(st));
+            for (uint64_t i = 0; i < batch_hits; ++i)
+                if (!overflowed[pats[i]])
+                    all.push_back(tagged_hit{ids[pats[i]], static_cast<uint32_t>(keys[i] >> 32), static_cast<uint32_t>(keys[i]), ends[i]});
+        }
+    }
+    if (!shared_pass)
+        for (uint32_t i = 0; i < n_patterns; ++i)
+            single.push_back(i);
+
+    // ---- patterns without a usable prefilter, with an alphabet of their own, or with too many candidate records:
+    // pattern at a time, pipelined over the scan slots like a caller of trx_regex_scan_begin/_end would
+    if (stats)
+        stats[2] = single.size();
+    {
+        std::vector<trx_hit> buf;
+        std::vector<std::pair<int, uint32_t>> pending; // (ticket, pattern)
+        uint64_t const one_cap = cap ? cap : 1;
+        auto finish = [&](std::pair<int, uint32_t> pr) -> int {
+            buf.resize(one_cap);
+            uint64_t n = 0;
+            int const rc = trx_regex_scan_end(t, pr.first, buf.data(), &n, nullptr);
+            if (rc == TRX_ECAPACITY)
+                *n_hits = all.size() + n;
+            TRX_TRY(rc);
+            for (uint64_t i = 0; i < n; ++i)
+                all.push_back(tagged_hit{pr.second, buf[i].record, buf[i].start, buf[i].end});
+            return TRX_OK;
+        };
+        int rc = TRX_OK;
+        for (uint32_t i : single)
+        {
+            if (pending.size() == 3)
+            {
+                rc = finish(pending.front());
+                pending.erase(pending.begin());
+                if (rc != TRX_OK)
+                    break;
+            }
+            int ticket = -1;
+            rc = trx_regex_scan_begin(t, regexes[i], cand_of(i), 0, nullptr, one_cap, &ticket);
+            if (rc != TRX_OK)
+                break;
+            pending.push_back({ticket, i});
+        }
+        for (auto const & pr : pending)
+        {
+            if (rc == TRX_OK)
+                rc = finish(pr);
+            else
+                trx_regex_scan_end(t, pr.first, nullptr, nullptr, nullptr); // abandon
+        }
+        TRX_TRY(rc);
+    }
+
+    // ---- print order per pattern: (pattern, bin, record, start); records are grouped by ascending bin
+    *n_hits = all.size();
+    if (all.size() > cap)
+        return set_error(TRX_ECAPACITY, "trx_regex_scan_multi: %llu hits, room for %llu", (unsigned long long)all.size(),
+                         (unsigned long long)cap);
+    std::sort(all.begin(), all.end(), [](tagged_hit const & a, tagged_hit const & b) {
+        return a.pat != b.pat ? a.pat < b.pat : (a.rec != b.rec ? a.rec < b.rec : a.start < b.start);
+    });
+    for (size_t i = 0; i < all.size(); ++i)
+    {
+        hits[i] = trx_hit{t->h_rec_bin[all[i].rec], all[i].rec, all[i].start, all[i].end};
+        hit_pattern[i] = all[i].pat;
+        if (per_pattern_hits)
+            ++per_pattern_hits[all[i].pat];
     }
     return TRX_OK;
 }
