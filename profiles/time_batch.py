@@ -24,3 +24,10 @@ t0 = time.perf_counter(); piped = txt.scan_many(regs, cap=1 << 20, depth=int(os.
 cnt = {k: kinds.count(k) for k in per}
 print(f"max_pass={os.environ.get('TRX_FILTER_MAX_PASS', 'default')}: census {cnt}  sequential {len(pats)/dt:7.0f} scans/s  pipelined {len(pats)/dtp:7.0f} scans/s  "
       f"mean us: " + ", ".join(f"{k} {per[k]/max(cnt[k],1)*1e6:.0f}" for k in per) + f"  hits {hits} / {sum(len(h) for h in piped)}")
+# N4: shared passes over the text (trx_regex_scan_multi)
+t0 = time.perf_counter(); txt.scan_multi(regs, cap=1 << 21); dt_first = time.perf_counter() - t0  # derives the multi plans
+t0 = time.perf_counter(); multi, st = txt.scan_multi(regs, cap=1 << 21, stats=True); dtm = time.perf_counter() - t0
+print(f"multi first call (plans derived) {dt_first*1e3:.1f} ms")
+same = all(np.array_equal(a, b) for a, b in zip(multi, piped))
+print(f"multi-pattern passes: {len(pats)/dtm:7.0f} scans/s ({dtm*1e3:.1f} ms for the batch, {st}), hit lists equal pipelined: {same}, "
+      f"launches so far {ctx.launches}")

@@ -66,6 +66,7 @@ struct filter_spec
 // dominator chain.
 constexpr int kMaxAtomTerms = 16;
 constexpr int kMaxConfirm = 6;
+constexpr int kMultiLetters = 24; // alphabet of a multi-pattern batch (regex_filter_multi); also the room in atom_spec::splat
 // Second stage of the gapped prefilter, evaluated only at the anchors the SIMD stage lets through: "the byte at address
 // anchor + d belongs to `mask` for some d in [lo, hi]" (offsets may be negative; classes of any size).  These are the
 // necessary positions that do not fit the SIMD stage's budget of 4 distinct bytes.
@@ -81,7 +82,7 @@ struct atom_spec
     int32_t n_atoms;
     int32_t n_terms;
     int32_t start_lo, start_hi;
-    uint32_t splat[4];
+    uint32_t splat[kMultiLetters];   // the single-pattern kernel uses the first n_lit <= 4
     uint8_t term_lit[kMaxAtomTerms]; // index into splat
     uint8_t term_lo[kMaxAtomTerms], term_hi[kMaxAtomTerms];
     uint8_t term_end[kMaxAtomTerms]; // 1 = last term of its atom
@@ -1175,9 +1176,8 @@ __global__ void __launch_bounds__(256) byte_histogram_kernel(uint8_t const * __r
 // of an atom ORed — costs 5 LDS + a few funnel shifts per term and 128 anchors: ~0.5 instructions per residue and
 // pattern instead of 2.75-3.75, and no HBM traffic at all after the first pattern.  Survivors are confirmed (classes,
 // signed offsets: the plan's second stage) and listed per pattern for regex_scan_phase2_multi.
-constexpr int kMultiLetters = 24;
 constexpr int kMultiPatterns = 128; // per launch
-constexpr uint32_t kMultiListCap = 8192; // listed records per pattern; more = a pattern for the single-pattern path
+constexpr uint32_t kMultiListCap = 32768; // listed records per pattern; more = a pattern for the single-pattern path
 
 struct multi_terms // the part every thread walks for every tile: kept in shared memory
 {
@@ -1192,6 +1192,7 @@ struct multi_program // per pattern, in global memory; the rest is only touched 
     int32_t n_confirm;
     confirm_check confirm[kMaxConfirm];
     uint64_t const * cand_words; // candidate bins of THIS pattern
+    uint32_t * chunk_flags;      // bitmap over 128-byte chunks: a match of this pattern may start here (phase 2 skips the rest)
     uint32_t * rec_flags;        // bitmap over records already listed for this pattern
     uint32_t * rec_list;         // kMultiListCap entries
     unsigned int * rec_count;
@@ -1203,7 +1204,78 @@ struct multi_params
     uint32_t n_patterns;
     uint32_t n_letters;
     uint32_t splat[kMultiLetters]; // letter byte replicated into the four lanes
+    uint32_t const * terms;        // the batch's terms, packed (multi_pack_term), pattern after pattern
+    uint32_t n_terms_total;
 };
+
+// rare path of regex_filter_multi: every surviving bit is an anchor of the pattern; confirm, flag its chunks, list its records
+__device__ __noinline__ void multi_survivors(scan_params const & p, multi_program const & P, uint64_t g_lo, uint32_t a0, uint32_t a1,
+                                             uint32_t a2, uint32_t a3)
+{
+    uint32_t const acc[4] = {a0, a1, a2, a3};
+    for (int q = 0; q < 4; ++q)
+    {
+        uint32_t bits = acc[q];
+        while (bits)
+        {
+            int const b = __ffs(bits) - 1;
+            bits &= bits - 1;
+            int64_t const anchor = static_cast<int64_t>(g_lo) + 32 * q + b;
+            bool confirmed = true;
+            for (int c = 0; c < P.n_confirm && confirmed; ++c)
+            {
+                bool found = false;
+                for (int d = P.confirm[c].lo; d <= P.confirm[c].hi && !found; ++d)
+                {
+                    int64_t const a = anchor + d;
+                    if (a >= 0 && a < static_cast<int64_t>(p.n_text))
+                    {
+                        uint32_t const byte = __ldg(p.text + a);
+                        found = (P.confirm[c].mask[byte >> 5] >> (byte & 31)) & 1;
+                    }
+                }
+                confirmed = found;
+            }
+            if (!confirmed)
+                continue;
+            int64_t lo = anchor + P.start_lo, hi = anchor + P.start_hi;
+            if (hi < 0 || lo >= static_cast<int64_t>(p.n_text))
+                continue;
+            lo = lo < 0 ? 0 : lo;
+            hi = hi >= static_cast<int64_t>(p.n_text) ? static_cast<int64_t>(p.n_text) - 1 : hi;
+            for (uint64_t c = static_cast<uint64_t>(lo) / kChunkBytes; c <= static_cast<uint64_t>(hi) / kChunkBytes; ++c)
+                atomicOr(P.chunk_flags + (c >> 5), 1u << (c & 31));
+            uint64_t r = record_of(p.rec_offsets, p.n_records, static_cast<uint64_t>(lo));
+            while (r < p.n_records && __ldg(p.rec_offsets + r) <= static_cast<uint64_t>(hi))
+            {
+                if (__ldg(p.rec_offsets + r + 1) > static_cast<uint64_t>(lo) && is_candidate(P.cand_words, __ldg(p.rec_bin + r)))
+                {
+                    uint32_t const bit = 1u << (r & 31);
+                    uint32_t const old = atomicOr(P.rec_flags + (r >> 5), bit);
+                    if (!(old & bit))
+                    {
+                        unsigned const at = atomicAdd(P.rec_count, 1u);
+                        if (at < kMultiListCap)
+                            P.rec_list[at] = static_cast<uint32_t>(r);
+                    }
+                }
+                ++r;
+            }
+        }
+    }
+}
+
+// packed term: letter | offset << 8 | rounds left in this pattern after this one << 16 | end-of-atom << 24 |
+// end-of-pattern << 25.  Offset ranges are expanded on the host into one term per offset (terms of an atom are ORed
+// anyway), so the kernel's term is "r |= mask[letter] >> offset"; every pattern's list is padded to whole rounds of four
+// terms (with copies of its first term: ORing the same mask twice changes nothing), most selective atoms first, so that a
+// warp can drop a pattern at a round boundary once none of its 4096 anchors survives the atoms merged so far.
+__host__ __device__ __forceinline__ uint32_t multi_pack_term(uint32_t letter, uint32_t offset, uint32_t rounds_left, bool end_atom,
+                                                             bool end_pattern)
+{
+    return letter | (offset << 8) | (rounds_left << 16) | (end_atom ? 1u << 24 : 0u) | (end_pattern ? 1u << 25 : 0u);
+}
+constexpr int kMultiMaxTermsPerPattern = 40; // after range expansion and padding; patterns that need more take the single-pattern path
 
 template <int STAGES>
 __global__ void __launch_bounds__(kScanThreads + 32)
@@ -1213,15 +1285,14 @@ __global__ void __launch_bounds__(kScanThreads + 32)
     using ring_t = tile_ring<STAGES, kScanThreads>;
     ring_t ring;
     ring.init(smem_raw);
-    // [letter][word 0..3][row]: masks of the tile in flight; lookahead[letter]: first word of the row after the tile
-    uint32_t * const masks = reinterpret_cast<uint32_t *>(smem_raw + ((ring_t::kRingBytes + 15) & ~15));
-    uint32_t * const lookahead = masks + kMultiLetters * 4 * kScanThreads;
-    multi_terms * const s_terms = reinterpret_cast<multi_terms *>(lookahead + kMultiLetters);
-    for (uint32_t i = threadIdx.x; i < mp.n_patterns * (sizeof(multi_terms) / 4); i += blockDim.x)
-    {
-        uint32_t const pat = i / (sizeof(multi_terms) / 4), w = i % (sizeof(multi_terms) / 4);
-        reinterpret_cast<uint32_t *>(s_terms + pat)[w] = reinterpret_cast<uint32_t const *>(&mp.programs[pat].terms)[w];
-    }
+    // masks4[letter][row] = the row's four 32-position mask words; next0[letter][row] = word 0 of the FOLLOWING row (the
+    // 32 positions a shifted window runs into; row 255's comes from global memory); terms[] = the batch's packed terms
+    uint4 * const masks4 = reinterpret_cast<uint4 *>(smem_raw + ((ring_t::kRingBytes + 15) & ~15));
+    uint32_t * const next0 = reinterpret_cast<uint32_t *>(masks4 + kMultiLetters * kScanThreads);
+    uint32_t * const terms = next0 + kMultiLetters * kScanThreads;
+    uint32_t const n_terms4 = (mp.n_terms_total + 3) & ~3u;
+    for (uint32_t i = threadIdx.x; i < n_terms4 + 4; i += blockDim.x)
+        terms[i] = i < mp.n_terms_total ? mp.terms[i] : 0u; // padding after the last pattern: harmless ORs into r
     __syncthreads();
     if (ring.is_producer())
     {
@@ -1229,6 +1300,8 @@ __global__ void __launch_bounds__(kScanThreads + 32)
         return;
     }
     int const tid = threadIdx.x;
+    uint4 const * const my_masks = masks4 + tid;
+    uint32_t const * const my_next = next0 + tid;
     uint8_t const * tile;
     uint32_t tile_id;
     while (ring.acquire(tile, tile_id))
@@ -1251,15 +1324,18 @@ __global__ void __launch_bounds__(kScanThreads + 32)
         for (uint32_t l = 0; l < mp.n_letters; ++l)
         {
             uint32_t const x = mp.splat[l];
+            uint32_t mm[4];
 #pragma unroll
             for (int q = 0; q < 4; ++q)
             {
-                uint32_t mm = 0;
+                mm[q] = 0;
 #pragma unroll
                 for (int j = 0; j < 8; ++j)
-                    mm |= literal_nibble(w[8 * q + j], x) << (4 * j);
-                masks[(l * 4 + q) * kScanThreads + tid] = mm;
+                    mm[q] |= literal_nibble(w[8 * q + j], x) << (4 * j);
             }
+            masks4[l * kScanThreads + tid] = make_uint4(mm[0], mm[1], mm[2], mm[3]);
+            if (tid > 0)
+                next0[l * kScanThreads + tid - 1] = mm[0];
         }
         if (tid == kScanThreads - 1)
         {
@@ -1277,86 +1353,60 @@ __global__ void __launch_bounds__(kScanThreads + 32)
 #pragma unroll
                 for (int j = 0; j < 8; ++j)
                     mm |= literal_nibble(la[j], mp.splat[l]) << (4 * j);
-                // zero padding compares equal to a letter only if that letter is byte 0, which no pattern literal is
-                lookahead[l] = mm;
+                next0[l * kScanThreads + tid] = mm; // zero padding never equals a letter (no pattern literal is byte 0)
             }
         }
         asm volatile("bar.sync 1, %0;" ::"n"(kScanThreads) : "memory"); // consumers only; once per tile and BATCH
         bool const real = g_lo < p.n_text;
-        for (uint32_t pat = 0; pat < mp.n_patterns; ++pat)
+        uint32_t acc0 = ~0u, acc1 = ~0u, acc2 = ~0u, acc3 = ~0u, r0 = 0, r1 = 0, r2 = 0, r3 = 0;
+        uint32_t pat = 0;
+        // four terms per round, all eight operand loads issued before the first use: there are only eight consumer warps
+        // per SM (the masks take the shared memory), so the latency has to be hidden inside the thread
+        for (uint32_t k = 0; k < n_terms4; k += 4)
         {
-            multi_terms const & T = s_terms[pat];
-            uint32_t acc0 = ~0u, acc1 = ~0u, acc2 = ~0u, acc3 = ~0u, r0 = 0, r1 = 0, r2 = 0, r3 = 0;
-            for (int i = 0; i < T.n_terms; ++i)
+            uint4 const tw4 = *reinterpret_cast<uint4 const *>(terms + k);
+            uint32_t const tw[4] = {tw4.x, tw4.y, tw4.z, tw4.w};
+            uint32_t const rounds_left = (tw4.x >> 16) & 0xFF;
+            uint4 m[4];
+            uint32_t nx[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
             {
-                uint32_t const * const m = masks + static_cast<uint32_t>(T.letter[i]) * 4 * kScanThreads + tid;
-                uint32_t const m0 = m[0], m1 = m[kScanThreads], m2 = m[2 * kScanThreads], m3 = m[3 * kScanThreads];
-                uint32_t const m4 = tid + 1 < kScanThreads ? m[1] : lookahead[T.letter[i]];
-                for (uint32_t d = T.lo[i]; d <= T.hi[i]; ++d)
+                uint32_t const l = tw[u] & 0xFF;
+                m[u] = my_masks[l * kScanThreads];
+                nx[u] = my_next[l * kScanThreads];
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+            {
+                uint32_t const d = (tw[u] >> 8) & 0xFF;
+                r0 |= __funnelshift_r(m[u].x, m[u].y, d);
+                r1 |= __funnelshift_r(m[u].y, m[u].z, d);
+                r2 |= __funnelshift_r(m[u].z, m[u].w, d);
+                r3 |= __funnelshift_r(m[u].w, nx[u], d);
+                if (tw[u] & (3u << 24))
                 {
-                    r0 |= __funnelshift_r(m0, m1, d);
-                    r1 |= __funnelshift_r(m1, m2, d);
-                    r2 |= __funnelshift_r(m2, m3, d);
-                    r3 |= __funnelshift_r(m3, m4, d);
-                }
-                if (T.end[i])
-                {
-                    acc0 &= r0, acc1 &= r1, acc2 &= r2, acc3 &= r3;
-                    r0 = r1 = r2 = r3 = 0;
+                    if (tw[u] & (1u << 24))
+                    {
+                        acc0 &= r0, acc1 &= r1, acc2 &= r2, acc3 &= r3;
+                        r0 = r1 = r2 = r3 = 0;
+                    }
+                    if (tw[u] & (1u << 25))
+                    {
+                        if ((acc0 | acc1 | acc2 | acc3) && real)
+                            multi_survivors(p, mp.programs[pat], g_lo, acc0, acc1, acc2, acc3);
+                        acc0 = acc1 = acc2 = acc3 = ~0u;
+                        ++pat;
+                    }
                 }
             }
-            if (!((acc0 | acc1 | acc2 | acc3) && real))
-                continue;
-            // rare path: every surviving bit is an anchor of pattern `pat`
-            multi_program const & P = mp.programs[pat];
-            uint32_t const acc[4] = {acc0, acc1, acc2, acc3};
-            for (int q = 0; q < 4; ++q)
+            // nothing left of this pattern in the whole warp: its remaining rounds cannot bring anything back
+            if (rounds_left && !__any_sync(0xffffffffu, (acc0 | acc1 | acc2 | acc3) != 0))
             {
-                uint32_t bits = acc[q];
-                while (bits)
-                {
-                    int const b = __ffs(bits) - 1;
-                    bits &= bits - 1;
-                    int64_t const anchor = static_cast<int64_t>(g_lo) + 32 * q + b;
-                    bool confirmed = true;
-                    for (int c = 0; c < P.n_confirm && confirmed; ++c)
-                    {
-                        bool found = false;
-                        for (int d = P.confirm[c].lo; d <= P.confirm[c].hi && !found; ++d)
-                        {
-                            int64_t const a = anchor + d;
-                            if (a >= 0 && a < static_cast<int64_t>(p.n_text))
-                            {
-                                uint32_t const byte = __ldg(p.text + a);
-                                found = (P.confirm[c].mask[byte >> 5] >> (byte & 31)) & 1;
-                            }
-                        }
-                        confirmed = found;
-                    }
-                    if (!confirmed)
-                        continue;
-                    int64_t lo = anchor + P.start_lo, hi = anchor + P.start_hi;
-                    if (hi < 0 || lo >= static_cast<int64_t>(p.n_text))
-                        continue;
-                    lo = lo < 0 ? 0 : lo;
-                    hi = hi >= static_cast<int64_t>(p.n_text) ? static_cast<int64_t>(p.n_text) - 1 : hi;
-                    uint64_t r = record_of(p.rec_offsets, p.n_records, static_cast<uint64_t>(lo));
-                    while (r < p.n_records && __ldg(p.rec_offsets + r) <= static_cast<uint64_t>(hi))
-                    {
-                        if (__ldg(p.rec_offsets + r + 1) > static_cast<uint64_t>(lo) && is_candidate(P.cand_words, __ldg(p.rec_bin + r)))
-                        {
-                            uint32_t const bit = 1u << (r & 31);
-                            uint32_t const old = atomicOr(P.rec_flags + (r >> 5), bit);
-                            if (!(old & bit))
-                            {
-                                unsigned const at = atomicAdd(P.rec_count, 1u);
-                                if (at < kMultiListCap)
-                                    P.rec_list[at] = static_cast<uint32_t>(r);
-                            }
-                        }
-                        ++r;
-                    }
-                }
+                k += 4 * rounds_left;
+                acc0 = acc1 = acc2 = acc3 = ~0u;
+                r0 = r1 = r2 = r3 = 0;
+                ++pat;
             }
         }
         asm volatile("bar.sync 1, %0;" ::"n"(kScanThreads) : "memory"); // nobody still reads the masks of this tile

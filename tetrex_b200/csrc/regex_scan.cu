@@ -66,6 +66,9 @@ struct trx_text
         int reverse, mode, kind;
         trx::filter_spec window;
         trx::atom_spec atoms;
+        // the plan for multi-pattern passes (whole alphabet, larger classes, as selective as the pattern allows)
+        int multi_kind{-1}; // -1 = not derived yet
+        trx::atom_spec multi_atoms;
     };
     std::vector<cached_choice> choices;
     // per-scan scratch
@@ -667,7 +670,19 @@ bool walk_range(automaton_graph const & g, int src, int dst, int & lo, int & hi)
     return true;
 }
 
-atom_plan derive_atoms(regex_dev const & img, double const * freq, bool reverse)
+// what the SIMD stage of a gapped plan may spend.  The single-pattern kernel builds its occurrence masks itself (4 distinct
+// bytes, classes of <= 3); the multi-pattern kernel finds the masks of the whole batch alphabet ready in shared memory, so a
+// term costs it three memory instructions whatever the byte: it takes every necessary position it can get.
+struct atom_budget
+{
+    int max_lits{4};
+    int max_class{3};
+    int max_atoms{8};
+    double good_enough{2e-5};
+};
+constexpr int kMaxClassBytes = 6;
+
+atom_plan derive_atoms(regex_dev const & img, double const * freq, bool reverse, atom_budget const & budget = atom_budget{})
 {
     atom_plan none;
     automaton_graph const g = build_graph(img);
@@ -676,11 +691,11 @@ atom_plan derive_atoms(regex_dev const & img, double const * freq, bool reverse)
         return none;
     // class of a position = the raw bytes it accepts.  At most 3 of them: usable as a SIMD atom; any other class that
     // is not nearly everything: usable as a confirm check at the anchors the SIMD stage lets through.
-    constexpr int kMaxClass = 3;
+    int const kMaxClass = budget.max_class;
     struct small_class
     {
-        int n{0};          // 1..3: SIMD-capable; 0: not
-        int byte[kMaxClass]{};
+        int n{0};          // 1..max_class: SIMD-capable; 0: not
+        int byte[kMaxClassBytes]{};
         double freq{0.0};  // expected fraction of text bytes in the class
         uint32_t mask[8]{};
         bool usable{false}; // as a confirm check
@@ -692,7 +707,7 @@ atom_plan derive_atoms(regex_dev const & img, double const * freq, bool reverse)
             for (int pos = 0; pos < P; ++pos)
                 if ((img.B[c][pos >> 6] >> (pos & 63)) & 1)
                 {
-                    if (count[pos] < kMaxClass)
+                    if (count[pos] < kMaxClassBytes)
                         cls[pos].byte[count[pos]] = c;
                     ++count[pos];
                     cls[pos].mask[c >> 5] |= 1u << (c & 31);
@@ -744,8 +759,9 @@ atom_plan derive_atoms(regex_dev const & img, double const * freq, bool reverse)
     if (chain.empty())
         return none;
 
-    constexpr double kGoodEnough = 2e-5;
-    constexpr int kMaxStartSpread = 1024, kMaxAtoms = 8;
+    double const kGoodEnough = budget.good_enough;
+    constexpr int kMaxStartSpread = 1024;
+    int const kMaxAtoms = budget.max_atoms;
     atom_plan best;
     int best_lits = 99;
     int const n = static_cast<int>(chain.size());
@@ -784,7 +800,7 @@ atom_plan derive_atoms(regex_dev const & img, double const * freq, bool reverse)
             cands.push_back(cand{chain[i].pos, lo, hi, f});
         }
         std::sort(cands.begin(), cands.end(), [](cand const & a, cand const & b) { return a.factor < b.factor; });
-        int lits[4], n_lit = 0, n_terms = 0;
+        int lits[kMultiLetters], n_lit = 0, n_terms = 0;
         auto lits_after = [&](small_class const & c)
         {
             int extra = 0;
@@ -818,7 +834,7 @@ atom_plan derive_atoms(regex_dev const & img, double const * freq, bool reverse)
             if (pass <= kGoodEnough || static_cast<int>(chosen.size()) >= kMaxAtoms)
                 break;
             small_class const & c = cls[cd.pos];
-            if (lits_after(c) > 4 || n_terms + c.n > kMaxAtomTerms)
+            if (lits_after(c) > budget.max_lits || n_terms + c.n > kMaxAtomTerms)
                 continue;
             take(c);
             chosen.push_back(cd);
@@ -1429,6 +1445,11 @@ bool plan_for_multi(filter_kind kind, filter_spec const & window, atom_spec cons
         return false;
     if (P.terms.n_terms <= 0)
         return false;
+    int expanded = 0;
+    for (int i = 0; i < P.terms.n_terms; ++i)
+        expanded += P.terms.hi[i] >= P.terms.lo[i] ? P.terms.hi[i] - P.terms.lo[i] + 1 : 0;
+    if (expanded + 3 > kMultiMaxTermsPerPattern)
+        return false;
     memcpy(letter_of, local_of, sizeof local_of);
     memcpy(splat, local_splat, sizeof local_splat);
     n_letters = local_n;
@@ -1471,7 +1492,11 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
     {
         uint32_t pat, rec, start, end;
     };
-    std::vector<tagged_hit> all;
+    // hits per pattern: the shared passes deliver them in arbitrary order (sorted per pattern at the end, they are few),
+    // the single-pattern path in print order already (its lists can be hundreds of thousands long)
+    std::vector<std::vector<tagged_hit>> per(n_patterns);
+    std::vector<char> needs_sort(n_patterns, 0);
+    uint64_t total_hits = 0;
     std::vector<uint32_t> single; // patterns for the pattern-at-a-time path
 
     // ---- every pattern's phase-1 plan (cached per text like the single-pattern path does)
@@ -1479,9 +1504,14 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
     char const * multi_off = getenv("TRX_REGEX_MULTI"); // TRX_REGEX_MULTI=off: every pattern on the single path (A/B, tests)
     bool const shared_pass = t->has_tmap && !filt && !(multi_off && strcmp(multi_off, "off") == 0);
     auto img = std::make_unique<regex_dev>();
+    static bool const trace = getenv("TRX_SCAN_TRACE") != nullptr;
+    auto const now = [] { return std::chrono::steady_clock::now(); };
+    auto const us = [](auto a, auto b) { return std::chrono::duration<double, std::micro>(b - a).count(); };
+    double us_plan = 0, us_stage = 0, us_device = 0, us_single = 0;
     uint32_t next = 0;
     while (shared_pass && next < n_patterns)
     {
+        auto const t_batch = now();
         // ---- a batch: up to kMultiPatterns patterns whose prefilter literals fit one alphabet of kMultiLetters bytes
         int letter_of[256];
         for (int & x : letter_of)
@@ -1507,14 +1537,40 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
                 t->choices.push_back(cc);
                 found = &t->choices.back();
             }
+            if (found->multi_kind < 0)
+            {
+                fill_image(*re, false, nullptr, img.get());
+                atom_budget budget;
+                budget.max_lits = kMultiLetters - 2;
+                budget.max_class = kMaxClassBytes;
+                budget.max_atoms = 12;
+                budget.good_enough = 1e-7;
+                if (char const * e = getenv("TRX_MULTI_GOOD_ENOUGH")) // A/B: SIMD-stage terms against survivors
+                    budget.good_enough = atof(e);
+                if (char const * e = getenv("TRX_MULTI_MAX_ATOMS"))
+                    budget.max_atoms = atoi(e);
+                atom_plan const strong = derive_atoms(*img, t->byte_freq, false, budget);
+                auto & mut = const_cast<trx_text::cached_choice &>(*found);
+                if (strong.spec.n_lit >= 1 && (found->kind != kFilterWindow || strong.confirmed < 1e-6))
+                {
+                    mut.multi_kind = kFilterAtoms;
+                    mut.multi_atoms = strong.spec;
+                }
+                else
+                {
+                    mut.multi_kind = found->kind; // the fixed window, the single-pattern atoms, or nothing
+                    mut.multi_atoms = found->atoms;
+                }
+            }
+            trx::atom_spec const & multi_atoms = found->multi_atoms;
             multi_plan plan;
             uint32_t const letters_before = mp.n_letters;
             bool const ok = re->follow_list.size() <= sizeof(regex_dev::follow_list) &&
-                            plan_for_multi(static_cast<filter_kind>(found->kind), found->window, found->atoms, letter_of, mp.splat,
+                            plan_for_multi(static_cast<filter_kind>(found->multi_kind), found->window, multi_atoms, letter_of, mp.splat,
                                            mp.n_letters, plan);
             if (!ok)
             {
-                bool const alphabet_full = found->kind != kFilterNone && letters_before > 0 && !ids.empty() &&
+                bool const alphabet_full = found->multi_kind != kFilterNone && letters_before > 0 && !ids.empty() &&
                                            re->follow_list.size() <= sizeof(regex_dev::follow_list);
                 if (alphabet_full)
                 {
@@ -1524,7 +1580,7 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
                         x = -1;
                     uint32_t fresh_splat[kMultiLetters], fresh_n = 0;
                     multi_plan probe;
-                    if (plan_for_multi(static_cast<filter_kind>(found->kind), found->window, found->atoms, fresh_of, fresh_splat,
+                    if (plan_for_multi(static_cast<filter_kind>(found->multi_kind), found->window, multi_atoms, fresh_of, fresh_splat,
                                        fresh_n, probe))
                         break; // close this batch, the pattern is retried as the first of the next one
                 }
@@ -1534,6 +1590,8 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
             plans.push_back(plan);
             ids.push_back(next++);
         }
+        auto const t_planned = now();
+        us_plan += us(t_batch, t_planned);
         if (ids.empty())
             continue;
         uint32_t const nb = static_cast<uint32_t>(ids.size());
@@ -1576,11 +1634,13 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
         size_t const off_img = align16(off_prog + nb * sizeof(multi_program));
         size_t const off_cand = align16(off_img + nb * sizeof(regex_dev));
         size_t const off_rp = align16(off_cand + static_cast<size_t>(nb) * cand_words * 8);
-        size_t const stage_bytes = off_rp + nb * sizeof(resolve_params);
+        size_t const off_terms = align16(off_rp + nb * sizeof(resolve_params));
+        size_t const stage_bytes = off_terms + (static_cast<size_t>(nb) * kMultiMaxTermsPerPattern + 8) * 4;
+        uint64_t const cfw = t->n_chunk_flag_words;
         t->m_h_stage.pinned_host = true;
         TRX_TRY(t->m_h_stage.reserve(stage_bytes));
         TRX_TRY(t->m_d_stage.reserve(stage_bytes));
-        TRX_TRY(t->m_d_flags.reserve(static_cast<size_t>(nb) * rfw * 4));
+        TRX_TRY(t->m_d_flags.reserve(static_cast<size_t>(nb) * (rfw + cfw) * 4));
         TRX_TRY(t->m_d_lists.reserve(static_cast<size_t>(nb) * kMultiListCap * 4));
         size_t const counter_bytes = 16 + static_cast<size_t>(nb) * 4; // hit count (u64), tile counter (u32), pad, listed records per pattern
         TRX_TRY(t->m_d_counters.reserve(counter_bytes));
@@ -1602,6 +1662,28 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
             P = plans[k].prog;
             P.cand_words = reinterpret_cast<uint64_t const *>(ds + off_cand) + static_cast<size_t>(k) * cand_words;
             P.rec_flags = static_cast<uint32_t *>(t->m_d_flags.ptr) + static_cast<size_t>(k) * rfw;
+            P.chunk_flags = static_cast<uint32_t *>(t->m_d_flags.ptr) + static_cast<size_t>(nb) * rfw + static_cast<size_t>(k) * cfw;
+            {
+                // a range = one term per offset (ORed like the atom's other terms); the list is padded in front to whole
+                // rounds of four with copies of its first term, and every round's first word says how many rounds follow
+                struct flat
+                {
+                    uint32_t letter, d;
+                    bool end_atom, end_pattern;
+                };
+                std::vector<flat> fl;
+                for (int i = 0; i < P.terms.n_terms; ++i)
+                    for (uint32_t d = P.terms.lo[i]; d <= P.terms.hi[i]; ++d)
+                        fl.push_back(flat{P.terms.letter[i], d, P.terms.end[i] != 0 && d == P.terms.hi[i],
+                                          i + 1 == P.terms.n_terms && d == P.terms.hi[i]});
+                while (fl.size() % 4)
+                    fl.insert(fl.begin(), flat{fl[0].letter, fl[0].d, false, false});
+                uint32_t const rounds = static_cast<uint32_t>(fl.size() / 4);
+                auto * out = reinterpret_cast<uint32_t *>(hs + off_terms);
+                for (size_t i = 0; i < fl.size(); ++i)
+                    out[mp.n_terms_total++] = multi_pack_term(fl[i].letter, fl[i].d, rounds - 1 - static_cast<uint32_t>(i / 4),
+                                                              fl[i].end_atom, fl[i].end_pattern);
+            }
             P.rec_list = static_cast<uint32_t *>(t->m_d_lists.ptr) + static_cast<size_t>(k) * kMultiListCap;
             P.rec_count = reinterpret_cast<unsigned int *>(d_counters + 16) + k;
             resolve_params & rp = h_rp[k];
@@ -1610,7 +1692,7 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
             rp.rec_offsets = t->d_rec_offsets;
             rp.rec_list = P.rec_list;
             rp.rec_count = P.rec_count;
-            rp.chunk_flags = nullptr; // per-pattern chunk bitmaps would cost 200 KB each: phase 2 tests every start
+            rp.chunk_flags = P.chunk_flags;
             rp.re = reinterpret_cast<regex_dev const *>(ds + off_img) + k;
             rp.hit_count = reinterpret_cast<unsigned long long *>(d_counters);
             rp.hit_keys = static_cast<uint64_t *>(t->m_d_hit_keys.ptr);
@@ -1620,11 +1702,14 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
             rp.rec_cap = kMultiListCap;
             rp.cap = cap;
         }
-        TRX_CUDA(cudaMemsetAsync(t->m_d_flags.ptr, 0, static_cast<size_t>(nb) * rfw * 4, st));
+        auto const t_staged = now();
+        us_stage += us(t_planned, t_staged);
+        TRX_CUDA(cudaMemsetAsync(t->m_d_flags.ptr, 0, static_cast<size_t>(nb) * (rfw + cfw) * 4, st));
         TRX_CUDA(cudaMemsetAsync(d_counters, 0, counter_bytes, st));
         TRX_CUDA(cudaMemcpyAsync(ds, hs, stage_bytes, cudaMemcpyHostToDevice, st));
         TRX_CUDA(cudaMemcpyAsync(t->m_d_tiles.ptr, tiles.data(), tiles.size() * 4, cudaMemcpyHostToDevice, st));
         mp.programs = reinterpret_cast<multi_program const *>(ds + off_prog);
+        mp.terms = reinterpret_cast<uint32_t const *>(ds + off_terms);
         scan_params sp{};
         sp.text = t->d_text;
         sp.n_text = t->n_text;
@@ -1638,8 +1723,8 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
         {
             constexpr int STAGES = 2;
             size_t const smem = ((tile_ring<STAGES, kScanThreads>::kRingBytes + 15) & ~size_t{15}) +
-                                (static_cast<size_t>(kMultiLetters) * 4 * kScanThreads + kMultiLetters) * 4 +
-                                static_cast<size_t>(kMultiPatterns) * sizeof(multi_terms) + 1024;
+                                static_cast<size_t>(kMultiLetters) * 5 * kScanThreads * 4 +
+                                (static_cast<size_t>(kMultiPatterns) * kMultiMaxTermsPerPattern + 8) * 4 + 1024;
             if (!t->multi_attr_set)
             {
                 TRX_CUDA(cudaFuncSetAttribute(regex_filter_multi<STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -1651,7 +1736,7 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
             ++c->launches;
             TRX_CUDA(cudaGetLastError());
         }
-        regex_scan_phase2_multi<2, 1><<<dim3(16, nb), 128, 0, st>>>(reinterpret_cast<resolve_params const *>(ds + off_rp));
+        regex_scan_phase2_multi<2, 1><<<dim3(32, nb), 128, 0, st>>>(reinterpret_cast<resolve_params const *>(ds + off_rp));
         ++c->launches;
         TRX_CUDA(cudaGetLastError());
 
@@ -1665,9 +1750,9 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
         auto const * listed = reinterpret_cast<uint32_t const *>(h_back + 16);
         if (batch_hits > cap)
         {
-            *n_hits = all.size() + batch_hits;
+            *n_hits = total_hits + batch_hits;
             return set_error(TRX_ECAPACITY, "trx_regex_scan_multi: at least %llu hits, room for %llu",
-                             (unsigned long long)(all.size() + batch_hits), (unsigned long long)cap);
+                             (unsigned long long)(total_hits + batch_hits), (unsigned long long)cap);
         }
         std::vector<char> overflowed(nb, 0);
         for (uint32_t k = 0; k < nb; ++k)
@@ -1688,9 +1773,16 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
             TRX_CUDA(cudaStreamSynchronize(st));
             for (uint64_t i = 0; i < batch_hits; ++i)
                 if (!overflowed[pats[i]])
-                    all.push_back(tagged_hit{ids[pats[i]], static_cast<uint32_t>(keys[i] >> 32), static_cast<uint32_t>(keys[i]), ends[i]});
+                {
+                    uint32_t const id = ids[pats[i]];
+                    per[id].push_back(tagged_hit{id, static_cast<uint32_t>(keys[i] >> 32), static_cast<uint32_t>(keys[i]), ends[i]});
+                    needs_sort[id] = 1;
+                    ++total_hits;
+                }
         }
+        us_device += us(t_staged, now());
     }
+    auto const t_single = now();
     if (!shared_pass)
         for (uint32_t i = 0; i < n_patterns; ++i)
             single.push_back(i);
@@ -1708,10 +1800,12 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
             uint64_t n = 0;
             int const rc = trx_regex_scan_end(t, pr.first, buf.data(), &n, nullptr);
             if (rc == TRX_ECAPACITY)
-                *n_hits = all.size() + n;
+                *n_hits = total_hits + n;
             TRX_TRY(rc);
+            per[pr.second].reserve(n);
             for (uint64_t i = 0; i < n; ++i)
-                all.push_back(tagged_hit{pr.second, buf[i].record, buf[i].start, buf[i].end});
+                per[pr.second].push_back(tagged_hit{pr.second, buf[i].record, buf[i].start, buf[i].end});
+            total_hits += n;
             return TRX_OK;
         };
         int rc = TRX_OK;
@@ -1740,20 +1834,30 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
         TRX_TRY(rc);
     }
 
+    us_single = us(t_single, now());
+    if (trace)
+        fprintf(stderr, "trx_regex_scan_multi: %u patterns: plans %.0f us, staging %.0f us, shared passes (enqueue .. hits back) %.0f us, "
+                        "%zu single-path patterns %.0f us\n", n_patterns, us_plan, us_stage, us_device, single.size(), us_single);
     // ---- print order per pattern: (pattern, bin, record, start); records are grouped by ascending bin
-    *n_hits = all.size();
-    if (all.size() > cap)
-        return set_error(TRX_ECAPACITY, "trx_regex_scan_multi: %llu hits, room for %llu", (unsigned long long)all.size(),
+    *n_hits = total_hits;
+    if (total_hits > cap)
+        return set_error(TRX_ECAPACITY, "trx_regex_scan_multi: %llu hits, room for %llu", (unsigned long long)total_hits,
                          (unsigned long long)cap);
-    std::sort(all.begin(), all.end(), [](tagged_hit const & a, tagged_hit const & b) {
-        return a.pat != b.pat ? a.pat < b.pat : (a.rec != b.rec ? a.rec < b.rec : a.start < b.start);
-    });
-    for (size_t i = 0; i < all.size(); ++i)
+    uint64_t o = 0;
+    for (uint32_t i = 0; i < n_patterns; ++i)
     {
-        hits[i] = trx_hit{t->h_rec_bin[all[i].rec], all[i].rec, all[i].start, all[i].end};
-        hit_pattern[i] = all[i].pat;
+        std::vector<tagged_hit> & v = per[i];
+        if (needs_sort[i])
+            std::sort(v.begin(), v.end(), [](tagged_hit const & a, tagged_hit const & b) {
+                return a.rec != b.rec ? a.rec < b.rec : a.start < b.start;
+            });
+        for (tagged_hit const & h : v)
+        {
+            hits[o] = trx_hit{t->h_rec_bin[h.rec], h.rec, h.start, h.end};
+            hit_pattern[o++] = i;
+        }
         if (per_pattern_hits)
-            ++per_pattern_hits[all[i].pat];
+            per_pattern_hits[i] = v.size();
     }
     return TRX_OK;
 }
