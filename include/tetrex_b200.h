@@ -230,6 +230,10 @@ void trx_text_destroy(trx_text_t *t);
 int trx_regex_compile(const char *pattern, int posix_longest, trx_regex_t **out);
 void trx_regex_destroy(trx_regex_t *re);
 int trx_regex_positions(const trx_regex_t *re);
+/* Host only (output formatting of the conjunction path, src/query.cpp:318-339): end (exclusive) of the earliest-ENDING
+ * match of re in text[0, len), -1 if none.  RE2::Set::Match lists the rules of a set in the order in which their first
+ * matches complete; verify_fasta_set prints them in that order. */
+int64_t trx_regex_first_match_end(const trx_regex_t *re, const uint8_t *text, uint64_t len);
 
 typedef struct trx_hit {
     uint32_t bin;

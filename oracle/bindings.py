@@ -131,6 +131,8 @@ def ref():
         lib.ref_re2_scan_records.argtypes = [C.c_char_p, C.c_int, C.c_void_p, u64p, C.c_uint64, C.c_int]
         lib.ref_re2_scan_records_hits.restype = C.c_int64
         lib.ref_re2_scan_records_hits.argtypes = [C.c_char_p, C.c_int, C.c_void_p, u64p, C.c_uint64, C.c_int, u32p, C.c_uint64]
+        lib.ref_index_conjunction.restype = C.c_int
+        lib.ref_index_conjunction.argtypes = [C.c_char_p, C.c_char_p, C.c_int, u64p, C.c_uint64, C.c_char_p]
         lib.ref_rh_pop_order.restype = C.c_uint64
         lib.ref_rh_pop_order.argtypes = [u64p, C.c_uint64, u32p]
         _ref = lib
@@ -480,6 +482,21 @@ def ref_rh_pop_order(keys) -> np.ndarray:
     out = np.zeros(len(k), dtype=np.uint32)
     n = ref().ref_rh_pop_order(_p(k, u64p), len(k), _p(out, u32p))
     return out[:n].copy()
+
+
+def ref_index_conjunction(index_path, regex_list, threads=1):
+    """`tetrex query -c`: AND of the filters of the ':'-separated queries + RE2::Set verify: (hit words, stdout)."""
+    import tempfile
+    words = np.zeros(1 << 14, dtype=np.uint64)
+    tmp = tempfile.mktemp(prefix="ref_stdout_")
+    n = ref().ref_index_conjunction(index_path.encode(), regex_list.encode(), threads, _p(words, u64p), len(words), tmp.encode())
+    if n < 0:
+        raise RuntimeError(ref().ref_last_error().decode())
+    text = ""
+    if os.path.exists(tmp):
+        text = open(tmp).read()
+        os.unlink(tmp)
+    return words[:n].copy(), text
 
 
 def guarded(fn, *args):

@@ -896,3 +896,67 @@ int64_t ref_re2_scan_records_hits(char const * regex, int posix_longest, char co
 }
 
 } // extern "C"
+
+namespace
+{
+template <class flavor_t, class mol_t>
+int harness_conjunction(std::string const & index_path, std::string const & regex_list, int threads, uint64_t * hit_words,
+                        uint64_t cap_words, char const * stdout_path)
+{
+    // run_conjunction (include/query.h:293-326) without the timing / verbose prints: AND of process_query over the ':'-
+    // separated queries (src/query.cpp:463-466), then iter_disk_search_set (include/query.h:191-224)
+    omp_set_num_threads(threads < 1 ? 1 : threads);
+    TetrexIndex<flavor_t, mol_t> ibf;
+    load_ibf(ibf, std::filesystem::path{index_path});
+    ibf.spawn_agent();
+    std::vector<std::string> queries = split_string(regex_list, ':');
+    bitvector hit_vector(ibf.getBinCount(), true);
+    DGramIndex dibf{};
+    if (ibf.getBinCount() > 1u)
+        for (auto rx : queries)
+            hit_vector &= process_query(rx, ibf, false, false, false, false, dibf);
+    size_t const words = (ibf.getBinCount() + 63) / 64;
+    for (size_t i = 0; i < words && i < cap_words; ++i)
+        hit_words[i] = hit_vector.data()[i];
+    if (!hit_vector.none())
+    {
+        fd_capture cap(stdout_path);
+        iter_disk_search_set(hit_vector, queries, ibf);
+    }
+    return static_cast<int>(words);
+}
+} // namespace
+
+extern "C"
+{
+
+// `tetrex query -c idx "q1:q2:..."` as the reference runs it (peptide HIBF is the only flavour its CLI wires up; the
+// templates work for all four).  Returns #words or <0; stdout of the verify step goes to stdout_path.
+int ref_index_conjunction(char const * index_path, char const * regex_list, int threads, uint64_t * hit_words,
+                          uint64_t cap_words, char const * stdout_path)
+{
+    try
+    {
+        index_params params;
+        load_params(params, std::filesystem::path{index_path});
+        bool const na = params.molecule_ == "na";
+        if (!params.is_hibf_ && na)
+            return harness_conjunction<index_structure::IBF, molecules::nucleotide>(index_path, regex_list, threads, hit_words,
+                                                                                    cap_words, stdout_path);
+        if (params.is_hibf_ && na)
+            return harness_conjunction<index_structure::HIBF, molecules::nucleotide>(index_path, regex_list, threads, hit_words,
+                                                                                     cap_words, stdout_path);
+        if (!params.is_hibf_)
+            return harness_conjunction<index_structure::IBF, molecules::peptide>(index_path, regex_list, threads, hit_words,
+                                                                                 cap_words, stdout_path);
+        return harness_conjunction<index_structure::HIBF, molecules::peptide>(index_path, regex_list, threads, hit_words,
+                                                                              cap_words, stdout_path);
+    }
+    catch (std::exception const & e)
+    {
+        g_err = e.what();
+        return -1;
+    }
+}
+
+} // extern "C"

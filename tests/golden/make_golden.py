@@ -548,6 +548,43 @@ def golden_prosite_filter():
           sum(1 for c in out if c["bins"]), "with candidates, mean", sum(len(c["bins"]) for c in out) / len(out), "bins")
 
 
+CONJ_CASES = [
+    ("pep_hibf_k4", "WKC(DE)+FH:PWDEHI*K"), ("pep_hibf_k4", "PWDEHI*K:WKC(DE)+FH"), ("pep_hibf_k4", "WKCDEDEFH:MKAPLW:PWDEHIIK"),
+    ("pep_hibf_k4", "PWDEHIIK:MKAPLW:WKCDEDEFH"), ("pep_hibf_k4", "MKAPLW:WKCDEDEFH:PWDEHIIK"), ("pep_hibf_k4", "HHC.{2}CW:KR{2}T"),
+    ("pep_hibf_k4", "KRRT:HHCAKCW"), ("pep_hibf_k4", "LMA(E|Q)GLYN:WKCDEDEFH"), ("pep_hibf_k4", "LMAEGLYN:MKTA"),
+    ("pep_hibf_k4", "KRRT"), ("pep_hibf_k4", "KRRT:KRRT"), ("pep_hibf_k4", "G(LY|QP)NW?K:CAACLLLV"),
+    ("pep_flat_k4", "WKCDEDEFH:PWDEHIIK"), ("pep_flat_k4", "KRRT:PWDEHIIK:AAAA"),
+    ("wide_hibf_k4", "AAAAAAAA:CAACLLLV"), ("wide_hibf_k4", "CAACLLLV:AAAAAAAA"), ("wide_hibf_k4", "MKTA:MKAPLW:WKCDEDEFH"),
+    ("wide_hibf_k4", "WKCDEDEFH:MKAPLW:MKTA"), ("wide_hibf_k4", "LMAEGLYN:GLYNWK"), ("wide_hibf_k4", "GQPNK:LMAEGLYN:HHCAKCW"),
+]
+
+
+def golden_cli_conj():
+    """`tetrex query -c "q1:q2:…"` (src/query.cpp:463-466, include/query.h:191-224,293-326): AND of the queries' filters,
+    then RE2::Set per record of the candidate bins; the rule order inside a printed line comes out of RE2's DFA."""
+    cwd = os.getcwd()
+    os.chdir(ROOT)
+    out = []
+    try:
+        cli = json.load(open(os.path.join(OUT, "cli.json")))
+        for name, qs in CONJ_CASES:
+            idx = os.path.join("tests", "golden", "cli", name + ".ibf")
+            files = next(c["files"] for c in cli if c["index"] == idx)
+            got = guarded(ob.ref_index_conjunction, idx, qs)
+            if got is None:
+                print("reference aborts on", name, qs)
+                continue
+            words, text = got
+            out.append(dict(index=idx, regex=qs, bins=[b for b in range(len(files)) if int(words[b // 64]) >> (b % 64) & 1],
+                            stdout=text))
+    finally:
+        os.chdir(cwd)
+    json.dump(out, open(os.path.join(OUT, "cli_conj.json"), "w"), indent=0)
+    print("cli_conj.json:", len(out), "cases,", sum(len(c["stdout"].splitlines()) for c in out), "lines")
+    for c in out:
+        print(c["regex"], c["bins"], repr(c["stdout"][:300]))
+
+
 def golden_rh_order():
     """Pop orders of the real robin_hood::unordered_map for key lists shaped like a rank's sub-k-mer keys."""
     rng = random.Random(99)
@@ -562,7 +599,7 @@ def golden_rh_order():
 
 STEPS = {"decompose": golden_decompose, "ibf": golden_ibf, "hibf": golden_hibf, "regex": golden_regex,
          "kgraph": golden_kgraph, "cli": golden_cli, "c1": golden_c1, "collector_fuzz": golden_collector_fuzz, "rh_order": golden_rh_order,
-         "prosite_batch": golden_prosite_batch, "c2_twin_hibf": golden_c2_twin_hibf, "cli_ws": golden_cli_ws, "prosite_filter": golden_prosite_filter}
+         "prosite_batch": golden_prosite_batch, "c2_twin_hibf": golden_c2_twin_hibf, "cli_ws": golden_cli_ws, "prosite_filter": golden_prosite_filter, "cli_conj": golden_cli_conj}
 
 if __name__ == "__main__":
     assert ob.have_ref(), "build oracle/_ref first: make -C oracle ref"

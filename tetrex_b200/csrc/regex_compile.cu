@@ -523,4 +523,42 @@ int trx_regex_positions(const trx_regex_t * re)
     return re ? re->positions : 0;
 }
 
+// Host only, for output formatting: where the EARLIEST-ENDING match of `re` in text[0, len) ends (exclusive), -1 if there
+// is none.  RE2::Set::Match reports the rules of a conjunction in the order in which their first matches complete
+// (verify_fasta_set prints them in that order, src/query.cpp:318-339); the records concerned are the handful that K4
+// found to match every rule.  One step of the position automaton per byte: S' = (Follow(S) | First) & B[c].
+int64_t trx_regex_first_match_end(const trx_regex_t * re, const uint8_t * text, uint64_t len)
+{
+    if (!re || (!text && len))
+        return -1;
+    trx::regex_masks const & m = re->masks;
+    uint64_t s[trx::kRegexWords] = {0, 0};
+    for (uint64_t i = 0; i < len; ++i)
+    {
+        uint64_t nx[trx::kRegexWords] = {0, 0};
+        for (int w = 0; w < trx::kRegexWords; ++w)
+        {
+            uint64_t bits = s[w];
+            while (bits)
+            {
+                int const b = __builtin_ctzll(bits);
+                bits &= bits - 1;
+                for (int k = 0; k < trx::kRegexWords; ++k)
+                    nx[k] |= m.follow[w * 64 + b][k];
+            }
+        }
+        bool hit = false;
+        for (int k = 0; k < trx::kRegexWords; ++k)
+        {
+            if (!re->anchor_begin || i == 0)
+                nx[k] |= m.first[k];
+            s[k] = nx[k] & m.B[text[i]][k];
+            hit = hit || (s[k] & m.last[k]);
+        }
+        if (hit && (!re->anchor_end || i + 1 == len))
+            return static_cast<int64_t>(i + 1);
+    }
+    return -1;
+}
+
 } // extern "C"

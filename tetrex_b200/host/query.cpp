@@ -2,8 +2,11 @@
 // (include/query.h:250-291), run_multiple_queries (:330-340), drive_query (src/query.cpp:477-498), drive_index
 // (src/index_base.cpp:73-118) and drive_inspection (src/inspect_idx.cpp).  Same messages on the same streams
 // (seqan3::debug_stream is stderr), same output lines; every scan is one trx_regex_scan call (K4).
+#include <algorithm>
 #include <bit>
 #include <chrono>
+#include <iterator>
+#include <memory>
 #include <fstream>
 #include <iomanip>
 #include <iostream>
@@ -216,6 +219,248 @@ double now()
     return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }
 
+// candidate words as the verify step sees them: real bins only, this shard's bins only
+bitvector verify_candidates(bitvector const & hits_in, DeviceIndex & index)
+{
+    std::vector<std::string> const & libs = index.acid_libs();
+    bitvector cand((libs.size() + 63) / 64, 0);
+    if (libs.size() == 1)
+        cand[0] = 1;
+    else
+        for (size_t w = 0; w < cand.size() && w < hits_in.size(); ++w)
+            cand[w] = hits_in[w];
+    if (index.shard_count() > 1)
+        for (size_t w = 0; w < cand.size(); ++w)
+            if (w < index.shard_word_begin() || w >= index.shard_word_begin() + index.shard_words())
+                cand[w] = 0;
+    if (libs.size() % 64)
+        cand.back() &= (1ull << (libs.size() % 64)) - 1;
+    return cand;
+}
+
+// K4 for a batch of patterns in shared passes over the text (trx_regex_scan_multi); hits grouped per pattern
+std::vector<std::vector<trx_hit>> scan_batch(DeviceIndex::text_store const & store, std::vector<regex_handle *> const & rx,
+                                             std::vector<uint64_t> const & cand_flat, uint64_t stride)
+{
+    std::vector<trx_regex_t *> handles;
+    for (regex_handle * r : rx)
+        handles.push_back(r->re);
+    std::vector<trx_hit> hits(1 << 16);
+    std::vector<uint32_t> pats(hits.size());
+    std::vector<uint64_t> per(rx.size());
+    for (;;)
+    {
+        uint64_t n = 0;
+        int const rc = trx_regex_scan_multi(store.text, handles.data(), static_cast<uint32_t>(handles.size()), cand_flat.data(),
+                                            stride, hits.data(), pats.data(), hits.size(), &n, per.data(), nullptr);
+        if (rc == TRX_ECAPACITY)
+        {
+            hits.resize(std::max<uint64_t>(2 * hits.size(), n + n / 4 + 16));
+            pats.resize(hits.size());
+            continue;
+        }
+        check(rc);
+        std::vector<std::vector<trx_hit>> out(rx.size());
+        uint64_t o = 0;
+        for (size_t i = 0; i < rx.size(); ++i)
+        {
+            out[i].assign(hits.begin() + o, hits.begin() + o + per[i]);
+            o += per[i];
+        }
+        return out;
+    }
+}
+
+// iter_disk_search_set + verify_fasta_set (include/query.h:191-224, src/query.cpp:318-339): a record of a candidate bin is
+// reported when EVERY query matches somewhere in it; the line names the queries in the order RE2::Set::Match returns
+// them — the order in which their first matches complete in the record, ties in descending order of "(" + query + ")"
+// (RE2 sorts the set's patterns and reads the match list of its final DFA state backwards).  The reference compiles the
+// queries as given (no alphabet reduction, forward strand only) and writes to stdout whatever -o says.
+uint64_t iter_disk_search_set(bitvector const & hits_in, std::vector<std::string> const & queries, DeviceIndex & index,
+                              std::ostream & out)
+{
+    bitvector const cand = verify_candidates(hits_in, index);
+    if (popcount(cand) == 0 || queries.empty())
+        return 0;
+    DeviceIndex::text_store const & store = index.text(cand);
+    std::vector<std::unique_ptr<regex_handle>> owned;
+    std::vector<regex_handle *> rx;
+    for (std::string const & q : queries)
+    {
+        owned.push_back(std::make_unique<regex_handle>(q, /*posix=*/false)); // RE2::DefaultOptions; existence is all that counts
+        rx.push_back(owned.back().get());
+    }
+    std::vector<std::vector<trx_hit>> const per = scan_batch(store, rx, cand, 0);
+    // records in which every query has a match: intersect the (sorted) record lists
+    std::vector<uint32_t> records;
+    for (size_t i = 0; i < per.size(); ++i)
+    {
+        std::vector<uint32_t> mine;
+        for (trx_hit const & h : per[i])
+            if (mine.empty() || mine.back() != h.record)
+                mine.push_back(h.record);
+        if (i == 0)
+            records = mine;
+        else
+        {
+            std::vector<uint32_t> both;
+            std::set_intersection(records.begin(), records.end(), mine.begin(), mine.end(), std::back_inserter(both));
+            records.swap(both);
+        }
+    }
+    std::vector<std::string> const & libs = index.acid_libs();
+    uint64_t lines = 0;
+    for (uint32_t r : records)
+    {
+        auto const * rec = reinterpret_cast<uint8_t const *>(store.residues.data() + store.offsets[r]);
+        uint64_t const len = store.offsets[r + 1] - store.offsets[r];
+        std::vector<std::pair<int64_t, size_t>> order;
+        for (size_t i = 0; i < queries.size(); ++i)
+            order.emplace_back(trx_regex_first_match_end(rx[i]->re, rec, len), i);
+        std::stable_sort(order.begin(), order.end(), [&](auto const & a, auto const & b) {
+            if (a.first != b.first)
+                return a.first < b.first;
+            return "(" + queries[a.second] + ")" > "(" + queries[b.second] + ")";
+        });
+        out << libs[store.rec_bin[r]] << '\t' << store.names[r] << "\tN --> ";
+        for (auto const & o : order)
+            out << queries[o.second] << " --> ";
+        out << "C" << std::endl;
+        ++lines;
+    }
+    return lines;
+}
+
+// run_conjunction (include/query.h:293-326): the candidate bins of a conjunction are the AND of its queries' filters
+void run_conjunction(query_arguments & args, DeviceIndex & index)
+{
+    double const t1 = now();
+    std::vector<std::string> queries; // split_string(input_regex, ':') (src/query.cpp:365-371, :463-466)
+    {
+        std::stringstream ss(args.regex);
+        std::string token;
+        while (std::getline(ss, token, ':'))
+            queries.push_back(token);
+    }
+    bitvector hit_vector(index.bin_words(), 0);
+    for (uint64_t b = 0; b < index.bin_count(); ++b)
+        hit_vector[b / 64] |= 1ull << (b % 64);
+    if (index.bin_count() > 1)
+    {
+        for (std::string const & q : queries)
+        {
+            bitvector got = process_query(q, index);
+            for (size_t w = 0; w < hit_vector.size(); ++w)
+                hit_vector[w] &= got[w];
+        }
+    }
+    else
+        std::cerr << "[WARNING] Index contains only 1 bin. Unable to accelerate search using the TetRex algorithm. "
+                     "Performing Linear Scan"
+                  << std::endl;
+    if (args.verbose)
+        std::cerr << "Narrowed Search to " << popcount(hit_vector) << " possible bins" << std::endl;
+    if (popcount(hit_vector) != 0)
+    {
+        try
+        {
+            iter_disk_search_set(hit_vector, queries, index, std::cout);
+        }
+        catch (std::exception const & e)
+        {
+            std::cerr << e.what() << '\n';
+        }
+    }
+    if (args.verbose)
+        std::cerr << "Query Time: " << (now() - t1) << std::endl;
+}
+
+// run_multiple_queries (include/query.h:330-340) for a whole file of motifs: the filter phase runs motif by motif (every
+// motif has its own k-graph and candidate bins), the verify phase ONCE for all of them — pattern i over its own candidate
+// bins, every tile of the union read once per 128 patterns.  Same files (<id>.tsv), same lines, same stderr fields as the
+// loop over run_collection; "Query Time" is the motif's filter time plus its share of the shared verify.
+void run_motif_batch(std::vector<std::pair<std::string, std::string>> const & motifs, DeviceIndex & index)
+{
+    size_t const n = motifs.size();
+    uint64_t const words = (index.acid_libs().size() + 63) / 64;
+    std::vector<uint64_t> cands(n * words, 0);
+    std::vector<double> filter_s(n, 0.0);
+    std::vector<uint64_t> bin_count(n, 0);
+    std::vector<std::unique_ptr<regex_handle>> owned(n);
+    std::vector<size_t> live; // motifs that reach the verify phase
+    bitvector uni(words, 0);
+    for (size_t i = 0; i < n; ++i)
+    {
+        double const t1 = now();
+        try
+        {
+            bitvector hit_vector(index.bin_words(), 0);
+            for (uint64_t b = 0; b < index.bin_count(); ++b)
+                hit_vector[b / 64] |= 1ull << (b % 64);
+            bitvector got = process_query(motifs[i].second, index);
+            for (size_t w = 0; w < hit_vector.size(); ++w)
+                hit_vector[w] &= got[w];
+            bin_count[i] = popcount(hit_vector);
+            if (bin_count[i])
+            {
+                bitvector const c = verify_candidates(hit_vector, index);
+                std::copy(c.begin(), c.end(), cands.begin() + i * words);
+                owned[i] = std::make_unique<regex_handle>(motifs[i].second, /*posix=*/true);
+                live.push_back(i);
+                for (size_t w = 0; w < words; ++w)
+                    uni[w] |= c[w];
+            }
+        }
+        catch (std::exception const & e)
+        {
+            std::cerr << motifs[i].first << "\t" << e.what() << '\n';
+            bin_count[i] = UINT64_MAX;
+        }
+        filter_s[i] = now() - t1;
+    }
+    double verify_s = 0.0;
+    std::vector<std::vector<trx_hit>> per;
+    DeviceIndex::text_store const * store = nullptr;
+    if (!live.empty() && popcount(uni))
+    {
+        double const t1 = now();
+        store = &index.text(uni);
+        std::vector<regex_handle *> rx;
+        std::vector<uint64_t> flat(live.size() * words);
+        for (size_t k = 0; k < live.size(); ++k)
+        {
+            rx.push_back(owned[live[k]].get());
+            std::copy(cands.begin() + live[k] * words, cands.begin() + (live[k] + 1) * words, flat.begin() + k * words);
+        }
+        per = scan_batch(*store, rx, flat, words);
+        verify_s = now() - t1;
+    }
+    std::vector<std::string> const & libs = index.acid_libs();
+    size_t k = 0;
+    std::string match;
+    for (size_t i = 0; i < n; ++i)
+    {
+        if (bin_count[i] == UINT64_MAX)
+            continue;
+        std::cerr << motifs[i].first << "\t" << "Bin Count: " << bin_count[i] << "\t";
+        if (bin_count[i])
+        {
+            std::ofstream out(motifs[i].first + ".tsv");
+            if (!out)
+                std::cerr << "Failed to open output file: " << motifs[i].first << ".tsv" << '\n';
+            else if (k < per.size())
+                for (trx_hit const & h : per[k])
+                {
+                    char const * rec = store->residues.data() + store->offsets[h.record];
+                    match.assign(rec + h.start, h.end - h.start);
+                    out << libs[h.bin] << '\t' << store->names[h.record] << '\t' << match << '\t' << h.start << ',' << h.end << '\n';
+                }
+            ++k;
+        }
+        std::cerr << "Query Time: " << (filter_s[i] + verify_s / std::max<size_t>(live.size(), 1)) << std::endl;
+    }
+}
+
 // run_collection (include/query.h:250-291)
 void run_collection(query_arguments & args, bool read_file, DeviceIndex & index)
 {
@@ -260,8 +505,8 @@ void drive_query(query_arguments & args)
 {
     if (args.regex == "-")
         std::cin >> args.regex; // src/query.cpp:479
-    if (args.augment || args.draw || args.dibf != "-" || args.conjunction != "-")
-        throw error("-a / -d / -g / -c (augmentation, graph drawing, DGram index, conjunction) are outside this build: "
+    if (args.augment || args.draw || args.dibf != "-")
+        throw error("-a / -d / -g (augmentation, graph drawing, DGram index) are outside this build: "
                     "see DESIGN.md \"out of scope\"");
     {
         // load_params comes first in the reference too (src/query.cpp:480-481): an unreadable file is reported before
@@ -285,6 +530,7 @@ void drive_query(query_arguments & args)
             if (!in.is_open())
                 throw error("Could not open file: " + args.read_file);
             std::string line;
+            std::vector<std::pair<std::string, std::string>> motifs; // (id, motif)
             while (std::getline(in, line))
             {
                 if (line.empty())
@@ -293,12 +539,23 @@ void drive_query(query_arguments & args)
                 std::string id, motif;
                 if (!std::getline(iss, id, '\t') || !std::getline(iss, motif, '\t'))
                     continue;
-                args.regex = motif;
-                args.ofile = id + ".tsv";
-                std::cerr << id << "\t";
-                run_collection(args, true, index);
+                motifs.emplace_back(id, motif);
             }
+            // Peptide indexes without alphabet reduction verify the whole file of motifs in shared passes over the text
+            // (K4 multi-pattern scan); everything else (DNA: two strands; reduced alphabets: mapped text) one by one.
+            if (!index.is_dna() && index.reduction() == 0 && index.bin_count() > 1 && motifs.size() > 1)
+                run_motif_batch(motifs, index);
+            else
+                for (auto const & [id, motif] : motifs)
+                {
+                    args.regex = motif;
+                    args.ofile = id + ".tsv";
+                    std::cerr << id << "\t";
+                    run_collection(args, true, index);
+                }
         }
+        else if (args.conjunction != "-")
+            run_conjunction(args, index); // the reference wires -c up for peptide HIBFs only (src/query.cpp:463-466); here: any index
         else
             run_collection(args, false, index);
     }
