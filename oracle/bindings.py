@@ -419,7 +419,7 @@ class RefHIBF:
         return out
 
 
-def ref_kgraph(regex: str, molecule: int, k: int, reduction: int = 0):
+def ref_kgraph(regex: str, molecule: int, k: int, reduction: int = 0, augment: bool = False):
     """The k-graph the reference builds (construct_kgraph / construct_reduced_kgraph + determine_top_sort):
     (postfix, [(symbol, first, second, rank) per node id]) or None if the reference threw."""
     cap = 1 << 17
@@ -429,7 +429,7 @@ def ref_kgraph(regex: str, molecule: int, k: int, reduction: int = 0):
     rk = np.zeros(cap, dtype=np.int32)
     pf = C.create_string_buffer(1 << 16)
     i32p = C.POINTER(C.c_int32)
-    n = ref().ref_kgraph(regex.encode(), molecule, k, reduction, 0, sym.ctypes.data_as(i32p), fi.ctypes.data_as(i32p),
+    n = ref().ref_kgraph(regex.encode(), molecule, k, reduction, int(augment), sym.ctypes.data_as(i32p), fi.ctypes.data_as(i32p),
                          se.ctypes.data_as(i32p), rk.ctypes.data_as(i32p), cap, pf, 1 << 16)
     if n < 0:
         return None

@@ -269,7 +269,8 @@ bitvector collect(kgraph const & g, DeviceIndex & index, collect_stats * stats, 
     return out;
 }
 
-bitvector process_query(std::string const & regex, DeviceIndex & index, collect_stats * stats, shard_hooks const * hooks)
+bitvector process_query(std::string const & regex, DeviceIndex & index, collect_stats * stats, shard_hooks const * hooks,
+                        bool augment)
 {
     // preprocess_query (include/query.h:80-94): peptides reduce (if the index is reduced) and trim, DNA only translates
     std::string rx = regex;
@@ -281,6 +282,8 @@ bitvector process_query(std::string const & regex, DeviceIndex & index, collect_
     }
     std::string postfix = translate(rx);
     kgraph g = construct_kgraph(postfix, index.k(), index.reduction() != TRX_RED_BASE); // include/query.h:239-240
+    if (augment)
+        g.augment(); // include/query.h:243: `if(augment && catsites.size() > 0) collector.augment(catsites);`
     return collect(g, index, stats, hooks);
 }
 

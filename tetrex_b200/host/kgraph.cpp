@@ -11,6 +11,7 @@
 #include <algorithm>
 #include <stack>
 
+#include "rh_order.hpp"
 #include "trx_host.hpp"
 
 namespace trxh
@@ -21,6 +22,7 @@ int kgraph::add_node(int sym)
     symbol.push_back(sym);
     first.push_back(-1);
     second.push_back(-1);
+    gap.push_back(0);
     return static_cast<int>(symbol.size()) - 1;
 }
 
@@ -82,12 +84,150 @@ void kgraph::compute_ranks()
     }
 }
 
+void kgraph::augment()
+{
+    if (catsites.empty())
+        return;
+    // merge_catsites (include/otf_collector.h:438-464): by rank of the entry node; a catsite that starts right after the
+    // previous one ends is folded into it (gaps = all pairwise sums)
+    std::vector<catsite> cats = catsites;
+    std::sort(cats.begin(), cats.end(), [&](catsite const & a, catsite const & b) { return rank[a.cleavage_start] < rank[b.cleavage_start]; });
+    {
+        std::vector<catsite> merged;
+        bool done = false;
+        for (catsite const & c : cats)
+        {
+            if (merged.empty() || static_cast<size_t>(rank[c.cleavage_start]) - 1 != static_cast<size_t>(rank[merged.back().cleavage_end]))
+            {
+                merged.push_back(c);
+                continue;
+            }
+            merged.back().cleavage_end = c.cleavage_end;
+            rh_slots sums; // sumGaps (:426-436)
+            std::vector<uint64_t> a, b;
+            merged.back().gaps.for_each_key([&](uint64_t k) { a.push_back(k); });
+            c.gaps.for_each_key([&](uint64_t k) { b.push_back(k); });
+            for (uint64_t x : a)
+                for (uint64_t y : b)
+                    sums.insert_key(x + y);
+            merged.back().gaps = sums;
+            done = true;
+        }
+        if (done)
+            cats = merged;
+    }
+    for (catsite & c : cats)
+    {
+        std::vector<uint64_t> gaps;
+        c.gaps.for_each_key([&](uint64_t k) { gaps.push_back(k); });
+        c.downstream = first[c.cleavage_end]; // complete(): arcs.find(id(cleavage_end_))->second.first
+        auto add_gap = [&](uint64_t gapsize) {
+            int const node = add_node(Gap);
+            gap[node] = gapsize;
+            add_arc(c.cleavage_site, node);
+            add_arc(node, c.downstream);
+        };
+        if (gaps.size() == 1)
+            add_gap(gaps[0]);
+        else
+        {
+            // add_guard (:407-418): a Split in front, a Ghost behind; the gaps hang between them.  A split only has two
+            // slots in the arc map, so of three or more gaps the walk sees the first and the LAST one added — as in
+            // the reference
+            int const split = add_node(Split);
+            int const ghost = add_node(Ghost);
+            add_arc(c.cleavage_site, split);
+            add_arc(ghost, c.downstream);
+            c.cleavage_site = split;
+            c.downstream = ghost;
+            for (uint64_t gsz : gaps)
+                add_gap(gsz);
+        }
+    }
+    compute_ranks();
+}
+
 namespace
 {
 
+// Subgraph's bookkeeping for catsite detection (include/construction_tools.h:74-146): number of paths through the
+// subgraph and the set of their lengths.  `lengths` is a robin_hood::unordered_set in the reference and its ITERATION
+// order is visible (it decides the order in which augment() creates Gap nodes, and which gap `*gaps.begin()` is), so it
+// is kept in a table that places keys exactly like that container does (rh_order.hpp), filled by the same inserts in
+// the same order.
 struct subgraph
 {
     int start{-1}, end{-1};
+    size_t split_run_count{0};
+    size_t paths{1};
+    rh_slots lengths;
+
+    static subgraph twins(int node) // {node, node, 0u, 1u, {1u}, Default}
+    {
+        subgraph s{node, node};
+        s.lengths.insert_key(1);
+        return s;
+    }
+    std::vector<uint64_t> length_list() const
+    {
+        std::vector<uint64_t> v;
+        lengths.for_each_key([&](uint64_t k) { v.push_back(k); });
+        return v;
+    }
+    void concat_info(subgraph const & a, subgraph const & b)
+    {
+        paths = a.paths * b.paths;
+        for (uint64_t l : a.length_list())
+            for (uint64_t j : b.length_list())
+                lengths.insert_key(l + j);
+        split_run_count = std::max(a.split_run_count, b.split_run_count);
+    }
+    void union_info(subgraph const & a, subgraph const & b)
+    {
+        // std::set_union over the two sets' iteration orders (which are not sorted: the merge is what it is)
+        std::vector<uint64_t> const x = a.length_list(), y = b.length_list();
+        size_t i = 0, j = 0;
+        while (i < x.size() && j < y.size())
+        {
+            if (x[i] < y[j])
+                lengths.insert_key(x[i++]);
+            else if (y[j] < x[i])
+                lengths.insert_key(y[j++]);
+            else
+            {
+                lengths.insert_key(x[i++]);
+                ++j;
+            }
+        }
+        for (; i < x.size(); ++i)
+            lengths.insert_key(x[i]);
+        for (; j < y.size(); ++j)
+            lengths.insert_key(y[j]);
+        split_run_count = a.split_run_count + b.split_run_count + 1;
+        paths = a.paths + b.paths;
+    }
+    void option_info(subgraph const & a)
+    {
+        lengths.insert_key(0);
+        for (uint64_t l : a.length_list())
+            lengths.insert_key(l);
+        split_run_count = a.split_run_count + 1;
+        paths = a.paths + 1;
+    }
+    void kleene_info(subgraph const & a, uint8_t repeats)
+    {
+        for (size_t i = 0; i < repeats; ++i)
+            for (uint64_t l : a.length_list())
+                lengths.insert_key(i * l);
+        split_run_count = a.split_run_count;
+        paths = a.paths * repeats;
+    }
+    void copy_meta(subgraph const & a)
+    {
+        split_run_count = a.split_run_count;
+        paths = a.paths;
+        lengths = a.lengths;
+    }
 };
 
 // `reduced` selects construct_reduced_kgraph (src/construct_reduced_nfa.cpp), which the reference uses whenever the
@@ -102,8 +242,23 @@ struct builder
     std::stack<subgraph> stack;
     bool reduced{false};
     std::vector<int> buffer;
+    std::vector<catsite> cats;
 
     static bool twins(subgraph const & s) { return s.start == s.end; }
+
+    // detect_bad_graphs (src/construction_tools.cpp:161-180)
+    void detect_bad_graphs(subgraph const & a, subgraph const & b, subgraph const & joined)
+    {
+        if (b.paths >= 15 || (joined.paths >= 690000u && b.start != b.end))
+        {
+            catsite c;
+            c.cleavage_site = a.end;
+            c.cleavage_start = b.start;
+            c.cleavage_end = b.end;
+            c.gaps = b.lengths;
+            cats.push_back(c);
+        }
+    }
 
     // twin_procedure (src/construct_reduced_nfa.cpp:107-112)
     void materialise(subgraph & s)
@@ -115,7 +270,7 @@ struct builder
         int sym = buffer.back();
         buffer.pop_back();
         int node = g.add_node(sym);
-        s = {node, node};
+        s = subgraph::twins(node);
     }
 
     subgraph pop()
@@ -142,7 +297,9 @@ struct builder
             else
                 throw error("regular expression not supported on a reduced alphabet (empty symbol buffer in the reference)");
             int twin = g.add_node(sym);
-            return {twin, twin};
+            subgraph c{twin, twin};
+            c.copy_meta(sg);
+            return c;
         }
         int const n = static_cast<int>(g.size());
         int const n_arcs = static_cast<int>(g.arcs.size());
@@ -180,7 +337,9 @@ struct builder
             if (twin[u] >= 0 && twin[v] >= 0)
                 g.add_arc(twin[u], twin[v]);
         }
-        return {twin[sg.start], twin[sg.end]};
+        subgraph c{twin[sg.start], twin[sg.end]};
+        c.copy_meta(sg);
+        return c;
     }
 
     void symbol(int c)
@@ -188,11 +347,11 @@ struct builder
         if (reduced)
         {
             buffer.push_back(c);
-            stack.push({-1, -1}); // placeholder twins
+            stack.push(subgraph::twins(-1)); // placeholder twins
             return;
         }
         int node = g.add_node(c);
-        stack.push({node, node});
+        stack.push(subgraph::twins(node));
     }
 
     void concat()
@@ -201,7 +360,10 @@ struct builder
         materialise(b);
         materialise(a);
         g.add_arc(a.end, b.start);
-        stack.push({a.start, b.end});
+        subgraph joined{a.start, b.end};
+        joined.concat_info(a, b);
+        detect_bad_graphs(a, b, joined);
+        stack.push(joined);
     }
 
     void alternation()
@@ -228,7 +390,9 @@ struct builder
         int ghost = g.add_node(Ghost);
         g.add_arc(a.end, ghost);
         g.add_arc(b.end, ghost);
-        stack.push({split, ghost});
+        subgraph u{split, ghost};
+        u.union_info(a, b);
+        stack.push(u);
     }
 
     void optional()
@@ -240,7 +404,9 @@ struct builder
         int ghost = g.add_node(Ghost);
         g.add_arc(split, ghost);
         g.add_arc(a.end, ghost);
-        stack.push({split, ghost});
+        subgraph o{split, ghost};
+        o.option_info(a);
+        stack.push(o);
     }
 
     // '*' unrolled: ε, X, …, X^(k-1)   (src/construct_nfa.cpp:146-192)
@@ -267,7 +433,9 @@ struct builder
             }
             back = c.end;
         }
-        stack.push({split, ghost});
+        subgraph ks{split, ghost};
+        ks.kleene_info(a, static_cast<uint8_t>(k));
+        stack.push(ks);
     }
 
     // '+' unrolled: X, …, X^(k-1)   (src/construct_nfa.cpp:195-223)
@@ -291,7 +459,7 @@ struct builder
             }
             back = c.end;
         }
-        stack.push({a.start, ghost});
+        stack.push(subgraph{a.start, ghost}); // no meta: Subgraph stack_subgraph{subgraph.start, ghost_node} (:221)
     }
 
     // {m,n} / {m}   (src/construct_nfa.cpp:226-262); returns true if the next '-' has to be skipped
@@ -409,6 +577,7 @@ kgraph construct_kgraph(std::string const & postfix, uint8_t k, bool reduced)
     int const match = b.g.add_node(Match);
     b.g.add_arc(whole.end, match);
     b.g.compute_ranks();
+    b.g.catsites = std::move(b.cats);
     return std::move(b.g);
 }
 

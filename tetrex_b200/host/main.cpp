@@ -145,12 +145,14 @@ int run_kgraph(arg_reader a)
     unsigned k = 3;
     bool dna = false;
     int reduction = TRX_RED_BASE;
+    bool augment = false;
     std::string regex;
     while (!a.done())
     {
         std::string s = a.next("argument");
         if (s == "-k") k = to_uint(a.next("-k"), "-k");
         else if (s == "-n") dna = true;
+        else if (s == "-a") augment = true;
         else if (s == "-r")
         {
             std::string r = a.next("-r");
@@ -172,9 +174,12 @@ int run_kgraph(arg_reader a)
     std::string postfix = translate(rx);
     std::cout << "postfix\t" << postfix << "\n";
     kgraph g = construct_kgraph(postfix, static_cast<uint8_t>(k), reduction != TRX_RED_BASE);
+    if (augment)
+        g.augment(); // -a: the graph the collector walks after OTFCollector::augment
     std::cout << "nodes\t" << g.size() << "\n";
-    for (size_t i = 0; i < g.size(); ++i)
-        std::cout << i << "\t" << g.symbol[i] << "\t" << g.first[i] << "\t" << g.second[i] << "\t" << g.rank[i] << "\n";
+    for (size_t i = 0; i < g.size(); ++i) // a Gap node's length rides in the second slot
+        std::cout << i << "\t" << g.symbol[i] << "\t" << g.first[i] << "\t"
+                  << (g.symbol[i] == Gap ? static_cast<long>(g.gap[i]) : static_cast<long>(g.second[i])) << "\t" << g.rank[i] << "\n";
     return 0;
 }
 

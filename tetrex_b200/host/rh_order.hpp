@@ -93,6 +93,21 @@ public:
                 f(vals_[i]);
     }
 
+    // f(key) in slot order: iteration order of a robin_hood::unordered_set<size_t> filled by the same inserts
+    template <class F>
+    void for_each_key(F && f) const
+    {
+        for (size_t i = 0; i < with_buffer_; ++i)
+            if (info_[i])
+                f(keys_[i]);
+    }
+    // insert() of a set: a key that is already there is left alone
+    void insert_key(uint64_t key)
+    {
+        if (find(key) == npos)
+            insert_new(key, 0);
+    }
+
 private:
     static size_t max_allowed_for(size_t n) { return n * 80 / 100; }
     static size_t with_buffer_for(size_t n)

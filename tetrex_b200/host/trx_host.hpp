@@ -15,6 +15,7 @@
 #include <vector>
 
 #include "../../include/tetrex_b200.h"
+#include "rh_order.hpp"
 
 namespace trxh
 {
@@ -128,12 +129,28 @@ enum node_symbol : int { Match = 256, Ghost = 257, Split = 258, Gap = 259 };
 // Linearised acyclic NFA of construct_kgraph (src/construct_nfa.cpp:265-335): node ids, symbols and the
 // two-slot arc map exactly as the reference numbers them, plus the collector's ranks
 // (include/otf_collector.h:328-339).
+// Catsite (include/construction_tools.h:151-185): a concatenation whose right operand has so many paths that walking it
+// would explode; `-a` replaces the operand by Gap nodes, one per distinct length.
+struct catsite
+{
+    int cleavage_site{-1};  // node before the high-complexity subgraph
+    int cleavage_start{-1}; // its entry node
+    int cleavage_end{-1};   // its exit node
+    int downstream{-1};     // where the exit node leads (complete())
+    rh_slots gaps;          // lengths of the paths through it, in the reference's robin_hood iteration order
+};
+
 struct kgraph
 {
     std::vector<int> symbol;
     std::vector<int> first, second; // arc_map slots; -1 = none
     std::vector<int> rank;
+    std::vector<size_t> gap;        // gap_map: length a Gap node stands for
     std::vector<std::pair<int, int>> arcs; // in creation order (source, target)
+    std::vector<catsite> catsites;  // detect_bad_graphs (src/construction_tools.cpp:161-180), in detection order
+    // OTFCollector::augment (include/otf_collector.h:466-493): merge neighbouring catsites, bridge each with Gap nodes,
+    // rank again.  No-op without catsites.
+    void augment();
     int add_node(int sym);
     void add_arc(int source, int target); // update_arc_map (src/construction_tools.cpp:136-158)
     void compute_ranks();
@@ -257,8 +274,10 @@ struct collect_stats
 // process_query (include/query.h:226-247): preprocess, k-graph, OTFCollector::collect with every probe, path
 // AND, none() test and path OR executed on the device.
 // A sharded flat index returns the whole-width vector with only its own words filled in (the caller ORs / gathers).
+// augment: collector.augment(catsites) before the walk (`-a`); a DGram index attached to `index` (`-g`) is probed by the
+// gapped items (include/otf_collector.h:216-245,290-312).
 bitvector process_query(std::string const & regex, DeviceIndex & index, collect_stats * stats = nullptr,
-                        shard_hooks const * hooks = nullptr);
+                        shard_hooks const * hooks = nullptr, bool augment = false);
 // the collector alone on a ready k-graph (OTFCollector::collect, include/otf_collector.h:341-393)
 bitvector collect(kgraph const & g, DeviceIndex & index, collect_stats * stats = nullptr, shard_hooks const * hooks = nullptr);
 
