@@ -135,6 +135,27 @@ int trx_emplace_records_slab_dev(trx_ibf_t *ibf, int molecule, uint32_t k, int r
                                  uint64_t n_residues, const uint64_t *d_rec_offsets, const uint32_t *d_rec_bin,
                                  uint64_t n_records, uint64_t first_bin, uint64_t n_bins);
 
+/* N2 — DGramIndex, the gapped 3+3-mer filter behind `tetrex dindex` / `tetrex query -g` (include/dGramIndex.h).
+ * DGramIndex::process_sequence (:194-243) run for every record at once: position i >= 2 with i + min_gap + 3 < L, the
+ * three residues ending at i, a gap of min_gap..max_gap, the three residues from j = i + gap + 1 (stop at the first gap
+ * with j + 2 >= L); all six must be upper-case letters of "ACDEFGHIKLMNPQRSTVWY"; records shorter than min_gap + 7 give
+ * nothing; code = gap*20^6 + a1*20^5 + a2*20^4 + a3*20^3 + b1*400 + b2*20 + b3.
+ *  trx_dgram_count   : per_bin[b] = how many codes bin b receives, duplicates included — what dgram_buffer_[b].size()
+ *                      is after populate() (:103-111); its maximum sizes the filter (find_largest_bin / compute_bitcount,
+ *                      :128-142).  per_bin[0..n_bins) is overwritten.
+ *  trx_dgram_emplace : init_ibf's loop (:149-153): every code is emplaced into its record's bin.
+ * max_gap is limited to TRX_DGRAM_MAX_GAP (the reference's default upper bound is 21). */
+#define TRX_DGRAM_MAX_GAP 4096u
+int trx_dgram_count(trx_ctx_t *ctx, const uint8_t *residues, const uint64_t *rec_offsets, const uint32_t *rec_bin,
+                    uint64_t n_records, uint32_t min_gap, uint32_t max_gap, uint64_t n_bins, uint64_t *per_bin);
+int trx_dgram_count_dev(trx_ctx_t *ctx, const uint8_t *d_residues, uint64_t n_residues, const uint64_t *d_rec_offsets,
+                        const uint32_t *d_rec_bin, uint64_t n_records, uint32_t min_gap, uint32_t max_gap,
+                        uint64_t n_bins, uint64_t *d_per_bin);
+int trx_dgram_emplace(trx_ibf_t *ibf, const uint8_t *residues, const uint64_t *rec_offsets, const uint32_t *rec_bin,
+                      uint64_t n_records, uint32_t min_gap, uint32_t max_gap);
+int trx_dgram_emplace_dev(trx_ibf_t *ibf, const uint8_t *d_residues, uint64_t n_residues, const uint64_t *d_rec_offsets,
+                          const uint32_t *d_rec_bin, uint64_t n_records, uint32_t min_gap, uint32_t max_gap);
+
 /* K2 — containment_agent_type::bulk_contains (…cpp:203-290) / IBFIndex::query (index_ibf.h:146-150)
  * for a batch: out_words[i*shard_words + w] = AND_h row_h(kmers[i])[w]. */
 int trx_bulk_contains(trx_ibf_t *ibf, const uint64_t *kmers, uint64_t n, uint64_t *out_words);

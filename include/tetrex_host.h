@@ -6,6 +6,7 @@
  *   load_ibf                      include/index_base.h:189-195
  *   process_query                 include/query.h:226-247   (preprocess, construct_kgraph, OTFCollector::collect)
  *   iter_disk_search              include/query.h:97-188    (verify_fasta_hit & co., src/query.cpp:167-315)
+ *   DGramIndex / drive_dindex     include/dGramIndex.h:64-326, src/dGramIndex.cpp:19-38
  * Every function returns 0, or -1 with the message in trxh_last_error() (thread-local): the messages are the ones the
  * C++ layer throws (trxh::error / trxh::archive_error), i.e. what src/main.cpp prints for std::runtime_error /
  * cereal::Exception.  There is no CPU fallback underneath: the handle lives on the device of the trx_ctx_t. */
@@ -37,6 +38,19 @@ int trxh_attach_comm(void *handle, trx_comm_t *comm);
 /* resident processes (servers, benchmarks): load every bin of the shard into HBM on the first verify; the default reads
  * the candidate bins' FASTA files only, like iter_disk_search (include/query.h:126-131) */
 int trxh_preload_text(void *handle, int on);
+
+/* `tetrex query -a` (include/arg_parse.h:65, include/query.h:243): trxh_process_query runs OTFCollector::augment
+ * (include/otf_collector.h:466-493) on the k-graph before the walk — high-complexity stretches become Gap nodes. */
+int trxh_set_augment(void *handle, int on);
+/* `tetrex query -g FILE` (include/arg_parse.h:68, include/query.h:258-264): load_dindex (include/dGramIndex.h:320-326) onto
+ * the handle's device; gapped collector items probe it (include/otf_collector.h:216-245).  The DGram index must have the
+ * index's bin count.  NULL or "" detaches. */
+int trxh_attach_dgram(void *handle, const char *path);
+/* `tetrex dindex` (src/dGramIndex.cpp:19-38, include/dGramIndex.h:90-154): DGramIndex(min, max, 1, hash_count, fpr, files),
+ * populate() and save_dindex(out_path) with the counting and the emplacing done on ctx's device (trx_dgram_count_dev /
+ * trx_dgram_emplace_dev).  File names are stored as given.  per_bin (nullable): dgram_buffer_[b].size() per file. */
+int trxh_dindex_build(trx_ctx_t *ctx, const char *const *files, uint64_t n_files, uint64_t min_gap, uint64_t max_gap,
+                      uint32_t hash_count, float fpr, const char *out_path, uint64_t *per_bin);
 
 /* ORs n bytes over all shards in place (all-reduce MAX): the collector's `path_.none()` (include/otf_collector.h:383) is
  * a statement about all bins.  Called once per probing rank of the k-graph, on the calling thread. */

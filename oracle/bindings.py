@@ -115,6 +115,12 @@ def ref():
                                         C.c_int, C.c_int, C.c_int, C.c_char_p]
         lib.ref_index_query.restype = C.c_int
         lib.ref_index_query.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.c_int, u64p, C.c_uint64, C.c_char_p]
+        lib.ref_index_query_dibf.restype = C.c_int
+        lib.ref_index_query_dibf.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_char_p, C.c_int, C.c_int, u64p, C.c_uint64,
+                                             C.c_char_p]
+        lib.ref_dindex_build.restype = C.c_int
+        lib.ref_dindex_build.argtypes = [C.POINTER(C.c_char_p), C.c_uint64, C.c_uint64, C.c_uint64, C.c_int, C.c_float,
+                                         C.c_char_p, u64p]
         lib.ref_kgraph.restype = C.c_int
         lib.ref_kgraph.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, i32p, i32p, i32p, i32p, C.c_uint64,
                                    C.c_char_p, C.c_uint64]
@@ -444,13 +450,28 @@ def ref_index_build(files, k, fpr, hash_count, molecule, flavor, reduction, out_
         raise RuntimeError(ref().ref_last_error().decode())
 
 
-def ref_index_query(index_path, regex, verify=True, threads=1, stdout_path=None):
-    """process_query (+ iter_disk_search) of the reference on an index file: (hit words, captured stdout)."""
+def ref_dindex_build(files, min_gap, max_gap, hash_count, fpr, out_path) -> np.ndarray:
+    """drive_dindex's work with the reference's DGramIndex; writes out_path, returns the codes each bin buffered."""
+    arr = (C.c_char_p * len(files))(*[f.encode() for f in files])
+    per_bin = np.zeros(len(files), dtype=np.uint64)
+    rc = ref().ref_dindex_build(arr, len(files), min_gap, max_gap, hash_count, fpr, out_path.encode(), _p(per_bin, u64p))
+    if rc != 0:
+        raise RuntimeError(ref().ref_last_error().decode())
+    return per_bin
+
+
+def ref_index_query(index_path, regex, verify=True, threads=1, stdout_path=None, augment=False, dibf_path=None):
+    """process_query (+ iter_disk_search) of the reference on an index file: (hit words, captured stdout).
+    augment = `-a`, dibf_path = `-g`."""
     import tempfile
     words = np.zeros(1 << 14, dtype=np.uint64)
     tmp = stdout_path or tempfile.mktemp(prefix="ref_stdout_")
-    n = ref().ref_index_query(index_path.encode(), regex.encode(), 0, 1 if verify else 0, threads, _p(words, u64p), len(words),
-                              tmp.encode())
+    if dibf_path:
+        n = ref().ref_index_query_dibf(index_path.encode(), regex.encode(), 1 if augment else 0, dibf_path.encode(),
+                                       1 if verify else 0, threads, _p(words, u64p), len(words), tmp.encode())
+    else:
+        n = ref().ref_index_query(index_path.encode(), regex.encode(), 1 if augment else 0, 1 if verify else 0, threads,
+                                  _p(words, u64p), len(words), tmp.encode())
     if n < 0:
         raise RuntimeError(ref().ref_last_error().decode())
     text = ""

@@ -459,7 +459,7 @@ struct fd_capture
 
 template <class flavor_t, class mol_t>
 int harness_query(std::string const & index_path, std::string regex, bool augment, bool verify, int threads,
-                  uint64_t * hit_words, uint64_t cap_words, char const * stdout_path)
+                  uint64_t * hit_words, uint64_t cap_words, char const * stdout_path, char const * dibf_path = nullptr)
 {
     // src/query.cpp:375-475 (query_*), include/query.h:250-290 (run_collection)
     omp_set_num_threads(threads < 1 ? 1 : threads);
@@ -468,8 +468,14 @@ int harness_query(std::string const & index_path, std::string regex, bool augmen
     ibf.spawn_agent();
     bitvector hit_vector(ibf.getBinCount(), true);
     DGramIndex dibf{};
+    bool has_dibf = false;
+    if (dibf_path && *dibf_path) // run_collection, include/query.h:258-264
+    {
+        load_dindex(dibf, std::filesystem::path{dibf_path});
+        has_dibf = true;
+    }
     if (ibf.getBinCount() > 1u)
-        hit_vector &= process_query(regex, ibf, false, augment, false, false, dibf);
+        hit_vector &= process_query(regex, ibf, false, augment, false, has_dibf, dibf);
     size_t const words = (ibf.getBinCount() + 63) / 64;
     for (size_t i = 0; i < words && i < cap_words; ++i)
         hit_words[i] = hit_vector.data()[i];
@@ -536,6 +542,56 @@ int ref_index_query(char const * index_path, char const * regex, int augment, in
                                                                            threads, hit_words, cap_words, stdout_path);
         return harness_query<index_structure::HIBF, molecules::peptide>(index_path, regex, augment, verify, threads,
                                                                         hit_words, cap_words, stdout_path);
+    }
+    catch (std::exception const & e)
+    {
+        g_err = e.what();
+        return -1;
+    }
+}
+
+// The same with a DGram index (`-g`) next to the index: run_collection's has_dibf path.
+int ref_index_query_dibf(char const * index_path, char const * regex, int augment, char const * dibf_path, int verify,
+                         int threads, uint64_t * hit_words, uint64_t cap_words, char const * stdout_path)
+{
+    try
+    {
+        index_params params;
+        load_params(params, std::filesystem::path{index_path});
+        bool const na = params.molecule_ == "na";
+        if (!params.is_hibf_ && na)
+            return harness_query<index_structure::IBF, molecules::nucleotide>(index_path, regex, augment, verify, threads,
+                                                                              hit_words, cap_words, stdout_path, dibf_path);
+        if (params.is_hibf_ && na)
+            return harness_query<index_structure::HIBF, molecules::nucleotide>(index_path, regex, augment, verify, threads,
+                                                                               hit_words, cap_words, stdout_path, dibf_path);
+        if (!params.is_hibf_)
+            return harness_query<index_structure::IBF, molecules::peptide>(index_path, regex, augment, verify, threads,
+                                                                           hit_words, cap_words, stdout_path, dibf_path);
+        return harness_query<index_structure::HIBF, molecules::peptide>(index_path, regex, augment, verify, threads,
+                                                                        hit_words, cap_words, stdout_path, dibf_path);
+    }
+    catch (std::exception const & e)
+    {
+        g_err = e.what();
+        return -1;
+    }
+}
+
+// drive_dindex's work (src/dGramIndex.cpp:35-37): DGramIndex(min, max, pad, hc, fpr, files).populate() + save_dindex.
+// per_bin[b] = dgram_buffer_[b].size().
+int ref_dindex_build(char const * const * files, uint64_t n_files, uint64_t min_gap, uint64_t max_gap, int hash_count, float fpr,
+                     char const * out_path, uint64_t * per_bin)
+{
+    try
+    {
+        std::vector<std::string> f(files, files + n_files);
+        DGramIndex dindex(min_gap, max_gap, 1, static_cast<size_t>(hash_count), fpr, f);
+        dindex.populate();
+        for (uint64_t b = 0; b < n_files && per_bin; ++b)
+            per_bin[b] = dindex.dgrams()[b].size();
+        save_dindex(dindex, std::filesystem::path{out_path});
+        return 0;
     }
     catch (std::exception const & e)
     {

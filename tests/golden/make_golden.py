@@ -585,6 +585,127 @@ def golden_cli_conj():
         print(c["regex"], c["bins"], repr(c["stdout"][:300]))
 
 
+def gap_regexes(rng, records, n):
+    """Patterns with a wildcard stretch between two literal anchors cut out of real records: what `-a` turns into a Gap
+    node.  Left anchors of >= 3 residues and gaps inside the DGram bounds make gapped items; short anchors, short right
+    sides, gaps outside the bounds, several wildcard stretches and mismatching right sides cover the other branches of
+    gap_procedure / update_gapped (include/otf_collector.h:216-245,290-312)."""
+    out = []
+    while len(out) < n:
+        rec = rng.choice(records)
+        la, g, ra = rng.randint(1, 6), rng.randint(1, 9), rng.randint(0, 6)
+        if len(rec) < la + g + ra + 12:
+            continue
+        at = rng.randint(0, len(rec) - (la + g + ra + 10))
+        left, right = rec[at:at + la], rec[at + la + g:at + la + g + ra]
+        u = rng.random()
+        if u < 0.35:
+            mid = ".{%d}" % g
+        elif u < 0.5:
+            mid = "." * g
+        elif u < 0.75:
+            lo = max(0, g - rng.randint(0, 2))
+            mid = ".{%d,%d}" % (lo, g + rng.randint(0, 2))
+        elif u < 0.85:
+            a = rng.randint(1, g) if g > 1 else 1
+            mid = ".{%d}" % a + (".{%d,%d}" % (g - a, g - a + 1) if g - a > 0 else "")
+        else:
+            mid = "[^P]{%d}" % g
+        if right and rng.random() < 0.2:  # a right side that is not in the record
+            j = rng.randrange(len(right))
+            right = right[:j] + rng.choice(AA.decode().replace(right[j], "")) + right[j + 1:]
+        tail = ""
+        if rng.random() < 0.25:  # a second stretch further right
+            g2 = rng.randint(1, 5)
+            st = at + la + g + ra + g2
+            tail = ".{%d}" % g2 + rec[st:st + rng.randint(1, 4)]
+        out.append(left + mid + right + tail)
+    return out
+
+
+def golden_dgram():
+    """`tetrex dindex` + `tetrex query -a [-g]` (include/dGramIndex.h, include/otf_collector.h:216-245,290-312,395-493):
+    the reference builds DGram indexes over tests/data (per-bin code counts and the sha256 of the file it writes are kept —
+    the files themselves are up to 1.3 MB), then answers gap patterns with augmentation, with and without the DGram
+    filter.  A tiny two-bin DGram file is committed whole for the CPU-side reader/writer round trip."""
+    import hashlib
+    rng = random.Random(424242)
+    cwd = os.getcwd()
+    os.chdir(ROOT)
+    out = dict(builds=[], queries=[])
+    tmp = os.path.join("tests", "golden", "_tmp_dgram")
+    os.makedirs(tmp, exist_ok=True)
+    try:
+        cli = json.load(open(os.path.join(OUT, "cli.json")))
+        files_of = {c["index"]: c["files"] for c in cli}
+        tiny = [os.path.join("tests", "data", "ws_%d.fa" % i) for i in range(2)]
+        tiny = [f for f in tiny if os.path.exists(f)] or files_of["tests/golden/cli/pep_flat_k4.ibf"][:2]
+        per = ob.ref_dindex_build(tiny, 2, 3, 3, 0.05, os.path.join("tests", "golden", "tiny.dibf"))
+        out["tiny"] = dict(files=tiny, min=2, max=3, per_bin=[int(x) for x in per])
+        hand = ["WKC.{3}EFH", "WKC...EFH", "WKCD.{3}FH", "PWD.{3,4}IK", "PWDE.{2,3}K", "LMA.GLYN", "LMA.{1}GLYN", "LMAE.{3}N",
+                "CAAC.{2}LV", "CAA.{3}LV", "MKA.{2,4}W", "HHC.{3}W", "HHCA.{1,3}", "AAA.{2}AAA", "GQP.K", "WKCD.{4}H",
+                "WKC.{5}EFH", "WKC.{3}EFW", "LMA(E|Q).{0,2}LYN", "WKC.{2}.{1,2}EFH", "GLY.{3}[ACDEFGHIKLMNPQRSTVWY]K",
+                "KRRT.{3,8}[LIV]", "WKC.{3}EF.{2}[A-Z]", "WKCDEDE.{0}FH", "XKC.{3}EFH", "WKC.{3}XFH", "WKC.{3}BFH"]
+        for name, lo, hi in [("pep_flat_k4", 3, 21), ("pep_hibf_k4", 1, 4), ("wide_hibf_k4", 3, 21), ("pep_flat_k3_murphy", 2, 6)]:
+            idx = os.path.join("tests", "golden", "cli", name + ".ibf")
+            files = files_of[idx]
+            dpath = os.path.join(tmp, "%s_%d_%d.dibf" % (name, lo, hi))
+            per = ob.ref_dindex_build(files, lo, hi, 3, 0.05, dpath)
+            out["builds"].append(dict(name=name, files=files, min=lo, max=hi, per_bin=[int(x) for x in per],
+                                      sha256=hashlib.sha256(open(dpath, "rb").read()).hexdigest(), bytes=os.path.getsize(dpath)))
+            records = [r for f in files for r in read_records(f)]
+            pats = hand + gap_regexes(rng, records, 60 if "wide" not in name else 30)
+            for q in pats:
+                for dibf in (None, dpath):
+                    got = guarded_timed(ob.ref_index_query, 20, idx, q, True, 1, None, True, dibf)
+                    if got is None:
+                        # the reference dies in iter_disk_search when no k-mer was probed at all (every bit of the start
+                        # vector, padding included, survives): keep at least the filter's answer
+                        got = guarded_timed(ob.ref_index_query, 20, idx, q, False, 1, None, True, dibf)
+                        if got is None:
+                            out["queries"].append(dict(index=idx, build=len(out["builds"]) - 1, regex=q, dibf=bool(dibf),
+                                                       reference_aborts=True))
+                            continue
+                        got = (got[0], None)
+                    words, text = got
+                    out["queries"].append(dict(index=idx, build=len(out["builds"]) - 1, regex=q, dibf=bool(dibf), stdout=text,
+                                               bins=[b for b in range(len(files)) if int(words[b // 64]) >> (b % 64) & 1]))
+    finally:
+        import shutil
+        shutil.rmtree(tmp, ignore_errors=True)
+        os.chdir(cwd)
+    json.dump(out, open(os.path.join(OUT, "dgram.json"), "w"), indent=0)
+    qs = out["queries"]
+    print("dgram.json:", len(out["builds"]), "builds,", len(qs), "queries,", sum(1 for c in qs if c.get("reference_aborts")),
+          "aborts,", sum(1 for c in qs if c.get("bins")), "with candidate bins,", sum(1 for c in qs if c.get("stdout")), "with lines,",
+          sum(1 for c in qs if "bins" in c and c["stdout"] is None), "filter only")
+    # how often the DGram filter changes the answer, and how often augmentation does
+    by = {}
+    for c in qs:
+        by.setdefault((c["index"], c["regex"]), {})[c["dibf"]] = c.get("bins")
+    print("  DGram filter narrows the candidates of", sum(1 for v in by.values() if v.get(True) != v.get(False)), "of", len(by))
+
+
+def golden_kgraph_aug():
+    """k-graphs after OTFCollector::augment (include/otf_collector.h:395-493): catsites from detect_bad_graphs merged by rank,
+    one Gap node per distinct path length (slot 2 of a Gap node = its length), Split/Ghost guards when there are several."""
+    from tetrex_b200 import synth
+    hand = ["AC.DEF", "LMA.{2,4}GLYN", "C.{2,4}C.{3}[LIVMFYWC].{8}H.{3,5}H", "A.?BCD", "A(.|CD)EFG", "AC.{1,2}.DE", "ACD.", "AC.+DE",
+            "LM.{0,2}AC", "W.{3}.{2,3}K", "WKC.{3}EFH", "PWD.{3,4}IK", "[^P]{2}ACD", "AC[^DE]F.G", "(AC|.{2})DEF", "MK.{2}(L|.)W"]
+    pats = hand + synth.prosite_patterns(50, 77)
+    cases = []
+    for k in (3, 4, 6):
+        for rx in pats:
+            got = guarded(ob.ref_kgraph, rx, 1, k, 0, True)
+            if got is None:
+                continue
+            cases.append({"regex": rx, "k": k, "postfix": got[0], "nodes": got[1]})
+    with open(os.path.join(OUT, "kgraph_aug.json"), "w") as f:
+        json.dump(cases, f, separators=(",", ":"))
+    print("kgraph_aug.json:", len(cases), "cases,", sum(1 for c in cases if any(n[0] == 259 for n in c["nodes"])), "with Gap nodes,",
+          sum(1 for c in cases if sum(1 for n in c["nodes"] if n[0] == 259) > 1), "with several")
+
+
 def golden_rh_order():
     """Pop orders of the real robin_hood::unordered_map for key lists shaped like a rank's sub-k-mer keys."""
     rng = random.Random(99)
@@ -599,7 +720,7 @@ def golden_rh_order():
 
 STEPS = {"decompose": golden_decompose, "ibf": golden_ibf, "hibf": golden_hibf, "regex": golden_regex,
          "kgraph": golden_kgraph, "cli": golden_cli, "c1": golden_c1, "collector_fuzz": golden_collector_fuzz, "rh_order": golden_rh_order,
-         "prosite_batch": golden_prosite_batch, "c2_twin_hibf": golden_c2_twin_hibf, "cli_ws": golden_cli_ws, "prosite_filter": golden_prosite_filter, "cli_conj": golden_cli_conj}
+         "prosite_batch": golden_prosite_batch, "c2_twin_hibf": golden_c2_twin_hibf, "cli_ws": golden_cli_ws, "prosite_filter": golden_prosite_filter, "cli_conj": golden_cli_conj, "dgram": golden_dgram, "kgraph_aug": golden_kgraph_aug}
 
 if __name__ == "__main__":
     assert ob.have_ref(), "build oracle/_ref first: make -C oracle ref"

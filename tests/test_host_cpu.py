@@ -49,6 +49,39 @@ def test_kgraph_matches_reference_golden(tetrex):
         assert got[1] == c["nodes"], (c["regex"], c["k"])
 
 
+def test_augmented_kgraph_matches_reference_golden(tetrex):
+    """`-a`: OTFCollector::augment (include/otf_collector.h:395-493) — Gap nodes, guards and the new ranks."""
+    cases = json.load(open(os.path.join(GOLDEN, "kgraph_aug.json")))
+    assert len(cases) >= 150 and sum(1 for c in cases if any(n[0] == 259 for n in c["nodes"])) >= 80
+    for c in cases:
+        out = subprocess.run([tetrex, "kgraph", "-a", "-k", str(c["k"]), c["regex"]], capture_output=True, text=True, timeout=60)
+        assert out.returncode == 0, (c["regex"], out.stderr)
+        lines = out.stdout.split("\n")
+        n = int(lines[1].split("\t")[1])
+        assert lines[0].split("\t")[1] == c["postfix"], c["regex"]
+        assert [[int(x) for x in line.split("\t")[1:]] for line in lines[2:2 + n]] == c["nodes"], (c["regex"], c["k"])
+
+
+def test_dgram_index_file_round_trip(tetrex, tmp_path):
+    """A DGram index written by the reference (tests/golden/tiny.dibf: save_dindex, include/dGramIndex.h:305-318) is read
+    and written back byte for byte by the host layer's cereal-layout reader/writer — no device involved."""
+    src = os.path.join(GOLDEN, "tiny.dibf")
+    out = tmp_path / "copy.dibf"
+    r = subprocess.run([tetrex, "dindex-rewrite", src, str(out)], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 0, r.stderr
+    fields = dict(line.split("\t") for line in r.stdout.strip().split("\n"))
+    tiny = json.load(open(os.path.join(GOLDEN, "dgram.json")))["tiny"]
+    assert int(fields["min_gap"]) == tiny["min"] and int(fields["max_gap"]) == tiny["max"]
+    assert int(fields["bins"]) == len(tiny["files"]) and int(fields["hash_count"]) == 3
+    from oracle import bindings as ob
+    assert int(fields["bin_size"]) == ob.compute_bitcount(max(tiny["per_bin"]), 0.05)
+    assert open(out, "rb").read() == open(src, "rb").read()
+    bad = tmp_path / "bad.dibf"
+    bad.write_bytes(open(src, "rb").read()[:100])
+    r = subprocess.run([tetrex, "dindex-rewrite", str(bad), str(out)], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 1 and "Failed to read" in r.stderr
+
+
 def test_kgraph_fuzz_against_compiled_reference(tetrex):
     """Live comparison with oracle/_ref (present in the dev container and shipped to the GPU box as a built .so)."""
     from oracle import bindings as ob

@@ -142,6 +142,16 @@ def compute_bitcount(n, fpr) -> int:
     return lib().trx_compute_bitcount(n, fpr)
 
 
+def dgram_count(ctx, residues, rec_offsets, rec_bin, min_gap: int, max_gap: int, n_bins: int) -> np.ndarray:
+    """dgram_buffer_[b].size() after DGramIndex::populate (include/dGramIndex.h:103-111,194-243), counted on the device."""
+    res = np.frombuffer(residues, dtype=np.uint8) if isinstance(residues, (bytes, bytearray)) else _np(residues, np.uint8)
+    offs = _np(rec_offsets, np.uint64)
+    rb = _np(rec_bin, np.uint32)
+    out = np.zeros(n_bins, dtype=np.uint64)
+    check(lib().trx_dgram_count(ctx._h, _ptr(res), _ptr(offs), _ptr(rb), len(rb), min_gap, max_gap, n_bins, _ptr(out)))
+    return out
+
+
 class IBF:
     """Flat interleaved Bloom filter resident in HBM (seqan::hibf::interleaved_bloom_filter)."""
 
@@ -205,6 +215,13 @@ class IBF:
                                  d_rec_bin: int, n_records: int, first_bin: int, n_bins: int):
         check(lib().trx_emplace_records_slab_dev(self._h, molecule, k, reduction, d_residues, n_residues, d_rec_offsets,
                                                  d_rec_bin, n_records, first_bin, n_bins))
+
+    def dgram_emplace(self, residues, rec_offsets, rec_bin, min_gap: int, max_gap: int):
+        """init_ibf of the DGram index (include/dGramIndex.h:144-154): every gapped 3+3-mer code of every record."""
+        res = np.frombuffer(residues, dtype=np.uint8) if isinstance(residues, (bytes, bytearray)) else _np(residues, np.uint8)
+        offs = _np(rec_offsets, np.uint64)
+        rb = _np(rec_bin, np.uint32)
+        check(lib().trx_dgram_emplace(self._h, _ptr(res), _ptr(offs), _ptr(rb), len(rb), min_gap, max_gap))
 
     def bulk_contains(self, kmers, out: np.ndarray | None = None) -> np.ndarray:
         v = _np(kmers, np.uint64)

@@ -486,6 +486,153 @@ int trx_decompose_records(trx_ctx_t * c, int molecule, uint32_t k, int reduction
     return TRX_OK;
 }
 
+// ------------------------------------------------------------------------------ DGram (gapped 3+3-mers)
+static int check_dgram_args(uint32_t min_gap, uint32_t max_gap)
+{
+    // the halo of one tile is max_gap + 5 bytes of shared memory next to the tile itself
+    if (max_gap > TRX_DGRAM_MAX_GAP)
+        return set_error(TRX_ERANGE, "DGram upper gap bound %u exceeds %u", max_gap, (unsigned)TRX_DGRAM_MAX_GAP);
+    (void)min_gap; // min_gap > max_gap is legal in the reference: the gap loop never runs, no code is produced
+    return TRX_OK;
+}
+
+extern "C++" {
+template <bool COUNT>
+static int launch_dgram(trx_ctx * c, ibf_geom g, const uint8_t * d_residues, uint64_t n_residues,
+                        const uint64_t * d_rec_offsets, const uint32_t * d_rec_bin, uint64_t n_records, uint32_t min_gap,
+                        uint32_t max_gap, unsigned long long * d_per_bin)
+{
+    uint64_t const n_tiles = (n_residues + kDgramTile - 1) / kDgramTile;
+    unsigned const grid = grid_for(n_tiles, 1, c->sm_count, 8);
+    size_t const smem = kDgramTile + 2 + max_gap + 3;
+    dgram_kernel<COUNT><<<grid, kDgramTile, smem, c->stream>>>(g, d_residues, n_residues, d_rec_offsets, d_rec_bin, n_records,
+                                                               min_gap, max_gap, d_per_bin);
+    ++c->launches;
+    TRX_CUDA(cudaGetLastError());
+    return TRX_OK;
+}
+} // extern "C++"
+
+int trx_dgram_count_dev(trx_ctx_t * c, const uint8_t * d_residues, uint64_t n_residues, const uint64_t * d_rec_offsets,
+                        const uint32_t * d_rec_bin, uint64_t n_records, uint32_t min_gap, uint32_t max_gap, uint64_t n_bins,
+                        uint64_t * d_per_bin)
+{
+    if (!c || !d_per_bin || n_bins == 0)
+        return set_error(TRX_EINVAL, "NULL argument");
+    TRX_TRY(check_dgram_args(min_gap, max_gap));
+    TRX_TRY(c->use());
+    TRX_CUDA(cudaMemsetAsync(d_per_bin, 0, n_bins * 8, c->stream));
+    if (n_records == 0 || n_residues == 0)
+        return TRX_OK;
+    if (!d_residues || !d_rec_offsets || !d_rec_bin)
+        return set_error(TRX_EINVAL, "NULL argument");
+    ibf_geom g{};
+    return launch_dgram<true>(c, g, d_residues, n_residues, d_rec_offsets, d_rec_bin, n_records, min_gap, max_gap,
+                              reinterpret_cast<unsigned long long *>(d_per_bin));
+}
+
+int trx_dgram_emplace_dev(trx_ibf_t * f, const uint8_t * d_residues, uint64_t n_residues, const uint64_t * d_rec_offsets,
+                          const uint32_t * d_rec_bin, uint64_t n_records, uint32_t min_gap, uint32_t max_gap)
+{
+    if (!f)
+        return set_error(TRX_EINVAL, "NULL argument");
+    TRX_TRY(check_dgram_args(min_gap, max_gap));
+    if (n_records == 0 || n_residues == 0)
+        return TRX_OK;
+    if (!d_residues || !d_rec_offsets || !d_rec_bin)
+        return set_error(TRX_EINVAL, "NULL argument");
+    trx_ctx * c = f->ctx;
+    TRX_TRY(c->use());
+    // like K1: a matrix beyond L2 is filled in row slices that fit (every pass re-derives the codes — reading shared
+    // memory — and fires only the atomics of its slice)
+    uint64_t window = 64ull << 20;
+    if (char const * e = getenv("TRX_EMPLACE_WINDOW_MB"))
+        window = static_cast<uint64_t>(atoll(e)) << 20;
+    uint64_t passes = window ? (f->bin_size * f->shard_words * 8 + window - 1) / window : 1;
+    if (passes < 1 || passes > 10)
+        passes = 1;
+    uint64_t const rows_per_pass = (f->bin_size + passes - 1) / passes;
+    for (uint64_t p = 0; p < passes; ++p)
+    {
+        ibf_geom g = geom_of(f);
+        g.row_lo = p * rows_per_pass;
+        g.row_hi = g.row_lo + rows_per_pass < f->bin_size ? g.row_lo + rows_per_pass : f->bin_size;
+        if (g.row_lo >= g.row_hi)
+            break;
+        TRX_TRY(launch_dgram<false>(c, g, d_residues, n_residues, d_rec_offsets, d_rec_bin, n_records, min_gap, max_gap, nullptr));
+    }
+    return TRX_OK;
+}
+
+static int check_record_table(const uint64_t * rec_offsets, const uint32_t * rec_bin, uint64_t n_records, uint64_t n_bins)
+{
+    if (rec_offsets[0] != 0)
+        return set_error(TRX_EINVAL, "rec_offsets[0] must be 0");
+    for (uint64_t i = 0; i < n_records; ++i)
+    {
+        if (rec_offsets[i + 1] < rec_offsets[i])
+            return set_error(TRX_EINVAL, "rec_offsets must be non-decreasing");
+        if (rec_bin[i] >= n_bins)
+            return set_error(TRX_ERANGE, "record %llu: bin %u >= bin count %llu", static_cast<unsigned long long>(i),
+                             rec_bin[i], static_cast<unsigned long long>(n_bins));
+    }
+    return TRX_OK;
+}
+
+static int stage_records(trx_ctx * c, const uint8_t * residues, const uint64_t * rec_offsets, const uint32_t * rec_bin,
+                         uint64_t n_records)
+{
+    uint64_t const n_res = rec_offsets[n_records];
+    TRX_TRY(c->d_in[0].reserve(n_res + 64));
+    TRX_TRY(c->d_in[1].reserve((n_records + 1) * 8));
+    TRX_TRY(c->d_in[2].reserve(n_records * 4));
+    TRX_CUDA(cudaMemcpyAsync(c->d_in[0].ptr, residues, n_res, cudaMemcpyHostToDevice, c->stream));
+    TRX_CUDA(cudaMemcpyAsync(c->d_in[1].ptr, rec_offsets, (n_records + 1) * 8, cudaMemcpyHostToDevice, c->stream));
+    TRX_CUDA(cudaMemcpyAsync(c->d_in[2].ptr, rec_bin, n_records * 4, cudaMemcpyHostToDevice, c->stream));
+    return TRX_OK;
+}
+
+int trx_dgram_count(trx_ctx_t * c, const uint8_t * residues, const uint64_t * rec_offsets, const uint32_t * rec_bin,
+                    uint64_t n_records, uint32_t min_gap, uint32_t max_gap, uint64_t n_bins, uint64_t * per_bin)
+{
+    if (!c || !per_bin || n_bins == 0 || (n_records && (!residues || !rec_offsets || !rec_bin)))
+        return set_error(TRX_EINVAL, "NULL argument");
+    TRX_TRY(check_dgram_args(min_gap, max_gap));
+    for (uint64_t b = 0; b < n_bins; ++b)
+        per_bin[b] = 0;
+    if (n_records == 0)
+        return TRX_OK;
+    TRX_TRY(check_record_table(rec_offsets, rec_bin, n_records, n_bins));
+    TRX_TRY(c->use());
+    TRX_TRY(stage_records(c, residues, rec_offsets, rec_bin, n_records));
+    TRX_TRY(c->d_out[0].reserve(n_bins * 8));
+    TRX_TRY(trx_dgram_count_dev(c, static_cast<uint8_t *>(c->d_in[0].ptr), rec_offsets[n_records],
+                                static_cast<uint64_t *>(c->d_in[1].ptr), static_cast<uint32_t *>(c->d_in[2].ptr), n_records,
+                                min_gap, max_gap, n_bins, static_cast<uint64_t *>(c->d_out[0].ptr)));
+    TRX_CUDA(cudaMemcpyAsync(per_bin, c->d_out[0].ptr, n_bins * 8, cudaMemcpyDeviceToHost, c->stream));
+    TRX_CUDA(cudaStreamSynchronize(c->stream));
+    return TRX_OK;
+}
+
+int trx_dgram_emplace(trx_ibf_t * f, const uint8_t * residues, const uint64_t * rec_offsets, const uint32_t * rec_bin,
+                      uint64_t n_records, uint32_t min_gap, uint32_t max_gap)
+{
+    if (!f || (n_records && (!residues || !rec_offsets || !rec_bin)))
+        return set_error(TRX_EINVAL, "NULL argument");
+    TRX_TRY(check_dgram_args(min_gap, max_gap));
+    if (n_records == 0)
+        return TRX_OK;
+    TRX_TRY(check_record_table(rec_offsets, rec_bin, n_records, f->bins));
+    trx_ctx * c = f->ctx;
+    TRX_TRY(c->use());
+    TRX_TRY(stage_records(c, residues, rec_offsets, rec_bin, n_records));
+    TRX_TRY(trx_dgram_emplace_dev(f, static_cast<uint8_t *>(c->d_in[0].ptr), rec_offsets[n_records],
+                                  static_cast<uint64_t *>(c->d_in[1].ptr), static_cast<uint32_t *>(c->d_in[2].ptr), n_records,
+                                  min_gap, max_gap));
+    TRX_CUDA(cudaStreamSynchronize(c->stream));
+    return TRX_OK;
+}
+
 // ------------------------------------------------------------------------------------------- K2
 int trx_bulk_contains_dev(trx_ibf_t * f, const uint64_t * d_kmers, uint64_t n, uint64_t * d_out_words)
 {

@@ -516,6 +516,108 @@ __global__ void __launch_bounds__(256)
     }
 }
 
+// ---------------------------------------------------------------------------------------- DGram (gapped 3+3-mers)
+// DGramIndex::process_sequence (include/dGramIndex.h:194-243) for every record at once.  The reference walks a record
+// with i = 2 .. while i + min_gap + 3 < L: the three residues ending at i, a gap of min_gap..max_gap residues, the three
+// residues starting at j = i + gap + 1; all six must be letters of "ACDEFGHIKLMNPQRSTVWY" (upper case only: alpha_map_
+// holds nothing else, :119-126), the inner loop stops at the first gap whose right side would leave the record
+// (`if (j + 2 >= L) break`), and records shorter than min_gap + 7 give nothing.  code = gap·20^6 + a1·20^5 + a2·20^4 +
+// a3·20^3 + b1·400 + b2·20 + b3.  One thread per position i; the block's residues plus a halo of max_gap + 3 are turned
+// into 0..19 / 0xFF codes in shared memory once, so the 3 + 3·gaps reads per position never leave the SM.
+//   COUNT = true : per_bin[bin] += number of codes (duplicates included — dgram_buffer_ keeps them, and the largest
+//                  buffer sizes the filter, :128-148)
+//   COUNT = false: every code goes through emplace (init_ibf, :149-153) — H atomic ORs each.
+constexpr int kDgramTile = 256;
+
+__device__ __forceinline__ uint8_t dgram_letter(uint8_t c)
+{
+    // "ACDEFGHIKLMNPQRSTVWY" → 0..19 (the alphabet is in alphabetical order, so the code of a letter is the number of
+    // alphabet letters below it); B J O U X Z and everything that is not an upper-case letter → 0xFF
+    constexpr uint32_t letters = 0x16fbdfdu;
+    uint32_t const d = static_cast<uint32_t>(c) - 'A';
+    if (d >= 26 || !(letters >> d & 1))
+        return 0xFF;
+    return static_cast<uint8_t>(__popc(letters & ((1u << d) - 1)));
+}
+
+template <bool COUNT>
+__global__ void __launch_bounds__(kDgramTile)
+    dgram_kernel(ibf_geom g, uint8_t const * __restrict__ text, uint64_t n_residues,
+                 uint64_t const * __restrict__ rec_offsets, uint32_t const * __restrict__ rec_bin, uint64_t n_records,
+                 uint32_t min_gap, uint32_t max_gap, unsigned long long * __restrict__ per_bin)
+{
+    extern __shared__ uint8_t s_code[]; // codes of positions [t0 - 2, t0 + kDgramTile + max_gap + 3)
+    uint32_t const span = kDgramTile + 2 + max_gap + 3;
+    uint64_t const n_tiles = (n_residues + kDgramTile - 1) / kDgramTile;
+    for (uint64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x)
+    {
+        uint64_t const t0 = tile * kDgramTile;
+        for (uint32_t j = threadIdx.x; j < span; j += kDgramTile)
+        {
+            uint64_t const p = t0 + j; // position + 2
+            s_code[j] = (p >= 2 && p - 2 < n_residues) ? dgram_letter(__ldg(text + p - 2)) : 0xFF;
+        }
+        __syncthreads();
+        uint64_t const p = t0 + threadIdx.x;
+        unsigned long long cnt = 0;
+        uint32_t bin = 0;
+        if (p < n_residues)
+        {
+            // record containing p: largest r with rec_offsets[r] <= p, stepping over empty records that share the offset
+            uint64_t lo = 0, hi = n_records;
+            while (hi - lo > 1)
+            {
+                uint64_t mid = (lo + hi) >> 1;
+                if (__ldg(rec_offsets + mid) <= p)
+                    lo = mid;
+                else
+                    hi = mid;
+            }
+            uint64_t const rec_begin = __ldg(rec_offsets + lo), rec_end = __ldg(rec_offsets + lo + 1);
+            uint64_t const L = rec_end - rec_begin, i = p - rec_begin;
+            uint8_t const * const w = s_code + threadIdx.x; // w[0..2] = residues i-2, i-1, i
+            bin = __ldg(rec_bin + lo);
+            if (L >= static_cast<uint64_t>(min_gap) + 7 && i >= 2 && i + min_gap + 3 < L && w[0] != 0xFF && w[1] != 0xFF &&
+                w[2] != 0xFF)
+            {
+                emplace_sink sink{g, 0, 0, false};
+                if constexpr (!COUNT)
+                    sink.set_bin(bin);
+                uint64_t const left = w[0] * 3200000ULL + w[1] * 160000ULL + w[2] * 8000ULL;
+                for (uint32_t gap = min_gap; gap <= max_gap; ++gap)
+                {
+                    if (i + gap + 3 >= L) // j + 2 >= L with j = i + gap + 1
+                        break;
+                    uint8_t const b1 = w[gap + 3], b2 = w[gap + 4], b3 = w[gap + 5];
+                    if (b1 == 0xFF || b2 == 0xFF || b3 == 0xFF)
+                        continue;
+                    if constexpr (COUNT)
+                        ++cnt;
+                    else
+                        sink(gap * 64000000ULL + left + b1 * 400ULL + b2 * 20ULL + b3);
+                }
+            }
+        }
+        if constexpr (COUNT)
+        {
+            // lanes of a warp nearly always sit in the same record: one atomic per warp then
+            unsigned const active = __activemask();
+            unsigned const same = __match_any_sync(active, bin);
+            if (same == active)
+            {
+                unsigned long long total = cnt;
+                for (int o = 16; o > 0; o >>= 1)
+                    total += __shfl_xor_sync(active, total, o);
+                if ((threadIdx.x & 31) == 0 && total)
+                    atomicAdd(per_bin + bin, total);
+            }
+            else if (cnt)
+                atomicAdd(per_bin + bin, cnt);
+        }
+        __syncthreads();
+    }
+}
+
 // Ordered emission (decompose_record's exact call sequence) for hand-off to HIBF construction and for
 // parity tests of rows a1/a2.  One thread per emitted value; packs its k symbols directly.
 template <int MOL>

@@ -22,6 +22,8 @@ struct handle
     trx_ctx_t * ctx;
     trxh::DeviceIndex index;
     trx_comm_t * comm{nullptr}; // not owned
+    bool augment{false};        // `-a`
+    std::unique_ptr<trxh::DGramIndex> dibf; // `-g`
     explicit handle(trx_ctx_t * c) : ctx(c), index(c) {}
 };
 
@@ -95,6 +97,52 @@ int trxh_preload_text(void * hv, int on)
     return guarded([&] { static_cast<handle *>(hv)->index.preload_all_text(on != 0); });
 }
 
+// `tetrex query -a`: trxh_process_query augments the k-graph (OTFCollector::augment) before the walk
+int trxh_set_augment(void * hv, int on)
+{
+    return guarded([&] { static_cast<handle *>(hv)->augment = on != 0; });
+}
+
+// `tetrex query -g FILE`: load_dindex (include/dGramIndex.h:320-326) onto the handle's device; the collector's gapped items
+// probe it from now on.  NULL or "" detaches.
+int trxh_attach_dgram(void * hv, const char * path)
+{
+    return guarded([&] {
+        auto * h = static_cast<handle *>(hv);
+        h->index.attach_dgram(nullptr);
+        h->dibf.reset();
+        if (!path || !*path)
+            return;
+        auto d = std::make_unique<trxh::DGramIndex>(h->ctx);
+        d->load(path);
+        h->index.attach_dgram(d.get());
+        h->dibf = std::move(d);
+    });
+}
+
+// drive_dindex's work (src/dGramIndex.cpp:35-37) on ctx's device: DGramIndex(min, max, 1, hash_count, fpr, files),
+// populate(), save_dindex(out_path).  The file names are stored as given.  per_bin (nullable, n_files entries) receives
+// dgram_buffer_[b].size().
+int trxh_dindex_build(trx_ctx_t * ctx, const char * const * files, uint64_t n_files, uint64_t min_gap, uint64_t max_gap,
+                      uint32_t hash_count, float fpr, const char * out_path, uint64_t * per_bin)
+{
+    return guarded([&] {
+        trxh::dindex_arguments args;
+        args.min = min_gap;
+        args.max = max_gap;
+        args.hash_count = static_cast<uint8_t>(hash_count);
+        args.fpr = fpr;
+        args.acid_libs.assign(files, files + n_files);
+        trxh::DGramIndex d(ctx);
+        d.build(args);
+        if (per_bin)
+            for (uint64_t b = 0; b < n_files; ++b)
+                per_bin[b] = d.codes_per_bin()[b];
+        if (out_path && *out_path)
+            d.store(out_path);
+    });
+}
+
 // out[0..8) = bin_count, bin_words, is_hibf, is_dna, k, shard_word_begin, shard_words, reduction
 int trxh_info(void * hv, uint64_t out[8])
 {
@@ -122,7 +170,8 @@ int trxh_process_query(void * hv, const char * regex, trxh_alive_fn alive, void 
             hooks.any_alive = [alive, user](uint8_t * a, size_t n) { alive(a, n, user); };
         hooks.comm = static_cast<handle *>(hv)->comm;
         trxh::collect_stats st;
-        trxh::bitvector got = trxh::process_query(regex, ix, &st, (alive || hooks.comm) ? &hooks : nullptr);
+        trxh::bitvector got = trxh::process_query(regex, ix, &st, (alive || hooks.comm) ? &hooks : nullptr,
+                                                   static_cast<handle *>(hv)->augment);
         // run_collection (include/query.h:256-262): the answer is ANDed into a vector of the real bins
         for (uint64_t w = 0; w < got.size(); ++w)
         {

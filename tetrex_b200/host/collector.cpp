@@ -30,7 +30,45 @@ struct item
     uint8_t shift_count;
     uint64_t kmer;
     uint32_t slot;
+    // `-a` (CollectorsItem::gapped_ / res_cache_1 / res_cache_2, otf_collector.h:26-28): the item has just jumped a Gap
+    // node; kmer holds the gapped code under construction and the next three residues complete it
+    bool gapped{false};
+    int res1{0}, res2{0};
 };
+
+// DGramTools::aa_to_num (include/dGramIndex.h:22-59): note X = 20 and the B/J/O/U/Z aliases — not the index side's
+// 20-letter map; anything that is not an upper-case letter is 0
+uint64_t dgram_aa_to_num(int symbol)
+{
+    char const aa = static_cast<char>(symbol);
+    if (aa < 'A' || aa > 'Z')
+        return 0;
+    switch (aa)
+    {
+    case 'A': return 0;
+    case 'C': return 1;
+    case 'D': case 'B': return 2;
+    case 'E': case 'Z': return 3;
+    case 'F': return 4;
+    case 'G': return 5;
+    case 'H': return 6;
+    case 'I': return 7;
+    case 'K': return 8;
+    case 'L': case 'J': return 9;
+    case 'M': return 10;
+    case 'N': return 11;
+    case 'P': return 12;
+    case 'Q': return 13;
+    case 'R': return 14;
+    case 'S': return 15;
+    case 'T': return 16;
+    case 'V': return 17;
+    case 'W': return 18;
+    case 'Y': return 19;
+    case 'X': case 'O': case 'U': return 20;
+    default: return 0;
+    }
+}
 
 struct bucket
 {
@@ -150,6 +188,13 @@ bitvector collect(kgraph const & g, DeviceIndex & index, collect_stats * stats, 
 
     push(0, item{0, 0, start_slot}, true);
 
+    // OTFCollector::dibf_ / has_dibf_: without `-g` the reference hands a default-constructed DGramIndex to the collector,
+    // whose gap bounds are both 0 (include/query.h:258-264, dGramIndex.h:67-68)
+    DGramIndex const * const dibf = index.dgram();
+    uint64_t const dgram_min = dibf ? dibf->min_gap() : 0, dgram_max = dibf ? dibf->max_gap() : 0;
+    std::vector<uint64_t> dgram_codes;
+    std::vector<uint32_t> dgram_slots, dgram_item;
+
     DeviceIndex::collector_scratch & sc = index.scratch();
     std::vector<uint64_t> probe_kmers;
     std::vector<uint32_t> probe_slots, probe_item;
@@ -193,23 +238,75 @@ bitvector collect(kgraph const & g, DeviceIndex & index, collect_stats * stats, 
         }
         else if (sym == Gap)
         {
-            throw error("Gap nodes (-a augmentation) are not part of this build");
+            // gap_procedure (otf_collector.h:290-312)
+            uint64_t const gap = g.gap[node];
+            for (item const & it : b.items)
+            {
+                item nx{0, 0, it.slot};
+                if (!(it.shift_count < 3 || gap < dgram_min || gap > dgram_max))
+                {
+                    // the last three residues as update_kmer packed them (5 bits each), weighted like the index side's
+                    // a1 a2 a3 — the packed codes, not aa_to_num: restated as written
+                    uint64_t const a1 = (it.kmer & 0b111110000000000) >> 10, a2 = (it.kmer & 0b1111100000) >> 5, a3 = it.kmer & 0b11111;
+                    nx.kmer = gap * 64000000ULL + a1 * 3200000ULL + a2 * 160000ULL + a3 * 8000ULL;
+                    nx.gapped = true;
+                }
+                push(g.first[node], nx, true);
+            }
         }
         else
         {
-            // update_path (otf_collector.h:247-279)
+            // update_gapped (otf_collector.h:216-245) for items that have just jumped a Gap node, update_path (:247-279)
+            // for the rest
             probe_kmers.clear();
             probe_slots.clear();
             probe_item.clear();
+            dgram_codes.clear();
+            dgram_slots.clear();
+            dgram_item.clear();
             for (size_t i = 0; i < b.items.size(); ++i)
             {
                 item & it = b.items[i];
+                if (it.gapped)
+                {
+                    if (it.shift_count == 0)
+                    {
+                        it.kmer += 400ULL * dgram_aa_to_num(sym);
+                        it.res1 = sym;
+                        ++it.shift_count;
+                    }
+                    else if (it.shift_count == 1)
+                    {
+                        it.kmer += 20ULL * dgram_aa_to_num(sym);
+                        it.res2 = sym;
+                        ++it.shift_count;
+                    }
+                    else if (it.shift_count == 2)
+                    {
+                        if (dibf) // `if(has_dibf_) path_ &= dibf_->query(dgram)`
+                        {
+                            dgram_codes.push_back(it.kmer + dgram_aa_to_num(sym));
+                            dgram_slots.push_back(it.slot);
+                            dgram_item.push_back(static_cast<uint32_t>(i));
+                        }
+                        it.kmer = 0; // the three residues after the gap start the next k-mer
+                        index.update_kmer(it.res1, it.kmer);
+                        index.update_kmer(it.res2, it.kmer);
+                        index.update_kmer(sym, it.kmer);
+                        ++it.shift_count;
+                        it.gapped = false;
+                        it.res1 = it.res2 = 0;
+                    }
+                    continue;
+                }
                 if (it.shift_count + 1 < k)
                 {
                     index.update_kmer(sym, it.kmer);
                     ++it.shift_count;
                     continue;
                 }
+                if (it.shift_count > k) // k < 3 after a gap: none of update_path's three cases (:251,:256,:268) applies
+                    continue;
                 uint64_t const probe = index.update_kmer(sym, it.kmer);
                 if (it.shift_count + 1 == k)
                     ++it.shift_count;
@@ -249,6 +346,16 @@ bitvector collect(kgraph const & g, DeviceIndex & index, collect_stats * stats, 
                     alive[probe_item[j]] = res[j];
                 if (stats)
                     stats->probes += probe_kmers.size();
+            }
+            if (!dgram_codes.empty())
+            {
+                std::vector<uint8_t> res(dgram_codes.size());
+                check(trx_paths_step(dibf->flat(), pool.paths(), dgram_codes.data(), dgram_slots.data(), dgram_codes.size(),
+                                     res.data()));
+                for (size_t j = 0; j < res.size(); ++j)
+                    alive[dgram_item[j]] = res[j];
+                if (stats)
+                    stats->probes += dgram_codes.size();
             }
             for (size_t i = 0; i < b.items.size(); ++i)
                 if (alive[i]) // `if(top.path_.none()) break;` drops dead paths at once

@@ -136,6 +136,44 @@ ibf_image read_ibf(reader & r)
 
 } // namespace
 
+// DGramIndex::serialize (include/dGramIndex.h:305-309)
+void write_dindex(dgram_image const & img, std::string const & path)
+{
+    writer w(path);
+    w.pod(img.min_gap);
+    w.pod(img.max_gap);
+    w.pod(img.pad);
+    w.pod(img.hash_count);
+    w.pod(img.fpr);
+    w.strs(img.bins);
+    write_ibf(w, img.ibf);
+    w.pod(img.bin_count);
+    w.pod(img.hits_bits); // bit_vector::save: size in bits, then its words
+    w.os.write(reinterpret_cast<char const *>(img.hits_words.data()), static_cast<std::streamsize>(img.hits_words.size() * 8));
+    if (!w.os)
+        throw error("Failed to write " + path);
+}
+
+dgram_image read_dindex(std::string const & path)
+{
+    reader r(path);
+    dgram_image img;
+    img.min_gap = r.pod<uint64_t>();
+    img.max_gap = r.pod<uint64_t>();
+    img.pad = r.pod<uint64_t>();
+    img.hash_count = r.pod<uint8_t>();
+    img.fpr = r.pod<float>();
+    img.bins = r.strs();
+    img.ibf = read_ibf(r);
+    img.bin_count = r.pod<uint64_t>();
+    img.hits_bits = r.pod<uint64_t>();
+    if (img.hits_bits > (1ull << 40))
+        throw archive_error("implausible container size in " + path + " (not a TetRex DGram index?)");
+    img.hits_words.resize((img.hits_bits + 63) / 64);
+    r.raw(img.hits_words.data(), img.hits_words.size() * 8);
+    return img;
+}
+
 void write_index(index_image const & img, std::string const & path)
 {
     writer w(path);

@@ -1,7 +1,8 @@
 // main.cpp — `tetrex` command line (src/main.cpp, include/arg_parse.h): index / query / inspect with the
 // reference's option letters.  Two extra developer sub-commands print intermediate results for the parity tests:
 //   tetrex kgraph [-n] [-r murphy|li] -k K REGEX      postfix string + every node of the k-graph
-//   tetrex bins IDX REGEX                             the candidate bins of process_query, one index per line
+//   tetrex bins [-a] [-g DINDEX] IDX REGEX            the candidate bins of process_query, one index per line
+//   tetrex dindex-rewrite IN OUT                      DGram index file → image → file (host only)
 // Unlike the reference (molecule_/ibf_ are frozen before parsing, so its -n and -i are dead) the
 // flags take effect here.
 #include <cstring>
@@ -140,6 +141,36 @@ int run_query(arg_reader a)
     return 0;
 }
 
+// run_dindex (src/main.cpp:95-109, initialize_dgram_parser include/arg_parse.h:111-123)
+int run_dindex(arg_reader a)
+{
+    dindex_arguments args;
+    std::vector<std::string> positional;
+    try
+    {
+        while (!a.done())
+        {
+            std::string s = a.next("argument");
+            if (is_flag(s, 'l', "lower")) args.min = to_uint(a.next("-l"), "-l");
+            else if (is_flag(s, 'u', "upper")) args.max = to_uint(a.next("-u"), "-u");
+            else if (is_flag(s, 'n', "nucleic_acid") || is_flag(s, 'i', "ibf")) {} // parsed and never read by drive_dindex
+            else if (s.size() > 1 && s[0] == '-') throw error("Unknown option " + s + ".");
+            else positional.push_back(s);
+        }
+        if (positional.size() < 2)
+            throw error("Not enough positional arguments provided (Need at least 2).");
+    }
+    catch (std::exception const & e)
+    {
+        std::cerr << "[Error TetRex Dgram Indexing module " << e.what() << "\n"; // src/main.cpp:105
+        return 0;
+    }
+    args.ofile = positional[0];
+    args.acid_libs.assign(positional.begin() + 1, positional.end());
+    drive_dindex(args);
+    return 0;
+}
+
 int run_kgraph(arg_reader a)
 {
     unsigned k = 3;
@@ -185,7 +216,20 @@ int run_kgraph(arg_reader a)
 
 int run_bins(arg_reader a)
 {
-    std::string idx = a.next("index"), regex = a.next("regex");
+    bool augment = false;
+    std::string dibf_path, idx, regex;
+    std::vector<std::string> positional;
+    while (!a.done())
+    {
+        std::string s = a.next("argument");
+        if (s == "-a" && positional.empty()) augment = true;
+        else if (s == "-g" && positional.empty()) dibf_path = a.next("-g");
+        else positional.push_back(s);
+    }
+    if (positional.size() != 2)
+        throw error("usage: tetrex bins [-a] [-g DINDEX] IDX REGEX");
+    idx = positional[0];
+    regex = positional[1];
     trx_ctx_t * ctx = nullptr;
     check(trx_ctx_create(0, nullptr, &ctx));
     int rc = 0;
@@ -193,8 +237,14 @@ int run_bins(arg_reader a)
     {
         DeviceIndex index(ctx);
         index.load(idx);
+        DGramIndex dibf(ctx);
+        if (!dibf_path.empty())
+        {
+            dibf.load(dibf_path);
+            index.attach_dgram(&dibf);
+        }
         collect_stats st;
-        bitvector v = process_query(regex, index, &st);
+        bitvector v = process_query(regex, index, &st, nullptr, augment);
         for (uint64_t b = 0; b < index.bin_count(); ++b)
             if (v[b / 64] >> (b % 64) & 1)
                 std::cout << b << "\n";
@@ -209,11 +259,23 @@ int run_bins(arg_reader a)
     return rc;
 }
 
+// reads a DGram index file and writes it back (no device involved): the reader/writer round trip of the parity tests
+int run_dindex_rewrite(arg_reader a)
+{
+    std::string in = a.next("input"), out = a.next("output");
+    dgram_image img = read_dindex(in);
+    write_dindex(img, out);
+    std::cout << "min_gap\t" << img.min_gap << "\nmax_gap\t" << img.max_gap << "\nhash_count\t" << static_cast<int>(img.hash_count)
+              << "\nfpr\t" << img.fpr << "\nbins\t" << img.bin_count << "\nbin_size\t" << img.ibf.bin_size << "\n";
+    return 0;
+}
+
 void usage()
 {
     std::cerr << "tetrex - regular expression search over (H)IBF-indexed sequence libraries (B200 build)\n"
                  "  tetrex index [-k K] [-p FPR] [-c HASHES] [-n] [-i] [-r murphy|li] OUT LIB...\n"
-                 "  tetrex query [-v] [-f] [-o FILE] IDX REGEX\n"
+                 "  tetrex query [-v] [-f] [-c] [-a] [-g DINDEX] [-o FILE] IDX REGEX\n"
+                 "  tetrex dindex [-l LOWER] [-u UPPER] OUT LIB...\n"
                  "  tetrex inspect IDX\n";
 }
 
@@ -244,7 +306,9 @@ int main(int argc, char ** argv)
         }
         if (cmd == "kgraph") return run_kgraph(a);
         if (cmd == "bins") return run_bins(a);
-        if (cmd == "model" || cmd == "dindex")
+        if (cmd == "dindex-rewrite") return run_dindex_rewrite(a);
+        if (cmd == "dindex") return run_dindex(a);
+        if (cmd == "model")
         {
             std::cerr << "[Error] sub-command '" << cmd << "' is outside this build (DESIGN.md, out of scope)\n";
             return 1;

@@ -349,7 +349,7 @@ void run_conjunction(query_arguments & args, DeviceIndex & index)
     {
         for (std::string const & q : queries)
         {
-            bitvector got = process_query(q, index);
+            bitvector got = process_query(q, index, nullptr, nullptr, args.augment);
             for (size_t w = 0; w < hit_vector.size(); ++w)
                 hit_vector[w] &= got[w];
         }
@@ -379,7 +379,7 @@ void run_conjunction(query_arguments & args, DeviceIndex & index)
 // motif has its own k-graph and candidate bins), the verify phase ONCE for all of them — pattern i over its own candidate
 // bins, every tile of the union read once per 128 patterns.  Same files (<id>.tsv), same lines, same stderr fields as the
 // loop over run_collection; "Query Time" is the motif's filter time plus its share of the shared verify.
-void run_motif_batch(std::vector<std::pair<std::string, std::string>> const & motifs, DeviceIndex & index)
+void run_motif_batch(std::vector<std::pair<std::string, std::string>> const & motifs, DeviceIndex & index, bool augment)
 {
     size_t const n = motifs.size();
     uint64_t const words = (index.acid_libs().size() + 63) / 64;
@@ -397,7 +397,7 @@ void run_motif_batch(std::vector<std::pair<std::string, std::string>> const & mo
             bitvector hit_vector(index.bin_words(), 0);
             for (uint64_t b = 0; b < index.bin_count(); ++b)
                 hit_vector[b / 64] |= 1ull << (b % 64);
-            bitvector got = process_query(motifs[i].second, index);
+            bitvector got = process_query(motifs[i].second, index, nullptr, nullptr, augment);
             for (size_t w = 0; w < hit_vector.size(); ++w)
                 hit_vector[w] &= got[w];
             bin_count[i] = popcount(hit_vector);
@@ -471,7 +471,7 @@ void run_collection(query_arguments & args, bool read_file, DeviceIndex & index)
         hit_vector[b / 64] |= 1ull << (b % 64);
     if (index.bin_count() > 1)
     {
-        bitvector got = process_query(args.regex, index);
+        bitvector got = process_query(args.regex, index, nullptr, nullptr, args.augment);
         for (size_t w = 0; w < hit_vector.size(); ++w)
             hit_vector[w] &= got[w];
     }
@@ -505,9 +505,8 @@ void drive_query(query_arguments & args)
 {
     if (args.regex == "-")
         std::cin >> args.regex; // src/query.cpp:479
-    if (args.augment || args.draw || args.dibf != "-")
-        throw error("-a / -d / -g (augmentation, graph drawing, DGram index) are outside this build: "
-                    "see DESIGN.md \"out of scope\"");
+    if (args.draw)
+        throw error("-d (graph drawing) is outside this build: see DESIGN.md \"out of scope\"");
     {
         // load_params comes first in the reference too (src/query.cpp:480-481): an unreadable file is reported before
         // anything else happens
@@ -522,6 +521,14 @@ void drive_query(query_arguments & args)
     {
         DeviceIndex index(ctx);
         index.load(args.idx);
+        // run_collection loads the DGram index named by -g (include/query.h:258-264); run_conjunction only would if
+        // has_dibf were already set, which nothing does (:300-301) — so `-c` walks with the gap bounds 0..0 and no filter
+        DGramIndex dibf(ctx);
+        if (args.dibf != "-" && args.conjunction == "-")
+        {
+            dibf.load(args.dibf);
+            index.attach_dgram(&dibf);
+        }
         if (args.read_file != "-")
         {
             // read_regex_from_file + run_multiple_queries (src/query.cpp:372-395, include/query.h:330-340):
@@ -544,7 +551,7 @@ void drive_query(query_arguments & args)
             // Peptide indexes without alphabet reduction verify the whole file of motifs in shared passes over the text
             // (K4 multi-pattern scan); everything else (DNA: two strands; reduced alphabets: mapped text) one by one.
             if (!index.is_dna() && index.reduction() == 0 && index.bin_count() > 1 && motifs.size() > 1)
-                run_motif_batch(motifs, index);
+                run_motif_batch(motifs, index, args.augment);
             else
                 for (auto const & [id, motif] : motifs)
                 {

@@ -49,6 +49,18 @@ struct index_arguments
     std::vector<std::string> acid_libs;
 };
 
+// include/arg_parse.h:95-123 (`tetrex dindex`): -l / -u bound the gap; hash count, fpr and pad have no option letter
+struct dindex_arguments
+{
+    size_t min = 3;
+    size_t max = 21;
+    size_t pad = 1;
+    uint8_t hash_count = 3;
+    float fpr = 0.05f;
+    std::string ofile;
+    std::vector<std::string> acid_libs;
+};
+
 struct query_arguments
 {
     uint8_t t = 1;
@@ -99,6 +111,22 @@ struct index_image
     ibf_image flat;
     hibf_image hibf;
 };
+
+// DGramIndex as it lies on disk (include/dGramIndex.h:305-309): archive(min_gap_, max_gap_, pad_, hc_, fpr_, bins_, dibf_,
+// bc_, hits_)
+struct dgram_image
+{
+    uint64_t min_gap{}, max_gap{}, pad{};
+    uint8_t hash_count{};
+    float fpr{};
+    std::vector<std::string> bins; // one FASTA file per bin
+    ibf_image ibf;
+    uint64_t bin_count{1};
+    uint64_t hits_bits{};             // hits_: bitvector(bc_, true) as it was when the index was saved
+    std::vector<uint64_t> hits_words;
+};
+void write_dindex(dgram_image const & img, std::string const & path);
+dgram_image read_dindex(std::string const & path);
 
 void write_index(index_image const & img, std::string const & path);
 index_image read_index(std::string const & path);
@@ -158,6 +186,35 @@ struct kgraph
 };
 // reduced = true → construct_reduced_kgraph (src/construct_reduced_nfa.cpp), used when the index alphabet is reduced
 kgraph construct_kgraph(std::string const & postfix, uint8_t k, bool reduced = false);
+
+// ----------------------------------------------------------------------------------------- DGram index
+// DGramIndex (include/dGramIndex.h:64-310) with its filter in HBM: gapped 3+3-mers "abc, gap g, def" of every record, one
+// bin per FASTA file.  build() = constructor + populate(): two launches over the residues (count per bin → size the
+// filter like compute_bitcount → emplace); the collector probes it from gapped items when it is attached to an index.
+class DGramIndex
+{
+public:
+    explicit DGramIndex(trx_ctx_t * ctx) : ctx_(ctx) {}
+    ~DGramIndex();
+    DGramIndex(DGramIndex const &) = delete;
+    DGramIndex & operator=(DGramIndex const &) = delete;
+    void build(dindex_arguments const & args);
+    void store(std::string const & path) const; // save_dindex (:312-318)
+    void load(std::string const & path);        // load_dindex (:320-326) + upload
+    uint64_t min_gap() const { return img_.min_gap; }
+    uint64_t max_gap() const { return img_.max_gap; }
+    uint64_t bin_count() const { return img_.bin_count; }
+    dgram_image const & image() const { return img_; }
+    std::vector<uint64_t> const & codes_per_bin() const { return codes_per_bin_; } // dgram_buffer_[b].size(), after build()
+    trx_ibf_t * flat() const { return flat_; }
+
+private:
+    trx_ctx_t * ctx_;
+    dgram_image img_;
+    trx_ibf_t * flat_{nullptr};
+    std::vector<uint64_t> codes_per_bin_;
+};
+void drive_dindex(dindex_arguments const & args); // src/dGramIndex.cpp:19-38
 
 // ------------------------------------------------------------------------------------------------ index
 // TetrexIndex<flavor, molecule> with its bit matrix in HBM.
@@ -233,6 +290,10 @@ public:
     };
     collector_scratch & scratch() { return scratch_; }
 
+    // `-g`: the DGram index the collector's gapped items probe (OTFCollector::dibf_ / has_dibf_).  Not owned.
+    void attach_dgram(DGramIndex const * d);
+    DGramIndex const * dgram() const { return dgram_; }
+
 private:
     void upload();
     void init_maps();
@@ -246,6 +307,7 @@ private:
     bool preload_all_{false};
     std::unique_ptr<text_store> text_;
     collector_scratch scratch_;
+    DGramIndex const * dgram_{nullptr};
 };
 
 // ------------------------------------------------------------------------------------------ query path

@@ -50,6 +50,10 @@ def host_lib():
         h.trxh_free.restype = None
         h.trxh_attach_comm.argtypes = [vp, vp]
         h.trxh_preload_text.argtypes = [vp, C.c_int]
+        h.trxh_set_augment.argtypes = [vp, C.c_int]
+        h.trxh_attach_dgram.argtypes = [vp, C.c_char_p]
+        h.trxh_dindex_build.argtypes = [vp, C.POINTER(C.c_char_p), C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint32, C.c_float,
+                                        C.c_char_p, u64p]
         _host = h
     return _host
 
@@ -57,6 +61,16 @@ def host_lib():
 def _check(rc):
     if rc != 0:
         raise HostError(host_lib().trxh_last_error().decode(errors="replace"))
+
+
+def dindex_build(ctx, files, min_gap: int = 3, max_gap: int = 21, hash_count: int = 3, fpr: float = 0.05,
+                 out_path: str | None = None) -> np.ndarray:
+    """`tetrex dindex` (src/dGramIndex.cpp:19-38) on ctx's device; returns the gapped codes each bin contributed."""
+    arr = (C.c_char_p * len(files))(*[os.fsencode(f) for f in files])
+    per_bin = np.zeros(len(files), dtype=np.uint64)
+    _check(host_lib().trxh_dindex_build(ctx._h, arr, len(files), min_gap, max_gap, hash_count, fpr,
+                                        os.fsencode(out_path) if out_path else None, per_bin.ctypes.data_as(C.POINTER(C.c_uint64))))
+    return per_bin
 
 
 class ShardedIndex:
@@ -90,6 +104,14 @@ class ShardedIndex:
             a[:] = self._any_alive(a)
 
         self._cb = _ALIVE_FN(_cb)  # must outlive every call
+
+    def set_augment(self, on: bool = True):
+        """`tetrex query -a`: high-complexity stretches of the k-graph become Gap nodes before the walk."""
+        _check(host_lib().trxh_set_augment(self._h, 1 if on else 0))
+
+    def attach_dgram(self, path: str | None):
+        """`tetrex query -g FILE`: the DGram index the gapped items probe (None detaches)."""
+        _check(host_lib().trxh_attach_dgram(self._h, os.fsencode(path) if path else None))
 
     def close(self):
         if self._h:
