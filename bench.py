@@ -216,6 +216,19 @@ def run_ours(args):
     barrier()
     e2e_value = sum_over_ranks(float(args.batch * e_steps)) / (e_ms / 1e3)
     assert int(out_np.view(np.int64).sum()) == checksum_dev, "host-buffer path and device path disagree"
+    # what bounds that number: the 128-byte row per k-mer going back over PCIe.  A plain pinned device→host copy of the
+    # same result buffer, timed the same way, is the ceiling of any host-buffer API that returns whole bitvectors.
+    pin_out.copy_(d_out, non_blocking=True)
+    torch.cuda.synchronize()
+    tw = time.perf_counter()
+    for _ in range(3):
+        pin_out.copy_(d_out, non_blocking=True)
+    torch.cuda.synchronize()
+    d2h_gbs = 3 * args.batch * W * 8 / (time.perf_counter() - tw) / 1e9
+    e2e_pcie = {"bound": "pcie d2h", "achieved": args.batch * W * 8 / (e_ms / e_steps / 1e3) / 1e9, "peak": d2h_gbs, "unit": "GB/s",
+                "frac": args.batch * W * 8 / (e_ms / e_steps / 1e3) / 1e9 / d2h_gbs,
+                "note": "result bytes of one step / its wall time, against a plain pinned cudaMemcpy D2H of the same buffer "
+                        "measured in this run (per rank)"}
 
     # ---------------- end to end the way the collector uses the device (OTFCollector::update_path, include/otf_collector.h:
     # 247-279): k-mers and their path slots go in from pinned host memory, the hit vectors are ANDed into HBM-resident
@@ -309,6 +322,7 @@ def run_ours(args):
                     "d2h_bytes_per_step": args.batch * W * 8, "steps": e_steps},
             "gpu_launches": int(launches), "clocks": clocks,
         }
+        line["e2e"]["roofline"] = e2e_pcie
         if collector_e2e is not None:
             line["e2e"]["collector_step"] = collector_e2e
         if flat_c4 is not None:
@@ -392,7 +406,7 @@ def host_path_queries(t, ctx, residues, offs, rec_bin, reps=100, on_index=None):
                          "iter_disk_search_us": (t2 - t1) / reps * 1e6, "candidate_bins": int(np.bitwise_count(words).sum()),
                          "lines": lines, "collector": st, "index_build_s_incl_process_start_and_fasta_parse": round(build_s, 2)}
             if on_index is not None:
-                on_index(name, ix)
+                on_index(name, ix, files, d)
             ix.close()
         res["query"] = QUERY
         return res
@@ -631,9 +645,13 @@ def extra_measurements(t, ctx, torch, residues, offs, rec_bin, planted, hibf, pe
         import bench_configs as bc
         c3 = {}
 
-        def on_index(name, ix):
+        def on_index(name, ix, files, workdir):
             if name == "flat":
-                c3["pattern_batch_filter_and_verify"] = bc.measure_c3_patterns(ix, pats, lambda p: pattern_hits[p])
+                c3["pattern_batch_filter_and_verify"] = bc.measure_c3_patterns(ix, pats, lambda p: pattern_hits[p], budget_s=30.0)
+                # the same batch the way SURVEY.md Appendix B says config 3 is meant to run: `-a` (high-fan-out stretches
+                # become Gap nodes) with a DGram index built on the device (`tetrex dindex`, gaps 3..21) as `-g`
+                c3["pattern_batch_augmented"] = bc.measure_c3_augmented(t, ctx, ix, files, workdir, pats,
+                                                                         lambda p: pattern_hits[p])
         out["host_path_queries"] = host_path_queries(t, ctx, residues, offs, rec_bin, on_index=on_index)
         out["C3"] = c3
     except Exception as e:  # never lose the bench line over a side measurement
@@ -678,6 +696,31 @@ def extra_measurements(t, ctx, torch, residues, offs, rec_bin, planted, hibf, pe
     except Exception as e:
         c3["cpu_baseline"] = {"error": f"{type(e).__name__}: {e}"[:200]}
     flat.close()
+    del q, o
+    # ---- DGram index build on the device (`tetrex dindex`, include/dGramIndex.h:103-154,194-243): gaps 3..21 over the
+    # same residues — count per bin, size like compute_bitcount, emplace every gapped 3+3-mer code
+    try:
+        import ctypes as C
+        from tetrex_b200._abi import check
+        d_cnt = torch.zeros(N_BINS, dtype=torch.int64, device="cuda")
+        lo, hi = 3, 21
+        cnt_s = timed(lambda: check(t.lib().trx_dgram_count_dev(ctx._h, d_res.data_ptr(), len(residues), d_offs.data_ptr(),
+                                                                 d_bin.data_ptr(), len(rec_bin), lo, hi, N_BINS, d_cnt.data_ptr())), 3)
+        codes = int(d_cnt.sum().item())
+        dsize = t.compute_bitcount(int(d_cnt.max().item()), FPR)
+        dflat = t.IBF(ctx, N_BINS, dsize, HASH_FUNS)
+        emp_s = timed(lambda: check(t.lib().trx_dgram_emplace_dev(dflat._h, d_res.data_ptr(), len(residues), d_offs.data_ptr(),
+                                                                   d_bin.data_ptr(), len(rec_bin), lo, hi)), 2)
+        algo = codes * (HASH_FUNS * 64) + len(residues)
+        c3["dgram_build"] = {"gaps": [lo, hi], "codes": codes, "matrix_gb": dflat.n_words * 8 / 1e9,
+                             "count_ms": cnt_s * 1e3, "emplace_ms": emp_s * 1e3, "codes_per_s": codes / emp_s,
+                             "roofline": {"bound": "hbm", "achieved": algo / emp_s / 1e9, "peak": peak, "unit": "GB/s",
+                                          "frac": algo / emp_s / 1e9 / peak, "traffic": None, "kernel": "dgram_kernel<false>",
+                                          "note": "h x 64 B per code (32 B sector fill + write-back per atomicOr into a "
+                                                  "matrix >> L2, the K1 figure of SURVEY 8(d)) + 1 B per residue"}}
+        dflat.close()
+    except Exception as e:
+        c3["dgram_build"] = {"error": f"{type(e).__name__}: {e}"[:200]}
     return out
 
 

@@ -392,6 +392,36 @@ def measure_c3_patterns(ix, patterns, scan_all_bins, budget_s=40.0):
                     "on the candidate bins only, one pattern at a time"}
 
 
+def measure_c3_augmented(t, ctx, ix, files, workdir, patterns, scan_all_bins, budget_s=30.0):
+    """Config 3's filter phase with `-a -g`: DGramIndex built by this repo on the device over the same 1024 files, then the
+    pattern batch again with augmentation.  Reports the build (codes/s through count + emplace, file written) and the
+    batch; the comparison with the plain leg is in refused patterns and filter time per query."""
+    import os
+    from tetrex_b200 import sharded
+    path = os.path.join(workdir, "c3.dibf")
+    t0 = time.perf_counter()
+    per_bin = sharded.dindex_build(ctx, files, 3, 21, 3, 0.05, path)
+    build_s = time.perf_counter() - t0
+    out = {"dgram_index": {"gaps": [3, 21], "codes": int(per_bin.sum()), "largest_bin_codes": int(per_bin.max()),
+                           "file_gb": os.path.getsize(path) / 1e9,
+                           "build_s_incl_fasta_parse_download_and_file_write": round(build_s, 2)}}
+    ix.set_augment(True)
+    res_no = measure_c3_patterns(ix, patterns, scan_all_bins, budget_s=budget_s / 2)
+    t0 = time.perf_counter()
+    ix.attach_dgram(path)
+    out["dgram_index"]["load_s"] = round(time.perf_counter() - t0, 2)
+    res_g = measure_c3_patterns(ix, patterns, scan_all_bins, budget_s=budget_s / 2)
+    ix.attach_dgram(None)
+    ix.set_augment(False)
+    for r in (res_no, res_g):
+        r["what"] = "the same with tetrex query -a: OTFCollector::augment before the walk"
+    res_g["what"] += ", DGram index attached (-g)"
+    out["augment_only"] = res_no
+    out["augment_with_dgram"] = res_g
+    os.unlink(path)
+    return out
+
+
 def cpu_baseline_flat_probe(bins, bin_size, h, kmers):
     """The reference's bulk_contains on a flat IBF of the config's shape, all cores and one core."""
     from oracle import bindings as ob

@@ -255,6 +255,16 @@ int trx_regex_positions(const trx_regex_t *re);
  * match of re in text[0, len), -1 if none.  RE2::Set::Match lists the rules of a set in the order in which their first
  * matches complete; verify_fasta_set prints them in that order. */
 int64_t trx_regex_first_match_end(const trx_regex_t *re, const uint8_t *text, uint64_t len);
+/* Host only (tests): the determinised matcher phase 2 uses for POSIX leftmost-longest patterns whose subset automaton stays
+ * small (FindAndConsume's anchored step, lib/re2/re2/re2.h:668-669).  info[0..3) = states, byte classes, first accepting
+ * state; returns 0 if the pattern has no such matcher (leftmost-first, or too many subsets).  trx_regex_dfa_match_end:
+ * end (exclusive) of the longest match that STARTS at text[start], -1 if none, -2 if there is no DFA.
+ * trx_regex_dfa_starts: the reverse searcher phase 1 uses for patterns without a selective necessary factor (bounded match
+ * length, no anchors), run over text[0, len) as one record: starts[p] = 1 iff some match starts at p; returns the longest
+ * possible match length, 0 if the pattern has no such searcher. */
+int trx_regex_dfa_info(trx_regex_t *re, uint32_t info[3]);
+uint32_t trx_regex_dfa_starts(trx_regex_t *re, const uint8_t *text, uint64_t len, uint8_t *starts);
+int64_t trx_regex_dfa_match_end(trx_regex_t *re, const uint8_t *text, uint64_t len, uint64_t start);
 
 typedef struct trx_hit {
     uint32_t bin;

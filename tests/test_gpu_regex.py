@@ -96,6 +96,35 @@ def test_regex_staging_variants_agree(ctx, monkeypatch):
     txt.close()
 
 
+def test_dfa_matcher_equals_position_automaton(ctx, monkeypatch):
+    """Phase 2 resolves POSIX patterns with a determinised matcher (TRX_REGEX_DFA=off: the position automaton), and patterns
+    without any necessary factor skip phase 1 when they have one: same hits either way and equal to RE2 / the Python
+    restatement, including a pattern dense enough for the device-side hit formatting (> 1024 hits)."""
+    rng = random.Random(77)
+    aa = b"ACDEFGHIKLMNPQRSTVWY"
+    seqs = [bytes(rng.choice(aa) for _ in range(L)) for L in [30000, 127, 128, 5, 0, 90000, 129, 4000, 1, 2, 3, 700]]
+    rec_bin = [0, 0, 1, 1, 2, 3, 3, 4, 4, 4, 5, 5]
+    txt = build_text(ctx, seqs, rec_bin, 6)
+    finder = ob.ref_find_all if ob.have_ref() else ob.find_all_python
+    cand_some = np.zeros(1, dtype=np.uint64)
+    cand_some[0] = 0b101010
+    for pat in ["...[GHKM]V[FHKL].", "[ST].[RK]", ".[ACDEL]D.{2,4}.[AEGQT]S", "L.A.G", "[LI]MAQ", "AQGL+YN", "^..[DE]", "[KR]{2,3}$",
+                "C.{2,4}C.{3}[LIVMFYWC]", "(LMAQ|GL.N|W{2})"]:
+        rx = t.Regex(pat, True)
+        a = txt.scan(rx, cap=1 << 20)
+        a_some = txt.scan(rx, candidate_bins=cand_some, cap=1 << 20)
+        monkeypatch.setenv("TRX_REGEX_DFA", "off")
+        b = txt.scan(rx, cap=1 << 20)
+        monkeypatch.delenv("TRX_REGEX_DFA")
+        want = expected_hits(seqs, rec_bin, pat, True, finder)
+        assert np.array_equal(a, want), pat
+        assert np.array_equal(b, want), pat
+        assert np.array_equal(a_some, expected_hits(seqs, rec_bin, pat, True, finder, cand={1, 3, 5})), pat
+    dense = txt.scan(t.Regex("[ST].[RK]", True), cap=1 << 20)
+    assert len(dense) > 1024
+    txt.close()
+
+
 def test_factor_filter_equals_exact_automaton(ctx, monkeypatch):
     """Phase 1 has two variants (SIMD necessary-factor filter / exact automaton); both must lead to the same hits."""
     rng = random.Random(12)

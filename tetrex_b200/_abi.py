@@ -86,6 +86,9 @@ PROTOTYPES = {
     "trx_regex_compile": (C.c_int, [C.c_char_p, C.c_int, vpp]),
     "trx_regex_destroy": (None, [vp]),
     "trx_regex_positions": (C.c_int, [vp]),
+    "trx_regex_dfa_info": (C.c_int, [vp, vp]),
+    "trx_regex_dfa_starts": (C.c_uint32, [vp, vp, C.c_uint64, vp]),
+    "trx_regex_dfa_match_end": (C.c_int64, [vp, vp, C.c_uint64, C.c_uint64]),
     "trx_regex_first_match_end": (C.c_int64, [vp, vp, C.c_uint64]),
     "trx_regex_scan": (C.c_int, [vp, vp, vp, C.c_int, vp, vp, C.c_uint64, u64p, u64p]),
     "trx_regex_scan_begin": (C.c_int, [vp, vp, vp, C.c_int, vp, C.c_uint64, C.POINTER(C.c_int)]),

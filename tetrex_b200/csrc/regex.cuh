@@ -29,6 +29,30 @@ struct regex_masks
 
 } // namespace trx
 
+namespace trx
+{
+// Subset automaton of the anchored (no re-injection) position automaton as one scan sees it (byte maps folded in):
+// state 0 = dead, 1 = before the first byte, accepting states last.  usable = false: too many subsets, or the pattern
+// is not POSIX leftmost-longest (leftmost-first needs thread priorities, which a DFA state does not carry).
+struct dfa_table
+{
+    bool usable{false};
+    uint32_t n_states{0}, n_classes{0}, first_accept{0};
+    uint8_t cls[256]{};
+    std::vector<uint16_t> trans; // n_states x n_classes
+    // Reverse searcher over the same classes: read the text BACKWARDS with a new match end injected at every byte
+    // (state 0 = nothing live); a state >= r_first_accept after consuming text[p] means "some match starts at p".
+    // Only for patterns whose matches have a bounded length (max_len; no '*' / '+') and no anchors: a scan of one 128-byte
+    // chunk warms up on the max_len - 1 bytes that follow it.
+    bool r_usable{false};
+    uint32_t r_states{0}, r_first_accept{0}, max_len{0};
+    std::vector<uint16_t> r_trans; // r_states x n_classes
+    // key of the cache below
+    int reverse{0};
+    uint64_t map_hash{0};
+};
+} // namespace trx
+
 struct trx_regex
 {
     int positions{0};
@@ -43,4 +67,7 @@ struct trx_regex
     std::vector<uint8_t> follow_list;
     std::string pattern;
     uint64_t serial{0}; // unique per compiled regex: key of the per-text filter-plan cache
+    // determinised matchers built on first use, one per (strand, byte map) this regex was scanned with; a handle is used
+    // by one host thread at a time (like every handle of this library)
+    std::vector<trx::dfa_table> dfas;
 };

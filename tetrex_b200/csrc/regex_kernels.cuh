@@ -491,6 +491,16 @@ struct resolve_params
     uint32_t * hit_pats;
     uint32_t pattern_id;
     uint32_t rec_cap;
+    // Determinised anchored matcher (POSIX leftmost-longest patterns whose subset automaton stays small): state 0 = dead,
+    // state 1 = before the first byte, states >= dfa_first_accept hold an accepting position.  The device copy of the table
+    // holds states PRE-MULTIPLIED by dfa_classes: next = trans[state * dfa_classes + cls[byte]] is again such a product.
+    // nullptr = simulate the position automaton (match_longest / match_first).
+    uint16_t const * dfa_trans;
+    uint8_t const * dfa_cls; // 256 bytes
+    uint32_t dfa_classes;
+    uint32_t dfa_states;
+    uint32_t dfa_first_accept;
+    uint32_t anchor_begin, anchor_end; // copies of the automaton's flags: the DFA route never stages regex_dev
 };
 
 // Anchored leftmost-longest match starting at position s of a record read through `at`: the automaton
@@ -596,16 +606,55 @@ __device__ int64_t match_first(regex_dev const & re, At at, int64_t s, int64_t L
     return best;
 }
 
+// The same anchored leftmost-longest match on the determinised automaton: one table lookup per byte instead of a loop over
+// the live positions.  Semantics are match_longest's: the last position at which an accepting state was live wins.
+template <class At>
+__device__ __forceinline__ int64_t match_longest_dfa(resolve_params const & p, uint16_t const * trans, uint8_t const * s_cls, At at,
+                                                     int64_t s, int64_t L)
+{
+    uint32_t const ncls = p.dfa_classes, accept_from = p.dfa_first_accept * ncls; // the table holds next_state * classes
+    uint32_t st = ncls;
+    int64_t best = -1;
+    for (int64_t pos = s; pos < L;)
+    {
+        st = trans[st + s_cls[at(pos)]];
+        if (st == 0)
+            break;
+        ++pos;
+        if (st >= accept_from && (!p.anchor_end || pos == L))
+            best = pos;
+    }
+    return best;
+}
+
 // One WARP per record that phase 1 listed (the list length is read from device memory, so no host round trip
 // separates the two phases).  The 32 lanes try 32 consecutive start positions at once — almost all die on the
 // first byte — and a ballot picks the leftmost start that really matches; the warp then jumps to the end of
 // that match (FindAndConsume) and goes on.  Chunks phase 1 did not flag are skipped whole.
 template <int W, int DIR>
-__device__ __forceinline__ void phase2_body(resolve_params const & p, regex_dev & s_re)
+__device__ __forceinline__ void phase2_body(resolve_params const & p, regex_dev & s_re, uint8_t * s_cls)
 {
     // usually a handful of records are listed: CTAs without work leave before staging anything
     if (static_cast<uint64_t>(blockIdx.x) * (blockDim.x >> 5) >= *p.rec_count)
         return;
+    bool const dfa = p.dfa_trans != nullptr;
+    uint16_t const * trans = p.dfa_trans;
+    if (dfa)
+    {
+        for (unsigned i = threadIdx.x; i < 256; i += blockDim.x)
+            s_cls[i] = p.dfa_cls[i];
+        // the table of a typical pattern is a few KB (config 3: <= 2.1 KB): it takes the shared memory the automaton image
+        // would have used; larger ones are read through L1
+        unsigned const entries = p.dfa_states * p.dfa_classes;
+        if (entries * 2 <= sizeof(regex_dev))
+        {
+            uint16_t * dst = reinterpret_cast<uint16_t *>(&s_re);
+            for (unsigned i = threadIdx.x; i < entries; i += blockDim.x)
+                dst[i] = p.dfa_trans[i];
+            trans = dst;
+        }
+    }
+    else
     {
         uint32_t const * src = reinterpret_cast<uint32_t const *>(p.re);
         uint32_t * dst = reinterpret_cast<uint32_t *>(&s_re);
@@ -614,6 +663,7 @@ __device__ __forceinline__ void phase2_body(resolve_params const & p, regex_dev 
     }
     __syncthreads();
     regex_dev const & re = s_re;
+    bool const anchor_begin = p.anchor_begin != 0;
     unsigned const lane = threadIdx.x & 31;
     uint64_t n_listed = *p.rec_count;
     if (p.rec_cap && n_listed > p.rec_cap)
@@ -637,7 +687,7 @@ __device__ __forceinline__ void phase2_body(resolve_params const & p, regex_dev 
             // first position (reading direction) that lies in the next chunk
             int64_t const next_chunk = DIR > 0 ? static_cast<int64_t>((ch + 1) * kChunkBytes - rb)
                                                : static_cast<int64_t>(re_off) - static_cast<int64_t>(ch * kChunkBytes);
-            if (!re.anchor_begin && p.chunk_flags && !((p.chunk_flags[ch >> 5] >> (ch & 31)) & 1))
+            if (!anchor_begin && p.chunk_flags && !((p.chunk_flags[ch >> 5] >> (ch & 31)) & 1))
             {
                 s = next_chunk; // no match starts anywhere in this chunk
                 continue;
@@ -645,15 +695,20 @@ __device__ __forceinline__ void phase2_body(resolve_params const & p, regex_dev 
             int64_t const limit = next_chunk < L ? next_chunk : L;
             int64_t const my_s = s + lane;
             int64_t e = -1;
-            if (my_s < limit && (!re.anchor_begin || lane == 0))
+            if (my_s < limit && (!anchor_begin || lane == 0))
             {
-                uint8_t const c = at(my_s);
-                uint64_t quick = 0;
+                if (dfa)
+                    e = match_longest_dfa(p, trans, s_cls, at, my_s, L);
+                else
+                {
+                    uint8_t const c = at(my_s);
+                    uint64_t quick = 0;
 #pragma unroll
-                for (int k = 0; k < W; ++k)
-                    quick |= re.first[k] & re.B[c][k];
-                if (quick)
-                    e = re.posix_longest ? match_longest<W>(re, at, my_s, L) : match_first(re, at, my_s, L);
+                    for (int k = 0; k < W; ++k)
+                        quick |= re.first[k] & re.B[c][k];
+                    if (quick)
+                        e = re.posix_longest ? match_longest<W>(re, at, my_s, L) : match_first(re, at, my_s, L);
+                }
             }
             unsigned const found = __ballot_sync(0xffffffffu, e > my_s);
             if (found)
@@ -688,7 +743,7 @@ __device__ __forceinline__ void phase2_body(resolve_params const & p, regex_dev 
             }
             else
             {
-                if (re.anchor_begin)
+                if (anchor_begin)
                     break; // '^' can only match at the resume point
                 s = (s + 32 < limit) ? s + 32 : limit;
             }
@@ -696,11 +751,212 @@ __device__ __forceinline__ void phase2_body(resolve_params const & p, regex_dev 
     }
 }
 
+// The DFA route of phase 2, written for instruction count (it is issue-bound: ~1 G table steps per 204 M start positions):
+// the lanes of a warp try 32 consecutive starts, so the warp first turns the 48 bytes those starts can see in their first
+// 16 steps into byte classes in a warp-private shared-memory window (every text byte is loaded and classified once, not
+// once per lane and step), each lane pulls its 16 classes into registers with aligned word loads + funnel shifts, and a
+// step is then: add the class to the (pre-multiplied) state, one shared-memory load, two compares.  The table holds
+// next_state * classes, so there is no multiply on the chain; positions are 32-bit offsets into the record; the warp
+// leaves the unrolled walk as soon as no lane is alive.  Walks that outlive 16 steps continue byte by byte.
+template <int DIR, bool ANCHOR_END>
+__device__ __forceinline__ void phase2_dfa_body(resolve_params const & p, uint16_t const * __restrict__ trans,
+                                                uint8_t const * __restrict__ s_cls, uint32_t * __restrict__ win)
+{
+    unsigned const lane = threadIdx.x & 31;
+    bool const anchor_begin = p.anchor_begin != 0;
+    uint32_t const ncls = p.dfa_classes, accept_from = p.dfa_first_accept * ncls; // states are stored pre-multiplied
+    uint64_t n_listed = *p.rec_count;
+    if (p.rec_cap && n_listed > p.rec_cap)
+        n_listed = p.rec_cap;
+    uint64_t const warp0 = (static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+    uint64_t const n_warps = (static_cast<uint64_t>(gridDim.x) * blockDim.x) >> 5;
+    uint8_t * const win8 = reinterpret_cast<uint8_t *>(win);
+    unsigned const w0 = lane >> 2, sh = (lane & 3) * 8;
+    for (uint64_t i = warp0; i < n_listed; i += n_warps)
+    {
+        uint64_t const r = p.rec_list[i];
+        uint64_t const rb = p.rec_offsets[r], re_off = p.rec_offsets[r + 1];
+        uint32_t const L = static_cast<uint32_t>(re_off - rb);
+        uint8_t const * const base = DIR > 0 ? p.text + rb : p.text + re_off - 1;
+        auto at = [&](uint32_t pos) -> uint8_t { return DIR > 0 ? __ldg(base + pos) : __ldg(base - pos); };
+        uint32_t s = 0; // warp-uniform
+        while (s < L)
+        {
+            uint32_t limit = L;
+            if (p.chunk_flags)
+            {
+                uint64_t const ch = (DIR > 0 ? rb + s : re_off - 1 - s) / kChunkBytes;
+                uint32_t const next_chunk = DIR > 0 ? static_cast<uint32_t>((ch + 1) * kChunkBytes - rb)
+                                                    : static_cast<uint32_t>(re_off - ch * kChunkBytes);
+                if (!anchor_begin && !((p.chunk_flags[ch >> 5] >> (ch & 31)) & 1))
+                {
+                    s = next_chunk; // no match starts anywhere in this chunk
+                    continue;
+                }
+                limit = next_chunk < L ? next_chunk : L;
+            }
+            // classes of positions [s, s + 48); beyond the record: class 0, which every state leaves for the dead state
+            __syncwarp();
+            win8[lane] = s + lane < L ? s_cls[at(s + lane)] : 0;
+            if (lane < 16)
+                win8[32 + lane] = s + 32 + lane < L ? s_cls[at(s + 32 + lane)] : 0;
+            __syncwarp();
+            uint32_t const my_s = s + lane;
+            uint32_t e = 0; // 0 = no match (a match is never empty)
+            bool const active = my_s < limit && (!anchor_begin || lane == 0);
+            uint32_t st = active ? ncls : 0; // state 1, pre-multiplied
+            {
+                uint32_t const a = win[w0], b = win[w0 + 1], c2 = win[w0 + 2], d = win[w0 + 3], f = win[w0 + 4];
+                uint32_t const reg[4] = {__funnelshift_r(a, b, sh), __funnelshift_r(b, c2, sh), __funnelshift_r(c2, d, sh),
+                                         __funnelshift_r(d, f, sh)};
+#pragma unroll
+                for (int j = 0; j < 16; ++j)
+                {
+                    if ((j & 3) == 0 && j > 0 && !__any_sync(0xffffffffu, st != 0))
+                        break;
+                    if (st != 0)
+                    {
+                        st = trans[st + ((reg[j >> 2] >> ((j & 3) * 8)) & 0xFF)];
+                        if (st >= accept_from && (!ANCHOR_END || my_s + j + 1 == L))
+                            e = my_s + j + 1;
+                    }
+                }
+                uint32_t pos = my_s + 16;
+                while (st != 0 && pos < L) // long walks: byte by byte
+                {
+                    st = trans[st + s_cls[at(pos)]];
+                    ++pos;
+                    if (st >= accept_from && (!ANCHOR_END || pos == L))
+                        e = pos;
+                }
+            }
+            unsigned const found = __ballot_sync(0xffffffffu, e != 0);
+            if (found)
+            {
+                int const leader = __ffs(found) - 1;
+                uint32_t const e_hit = __shfl_sync(0xffffffffu, e, leader);
+                if (lane == 0)
+                {
+                    unsigned long long idx = atomicAdd(p.hit_count, 1ULL);
+                    if (idx < p.cap)
+                    {
+                        uint64_t const key = (r << 32) | static_cast<uint64_t>(s + leader);
+                        if (p.hit_pats)
+                        {
+                            p.hit_keys[idx] = key;
+                            p.hit_ends[idx] = e_hit;
+                            p.hit_pats[idx] = p.pattern_id;
+                        }
+                        else if (idx < kSmallHits)
+                        {
+                            p.small_keys[idx] = key;
+                            p.small_ends[idx] = e_hit;
+                        }
+                        else
+                        {
+                            p.hit_keys[idx] = key;
+                            p.hit_ends[idx] = e_hit;
+                        }
+                    }
+                }
+                s = e_hit; // FindAndConsume: the next search starts where this match ended
+            }
+            else
+            {
+                if (anchor_begin)
+                    break; // '^' can only match at the resume point
+                s = (s + 32 < limit) ? s + 32 : limit;
+            }
+        }
+    }
+}
+
+// dynamic shared memory: [256 class bytes | 16 window words per warp (4 warps) | transition table if <= kDfaSmemBytes]
+constexpr unsigned kDfaSmemBytes = 32 * 1024;
+constexpr unsigned kDfaSmemFixed = 256 + 4 * 64;
+
+__host__ __device__ inline unsigned dfa_smem_bytes(unsigned states, unsigned classes)
+{
+    unsigned const table = states * classes * 2;
+    return kDfaSmemFixed + (table <= kDfaSmemBytes ? ((table + 15) & ~15u) : 0);
+}
+
+template <int DIR>
+__device__ __forceinline__ void phase2_dfa_block(resolve_params const & p, uint8_t * smem)
+{
+    if (static_cast<uint64_t>(blockIdx.x) * (blockDim.x >> 5) >= *p.rec_count)
+        return;
+    unsigned const entries = p.dfa_states * p.dfa_classes;
+    bool const staged = entries * 2 <= kDfaSmemBytes;
+    uint8_t * const s_cls = smem;
+    uint32_t * const s_win_all = reinterpret_cast<uint32_t *>(smem + 256);
+    uint16_t * const s_trans = reinterpret_cast<uint16_t *>(smem + kDfaSmemFixed);
+    for (unsigned i = threadIdx.x; i < 256; i += blockDim.x)
+        s_cls[i] = p.dfa_cls[i];
+    if (staged)
+        for (unsigned i = threadIdx.x; i < entries; i += blockDim.x)
+            s_trans[i] = p.dfa_trans[i];
+    if (threadIdx.x < 64)
+        s_win_all[threadIdx.x] = 0;
+    __syncthreads();
+    if (p.anchor_end)
+        phase2_dfa_body<DIR, true>(p, staged ? s_trans : p.dfa_trans, s_cls, s_win_all + (threadIdx.x >> 5) * 16);
+    else
+        phase2_dfa_body<DIR, false>(p, staged ? s_trans : p.dfa_trans, s_cls, s_win_all + (threadIdx.x >> 5) * 16);
+}
+
+template <int DIR>
+__global__ void __launch_bounds__(128) regex_scan_phase2_dfa(resolve_params p)
+{
+    extern __shared__ __align__(16) uint8_t dfa_smem[];
+    phase2_dfa_block<DIR>(p, dfa_smem);
+}
+
 template <int W, int DIR>
 __global__ void __launch_bounds__(128) regex_scan_phase2(resolve_params p)
 {
     __shared__ regex_dev s_re; // the automaton, staged once per CTA: every attempt starts with a B[] lookup
-    phase2_body<W, DIR>(p, s_re);
+    __shared__ uint8_t s_cls[256];
+    phase2_body<W, DIR>(p, s_re, s_cls);
+}
+
+// Patterns without any selective necessary factor and with a determinised matcher skip phase 1: every record of a
+// candidate bin is resolved directly (one table lookup per byte and start position is cheaper than streaming the text
+// through the position automaton first).
+__global__ void __launch_bounds__(256)
+    list_candidate_records_kernel(uint32_t const * __restrict__ rec_bin, uint64_t const * __restrict__ cand_words, uint64_t n_records,
+                                  uint32_t * __restrict__ rec_list, unsigned int * __restrict__ rec_count)
+{
+    for (uint64_t r = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; r < n_records;
+         r += static_cast<uint64_t>(gridDim.x) * blockDim.x)
+    {
+        bool const take = is_candidate(cand_words, __ldg(rec_bin + r));
+        unsigned const m = __ballot_sync(__activemask(), take);
+        if (!m)
+            continue;
+        unsigned const lane = threadIdx.x & 31;
+        unsigned const leader = __ffs(m) - 1;
+        unsigned base = 0;
+        if (lane == leader)
+            base = atomicAdd(rec_count, __popc(m));
+        base = __shfl_sync(__activemask(), base, leader);
+        if (take)
+            rec_list[base + __popc(m & ((1u << lane) - 1))] = static_cast<uint32_t>(r);
+    }
+}
+
+// sorted (record << 32 | start, end) pairs → the trx_hit records the caller receives: one copy instead of a host loop
+__global__ void __launch_bounds__(256)
+    format_hits_kernel(uint64_t const * __restrict__ keys, uint32_t const * __restrict__ ends, uint32_t const * __restrict__ rec_bin,
+                       uint64_t n, uint4 * __restrict__ out)
+{
+    for (uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+         i += static_cast<uint64_t>(gridDim.x) * blockDim.x)
+    {
+        uint64_t const k = keys[i];
+        uint32_t const rec = static_cast<uint32_t>(k >> 32);
+        out[i] = make_uint4(__ldg(rec_bin + rec), rec, static_cast<uint32_t>(k), ends[i]); // {bin, record, start, end}
+    }
 }
 
 // one launch for a batch of patterns: blockIdx.y = pattern; its CTAs take that pattern's automaton and work list
@@ -708,11 +964,16 @@ template <int W, int DIR>
 __global__ void __launch_bounds__(128) regex_scan_phase2_multi(resolve_params const * __restrict__ params)
 {
     __shared__ regex_dev s_re;
+    __shared__ uint8_t s_cls[256];
     __shared__ resolve_params s_p;
+    extern __shared__ __align__(16) uint8_t dfa_smem[]; // sized by the host for the largest DFA of the batch
     if (threadIdx.x == 0)
         s_p = params[blockIdx.y];
     __syncthreads();
-    phase2_body<W, DIR>(s_p, s_re);
+    if (s_p.dfa_trans)
+        phase2_dfa_block<DIR>(s_p, dfa_smem);
+    else
+        phase2_body<W, DIR>(s_p, s_re, s_cls);
 }
 
 } // namespace trx

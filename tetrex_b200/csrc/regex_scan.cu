@@ -7,6 +7,7 @@
 #include <cstdlib>
 #include <functional>
 #include <memory>
+#include <unordered_map>
 #include <vector>
 
 #include <cub/device/device_radix_sort.cuh>
@@ -72,7 +73,7 @@ struct trx_text
     };
     std::vector<cached_choice> choices;
     // per-scan scratch
-    trx::scratch d_keys2, d_ends2, d_sort_tmp;
+    trx::scratch d_keys2, d_ends2, d_sort_tmp, d_hits_fmt;
     // multi-pattern scans (trx_regex_scan_multi): one staging block up (programs, automata, candidate words, phase-2
     // parameters), one block of flags / lists / counters, one hit list
     trx::scratch m_h_stage, m_d_stage, m_d_flags, m_d_lists, m_d_counters, m_d_tiles, m_d_hit_keys, m_d_hit_ends, m_d_hit_pats,
@@ -247,7 +248,7 @@ void trx_text_destroy(trx_text_t * t)
         for (trx::scratch * s : {&sl.d_stage, &sl.h_stage, &sl.h_small, &sl.d_keys, &sl.d_ends, &sl.d_tiles})
             s->release();
     }
-    for (trx::scratch * s : {&t->d_keys2, &t->d_ends2, &t->d_sort_tmp, &t->m_h_stage, &t->m_d_stage, &t->m_d_flags, &t->m_d_lists,
+    for (trx::scratch * s : {&t->d_keys2, &t->d_ends2, &t->d_sort_tmp, &t->d_hits_fmt, &t->m_h_stage, &t->m_d_stage, &t->m_d_flags, &t->m_d_lists,
                              &t->m_d_counters, &t->m_d_tiles, &t->m_d_hit_keys, &t->m_d_hit_ends, &t->m_d_hit_pats, &t->m_h_back})
         s->release();
     delete t;
@@ -973,6 +974,263 @@ void fill_image(trx_regex const & rx, bool reverse_strand, uint8_t const * map25
     img->anchor_end = re->anchor_end;
 }
 
+// Subset construction over the position automaton of `img` WITHOUT re-injection: the matcher phase 2 runs from one start
+// position.  Bytes with the same B column share a class; class 0 = bytes no position accepts.  Capped: a pattern whose
+// subset automaton outgrows max_states keeps the position-automaton matcher.
+constexpr uint32_t kDfaMaxStates = 2048;
+constexpr size_t kDfaMaxBytes = 96 * 1024; // entries = bytes / 2 < 65536: pre-multiplied states fit 16 bits
+
+constexpr uint32_t kReverseDfaMaxEntries = 16384; // 32 KB of shared memory
+
+// The reverse searcher of dfa_table (see regex.cuh): subsets of positions reachable by reading backwards,
+// X' = (pred(X) | last) & B[c], accepting when X meets `first`.
+void build_reverse_dfa(regex_dev const & img, std::vector<std::pair<uint64_t, uint64_t>> const & cols, dfa_table & out)
+{
+    out.r_usable = false;
+    out.r_trans.clear();
+    if (img.anchor_begin || img.anchor_end)
+        return;
+    int const n = img.positions;
+    // longest match = longest path first → last in the follow graph; a cycle means unbounded
+    std::vector<int> longest(n, 0), mark(n, 0); // mark: 0 new, 1 on stack, 2 done
+    bool cyclic = false;
+    std::function<int(int)> dfs = [&](int i) -> int {
+        if (mark[i] == 2)
+            return longest[i];
+        if (mark[i] == 1)
+        {
+            cyclic = true;
+            return 0;
+        }
+        mark[i] = 1;
+        int best = 1;
+        for (int j = 0; j < n && !cyclic; ++j)
+            if ((img.follow[i][j >> 6] >> (j & 63)) & 1)
+                best = std::max(best, 1 + dfs(j));
+        mark[i] = 2;
+        return longest[i] = best;
+    };
+    int max_len = 0;
+    for (int i = 0; i < n && !cyclic; ++i)
+        if ((img.first[i >> 6] >> (i & 63)) & 1)
+            max_len = std::max(max_len, dfs(i));
+    if (cyclic || max_len == 0 || max_len > 1024)
+        return;
+    uint64_t pred[128][2] = {};
+    for (int i = 0; i < n; ++i)
+        for (int j = 0; j < n; ++j)
+            if ((img.follow[i][j >> 6] >> (j & 63)) & 1)
+                pred[j][i >> 6] |= 1ull << (i & 63);
+    uint32_t const nc = static_cast<uint32_t>(cols.size());
+    struct key
+    {
+        uint64_t a, b;
+        bool operator==(key const & o) const { return a == o.a && b == o.b; }
+    };
+    struct key_hash
+    {
+        size_t operator()(key const & k) const { return static_cast<size_t>((k.a * 0x9E3779B97F4A7C15ull) ^ (k.b + 0x7F4A7C15ull) * 0xC2B2AE3D27D4EB4Full); }
+    };
+    std::unordered_map<key, uint32_t, key_hash> id_of;
+    std::vector<key> sets{key{0, 0}};
+    id_of.emplace(key{0, 0}, 0);
+    std::vector<uint32_t> trans(nc, 0);
+    for (uint32_t s = 0; s < sets.size(); ++s)
+    {
+        if (sets.size() * nc > kReverseDfaMaxEntries)
+            return;
+        key const cur = sets[s];
+        uint64_t p0 = img.last[0], p1 = img.last[1];
+        for (int w = 0; w < 2; ++w)
+        {
+            uint64_t bits = w == 0 ? cur.a : cur.b;
+            while (bits)
+            {
+                int const j = __builtin_ctzll(bits) + 64 * w;
+                bits &= bits - 1;
+                p0 |= pred[j][0];
+                p1 |= pred[j][1];
+            }
+        }
+        for (uint32_t c = 0; c < nc; ++c)
+        {
+            key const to{p0 & cols[c].first, p1 & cols[c].second};
+            auto it = id_of.find(to);
+            uint32_t id;
+            if (it != id_of.end())
+                id = it->second;
+            else
+            {
+                id = static_cast<uint32_t>(sets.size());
+                id_of.emplace(to, id);
+                sets.push_back(to);
+                trans.resize(trans.size() + nc, 0);
+            }
+            trans[static_cast<size_t>(s) * nc + c] = id;
+        }
+    }
+    if (sets.size() * nc > kReverseDfaMaxEntries)
+        return;
+    uint32_t const ns = static_cast<uint32_t>(sets.size());
+    std::vector<uint32_t> new_id(ns, 0);
+    uint32_t next = 1; // state 0 (nothing live) keeps its number
+    auto accepting = [&](uint32_t s) { return ((sets[s].a & img.first[0]) | (sets[s].b & img.first[1])) != 0; };
+    for (uint32_t s = 1; s < ns; ++s)
+        if (!accepting(s))
+            new_id[s] = next++;
+    out.r_first_accept = next;
+    for (uint32_t s = 1; s < ns; ++s)
+        if (accepting(s))
+            new_id[s] = next++;
+    out.r_states = ns;
+    out.max_len = static_cast<uint32_t>(max_len);
+    out.r_trans.assign(static_cast<size_t>(ns) * nc, 0);
+    for (uint32_t s = 0; s < ns; ++s)
+        for (uint32_t c = 0; c < nc; ++c)
+            out.r_trans[static_cast<size_t>(new_id[s]) * nc + c] = static_cast<uint16_t>(new_id[trans[static_cast<size_t>(s) * nc + c]]);
+    out.r_usable = true;
+}
+
+void build_dfa(regex_dev const & img, dfa_table & out)
+{
+    out.usable = false;
+    out.trans.clear();
+    if (!img.posix_longest)
+        return;
+    // byte classes
+    std::vector<std::pair<uint64_t, uint64_t>> cols; // class → column
+    cols.push_back({0, 0});
+    for (int ch = 0; ch < 256; ++ch)
+    {
+        std::pair<uint64_t, uint64_t> const col{img.B[ch][0], img.B[ch][1]};
+        size_t k = 0;
+        while (k < cols.size() && cols[k] != col)
+            ++k;
+        if (k == cols.size())
+            cols.push_back(col);
+        out.cls[ch] = static_cast<uint8_t>(k);
+    }
+    uint32_t const nc = static_cast<uint32_t>(cols.size());
+    if (nc > 64)
+        return;
+    struct key
+    {
+        uint64_t a, b;
+        bool operator==(key const & o) const { return a == o.a && b == o.b; }
+    };
+    struct key_hash
+    {
+        size_t operator()(key const & k) const { return static_cast<size_t>((k.a * 0x9E3779B97F4A7C15ull) ^ (k.b + 0x7F4A7C15ull) * 0xC2B2AE3D27D4EB4Full); }
+    };
+    std::unordered_map<key, uint32_t, key_hash> id_of;
+    std::vector<key> sets;      // provisional id → subset (ids 0 = dead, 1 = start are not subsets)
+    sets.push_back({0, 0});
+    sets.push_back({0, 0});
+    std::vector<uint32_t> trans; // provisional ids
+    trans.assign(2 * nc, 0);
+    auto id_for = [&](key const & k) -> uint32_t {
+        if ((k.a | k.b) == 0)
+            return 0;
+        auto it = id_of.find(k);
+        if (it != id_of.end())
+            return it->second;
+        uint32_t const id = static_cast<uint32_t>(sets.size());
+        id_of.emplace(k, id);
+        sets.push_back(k);
+        trans.resize(trans.size() + nc, 0);
+        return id;
+    };
+    // start: S = first & B[c]
+    for (uint32_t c = 1; c < nc; ++c)
+    {
+        uint32_t const to = id_for(key{img.first[0] & cols[c].first, img.first[1] & cols[c].second});
+        trans[1 * nc + c] = to;
+    }
+    for (uint32_t s = 2; s < sets.size(); ++s)
+    {
+        if (sets.size() > kDfaMaxStates || sets.size() * nc * 2 > kDfaMaxBytes)
+            return;
+        key const cur = sets[s];
+        uint64_t f0 = 0, f1 = 0;
+        for (int w = 0; w < 2; ++w)
+        {
+            uint64_t bits = w == 0 ? cur.a : cur.b;
+            while (bits)
+            {
+                int const i = __builtin_ctzll(bits);
+                bits &= bits - 1;
+                f0 |= img.follow[w * 64 + i][0];
+                f1 |= img.follow[w * 64 + i][1];
+            }
+        }
+        for (uint32_t c = 1; c < nc; ++c)
+        {
+            uint32_t const to = id_for(key{f0 & cols[c].first, f1 & cols[c].second}); // may grow sets / trans
+            trans[static_cast<size_t>(s) * nc + c] = to;
+        }
+    }
+    if (sets.size() > kDfaMaxStates || sets.size() * nc * 2 > kDfaMaxBytes)
+        return;
+    // renumber: accepting subsets last
+    uint32_t const n = static_cast<uint32_t>(sets.size());
+    std::vector<uint32_t> new_id(n, 0);
+    uint32_t next = 2;
+    new_id[0] = 0;
+    new_id[1] = 1;
+    auto accepting = [&](uint32_t s) { return ((sets[s].a & img.last[0]) | (sets[s].b & img.last[1])) != 0; };
+    for (uint32_t s = 2; s < n; ++s)
+        if (!accepting(s))
+            new_id[s] = next++;
+    out.first_accept = next;
+    for (uint32_t s = 2; s < n; ++s)
+        if (accepting(s))
+            new_id[s] = next++;
+    out.n_states = n;
+    out.n_classes = nc;
+    out.trans.assign(static_cast<size_t>(n) * nc, 0);
+    for (uint32_t s = 0; s < n; ++s)
+        for (uint32_t c = 0; c < nc; ++c)
+            out.trans[static_cast<size_t>(new_id[s]) * nc + c] = static_cast<uint16_t>(new_id[trans[static_cast<size_t>(s) * nc + c]]);
+    out.usable = true;
+    build_reverse_dfa(img, cols, out);
+}
+
+// device form of the table: every state pre-multiplied by the class count (n_states * n_classes < 65536 by construction)
+void stage_dfa_table(dfa_table const & d, uint16_t * dst)
+{
+    for (size_t i = 0; i < d.trans.size(); ++i)
+        dst[i] = static_cast<uint16_t>(d.trans[i] * d.n_classes);
+}
+
+uint64_t hash_map256(uint8_t const * map256)
+{
+    if (!map256)
+        return 0;
+    uint64_t h = 1469598103934665603ull; // FNV-1a
+    for (int i = 0; i < 256; ++i)
+        h = (h ^ map256[i]) * 1099511628211ull;
+    return h;
+}
+
+// the regex's matcher for this (strand, byte map), built on first use.  TRX_REGEX_DFA=off: never (A/B evidence, tests)
+dfa_table const * dfa_for(trx_regex & re, regex_dev const & img, int reverse, uint64_t map_hash)
+{
+    char const * const env = getenv("TRX_REGEX_DFA");
+    if ((env && strcmp(env, "off") == 0) || !re.posix_longest)
+        return nullptr;
+    for (dfa_table const & d : re.dfas)
+        if (d.reverse == reverse && d.map_hash == map_hash)
+            return d.usable ? &d : nullptr;
+    if (re.dfas.size() >= 8)
+        re.dfas.clear();
+    re.dfas.emplace_back();
+    dfa_table & d = re.dfas.back();
+    d.reverse = reverse;
+    d.map_hash = map_hash;
+    build_dfa(img, d);
+    return d.usable ? &d : nullptr;
+}
+
 enum filter_kind : int { kFilterNone = 0, kFilterWindow = 1, kFilterAtoms = 2 };
 
 // Chooses phase 1 for one scan.  TRX_REGEX_FILTER = off | window | atoms restricts the choice (A/B evidence, tests).
@@ -1096,14 +1354,23 @@ int trx_regex_scan_begin(trx_text_t * t, trx_regex_t * re, const uint64_t * cand
     static_assert(sizeof(regex_dev) < 16384, "regex_dev grew unexpectedly");
     size_t const off_cand = 0;
     size_t const off_regex = align16(off_cand + cand_words * 8);
-    size_t const stage_bytes = off_regex + sizeof(regex_dev);
+    size_t const off_dfa = align16(off_regex + sizeof(regex_dev)); // [256 class bytes | transitions] when there is a DFA
     sl.h_stage.pinned_host = true;
-    TRX_TRY(sl.h_stage.reserve(stage_bytes));
-    TRX_TRY(sl.d_stage.reserve(stage_bytes));
+    TRX_TRY(sl.h_stage.reserve(off_dfa + 256 + kDfaMaxBytes));
+    TRX_TRY(sl.d_stage.reserve(off_dfa + 256 + kDfaMaxBytes));
     auto * hs = static_cast<uint8_t *>(sl.h_stage.ptr);
     memcpy(hs + off_cand, candidate_bin_words, cand_words * 8);
     auto * img = reinterpret_cast<regex_dev *>(hs + off_regex);
     fill_image(*re, reverse_strand != 0, map256, img);
+    uint64_t const map_hash = hash_map256(map256);
+    dfa_table const * const dfa = dfa_for(*re, *img, reverse_strand, map_hash);
+    size_t stage_bytes = off_dfa;
+    if (dfa)
+    {
+        memcpy(hs + off_dfa, dfa->cls, 256);
+        stage_dfa_table(*dfa, reinterpret_cast<uint16_t *>(hs + off_dfa + 256));
+        stage_bytes = off_dfa + 256 + dfa->trans.size() * 2;
+    }
     t_image = now();
 
     if (cap > (1ull << 31))
@@ -1140,13 +1407,6 @@ int trx_regex_scan_begin(trx_text_t * t, trx_regex_t * re, const uint64_t * cand
     {
         char const * filt = getenv("TRX_REGEX_FILTER");
         int const mode = !filt ? 0 : (filt[0] == 'o' ? 1 : (filt[0] == 'w' ? 2 : (filt[0] == 'a' ? 3 : 4)));
-        uint64_t map_hash = 0;
-        if (map256)
-        {
-            map_hash = 1469598103934665603ull; // FNV-1a
-            for (int i = 0; i < 256; ++i)
-                map_hash = (map_hash ^ map256[i]) * 1099511628211ull;
-        }
         trx_text::cached_choice const * found = nullptr;
         for (auto const & cc : t->choices)
             if (cc.serial == re->serial && cc.reverse == reverse_strand && cc.mode == mode && cc.map_hash == map_hash)
@@ -1169,11 +1429,22 @@ int trx_regex_scan_begin(trx_text_t * t, trx_regex_t * re, const uint64_t * cand
         sp.atoms = found->atoms;
     }
     bool const use_atoms = kind == kFilterAtoms, use_window = kind == kFilterWindow;
+    // no selective necessary factor, but a determinised matcher: resolving every candidate record directly (one table
+    // lookup per byte and start) beats streaming the text through the position automaton first.  An explicit
+    // TRX_REGEX_FILTER keeps the exact phase-1 kernel reachable for A/B runs and tests.
+    bool const skip_phase1 = kind == kFilterNone && dfa != nullptr && use_tma && !getenv("TRX_REGEX_FILTER");
     t_choice = now();
     sl.filter_units = use_atoms ? static_cast<uint64_t>(sp.atoms.n_atoms)
                                 : (use_window ? static_cast<uint64_t>(sp.filter.n_a + sp.filter.n_b) : 0);
     if (tiles.empty())
         ; // nothing to scan: no kernel, the read-back below returns the zeroed counters
+    else if (skip_phase1)
+    {
+        list_candidate_records_kernel<<<grid_for(t->n_records, 256, c->sm_count, 8), 256, 0, st>>>(
+            t->d_rec_bin, sp.cand_words, t->n_records, sl.d_rec_list, sp.rec_count);
+        ++c->launches;
+        TRX_CUDA(cudaGetLastError());
+    }
     else if (use_atoms)
         TRX_TRY(launch_atoms_any(c, st, sp, t->tmap));
     else if (use_window)
@@ -1188,8 +1459,18 @@ int trx_regex_scan_begin(trx_text_t * t, trx_regex_t * re, const uint64_t * cand
     rp.rec_offsets = t->d_rec_offsets;
     rp.rec_list = sl.d_rec_list;
     rp.rec_count = sp.rec_count;
-    rp.chunk_flags = sl.d_chunk_flags;
+    rp.chunk_flags = skip_phase1 ? nullptr : sl.d_chunk_flags;
     rp.re = sp.re;
+    rp.anchor_begin = re->anchor_begin;
+    rp.anchor_end = re->anchor_end;
+    if (dfa)
+    {
+        rp.dfa_cls = ds + off_dfa;
+        rp.dfa_trans = reinterpret_cast<uint16_t const *>(ds + off_dfa + 256);
+        rp.dfa_classes = dfa->n_classes;
+        rp.dfa_states = dfa->n_states;
+        rp.dfa_first_accept = dfa->first_accept;
+    }
     rp.hit_count = reinterpret_cast<unsigned long long *>(sl.d_counters);
     rp.hit_keys = static_cast<uint64_t *>(sl.d_keys.ptr);
     rp.hit_ends = static_cast<uint32_t *>(sl.d_ends.ptr);
@@ -1198,6 +1479,17 @@ int trx_regex_scan_begin(trx_text_t * t, trx_regex_t * re, const uint64_t * cand
     rp.cap = cap;
     if (tiles.empty())
         ;
+    else if (dfa)
+    {
+        unsigned const smem = dfa_smem_bytes(dfa->n_states, dfa->n_classes);
+        unsigned const grid = static_cast<unsigned>(c->sm_count) * 16;
+        if (reverse)
+            regex_scan_phase2_dfa<-1><<<grid, 128, smem, st>>>(rp);
+        else
+            regex_scan_phase2_dfa<1><<<grid, 128, smem, st>>>(rp);
+        ++c->launches;
+        TRX_CUDA(cudaGetLastError());
+    }
     else if (re->words == 1)
         TRX_TRY(launch_phase2_w<1>(c, st, rp, reverse));
     else
@@ -1295,16 +1587,17 @@ int trx_regex_scan_end(trx_text_t * t, int ticket, trx_hit * hits, uint64_t * n_
                                              static_cast<uint64_t *>(t->d_keys2.ptr), d_hit_ends,
                                              static_cast<uint32_t *>(t->d_ends2.ptr), static_cast<int>(n), 0, 64, st));
     c->launches += 3; // cub's histogram + onesweep passes
-    std::vector<uint64_t> keys(n);
-    std::vector<uint32_t> ends(n);
-    TRX_CUDA(cudaMemcpyAsync(keys.data(), t->d_keys2.ptr, n * 8, cudaMemcpyDeviceToHost, st));
-    TRX_CUDA(cudaMemcpyAsync(ends.data(), t->d_ends2.ptr, n * 4, cudaMemcpyDeviceToHost, st));
+    // the sorted pairs become trx_hit records on the device (the unsorted key buffer is free again: n x 8 B of the n x 16 B
+    // needed, the rest comes from the ends buffer's neighbour) and reach the caller's array in ONE copy
+    static_assert(sizeof(trx_hit) == 16, "format_hits_kernel writes uint4");
+    TRX_TRY(t->d_hits_fmt.reserve(n * sizeof(trx_hit)));
+    format_hits_kernel<<<grid_for(n, 256, c->sm_count, 8), 256, 0, st>>>(static_cast<uint64_t const *>(t->d_keys2.ptr),
+                                                                           static_cast<uint32_t const *>(t->d_ends2.ptr), t->d_rec_bin,
+                                                                           n, static_cast<uint4 *>(t->d_hits_fmt.ptr));
+    ++c->launches;
+    TRX_CUDA(cudaGetLastError());
+    TRX_CUDA(cudaMemcpyAsync(hits, t->d_hits_fmt.ptr, n * sizeof(trx_hit), cudaMemcpyDeviceToHost, st));
     TRX_CUDA(cudaStreamSynchronize(st));
-    for (uint64_t i = 0; i < n; ++i)
-    {
-        uint32_t rec = static_cast<uint32_t>(keys[i] >> 32);
-        hits[i] = trx_hit{t->h_rec_bin[rec], rec, static_cast<uint32_t>(keys[i]), ends[i]};
-    }
     return TRX_OK;
 }
 
@@ -1317,6 +1610,63 @@ int trx_regex_scan(trx_text_t * t, trx_regex_t * re, const uint64_t * candidate_
     int ticket = -1;
     TRX_TRY(trx_regex_scan_begin(t, re, candidate_bin_words, reverse_strand, map256, cap, &ticket));
     return trx_regex_scan_end(t, ticket, hits, n_hits, stats);
+}
+
+// host-only (tests): the reverse searcher run over text[0, len) as ONE record: starts[p] = 1 iff some match starts at p.
+// Returns the longest possible match length, 0 if the pattern has no reverse searcher.
+uint32_t trx_regex_dfa_starts(trx_regex_t * re, const uint8_t * text, uint64_t len, uint8_t * starts)
+{
+    if (!re || (len && (!text || !starts)))
+        return 0;
+    auto img = std::make_unique<regex_dev>();
+    fill_image(*re, false, nullptr, img.get());
+    dfa_table const * d = dfa_for(*re, *img, 0, 0);
+    if (!d || !d->r_usable)
+        return 0;
+    uint32_t st = 0;
+    for (uint64_t p = len; p-- > 0;)
+    {
+        st = d->r_trans[static_cast<size_t>(st) * d->n_classes + d->cls[text[p]]];
+        starts[p] = st >= d->r_first_accept;
+    }
+    return d->max_len;
+}
+
+int trx_regex_dfa_info(trx_regex_t * re, uint32_t info[3])
+{
+    if (!re || !info)
+        return 0;
+    auto img = std::make_unique<regex_dev>();
+    fill_image(*re, false, nullptr, img.get());
+    dfa_table const * d = dfa_for(*re, *img, 0, 0);
+    info[0] = d ? d->n_states : 0;
+    info[1] = d ? d->n_classes : 0;
+    info[2] = d ? d->first_accept : 0;
+    return d ? 1 : 0;
+}
+
+// the device's match_longest_dfa (regex_kernels.cuh) on the host, for CPU-side parity tests of the subset construction
+int64_t trx_regex_dfa_match_end(trx_regex_t * re, const uint8_t * text, uint64_t len, uint64_t start)
+{
+    if (!re || (len && !text))
+        return -2;
+    auto img = std::make_unique<regex_dev>();
+    fill_image(*re, false, nullptr, img.get());
+    dfa_table const * d = dfa_for(*re, *img, 0, 0);
+    if (!d)
+        return -2;
+    uint32_t st = 1;
+    int64_t best = -1;
+    for (uint64_t pos = start; pos < len;)
+    {
+        st = d->trans[static_cast<size_t>(st) * d->n_classes + d->cls[text[pos]]];
+        if (st == 0)
+            break;
+        ++pos;
+        if (st >= d->first_accept && (!re->anchor_end || pos == len))
+            best = static_cast<int64_t>(pos);
+    }
+    return best;
 }
 
 int trx_regex_filter_plan(const trx_regex_t * re, const double * byte_freq, int reverse_strand, const uint8_t * map256,
@@ -1628,14 +1978,32 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
         if (tiles.empty())
             continue; // no candidate bin holds a residue: no hits for this batch
 
-        // ---- device blocks.  staging (one H2D): [programs | automata | candidate words | phase-2 parameters]
+        // ---- device blocks.  staging (one H2D): [programs | automata | candidate words | phase-2 parameters | terms | DFAs]
         uint64_t const rfw = t->n_rec_flag_words;
         size_t const off_prog = 0;
         size_t const off_img = align16(off_prog + nb * sizeof(multi_program));
         size_t const off_cand = align16(off_img + nb * sizeof(regex_dev));
         size_t const off_rp = align16(off_cand + static_cast<size_t>(nb) * cand_words * 8);
         size_t const off_terms = align16(off_rp + nb * sizeof(resolve_params));
-        size_t const stage_bytes = off_terms + (static_cast<size_t>(nb) * kMultiMaxTermsPerPattern + 8) * 4;
+        size_t const off_dfa = align16(off_terms + (static_cast<size_t>(nb) * kMultiMaxTermsPerPattern + 8) * 4);
+        std::vector<dfa_table const *> dfas(nb, nullptr);
+        std::vector<size_t> dfa_at(nb, 0);
+        size_t stage_bytes = off_dfa;
+        for (uint32_t k = 0; k < nb; ++k)
+        {
+            trx_regex & rx = *regexes[ids[k]];
+            bool cached = false;
+            for (dfa_table const & d : rx.dfas)
+                cached = cached || (d.reverse == 0 && d.map_hash == 0);
+            if (!cached)
+                fill_image(rx, false, nullptr, img.get());
+            dfas[k] = dfa_for(rx, *img, 0, 0);
+            if (dfas[k])
+            {
+                dfa_at[k] = stage_bytes;
+                stage_bytes = align16(stage_bytes + 256 + dfas[k]->trans.size() * 2);
+            }
+        }
         uint64_t const cfw = t->n_chunk_flag_words;
         t->m_h_stage.pinned_host = true;
         TRX_TRY(t->m_h_stage.reserve(stage_bytes));
@@ -1701,6 +2069,18 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
             rp.pattern_id = k;
             rp.rec_cap = kMultiListCap;
             rp.cap = cap;
+            rp.anchor_begin = regexes[ids[k]]->anchor_begin;
+            rp.anchor_end = regexes[ids[k]]->anchor_end;
+            if (dfas[k])
+            {
+                memcpy(hs + dfa_at[k], dfas[k]->cls, 256);
+                stage_dfa_table(*dfas[k], reinterpret_cast<uint16_t *>(hs + dfa_at[k] + 256));
+                rp.dfa_cls = ds + dfa_at[k];
+                rp.dfa_trans = reinterpret_cast<uint16_t const *>(ds + dfa_at[k] + 256);
+                rp.dfa_classes = dfas[k]->n_classes;
+                rp.dfa_states = dfas[k]->n_states;
+                rp.dfa_first_accept = dfas[k]->first_accept;
+            }
         }
         auto const t_staged = now();
         us_stage += us(t_planned, t_staged);
@@ -1736,7 +2116,11 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
             ++c->launches;
             TRX_CUDA(cudaGetLastError());
         }
-        regex_scan_phase2_multi<2, 1><<<dim3(32, nb), 128, 0, st>>>(reinterpret_cast<resolve_params const *>(ds + off_rp));
+        unsigned dyn_smem = 0;
+        for (uint32_t k = 0; k < nb; ++k)
+            if (dfas[k])
+                dyn_smem = std::max(dyn_smem, dfa_smem_bytes(dfas[k]->n_states, dfas[k]->n_classes));
+        regex_scan_phase2_multi<2, 1><<<dim3(32, nb), 128, dyn_smem, st>>>(reinterpret_cast<resolve_params const *>(ds + off_rp));
         ++c->launches;
         TRX_CUDA(cudaGetLastError());
 
