@@ -116,9 +116,13 @@ def test_dfa_matcher_equals_position_automaton(ctx, monkeypatch):
         monkeypatch.setenv("TRX_REGEX_DFA", "off")
         b = txt.scan(rx, cap=1 << 20)
         monkeypatch.delenv("TRX_REGEX_DFA")
+        monkeypatch.setenv("TRX_REGEX_STARTS", "off")  # no reverse searcher: every record of a candidate bin, every start
+        c = txt.scan(rx, cap=1 << 20)
+        monkeypatch.delenv("TRX_REGEX_STARTS")
         want = expected_hits(seqs, rec_bin, pat, True, finder)
         assert np.array_equal(a, want), pat
         assert np.array_equal(b, want), pat
+        assert np.array_equal(c, want), pat
         assert np.array_equal(a_some, expected_hits(seqs, rec_bin, pat, True, finder, cand={1, 3, 5})), pat
     dense = txt.scan(t.Regex("[ST].[RK]", True), cap=1 << 20)
     assert len(dense) > 1024

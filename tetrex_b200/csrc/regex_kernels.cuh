@@ -109,6 +109,11 @@ struct scan_params
     regex_dev const * re;
     filter_spec filter;
     atom_spec atoms;
+    // reverse searcher (regex_scan_starts_dfa): exact match starts, one bit per text byte
+    uint32_t * start_bits;         // n_text_padded / 32 words, zeroed per scan
+    uint16_t const * r_trans;      // states pre-multiplied by r_classes, like the matcher's table
+    uint8_t const * r_cls;         // 256 bytes
+    uint32_t r_classes, r_states, r_first_accept, r_max_len;
 };
 
 // first flagging of a record appends it to the phase-2 work list
@@ -466,6 +471,155 @@ __global__ void __launch_bounds__(kScanThreads)
     }
 }
 
+// Phase 1 for patterns without a selective necessary factor: the reverse searcher DFA (regex.cuh) reads every chunk
+// BACKWARDS, one table lookup per byte, after warming up on the max_len - 1 bytes that follow the chunk in its record, and
+// writes the exact set of match starts as one bit per text byte.  Same tile ring as the exact automaton kernel (thread per
+// 128-byte row of a TMA tile).  The position-automaton kernel above costs 43 thread-instructions per residue; this one a
+// class lookup and a table lookup.
+__global__ void __launch_bounds__(kScanThreads)
+    regex_scan_starts_dfa(scan_params p, const __grid_constant__ CUtensorMap tmap)
+{
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    // layout: [tile stage 0][tile stage 1][256 class bytes][barriers][table]
+    uint8_t * tiles = smem_raw;
+    uint8_t * s_cls = smem_raw + kStages * kTileBytes;
+    uint64_t * bars = reinterpret_cast<uint64_t *>(s_cls + 256);
+    uint16_t * s_trans = reinterpret_cast<uint16_t *>(s_cls + 256 + 16);
+    int const tid = threadIdx.x;
+    for (int c = tid; c < 256; c += kScanThreads)
+        s_cls[c] = p.r_cls[c];
+    for (unsigned i = tid; i < p.r_states * p.r_classes; i += kScanThreads)
+        s_trans[i] = p.r_trans[i];
+    uint32_t const accept_from = p.r_first_accept * p.r_classes;
+    if (tid == 0)
+    {
+        mbar_init(&bars[0], 1);
+        mbar_init(&bars[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    uint32_t const first_tile = blockIdx.x;
+    if (tid == 0 && first_tile < p.n_tiles)
+        tma_load_tile(&tmap, tiles, &bars[0], static_cast<int32_t>(p.tiles[first_tile]) * kScanThreads);
+    uint32_t it = 0;
+    for (uint32_t t = first_tile; t < p.n_tiles; t += gridDim.x, ++it)
+    {
+        uint32_t const stage = it & 1;
+        uint32_t const tn = t + gridDim.x;
+        if (tid == 0 && tn < p.n_tiles)
+        {
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            tma_load_tile(&tmap, tiles + (stage ^ 1) * kTileBytes, &bars[stage ^ 1], static_cast<int32_t>(p.tiles[tn]) * kScanThreads);
+        }
+        mbar_wait(&bars[stage], (it >> 1) & 1);
+        uint64_t const chunk_id = static_cast<uint64_t>(p.tiles[t]) * kScanThreads + tid;
+        uint64_t const g_lo = chunk_id * kChunkBytes;
+        if (g_lo < p.n_text)
+        {
+            uint64_t const g_hi = min(g_lo + kChunkBytes, p.n_text); // exclusive
+            uint64_t const r_last = [&] {
+                uint64_t r = record_of(p.rec_offsets, p.n_records, g_hi - 1);
+                while (__ldg(p.rec_offsets + r + 1) <= g_hi - 1) // empty records sharing this offset
+                    ++r;
+                return r;
+            }();
+            // Everything that depends on record boundaries is decided BEFORE the byte loop, as two 128-bit masks over the
+            // chunk, so that the loop itself is the same instruction stream for every lane (with the bookkeeping inside
+            // the loop the warps ran at 13 of 32 threads): `ends` = last byte of a record (the state is cleared before
+            // such a byte is consumed), `valid` = byte of a record in a candidate bin (only those may report a start).
+            uint32_t ends[4] = {0, 0, 0, 0}, valid[4] = {0, 0, 0, 0};
+            auto or_range = [](uint32_t (&m)[4], uint32_t lo, uint32_t hi) { // bits [lo, hi) of a 128-bit mask
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                {
+                    uint32_t const a = lo > 32u * k ? lo - 32u * k : 0u, b = hi > 32u * k ? hi - 32u * k : 0u;
+                    if (a < 32 && b > a)
+                        m[k] |= (b >= 32 ? ~0u : ((1u << b) - 1)) & (~0u << a);
+                }
+            };
+            {
+                uint64_t r = r_last, rb = __ldg(p.rec_offsets + r), re = __ldg(p.rec_offsets + r + 1);
+                while (true)
+                {
+                    uint32_t const lo = rb > g_lo ? static_cast<uint32_t>(rb - g_lo) : 0u;
+                    uint32_t const hi = static_cast<uint32_t>(min(re, g_hi) - g_lo);
+                    if (hi > lo)
+                    {
+                        if (is_candidate(p.cand_words, __ldg(p.rec_bin + r)))
+                            or_range(valid, lo, hi);
+                        if (re <= g_hi)
+                            ends[(hi - 1) >> 5] |= 1u << ((hi - 1) & 31);
+                    }
+                    if (rb <= g_lo || r == 0)
+                        break;
+                    --r;
+                    re = rb;
+                    rb = __ldg(p.rec_offsets + r);
+                }
+            }
+            // warm-up on the bytes that follow the chunk in its last record: the same number of steps for every lane
+            uint32_t st = 0;
+            {
+                uint64_t const re = __ldg(p.rec_offsets + r_last + 1);
+                uint64_t const w_end = min(g_hi + p.r_max_len - 1, re);
+                for (uint32_t k = p.r_max_len - 1; k-- > 0;)
+                {
+                    uint64_t const g = g_hi + k;
+                    if (g < w_end)
+                        st = s_trans[st + s_cls[__ldg(p.text + g)]];
+                }
+            }
+            uint32_t mask[4] = {0, 0, 0, 0};
+            uint8_t const * row = tiles + stage * kTileBytes + tid * kChunkBytes;
+#pragma unroll
+            for (int piece = kChunkBytes / 16 - 1; piece >= 0; --piece)
+            {
+                uint4 const v = *reinterpret_cast<uint4 const *>(row + ((piece ^ (tid & 7)) << 4));
+                uint32_t const words[4] = {v.x, v.y, v.z, v.w};
+                uint32_t const end16 = (ends[piece >> 1] >> ((piece & 1) * 16)) & 0xFFFFu;
+                uint32_t piece_mask = 0;
+#pragma unroll
+                for (int b = 15; b >= 0; --b)
+                {
+                    uint32_t const cl = s_cls[(words[b >> 2] >> ((b & 3) * 8)) & 0xFF]; // independent of the state
+                    st = (end16 >> b) & 1 ? 0u : st;
+                    st = s_trans[st + cl];
+                    piece_mask |= st >= accept_from ? 1u << b : 0u;
+                }
+                mask[piece >> 1] |= piece_mask << ((piece & 1) * 16);
+            }
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                mask[k] &= valid[k];
+            if (mask[0] | mask[1] | mask[2] | mask[3])
+            {
+                *reinterpret_cast<uint4 *>(p.start_bits + chunk_id * 4) = make_uint4(mask[0], mask[1], mask[2], mask[3]);
+                atomicOr(p.chunk_flags + (chunk_id >> 5), 1u << (chunk_id & 31));
+                // list the records that own a start
+                uint64_t r = r_last, rb = __ldg(p.rec_offsets + r), re = __ldg(p.rec_offsets + r + 1);
+                while (true)
+                {
+                    uint32_t const lo = rb > g_lo ? static_cast<uint32_t>(rb - g_lo) : 0u;
+                    uint32_t const hi = static_cast<uint32_t>(min(re, g_hi) - g_lo);
+                    if (hi > lo)
+                    {
+                        uint32_t range[4] = {0, 0, 0, 0};
+                        or_range(range, lo, hi);
+                        if ((range[0] & mask[0]) | (range[1] & mask[1]) | (range[2] & mask[2]) | (range[3] & mask[3]))
+                            list_record(p, r);
+                    }
+                    if (rb <= g_lo || r == 0)
+                        break;
+                    --r;
+                    re = rb;
+                    rb = __ldg(p.rec_offsets + r);
+                }
+            }
+        }
+        __syncthreads(); // everyone is done with this stage before it is refilled
+    }
+}
+
 } // namespace trx
 
 namespace trx
@@ -501,6 +655,7 @@ struct resolve_params
     uint32_t dfa_states;
     uint32_t dfa_first_accept;
     uint32_t anchor_begin, anchor_end; // copies of the automaton's flags: the DFA route never stages regex_dev
+    uint32_t const * start_bits;       // exact match starts from regex_scan_starts_dfa (nullptr: every position is tried)
 };
 
 // Anchored leftmost-longest match starting at position s of a record read through `at`: the automaton
@@ -795,6 +950,18 @@ __device__ __forceinline__ void phase2_dfa_body(resolve_params const & p, uint16
                 }
                 limit = next_chunk < L ? next_chunk : L;
             }
+            if (p.start_bits) // exact starts are known (regex_scan_starts_dfa): most windows of 32 have none
+            {
+                uint64_t const g = (DIR > 0 ? rb + s : re_off - 1 - s) + (DIR > 0 ? lane : 0) - (DIR > 0 ? 0 : lane);
+                bool const bit = s + lane < limit && ((__ldg(p.start_bits + (g >> 5)) >> (g & 31)) & 1);
+                unsigned const any = __ballot_sync(0xffffffffu, bit);
+                if (!any)
+                {
+                    s = (s + 32 < limit) ? s + 32 : limit;
+                    continue;
+                }
+                s += __ffs(any) - 1; // the leftmost start of this window becomes lane 0: it is the next match
+            }
             // classes of positions [s, s + 48); beyond the record: class 0, which every state leaves for the dead state
             __syncwarp();
             win8[lane] = s + lane < L ? s_cls[at(s + lane)] : 0;
@@ -803,7 +970,8 @@ __device__ __forceinline__ void phase2_dfa_body(resolve_params const & p, uint16
             __syncwarp();
             uint32_t const my_s = s + lane;
             uint32_t e = 0; // 0 = no match (a match is never empty)
-            bool const active = my_s < limit && (!anchor_begin || lane == 0);
+            // with exact starts lane 0 sits on the leftmost one: its longest match is the next hit, nobody else needs to walk
+            bool const active = my_s < limit && ((!anchor_begin && !p.start_bits) || lane == 0);
             uint32_t st = active ? ncls : 0; // state 1, pre-multiplied
             {
                 uint32_t const a = win[w0], b = win[w0 + 1], c2 = win[w0 + 2], d = win[w0 + 3], f = win[w0 + 4];
@@ -871,6 +1039,99 @@ __device__ __forceinline__ void phase2_dfa_body(resolve_params const & p, uint16
     }
 }
 
+// Phase 2 when phase 1 delivered the EXACT starts (regex_scan_starts_dfa; forward strand, no anchors): a warp looks at
+// 1024 start bits of its record per step (one word per lane, one ballot), jumps to the first start at or behind the
+// resume point, lane 0 walks the matcher from there — that start IS the next match — and the search resumes at its end.
+__device__ __forceinline__ void phase2_starts_body(resolve_params const & p, uint16_t const * __restrict__ trans,
+                                                   uint8_t const * __restrict__ s_cls)
+{
+    unsigned const lane = threadIdx.x & 31;
+    uint32_t const ncls = p.dfa_classes, accept_from = p.dfa_first_accept * ncls;
+    uint64_t n_listed = *p.rec_count;
+    if (p.rec_cap && n_listed > p.rec_cap)
+        n_listed = p.rec_cap;
+    uint64_t const warp0 = (static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+    uint64_t const n_warps = (static_cast<uint64_t>(gridDim.x) * blockDim.x) >> 5;
+    for (uint64_t i = warp0; i < n_listed; i += n_warps)
+    {
+        uint64_t const r = p.rec_list[i];
+        uint64_t const rb = p.rec_offsets[r], re_off = p.rec_offsets[r + 1];
+        uint64_t g = rb; // resume point (global byte index), warp-uniform
+        while (g < re_off)
+        {
+            uint64_t const w = (g >> 5) + lane;
+            uint32_t bits = w * 32 < re_off ? __ldg(p.start_bits + w) : 0;
+            if (lane == 0)
+                bits &= ~0u << (g & 31); // starts before the resume point lie inside the previous match
+            if (w * 32 + 32 > re_off && w * 32 < re_off)
+                bits &= (re_off & 31) ? ~(~0u << (re_off & 31)) : ~0u; // the next record's starts share this word
+            unsigned const any = __ballot_sync(0xffffffffu, bits != 0);
+            if (!any)
+            {
+                g = ((g >> 5) + 32) << 5;
+                continue;
+            }
+            int const src = __ffs(any) - 1;
+            uint32_t const word = __shfl_sync(0xffffffffu, bits, src);
+            uint64_t const q = (((g >> 5) + src) << 5) + (__ffs(word) - 1); // the next match starts here
+            // the walk: every lane fetches and classifies ONE byte of the 32 behind q (one memory latency for the whole
+            // match instead of one per byte), then all lanes run the same chain on classes handed round by shuffles
+            uint32_t e = 0;
+            {
+                uint32_t const my_cl = q + lane < re_off ? s_cls[__ldg(p.text + q + lane)] : 0u; // class 0: every state dies
+                uint32_t st = ncls;
+#pragma unroll 4
+                for (int j = 0; j < 32; ++j)
+                {
+                    st = trans[st + __shfl_sync(0xffffffffu, my_cl, j)];
+                    if (st == 0)
+                        break; // warp-uniform
+                    if (st >= accept_from)
+                        e = static_cast<uint32_t>(q - rb) + j + 1;
+                }
+                if (st != 0) // a match longer than 32 bytes: byte by byte
+                {
+                    uint64_t pos = q + 32;
+                    while (pos < re_off)
+                    {
+                        st = trans[st + s_cls[__ldg(p.text + pos)]];
+                        if (st == 0)
+                            break;
+                        ++pos;
+                        if (st >= accept_from)
+                            e = static_cast<uint32_t>(pos - rb);
+                    }
+                }
+                if (lane == 0 && e != 0)
+                {
+                    unsigned long long idx = atomicAdd(p.hit_count, 1ULL);
+                    if (idx < p.cap)
+                    {
+                        uint64_t const key = (r << 32) | (q - rb);
+                        if (p.hit_pats)
+                        {
+                            p.hit_keys[idx] = key;
+                            p.hit_ends[idx] = e;
+                            p.hit_pats[idx] = p.pattern_id;
+                        }
+                        else if (idx < kSmallHits)
+                        {
+                            p.small_keys[idx] = key;
+                            p.small_ends[idx] = e;
+                        }
+                        else
+                        {
+                            p.hit_keys[idx] = key;
+                            p.hit_ends[idx] = e;
+                        }
+                    }
+                }
+            }
+            g = e != 0 ? rb + e : q + 1; // (e == 0 cannot happen for an exact start; stay safe and move on)
+        }
+    }
+}
+
 // dynamic shared memory: [256 class bytes | 16 window words per warp (4 warps) | transition table if <= kDfaSmemBytes]
 constexpr unsigned kDfaSmemBytes = 32 * 1024;
 constexpr unsigned kDfaSmemFixed = 256 + 4 * 64;
@@ -899,7 +1160,9 @@ __device__ __forceinline__ void phase2_dfa_block(resolve_params const & p, uint8
     if (threadIdx.x < 64)
         s_win_all[threadIdx.x] = 0;
     __syncthreads();
-    if (p.anchor_end)
+    if (p.start_bits && DIR > 0)
+        phase2_starts_body(p, staged ? s_trans : p.dfa_trans, s_cls);
+    else if (p.anchor_end)
         phase2_dfa_body<DIR, true>(p, staged ? s_trans : p.dfa_trans, s_cls, s_win_all + (threadIdx.x >> 5) * 16);
     else
         phase2_dfa_body<DIR, false>(p, staged ? s_trans : p.dfa_trans, s_cls, s_win_all + (threadIdx.x >> 5) * 16);

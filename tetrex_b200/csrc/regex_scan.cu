@@ -35,7 +35,7 @@ struct trx_text
         uint32_t * d_rec_flags{nullptr};   // bitmap
         uint8_t * d_counters{nullptr};     // hit count (u64), listed-record count (u32), next tile (u32)
         uint32_t * d_rec_list{nullptr};
-        trx::scratch d_stage, h_stage, h_small, d_keys, d_ends, d_tiles;
+        trx::scratch d_stage, h_stage, h_small, d_keys, d_ends, d_tiles, d_start_bits;
         uint64_t tiles_serial{0};          // plan_serial of the tile list in d_tiles
         cudaStream_t stream{nullptr};      // a stream per slot: the copies and the clear of one scan overlap the kernels of another
         cudaEvent_t done{nullptr};
@@ -245,7 +245,7 @@ void trx_text_destroy(trx_text_t * t)
         }
         if (sl.done)
             cudaEventDestroy(sl.done);
-        for (trx::scratch * s : {&sl.d_stage, &sl.h_stage, &sl.h_small, &sl.d_keys, &sl.d_ends, &sl.d_tiles})
+        for (trx::scratch * s : {&sl.d_stage, &sl.h_stage, &sl.h_small, &sl.d_keys, &sl.d_ends, &sl.d_tiles, &sl.d_start_bits})
             s->release();
     }
     for (trx::scratch * s : {&t->d_keys2, &t->d_ends2, &t->d_sort_tmp, &t->d_hits_fmt, &t->m_h_stage, &t->m_d_stage, &t->m_d_flags, &t->m_d_lists,
@@ -1356,8 +1356,8 @@ int trx_regex_scan_begin(trx_text_t * t, trx_regex_t * re, const uint64_t * cand
     size_t const off_regex = align16(off_cand + cand_words * 8);
     size_t const off_dfa = align16(off_regex + sizeof(regex_dev)); // [256 class bytes | transitions] when there is a DFA
     sl.h_stage.pinned_host = true;
-    TRX_TRY(sl.h_stage.reserve(off_dfa + 256 + kDfaMaxBytes));
-    TRX_TRY(sl.d_stage.reserve(off_dfa + 256 + kDfaMaxBytes));
+    TRX_TRY(sl.h_stage.reserve(off_dfa + 256 + kDfaMaxBytes + 16 + kReverseDfaMaxEntries * 2));
+    TRX_TRY(sl.d_stage.reserve(off_dfa + 256 + kDfaMaxBytes + 16 + kReverseDfaMaxEntries * 2));
     auto * hs = static_cast<uint8_t *>(sl.h_stage.ptr);
     memcpy(hs + off_cand, candidate_bin_words, cand_words * 8);
     auto * img = reinterpret_cast<regex_dev *>(hs + off_regex);
@@ -1365,11 +1365,20 @@ int trx_regex_scan_begin(trx_text_t * t, trx_regex_t * re, const uint64_t * cand
     uint64_t const map_hash = hash_map256(map256);
     dfa_table const * const dfa = dfa_for(*re, *img, reverse_strand, map_hash);
     size_t stage_bytes = off_dfa;
+    size_t off_rdfa = 0;
     if (dfa)
     {
         memcpy(hs + off_dfa, dfa->cls, 256);
         stage_dfa_table(*dfa, reinterpret_cast<uint16_t *>(hs + off_dfa + 256));
         stage_bytes = off_dfa + 256 + dfa->trans.size() * 2;
+        if (dfa->r_usable) // the reverse searcher: a few KB, staged whether or not this scan ends up using it
+        {
+            off_rdfa = align16(stage_bytes);
+            uint16_t * dst = reinterpret_cast<uint16_t *>(hs + off_rdfa);
+            for (size_t i = 0; i < dfa->r_trans.size(); ++i)
+                dst[i] = static_cast<uint16_t>(dfa->r_trans[i] * dfa->n_classes);
+            stage_bytes = off_rdfa + dfa->r_trans.size() * 2;
+        }
     }
     t_image = now();
 
@@ -1433,11 +1442,38 @@ int trx_regex_scan_begin(trx_text_t * t, trx_regex_t * re, const uint64_t * cand
     // lookup per byte and start) beats streaming the text through the position automaton first.  An explicit
     // TRX_REGEX_FILTER keeps the exact phase-1 kernel reachable for A/B runs and tests.
     bool const skip_phase1 = kind == kFilterNone && dfa != nullptr && use_tma && !getenv("TRX_REGEX_FILTER");
+    bool use_start_bits = false;
     t_choice = now();
     sl.filter_units = use_atoms ? static_cast<uint64_t>(sp.atoms.n_atoms)
                                 : (use_window ? static_cast<uint64_t>(sp.filter.n_a + sp.filter.n_b) : 0);
     if (tiles.empty())
         ; // nothing to scan: no kernel, the read-back below returns the zeroed counters
+    else if (skip_phase1 && dfa->r_usable && !(getenv("TRX_REGEX_STARTS") && strcmp(getenv("TRX_REGEX_STARTS"), "off") == 0))
+    {
+        // exact match starts from the reverse searcher, one bit per text byte
+        uint64_t const bits_bytes = t->n_text_padded / 8;
+        TRX_TRY(sl.d_start_bits.reserve(bits_bytes));
+        TRX_CUDA(cudaMemsetAsync(sl.d_start_bits.ptr, 0, bits_bytes, st));
+        sp.start_bits = static_cast<uint32_t *>(sl.d_start_bits.ptr);
+        sp.r_trans = reinterpret_cast<uint16_t const *>(ds + off_rdfa);
+        sp.r_cls = ds + off_dfa;
+        sp.r_classes = dfa->n_classes;
+        sp.r_states = dfa->r_states;
+        sp.r_first_accept = dfa->r_first_accept;
+        sp.r_max_len = dfa->max_len;
+        use_start_bits = true;
+        size_t const smem = kStages * kTileBytes + 256 + 16 + ((dfa->r_trans.size() * 2 + 15) & ~size_t{15});
+        static size_t attr_smem = 0;
+        if (smem > attr_smem)
+        {
+            TRX_CUDA(cudaFuncSetAttribute(regex_scan_starts_dfa, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+            attr_smem = smem;
+        }
+        unsigned const grid = static_cast<unsigned>(std::min<uint64_t>(sp.n_tiles, static_cast<uint64_t>(c->sm_count) * 2));
+        regex_scan_starts_dfa<<<grid, kScanThreads, smem, st>>>(sp, t->tmap);
+        ++c->launches;
+        TRX_CUDA(cudaGetLastError());
+    }
     else if (skip_phase1)
     {
         list_candidate_records_kernel<<<grid_for(t->n_records, 256, c->sm_count, 8), 256, 0, st>>>(
@@ -1459,7 +1495,8 @@ int trx_regex_scan_begin(trx_text_t * t, trx_regex_t * re, const uint64_t * cand
     rp.rec_offsets = t->d_rec_offsets;
     rp.rec_list = sl.d_rec_list;
     rp.rec_count = sp.rec_count;
-    rp.chunk_flags = skip_phase1 ? nullptr : sl.d_chunk_flags;
+    rp.chunk_flags = (skip_phase1 && !use_start_bits) ? nullptr : sl.d_chunk_flags;
+    rp.start_bits = use_start_bits ? static_cast<uint32_t const *>(sl.d_start_bits.ptr) : nullptr;
     rp.re = sp.re;
     rp.anchor_begin = re->anchor_begin;
     rp.anchor_end = re->anchor_end;
