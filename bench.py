@@ -531,6 +531,22 @@ def extra_measurements(t, ctx, torch, residues, offs, rec_bin, planted, hibf, pe
     os.environ.pop("TRX_REGEX_FILTER")
     out["verify_prosite"]["exact_automaton_residues_per_s"] = n_res / sec2x
     out["verify_prosite"]["hits_equal_exact_automaton"] = bool(np.array_equal(h2, h2x))
+    out["verify_prosite"]["exact_automaton_note"] = ("no prefilter: reverse-searcher DFA phase 1 (exact match starts, one table "
+                                                     "lookup per residue) + DFA phase 2")
+    os.environ["TRX_REGEX_FILTER"] = "off"
+    os.environ["TRX_REGEX_DFA"] = "off"
+    h2n = txt.scan(rx2)
+    sec2n = timed(lambda: txt.scan(rx2), 2)
+    os.environ.pop("TRX_REGEX_FILTER")
+    os.environ.pop("TRX_REGEX_DFA")
+    out["verify_prosite"]["position_automaton_residues_per_s"] = n_res / sec2n
+    out["verify_prosite"]["hits_equal_position_automaton"] = bool(np.array_equal(h2, h2n))
+    # the densest pattern of the config-3 batch: no necessary factor at all, 513 k hits
+    rx3 = t.Regex("...[GHKM]V[FHKL].", True)
+    h3 = txt.scan(rx3, cap=1 << 21)
+    sec3 = timed(lambda: txt.scan(rx3, cap=1 << 21), 3)
+    out["verify_dense"] = {"pattern": "...[GHKM]V[FHKL].", "hits": int(len(h3)), "residues_per_s": n_res / sec3,
+                           "us_per_scan": sec3 * 1e6, "note": "whole call incl. sorting and returning the hits to the host"}
     txt.close()
 
     # ---- K4 at a size where the per-call latencies (one H2D, one memset, two launches, one D2H, one sync ~ 50 us) no longer

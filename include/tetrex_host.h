@@ -72,6 +72,15 @@ void trxh_free(void *p);
  * out[j] = index into keys of the j-th item popped; returns the number of items. */
 uint64_t trxh_rank_pop_order(const uint64_t *keys, uint64_t n, uint32_t *out);
 
+/* Host only (no device): the layout seqan::hibf computes for user bins given as k-mer lists — HyperLogLog sketches
+ * (lib/hibf/src/sketch/hyperloglog.cpp), k-mer count estimates, compute_layout (every file of lib/hibf/src/layout,
+ * lib/hibf/src/sketch/toolbox.cpp) as HIBFIndex::populate_index triggers it (include/index_hibf.h:124-129).  Dump (uint64
+ * words): tmax, top_level_max_bin_id, #max_bins, per max bin {len, indices..., id}, #user_bins, per user bin {len, prev...,
+ * storage_TB_id, number_of_technical_bins, idx}, then the n_bins estimates.  Returns the number of words (may exceed cap),
+ * 0 on error. */
+uint64_t trxh_hibf_layout(const uint64_t *values, const uint64_t *bin_offsets, uint64_t n_bins, uint32_t hash_funs, float fpr,
+                          uint64_t *out, uint64_t cap);
+
 /* diagnostic: print a native backtrace on SIGSEGV */
 void trxh_debug_backtrace_on_segv(void);
 

@@ -102,6 +102,8 @@ def ref():
         lib.ref_hibf_build.restype = C.c_void_p
         lib.ref_hibf_build.argtypes = [u64p, u64p, C.c_uint64, C.c_uint32, C.c_float, C.c_int]
         lib.ref_hibf_free.argtypes = [C.c_void_p]
+        lib.ref_hibf_layout.restype = C.c_uint64
+        lib.ref_hibf_layout.argtypes = [u64p, u64p, C.c_uint64, C.c_uint32, C.c_float, C.c_int, u64p, C.c_uint64]
         lib.ref_hibf_ibf_count.restype = C.c_uint64
         lib.ref_hibf_ibf_count.argtypes = [C.c_void_p]
         lib.ref_hibf_ibf_params.argtypes = [C.c_void_p, C.c_uint64, u64p]
@@ -440,6 +442,36 @@ def ref_kgraph(regex: str, molecule: int, k: int, reduction: int = 0, augment: b
     if n < 0:
         return None
     return pf.value.decode(), [[int(sym[i]), int(fi[i]), int(se[i]), int(rk[i])] for i in range(n)]
+
+
+def parse_layout_dump(w: np.ndarray, n_bins: int) -> dict:
+    """The word dump of ref_hibf_layout / trxh_hibf_layout as a dict."""
+    w = [int(x) for x in w]
+    it = iter(w)
+    out = {"tmax": next(it), "top_level_max_bin_id": next(it), "max_bins": [], "user_bins": []}
+    for _ in range(next(it)):
+        n = next(it)
+        out["max_bins"].append(([next(it) for _ in range(n)], next(it)))
+    for _ in range(next(it)):
+        n = next(it)
+        out["user_bins"].append(([next(it) for _ in range(n)], next(it), next(it), next(it)))
+    out["kmer_counts"] = [next(it) for _ in range(n_bins)]
+    return out
+
+
+def ref_hibf_layout(values: np.ndarray, bin_offsets: np.ndarray, hash_funs: int, fpr: float, threads: int = 1) -> dict:
+    """seqan::hibf's layout (sketches, k-mer count estimates, DP, rearrangement) for user bins given as k-mer lists."""
+    values = np.ascontiguousarray(values, dtype=np.uint64)
+    offs = np.ascontiguousarray(bin_offsets, dtype=np.uint64)
+    n_bins = len(offs) - 1
+    out = np.zeros(64 + 16 * n_bins + 4096, dtype=np.uint64)
+    n = ref().ref_hibf_layout(_p(values, u64p), _p(offs, u64p), n_bins, hash_funs, fpr, threads, _p(out, u64p), len(out))
+    if n == 0:
+        raise RuntimeError(ref().ref_last_error().decode())
+    if n > len(out):
+        out = np.zeros(n, dtype=np.uint64)
+        ref().ref_hibf_layout(_p(values, u64p), _p(offs, u64p), n_bins, hash_funs, fpr, threads, _p(out, u64p), len(out))
+    return parse_layout_dump(out[:n], n_bins)
 
 
 def ref_index_build(files, k, fpr, hash_count, molecule, flavor, reduction, out_path, threads=1):

@@ -94,6 +94,11 @@
 #include <hibf/interleaved_bloom_filter.hpp>
 #include <hibf/misc/bit_vector.hpp>
 #include <hibf/misc/divide_and_ceil.hpp>
+#include <hibf/layout/compute_layout.hpp>
+#include <hibf/layout/layout.hpp>
+#include <hibf/sketch/compute_sketches.hpp>
+#include <hibf/sketch/estimate_kmer_counts.hpp>
+#include <hibf/sketch/hyperloglog.hpp>
 #include <sharg/all.hpp>
 #include <seqan3/core/debug_stream.hpp>
 #include <lemon/smart_graph.h>
@@ -329,6 +334,65 @@ void * ref_hibf_build(uint64_t const * values, uint64_t const * bin_offsets, uin
     {
         g_err = e.what();
         return nullptr;
+    }
+}
+
+// The layout alone: compute_sketches → estimate_kmer_counts → compute_layout exactly as the HIBF constructor runs them
+// (lib/hibf/src/hierarchical_interleaved_bloom_filter.cpp:212-245).  Dump (uint64 words): tmax, top_level_max_bin_id,
+// #max_bins, then per max bin {len, indices..., id}, #user_bins, then per user bin {len, prev..., storage_TB_id,
+// number_of_technical_bins, idx}, then n_bins k-mer count estimates.  Returns the number of words (may exceed cap), 0 on error.
+uint64_t ref_hibf_layout(uint64_t const * values, uint64_t const * bin_offsets, uint64_t n_bins, uint32_t hash_funs, float fpr,
+                         int threads, uint64_t * out, uint64_t cap)
+{
+    try
+    {
+        auto get_user_bin_data = [&](size_t const user_bin_id, seqan::hibf::insert_iterator it)
+        {
+            for (uint64_t i = bin_offsets[user_bin_id]; i < bin_offsets[user_bin_id + 1]; ++i)
+                it = values[i];
+        };
+        seqan::hibf::config config{.input_fn = get_user_bin_data,
+                                   .number_of_user_bins = n_bins,
+                                   .number_of_hash_functions = hash_funs,
+                                   .maximum_fpr = fpr,
+                                   .threads = static_cast<size_t>(threads < 1 ? 1 : threads)};
+        config.validate_and_set_defaults();
+        std::vector<seqan::hibf::sketch::hyperloglog> sketches{};
+        std::vector<size_t> kmer_counts{};
+        seqan::hibf::sketch::compute_sketches(config, sketches);
+        seqan::hibf::sketch::estimate_kmer_counts(sketches, kmer_counts);
+        auto layout = seqan::hibf::layout::compute_layout(config, kmer_counts, sketches);
+        std::vector<uint64_t> w;
+        w.push_back(config.tmax);
+        w.push_back(layout.top_level_max_bin_id);
+        w.push_back(layout.max_bins.size());
+        for (auto const & mb : layout.max_bins)
+        {
+            w.push_back(mb.previous_TB_indices.size());
+            for (size_t x : mb.previous_TB_indices)
+                w.push_back(x);
+            w.push_back(mb.id);
+        }
+        w.push_back(layout.user_bins.size());
+        for (auto const & ub : layout.user_bins)
+        {
+            w.push_back(ub.previous_TB_indices.size());
+            for (size_t x : ub.previous_TB_indices)
+                w.push_back(x);
+            w.push_back(ub.storage_TB_id);
+            w.push_back(ub.number_of_technical_bins);
+            w.push_back(ub.idx);
+        }
+        for (size_t c : kmer_counts)
+            w.push_back(c);
+        for (size_t i = 0; i < w.size() && i < cap; ++i)
+            out[i] = w[i];
+        return w.size();
+    }
+    catch (std::exception const & e)
+    {
+        g_err = e.what();
+        return 0;
     }
 }
 

@@ -1439,9 +1439,10 @@ int trx_regex_scan_begin(trx_text_t * t, trx_regex_t * re, const uint64_t * cand
     }
     bool const use_atoms = kind == kFilterAtoms, use_window = kind == kFilterWindow;
     // no selective necessary factor, but a determinised matcher: resolving every candidate record directly (one table
-    // lookup per byte and start) beats streaming the text through the position automaton first.  An explicit
-    // TRX_REGEX_FILTER keeps the exact phase-1 kernel reachable for A/B runs and tests.
-    bool const skip_phase1 = kind == kFilterNone && dfa != nullptr && use_tma && !getenv("TRX_REGEX_FILTER");
+    // lookup per byte and start) beats streaming the text through the position automaton first.  TRX_REGEX_DFA=off keeps
+    // the position-automaton kernels reachable for A/B runs and tests.
+    char const * const filt_env = getenv("TRX_REGEX_FILTER");
+    bool const skip_phase1 = kind == kFilterNone && dfa != nullptr && use_tma && (!filt_env || strcmp(filt_env, "off") == 0);
     bool use_start_bits = false;
     t_choice = now();
     sl.filter_units = use_atoms ? static_cast<uint64_t>(sp.atoms.n_atoms)

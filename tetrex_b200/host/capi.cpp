@@ -11,6 +11,7 @@
 
 #include "../../include/tetrex_host.h"
 #include "rh_order.hpp"
+#include "hibf_layout.hpp"
 #include "trx_host.hpp"
 
 namespace
@@ -141,6 +142,55 @@ int trxh_dindex_build(trx_ctx_t * ctx, const char * const * files, uint64_t n_fi
         if (out_path && *out_path)
             d.store(out_path);
     });
+}
+
+// Host only: seqan::hibf's layout for user bins given as k-mer lists (values[bin_offsets[b] .. bin_offsets[b+1]) in the
+// order HIBFIndex::emplace collected them): HyperLogLog sketches, k-mer count estimates, compute_layout
+// (lib/hibf/src/hierarchical_interleaved_bloom_filter.cpp:212-236).  Dump (uint64 words): tmax, top_level_max_bin_id,
+// #max_bins, per max bin {len, indices..., id}, #user_bins, per user bin {len, prev..., storage_TB_id,
+// number_of_technical_bins, idx}, then the n_bins estimates.  Returns the number of words (may exceed cap), 0 on error.
+uint64_t trxh_hibf_layout(const uint64_t * values, const uint64_t * bin_offsets, uint64_t n_bins, uint32_t hash_funs, float fpr,
+                          uint64_t * out, uint64_t cap)
+{
+    uint64_t n = 0;
+    int const rc = guarded([&] {
+        namespace h = trxh::hibf;
+        h::config cfg;
+        cfg.number_of_user_bins = n_bins;
+        cfg.number_of_hash_functions = hash_funs;
+        cfg.maximum_fpr = fpr; // float → double, like `.maximum_fpr = fpr_` (include/index_hibf.h:127)
+        cfg.validate_and_set_defaults();
+        std::vector<h::hyperloglog> sketches(n_bins, h::hyperloglog{cfg.sketch_bits});
+        std::vector<size_t> counts(n_bins);
+        for (uint64_t b = 0; b < n_bins; ++b)
+        {
+            for (uint64_t i = bin_offsets[b]; i < bin_offsets[b + 1]; ++i)
+                sketches[b].add(values[i]);
+            counts[b] = sketches[b].estimate();
+        }
+        h::layout const l = h::compute_layout(cfg, counts, sketches);
+        std::vector<uint64_t> w{cfg.tmax, l.top_level_max_bin_id, l.max_bins.size()};
+        for (auto const & mb : l.max_bins)
+        {
+            w.push_back(mb.previous_TB_indices.size());
+            w.insert(w.end(), mb.previous_TB_indices.begin(), mb.previous_TB_indices.end());
+            w.push_back(mb.id);
+        }
+        w.push_back(l.user_bins.size());
+        for (auto const & ub : l.user_bins)
+        {
+            w.push_back(ub.previous_TB_indices.size());
+            w.insert(w.end(), ub.previous_TB_indices.begin(), ub.previous_TB_indices.end());
+            w.push_back(ub.storage_TB_id);
+            w.push_back(ub.number_of_technical_bins);
+            w.push_back(ub.idx);
+        }
+        w.insert(w.end(), counts.begin(), counts.end());
+        for (size_t i = 0; i < w.size() && i < cap; ++i)
+            out[i] = w[i];
+        n = w.size();
+    });
+    return rc == 0 ? n : 0;
 }
 
 // out[0..8) = bin_count, bin_words, is_hibf, is_dna, k, shard_word_begin, shard_words, reduction
