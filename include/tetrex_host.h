@@ -81,6 +81,11 @@ uint64_t trxh_rank_pop_order(const uint64_t *keys, uint64_t n, uint32_t *out);
 uint64_t trxh_hibf_layout(const uint64_t *values, const uint64_t *bin_offsets, uint64_t n_bins, uint32_t hash_funs, float fpr,
                           uint64_t *out, uint64_t cap);
 
+/* Host only: iteration order of seqan::hibf's k-mer sets (robin_hood::unordered_flat_set<uint64_t>, lib/hibf/include/hibf/
+ * contrib/robin_hood.hpp) after a script of op[i] = 0: insert(keys[i]) / 1: clear().  insert_into_ibf cuts a split user
+ * bin into technical bins along that order (lib/hibf/src/build/insert_into_ibf.cpp:28-45), so it is part of the index. */
+uint64_t trxh_flat_set_script(const uint64_t *keys, const uint8_t *op, uint64_t n, uint64_t *out);
+
 /* diagnostic: print a native backtrace on SIGSEGV */
 void trxh_debug_backtrace_on_segv(void);
 

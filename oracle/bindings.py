@@ -141,6 +141,8 @@ def ref():
         lib.ref_re2_scan_records_hits.argtypes = [C.c_char_p, C.c_int, C.c_void_p, u64p, C.c_uint64, C.c_int, u32p, C.c_uint64]
         lib.ref_index_conjunction.restype = C.c_int
         lib.ref_index_conjunction.argtypes = [C.c_char_p, C.c_char_p, C.c_int, u64p, C.c_uint64, C.c_char_p]
+        lib.ref_flat_set_script.restype = C.c_uint64
+        lib.ref_flat_set_script.argtypes = [u64p, u8p, C.c_uint64, u64p]
         lib.ref_rh_pop_order.restype = C.c_uint64
         lib.ref_rh_pop_order.argtypes = [u64p, C.c_uint64, u32p]
         _ref = lib
@@ -526,6 +528,15 @@ def ref_scan_records_hits(pattern: str, posix_longest: bool, text: np.ndarray, r
         raise ValueError(ref().ref_last_error().decode())
     if n > cap:
         return ref_scan_records_hits(pattern, posix_longest, text, rec_offsets, threads, cap=int(n))
+    return out[:n].copy()
+
+
+def ref_flat_set_script(keys, ops) -> np.ndarray:
+    """Iteration order of hibf's robin_hood::unordered_flat_set<uint64_t> after ops[i] = 0: insert(keys[i]) / 1: clear()."""
+    k = np.ascontiguousarray(keys, dtype=np.uint64)
+    o = np.ascontiguousarray(ops, dtype=np.uint8)
+    out = np.zeros(max(len(k), 1), dtype=np.uint64)
+    n = ref().ref_flat_set_script(_p(k, u64p), _p(o, u8p), len(k), _p(out, u64p))
     return out[:n].copy()
 
 

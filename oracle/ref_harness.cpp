@@ -961,6 +961,25 @@ uint64_t ref_rh_pop_order(uint64_t const * keys, uint64_t n, uint32_t * out)
     return j;
 }
 
+// The k-mer sets of seqan::hibf's build (robin_hood::unordered_flat_set<uint64_t>, lib/hibf/include/hibf/contrib/
+// robin_hood.hpp) under a script of operations: op[i] = 0 → insert(keys[i]), 1 → clear().  Writes the final iteration
+// order (which decides how insert_into_ibf chunks a split user bin) and returns the number of elements.
+uint64_t ref_flat_set_script(uint64_t const * keys, uint8_t const * op, uint64_t n, uint64_t * out)
+{
+    robin_hood::unordered_flat_set<uint64_t> set;
+    for (uint64_t i = 0; i < n; ++i)
+    {
+        if (op[i] == 1)
+            set.clear();
+        else
+            set.insert(keys[i]);
+    }
+    uint64_t j = 0;
+    for (uint64_t v : set)
+        out[j++] = v;
+    return j;
+}
+
 } // extern "C"
 
 extern "C"

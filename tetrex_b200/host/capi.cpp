@@ -272,4 +272,21 @@ uint64_t trxh_rank_pop_order(const uint64_t * keys, uint64_t n, uint32_t * out)
     return j;
 }
 
+// Host only: hibf's k-mer set (robin_hood::unordered_flat_set<uint64_t>) under a script — op[i] = 0: insert(keys[i]),
+// 1: clear() — restated by rh_order.hpp; writes the final iteration order, returns the number of elements.
+uint64_t trxh_flat_set_script(const uint64_t * keys, const uint8_t * op, uint64_t n, uint64_t * out)
+{
+    trxh::rh_slots t;
+    for (uint64_t i = 0; i < n; ++i)
+    {
+        if (op[i] == 1)
+            t.clear_keep_capacity();
+        else
+            t.insert_key(keys[i]);
+    }
+    uint64_t j = 0;
+    t.for_each_key([&](uint64_t k) { out[j++] = k; });
+    return j;
+}
+
 } // extern "C"

@@ -240,13 +240,38 @@ void DeviceIndex::build(index_arguments const & args)
         img_.flat = build_one(ctx_, dev, lib, 0, lib.rec_bin.size(), lib.rec_bin, files.size(), bin_size, args.hash_count,
                               molecule, args.k, img_.reduction, &flat_);
     }
+    else if (!(getenv("TRX_HIBF_LAYOUT") && std::string(getenv("TRX_HIBF_LAYOUT")) == "simple"))
+    {
+        // HIBFIndex::populate_index (include/index_hibf.h:86-130): every k-mer of every bin, in decomposition order, goes to
+        // seqan::hibf — sketches, layout, hierarchical build — restated in hibf_layout.cpp / hibf_build.cpp.  The k-mers
+        // are decomposed on the device (ordered emission), the sets and the layout are host work like in the reference,
+        // every bit is set by K1.
+        uint64_t const n_records = lib.rec_bin.size();
+        std::vector<uint64_t> out_offsets(n_records + 1, 0);
+        uint64_t total = 0;
+        for (uint64_t r = 0; r < n_records; ++r)
+            total += trx_emit_count(molecule, args.k, lib.offsets[r + 1] - lib.offsets[r]);
+        std::vector<uint64_t> values(total);
+        check(trx_decompose_records(ctx_, molecule, args.k, img_.reduction, reinterpret_cast<uint8_t const *>(lib.residues.data()),
+                                    lib.offsets.data(), n_records, values.data(), values.size(), out_offsets.data()));
+        std::vector<uint64_t> bin_offsets(files.size() + 1, total);
+        {
+            uint64_t r = 0;
+            for (uint64_t b = 0; b < files.size(); ++b)
+            {
+                while (r < n_records && lib.rec_bin[r] < b)
+                    ++r;
+                bin_offsets[b] = r < n_records ? out_offsets[r] : total;
+            }
+        }
+        img_.hibf = build_hibf_like_seqan(ctx_, values, bin_offsets, args.hash_count, args.fpr, args.t);
+        upload();
+    }
     else
     {
-        // The reference hands the per-bin k-mer sets to seqan::hibf's layout algorithm (sketching + DP,
-        // lib/hibf/src/layout/*), which is outside the probe/verify path (DESIGN.md "out of scope").  The layout used
-        // here is the plain two-level one: T = 64*ceil(sqrt(n)/64) technical bins on top; with n <= T every user bin
-        // gets its own technical bin, otherwise consecutive user bins share a merged bin that owns a lower-level IBF.
-        // Membership answers are a superset of the truth either way, and verify prints exactly the true matches.
+        // TRX_HIBF_LAYOUT=simple: the plain two-level layout of round 1 (no sketches, no split bins) — T = 64*ceil(sqrt(n)/64)
+        // technical bins on top; with n <= T every user bin gets its own technical bin, otherwise consecutive user bins share
+        // a merged bin that owns a lower-level IBF.  A valid seqan archive whose false positives differ from the reference's.
         uint64_t const n = files.size();
         uint64_t const T = 64 * static_cast<uint64_t>(std::ceil(std::sqrt(static_cast<double>(n)) / 64.0));
         hibf_image & h = img_.hibf;

@@ -3,6 +3,7 @@
 //   tetrex kgraph [-n] [-r murphy|li] -k K REGEX      postfix string + every node of the k-graph
 //   tetrex bins [-a] [-g DINDEX] IDX REGEX            the candidate bins of process_query, one index per line
 //   tetrex dindex-rewrite IN OUT                      DGram index file → image → file (host only)
+//   tetrex hibf-canon IDX                             numbering-independent dump of a HIBF index file (host only)
 // Unlike the reference (molecule_/ibf_ are frozen before parsing, so its -n and -i are dead) the
 // flags take effect here.
 #include <cstring>
@@ -270,6 +271,43 @@ int run_dindex_rewrite(arg_reader a)
     return 0;
 }
 
+// Canonical, numbering-independent description of a HIBF index file: a depth-first walk from the root that prints, for
+// every IBF, its geometry and a hash of its bit matrix, and for every technical bin the user bin it belongs to or the
+// IBF below it.  Two files with the same output answer every membership query identically (the reference numbers its
+// IBFs in a shuffled order, lib/hibf/src/hierarchical_interleaved_bloom_filter.cpp:118-121, so files cannot be compared
+// byte for byte).
+void canon_ibf(index_image const & img, uint64_t id, std::string const & indent)
+{
+    ibf_image const & f = img.hibf.ibf_vector[id];
+    uint64_t h = 1469598103934665603ull;
+    for (uint64_t w : f.words)
+        h = (h ^ w) * 1099511628211ull;
+    std::cout << indent << "ibf bins " << f.bins << " technical " << f.technical_bins << " bin_size " << f.bin_size << " hash_funs "
+              << f.hash_funs << " words " << f.words.size() << " fnv " << h << "\n";
+    auto const & next = img.hibf.next_ibf_id[id];
+    auto const & ub = img.hibf.ibf_bin_to_user_bin_id[id];
+    for (size_t tb = 0; tb < next.size(); ++tb)
+    {
+        if (next[tb] != id)
+        {
+            std::cout << indent << " tb " << tb << " merged\n";
+            canon_ibf(img, next[tb], indent + "  ");
+        }
+        else
+            std::cout << indent << " tb " << tb << " user_bin " << static_cast<int64_t>(ub[tb]) << "\n";
+    }
+}
+
+int run_hibf_canon(arg_reader a)
+{
+    index_image img = read_index(a.next("index"));
+    if (!img.is_hibf)
+        throw error("not a HIBF index");
+    std::cout << "user_bins " << img.hibf.number_of_user_bins << " ibfs " << img.hibf.ibf_vector.size() << "\n";
+    canon_ibf(img, 0, "");
+    return 0;
+}
+
 void usage()
 {
     std::cerr << "tetrex - regular expression search over (H)IBF-indexed sequence libraries (B200 build)\n"
@@ -307,6 +345,7 @@ int main(int argc, char ** argv)
         if (cmd == "kgraph") return run_kgraph(a);
         if (cmd == "bins") return run_bins(a);
         if (cmd == "dindex-rewrite") return run_dindex_rewrite(a);
+        if (cmd == "hibf-canon") return run_hibf_canon(a);
         if (cmd == "dindex") return run_dindex(a);
         if (cmd == "model")
         {

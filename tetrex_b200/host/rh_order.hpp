@@ -16,6 +16,7 @@
 // tests/test_host_cpu.py drives it against the real container through oracle/_ref (ref_rh_pop_order).
 #pragma once
 
+#include <algorithm>
 #include <cstdint>
 #include <stdexcept>
 #include <vector>
@@ -37,6 +38,19 @@ public:
         inc_ = 32;
         shift_ = 0;
         mult_ = UINT64_C(0xc4ceb9fe1a85ec53);
+    }
+    // Table::clear() (include/robin_hood.h:1682-1700): the elements go, the array keeps its size, the info counters start
+    // over; the element limit and the hash multiplier stay as they were — a set that was big once keeps iterating in the
+    // order of a big table
+    void clear_keep_capacity()
+    {
+        if (num_ == 0)
+            return;
+        num_ = 0;
+        std::fill(info_.begin(), info_.end(), uint8_t{0});
+        info_[with_buffer_] = 1;
+        inc_ = 32;
+        shift_ = 0;
     }
     bool empty() const { return num_ == 0; }
     size_t size() const { return num_; }

@@ -128,6 +128,12 @@ struct dgram_image
 void write_dindex(dgram_image const & img, std::string const & path);
 dgram_image read_dindex(std::string const & path);
 
+// seqan::hibf::hierarchical_interleaved_bloom_filter{config} (lib/hibf/src/hierarchical_interleaved_bloom_filter.cpp:212-245)
+// for user bins given as k-mer lists in HIBFIndex::emplace order (user bin b = values[offsets[b], offsets[b+1])): the
+// reference's sketches, layout and hierarchical build (hibf_layout.cpp, hibf_build.cpp) with K1 setting the bits.
+hibf_image build_hibf_like_seqan(trx_ctx_t * ctx, std::vector<uint64_t> const & values, std::vector<uint64_t> const & offsets,
+                                 size_t hash_count, float fpr, size_t threads);
+
 void write_index(index_image const & img, std::string const & path);
 index_image read_index(std::string const & path);
 // index_params / load_params (include/index_base.h:5-16,197-202): only the three leading fields
