@@ -156,6 +156,18 @@ int trx_dgram_emplace(trx_ibf_t *ibf, const uint8_t *residues, const uint64_t *r
 int trx_dgram_emplace_dev(trx_ibf_t *ibf, const uint8_t *d_residues, uint64_t n_residues, const uint64_t *d_rec_offsets,
                           const uint32_t *d_rec_bin, uint64_t n_records, uint32_t min_gap, uint32_t max_gap);
 
+/* N3 — seqan::hibf::sketch::compute_sketches (lib/hibf/src/sketch/compute_sketches.cpp:27-43) with hyperloglog::add
+ * (lib/hibf/src/sketch/hyperloglog.cpp:54-70) fused into K1's decomposition: the HyperLogLog sketch of every user bin,
+ * straight from the residues, over exactly the k-mers HIBFIndex::emplace would buffer (include/index_hibf.h:81-84,110-114).
+ * registers: n_bins << sketch_bits bytes (bin b's sketch at b << sketch_bits), seqan's register layout; sketch_bits 5..20
+ * (the reference uses 12).  The layout algorithm that consumes them runs on the host (tetrex_b200/host/hibf_layout.cpp). */
+int trx_hll_sketch_records(trx_ctx_t *ctx, int molecule, uint32_t k, int reduction, const uint8_t *residues,
+                           const uint64_t *rec_offsets, const uint32_t *rec_bin, uint64_t n_records, uint64_t n_bins,
+                           uint32_t sketch_bits, uint8_t *registers);
+int trx_hll_sketch_records_dev(trx_ctx_t *ctx, int molecule, uint32_t k, int reduction, const uint8_t *d_residues,
+                               uint64_t n_residues, const uint64_t *d_rec_offsets, const uint32_t *d_rec_bin,
+                               uint64_t n_records, uint64_t n_bins, uint32_t sketch_bits, uint8_t *d_registers);
+
 /* K2 — containment_agent_type::bulk_contains (…cpp:203-290) / IBFIndex::query (index_ibf.h:146-150)
  * for a batch: out_words[i*shard_words + w] = AND_h row_h(kmers[i])[w]. */
 int trx_bulk_contains(trx_ibf_t *ibf, const uint64_t *kmers, uint64_t n, uint64_t *out_words);

@@ -706,6 +706,30 @@ def golden_kgraph_aug():
           sum(1 for c in cases if sum(1 for n in c["nodes"] if n[0] == 259) > 1), "with several")
 
 
+LAYOUT_CASES = [(1, 5, 300, 0, 0, 3, 0.05), (2, 12, 2000, 1, 0, 3, 0.05), (3, 64, 500, 1, 1, 2, 0.05), (4, 65, 500, 0, 1, 3, 0.01),
+                (5, 70, 800, 1, 0, 3, 0.05), (6, 130, 300, 1, 1, 3, 0.05), (7, 300, 400, 1, 1, 4, 0.05), (8, 600, 150, 1, 0, 3, 0.05)]
+
+
+def golden_hibf_layout():
+    """seqan::hibf's layout (HyperLogLog estimates, size sort + clustering, DP, lower levels) for seeded collections
+    (synth.layout_collection), one thread; and iteration orders of its k-mer set under seeded insert/clear scripts
+    (synth.set_script)."""
+    import hashlib
+    from tetrex_b200 import synth
+    out = {"layouts": [], "set_scripts": []}
+    for seed, n_bins, mean, ov, sk, hf, fpr in LAYOUT_CASES:
+        v, o = synth.layout_collection(seed, n_bins, mean, ov, sk)
+        lay = ob.ref_hibf_layout(v, o, hf, fpr, 1)
+        out["layouts"].append(dict(seed=seed, n_bins=n_bins, mean=mean, overlap=ov, skew=sk, hash_funs=hf, fpr=fpr, layout=lay))
+    for seed in range(100, 116):
+        keys, ops = synth.set_script(seed)
+        order = ob.ref_flat_set_script(keys, ops)
+        out["set_scripts"].append(dict(seed=seed, operations=len(keys), n=len(order), sha256=hashlib.sha256(order.tobytes()).hexdigest(),
+                                       head=[str(int(x)) for x in order[:8]]))
+    json.dump(out, open(os.path.join(OUT, "hibf_layout.json"), "w"), separators=(",", ":"))
+    print("hibf_layout.json:", len(out["layouts"]), "layouts,", len(out["set_scripts"]), "set scripts")
+
+
 def golden_rh_order():
     """Pop orders of the real robin_hood::unordered_map for key lists shaped like a rank's sub-k-mer keys."""
     rng = random.Random(99)
@@ -720,7 +744,7 @@ def golden_rh_order():
 
 STEPS = {"decompose": golden_decompose, "ibf": golden_ibf, "hibf": golden_hibf, "regex": golden_regex,
          "kgraph": golden_kgraph, "cli": golden_cli, "c1": golden_c1, "collector_fuzz": golden_collector_fuzz, "rh_order": golden_rh_order,
-         "prosite_batch": golden_prosite_batch, "c2_twin_hibf": golden_c2_twin_hibf, "cli_ws": golden_cli_ws, "prosite_filter": golden_prosite_filter, "cli_conj": golden_cli_conj, "dgram": golden_dgram, "kgraph_aug": golden_kgraph_aug}
+         "prosite_batch": golden_prosite_batch, "c2_twin_hibf": golden_c2_twin_hibf, "cli_ws": golden_cli_ws, "prosite_filter": golden_prosite_filter, "cli_conj": golden_cli_conj, "dgram": golden_dgram, "kgraph_aug": golden_kgraph_aug, "hibf_layout": golden_hibf_layout}
 
 if __name__ == "__main__":
     assert ob.have_ref(), "build oracle/_ref first: make -C oracle ref"

@@ -79,3 +79,33 @@ def test_config2_twin_hibf_equals_live_reference_build(tmp_path):
         words, _ = ob.guarded(ob.ref_index_query, str(tmp_path / "ref.ibf"), q, False)
         want = [b for b in range(1024) if int(words[b // 64]) >> (b % 64) & 1]
         assert got == want, q
+
+
+def test_device_sketches_equal_hyperloglog_of_the_emitted_kmers(ctx):
+    """trx_hll_sketch_records (K1's decomposition with a HyperLogLog sink) against hyperloglog::add
+    (lib/hibf/src/sketch/hyperloglog.cpp:54-70) applied to the oracle's decompose_record output: registers bit-exact, DNA
+    (wrap-around k-mers included) and peptides, ragged records, an empty bin."""
+    import tetrex_b200 as t
+    from oracle import bindings as ob
+    rng = np.random.default_rng(8)
+
+    def sketch(values, bits=12):
+        reg = np.zeros(1 << bits, dtype=np.uint8)
+        for v in values:
+            p = int(v) * 0x9E3779B97F4A7C15
+            h = (p & 0xFFFFFFFFFFFFFFFF) ^ (p >> 64)
+            rest = ((h << bits) & 0xFFFFFFFFFFFFFFFF) | ((1 << bits) - 1)
+            rank = 64 - rest.bit_length() + 1
+            idx = h >> (64 - bits)
+            reg[idx] = max(reg[idx], rank)
+        return reg
+    for mol, k, red, alpha in [(t.MOL_AA, 6, 0, b"ACDEFGHIKLMNPQRSTVWY"), (t.MOL_NA, 8, 0, b"ACGT"), (t.MOL_AA, 4, 1, b"ACDEFGHIKLMNPQRSTVWY")]:
+        recs = [bytes(rng.choice(np.frombuffer(alpha, dtype=np.uint8), n)) for n in [300, 3, 0, 1500, 77, 2000, 9, 640]]
+        rec_bin = np.array([0, 0, 1, 1, 3, 3, 3, 4], dtype=np.uint32)  # bin 2 stays empty
+        offs = np.concatenate([[0], np.cumsum([len(r) for r in recs])]).astype(np.uint64)
+        got = t.hll_sketch_records(ctx, mol, k, red, b"".join(recs), offs, rec_bin, 5)
+        for b in range(5):
+            vals = np.concatenate([ob.decompose(mol, k, red, r) for r, rb in zip(recs, rec_bin) if rb == b and len(r) >= k] or
+                                  [np.zeros(0, dtype=np.uint64)])
+            assert np.array_equal(got[b], sketch(vals)), (mol, k, b)
+        assert not got[2].any() and got[0].any()

@@ -5,7 +5,7 @@ The product is the CUDA library ``tetrex_b200/lib/libtetrex_cuda.so`` behind the
 There is no CPU fallback: importing works anywhere, using it needs the built library and a B200.
 """
 from ._abi import LIB_PATH, TetrexError, lib  # noqa: F401
-from .api import (HIBF, IBF, dgram_count, Comm, MOL_AA, MOL_NA, RED_BASE, RED_LI, RED_MURPHY, Context, Paths, Regex, Text,  # noqa: F401
+from .api import (HIBF, IBF, dgram_count, hll_sketch_records, Comm, MOL_AA, MOL_NA, RED_BASE, RED_LI, RED_MURPHY, Context, Paths, Regex, Text,  # noqa: F401
                   compute_bitcount, emit_count, peptide_maps)
 
 __version__ = "0.1.0"

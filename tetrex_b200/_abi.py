@@ -62,6 +62,9 @@ PROTOTYPES = {
     "trx_dgram_count_dev": (C.c_int, [vp, vp, C.c_uint64, vp, vp, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint64, vp]),
     "trx_dgram_emplace": (C.c_int, [vp, vp, vp, vp, C.c_uint64, C.c_uint32, C.c_uint32]),
     "trx_dgram_emplace_dev": (C.c_int, [vp, vp, C.c_uint64, vp, vp, C.c_uint64, C.c_uint32, C.c_uint32]),
+    "trx_hll_sketch_records": (C.c_int, [vp, C.c_int, C.c_uint32, C.c_int, vp, vp, vp, C.c_uint64, C.c_uint64, C.c_uint32, vp]),
+    "trx_hll_sketch_records_dev": (C.c_int, [vp, C.c_int, C.c_uint32, C.c_int, vp, C.c_uint64, vp, vp, C.c_uint64, C.c_uint64,
+                                             C.c_uint32, vp]),
     "trx_bulk_contains": (C.c_int, [vp, vp, C.c_uint64, vp]),
     "trx_bulk_contains_dev": (C.c_int, [vp, vp, C.c_uint64, vp]),
     "trx_bulk_contains_noalloc": (C.c_int, [vp, vp, C.c_uint64, vp]),

@@ -152,6 +152,17 @@ def dgram_count(ctx, residues, rec_offsets, rec_bin, min_gap: int, max_gap: int,
     return out
 
 
+def hll_sketch_records(ctx, molecule, k, reduction, residues, rec_offsets, rec_bin, n_bins: int, sketch_bits: int = 12) -> np.ndarray:
+    """compute_sketches (lib/hibf/src/sketch/compute_sketches.cpp:27-43) on the device: (n_bins, 2**sketch_bits) uint8."""
+    res = np.frombuffer(residues, dtype=np.uint8) if isinstance(residues, (bytes, bytearray)) else _np(residues, np.uint8)
+    offs = _np(rec_offsets, np.uint64)
+    rb = _np(rec_bin, np.uint32)
+    out = np.zeros((n_bins, 1 << sketch_bits), dtype=np.uint8)
+    check(lib().trx_hll_sketch_records(ctx._h, molecule, k, reduction, _ptr(res), _ptr(offs), _ptr(rb), len(rb), n_bins, sketch_bits,
+                                       _ptr(out)))
+    return out
+
+
 class IBF:
     """Flat interleaved Bloom filter resident in HBM (seqan::hibf::interleaved_bloom_filter)."""
 

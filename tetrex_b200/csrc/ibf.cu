@@ -11,7 +11,8 @@ namespace trx
 static ibf_geom geom_of(trx_ibf const * f)
 {
     return ibf_geom{f->d_words, f->bin_size, f->shard_words, f->shard_word_begin,
-                    static_cast<uint32_t>(f->hash_shift), static_cast<uint32_t>(f->hash_funs), 0, f->bin_size, nullptr, 0, 0};
+                    static_cast<uint32_t>(f->hash_shift), static_cast<uint32_t>(f->hash_funs), 0, f->bin_size, nullptr, 0, 0,
+                    nullptr, 0};
 }
 
 // host-buffer entry points of the path algebra go zero-copy (pinned host memory read by the kernel) up to this many items
@@ -433,6 +434,82 @@ int trx_emplace_records(trx_ibf_t * f, int molecule, uint32_t k, int reduction, 
     TRX_TRY(emplace_records_impl(f, molecule, k, reduction, static_cast<uint8_t *>(c->d_in[0].ptr), n_res,
                                  static_cast<uint64_t *>(c->d_in[1].ptr), static_cast<uint32_t *>(c->d_in[2].ptr), n_records,
                                  bin_lo, static_cast<uint64_t>(bin_hi) - bin_lo + 1));
+    TRX_CUDA(cudaStreamSynchronize(c->stream));
+    return TRX_OK;
+}
+
+static int check_record_table(const uint64_t * rec_offsets, const uint32_t * rec_bin, uint64_t n_records, uint64_t n_bins);
+static int stage_records(trx_ctx * c, const uint8_t * residues, const uint64_t * rec_offsets, const uint32_t * rec_bin,
+                         uint64_t n_records);
+
+// N3 — compute_sketches (lib/hibf/src/sketch/compute_sketches.cpp:27-43): the HyperLogLog sketch of every user bin,
+// straight from the residues with K1's decomposition (so a sketch sees exactly the k-mers HIBFIndex::emplace would buffer,
+// duplicates and wrap-around k-mers included).  d_registers: n_bins << sketch_bits bytes, seqan's register layout.
+int trx_hll_sketch_records_dev(trx_ctx_t * c, int molecule, uint32_t k, int reduction, const uint8_t * d_residues,
+                               uint64_t n_residues, const uint64_t * d_rec_offsets, const uint32_t * d_rec_bin, uint64_t n_records,
+                               uint64_t n_bins, uint32_t sketch_bits, uint8_t * d_registers)
+{
+    if (!c || !d_registers || n_bins == 0)
+        return set_error(TRX_EINVAL, "NULL argument");
+    if (sketch_bits < 5 || sketch_bits > 20)
+        return set_error(TRX_ERANGE, "sketch_bits %u outside [5, 20]", sketch_bits);
+    TRX_TRY(check_kmer_args(molecule, k));
+    TRX_TRY(c->use());
+    uint64_t const n_regs = n_bins << sketch_bits;
+    TRX_TRY(c->d_out[1].reserve(n_regs * 4));
+    auto * d_regs = static_cast<unsigned int *>(c->d_out[1].ptr);
+    TRX_CUDA(cudaMemsetAsync(d_regs, 0, n_regs * 4, c->stream));
+    if (n_records && n_residues)
+    {
+        if (!d_residues || !d_rec_offsets || !d_rec_bin)
+            return set_error(TRX_EINVAL, "NULL argument");
+        ibf_geom g{};
+        g.bin_size = 1;
+        g.shard_words = (n_bins + 63) / 64;
+        g.hash_funs = 1;
+        g.row_hi = 1;
+        g.hll = d_regs;
+        g.hll_bits = sketch_bits;
+        uint32_t const dna_run = 64;
+        uint64_t const per_thread = molecule == TRX_MOL_NA ? dna_run : static_cast<uint32_t>(kRun);
+        unsigned const grid = grid_for((n_residues + per_thread - 1) / per_thread, 256, c->sm_count, 8);
+        if (molecule == TRX_MOL_NA)
+            emplace_dna_kernel<<<grid, 256, 0, c->stream>>>(g, d_residues, n_residues, d_rec_offsets, d_rec_bin, n_records, k, dna_run);
+        else
+        {
+            uint8_t * d_map = nullptr;
+            TRX_TRY(upload_aamap(c, reduction, &d_map));
+            emplace_records_kernel<TRX_MOL_AA><<<grid, 256, 0, c->stream>>>(g, d_residues, n_residues, d_rec_offsets, d_rec_bin,
+                                                                            n_records, k, d_map);
+        }
+        ++c->launches;
+        TRX_CUDA(cudaGetLastError());
+    }
+    hll_pack_kernel<<<grid_for(n_regs, 256, c->sm_count, 8), 256, 0, c->stream>>>(d_regs, d_registers, n_regs);
+    ++c->launches;
+    TRX_CUDA(cudaGetLastError());
+    return TRX_OK;
+}
+
+int trx_hll_sketch_records(trx_ctx_t * c, int molecule, uint32_t k, int reduction, const uint8_t * residues,
+                           const uint64_t * rec_offsets, const uint32_t * rec_bin, uint64_t n_records, uint64_t n_bins,
+                           uint32_t sketch_bits, uint8_t * registers)
+{
+    if (!c || !registers || n_bins == 0 || (n_records && (!residues || !rec_offsets || !rec_bin)))
+        return set_error(TRX_EINVAL, "NULL argument");
+    TRX_TRY(c->use());
+    uint64_t const n_regs = n_bins << sketch_bits;
+    TRX_TRY(c->d_out[0].reserve(n_regs));
+    if (n_records)
+    {
+        TRX_TRY(check_record_table(rec_offsets, rec_bin, n_records, n_bins));
+        TRX_TRY(stage_records(c, residues, rec_offsets, rec_bin, n_records));
+    }
+    TRX_TRY(trx_hll_sketch_records_dev(c, molecule, k, reduction, static_cast<uint8_t *>(c->d_in[0].ptr),
+                                       n_records ? rec_offsets[n_records] : 0, static_cast<uint64_t *>(c->d_in[1].ptr),
+                                       static_cast<uint32_t *>(c->d_in[2].ptr), n_records, n_bins, sketch_bits,
+                                       static_cast<uint8_t *>(c->d_out[0].ptr)));
+    TRX_CUDA(cudaMemcpyAsync(registers, c->d_out[0].ptr, n_regs, cudaMemcpyDeviceToHost, c->stream));
     TRX_CUDA(cudaStreamSynchronize(c->stream));
     return TRX_OK;
 }

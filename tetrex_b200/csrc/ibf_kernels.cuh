@@ -24,6 +24,10 @@ struct ibf_geom
     // slab into the matrix afterwards (slab_merge_kernel).  nullptr = everything goes to `words`.
     uint64_t * slab;
     uint64_t slab_words, slab_begin;
+    // N3, optional: HyperLogLog sketching instead of emplacing (trx_hll_sketch_records): one sketch of 2^hll_bits 32-bit
+    // registers per bin; every emitted k-mer updates a register of its bin's sketch.  nullptr = emplace.
+    unsigned int * hll;
+    uint32_t hll_bits;
 };
 
 // ------------------------------------------------------------------------------------------- K2
@@ -273,8 +277,15 @@ struct emplace_sink
     bool mine;
     uint64_t * base;
     uint64_t stride;
+    unsigned int * sketch; // HLL mode: this bin's registers
     __device__ __forceinline__ void set_bin(uint32_t b)
     {
+        if (g.hll)
+        {
+            sketch = g.hll + (static_cast<uint64_t>(b) << g.hll_bits);
+            mine = true;
+            return;
+        }
         uint64_t c = b >> 6;
         mine = c >= g.word_begin && c < g.word_begin + g.shard_words;
         col = c - g.word_begin;
@@ -298,6 +309,16 @@ struct emplace_sink
     {
         if (!mine)
             return;
+        if (g.hll)
+        {
+            // seqan::hibf::sketch::hyperloglog::add (lib/hibf/src/sketch/hyperloglog.cpp:54-70): 64x64→128 multiply folded
+            // to 64 bits, top bits = register, rank = leading zeros of the rest + 1
+            uint64_t const lo = v * 0x9E3779B97F4A7C15ULL, hi = __umul64hi(v, 0x9E3779B97F4A7C15ULL);
+            uint64_t const hash = lo ^ hi;
+            uint64_t const rest = (hash << g.hll_bits) | ((1ULL << g.hll_bits) - 1);
+            atomicMax(sketch + (hash >> (64 - g.hll_bits)), static_cast<unsigned int>(__clzll(static_cast<long long>(rest)) + 1));
+            return;
+        }
         if (g.bin_size >> 32 == 0)
         {
             uint64_t const bs = static_cast<uint32_t>(g.bin_size);
@@ -348,6 +369,14 @@ __global__ void __launch_bounds__(256)
         uint64_t * const dst = matrix + r * shard_words + col0 + j;
         *dst |= v;
     }
+}
+
+// 32-bit sketch registers → the bytes seqan's hyperloglog keeps
+__global__ void __launch_bounds__(256) hll_pack_kernel(unsigned int const * __restrict__ regs, uint8_t * __restrict__ out, uint64_t n)
+{
+    for (uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+         i += static_cast<uint64_t>(gridDim.x) * blockDim.x)
+        out[i] = static_cast<uint8_t>(regs[i]);
 }
 
 constexpr int kRun = 16;          // residues per thread = one LDG.128

@@ -207,7 +207,7 @@ struct builder
 
 // hierarchical_interleaved_bloom_filter{config} (…cpp:212-245) for user bins given as k-mer lists
 hibf_image build_hibf_like_seqan(trx_ctx_t * ctx, std::vector<uint64_t> const & values, std::vector<uint64_t> const & offsets,
-                                 size_t hash_count, float fpr, size_t threads)
+                                 size_t hash_count, float fpr, size_t threads, std::vector<uint8_t> const * sketch_registers)
 {
     hibf::config cfg;
     cfg.number_of_user_bins = offsets.size() - 1;
@@ -218,10 +218,17 @@ hibf_image build_hibf_like_seqan(trx_ctx_t * ctx, std::vector<uint64_t> const & 
 
     std::vector<hibf::hyperloglog> sketches(cfg.number_of_user_bins, hibf::hyperloglog{cfg.sketch_bits});
     std::vector<size_t> kmer_counts(cfg.number_of_user_bins);
+    size_t const sketch_size = size_t{1} << cfg.sketch_bits;
+    if (sketch_registers && sketch_registers->size() != cfg.number_of_user_bins * sketch_size)
+        throw error("sketch registers: expected " + std::to_string(cfg.number_of_user_bins * sketch_size) + " bytes");
     for (size_t b = 0; b < cfg.number_of_user_bins; ++b)
     {
-        for (uint64_t i = offsets[b]; i < offsets[b + 1]; ++i)
-            sketches[b].add(values[i]);
+        if (sketch_registers) // sketched on the device (trx_hll_sketch_records_dev)
+            std::copy(sketch_registers->begin() + b * sketch_size, sketch_registers->begin() + (b + 1) * sketch_size,
+                      sketches[b].registers().begin());
+        else
+            for (uint64_t i = offsets[b]; i < offsets[b + 1]; ++i)
+                sketches[b].add(values[i]);
         kmer_counts[b] = sketches[b].estimate();
         if (kmer_counts[b] == 0)
             throw error("user bin " + std::to_string(b) + " holds no k-mer: the HIBF layout needs at least one per bin");

@@ -264,7 +264,22 @@ void DeviceIndex::build(index_arguments const & args)
                 bin_offsets[b] = r < n_records ? out_offsets[r] : total;
             }
         }
-        img_.hibf = build_hibf_like_seqan(ctx_, values, bin_offsets, args.hash_count, args.fpr, args.t);
+        // compute_sketches on the device: K1's decomposition with a HyperLogLog sink (N3)
+        std::vector<uint8_t> registers(files.size() << 12);
+        {
+            void * d_regs = nullptr;
+            check(trx_dev_alloc(ctx_, registers.size(), &d_regs));
+            check(trx_copy_h2d(ctx_, dev.offsets, lib.offsets.data(), lib.offsets.size() * 8));
+            check(trx_copy_h2d(ctx_, dev.rec_bin, lib.rec_bin.data(), lib.rec_bin.size() * 4));
+            int const rc = trx_hll_sketch_records_dev(ctx_, molecule, args.k, img_.reduction, static_cast<uint8_t *>(dev.residues),
+                                                      lib.residues.size(), static_cast<uint64_t *>(dev.offsets),
+                                                      static_cast<uint32_t *>(dev.rec_bin), n_records, files.size(), 12,
+                                                      static_cast<uint8_t *>(d_regs));
+            int const rc2 = rc == TRX_OK ? trx_copy_d2h(ctx_, registers.data(), d_regs, registers.size()) : rc;
+            trx_dev_free(ctx_, d_regs);
+            check(rc2);
+        }
+        img_.hibf = build_hibf_like_seqan(ctx_, values, bin_offsets, args.hash_count, args.fpr, args.t, &registers);
         upload();
     }
     else

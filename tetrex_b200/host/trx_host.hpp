@@ -131,8 +131,10 @@ dgram_image read_dindex(std::string const & path);
 // seqan::hibf::hierarchical_interleaved_bloom_filter{config} (lib/hibf/src/hierarchical_interleaved_bloom_filter.cpp:212-245)
 // for user bins given as k-mer lists in HIBFIndex::emplace order (user bin b = values[offsets[b], offsets[b+1])): the
 // reference's sketches, layout and hierarchical build (hibf_layout.cpp, hibf_build.cpp) with K1 setting the bits.
+// sketch_registers (optional): the user bins' HyperLogLog sketches (12 bits, one after the other) when they were computed
+// on the device (trx_hll_sketch_records_dev); otherwise they are computed here from the lists.
 hibf_image build_hibf_like_seqan(trx_ctx_t * ctx, std::vector<uint64_t> const & values, std::vector<uint64_t> const & offsets,
-                                 size_t hash_count, float fpr, size_t threads);
+                                 size_t hash_count, float fpr, size_t threads, std::vector<uint8_t> const * sketch_registers = nullptr);
 
 void write_index(index_image const & img, std::string const & path);
 index_image read_index(std::string const & path);

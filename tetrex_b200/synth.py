@@ -210,3 +210,39 @@ def build_swissprot_hibf(ibf_factory, residues, rec_offsets, rec_bin, n_bins: in
         tables["user_bin"].append((j * pm + np.arange(t_max) // split).astype(np.uint64))
         f.close()
     return tables
+
+
+def layout_collection(seed: int, n_bins: int, mean: int, overlap: int, skew: int):
+    """Seeded user bins as k-mer lists (values, offsets): sizes uniform or heavy-tailed, neighbours optionally sharing half
+    their k-mers — input of the HIBF layout tests (tests/golden/hibf_layout.json)."""
+    rng = np.random.default_rng(seed)
+    pool = rng.integers(0, 2 ** 40, size=int(mean * n_bins * 1.5) + 10, dtype=np.uint64)
+    vals, offs = [], [0]
+    for b in range(n_bins):
+        sz = max(1, int(mean * (rng.pareto(2) + 0.2 if skew else rng.uniform(0.5, 1.5))))
+        if overlap and b % 3 and vals:
+            base = vals[-1][:sz // 2]
+            v = np.concatenate([base, rng.choice(pool, sz - len(base))])
+        else:
+            v = rng.integers(0, 2 ** 40, size=sz, dtype=np.uint64)
+        vals.append(v.astype(np.uint64))
+        offs.append(offs[-1] + len(v))
+    return np.concatenate(vals), np.array(offs, dtype=np.uint64)
+
+
+def set_script(seed: int):
+    """Seeded script for a hash-set emulation test: (keys, ops) with ops[i] = 0: insert keys[i], 1: clear; a few segments of
+    3 .. 120 000 keys, some with duplicates, most followed by a clear."""
+    rng = np.random.default_rng(seed)
+    keys, ops = [], []
+    for _ in range(int(rng.integers(1, 5))):
+        n = int(rng.choice([3, 50, 700, 9000, 120000]))
+        k = rng.integers(0, 2 ** int(rng.choice([30, 40, 63])), size=n, dtype=np.uint64)
+        if rng.random() < 0.5:
+            k = np.concatenate([k, k[:n // 3]])
+        keys.append(k)
+        ops.append(np.zeros(len(k), dtype=np.uint8))
+        if rng.random() < 0.7:
+            keys.append(np.zeros(1, dtype=np.uint64))
+            ops.append(np.ones(1, dtype=np.uint8))
+    return np.concatenate(keys), np.concatenate(ops)
