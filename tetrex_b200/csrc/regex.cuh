@@ -40,6 +40,7 @@ struct dfa_table
     uint32_t n_states{0}, n_classes{0}, first_accept{0};
     uint8_t cls[256]{};
     std::vector<uint16_t> trans; // n_states x n_classes
+    std::vector<uint8_t> start_class; // [n_classes]: 1 = a byte of this class can begin a match
     // Reverse searcher over the same classes: read the text BACKWARDS with a new match end injected at every byte
     // (state 0 = nothing live); a state >= r_first_accept after consuming text[p] means "some match starts at p".
     // Only for patterns whose matches have a bounded length (max_len; no '*' / '+') and no anchors: a scan of one 128-byte

@@ -963,8 +963,17 @@ __device__ __forceinline__ void phase2_dfa_body(resolve_params const & p, uint16
                 s += __ffs(any) - 1; // the leftmost start of this window becomes lane 0: it is the next match
             }
             // classes of positions [s, s + 48); beyond the record: class 0, which every state leaves for the dead state
+            uint32_t const my_cl = s + lane < L ? s_cls[at(s + lane)] : 0u;
+            // most windows of 32 hold no byte a match can start with: one lookup and one ballot settle those
+            if (!__ballot_sync(0xffffffffu, s + lane < limit && trans[ncls + my_cl] != 0))
+            {
+                if (anchor_begin)
+                    break;
+                s = (s + 32 < limit) ? s + 32 : limit;
+                continue;
+            }
             __syncwarp();
-            win8[lane] = s + lane < L ? s_cls[at(s + lane)] : 0;
+            win8[lane] = static_cast<uint8_t>(my_cl);
             if (lane < 16)
                 win8[32 + lane] = s + 32 + lane < L ? s_cls[at(s + 32 + lane)] : 0;
             __syncwarp();

@@ -1191,6 +1191,9 @@ void build_dfa(regex_dev const & img, dfa_table & out)
     for (uint32_t s = 0; s < n; ++s)
         for (uint32_t c = 0; c < nc; ++c)
             out.trans[static_cast<size_t>(new_id[s]) * nc + c] = static_cast<uint16_t>(new_id[trans[static_cast<size_t>(s) * nc + c]]);
+    out.start_class.assign(nc, 0);
+    for (uint32_t c = 0; c < nc; ++c)
+        out.start_class[c] = out.trans[static_cast<size_t>(1) * nc + c] != 0;
     out.usable = true;
     build_reverse_dfa(img, cols, out);
 }
@@ -1444,12 +1447,23 @@ int trx_regex_scan_begin(trx_text_t * t, trx_regex_t * re, const uint64_t * cand
     char const * const filt_env = getenv("TRX_REGEX_FILTER");
     bool const skip_phase1 = kind == kFilterNone && dfa != nullptr && use_tma && (!filt_env || strcmp(filt_env, "off") == 0);
     bool use_start_bits = false;
+    // Which no-prefilter route: when few text bytes can begin a match, trying every start (phase 2 settles a window of 32
+    // starts with one lookup and a ballot) is cheapest; when most can (patterns that begin with wildcards), the reverse
+    // searcher finds the exact starts with one lookup per byte — as long as its table is small enough to leave room for
+    // several CTAs per SM and the warm-up behind each chunk is short.
+    double p_first = 0;
+    if (skip_phase1)
+        for (int ch = 0; ch < 256; ++ch)
+            if (dfa->start_class[dfa->cls[ch]])
+                p_first += t->byte_freq[ch];
+    bool const starts_route = skip_phase1 && dfa->r_usable && p_first > 0.3 && dfa->r_trans.size() * 2 <= 8192 && dfa->max_len <= 64 &&
+                              !(getenv("TRX_REGEX_STARTS") && strcmp(getenv("TRX_REGEX_STARTS"), "off") == 0);
     t_choice = now();
     sl.filter_units = use_atoms ? static_cast<uint64_t>(sp.atoms.n_atoms)
                                 : (use_window ? static_cast<uint64_t>(sp.filter.n_a + sp.filter.n_b) : 0);
     if (tiles.empty())
         ; // nothing to scan: no kernel, the read-back below returns the zeroed counters
-    else if (skip_phase1 && dfa->r_usable && !(getenv("TRX_REGEX_STARTS") && strcmp(getenv("TRX_REGEX_STARTS"), "off") == 0))
+    else if (starts_route)
     {
         // exact match starts from the reverse searcher, one bit per text byte
         uint64_t const bits_bytes = t->n_text_padded / 8;
