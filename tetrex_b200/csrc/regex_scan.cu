@@ -1441,23 +1441,19 @@ int trx_regex_scan_begin(trx_text_t * t, trx_regex_t * re, const uint64_t * cand
         sp.atoms = found->atoms;
     }
     bool const use_atoms = kind == kFilterAtoms, use_window = kind == kFilterWindow;
-    // no selective necessary factor, but a determinised matcher: resolving every candidate record directly (one table
-    // lookup per byte and start) beats streaming the text through the position automaton first.  TRX_REGEX_DFA=off keeps
-    // the position-automaton kernels reachable for A/B runs and tests.
+    // no selective necessary factor (or TRX_REGEX_FILTER=off), but determinised automata: phase 1 need not be the position
+    // automaton.  TRX_REGEX_DFA=off keeps the position-automaton kernels reachable for A/B runs and tests.
     char const * const filt_env = getenv("TRX_REGEX_FILTER");
     bool const skip_phase1 = kind == kFilterNone && dfa != nullptr && use_tma && (!filt_env || strcmp(filt_env, "off") == 0);
     bool use_start_bits = false;
-    // Which no-prefilter route: when few text bytes can begin a match, trying every start (phase 2 settles a window of 32
-    // starts with one lookup and a ballot) is cheapest; when most can (patterns that begin with wildcards), the reverse
-    // searcher finds the exact starts with one lookup per byte — as long as its table is small enough to leave room for
-    // several CTAs per SM and the warm-up behind each chunk is short.
-    double p_first = 0;
-    if (skip_phase1)
-        for (int ch = 0; ch < 256; ++ch)
-            if (dfa->start_class[dfa->cls[ch]])
-                p_first += t->byte_freq[ch];
-    bool const starts_route = skip_phase1 && dfa->r_usable && p_first > 0.3 && dfa->r_trans.size() * 2 <= 8192 && dfa->max_len <= 64 &&
-                              !(getenv("TRX_REGEX_STARTS") && strcmp(getenv("TRX_REGEX_STARTS"), "off") == 0);
+    // Which no-prefilter route.  Measured on the C2 text (profiles/time_nofilter.py): the reverse searcher costs 0.32 ms per
+    // 204 MB whatever the pattern, as long as its table is small (several CTAs per SM) and the warm-up behind each chunk
+    // short; the position automaton 0.75-1.0 ms; trying every start in phase 2 1.0-3.4 ms (one dependent global load per
+    // window of 32 starts).  So: reverse searcher when it qualifies, otherwise the position automaton in phase 1 with the
+    // DFA in phase 2; "every start" stays reachable for tests (TRX_REGEX_STARTS=off).
+    bool const starts_off = getenv("TRX_REGEX_STARTS") && strcmp(getenv("TRX_REGEX_STARTS"), "off") == 0;
+    bool const starts_route = skip_phase1 && !starts_off && dfa->r_usable && dfa->r_trans.size() * 2 <= 8192 && dfa->max_len <= 64;
+    bool const every_start_route = skip_phase1 && starts_off;
     t_choice = now();
     sl.filter_units = use_atoms ? static_cast<uint64_t>(sp.atoms.n_atoms)
                                 : (use_window ? static_cast<uint64_t>(sp.filter.n_a + sp.filter.n_b) : 0);
@@ -1489,7 +1485,7 @@ int trx_regex_scan_begin(trx_text_t * t, trx_regex_t * re, const uint64_t * cand
         ++c->launches;
         TRX_CUDA(cudaGetLastError());
     }
-    else if (skip_phase1)
+    else if (every_start_route)
     {
         list_candidate_records_kernel<<<grid_for(t->n_records, 256, c->sm_count, 8), 256, 0, st>>>(
             t->d_rec_bin, sp.cand_words, t->n_records, sl.d_rec_list, sp.rec_count);
@@ -1510,7 +1506,7 @@ int trx_regex_scan_begin(trx_text_t * t, trx_regex_t * re, const uint64_t * cand
     rp.rec_offsets = t->d_rec_offsets;
     rp.rec_list = sl.d_rec_list;
     rp.rec_count = sp.rec_count;
-    rp.chunk_flags = (skip_phase1 && !use_start_bits) ? nullptr : sl.d_chunk_flags;
+    rp.chunk_flags = every_start_route ? nullptr : sl.d_chunk_flags;
     rp.start_bits = use_start_bits ? static_cast<uint32_t const *>(sl.d_start_bits.ptr) : nullptr;
     rp.re = sp.re;
     rp.anchor_begin = re->anchor_begin;
