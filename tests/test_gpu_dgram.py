@@ -106,6 +106,29 @@ def test_emplaced_codes_are_exactly_the_reference_codes(ctx):
         g.close()
 
 
+def test_slab_route_sets_the_same_bits(ctx, monkeypatch):
+    """Matrices far beyond L2 are filled slab by slab (64 bins at a time into a dense column, then folded in): same bits as
+    the direct route, here forced on a small matrix of 200 bins with ragged and empty bins."""
+    rng = np.random.default_rng(21)
+    alpha = np.frombuffer(b"ACDEFGHIKLMNPQRSTVWYX", dtype=np.uint8)
+    recs, rec_bin = [], []
+    for b in range(200):
+        for _ in range(int(rng.integers(0, 3))):
+            recs.append(rng.choice(alpha, int(rng.integers(0, 400))).tobytes())
+            rec_bin.append(b)
+    offs = np.concatenate([[0], np.cumsum([len(r) for r in recs])]).astype(np.uint64)
+    rec_bin = np.array(rec_bin, dtype=np.uint32)
+    direct = t.IBF(ctx, 200, 30011, 3)
+    direct.dgram_emplace(b"".join(recs), offs, rec_bin, 2, 9)
+    monkeypatch.setenv("TRX_DGRAM_SLAB_MIN_MB", "0")
+    slab = t.IBF(ctx, 200, 30011, 3)
+    slab.dgram_emplace(b"".join(recs), offs, rec_bin, 2, 9)
+    a, b = direct.download(), slab.download()
+    assert a.any() and np.array_equal(a, b)
+    direct.close()
+    slab.close()
+
+
 @pytest.mark.parametrize("build", range(len(GOLD["builds"])))
 def test_dindex_file_is_byte_identical(ctx, build, tmp_path):
     b = GOLD["builds"][build]

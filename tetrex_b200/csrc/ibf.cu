@@ -577,13 +577,13 @@ extern "C++" {
 template <bool COUNT>
 static int launch_dgram(trx_ctx * c, ibf_geom g, const uint8_t * d_residues, uint64_t n_residues,
                         const uint64_t * d_rec_offsets, const uint32_t * d_rec_bin, uint64_t n_records, uint32_t min_gap,
-                        uint32_t max_gap, unsigned long long * d_per_bin)
+                        uint32_t max_gap, unsigned long long * d_per_bin, const uint64_t * d_range = nullptr, uint64_t range_tiles = 0)
 {
-    uint64_t const n_tiles = (n_residues + kDgramTile - 1) / kDgramTile;
+    uint64_t const n_tiles = d_range ? range_tiles : (n_residues + kDgramTile - 1) / kDgramTile;
     unsigned const grid = grid_for(n_tiles, 1, c->sm_count, 8);
     size_t const smem = kDgramTile + 2 + max_gap + 3;
     dgram_kernel<COUNT><<<grid, kDgramTile, smem, c->stream>>>(g, d_residues, n_residues, d_rec_offsets, d_rec_bin, n_records,
-                                                               min_gap, max_gap, d_per_bin);
+                                                               min_gap, max_gap, d_per_bin, d_range);
     ++c->launches;
     TRX_CUDA(cudaGetLastError());
     return TRX_OK;
@@ -620,12 +620,50 @@ int trx_dgram_emplace_dev(trx_ibf_t * f, const uint8_t * d_residues, uint64_t n_
         return set_error(TRX_EINVAL, "NULL argument");
     trx_ctx * c = f->ctx;
     TRX_TRY(c->use());
-    // like K1: a matrix beyond L2 is filled in row slices that fit (every pass re-derives the codes — reading shared
-    // memory — and fires only the atomics of its slice)
+    uint64_t const matrix_bytes = f->bin_size * f->shard_words * 8;
+    uint64_t const n_slabs = f->shard_words; // one 64-bin word column each
+    char const * const slab_env = getenv("TRX_EMPLACE_SLAB");
+    uint64_t slab_min = 512ull << 20; // TRX_DGRAM_SLAB_MIN_MB: tests take the slab route on small matrices
+    if (char const * e = getenv("TRX_DGRAM_SLAB_MIN_MB"))
+        slab_min = static_cast<uint64_t>(atoll(e)) << 20;
+    if (matrix_bytes > slab_min && n_slabs > 1 && f->bin_size * 8 <= (1ull << 30) && f->shard_words == f->bin_words &&
+        !(slab_env && strcmp(slab_env, "off") == 0))
+    {
+        // Far beyond L2 every atomic is a DRAM read-modify-write (46 ps each measured here).  Records are grouped by bin,
+        // so the codes of one 64-bin slab come from one contiguous stretch of the text: its bits are collected in a DENSE
+        // copy of the slab's word column (rows x 8 B — C3 with gaps 3..21: 189 MB, hit by ~10 atomics per sector, served
+        // from L2) and folded into the interleaved matrix by one strided pass — K1's slab route.  The stretches are found
+        // on the device (one binary search per slab), so nothing here waits for the host.
+        TRX_TRY(f->slab.reserve(f->bin_size * 8));
+        auto * d_slab = static_cast<uint64_t *>(f->slab.ptr);
+        TRX_TRY(c->d_out[2].reserve((n_slabs + 1) * 8));
+        auto * d_ranges = static_cast<uint64_t *>(c->d_out[2].ptr);
+        dgram_slab_ranges_kernel<<<static_cast<unsigned>((n_slabs + 1 + 127) / 128), 128, 0, c->stream>>>(d_rec_offsets, d_rec_bin,
+                                                                                                         n_records, n_slabs, d_ranges);
+        ++c->launches;
+        uint64_t const tiles_per_slab = (n_residues / n_slabs) / kDgramTile + 2; // grid sizing only: the kernel strides
+        for (uint64_t s = 0; s < n_slabs; ++s)
+        {
+            TRX_CUDA(cudaMemsetAsync(d_slab, 0, f->bin_size * 8, c->stream));
+            ibf_geom g = geom_of(f);
+            g.slab = d_slab;
+            g.slab_words = 1;
+            g.slab_begin = f->shard_word_begin + s;
+            TRX_TRY(launch_dgram<false>(c, g, d_residues, n_residues, d_rec_offsets, d_rec_bin, n_records, min_gap, max_gap, nullptr,
+                                        d_ranges + s, tiles_per_slab));
+            slab_merge_kernel<<<grid_for(f->bin_size, 256, c->sm_count, 16), 256, 0, c->stream>>>(f->d_words, f->shard_words, s, d_slab,
+                                                                                                 1, f->bin_size);
+            ++c->launches;
+        }
+        TRX_CUDA(cudaGetLastError());
+        return TRX_OK;
+    }
+    // like K1: a matrix beyond L2 (but not far beyond) is filled in row slices that fit: every pass re-derives the codes —
+    // reading shared memory — and fires only the atomics of its slice
     uint64_t window = 64ull << 20;
     if (char const * e = getenv("TRX_EMPLACE_WINDOW_MB"))
         window = static_cast<uint64_t>(atoll(e)) << 20;
-    uint64_t passes = window ? (f->bin_size * f->shard_words * 8 + window - 1) / window : 1;
+    uint64_t passes = window ? (matrix_bytes + window - 1) / window : 1;
     if (passes < 1 || passes > 10)
         passes = 1;
     uint64_t const rows_per_pass = (f->bin_size + passes - 1) / passes;

@@ -569,16 +569,38 @@ __device__ __forceinline__ uint8_t dgram_letter(uint8_t c)
     return static_cast<uint8_t>(__popc(letters & ((1u << d) - 1)));
 }
 
+// residue range of every 64-bin slab (records are grouped by ascending bin): range[s] = offset of the first record whose
+// bin is >= 64 s, range[n_slabs] = n_residues.  One thread per slab, binary search over rec_bin.
+__global__ void dgram_slab_ranges_kernel(uint64_t const * __restrict__ rec_offsets, uint32_t const * __restrict__ rec_bin,
+                                         uint64_t n_records, uint64_t n_slabs, uint64_t * __restrict__ range)
+{
+    uint64_t const s = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (s > n_slabs)
+        return;
+    uint64_t lo = 0, hi = n_records; // first record with rec_bin >= 64 s
+    while (lo < hi)
+    {
+        uint64_t const mid = (lo + hi) >> 1;
+        if (static_cast<uint64_t>(rec_bin[mid]) < 64 * s)
+            lo = mid + 1;
+        else
+            hi = mid;
+    }
+    range[s] = rec_offsets[s == n_slabs ? n_records : lo];
+}
+
+// `range` (optional, device): only positions in [range[0], range[1]) are worked on — the residues of one slab of bins
 template <bool COUNT>
 __global__ void __launch_bounds__(kDgramTile)
     dgram_kernel(ibf_geom g, uint8_t const * __restrict__ text, uint64_t n_residues,
                  uint64_t const * __restrict__ rec_offsets, uint32_t const * __restrict__ rec_bin, uint64_t n_records,
-                 uint32_t min_gap, uint32_t max_gap, unsigned long long * __restrict__ per_bin)
+                 uint32_t min_gap, uint32_t max_gap, unsigned long long * __restrict__ per_bin, uint64_t const * __restrict__ range)
 {
     extern __shared__ uint8_t s_code[]; // codes of positions [t0 - 2, t0 + kDgramTile + max_gap + 3)
     uint32_t const span = kDgramTile + 2 + max_gap + 3;
-    uint64_t const n_tiles = (n_residues + kDgramTile - 1) / kDgramTile;
-    for (uint64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x)
+    uint64_t const p_lo = range ? range[0] : 0, p_hi = range ? range[1] : n_residues;
+    uint64_t const n_tiles = (p_hi + kDgramTile - 1) / kDgramTile;
+    for (uint64_t tile = p_lo / kDgramTile + blockIdx.x; tile < n_tiles; tile += gridDim.x)
     {
         uint64_t const t0 = tile * kDgramTile;
         for (uint32_t j = threadIdx.x; j < span; j += kDgramTile)
@@ -590,7 +612,7 @@ __global__ void __launch_bounds__(kDgramTile)
         uint64_t const p = t0 + threadIdx.x;
         unsigned long long cnt = 0;
         uint32_t bin = 0;
-        if (p < n_residues)
+        if (p >= p_lo && p < p_hi)
         {
             // record containing p: largest r with rec_offsets[r] <= p, stepping over empty records that share the offset
             uint64_t lo = 0, hi = n_records;
