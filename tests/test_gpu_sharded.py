@@ -113,3 +113,23 @@ def test_column_shard_without_reduction_is_refused(ctx, collection):
 def test_shard_count_must_divide_columns(ctx, collection):
     with pytest.raises(sharded.HostError, match="divide"):
         sharded.ShardedIndex(ctx, collection["flat"], 0, 3)
+
+
+@pytest.mark.parametrize("kind", ["flat", "hibf"])
+def test_cli_gpus_flag_equals_single_gpu(collection, kind):
+    """`tetrex query --gpus N` (one thread and one shard per device, NCCL inside the library) prints what the single-GPU
+    run prints.  Needs at least two devices: skipped on the one-GPU boxes of the default test run, exercised by
+    `gpurun --gpus 2` (log under profiles/)."""
+    import torch
+    n = min(torch.cuda.device_count(), 4)
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    path = collection[kind]
+    for q in QUERIES:
+        one = run(["query", path, q])
+        many = run(["query", "--gpus", str(n), path, q])
+        assert one.returncode == 0 and many.returncode == 0, many.stderr
+        assert many.stdout == one.stdout, (kind, q, many.stderr)
+    env_run = subprocess.run([TETREX, "query", path, QUERIES[0]], capture_output=True, text=True, cwd=ROOT, timeout=600,
+                             env=dict(os.environ, TETREX_GPUS=str(n)))
+    assert env_run.returncode == 0 and env_run.stdout == run(["query", path, QUERIES[0]]).stdout

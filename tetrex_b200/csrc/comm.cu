@@ -13,6 +13,7 @@
 #include "common.cuh"
 
 #include <dlfcn.h>
+#include <strings.h>
 
 using namespace trx;
 
@@ -48,6 +49,12 @@ nccl_api & api()
 {
     static nccl_api a = [] {
         nccl_api x;
+        // NCCL prints its version banner (NCCL_DEBUG=VERSION/INFO) to stdout, where `tetrex query` prints its hits: unless
+        // the caller chose a file, the banner goes to stderr
+        setenv("NCCL_DEBUG_FILE", "/dev/stderr", 0);
+        // (NCCL honours NCCL_DEBUG_FILE only above the VERSION level; WARN prints the same banner and nothing else)
+        if (char const * lvl = getenv("NCCL_DEBUG"); lvl && strcasecmp(lvl, "VERSION") == 0)
+            setenv("NCCL_DEBUG", "WARN", 1);
         for (char const * name : {"libnccl.so.2", "libnccl.so"})
             if ((x.lib = dlopen(name, RTLD_NOW | RTLD_GLOBAL)))
                 break;

@@ -264,7 +264,10 @@ int launch_phase1(trx_ctx * c, cudaStream_t st, scan_params const & sp, CUtensor
 {
     size_t smem = (USE_TMA ? kStages * kTileBytes : 0) + sizeof(scan_tables<W>) + 2 * sizeof(uint64_t);
     auto kern = regex_scan_phase1<W, DIR, USE_TMA>;
-    static int per_sm = 0; // per template instantiation: attribute + occupancy are queried once
+    // per template instantiation AND per device (function attributes belong to a device; `tetrex query --gpus N` drives
+    // several from one process): attribute + occupancy are queried once
+    static int per_sm_of[64] = {};
+    int & per_sm = per_sm_of[c->device & 63];
     if (per_sm == 0)
     {
         TRX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
@@ -306,7 +309,8 @@ int launch_filter_s(trx_ctx * c, cudaStream_t st, scan_params const & sp, CUtens
     constexpr int kThreads = kScanThreads * SPLIT + 32; // + the producer warp
     size_t smem = tile_ring<STAGES, kScanThreads * SPLIT>::kRingBytes;
     auto kern = regex_filter_simd<NA, NB, STAGES, SPLIT>;
-    static int per_sm = 0;
+    static int per_sm_of[64] = {};
+    int & per_sm = per_sm_of[c->device & 63];
     if (per_sm == 0)
     {
         TRX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
@@ -359,7 +363,8 @@ int launch_atoms_s(trx_ctx * c, cudaStream_t st, scan_params const & sp, CUtenso
     size_t smem = ((tile_ring<STAGES, kScanThreads * SPLIT>::kRingBytes + 15) & ~15) +
                   2 * NLIT * kScanThreads * SPLIT * sizeof(uint32_t);
     auto kern = regex_filter_atoms<NLIT, STAGES, SPLIT>;
-    static int per_sm = 0;
+    static int per_sm_of[64] = {};
+    int & per_sm = per_sm_of[c->device & 63];
     if (per_sm == 0)
     {
         TRX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
@@ -1474,7 +1479,8 @@ int trx_regex_scan_begin(trx_text_t * t, trx_regex_t * re, const uint64_t * cand
         sp.r_max_len = dfa->max_len;
         use_start_bits = true;
         size_t const smem = kStages * kTileBytes + 256 + 16 + ((dfa->r_trans.size() * 2 + 15) & ~size_t{15});
-        static size_t attr_smem = 0;
+        static size_t attr_smem_of[64] = {};
+        size_t & attr_smem = attr_smem_of[c->device & 63];
         if (smem > attr_smem)
         {
             TRX_CUDA(cudaFuncSetAttribute(regex_scan_starts_dfa, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));

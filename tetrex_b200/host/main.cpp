@@ -112,6 +112,7 @@ int run_query(arg_reader a)
             else if (is_flag(s, 't', "threads")) args.t = static_cast<uint8_t>(to_uint(a.next("-t"), "-t"));
             else if (is_flag(s, 'o', "output")) args.ofile = a.next("-o");
             else if (is_flag(s, 'g', "gibf")) args.dibf = a.next("-g");
+            else if (s == "--gpus") args.gpus = to_uint(a.next("--gpus"), "--gpus");
             else if (s.size() > 1 && s[0] == '-' && positional.size() < 1) throw error("Unknown option " + s + ".");
             else positional.push_back(s);
         }
@@ -312,7 +313,7 @@ void usage()
 {
     std::cerr << "tetrex - regular expression search over (H)IBF-indexed sequence libraries (B200 build)\n"
                  "  tetrex index [-k K] [-p FPR] [-c HASHES] [-n] [-i] [-r murphy|li] OUT LIB...\n"
-                 "  tetrex query [-v] [-f] [-c] [-a] [-g DINDEX] [-o FILE] IDX REGEX\n"
+                 "  tetrex query [-v] [-f] [-c] [-a] [-g DINDEX] [-o FILE] [--gpus N] IDX REGEX\n"
                  "  tetrex dindex [-l LOWER] [-u UPPER] OUT LIB...\n"
                  "  tetrex inspect IDX\n";
 }

@@ -11,6 +11,7 @@
 #include <iomanip>
 #include <iostream>
 #include <sstream>
+#include <thread>
 
 #include "trx_host.hpp"
 
@@ -501,10 +502,103 @@ void run_collection(query_arguments & args, bool read_file, DeviceIndex & index)
 
 } // namespace
 
+namespace
+{
+
+// `tetrex query --gpus N`: the single-query path on N devices of this node, one host thread and one shard per device
+// (SURVEY.md §5/§8(e)).  Flat IBF: device i holds the 64-bin column blocks i of N of every row, the pruning flags are
+// all-reduced and the candidate words all-gathered over NCCL inside the CUDA library (trx_comm_create_all); HIBF: every
+// device holds a replica.  Every device reads, uploads and verifies only the FASTA files of its own bins; the threads'
+// outputs are concatenated in shard order, which is the reference's -t 1 order.
+void run_collection_multi_gpu(query_arguments & args, unsigned n)
+{
+    double const t1 = now();
+    std::vector<trx_ctx_t *> ctxs(n, nullptr);
+    std::vector<trx_comm_t *> comms(n, nullptr);
+    auto cleanup = [&] {
+        for (trx_comm_t * c : comms)
+            if (c)
+                trx_comm_destroy(c);
+        for (trx_ctx_t * c : ctxs)
+            if (c)
+                trx_ctx_destroy(c);
+    };
+    try
+    {
+        for (unsigned i = 0; i < n; ++i)
+            check(trx_ctx_create(static_cast<int>(i), nullptr, &ctxs[i]));
+        check(trx_comm_create_all(ctxs.data(), static_cast<int>(n), comms.data()));
+        std::vector<std::string> outputs(n), errors(n);
+        std::vector<uint64_t> candidates(n, 0);
+        std::vector<std::thread> threads;
+        for (unsigned i = 0; i < n; ++i)
+            threads.emplace_back([&, i] {
+                try
+                {
+                    DeviceIndex index(ctxs[i]);
+                    index.set_shard(i, n);
+                    index.load(args.idx);
+                    shard_hooks hooks;
+                    hooks.comm = comms[i];
+                    bitvector hit_vector(index.bin_words(), 0);
+                    for (uint64_t b = 0; b < index.bin_count(); ++b)
+                        hit_vector[b / 64] |= 1ull << (b % 64);
+                    if (index.bin_count() > 1)
+                    {
+                        bitvector got = process_query(args.regex, index, nullptr, index.is_hibf() ? nullptr : &hooks, args.augment);
+                        for (size_t w = 0; w < hit_vector.size(); ++w)
+                            hit_vector[w] &= got[w];
+                    }
+                    candidates[i] = popcount(hit_vector);
+                    if (candidates[i])
+                    {
+                        std::ostringstream os;
+                        iter_disk_search(hit_vector, args.regex, index, os);
+                        outputs[i] = os.str();
+                    }
+                }
+                catch (std::exception const & e)
+                {
+                    errors[i] = e.what();
+                }
+            });
+        for (std::thread & t : threads)
+            t.join();
+        for (unsigned i = 0; i < n; ++i)
+            if (!errors[i].empty())
+                throw error("device " + std::to_string(i) + ": " + errors[i]);
+        if (args.verbose)
+            std::cerr << "Narrowed Search to " << candidates[0] << " possible bins" << std::endl;
+        std::ofstream file_out;
+        std::ostream * out = &std::cout;
+        if (args.ofile != "-")
+        {
+            file_out.open(args.ofile);
+            if (!file_out)
+                throw error("Failed to open output file: " + args.ofile);
+            out = &file_out;
+        }
+        for (unsigned i = 0; i < n; ++i)
+            *out << outputs[i];
+        if (args.verbose)
+            std::cerr << "Query Time: " << (now() - t1) << std::endl;
+    }
+    catch (...)
+    {
+        cleanup();
+        throw;
+    }
+    cleanup();
+}
+
+} // namespace
+
 void drive_query(query_arguments & args)
 {
     if (args.regex == "-")
         std::cin >> args.regex; // src/query.cpp:479
+    if (char const * e = getenv("TETREX_GPUS"); e && args.gpus <= 1)
+        args.gpus = static_cast<unsigned>(std::max(1, atoi(e)));
     if (args.draw)
         throw error("-d (graph drawing) is outside this build: see DESIGN.md \"out of scope\"");
     {
@@ -514,6 +608,11 @@ void drive_query(query_arguments & args)
         std::string molecule;
         bool is_hibf;
         read_index_params(args.idx, k, molecule, is_hibf);
+    }
+    if (args.gpus > 1 && args.read_file == "-" && args.conjunction == "-" && args.dibf == "-")
+    {
+        run_collection_multi_gpu(args, args.gpus);
+        return;
     }
     trx_ctx_t * ctx = nullptr;
     check(trx_ctx_create(0, nullptr, &ctx));

@@ -69,6 +69,7 @@ struct query_arguments
     bool augment = false;
     std::string idx;
     std::string regex;
+    unsigned gpus = 1; // --gpus N / TETREX_GPUS: one shard of the index per device of this node (not a reference flag)
     std::string read_file = "-";
     std::string conjunction = "-";
     std::string dibf = "-";
