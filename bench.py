@@ -230,6 +230,34 @@ def run_ours(args):
                 "note": "result bytes of one step / its wall time, against a plain pinned cudaMemcpy D2H of the same buffer "
                         "measured in this run (per rank)"}
 
+    # ---------------- end to end in membership_for's OWN result form: seqan returns the ids of the user bins that hold the
+    # value (hierarchical_interleaved_bloom_filter.hpp:321-355); TetRex turns them into a bitvector afterwards
+    # (include/index_hibf.h:132-147).  trx_hibf_membership_ids compacts the rows on the device, so what crosses PCIe is a
+    # 4-byte count and ~17 two-byte ids per k-mer instead of a 128-byte row.
+    pin_counts = torch.empty(args.batch, dtype=torch.int32).pin_memory()
+    pin_ids = torch.empty(args.batch * 48, dtype=torch.int16).pin_memory()
+    cnt_np = pin_counts.numpy().view(np.uint32)
+    ids_np = pin_ids.numpy().view(np.uint16)
+    for _ in range(2):
+        got_counts, got_ids = hibf.membership_ids(q_np, id_bytes=2, counts=cnt_np, ids=ids_np)
+    barrier()
+    tw = time.perf_counter()
+    for _ in range(e_steps):
+        got_counts, got_ids = hibf.membership_ids(q_np, id_bytes=2, counts=cnt_np, ids=ids_np)
+    torch.cuda.synchronize()
+    i_ms = max_over_ranks((time.perf_counter() - tw) * 1e3)
+    barrier()
+    ids_value = sum_over_ranks(float(args.batch * e_steps)) / (i_ms / 1e3)
+    n_ids = int(len(got_ids))
+    # same answer as the rows: every k-mer's count, and the ids of the first 8192 k-mers bit for bit
+    assert np.array_equal(got_counts, np.bitwise_count(out_np).sum(axis=1).astype(np.uint32)), "ids form: counts differ from the rows"
+    head = np.zeros((8192, W * 64), dtype=np.uint8)
+    ends = np.cumsum(got_counts[:8192].astype(np.int64))
+    head[np.repeat(np.arange(8192), got_counts[:8192]), got_ids[:ends[-1]].astype(np.int64)] = 1
+    assert np.array_equal(np.packbits(head, axis=1, bitorder="little").view(np.uint64), out_np[:8192]), "ids form: ids differ from the rows"
+    e2e_ids = {"value": ids_value, "unit": UNIT, "h2d_bytes_per_step": args.batch * 8,
+               "d2h_bytes_per_step": args.batch * 4 + n_ids * 2, "ids_per_kmer": n_ids / args.batch, "steps": e_steps}
+
     # ---------------- end to end the way the collector uses the device (OTFCollector::update_path, include/otf_collector.h:
     # 247-279): k-mers and their path slots go in from pinned host memory, the hit vectors are ANDed into HBM-resident
     # path bitvectors, ONE alive byte per k-mer comes back — the per-k-mer bitvectors never cross PCIe
@@ -318,11 +346,14 @@ def run_ours(args):
                          "note": "algorithmic = 32-byte sector per 8-byte row read x h x visited IBFs (SURVEY 8(d)); achieved = that / "
                                  "the step's device time (all K3 kernels); traffic = measured DRAM bytes per step (ncu), lower than "
                                  "algorithmic because the child windows are served from L2"},
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": args.batch * 8,
-                    "d2h_bytes_per_step": args.batch * W * 8, "steps": e_steps},
+            "e2e": dict(e2e_ids, what="trx_hibf_membership_ids with pinned host buffers: k-mers in, per k-mer a count and the ids of "
+                                      "its user bins out (membership_for's own result form), checked against the bitvector rows"),
             "gpu_launches": int(launches), "clocks": clocks,
         }
-        line["e2e"]["roofline"] = e2e_pcie
+        line["e2e"]["bitvector_form"] = {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": args.batch * 8,
+                                         "d2h_bytes_per_step": args.batch * W * 8, "steps": e_steps, "roofline": e2e_pcie,
+                                         "what": "trx_hibf_membership: one row of ceil(user bins / 64) words per k-mer "
+                                                 "(HIBFIndex::query's form) — bound by PCIe"}
         if collector_e2e is not None:
             line["e2e"]["collector_step"] = collector_e2e
         if flat_c4 is not None:
@@ -598,9 +629,11 @@ def extra_measurements(t, ctx, torch, residues, offs, rec_bin, planted, hibf, pe
     only_rx = [rxp for rxp, _ in compiled]
     txt.scan_many(only_rx[:8], cap=1 << 20)
     torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    piped = txt.scan_many(only_rx, cap=1 << 20, depth=3)
-    dt_piped = time.perf_counter() - t0
+    dt_piped = float("inf")
+    for _ in range(2):  # best of two: a 0.1 s host-driven loop is easily disturbed
+        t0 = time.perf_counter()
+        piped = txt.scan_many(only_rx, cap=1 << 20, depth=3)
+        dt_piped = min(dt_piped, time.perf_counter() - t0)
     out["verify_pattern_batch_pipelined"] = {"depth": 3, "scans_per_s": len(pats) / dt_piped,
                                              "residues_per_s": len(pats) * n_res / dt_piped,
                                              "frac_of_hbm_peak": len(pats) * n_res / dt_piped / 1e9 / peak,
@@ -615,9 +648,11 @@ def extra_measurements(t, ctx, torch, residues, offs, rec_bin, planted, hibf, pe
     # N4: the same batch in shared passes over the text (trx_regex_scan_multi: <= 128 patterns per pass)
     txt.scan_multi(only_rx[:128], cap=1 << 21)
     torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    multi, mst = txt.scan_multi(only_rx, cap=1 << 21, stats=True)
-    dt_multi = time.perf_counter() - t0
+    dt_multi = float("inf")
+    for _ in range(2):
+        t0 = time.perf_counter()
+        multi, mst = txt.scan_multi(only_rx, cap=1 << 21, stats=True)
+        dt_multi = min(dt_multi, time.perf_counter() - t0)
     out["verify_pattern_batch_multi"] = {
         "scans_per_s": len(pats) / dt_multi, "ms_total": dt_multi * 1e3, "hits": int(sum(len(h) for h in multi)),
         "hit_lists_equal_pattern_at_a_time": bool(all(np.array_equal(a, b) for a, b in zip(multi, piped))),

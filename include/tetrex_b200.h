@@ -243,6 +243,14 @@ void trx_hibf_destroy(trx_hibf_t *h);
 int trx_hibf_membership(trx_hibf_t *h, const uint64_t *kmers, uint64_t n, uint64_t *out_words, uint64_t *stats);
 int trx_hibf_membership_dev(trx_hibf_t *h, const uint64_t *d_kmers, uint64_t n, uint64_t *d_out_words,
                             uint64_t *stats);
+/* The same in seqan's own result form: membership_for returns the ids of the user bins that hold the value
+ * (…hpp:321-355,424-439); HIBFIndex::query only then turns them into a bitvector (include/index_hibf.h:132-147).
+ * counts[i] = number of user bins of k-mer i; ids = the ids of k-mer 0, then of k-mer 1, …, ascending inside a k-mer, as
+ * id_bytes = 2 (number_of_user_bins <= 65536) or 4 byte integers; cap = room in ids (entries), *n_ids = entries written.
+ * The rows are compacted on the device, so a host caller pays for the ids it gets, not for ceil(bins/64) words per k-mer.
+ * TRX_ECAPACITY with *n_ids = a lower bound of what is needed when cap is too small. */
+int trx_hibf_membership_ids(trx_hibf_t *h, const uint64_t *kmers, uint64_t n, uint32_t *counts, void *ids, uint32_t id_bytes,
+                            uint64_t cap, uint64_t *n_ids, uint64_t *stats);
 uint64_t trx_hibf_user_bin_words(const trx_hibf_t *h);
 
 /* ------------------------------------------------------------------------ a9/a10: verify */

@@ -431,4 +431,19 @@ def test_hibf_synthetic_shapes(ctx, case, monkeypatch):
         assert np.array_equal(one, want[:1])
         for m in (7, 2048, 2049):
             assert np.array_equal(h.membership(query[:m]), want[:m]), (case, fused, m)
+        if fused == "auto":
+            # membership_for's own result form: counts + ascending user-bin ids, compacted on the device
+            bits = np.unpackbits(want.view(np.uint8), axis=1, bitorder="little")
+            want_counts = bits.sum(axis=1).astype(np.uint32)
+            want_ids = np.nonzero(bits)[1]
+            for id_bytes in ((2, 4) if case["n_user"] <= 65536 else (4,)):
+                counts, ids = h.membership_ids(query, id_bytes=id_bytes)
+                assert np.array_equal(counts, want_counts) and np.array_equal(ids.astype(np.int64), want_ids), (case, id_bytes)
+            if case["n_user"] > 65536:
+                with pytest.raises(t.TetrexError):
+                    h.membership_ids(query, id_bytes=2)
+            with pytest.raises(t.TetrexError):  # too little room: an error, not a truncated answer
+                h.membership_ids(query, id_bytes=4, cap=max(int(want_counts.sum()) - 1, 0))
+            c0, i0 = h.membership_ids(query[:0], id_bytes=4)
+            assert len(c0) == 0 and len(i0) == 0
         h.close()

@@ -83,6 +83,7 @@ PROTOTYPES = {
     "trx_hibf_destroy": (None, [vp]),
     "trx_hibf_membership": (C.c_int, [vp, vp, C.c_uint64, vp, u64p]),
     "trx_hibf_membership_dev": (C.c_int, [vp, vp, C.c_uint64, vp, u64p]),
+    "trx_hibf_membership_ids": (C.c_int, [vp, vp, C.c_uint64, vp, vp, C.c_uint32, C.c_uint64, u64p, u64p]),
     "trx_hibf_user_bin_words": (C.c_uint64, [vp]),
     "trx_text_upload": (C.c_int, [vp, vp, vp, vp, C.c_uint64, C.c_uint64, vpp]),
     "trx_text_destroy": (None, [vp]),

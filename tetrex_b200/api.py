@@ -354,6 +354,21 @@ class HIBF:
         check(lib().trx_hibf_membership(self._h, _ptr(v), len(v), _ptr(out), st.ctypes.data_as(u64p)))
         return (out, st) if stats else out
 
+    def membership_ids(self, kmers, id_bytes: int = 2, cap: int | None = None, counts: np.ndarray | None = None,
+                       ids: np.ndarray | None = None):
+        """membership_for's own result form: (counts per k-mer, concatenated ascending user-bin ids).  counts / ids may be
+        caller-owned (e.g. pinned) buffers; returns (counts, ids[:n_ids])."""
+        v = _np(kmers, np.uint64)
+        if counts is None:
+            counts = np.zeros(len(v), dtype=np.uint32)
+        dt = np.uint16 if id_bytes == 2 else np.uint32
+        if ids is None:
+            ids = np.zeros(cap if cap is not None else max(len(v) * 64, 1), dtype=dt)
+        assert ids.dtype == dt and counts.dtype == np.uint32 and len(counts) >= len(v)
+        n_ids = C.c_uint64()
+        check(lib().trx_hibf_membership_ids(self._h, _ptr(v), len(v), _ptr(counts), _ptr(ids), id_bytes, len(ids), C.byref(n_ids), None))
+        return counts[:len(v)], ids[:n_ids.value]
+
     def membership_dev(self, d_kmers: int, n: int, d_out: int):
         st = np.zeros(2, dtype=np.uint64)
         check(lib().trx_hibf_membership_dev(self._h, d_kmers, n, d_out, st.ctypes.data_as(u64p)))

@@ -556,6 +556,7 @@ struct trx_hibf
     trx::scratch frontier[2];
     trx::scratch counters;
     trx::scratch d_kmers, d_out, sort_tmp;
+    trx::scratch d_id_counts, d_id_blocks, d_ids, h_id_total; // sparse result (trx_hibf_membership_ids)
     int ibf_bits{1}; // bits needed for an IBF id (radix-sort range)
     bool sort_frontier{true};
     bool fused{true};        // root + second level in one kernel (TRX_HIBF_FUSED=off → frontier kernels only)
@@ -593,6 +594,106 @@ using namespace trx;
 static constexpr uint64_t kChunk = 1ull << 20;   // k-mers per frontier pass
 static constexpr uint64_t kFanoutBudget = 32;    // frontier capacity = kFanoutBudget × chunk items
 static constexpr int kMaxLevels = 30;
+
+// ---- sparse result: result rows → (count per k-mer, ascending user-bin ids) ---------------------------------------------
+constexpr int kIdsBlock = 256;
+
+// counts[i] = popcount of row i; block_tot[b] = ids of block b's k-mers
+__global__ void __launch_bounds__(kIdsBlock) ids_count_kernel(uint64_t const * __restrict__ rows, uint64_t n, uint32_t W,
+                                                               uint32_t * __restrict__ counts, unsigned long long * __restrict__ block_tot)
+{
+    __shared__ unsigned int s_warp[kIdsBlock / 32];
+    uint64_t const i = static_cast<uint64_t>(blockIdx.x) * kIdsBlock + threadIdx.x;
+    unsigned int cnt = 0;
+    if (i < n)
+    {
+        for (uint32_t w = 0; w < W; ++w)
+            cnt += __popcll(rows[i * W + w]);
+        counts[i] = cnt;
+    }
+    for (int o = 16; o > 0; o >>= 1)
+        cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+    if ((threadIdx.x & 31) == 0)
+        s_warp[threadIdx.x >> 5] = cnt;
+    __syncthreads();
+    if (threadIdx.x == 0)
+    {
+        unsigned long long t = 0;
+        for (int w = 0; w < kIdsBlock / 32; ++w)
+            t += s_warp[w];
+        block_tot[blockIdx.x] = t;
+    }
+}
+
+// in place: block_tot[b] → ids before block b; block_tot[blocks] = all ids of the piece.  One CTA (≤ 4096 blocks per piece).
+__global__ void __launch_bounds__(1024) ids_scan_blocks_kernel(unsigned long long * __restrict__ block_tot, unsigned blocks)
+{
+    __shared__ unsigned long long s_part[1024];
+    unsigned const per = (blocks + 1023) / 1024, lo = threadIdx.x * per, hi = min(lo + per, blocks);
+    unsigned long long sum = 0;
+    for (unsigned b = lo; b < hi; ++b)
+        sum += block_tot[b];
+    s_part[threadIdx.x] = sum;
+    __syncthreads();
+    if (threadIdx.x == 0)
+    {
+        unsigned long long run = 0;
+        for (int t = 0; t < 1024; ++t)
+        {
+            unsigned long long const v = s_part[t];
+            s_part[t] = run;
+            run += v;
+        }
+        block_tot[blocks] = run;
+    }
+    __syncthreads();
+    unsigned long long run = s_part[threadIdx.x];
+    for (unsigned b = lo; b < hi; ++b)
+    {
+        unsigned long long const v = block_tot[b];
+        block_tot[b] = run;
+        run += v;
+    }
+}
+
+// ids of k-mer i go to out[block base + ids of the block's earlier k-mers ...): a CTA-wide exclusive scan of the counts
+template <class id_t>
+__global__ void __launch_bounds__(kIdsBlock) ids_write_kernel(uint64_t const * __restrict__ rows, uint64_t n, uint32_t W,
+                                                               unsigned long long const * __restrict__ block_base, id_t * __restrict__ out)
+{
+    __shared__ unsigned int s_warp[kIdsBlock / 32];
+    uint64_t const i = static_cast<uint64_t>(blockIdx.x) * kIdsBlock + threadIdx.x;
+    unsigned int cnt = 0;
+    if (i < n)
+        for (uint32_t w = 0; w < W; ++w)
+            cnt += __popcll(rows[i * W + w]);
+    unsigned int incl = cnt;
+    unsigned const lane = threadIdx.x & 31;
+    for (int o = 1; o < 32; o <<= 1)
+    {
+        unsigned int const v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= static_cast<unsigned>(o))
+            incl += v;
+    }
+    if (lane == 31)
+        s_warp[threadIdx.x >> 5] = incl;
+    __syncthreads();
+    unsigned int warp_base = 0;
+    for (unsigned w = 0; w < (threadIdx.x >> 5); ++w)
+        warp_base += s_warp[w];
+    if (i >= n || cnt == 0)
+        return;
+    id_t * dst = out + block_base[blockIdx.x] + warp_base + (incl - cnt);
+    for (uint32_t w = 0; w < W; ++w)
+    {
+        uint64_t bits = rows[i * W + w];
+        while (bits)
+        {
+            *dst++ = static_cast<id_t>(w * 64 + (__ffsll(static_cast<long long>(bits)) - 1));
+            bits &= bits - 1;
+        }
+    }
+}
 
 template <int H, bool FAST>
 static int launch_fused(trx_hibf * h, uint64_t const * d_kmers, uint64_t n, uint64_t * d_out, uint64_t * frontier,
@@ -1071,6 +1172,101 @@ int trx_hibf_membership_dev(trx_hibf_t * h, const uint64_t * d_kmers, uint64_t n
         stats[0] = visited;
         stats[1] = static_cast<uint64_t>(h->depth);
     }
+    return TRX_OK;
+}
+
+// seqan's own result form (membership_for returns user-bin ids): counts[i] ids per k-mer, ids concatenated in k-mer order,
+// ascending inside a k-mer.  The rows are computed like trx_hibf_membership's and compacted on the device before they
+// cross PCIe: at C2 a k-mer hits ~17 of 1024 user bins, so 2-byte ids are 38 B per k-mer instead of a 128-byte row.
+int trx_hibf_membership_ids(trx_hibf_t * h, const uint64_t * kmers, uint64_t n, uint32_t * counts, void * ids, uint32_t id_bytes,
+                            uint64_t cap, uint64_t * n_ids, uint64_t * stats)
+{
+    if (!h || !n_ids || (n && (!kmers || !counts)) || (cap && !ids))
+        return set_error(TRX_EINVAL, "NULL argument");
+    if (id_bytes != 2 && id_bytes != 4)
+        return set_error(TRX_EINVAL, "id_bytes must be 2 or 4");
+    if (id_bytes == 2 && h->n_user_bins > 65536)
+        return set_error(TRX_ERANGE, "%llu user bins do not fit 2-byte ids", (unsigned long long)h->n_user_bins);
+    *n_ids = 0;
+    if (stats)
+        stats[0] = 0, stats[1] = static_cast<uint64_t>(h->depth);
+    if (n == 0)
+        return TRX_OK;
+    trx_ctx * c = h->ctx;
+    TRX_TRY(c->use());
+    uint64_t const piece = 1ull << 20;
+    uint64_t const W = h->out_words;
+    TRX_TRY(h->d_kmers.reserve(n * 8));
+    TRX_TRY(h->d_out.reserve(piece * W * 8 * 2)); // two pieces of rows: one being compacted while the next is computed
+    TRX_TRY(h->d_id_counts.reserve(n * 4));
+    TRX_TRY(h->d_id_blocks.reserve(2 * ((piece + kIdsBlock - 1) / kIdsBlock + 2) * 8));
+    TRX_TRY(h->d_ids.reserve((cap ? cap : 1) * id_bytes));
+    h->h_id_total.pinned_host = true;
+    TRX_TRY(h->h_id_total.reserve(((n + piece - 1) / piece + 1) * 8));
+    auto * d_kmers = static_cast<uint64_t *>(h->d_kmers.ptr);
+    auto * d_rows = static_cast<uint64_t *>(h->d_out.ptr);
+    auto * d_counts = static_cast<uint32_t *>(h->d_id_counts.ptr);
+    auto * d_ids = static_cast<uint8_t *>(h->d_ids.ptr);
+    auto * h_totals = static_cast<unsigned long long *>(h->h_id_total.ptr);
+    TRX_CUDA(cudaMemcpyAsync(d_kmers, kmers, n * 8, cudaMemcpyHostToDevice, c->stream));
+    if (!c->copy_stream)
+        TRX_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+    uint64_t visited = 0, written = 0;
+    size_t k = 0;
+    for (uint64_t done = 0; done < n; done += piece, ++k)
+    {
+        uint64_t const m = n - done < piece ? n - done : piece;
+        uint64_t * const rows = d_rows + (k & 1) * piece * W;
+        uint64_t st[2] = {0, 0};
+        TRX_TRY(trx_hibf_membership_dev(h, d_kmers + done, m, rows, st));
+        visited += st[0];
+        unsigned const blocks = static_cast<unsigned>((m + kIdsBlock - 1) / kIdsBlock);
+        auto * d_block_tot = static_cast<unsigned long long *>(h->d_id_blocks.ptr) + (k & 1) * (blocks + 2);
+        ids_count_kernel<<<blocks, kIdsBlock, 0, c->stream>>>(rows, m, static_cast<uint32_t>(W), d_counts + done, d_block_tot);
+        ids_scan_blocks_kernel<<<1, 1024, 0, c->stream>>>(d_block_tot, blocks);
+        c->launches += 2;
+        TRX_CUDA(cudaMemcpyAsync(h_totals + k, d_block_tot + blocks, 8, cudaMemcpyDeviceToHost, c->stream));
+        TRX_CUDA(cudaStreamSynchronize(c->stream)); // how many ids this piece has (and whether they still fit)
+        uint64_t const piece_ids = h_totals[k];
+        if (written + piece_ids > cap)
+        {
+            *n_ids = written + piece_ids;
+            cudaStreamSynchronize(c->copy_stream);
+            return set_error(TRX_ECAPACITY, "trx_hibf_membership_ids: at least %llu ids, room for %llu",
+                             (unsigned long long)(written + piece_ids), (unsigned long long)cap);
+        }
+        if (piece_ids)
+        {
+            if (id_bytes == 2)
+                ids_write_kernel<uint16_t><<<blocks, kIdsBlock, 0, c->stream>>>(rows, m, static_cast<uint32_t>(W), d_block_tot,
+                                                                               reinterpret_cast<uint16_t *>(d_ids) + written);
+            else
+                ids_write_kernel<uint32_t><<<blocks, kIdsBlock, 0, c->stream>>>(rows, m, static_cast<uint32_t>(W), d_block_tot,
+                                                                               reinterpret_cast<uint32_t *>(d_ids) + written);
+            ++c->launches;
+        }
+        TRX_CUDA(cudaGetLastError());
+        if (k >= c->copy_events.size())
+        {
+            cudaEvent_t e;
+            TRX_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            c->copy_events.push_back(e);
+        }
+        TRX_CUDA(cudaEventRecord(c->copy_events[k], c->stream));
+        TRX_CUDA(cudaStreamWaitEvent(c->copy_stream, c->copy_events[k], 0));
+        TRX_CUDA(cudaMemcpyAsync(counts + done, d_counts + done, m * 4, cudaMemcpyDeviceToHost, c->copy_stream));
+        if (piece_ids)
+            TRX_CUDA(cudaMemcpyAsync(static_cast<uint8_t *>(ids) + written * id_bytes, d_ids + written * id_bytes, piece_ids * id_bytes,
+                                     cudaMemcpyDeviceToHost, c->copy_stream));
+        written += piece_ids;
+        // the rows buffer (k & 1) is reused two pieces later: its compaction must have finished by then — it has, the
+        // stream was synchronised above before the next piece's kernels were enqueued
+    }
+    TRX_CUDA(cudaStreamSynchronize(c->copy_stream));
+    TRX_CUDA(cudaStreamSynchronize(c->stream));
+    *n_ids = written;
+    if (stats)
+        stats[0] = visited;
     return TRX_OK;
 }
 
