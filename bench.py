@@ -322,7 +322,7 @@ def run_ours(args):
         peak, peak_src = peaks()
         algo_bytes = 32.0 * HASH_FUNS * visited_per_step
         traffic = None  # DRAM bytes per step of the K3 kernels, from the committed ncu --set full capture
-        tpath = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1_traffic.json")
+        tpath = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r2_traffic.json")
         if os.path.exists(tpath):
             traffic = json.load(open(tpath))["k3_dram_bytes_per_kmer"] * args.batch
         step_s = ms / 1e3 / args.steps
@@ -562,8 +562,17 @@ def extra_measurements(t, ctx, torch, residues, offs, rec_bin, planted, hibf, pe
     os.environ.pop("TRX_REGEX_FILTER")
     out["verify_prosite"]["exact_automaton_residues_per_s"] = n_res / sec2x
     out["verify_prosite"]["hits_equal_exact_automaton"] = bool(np.array_equal(h2, h2x))
-    out["verify_prosite"]["exact_automaton_note"] = ("no prefilter: reverse-searcher DFA phase 1 (exact match starts, one table "
-                                                     "lookup per residue) + DFA phase 2")
+    out["verify_prosite"]["exact_automaton_note"] = ("TRX_REGEX_FILTER=off; this pattern's reverse searcher is too large for "
+                                                     "the starts kernel: position automaton in phase 1, DFA in phase 2")
+    # the config's own query without a prefilter: small reverse searcher → regex_scan_starts_dfa (exact match starts, one
+    # table lookup per residue) + exact-start phase 2
+    os.environ["TRX_REGEX_FILTER"] = "off"
+    h1x = txt.scan(rx)
+    sec1x = timed(lambda: txt.scan(rx), 3)
+    os.environ.pop("TRX_REGEX_FILTER")
+    out["verify_no_prefilter"] = {"pattern": QUERY, "residues_per_s": n_res / sec1x, "us_per_scan": sec1x * 1e6,
+                                  "hits_equal_prefiltered_scan": bool(np.array_equal(h1x, hits)),
+                                  "route": "reverse-searcher DFA phase 1 + exact-start phase 2"}
     os.environ["TRX_REGEX_FILTER"] = "off"
     os.environ["TRX_REGEX_DFA"] = "off"
     h2n = txt.scan(rx2)
