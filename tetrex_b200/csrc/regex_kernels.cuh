@@ -761,55 +761,16 @@ __device__ int64_t match_first(regex_dev const & re, At at, int64_t s, int64_t L
     return best;
 }
 
-// The same anchored leftmost-longest match on the determinised automaton: one table lookup per byte instead of a loop over
-// the live positions.  Semantics are match_longest's: the last position at which an accepting state was live wins.
-template <class At>
-__device__ __forceinline__ int64_t match_longest_dfa(resolve_params const & p, uint16_t const * trans, uint8_t const * s_cls, At at,
-                                                     int64_t s, int64_t L)
-{
-    uint32_t const ncls = p.dfa_classes, accept_from = p.dfa_first_accept * ncls; // the table holds next_state * classes
-    uint32_t st = ncls;
-    int64_t best = -1;
-    for (int64_t pos = s; pos < L;)
-    {
-        st = trans[st + s_cls[at(pos)]];
-        if (st == 0)
-            break;
-        ++pos;
-        if (st >= accept_from && (!p.anchor_end || pos == L))
-            best = pos;
-    }
-    return best;
-}
-
 // One WARP per record that phase 1 listed (the list length is read from device memory, so no host round trip
 // separates the two phases).  The 32 lanes try 32 consecutive start positions at once — almost all die on the
 // first byte — and a ballot picks the leftmost start that really matches; the warp then jumps to the end of
 // that match (FindAndConsume) and goes on.  Chunks phase 1 did not flag are skipped whole.
 template <int W, int DIR>
-__device__ __forceinline__ void phase2_body(resolve_params const & p, regex_dev & s_re, uint8_t * s_cls)
+__device__ __forceinline__ void phase2_body(resolve_params const & p, regex_dev & s_re)
 {
     // usually a handful of records are listed: CTAs without work leave before staging anything
     if (static_cast<uint64_t>(blockIdx.x) * (blockDim.x >> 5) >= *p.rec_count)
         return;
-    bool const dfa = p.dfa_trans != nullptr;
-    uint16_t const * trans = p.dfa_trans;
-    if (dfa)
-    {
-        for (unsigned i = threadIdx.x; i < 256; i += blockDim.x)
-            s_cls[i] = p.dfa_cls[i];
-        // the table of a typical pattern is a few KB (config 3: <= 2.1 KB): it takes the shared memory the automaton image
-        // would have used; larger ones are read through L1
-        unsigned const entries = p.dfa_states * p.dfa_classes;
-        if (entries * 2 <= sizeof(regex_dev))
-        {
-            uint16_t * dst = reinterpret_cast<uint16_t *>(&s_re);
-            for (unsigned i = threadIdx.x; i < entries; i += blockDim.x)
-                dst[i] = p.dfa_trans[i];
-            trans = dst;
-        }
-    }
-    else
     {
         uint32_t const * src = reinterpret_cast<uint32_t const *>(p.re);
         uint32_t * dst = reinterpret_cast<uint32_t *>(&s_re);
@@ -852,18 +813,13 @@ __device__ __forceinline__ void phase2_body(resolve_params const & p, regex_dev 
             int64_t e = -1;
             if (my_s < limit && (!anchor_begin || lane == 0))
             {
-                if (dfa)
-                    e = match_longest_dfa(p, trans, s_cls, at, my_s, L);
-                else
-                {
-                    uint8_t const c = at(my_s);
-                    uint64_t quick = 0;
+                uint8_t const c = at(my_s);
+                uint64_t quick = 0;
 #pragma unroll
-                    for (int k = 0; k < W; ++k)
-                        quick |= re.first[k] & re.B[c][k];
-                    if (quick)
-                        e = re.posix_longest ? match_longest<W>(re, at, my_s, L) : match_first(re, at, my_s, L);
-                }
+                for (int k = 0; k < W; ++k)
+                    quick |= re.first[k] & re.B[c][k];
+                if (quick)
+                    e = re.posix_longest ? match_longest<W>(re, at, my_s, L) : match_first(re, at, my_s, L);
             }
             unsigned const found = __ballot_sync(0xffffffffu, e > my_s);
             if (found)
@@ -1188,8 +1144,7 @@ template <int W, int DIR>
 __global__ void __launch_bounds__(128) regex_scan_phase2(resolve_params p)
 {
     __shared__ regex_dev s_re; // the automaton, staged once per CTA: every attempt starts with a B[] lookup
-    __shared__ uint8_t s_cls[256];
-    phase2_body<W, DIR>(p, s_re, s_cls);
+    phase2_body<W, DIR>(p, s_re);
 }
 
 // Patterns without any selective necessary factor and with a determinised matcher skip phase 1: every record of a
@@ -1236,7 +1191,6 @@ template <int W, int DIR>
 __global__ void __launch_bounds__(128) regex_scan_phase2_multi(resolve_params const * __restrict__ params)
 {
     __shared__ regex_dev s_re;
-    __shared__ uint8_t s_cls[256];
     __shared__ resolve_params s_p;
     extern __shared__ __align__(16) uint8_t dfa_smem[]; // sized by the host for the largest DFA of the batch
     if (threadIdx.x == 0)
@@ -1245,7 +1199,7 @@ __global__ void __launch_bounds__(128) regex_scan_phase2_multi(resolve_params co
     if (s_p.dfa_trans)
         phase2_dfa_block<DIR>(s_p, dfa_smem);
     else
-        phase2_body<W, DIR>(s_p, s_re, s_cls);
+        phase2_body<W, DIR>(s_p, s_re);
 }
 
 } // namespace trx

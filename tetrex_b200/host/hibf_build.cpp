@@ -15,7 +15,10 @@
 // order shuffled with std::random_device (…cpp:118-121), so its own numbering differs from run to run; membership
 // answers do not depend on it.  Here the children are built in layout order.
 #include <algorithm>
+#include <chrono>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 
 #include "hibf_layout.hpp"
 #include "rh_order.hpp"
@@ -233,8 +236,13 @@ hibf_image build_hibf_like_seqan(trx_ctx_t * ctx, std::vector<uint64_t> const & 
         if (kmer_counts[b] == 0)
             throw error("user bin " + std::to_string(b) + " holds no k-mer: the HIBF layout needs at least one per bin");
     }
+    bool const trace = getenv("TRX_BUILD_TRACE") != nullptr; // phase times on stderr
+    auto const t0 = std::chrono::steady_clock::now();
+    auto const since = [&] { return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count(); };
     hibf::layout const l = hibf::compute_layout(cfg, kmer_counts, sketches);
     hibf::graph_node const root = hibf::make_graph(l);
+    if (trace)
+        fprintf(stderr, "hibf build: layout of %zu user bins (%zu lower-level IBFs) %.2f s\n", cfg.number_of_user_bins, l.max_bins.size(), since());
 
     hibf_image img;
     img.number_of_user_bins = cfg.number_of_user_bins;
@@ -246,6 +254,8 @@ hibf_image build_hibf_like_seqan(trx_ctx_t * ctx, std::vector<uint64_t> const & 
     builder b{ctx, cfg, values, offsets, hibf::compute_fpr_correction(cfg.maximum_fpr, cfg.number_of_hash_functions, root.number_of_technical_bins), img};
     kmer_set root_kmers;
     b.build_node(root_kmers, root, true, 0);
+    if (trace)
+        fprintf(stderr, "hibf build: hierarchical build (set replay + emplace) done at %.2f s\n", since());
     return img;
 }
 

@@ -11,7 +11,9 @@
 #include <queue>
 #include <random>
 #include <stdexcept>
+#include <atomic>
 #include <string>
+#include <thread>
 #include <unordered_map>
 
 namespace trxh::hibf
@@ -20,6 +22,30 @@ namespace trxh::hibf
 namespace
 {
 constexpr size_t none = std::numeric_limits<size_t>::max();
+
+// fn(i) for i in [begin, end) on the host's cores, handed out one index at a time.  Only used where the iterations write
+// to disjoint places and the result does not depend on their order (this toolchain has no OpenMP runtime).
+template <class F>
+void parallel_for(size_t begin, size_t end, F && fn)
+{
+    size_t const n = end > begin ? end - begin : 0;
+    unsigned const workers = static_cast<unsigned>(std::min<size_t>(std::max(1u, std::thread::hardware_concurrency()), n));
+    if (workers <= 1 || n < 8)
+    {
+        for (size_t i = begin; i < end; ++i)
+            fn(i);
+        return;
+    }
+    std::atomic<size_t> next{begin};
+    std::vector<std::thread> pool;
+    for (unsigned w = 0; w < workers; ++w)
+        pool.emplace_back([&] {
+            for (size_t i = next.fetch_add(1); i < end; i = next.fetch_add(1))
+                fn(i);
+        });
+    for (std::thread & t : pool)
+        t.join();
+}
 
 size_t next_multiple_of_64(size_t v) { return ((v + 63) >> 6) << 6; }          // include/hibf/misc/next_multiple_of_64.hpp
 size_t divide_and_ceil(size_t a, size_t b) { return (a + (b - 1)) / b; }       // include/hibf/misc/divide_and_ceil.hpp
@@ -335,16 +361,19 @@ void cluster_bins(std::vector<hyperloglog> const & sketches, std::vector<size_t>
     }
 
     double min_dist = std::numeric_limits<double>::max();
+    // every queue is filled by one thread in the reference's push order, the minimum is then taken in index order: the
+    // result is what one thread computes, the n^2/2 sketch merges just do not wait for each other
+    parallel_for(0, clustering.size(), [&](size_t i) {
+        for (size_t j = i + 1; j < clustering.size(); ++j)
+        {
+            hyperloglog temp = clustering[i].hll;
+            double const estimate_ij = temp.merge_and_estimate(clustering[j].hll);
+            double const distance = 2 - (estimates[i] + estimates[j]) / estimate_ij; // Jaccard distance estimate
+            dist[i].pq.push({j + first, distance});
+        }
+    });
     for (size_t i = 0; i < clustering.size(); ++i)
     {
-        for (size_t j = 0; j < clustering.size(); ++j)
-            if (i < j)
-            {
-                hyperloglog temp = clustering[i].hll;
-                double const estimate_ij = temp.merge_and_estimate(clustering[j].hll);
-                double const distance = 2 - (estimates[i] + estimates[j]) / estimate_ij; // Jaccard distance estimate
-                dist[i].pq.push({j + first, distance});
-            }
         if (dist[i].pq.empty())
             continue;
         neighbor const & curr = dist[i].pq.top();
@@ -378,17 +407,24 @@ void cluster_bins(std::vector<hyperloglog> const & sketches, std::vector<size_t>
         min_id_seen = none;
         min_dist = std::numeric_limits<double>::max();
         hyperloglog const new_hll = clustering.back().hll;
-        for (size_t i = 0; i < dist.size(); ++i)
-        {
+        // the queues are independent of each other (remaining_ids is only read here); the minimum is taken afterwards in
+        // index order, like the one thread of the reference does
+        parallel_for(0, dist.size(), [&](size_t i) {
             size_t const other_id = dist[i].id;
             if (other_id == new_id || !remaining_ids.count(other_id))
-                continue;
+                return;
             hyperloglog temp = new_hll;
             double const estimate_ij = temp.merge_and_estimate(clustering[other_id - first].hll);
             double const distance = 2 - (estimates[other_id - first] + estimates.back()) / estimate_ij;
             dist[i].pq.push({new_id, distance});
             while (!remaining_ids.count(dist[i].pq.top().id)) // lazy deletion of merged neighbours
                 dist[i].pq.pop();
+        });
+        for (size_t i = 0; i < dist.size(); ++i)
+        {
+            size_t const other_id = dist[i].id;
+            if (other_id == new_id || !remaining_ids.count(other_id))
+                continue;
             neighbor const & curr = dist[i].pq.top();
             if (curr.dist < min_dist)
             {
@@ -619,12 +655,26 @@ private:
     void recursion(matrix_t & matrix, matrix_t & ll_matrix, trace_t & trace)
     {
         auto const & counts = *data.kmer_counts;
+        // precompute_union_estimates_for(j) for every column at once: the chains of different columns do not depend on
+        // each other (n^2/2 sketch merges and estimates — most of the layout's time), rows of a lower-triangular table
+        std::vector<std::vector<uint64_t>> chains;
+        if (!cfg.disable_estimate_union)
+        {
+            chains.resize(num_user_bins);
+            parallel_for(1, num_user_bins, [&](size_t j) {
+                chains[j].resize(j + 1);
+                precompute_union_estimates_for(chains[j], *data.sketches, counts, data.positions, static_cast<int64_t>(j));
+            });
+        }
         for (size_t j = 1; j < num_user_bins; ++j)
         {
             size_t const current_weight = counts[data.positions[j]];
             double const ub_cardinality = static_cast<double>(current_weight);
             if (!cfg.disable_estimate_union)
-                precompute_union_estimates_for(data.union_estimates, *data.sketches, counts, data.positions, j);
+            {
+                std::copy(chains[j].begin(), chains[j].end(), data.union_estimates.begin());
+                std::vector<uint64_t>().swap(chains[j]);
+            }
             for (size_t i = 1; i < num_technical_bins; ++i)
             {
                 size_t minimum = none, full_minimum = none;
