@@ -64,6 +64,8 @@ int trx_ctx_sync(trx_ctx_t *ctx);
 void *trx_ctx_stream(trx_ctx_t *ctx);
 /* number of kernels this context has launched since creation (bench.py's gpu_launches) */
 uint64_t trx_ctx_launches(trx_ctx_t *ctx);
+/* CUDA device ordinal of the context (callers that open further contexts on the same device, one per host thread) */
+int trx_ctx_device(const trx_ctx_t *ctx);
 /* raw device memory for callers that have no CUDA runtime of their own (the C++ host layer) */
 int trx_dev_alloc(trx_ctx_t *ctx, uint64_t bytes, void **out);
 int trx_dev_free(trx_ctx_t *ctx, void *ptr);

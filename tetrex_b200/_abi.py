@@ -33,6 +33,7 @@ PROTOTYPES = {
     "trx_ctx_destroy": (None, [vp]),
     "trx_ctx_sync": (C.c_int, [vp]),
     "trx_ctx_stream": (vp, [vp]),
+    "trx_ctx_device": (C.c_int, [vp]),
     "trx_ctx_launches": (C.c_uint64, [vp]),
     "trx_dev_alloc": (C.c_int, [vp, C.c_uint64, vpp]),
     "trx_dev_free": (C.c_int, [vp, vp]),

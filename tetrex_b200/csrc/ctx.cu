@@ -158,6 +158,11 @@ uint64_t trx_ctx_launches(trx_ctx_t * ctx)
     return ctx ? ctx->launches : 0;
 }
 
+int trx_ctx_device(const trx_ctx_t * ctx)
+{
+    return ctx ? ctx->device : -1;
+}
+
 int trx_dev_alloc(trx_ctx_t * ctx, uint64_t bytes, void ** out)
 {
     if (!ctx || !out)

@@ -15,10 +15,15 @@
 // order shuffled with std::random_device (…cpp:118-121), so its own numbering differs from run to run; membership
 // answers do not depend on it.  Here the children are built in layout order.
 #include <algorithm>
+#include <atomic>
 #include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
+#include <functional>
+#include <mutex>
+#include <thread>
+#include <unordered_map>
 
 #include "hibf_layout.hpp"
 #include "rh_order.hpp"
@@ -60,9 +65,11 @@ struct builder
     hibf::config const & cfg;
     std::vector<uint64_t> const & values;  // k-mers of all user bins, in HIBFIndex::emplace order
     std::vector<uint64_t> const & offsets; // user bin b = values[offsets[b], offsets[b + 1])
-    std::vector<double> fpr_correction;
+    std::vector<double> const & fpr_correction;
     hibf_image & out;
-    size_t next_ibf{0};
+    // position of every node's IBF, fixed before anything is built: the order in which ONE thread would have reached the
+    // nodes (a node, its favourite child's subtree, then its other children in layout order)
+    std::unordered_map<graph_node const *, size_t> const & ibf_pos_of;
     std::vector<uint64_t> stage_values;
     std::vector<uint32_t> stage_bins;
 
@@ -111,7 +118,7 @@ struct builder
     // parent_kmers unless it is the root.
     size_t build_node(kmer_set & parent_kmers, graph_node const & node, bool is_root, size_t parent_ibf_idx)
     {
-        size_t const ibf_pos = next_ibf++;
+        size_t const ibf_pos = ibf_pos_of.at(&node);
         out.next_ibf_id[ibf_pos].assign(node.number_of_technical_bins, ibf_pos);
         out.ibf_bin_to_user_bin_id[ibf_pos].assign(node.number_of_technical_bins, UINT64_MAX); // bin_kind::merged
         kmer_set kmers;
@@ -150,18 +157,67 @@ struct builder
             kmers.clear();
 
             // the other merged bins: one lower-level IBF each
+            std::vector<size_t> todo;
             for (size_t c = 0; c < node.children.size(); ++c)
+                if (!(node.max_bin_is_merged() && c == *node.favourite_child_idx))
+                    todo.push_back(c);
+            unsigned const workers = is_root ? static_cast<unsigned>(std::min<size_t>({cfg.threads, todo.size(), size_t{32}})) : 1u;
+            if (workers <= 1)
             {
-                if (node.max_bin_is_merged() && c == *node.favourite_child_idx)
-                    continue;
-                graph_node const & child = node.children[c];
-                kmer_set local_kmers;
-                size_t const pos = build_node(local_kmers, child, false, ibf_pos);
-                out.prev_ibf_id[pos] = {parent_ibf_idx, child.parent_bin_index}; // as written: the caller's parent (…cpp:135)
-                out.next_ibf_id[ibf_pos][child.parent_bin_index] = pos;
-                insert_into_ibf(local_kmers, 1, child.parent_bin_index, ibf);
-                if (!is_root)
-                    parent_kmers.insert_all(local_kmers);
+                for (size_t c : todo)
+                {
+                    graph_node const & child = node.children[c];
+                    kmer_set local_kmers;
+                    size_t const pos = build_node(local_kmers, child, false, ibf_pos);
+                    out.prev_ibf_id[pos] = {parent_ibf_idx, child.parent_bin_index}; // as written: the caller's parent (…cpp:135)
+                    out.next_ibf_id[ibf_pos][child.parent_bin_index] = pos;
+                    insert_into_ibf(local_kmers, 1, child.parent_bin_index, ibf);
+                    if (!is_root)
+                        parent_kmers.insert_all(local_kmers);
+                }
+            }
+            else
+            {
+                // The root's children do not share anything but the root's matrix (…cpp:109-142 hands them to OpenMP threads
+                // for the same reason): every worker builds whole subtrees with a context of its own on the same device and
+                // takes a lock only to emplace a finished child's k-mers into the root's bin.  Nothing a worker computes
+                // depends on the others, so the index is the same as with one thread.
+                std::atomic<size_t> next{0};
+                std::mutex root_mutex;
+                std::vector<std::string> errors(workers);
+                std::vector<std::thread> pool;
+                int const device = trx_ctx_device(ctx);
+                for (unsigned w = 0; w < workers; ++w)
+                    pool.emplace_back([&, w] {
+                        trx_ctx_t * own = nullptr;
+                        try
+                        {
+                            check(trx_ctx_create(device, nullptr, &own));
+                            builder local{own, cfg, values, offsets, fpr_correction, out, ibf_pos_of};
+                            for (size_t i = next.fetch_add(1); i < todo.size(); i = next.fetch_add(1))
+                            {
+                                graph_node const & child = node.children[todo[i]];
+                                kmer_set local_kmers;
+                                size_t const pos = local.build_node(local_kmers, child, false, ibf_pos);
+                                out.prev_ibf_id[pos] = {parent_ibf_idx, child.parent_bin_index};
+                                std::lock_guard<std::mutex> guard(root_mutex);
+                                out.next_ibf_id[ibf_pos][child.parent_bin_index] = pos;
+                                local.insert_into_ibf(local_kmers, 1, child.parent_bin_index, ibf);
+                            }
+                        }
+                        catch (std::exception const & e)
+                        {
+                            errors[w] = e.what();
+                            next.store(todo.size());
+                        }
+                        if (own)
+                            trx_ctx_destroy(own);
+                    });
+                for (std::thread & t : pool)
+                    t.join();
+                for (std::string const & e : errors)
+                    if (!e.empty())
+                        throw error(e);
             }
 
             // the user bins that live in this IBF
@@ -216,7 +272,9 @@ hibf_image build_hibf_like_seqan(trx_ctx_t * ctx, std::vector<uint64_t> const & 
     cfg.number_of_user_bins = offsets.size() - 1;
     cfg.number_of_hash_functions = hash_count;
     cfg.maximum_fpr = fpr; // float → double like `.maximum_fpr = fpr_` (include/index_hibf.h:127)
-    cfg.threads = threads ? threads : 1;
+    // -t decides how many host threads build the root's children side by side; the index does not depend on it (unlike the
+    // reference's, whose clustering breaks ties by thread id), so the default is every core
+    cfg.threads = threads > 1 ? threads : std::max(1u, std::min(32u, std::thread::hardware_concurrency()));
     cfg.validate_and_set_defaults();
 
     std::vector<hibf::hyperloglog> sketches(cfg.number_of_user_bins, hibf::hyperloglog{cfg.sketch_bits});
@@ -251,7 +309,22 @@ hibf_image build_hibf_like_seqan(trx_ctx_t * ctx, std::vector<uint64_t> const & 
     img.ibf_bin_to_user_bin_id.resize(number_of_ibfs);
     img.prev_ibf_id.resize(number_of_ibfs, {0, 0});
     img.next_ibf_id.resize(number_of_ibfs);
-    builder b{ctx, cfg, values, offsets, hibf::compute_fpr_correction(cfg.maximum_fpr, cfg.number_of_hash_functions, root.number_of_technical_bins), img};
+    std::vector<double> const fpr_correction =
+        hibf::compute_fpr_correction(cfg.maximum_fpr, cfg.number_of_hash_functions, root.number_of_technical_bins);
+    std::unordered_map<graph_node const *, size_t> ibf_pos_of;
+    {
+        size_t next = 0;
+        std::function<void(graph_node const &)> number = [&](graph_node const & n) {
+            ibf_pos_of[&n] = next++;
+            if (n.max_bin_is_merged())
+                number(n.children[*n.favourite_child_idx]);
+            for (size_t c = 0; c < n.children.size(); ++c)
+                if (!(n.max_bin_is_merged() && c == *n.favourite_child_idx))
+                    number(n.children[c]);
+        };
+        number(root);
+    }
+    builder b{ctx, cfg, values, offsets, fpr_correction, img, ibf_pos_of};
     kmer_set root_kmers;
     b.build_node(root_kmers, root, true, 0);
     if (trace)
