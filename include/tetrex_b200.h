@@ -352,6 +352,16 @@ int trx_regex_scan_multi(trx_text_t *text, trx_regex_t *const *regexes, uint32_t
 int trx_regex_filter_plan(const trx_regex_t *re, const double *byte_freq, int reverse_strand, const uint8_t *map256,
                           int32_t out[136]);
 
+/* Host only: the class window trx_regex_scan_multi's bit-parallel first stage (regex_window_multi) would use for the
+ * pattern on a text with these byte frequencies: up to 6 CONSECUTIVE text bytes every match contains, each from a byte
+ * class.  out[0] = 1 usable / 0 none (the pattern then takes the term-list stage), out[1] = length, out[2], out[3] = the
+ * window's first byte lies at [match start + out[2], match start + out[3]]; classes[8k .. 8k+8) = 256-bit class of window
+ * byte k.  out[4] = confirm checks evaluated where the window holds (other necessary positions of the pattern): check c
+ * holds if the byte at window byte 0 + d is in its class for a d in [out[5+10c], out[6+10c]] (signed), class = 256-bit
+ * mask in out[7+10c .. 15+10c).  pass[0] = the fraction of text positions expected to pass the window, pass[1] = window
+ * and checks.  classes and pass may be NULL. */
+int trx_regex_window_plan(const trx_regex_t *re, const double *byte_freq, int32_t out[65], uint32_t classes[48], double pass[2]);
+
 /* ------------------------------------------------------------------- multi-GPU: collectives (8(e)) */
 /* One communicator per context = per GPU (NCCL over NVLink/NVSwitch, bound at run time: no link dependency, single-GPU
  * use never loads it).  The reference has nothing of the kind (single process, OpenMP over bins, include/query.h:113);

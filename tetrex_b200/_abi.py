@@ -100,6 +100,7 @@ PROTOTYPES = {
     "trx_regex_scan_end": (C.c_int, [vp, C.c_int, vp, u64p, u64p]),
     "trx_regex_scan_multi": (C.c_int, [vp, vpp, C.c_uint32, vp, C.c_uint64, vp, vp, C.c_uint64, u64p, vp, vp]),
     "trx_regex_filter_plan": (C.c_int, [vp, vp, C.c_int, vp, vp]),
+    "trx_regex_window_plan": (C.c_int, [vp, vp, vp, vp, vp]),
     "trx_comm_unique_id": (C.c_int, [vp]),
     "trx_comm_create": (C.c_int, [vp, C.c_int, C.c_int, vp, vpp]),
     "trx_comm_create_all": (C.c_int, [vpp, C.c_int, vpp]),

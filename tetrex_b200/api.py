@@ -7,7 +7,9 @@ Host-buffer methods take numpy arrays; ``*_dev`` methods take raw device pointer
 """
 from __future__ import annotations
 
+import atexit
 import ctypes as C
+import time
 import weakref
 
 import numpy as np
@@ -26,6 +28,20 @@ def _ptr(a):
     return a.ctypes.data if a is not None else None
 
 
+_live_contexts = weakref.WeakSet()
+
+
+@atexit.register
+def _close_contexts():
+    # device handles go while the CUDA runtime is still loaded: module globals die in no particular order at interpreter
+    # exit, and a trx_*_destroy after the runtime's own teardown is a crash
+    for ctx in list(_live_contexts):
+        try:
+            ctx.close()
+        except Exception:
+            pass
+
+
 class Context:
     """One CUDA device + one stream (trx_ctx_t).  stream = raw cudaStream_t or None."""
 
@@ -34,6 +50,7 @@ class Context:
         check(lib().trx_ctx_create(device, stream, C.byref(self._h)))
         self.device = device
         self._children = weakref.WeakSet()  # handles that must be destroyed before the context
+        _live_contexts.add(self)
 
     def close(self):
         if self._h:
@@ -382,6 +399,26 @@ class Regex:
         self.pattern = pattern
         self.positions = lib().trx_regex_positions(self._h)
 
+    def window_plan(self, byte_freq):
+        """The class window the multi-pattern first stage would use (host only), or None."""
+        f = _np(byte_freq, np.float64)
+        assert len(f) == 256
+        out = np.zeros(65, dtype=np.int32)
+        cls = np.zeros(48, dtype=np.uint32)
+        p = np.zeros(2, dtype=np.float64)
+        check(lib().trx_regex_window_plan(self._h, _ptr(f), _ptr(out), _ptr(cls), _ptr(p)))
+        if not out[0]:
+            return None
+
+        def members(words):
+            return bytes(32 * w + b for w in range(8) for b in range(32) if (int(words[w]) >> b) & 1)
+
+        sets = [members(cls[8 * k:8 * k + 8]) for k in range(int(out[1]))]
+        confirm = [(members(out[7 + 10 * c:15 + 10 * c].view(np.uint32)), int(out[5 + 10 * c]), int(out[6 + 10 * c]))
+                   for c in range(int(out[4]))]
+        return {"len": int(out[1]), "off_lo": int(out[2]), "off_hi": int(out[3]), "classes": sets, "confirm": confirm,
+                "pass": float(p[0]), "confirmed": float(p[1])}
+
     def filter_plan(self, byte_freq, reverse_strand=False, map256=None) -> dict:
         """The phase-1 prefilter a scan would use on a text with these relative byte frequencies (host only)."""
         f = _np(byte_freq, np.float64)
@@ -515,8 +552,10 @@ class Text:
         total = C.c_uint64()
         per = np.zeros(max(n, 1), dtype=np.uint64)
         st = np.zeros(4, dtype=np.uint64)
+        t0 = time.perf_counter()
         check(lib().trx_regex_scan_multi(self._h, handles, n, _ptr(cand), stride, C.addressof(self._mhit_buf), _ptr(self._mpat_buf),
                                          cap, C.byref(total), _ptr(per), _ptr(st)))
+        self.last_multi_call_seconds = time.perf_counter() - t0
         arr = np.frombuffer(self._mhit_buf, dtype=np.uint32, count=4 * total.value).reshape(-1, 4)
         bounds = np.concatenate([[0], np.cumsum(per[:n])]).astype(np.int64)
         out = [arr[bounds[i]:bounds[i + 1]].copy() for i in range(n)]

@@ -70,6 +70,12 @@ struct trx_text
         // the plan for multi-pattern passes (whole alphabet, larger classes, as selective as the pattern allows)
         int multi_kind{-1}; // -1 = not derived yet
         trx::atom_spec multi_atoms;
+        // class window for regex_window_multi (derive_class_window): -1 = not derived yet, 0 = none, 1 = usable
+        int win_state{-1};
+        int win_len{0}, win_off_lo{0}, win_off_hi{0};
+        uint32_t win_cls[trx::kWindowLen][8];
+        int win_n_confirm{0};
+        trx::confirm_check win_confirm[trx::kMaxConfirm];
     };
     std::vector<cached_choice> choices;
     // per-scan scratch
@@ -1781,6 +1787,162 @@ int trx_regex_filter_plan(const trx_regex_t * re, const double * byte_freq, int 
 namespace
 {
 
+// Class window of a pattern for regex_window_multi: up to kWindowLen CONSECUTIVE positions of the automaton that every
+// match passes through (dominators, each with its successor as the only way on), with the byte class of each.  "The text
+// carries class_0 .. class_{len-1} at p .. p+len-1" is then necessary for a match whose first byte lies in
+// [p - off_hi, p - off_lo].  The most selective such run (byte frequencies of the text) is taken; ok = selective enough to
+// hand its survivors to phase 2 directly.
+struct class_window
+{
+    bool ok{false};
+    int len{0};
+    int off_lo{0}, off_hi{0};
+    uint32_t cls[kWindowLen][8]; // 256-bit byte sets
+    double pass{1.0};            // expected fraction of text positions the window lets through …
+    double confirmed{1.0};       // … and of those the confirm checks keep
+    int n_confirm{0};
+    confirm_check confirm[kMaxConfirm]; // other necessary positions, offsets relative to the window's first byte
+};
+
+constexpr size_t kFewLeftovers = 24;         // patterns without a class window, when most of the batch has one
+constexpr double kMaxWindowPass = 2e-3;      // survivors per text position and pattern the window stage may hand to its confirm checks
+constexpr double kMaxWindowConfirmed = 1.2e-4; // … and to phase 2 (its record lists hold kMultiListCap entries; a longer list sends the pattern to the single-pattern path)
+
+class_window derive_class_window(regex_dev const & img, double const * freq)
+{
+    class_window none;
+    automaton_graph const g = build_graph(img);
+    int const P = g.P;
+    if (P <= 0 || img.anchor_begin || img.anchor_end)
+        return none;
+    std::vector<double> p_of(P, 0.0);
+    for (int q = 0; q < P; ++q)
+        for (int ch = 0; ch < 256; ++ch)
+            if ((img.B[ch][q >> 6] >> (q & 63)) & 1)
+                p_of[q] += freq[ch];
+    std::vector<char> dom(P, 0);
+    for (int q = 0; q < P; ++q)
+        dom[q] = !reachable_without(g, g.S(), g.F(), q);
+    struct cand
+    {
+        double pass;
+        int first, len;
+    };
+    std::vector<cand> cands;
+    for (int q = 0; q < P; ++q)
+    {
+        if (!dom[q])
+            continue;
+        double pass = 1.0;
+        int cur = q;
+        for (int len = 1; len <= kWindowLen; ++len)
+        {
+            pass *= p_of[cur];
+            cands.push_back({pass, q, len});
+            if (g.succ[cur].size() != 1 || g.succ[cur][0] == g.F() || g.succ[cur][0] == cur || !dom[g.succ[cur][0]])
+                break;
+            cur = g.succ[cur][0];
+        }
+    }
+    std::sort(cands.begin(), cands.end(), [](cand const & a, cand const & b) { return a.pass != b.pass ? a.pass < b.pass : a.len < b.len; });
+    // Confirm checks for a window whose first position is f (entered for the first time at text position p): a dominator
+    // d that every walk reaches only through f has its first visit after that, 1 + k bytes behind p with k in
+    // walk_range(f, d); a dominator d that every walk to f passes has its last visit before p at p - 1 - k, k in
+    // walk_range(d, f).  Both are necessary for a match — evaluated only where the window holds.
+    struct check
+    {
+        int pos, lo, hi;
+        double factor;
+    };
+    auto checks_for = [&](int first, int len) {
+        std::vector<char> in_window(P, 0);
+        int cur = first;
+        for (int i = 0; i < len; ++i)
+        {
+            in_window[cur] = 1;
+            if (i + 1 < len)
+                cur = g.succ[cur][0];
+        }
+        std::vector<check> out;
+        for (int d = 0; d < P; ++d)
+        {
+            if (!dom[d] || in_window[d] || p_of[d] > 0.6)
+                continue;
+            int lo = 0, hi = 0;
+            check c{d, 0, 0, 1.0};
+            if (!reachable_without(g, g.S(), d, first))
+            {
+                if (!walk_range(g, first, d, lo, hi) || hi >= kUnbounded)
+                    continue;
+                c.lo = 1 + lo;
+                c.hi = 1 + hi;
+            }
+            else if (!reachable_without(g, g.S(), first, d))
+            {
+                if (!walk_range(g, d, first, lo, hi) || hi >= kUnbounded)
+                    continue;
+                c.lo = -1 - hi;
+                c.hi = -1 - lo;
+            }
+            else
+                continue;
+            if (c.hi - c.lo > 23 || c.lo < -120 || c.hi > 120)
+                continue;
+            c.factor = std::min(1.0, (c.hi - c.lo + 1) * p_of[d]);
+            if (c.factor < 0.7)
+                out.push_back(c);
+        }
+        std::sort(out.begin(), out.end(), [](check const & a, check const & b) { return a.factor < b.factor; });
+        return out;
+    };
+    for (cand const & c : cands)
+    {
+        if (c.pass > kMaxWindowPass)
+            break;
+        int lo = 0, hi = 0;
+        if (!walk_range(g, g.S(), c.first, lo, hi) || hi >= kUnbounded || hi - lo > 31 || hi > 200)
+            continue;
+        class_window w;
+        w.confirmed = c.pass;
+        if (c.pass > kMaxWindowConfirmed)
+        {
+            std::vector<check> const checks = checks_for(c.first, c.len);
+            for (check const & k : checks)
+            {
+                if (w.n_confirm == kMaxConfirm || w.confirmed <= 1e-6)
+                    break;
+                confirm_check & out = w.confirm[w.n_confirm++];
+                memset(&out, 0, sizeof out);
+                out.lo = static_cast<int8_t>(k.lo);
+                out.hi = static_cast<int8_t>(k.hi);
+                for (int ch = 0; ch < 256; ++ch)
+                    if ((img.B[ch][k.pos >> 6] >> (k.pos & 63)) & 1)
+                        out.mask[ch >> 5] |= 1u << (ch & 31);
+                w.confirmed *= k.factor;
+            }
+            if (w.confirmed > kMaxWindowConfirmed)
+                continue;
+        }
+        w.ok = true;
+        w.len = c.len;
+        w.off_lo = lo;
+        w.off_hi = hi;
+        w.pass = c.pass;
+        memset(w.cls, 0, sizeof w.cls);
+        int cur = c.first;
+        for (int i = 0; i < c.len; ++i)
+        {
+            for (int ch = 0; ch < 256; ++ch)
+                if ((img.B[ch][cur >> 6] >> (cur & 63)) & 1)
+                    w.cls[i][ch >> 5] |= 1u << (ch & 31);
+            if (i + 1 < c.len)
+                cur = g.succ[cur][0];
+        }
+        return w;
+    }
+    return none;
+}
+
 struct multi_plan
 {
     multi_program prog{};           // terms / start range / confirm checks filled in, pointers not yet
@@ -1866,6 +2028,40 @@ bool plan_for_multi(filter_kind kind, filter_spec const & window, atom_spec cons
 extern "C"
 {
 
+int trx_regex_window_plan(const trx_regex_t * re, const double * byte_freq, int32_t out[5 + 10 * 6], uint32_t classes[48], double pass[2])
+{
+    if (!re || !byte_freq || !out)
+        return set_error(TRX_EINVAL, "trx_regex_window_plan: NULL argument");
+    auto img = std::make_unique<regex_dev>();
+    fill_image(*re, false, nullptr, img.get());
+    class_window const w = derive_class_window(*img, byte_freq);
+    out[0] = w.ok ? 1 : 0;
+    out[1] = w.len;
+    out[2] = w.off_lo;
+    out[3] = w.off_hi;
+    out[4] = w.ok ? w.n_confirm : 0;
+    for (int c = 0; c < out[4]; ++c)
+    {
+        out[5 + 10 * c] = w.confirm[c].lo;
+        out[6 + 10 * c] = w.confirm[c].hi;
+        for (int k = 0; k < 8; ++k)
+            out[7 + 10 * c + k] = static_cast<int32_t>(w.confirm[c].mask[k]);
+    }
+    if (classes)
+    {
+        memset(classes, 0, 48 * sizeof(uint32_t));
+        if (w.ok)
+            memcpy(classes, w.cls, sizeof w.cls);
+    }
+    if (pass)
+    {
+        pass[0] = w.pass;
+        pass[1] = w.confirmed;
+    }
+    return TRX_OK;
+}
+
+
 int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t n_patterns,
                          const uint64_t * candidate_bin_words, uint64_t cand_stride_words, trx_hit * hits,
                          uint32_t * hit_pattern, uint64_t cap, uint64_t * n_hits, uint64_t * per_pattern_hits,
@@ -1911,11 +2107,89 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
     static bool const trace = getenv("TRX_SCAN_TRACE") != nullptr;
     auto const now = [] { return std::chrono::steady_clock::now(); };
     auto const us = [](auto a, auto b) { return std::chrono::duration<double, std::micro>(b - a).count(); };
-    double us_plan = 0, us_stage = 0, us_device = 0, us_single = 0;
+    double us_plan = 0, us_stage = 0, us_device = 0, us_single = 0, us_wait = 0;
     uint32_t next = 0;
-    while (shared_pass && next < n_patterns)
+    // ---- patterns with a class window (derive_class_window) go first, 128 at a time through regex_window_multi: one pass
+    // over the tiles whose cost does not grow with the number of patterns.  TRX_MULTI_WINDOW=off: term lists for all (A/B)
+    struct staged_window
+    {
+        int len, off_lo, off_hi;
+        uint32_t cls[kWindowLen][8];
+        int n_confirm;
+        confirm_check confirm[kMaxConfirm];
+    };
+    std::vector<uint32_t> eligible;
+    std::vector<staged_window> wins;
+    std::vector<char> in_window(n_patterns, 0);
+    {
+        char const * e = getenv("TRX_MULTI_WINDOW");
+        bool const use_window = shared_pass && !(e && strcmp(e, "off") == 0);
+        auto const t_win = now();
+        for (uint32_t i = 0; use_window && i < n_patterns; ++i)
+        {
+            trx_regex_t * re = regexes[i];
+            if (re->follow_list.size() > sizeof(regex_dev::follow_list))
+                continue;
+            trx_text::cached_choice * found = nullptr;
+            for (auto & cc : t->choices)
+                if (cc.serial == re->serial && cc.reverse == 0 && cc.mode == 0 && cc.map_hash == 0)
+                    found = &cc;
+            if (!found)
+            {
+                fill_image(*re, false, nullptr, img.get());
+                trx_text::cached_choice cc{};
+                cc.serial = re->serial;
+                cc.kind = choose_filter(*img, t->byte_freq, false, cc.window, cc.atoms);
+                if (t->choices.size() >= 4096)
+                    t->choices.clear();
+                t->choices.push_back(cc);
+                found = &t->choices.back();
+            }
+            if (found->win_state < 0)
+            {
+                fill_image(*re, false, nullptr, img.get());
+                class_window const w = derive_class_window(*img, t->byte_freq);
+                found->win_state = w.ok ? 1 : 0;
+                found->win_len = w.len;
+                found->win_off_lo = w.off_lo;
+                found->win_off_hi = w.off_hi;
+                found->win_n_confirm = w.n_confirm;
+                if (w.ok)
+                {
+                    memcpy(found->win_cls, w.cls, sizeof w.cls);
+                    memcpy(found->win_confirm, w.confirm, sizeof w.confirm);
+                }
+            }
+            if (found->win_state != 1)
+                continue;
+            staged_window sw;
+            sw.len = found->win_len;
+            sw.off_lo = found->win_off_lo;
+            sw.off_hi = found->win_off_hi;
+            memcpy(sw.cls, found->win_cls, sizeof sw.cls);
+            sw.n_confirm = found->win_n_confirm;
+            memcpy(sw.confirm, found->win_confirm, sizeof sw.confirm);
+            wins.push_back(sw);
+            eligible.push_back(i);
+            in_window[i] = 1;
+        }
+        // a term-list pass for a handful of leftovers costs more than the patterns do one at a time (its fixed cost is
+        // one pass over the text with every leftover's weakest atoms): they join the single-pattern path
+        if (use_window && !eligible.empty() && n_patterns - eligible.size() <= kFewLeftovers)
+            for (uint32_t i = 0; i < n_patterns; ++i)
+                if (!in_window[i])
+                {
+                    in_window[i] = 1;
+                    single.push_back(i);
+                }
+        us_plan += us(t_win, now());
+    }
+    size_t wcur = 0;
+    while (shared_pass && (wcur < eligible.size() || next < n_patterns))
     {
         auto const t_batch = now();
+        bool const window_mode = wcur < eligible.size();
+        std::vector<uint4> wtab;
         // ---- a batch: up to kMultiPatterns patterns whose prefilter literals fit one alphabet of kMultiLetters bytes
         int letter_of[256];
         for (int & x : letter_of)
@@ -1923,8 +2197,35 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
         multi_params mp{};
         std::vector<multi_plan> plans;
         std::vector<uint32_t> ids;
-        while (next < n_patterns && ids.size() < static_cast<size_t>(kMultiPatterns))
+        if (window_mode)
         {
+            wtab.assign(static_cast<size_t>(kWindowLen) * 256, uint4{0, 0, 0, 0});
+            while (wcur < eligible.size() && ids.size() < static_cast<size_t>(kMultiPatterns))
+            {
+                staged_window const & w = wins[wcur];
+                uint32_t const k = static_cast<uint32_t>(ids.size());
+                multi_plan plan;
+                plan.prog = multi_program{};
+                plan.prog.start_lo = -w.off_hi;
+                plan.prog.start_hi = -w.off_lo;
+                plan.prog.n_confirm = w.n_confirm;
+                memcpy(plan.prog.confirm, w.confirm, sizeof w.confirm);
+                plan.usable = true;
+                for (int pos = 0; pos < kWindowLen; ++pos)
+                    for (int ch = 0; ch < 256; ++ch)
+                        if (pos >= w.len || ((w.cls[pos][ch >> 5] >> (ch & 31)) & 1))
+                            (&wtab[static_cast<size_t>(pos) * 256 + ch].x)[k >> 5] |= 1u << (k & 31);
+                plans.push_back(plan);
+                ids.push_back(eligible[wcur++]);
+            }
+        }
+        while (!window_mode && next < n_patterns && ids.size() < static_cast<size_t>(kMultiPatterns))
+        {
+            if (in_window[next])
+            {
+                ++next;
+                continue;
+            }
             trx_regex_t * re = regexes[next];
             trx_text::cached_choice const * found = nullptr;
             for (auto const & cc : t->choices)
@@ -2039,7 +2340,8 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
         size_t const off_cand = align16(off_img + nb * sizeof(regex_dev));
         size_t const off_rp = align16(off_cand + static_cast<size_t>(nb) * cand_words * 8);
         size_t const off_terms = align16(off_rp + nb * sizeof(resolve_params));
-        size_t const off_dfa = align16(off_terms + (static_cast<size_t>(nb) * kMultiMaxTermsPerPattern + 8) * 4);
+        size_t const off_dfa = align16(off_terms + std::max((static_cast<size_t>(nb) * kMultiMaxTermsPerPattern + 8) * 4,
+                                                            window_mode ? sizeof(uint4) * kWindowLen * 256 : size_t{0}));
         std::vector<dfa_table const *> dfas(nb, nullptr);
         std::vector<size_t> dfa_at(nb, 0);
         size_t stage_bytes = off_dfa;
@@ -2136,6 +2438,8 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
                 rp.dfa_first_accept = dfas[k]->first_accept;
             }
         }
+        if (window_mode) // the term region carries the class tables instead
+            memcpy(hs + off_terms, wtab.data(), wtab.size() * sizeof(uint4));
         auto const t_staged = now();
         us_stage += us(t_planned, t_staged);
         TRX_CUDA(cudaMemsetAsync(t->m_d_flags.ptr, 0, static_cast<size_t>(nb) * (rfw + cfw) * 4, st));
@@ -2154,6 +2458,28 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
         sp.tiles = static_cast<uint32_t *>(t->m_d_tiles.ptr);
         sp.n_tiles = static_cast<uint32_t>(tiles.size());
         sp.tile_counter = reinterpret_cast<unsigned int *>(d_counters + 8);
+        if (window_mode)
+        {
+            constexpr int STAGES = 2;
+            size_t const smem = ((tile_ring<STAGES, kScanThreads>::kRingBytes + 15) & ~size_t{15}) + sizeof(uint4) * kWindowLen * 256 + 1024;
+            static bool attr_set[64] = {};
+            int const dev = c->device >= 0 && c->device < 64 ? c->device : 0;
+            if (!attr_set[dev])
+            {
+                TRX_CUDA(cudaFuncSetAttribute(regex_window_multi<STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              static_cast<int>(smem)));
+                attr_set[dev] = true;
+            }
+            window_params wp{};
+            wp.programs = mp.programs;
+            wp.n_patterns = nb;
+            wp.tables = reinterpret_cast<uint4 const *>(ds + off_terms);
+            unsigned const grid = std::min<unsigned>(static_cast<unsigned>(c->sm_count), sp.n_tiles);
+            regex_window_multi<STAGES><<<grid, kScanThreads + 32, smem, st>>>(sp, wp, t->tmap);
+            ++c->launches;
+            TRX_CUDA(cudaGetLastError());
+        }
+        else
         {
             constexpr int STAGES = 2;
             size_t const smem = ((tile_ring<STAGES, kScanThreads>::kRingBytes + 15) & ~size_t{15}) +
@@ -2182,7 +2508,9 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
         t->m_h_back.pinned_host = true;
         TRX_TRY(t->m_h_back.reserve(counter_bytes));
         TRX_CUDA(cudaMemcpyAsync(t->m_h_back.ptr, d_counters, counter_bytes, cudaMemcpyDeviceToHost, st));
+        auto const t_enqueued = now();
         TRX_CUDA(cudaStreamSynchronize(st));
+        us_wait += us(t_enqueued, now());
         auto const * h_back = static_cast<uint8_t const *>(t->m_h_back.ptr);
         unsigned long long const batch_hits = *reinterpret_cast<unsigned long long const *>(h_back);
         auto const * listed = reinterpret_cast<uint32_t const *>(h_back + 16);
@@ -2230,13 +2558,14 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
     if (stats)
         stats[2] = single.size();
     {
-        std::vector<trx_hit> buf;
+        std::unique_ptr<trx_hit[]> buf; // cap entries, untouched until hits land in them (a vector would zero 16 * cap bytes)
         std::vector<std::pair<int, uint32_t>> pending; // (ticket, pattern)
         uint64_t const one_cap = cap ? cap : 1;
         auto finish = [&](std::pair<int, uint32_t> pr) -> int {
-            buf.resize(one_cap);
+            if (!buf)
+                buf.reset(new trx_hit[one_cap]);
             uint64_t n = 0;
-            int const rc = trx_regex_scan_end(t, pr.first, buf.data(), &n, nullptr);
+            int const rc = trx_regex_scan_end(t, pr.first, buf.get(), &n, nullptr);
             if (rc == TRX_ECAPACITY)
                 *n_hits = total_hits + n;
             TRX_TRY(rc);
@@ -2273,9 +2602,21 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
     }
 
     us_single = us(t_single, now());
-    if (trace)
-        fprintf(stderr, "trx_regex_scan_multi: %u patterns: plans %.0f us, staging %.0f us, shared passes (enqueue .. hits back) %.0f us, "
-                        "%zu single-path patterns %.0f us\n", n_patterns, us_plan, us_stage, us_device, single.size(), us_single);
+    auto const t_assemble = now();
+    struct trace_line
+    {
+        bool on;
+        std::function<void()> print;
+        ~trace_line()
+        {
+            if (on)
+                print();
+        }
+    } const at_return{trace, [&] {
+        fprintf(stderr, "trx_regex_scan_multi: %u patterns: plans %.0f us, staging %.0f us, shared passes (enqueue .. hits back) %.0f us "
+                        "(of it %.0f waiting for the device), %zu single-path patterns %.0f us, %zu class-window patterns, output %.0f us\n",
+                n_patterns, us_plan, us_stage, us_device, us_wait, single.size(), us_single, eligible.size(), us(t_assemble, now()));
+    }};
     // ---- print order per pattern: (pattern, bin, record, start); records are grouped by ascending bin
     *n_hits = total_hits;
     if (total_hits > cap)
