@@ -784,7 +784,7 @@ __device__ __forceinline__ void phase2_body(resolve_params const & p, regex_dev 
     unsigned const lane = threadIdx.x & 31;
     uint64_t n_listed = *p.rec_count;
     if (p.rec_cap && n_listed > p.rec_cap)
-        n_listed = p.rec_cap; // the list overflowed: the host repeats this pattern on the single-pattern path
+        n_listed = 0; // the list overflowed: the host repeats this pattern on the single-pattern path, nothing is reported here
     uint64_t const warp0 = (static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
     uint64_t const n_warps = (static_cast<uint64_t>(gridDim.x) * blockDim.x) >> 5;
     for (uint64_t i = warp0; i < n_listed; i += n_warps)
@@ -879,7 +879,7 @@ __device__ __forceinline__ void phase2_dfa_body(resolve_params const & p, uint16
     uint32_t const ncls = p.dfa_classes, accept_from = p.dfa_first_accept * ncls; // states are stored pre-multiplied
     uint64_t n_listed = *p.rec_count;
     if (p.rec_cap && n_listed > p.rec_cap)
-        n_listed = p.rec_cap;
+        n_listed = 0; // the list overflowed: the host repeats this pattern on the single-pattern path, nothing is reported here
     uint64_t const warp0 = (static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
     uint64_t const n_warps = (static_cast<uint64_t>(gridDim.x) * blockDim.x) >> 5;
     uint8_t * const win8 = reinterpret_cast<uint8_t *>(win);
@@ -1015,7 +1015,7 @@ __device__ __forceinline__ void phase2_starts_body(resolve_params const & p, uin
     uint32_t const ncls = p.dfa_classes, accept_from = p.dfa_first_accept * ncls;
     uint64_t n_listed = *p.rec_count;
     if (p.rec_cap && n_listed > p.rec_cap)
-        n_listed = p.rec_cap;
+        n_listed = 0; // the list overflowed: the host repeats this pattern on the single-pattern path, nothing is reported here
     uint64_t const warp0 = (static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
     uint64_t const n_warps = (static_cast<uint64_t>(gridDim.x) * blockDim.x) >> 5;
     for (uint64_t i = warp0; i < n_listed; i += n_warps)
@@ -1184,6 +1184,41 @@ __global__ void __launch_bounds__(256)
         uint64_t const k = keys[i];
         uint32_t const rec = static_cast<uint32_t>(k >> 32);
         out[i] = make_uint4(__ldg(rec_bin + rec), rec, static_cast<uint32_t>(k), ends[i]); // {bin, record, start, end}
+    }
+}
+
+// trx_regex_scan_multi's closing sort: (end, pattern) travel as one 64-bit value through the sort by key; the sort by
+// pattern then moves 32-bit indices only, and the formatting kernel gathers through them
+__global__ void __launch_bounds__(256)
+    multi_pack_kernel(uint32_t const * __restrict__ ends, uint32_t const * __restrict__ pats, uint64_t n, uint64_t * __restrict__ vals)
+{
+    for (uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+         i += static_cast<uint64_t>(gridDim.x) * blockDim.x)
+        vals[i] = static_cast<uint64_t>(ends[i]) | (static_cast<uint64_t>(pats[i]) << 32);
+}
+
+__global__ void __launch_bounds__(256)
+    multi_unpack_kernel(uint64_t const * __restrict__ vals, uint64_t n, uint32_t * __restrict__ pat, uint32_t * __restrict__ idx)
+{
+    for (uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+         i += static_cast<uint64_t>(gridDim.x) * blockDim.x)
+    {
+        pat[i] = static_cast<uint32_t>(vals[i] >> 32);
+        idx[i] = static_cast<uint32_t>(i);
+    }
+}
+
+__global__ void __launch_bounds__(256)
+    multi_format_kernel(uint64_t const * __restrict__ keys, uint64_t const * __restrict__ vals, uint32_t const * __restrict__ idx,
+                        uint32_t const * __restrict__ rec_bin, uint64_t n, uint4 * __restrict__ out)
+{
+    for (uint64_t i = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+         i += static_cast<uint64_t>(gridDim.x) * blockDim.x)
+    {
+        uint32_t const j = idx[i];
+        uint64_t const k = keys[j];
+        uint32_t const rec = static_cast<uint32_t>(k >> 32);
+        out[i] = make_uint4(__ldg(rec_bin + rec), rec, static_cast<uint32_t>(k), static_cast<uint32_t>(vals[j])); // {bin, record, start, end}
     }
 }
 

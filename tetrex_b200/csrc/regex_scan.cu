@@ -82,8 +82,17 @@ struct trx_text
     trx::scratch d_keys2, d_ends2, d_sort_tmp, d_hits_fmt;
     // multi-pattern scans (trx_regex_scan_multi): one staging block up (programs, automata, candidate words, phase-2
     // parameters), one block of flags / lists / counters, one hit list
-    trx::scratch m_h_stage, m_d_stage, m_d_flags, m_d_lists, m_d_counters, m_d_tiles, m_d_hit_keys, m_d_hit_ends, m_d_hit_pats,
-        m_h_back;
+    // two sets of per-pass blocks: the host stages pass n + 1 while the device works on pass n
+    struct multi_set
+    {
+        trx::scratch h_stage, d_stage, d_flags, d_lists, d_counters, h_back;
+        cudaEvent_t done{nullptr};
+        bool in_flight{false};
+        std::vector<uint32_t> ids; // the patterns of the pass in flight
+    };
+    multi_set m_sets[2];
+    // the hits of a whole call stay on the device (one list for all patterns, one counter) until they are sorted there
+    trx::scratch m_d_hit_keys, m_d_hit_ends, m_d_hit_pats, m_d_total, m_h_total, m_d_sort;
     bool multi_attr_set{false};
 };
 
@@ -254,9 +263,16 @@ void trx_text_destroy(trx_text_t * t)
         for (trx::scratch * s : {&sl.d_stage, &sl.h_stage, &sl.h_small, &sl.d_keys, &sl.d_ends, &sl.d_tiles, &sl.d_start_bits})
             s->release();
     }
-    for (trx::scratch * s : {&t->d_keys2, &t->d_ends2, &t->d_sort_tmp, &t->d_hits_fmt, &t->m_h_stage, &t->m_d_stage, &t->m_d_flags, &t->m_d_lists,
-                             &t->m_d_counters, &t->m_d_tiles, &t->m_d_hit_keys, &t->m_d_hit_ends, &t->m_d_hit_pats, &t->m_h_back})
+    for (trx::scratch * s : {&t->d_keys2, &t->d_ends2, &t->d_sort_tmp, &t->d_hits_fmt, &t->m_d_hit_keys, &t->m_d_hit_ends, &t->m_d_hit_pats, &t->m_d_total,
+                             &t->m_h_total, &t->m_d_sort})
         s->release();
+    for (trx_text::multi_set & ms : t->m_sets)
+    {
+        if (ms.done)
+            cudaEventDestroy(ms.done);
+        for (trx::scratch * s : {&ms.h_stage, &ms.d_stage, &ms.d_flags, &ms.d_lists, &ms.d_counters, &ms.h_back})
+            s->release();
+    }
     delete t;
 }
 
@@ -1290,8 +1306,19 @@ size_t align16(size_t x)
 extern "C"
 {
 
-int trx_regex_scan_begin(trx_text_t * t, trx_regex_t * re, const uint64_t * candidate_bin_words, int reverse_strand,
-                         const uint8_t * map256, uint64_t cap, int * ticket)
+// trx_regex_scan_multi's pattern-at-a-time scans report into the call's shared hit list instead of the slot's own
+struct hit_sink
+{
+    unsigned long long * count;
+    uint64_t * keys;
+    uint32_t * ends;
+    uint32_t * pats;
+    uint32_t pattern_id;
+    uint64_t cap;
+};
+
+static int scan_begin_impl(trx_text_t * t, trx_regex_t * re, const uint64_t * candidate_bin_words, int reverse_strand,
+                           const uint8_t * map256, uint64_t cap, int * ticket, hit_sink const * sink)
 {
     if (!t || !re || !candidate_bin_words || !ticket)
         return set_error(TRX_EINVAL, "trx_regex_scan_begin: NULL argument");
@@ -1537,6 +1564,15 @@ int trx_regex_scan_begin(trx_text_t * t, trx_regex_t * re, const uint64_t * cand
     rp.small_keys = reinterpret_cast<uint64_t *>(sl.d_counters + 16);
     rp.small_ends = reinterpret_cast<uint32_t *>(sl.d_counters + 16 + kSmallHits * 8);
     rp.cap = cap;
+    if (sink)
+    {
+        rp.hit_count = sink->count;
+        rp.hit_keys = sink->keys;
+        rp.hit_ends = sink->ends;
+        rp.hit_pats = sink->pats;
+        rp.pattern_id = sink->pattern_id;
+        rp.cap = sink->cap;
+    }
     if (tiles.empty())
         ;
     else if (dfa)
@@ -1571,6 +1607,12 @@ int trx_regex_scan_begin(trx_text_t * t, trx_regex_t * re, const uint64_t * cand
                 us(t_begin, t_plan), us(t_plan, t_image), us(t_image, t_choice), us(t_choice, now()), tiles.size(), slot_index);
     }
     return TRX_OK;
+}
+
+int trx_regex_scan_begin(trx_text_t * t, trx_regex_t * re, const uint64_t * candidate_bin_words, int reverse_strand,
+                         const uint8_t * map256, uint64_t cap, int * ticket)
+{
+    return scan_begin_impl(t, re, candidate_bin_words, reverse_strand, map256, cap, ticket, nullptr);
 }
 
 int trx_regex_scan_end(trx_text_t * t, int ticket, trx_hit * hits, uint64_t * n_hits, uint64_t * stats)
@@ -2088,16 +2130,44 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
     cudaStream_t const st = c->stream;
     auto cand_of = [&](uint32_t i) { return candidate_bin_words + static_cast<uint64_t>(i) * cand_stride_words; };
 
-    struct tagged_hit
-    {
-        uint32_t pat, rec, start, end;
-    };
-    // hits per pattern: the shared passes deliver them in arbitrary order (sorted per pattern at the end, they are few),
-    // the single-pattern path in print order already (its lists can be hundreds of thousands long)
-    std::vector<std::vector<tagged_hit>> per(n_patterns);
-    std::vector<char> needs_sort(n_patterns, 0);
-    uint64_t total_hits = 0;
+    // Hits of all patterns land in ONE device list (key = record << 32 | start, end, pattern) behind one counter, whichever
+    // path found them; nothing comes back before the list is sorted into print order on the device at the end.  The shared
+    // passes are enqueued back to back (two sets of staging blocks); the host only looks at a pass's record-list counters
+    // when it needs the set again.
     std::vector<uint32_t> single; // patterns for the pattern-at-a-time path
+    uint64_t const dev_cap = cap ? cap : 1;
+    TRX_TRY(t->m_d_hit_keys.reserve(dev_cap * 8));
+    TRX_TRY(t->m_d_hit_ends.reserve(dev_cap * 4));
+    TRX_TRY(t->m_d_hit_pats.reserve(dev_cap * 4));
+    TRX_TRY(t->m_d_total.reserve(16));
+    t->m_h_total.pinned_host = true;
+    TRX_TRY(t->m_h_total.reserve(16));
+    TRX_CUDA(cudaMemsetAsync(t->m_d_total.ptr, 0, 16, st));
+    for (trx_text::multi_set & ms : t->m_sets)
+    {
+        if (!ms.done)
+            TRX_CUDA(cudaEventCreateWithFlags(&ms.done, cudaEventDisableTiming));
+        if (ms.in_flight) // a call that ended in an error may have left a pass behind
+            cudaEventSynchronize(ms.done);
+        ms.in_flight = false;
+    }
+    // a pass is over: patterns whose record list overflowed (they reported nothing) go to the pattern-at-a-time path
+    auto retire = [&](trx_text::multi_set & ms) -> int {
+        if (!ms.in_flight)
+            return TRX_OK;
+        ms.in_flight = false;
+        TRX_CUDA(cudaEventSynchronize(ms.done));
+        auto const * listed = reinterpret_cast<uint32_t const *>(static_cast<uint8_t const *>(ms.h_back.ptr) + 16);
+        for (size_t k = 0; k < ms.ids.size(); ++k)
+            if (listed[k] > kMultiListCap)
+            {
+                single.push_back(ms.ids[k]);
+                if (stats)
+                    --stats[1];
+            }
+        return TRX_OK;
+    };
+    uint32_t n_passes = 0;
 
     // ---- every pattern's phase-1 plan (cached per text like the single-pattern path does)
     char const * filt = getenv("TRX_REGEX_FILTER");
@@ -2340,11 +2410,18 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
         size_t const off_cand = align16(off_img + nb * sizeof(regex_dev));
         size_t const off_rp = align16(off_cand + static_cast<size_t>(nb) * cand_words * 8);
         size_t const off_terms = align16(off_rp + nb * sizeof(resolve_params));
+        trx_text::multi_set & ms = t->m_sets[n_passes++ & 1];
+        {
+            auto const t_retire = now();
+            TRX_TRY(retire(ms));
+            us_wait += us(t_retire, now());
+        }
         size_t const off_dfa = align16(off_terms + std::max((static_cast<size_t>(nb) * kMultiMaxTermsPerPattern + 8) * 4,
                                                             window_mode ? sizeof(uint4) * kWindowLen * 256 : size_t{0}));
         std::vector<dfa_table const *> dfas(nb, nullptr);
         std::vector<size_t> dfa_at(nb, 0);
-        size_t stage_bytes = off_dfa;
+        size_t const off_tiles = off_dfa;
+        size_t stage_bytes = align16(off_tiles + tiles.size() * 4);
         for (uint32_t k = 0; k < nb; ++k)
         {
             trx_regex & rx = *regexes[ids[k]];
@@ -2361,21 +2438,19 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
             }
         }
         uint64_t const cfw = t->n_chunk_flag_words;
-        t->m_h_stage.pinned_host = true;
-        TRX_TRY(t->m_h_stage.reserve(stage_bytes));
-        TRX_TRY(t->m_d_stage.reserve(stage_bytes));
-        TRX_TRY(t->m_d_flags.reserve(static_cast<size_t>(nb) * (rfw + cfw) * 4));
-        TRX_TRY(t->m_d_lists.reserve(static_cast<size_t>(nb) * kMultiListCap * 4));
-        size_t const counter_bytes = 16 + static_cast<size_t>(nb) * 4; // hit count (u64), tile counter (u32), pad, listed records per pattern
-        TRX_TRY(t->m_d_counters.reserve(counter_bytes));
-        TRX_TRY(t->m_d_tiles.reserve(tiles.size() * 4));
-        uint64_t const dev_cap = cap ? cap : 1;
-        TRX_TRY(t->m_d_hit_keys.reserve(dev_cap * 8));
-        TRX_TRY(t->m_d_hit_ends.reserve(dev_cap * 4));
-        TRX_TRY(t->m_d_hit_pats.reserve(dev_cap * 4));
-        auto * hs = static_cast<uint8_t *>(t->m_h_stage.ptr);
-        auto * ds = static_cast<uint8_t *>(t->m_d_stage.ptr);
-        auto * d_counters = static_cast<uint8_t *>(t->m_d_counters.ptr);
+        ms.h_stage.pinned_host = true;
+        TRX_TRY(ms.h_stage.reserve(stage_bytes));
+        TRX_TRY(ms.d_stage.reserve(stage_bytes));
+        TRX_TRY(ms.d_flags.reserve(static_cast<size_t>(nb) * (rfw + cfw) * 4));
+        TRX_TRY(ms.d_lists.reserve(static_cast<size_t>(nb) * kMultiListCap * 4));
+        size_t const counter_bytes = 16 + static_cast<size_t>(nb) * 4; // unused (u64), tile counter (u32), pad, listed records per pattern
+        TRX_TRY(ms.d_counters.reserve(counter_bytes));
+        ms.h_back.pinned_host = true;
+        TRX_TRY(ms.h_back.reserve(counter_bytes));
+        auto * hs = static_cast<uint8_t *>(ms.h_stage.ptr);
+        auto * ds = static_cast<uint8_t *>(ms.d_stage.ptr);
+        auto * d_counters = static_cast<uint8_t *>(ms.d_counters.ptr);
+        memcpy(hs + off_tiles, tiles.data(), tiles.size() * 4);
         auto * h_prog = reinterpret_cast<multi_program *>(hs + off_prog);
         auto * h_rp = reinterpret_cast<resolve_params *>(hs + off_rp);
         for (uint32_t k = 0; k < nb; ++k)
@@ -2385,8 +2460,8 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
             multi_program & P = h_prog[k];
             P = plans[k].prog;
             P.cand_words = reinterpret_cast<uint64_t const *>(ds + off_cand) + static_cast<size_t>(k) * cand_words;
-            P.rec_flags = static_cast<uint32_t *>(t->m_d_flags.ptr) + static_cast<size_t>(k) * rfw;
-            P.chunk_flags = static_cast<uint32_t *>(t->m_d_flags.ptr) + static_cast<size_t>(nb) * rfw + static_cast<size_t>(k) * cfw;
+            P.rec_flags = static_cast<uint32_t *>(ms.d_flags.ptr) + static_cast<size_t>(k) * rfw;
+            P.chunk_flags = static_cast<uint32_t *>(ms.d_flags.ptr) + static_cast<size_t>(nb) * rfw + static_cast<size_t>(k) * cfw;
             {
                 // a range = one term per offset (ORed like the atom's other terms); the list is padded in front to whole
                 // rounds of four with copies of its first term, and every round's first word says how many rounds follow
@@ -2408,7 +2483,7 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
                     out[mp.n_terms_total++] = multi_pack_term(fl[i].letter, fl[i].d, rounds - 1 - static_cast<uint32_t>(i / 4),
                                                               fl[i].end_atom, fl[i].end_pattern);
             }
-            P.rec_list = static_cast<uint32_t *>(t->m_d_lists.ptr) + static_cast<size_t>(k) * kMultiListCap;
+            P.rec_list = static_cast<uint32_t *>(ms.d_lists.ptr) + static_cast<size_t>(k) * kMultiListCap;
             P.rec_count = reinterpret_cast<unsigned int *>(d_counters + 16) + k;
             resolve_params & rp = h_rp[k];
             rp = resolve_params{};
@@ -2418,11 +2493,11 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
             rp.rec_count = P.rec_count;
             rp.chunk_flags = P.chunk_flags;
             rp.re = reinterpret_cast<regex_dev const *>(ds + off_img) + k;
-            rp.hit_count = reinterpret_cast<unsigned long long *>(d_counters);
+            rp.hit_count = static_cast<unsigned long long *>(t->m_d_total.ptr);
             rp.hit_keys = static_cast<uint64_t *>(t->m_d_hit_keys.ptr);
             rp.hit_ends = static_cast<uint32_t *>(t->m_d_hit_ends.ptr);
             rp.hit_pats = static_cast<uint32_t *>(t->m_d_hit_pats.ptr);
-            rp.pattern_id = k;
+            rp.pattern_id = ids[k];
             rp.rec_cap = kMultiListCap;
             rp.cap = cap;
             rp.anchor_begin = regexes[ids[k]]->anchor_begin;
@@ -2442,10 +2517,9 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
             memcpy(hs + off_terms, wtab.data(), wtab.size() * sizeof(uint4));
         auto const t_staged = now();
         us_stage += us(t_planned, t_staged);
-        TRX_CUDA(cudaMemsetAsync(t->m_d_flags.ptr, 0, static_cast<size_t>(nb) * (rfw + cfw) * 4, st));
+        TRX_CUDA(cudaMemsetAsync(ms.d_flags.ptr, 0, static_cast<size_t>(nb) * (rfw + cfw) * 4, st));
         TRX_CUDA(cudaMemsetAsync(d_counters, 0, counter_bytes, st));
         TRX_CUDA(cudaMemcpyAsync(ds, hs, stage_bytes, cudaMemcpyHostToDevice, st));
-        TRX_CUDA(cudaMemcpyAsync(t->m_d_tiles.ptr, tiles.data(), tiles.size() * 4, cudaMemcpyHostToDevice, st));
         mp.programs = reinterpret_cast<multi_program const *>(ds + off_prog);
         mp.terms = reinterpret_cast<uint32_t const *>(ds + off_terms);
         scan_params sp{};
@@ -2455,7 +2529,7 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
         sp.rec_offsets = t->d_rec_offsets;
         sp.rec_bin = t->d_rec_bin;
         sp.n_records = t->n_records;
-        sp.tiles = static_cast<uint32_t *>(t->m_d_tiles.ptr);
+        sp.tiles = reinterpret_cast<uint32_t *>(ds + off_tiles);
         sp.n_tiles = static_cast<uint32_t>(tiles.size());
         sp.tile_counter = reinterpret_cast<unsigned int *>(d_counters + 8);
         if (window_mode)
@@ -2504,49 +2578,18 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
         ++c->launches;
         TRX_CUDA(cudaGetLastError());
 
-        // ---- read back: counters first (how many hits, which lists overflowed), then the hit triples
-        t->m_h_back.pinned_host = true;
-        TRX_TRY(t->m_h_back.reserve(counter_bytes));
-        TRX_CUDA(cudaMemcpyAsync(t->m_h_back.ptr, d_counters, counter_bytes, cudaMemcpyDeviceToHost, st));
-        auto const t_enqueued = now();
-        TRX_CUDA(cudaStreamSynchronize(st));
-        us_wait += us(t_enqueued, now());
-        auto const * h_back = static_cast<uint8_t const *>(t->m_h_back.ptr);
-        unsigned long long const batch_hits = *reinterpret_cast<unsigned long long const *>(h_back);
-        auto const * listed = reinterpret_cast<uint32_t const *>(h_back + 16);
-        if (batch_hits > cap)
-        {
-            *n_hits = total_hits + batch_hits;
-            return set_error(TRX_ECAPACITY, "trx_regex_scan_multi: at least %llu hits, room for %llu",
-                             (unsigned long long)(total_hits + batch_hits), (unsigned long long)cap);
-        }
-        std::vector<char> overflowed(nb, 0);
-        for (uint32_t k = 0; k < nb; ++k)
-            if (listed[k] > kMultiListCap)
-            {
-                overflowed[k] = 1; // more candidate records than the shared pass lists: the single-pattern path takes it
-                single.push_back(ids[k]);
-                if (stats)
-                    --stats[1];
-            }
-        if (batch_hits)
-        {
-            std::vector<uint64_t> keys(batch_hits);
-            std::vector<uint32_t> ends(batch_hits), pats(batch_hits);
-            TRX_CUDA(cudaMemcpyAsync(keys.data(), t->m_d_hit_keys.ptr, batch_hits * 8, cudaMemcpyDeviceToHost, st));
-            TRX_CUDA(cudaMemcpyAsync(ends.data(), t->m_d_hit_ends.ptr, batch_hits * 4, cudaMemcpyDeviceToHost, st));
-            TRX_CUDA(cudaMemcpyAsync(pats.data(), t->m_d_hit_pats.ptr, batch_hits * 4, cudaMemcpyDeviceToHost, st));
-            TRX_CUDA(cudaStreamSynchronize(st));
-            for (uint64_t i = 0; i < batch_hits; ++i)
-                if (!overflowed[pats[i]])
-                {
-                    uint32_t const id = ids[pats[i]];
-                    per[id].push_back(tagged_hit{id, static_cast<uint32_t>(keys[i] >> 32), static_cast<uint32_t>(keys[i]), ends[i]});
-                    needs_sort[id] = 1;
-                    ++total_hits;
-                }
-        }
+        // ---- the pass's record-list counters follow it to the host; nobody waits for them here
+        TRX_CUDA(cudaMemcpyAsync(ms.h_back.ptr, d_counters, counter_bytes, cudaMemcpyDeviceToHost, st));
+        TRX_CUDA(cudaEventRecord(ms.done, st));
+        ms.ids = ids;
+        ms.in_flight = true;
         us_device += us(t_staged, now());
+    }
+    {
+        auto const t_retire = now();
+        for (trx_text::multi_set & ms : t->m_sets)
+            TRX_TRY(retire(ms));
+        us_wait += us(t_retire, now());
     }
     auto const t_single = now();
     if (!shared_pass)
@@ -2558,22 +2601,14 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
     if (stats)
         stats[2] = single.size();
     {
-        std::unique_ptr<trx_hit[]> buf; // cap entries, untouched until hits land in them (a vector would zero 16 * cap bytes)
-        std::vector<std::pair<int, uint32_t>> pending; // (ticket, pattern)
-        uint64_t const one_cap = cap ? cap : 1;
-        auto finish = [&](std::pair<int, uint32_t> pr) -> int {
-            if (!buf)
-                buf.reset(new trx_hit[one_cap]);
+        // these scans run on the scan slots' streams: the counter was cleared on the context's stream, which every retired
+        // pass has synchronised with — except when there was no pass at all
+        if (n_passes == 0)
+            TRX_CUDA(cudaStreamSynchronize(st));
+        std::vector<int> pending; // tickets
+        auto finish = [&](int ticket) -> int {
             uint64_t n = 0;
-            int const rc = trx_regex_scan_end(t, pr.first, buf.get(), &n, nullptr);
-            if (rc == TRX_ECAPACITY)
-                *n_hits = total_hits + n;
-            TRX_TRY(rc);
-            per[pr.second].reserve(n);
-            for (uint64_t i = 0; i < n; ++i)
-                per[pr.second].push_back(tagged_hit{pr.second, buf[i].record, buf[i].start, buf[i].end});
-            total_hits += n;
-            return TRX_OK;
+            return trx_regex_scan_end(t, ticket, nullptr, &n, nullptr); // waits for the scan; its hits are in the shared list
         };
         int rc = TRX_OK;
         for (uint32_t i : single)
@@ -2585,18 +2620,20 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
                 if (rc != TRX_OK)
                     break;
             }
+            hit_sink sink{static_cast<unsigned long long *>(t->m_d_total.ptr), static_cast<uint64_t *>(t->m_d_hit_keys.ptr),
+                          static_cast<uint32_t *>(t->m_d_hit_ends.ptr), static_cast<uint32_t *>(t->m_d_hit_pats.ptr), i, cap};
             int ticket = -1;
-            rc = trx_regex_scan_begin(t, regexes[i], cand_of(i), 0, nullptr, one_cap, &ticket);
+            rc = scan_begin_impl(t, regexes[i], cand_of(i), 0, nullptr, 0, &ticket, &sink);
             if (rc != TRX_OK)
                 break;
-            pending.push_back({ticket, i});
+            pending.push_back(ticket);
         }
-        for (auto const & pr : pending)
+        for (int ticket : pending)
         {
             if (rc == TRX_OK)
-                rc = finish(pr);
+                rc = finish(ticket);
             else
-                trx_regex_scan_end(t, pr.first, nullptr, nullptr, nullptr); // abandon
+                trx_regex_scan_end(t, ticket, nullptr, nullptr, nullptr); // abandon
         }
         TRX_TRY(rc);
     }
@@ -2617,27 +2654,66 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
                         "(of it %.0f waiting for the device), %zu single-path patterns %.0f us, %zu class-window patterns, output %.0f us\n",
                 n_patterns, us_plan, us_stage, us_device, us_wait, single.size(), us_single, eligible.size(), us(t_assemble, now()));
     }};
-    // ---- print order per pattern: (pattern, bin, record, start); records are grouped by ascending bin
-    *n_hits = total_hits;
-    if (total_hits > cap)
-        return set_error(TRX_ECAPACITY, "trx_regex_scan_multi: %llu hits, room for %llu", (unsigned long long)total_hits,
-                         (unsigned long long)cap);
-    uint64_t o = 0;
-    for (uint32_t i = 0; i < n_patterns; ++i)
+    // ---- print order: (pattern, bin, record, start); records are grouped by ascending bin, so (pattern, record, start).
+    // Two stable radix sorts on the device — by key, then by pattern — one kernel that writes trx_hit records, and the
+    // caller's arrays are filled by two copies.
+    auto * h_total = static_cast<unsigned long long *>(t->m_h_total.ptr);
+    TRX_CUDA(cudaMemcpyAsync(h_total, t->m_d_total.ptr, 8, cudaMemcpyDeviceToHost, st));
+    TRX_CUDA(cudaStreamSynchronize(st));
+    uint64_t const n = *h_total;
+    *n_hits = n;
+    if (n > cap)
+        return set_error(TRX_ECAPACITY, "trx_regex_scan_multi: %llu hits, room for %llu", (unsigned long long)n, (unsigned long long)cap);
+    if (n == 0)
+        return TRX_OK;
     {
-        std::vector<tagged_hit> & v = per[i];
-        if (needs_sort[i])
-            std::sort(v.begin(), v.end(), [](tagged_hit const & a, tagged_hit const & b) {
-                return a.rec != b.rec ? a.rec < b.rec : a.start < b.start;
-            });
-        for (tagged_hit const & h : v)
-        {
-            hits[o] = trx_hit{t->h_rec_bin[h.rec], h.rec, h.start, h.end};
-            hit_pattern[o++] = i;
-        }
-        if (per_pattern_hits)
-            per_pattern_hits[i] = v.size();
+        int pat_bits = 1;
+        while ((1ull << pat_bits) < n_patterns)
+            ++pat_bits;
+        int rec_bits = 1;
+        while ((1ull << rec_bits) < t->n_records)
+            ++rec_bits;
+        size_t tmp_a = 0, tmp_b = 0;
+        TRX_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_a, static_cast<uint64_t *>(nullptr), static_cast<uint64_t *>(nullptr),
+                                                 static_cast<uint64_t *>(nullptr), static_cast<uint64_t *>(nullptr), static_cast<int>(n),
+                                                 0, 32 + rec_bits, st));
+        TRX_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_b, static_cast<uint32_t *>(nullptr), static_cast<uint32_t *>(nullptr),
+                                                 static_cast<uint32_t *>(nullptr), static_cast<uint32_t *>(nullptr), static_cast<int>(n),
+                                                 0, pat_bits, st));
+        size_t const tmp_bytes = align16(std::max(tmp_a, tmp_b));
+        // [keys2 8n | vals 8n | vals2 8n | pat 4n | pat2 4n | idx 4n | idx2 4n | hits 16n | temp]
+        size_t const n16 = align16(n * 4) / 4; // 16-byte aligned pieces
+        TRX_TRY(t->m_d_sort.reserve(n16 * 56 + tmp_bytes));
+        auto * base = static_cast<uint8_t *>(t->m_d_sort.ptr);
+        auto * keys2 = reinterpret_cast<uint64_t *>(base);
+        auto * vals = reinterpret_cast<uint64_t *>(base + n16 * 8);
+        auto * vals2 = reinterpret_cast<uint64_t *>(base + n16 * 16);
+        auto * pat = reinterpret_cast<uint32_t *>(base + n16 * 24);
+        auto * pat2 = reinterpret_cast<uint32_t *>(base + n16 * 28);
+        auto * idx = reinterpret_cast<uint32_t *>(base + n16 * 32);
+        auto * idx2 = reinterpret_cast<uint32_t *>(base + n16 * 36);
+        auto * fmt = reinterpret_cast<uint4 *>(base + n16 * 40);
+        void * tmp = base + n16 * 56;
+        unsigned const grid = grid_for(n, 256, c->sm_count, 8);
+        multi_pack_kernel<<<grid, 256, 0, st>>>(static_cast<uint32_t const *>(t->m_d_hit_ends.ptr),
+                                                static_cast<uint32_t const *>(t->m_d_hit_pats.ptr), n, vals);
+        size_t tb = tmp_bytes;
+        TRX_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tb, static_cast<uint64_t const *>(t->m_d_hit_keys.ptr), keys2,
+                                                 static_cast<uint64_t const *>(vals), vals2, static_cast<int>(n), 0, 32 + rec_bits, st));
+        multi_unpack_kernel<<<grid, 256, 0, st>>>(vals2, n, pat, idx);
+        tb = tmp_bytes;
+        TRX_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tb, static_cast<uint32_t const *>(pat), pat2, static_cast<uint32_t const *>(idx), idx2,
+                                                 static_cast<int>(n), 0, pat_bits, st));
+        multi_format_kernel<<<grid, 256, 0, st>>>(keys2, vals2, idx2, t->d_rec_bin, n, fmt);
+        c->launches += 3 + 6; // three kernels of ours + cub's histogram / onesweep passes
+        TRX_CUDA(cudaGetLastError());
+        TRX_CUDA(cudaMemcpyAsync(hits, fmt, n * sizeof(trx_hit), cudaMemcpyDeviceToHost, st));
+        TRX_CUDA(cudaMemcpyAsync(hit_pattern, pat2, n * 4, cudaMemcpyDeviceToHost, st));
+        TRX_CUDA(cudaStreamSynchronize(st));
     }
+    if (per_pattern_hits)
+        for (uint64_t i = 0; i < n; ++i)
+            ++per_pattern_hits[hit_pattern[i]];
     return TRX_OK;
 }
 
