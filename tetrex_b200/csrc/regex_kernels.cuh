@@ -1792,16 +1792,16 @@ __device__ __noinline__ void multi_survivors(scan_params const & p, multi_progra
 // Class-window first stage for batches of patterns: BIT-PARALLEL OVER THE PATTERNS.  Every pattern of the batch brings a
 // run of up to kWindowLen consecutive necessary positions with their byte classes (class_window, derived on the host);
 // tables[k][byte] is the 128-bit set of patterns whose k-th window position accepts the byte (patterns with a shorter
-// window accept everything there).  The patterns whose window can begin at text position j are then
+// window accept everything there), kept as four 32-bit rows.  The patterns whose window can begin at text position j are
 //      tables[0][t[j]] & tables[1][t[j+1]] & ... & tables[5][t[j+5]]
-// — six 16-byte shared-memory loads and twenty ANDs per position for up to 128 patterns, against one term list per pattern
+// — twenty-four conflict-free shared-memory loads and twenty ANDs per position for up to 128 patterns, against one term list per pattern
 // in regex_filter_multi (1.5 thread-instructions per residue and pattern).  Survivors (about one in 10^6 per pattern) flag
 // the chunks the match may start in and list the record, like regex_filter_multi's do.
 struct window_params
 {
     multi_program const * programs; // start_lo / start_hi and the confirm checks relative to the window's first byte
     uint32_t n_patterns;
-    uint4 const * tables;           // [kWindowLen][256]
+    uint32_t const * tables;        // [kWindowLen][4][256]: window position, group of 32 patterns, byte
 };
 
 __device__ __noinline__ void window_survivors(scan_params const & p, window_params const & wp, uint64_t position, uint4 cand)
@@ -1867,8 +1867,11 @@ __global__ void __launch_bounds__(kScanThreads + 32)
     using ring_t = tile_ring<STAGES, kScanThreads>;
     ring_t ring;
     ring.init(smem_raw);
-    uint4 * const tables = reinterpret_cast<uint4 *>(smem_raw + ((ring_t::kRingBytes + 15) & ~15));
-    for (uint32_t i = threadIdx.x; i < kWindowLen * 256; i += blockDim.x)
+    // 32-bit rows: the 20-odd letters of a sequence alphabet are consecutive byte values, so the rows a warp asks for lie
+    // in different banks (or are the same row: a broadcast).  With 16-byte rows more than half of the shared-memory
+    // wavefronts were bank conflicts (ncu: 172 M of 329 M).
+    uint32_t * const tables = reinterpret_cast<uint32_t *>(smem_raw + ((ring_t::kRingBytes + 15) & ~15));
+    for (uint32_t i = threadIdx.x; i < kWindowLen * 4 * 256; i += blockDim.x)
         tables[i] = wp.tables[i];
     __syncthreads();
     if (ring.is_producer())
@@ -1915,15 +1918,16 @@ __global__ void __launch_bounds__(kScanThreads + 32)
 #pragma unroll
                 for (int j = 0; j < 4; ++j)
                 {
-                    uint4 m = tables[by[j]];
+                    uint32_t const * row = tables + by[j];
+                    uint4 m = make_uint4(row[0], row[256], row[512], row[768]);
 #pragma unroll
                     for (int k = 1; k < kWindowLen; ++k)
                     {
-                        uint4 const t = tables[k * 256 + by[j + k]];
-                        m.x &= t.x;
-                        m.y &= t.y;
-                        m.z &= t.z;
-                        m.w &= t.w;
+                        row = tables + k * 1024 + by[j + k];
+                        m.x &= row[0];
+                        m.y &= row[256];
+                        m.z &= row[512];
+                        m.w &= row[768];
                     }
                     if (m.x | m.y | m.z | m.w)
                         window_survivors(p, wp, g_lo + 4 * q + j, m);

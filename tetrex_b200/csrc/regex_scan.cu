@@ -2259,7 +2259,7 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
     {
         auto const t_batch = now();
         bool const window_mode = wcur < eligible.size();
-        std::vector<uint4> wtab;
+        std::vector<uint32_t> wtab; // [kWindowLen][4][256]
         // ---- a batch: up to kMultiPatterns patterns whose prefilter literals fit one alphabet of kMultiLetters bytes
         int letter_of[256];
         for (int & x : letter_of)
@@ -2269,7 +2269,7 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
         std::vector<uint32_t> ids;
         if (window_mode)
         {
-            wtab.assign(static_cast<size_t>(kWindowLen) * 256, uint4{0, 0, 0, 0});
+            wtab.assign(static_cast<size_t>(kWindowLen) * 4 * 256, 0u);
             while (wcur < eligible.size() && ids.size() < static_cast<size_t>(kMultiPatterns))
             {
                 staged_window const & w = wins[wcur];
@@ -2284,7 +2284,7 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
                 for (int pos = 0; pos < kWindowLen; ++pos)
                     for (int ch = 0; ch < 256; ++ch)
                         if (pos >= w.len || ((w.cls[pos][ch >> 5] >> (ch & 31)) & 1))
-                            (&wtab[static_cast<size_t>(pos) * 256 + ch].x)[k >> 5] |= 1u << (k & 31);
+                            wtab[(static_cast<size_t>(pos) * 4 + (k >> 5)) * 256 + ch] |= 1u << (k & 31);
                 plans.push_back(plan);
                 ids.push_back(eligible[wcur++]);
             }
@@ -2514,7 +2514,7 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
             }
         }
         if (window_mode) // the term region carries the class tables instead
-            memcpy(hs + off_terms, wtab.data(), wtab.size() * sizeof(uint4));
+            memcpy(hs + off_terms, wtab.data(), wtab.size() * sizeof(uint32_t));
         auto const t_staged = now();
         us_stage += us(t_planned, t_staged);
         TRX_CUDA(cudaMemsetAsync(ms.d_flags.ptr, 0, static_cast<size_t>(nb) * (rfw + cfw) * 4, st));
@@ -2547,8 +2547,8 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
             window_params wp{};
             wp.programs = mp.programs;
             wp.n_patterns = nb;
-            wp.tables = reinterpret_cast<uint4 const *>(ds + off_terms);
-            unsigned const grid = std::min<unsigned>(static_cast<unsigned>(c->sm_count), sp.n_tiles);
+            wp.tables = reinterpret_cast<uint32_t const *>(ds + off_terms);
+            unsigned const grid = std::min<unsigned>(2u * static_cast<unsigned>(c->sm_count), sp.n_tiles); // two CTAs fit an SM
             regex_window_multi<STAGES><<<grid, kScanThreads + 32, smem, st>>>(sp, wp, t->tmap);
             ++c->launches;
             TRX_CUDA(cudaGetLastError());
@@ -2574,7 +2574,9 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
         for (uint32_t k = 0; k < nb; ++k)
             if (dfas[k])
                 dyn_smem = std::max(dyn_smem, dfa_smem_bytes(dfas[k]->n_states, dfas[k]->n_classes));
-        regex_scan_phase2_multi<2, 1><<<dim3(32, nb), 128, dyn_smem, st>>>(reinterpret_cast<resolve_params const *>(ds + off_rp));
+        // CTAs beyond a pattern's record list leave at once: the grid is sized for the longest lists (tens of thousands of
+        // records), which otherwise sit on 128 warps long after the other patterns are done
+        regex_scan_phase2_multi<2, 1><<<dim3(window_mode ? 128 : 32, nb), 128, dyn_smem, st>>>(reinterpret_cast<resolve_params const *>(ds + off_rp));
         ++c->launches;
         TRX_CUDA(cudaGetLastError());
 
