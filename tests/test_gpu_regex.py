@@ -471,3 +471,48 @@ def test_multi_pattern_scan_dna_and_edge_shapes(ctx):
     for rx in regexes:
         rx.close()
     txt.close()
+
+
+def test_multi_pattern_scan_overflowing_record_lists_and_result_views(ctx, monkeypatch):
+    """A pattern whose class window survives in more records than a shared pass lists (32 768) reports nothing there and is
+    scanned again on the single-pattern path inside the same call, its hits landing in the same device list as everybody
+    else's; the list comes back sorted by (pattern, record, start).  40 000 short records, three patterns that occur in
+    almost all of them, three that occur in a few, one that never occurs; with and without the class-window stage; and the
+    arrays a call returns stay valid while the next call runs."""
+    rng = random.Random(5)
+    alpha = b"ACDEFGHIKLMNPQRSTVWY"
+    seqs, rec_bin = [], []
+    for r in range(40000):
+        s = bytearray(rng.choice(alpha) for _ in range(rng.choice([24, 31, 40])))
+        if r % 50:
+            s[3:9] = b"WCWHWM"
+        if r % 1000 == 7:
+            s[12:18] = b"HHPGYK"
+        if r % 3 == 0:
+            s[18:23] = b"MMQWC"
+        seqs.append(bytes(s))
+        rec_bin.append(r // 400)
+    txt = build_text(ctx, seqs, rec_bin, 100)
+    pats = ["WCWHW", "HHPGYK", "CWHWM", "MMQWC", "HHP[GA]Y", "W.WHW", "YYYYWWWW", "[HK]HPGY"]
+    regexes = [t.Regex(p, True) for p in pats]
+    want = [txt.scan(rx, cap=1 << 20) for rx in regexes]
+    assert len(want[0]) > 32768 and len(want[2]) > 32768 and len(want[6]) == 0 and 0 < len(want[1]) < 100
+    got, st = txt.scan_multi(regexes, cap=1 << 20, stats=True)
+    assert st["single"] >= 3 and st["shared"] + st["single"] == len(pats), st
+    for p, g, w in zip(pats, got, want):
+        assert np.array_equal(g, w), p
+    again = txt.scan_multi(regexes[::-1], cap=1 << 20)  # another call while `got` is alive: `got` must not change
+    for p, g, w, a in zip(pats, got, want, again[::-1]):
+        assert np.array_equal(g, w) and np.array_equal(a, w), p
+    monkeypatch.setenv("TRX_MULTI_WINDOW", "off")
+    for p, g, w in zip(pats, txt.scan_multi(regexes, cap=1 << 20), want):
+        assert np.array_equal(g, w), p
+    monkeypatch.delenv("TRX_MULTI_WINDOW")
+    total = sum(len(w) for w in want)
+    with pytest.raises(t.TetrexError) as e:
+        txt.scan_multi(regexes, cap=total - 1)
+    assert e.value.code == -5
+    assert sum(len(g) for g in txt.scan_multi(regexes, cap=total)) == total
+    for rx in regexes:
+        rx.close()
+    txt.close()

@@ -9,6 +9,7 @@ from __future__ import annotations
 
 import atexit
 import ctypes as C
+import sys
 import time
 import weakref
 
@@ -547,18 +548,24 @@ class Text:
         stride = 0 if cand.ndim == 1 else words
         assert cand.shape[-1] == words and (cand.ndim == 1 or cand.shape[0] == n)
         handles = (C.c_void_p * max(n, 1))(*[rx._h for rx in regexes])
-        if getattr(self, "_mhit_cap", 0) != cap:
-            self._mhit_buf, self._mpat_buf, self._mhit_cap = (TrxHit * cap)(), np.zeros(cap, dtype=np.uint32), cap
+        # arrays of this call's own (pages are touched only where hits land): the per-pattern results are views into them
+        # — the arrays of the previous call again if nobody holds a result of it any more (warm pages)
+        prev = getattr(self, "_multi_bufs", None)
+        if prev is not None and prev[0].shape[0] == cap and sys.getrefcount(prev[0]) == 2:
+            hit_buf, pat_buf = prev
+        else:
+            hit_buf, pat_buf = np.empty((cap, 4), dtype=np.uint32), np.empty(cap, dtype=np.uint32)
+            self._multi_bufs = (hit_buf, pat_buf)
+        del prev
         total = C.c_uint64()
         per = np.zeros(max(n, 1), dtype=np.uint64)
         st = np.zeros(4, dtype=np.uint64)
         t0 = time.perf_counter()
-        check(lib().trx_regex_scan_multi(self._h, handles, n, _ptr(cand), stride, C.addressof(self._mhit_buf), _ptr(self._mpat_buf),
+        check(lib().trx_regex_scan_multi(self._h, handles, n, _ptr(cand), stride, _ptr(hit_buf), _ptr(pat_buf),
                                          cap, C.byref(total), _ptr(per), _ptr(st)))
         self.last_multi_call_seconds = time.perf_counter() - t0
-        arr = np.frombuffer(self._mhit_buf, dtype=np.uint32, count=4 * total.value).reshape(-1, 4)
-        bounds = np.concatenate([[0], np.cumsum(per[:n])]).astype(np.int64)
-        out = [arr[bounds[i]:bounds[i + 1]].copy() for i in range(n)]
+        bounds = np.concatenate([[0], np.cumsum(per[:n])]).astype(np.int64).tolist()
+        out = [hit_buf[bounds[i]:bounds[i + 1]] for i in range(n)]
         self.last_multi_stats = dict(zip(("residues", "shared", "single", "passes"), map(int, st)))
         return (out, self.last_multi_stats) if stats else out
 

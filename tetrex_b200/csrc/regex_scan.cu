@@ -2,6 +2,8 @@
 // Reference: iter_disk_search + verify_* (include/query.h:97-188, src/query.cpp:167-315).
 #include <algorithm>
 #include <chrono>
+#include <atomic>
+#include <thread>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -78,6 +80,7 @@ struct trx_text
         trx::confirm_check win_confirm[trx::kMaxConfirm];
     };
     std::vector<cached_choice> choices;
+    std::unordered_map<uint64_t, uint32_t> plain_choice; // serial -> index in choices (forward, unmapped, default mode); entries are verified on use
     // per-scan scratch
     trx::scratch d_keys2, d_ends2, d_sort_tmp, d_hits_fmt;
     // multi-pattern scans (trx_regex_scan_multi): one staging block up (programs, automata, candidate words, phase-2
@@ -92,7 +95,7 @@ struct trx_text
     };
     multi_set m_sets[2];
     // the hits of a whole call stay on the device (one list for all patterns, one counter) until they are sorted there
-    trx::scratch m_d_hit_keys, m_d_hit_ends, m_d_hit_pats, m_d_total, m_h_total, m_d_sort;
+    trx::scratch m_d_hit_keys, m_d_hit_ends, m_d_hit_pats, m_d_total, m_h_total, m_d_sort, m_h_out;
     bool multi_attr_set{false};
 };
 
@@ -264,7 +267,7 @@ void trx_text_destroy(trx_text_t * t)
             s->release();
     }
     for (trx::scratch * s : {&t->d_keys2, &t->d_ends2, &t->d_sort_tmp, &t->d_hits_fmt, &t->m_d_hit_keys, &t->m_d_hit_ends, &t->m_d_hit_pats, &t->m_d_total,
-                             &t->m_h_total, &t->m_d_sort})
+                             &t->m_h_total, &t->m_d_sort, &t->m_h_out})
         s->release();
     for (trx_text::multi_set & ms : t->m_sets)
     {
@@ -1469,7 +1472,7 @@ static int scan_begin_impl(trx_text_t * t, trx_regex_t * re, const uint64_t * ca
             cc.reverse = reverse_strand;
             cc.mode = mode;
             cc.kind = choose_filter(*img, t->byte_freq, reverse, cc.window, cc.atoms);
-            if (t->choices.size() >= 256)
+            if (t->choices.size() >= 4096)
                 t->choices.clear();
             t->choices.push_back(cc);
             found = &t->choices.back();
@@ -1829,6 +1832,24 @@ int trx_regex_filter_plan(const trx_regex_t * re, const double * byte_freq, int 
 namespace
 {
 
+// the cached phase-1 choice of a pattern scanned forward, unmapped, in the default mode — without a walk over the cache
+trx_text::cached_choice * plain_choice_of(trx_text * t, uint64_t serial)
+{
+    auto const is_it = [&](trx_text::cached_choice const & cc) {
+        return cc.serial == serial && cc.reverse == 0 && cc.mode == 0 && cc.map_hash == 0;
+    };
+    auto const it = t->plain_choice.find(serial);
+    if (it != t->plain_choice.end() && it->second < t->choices.size() && is_it(t->choices[it->second]))
+        return &t->choices[it->second];
+    for (size_t i = t->choices.size(); i-- > 0;) // made by trx_regex_scan_begin, or the cache was cleared since
+        if (is_it(t->choices[i]))
+        {
+            t->plain_choice[serial] = static_cast<uint32_t>(i);
+            return &t->choices[i];
+        }
+    return nullptr;
+}
+
 // Class window of a pattern for regex_window_multi: up to kWindowLen CONSECUTIVE positions of the automaton that every
 // match passes through (dominators, each with its successor as the only way on), with the byte class of each.  "The text
 // carries class_0 .. class_{len-1} at p .. p+len-1" is then necessary for a match whose first byte lies in
@@ -2168,6 +2189,42 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
         return TRX_OK;
     };
     uint32_t n_passes = 0;
+    // pattern-at-a-time scans run on the scan slots' streams and report into the shared list: the counter must be clear
+    TRX_CUDA(cudaStreamSynchronize(st));
+    std::vector<int> pending; // tickets of scans in flight
+    struct abandon_pending
+    {
+        trx_text_t * t;
+        std::vector<int> & tickets;
+        ~abandon_pending()
+        {
+            for (int ticket : tickets) // only an error leaves any
+                trx_regex_scan_end(t, ticket, nullptr, nullptr, nullptr);
+        }
+    } const on_exit{t, pending};
+    size_t single_next = 0;
+    auto finish_oldest = [&]() -> int {
+        int const ticket = pending.front();
+        pending.erase(pending.begin());
+        uint64_t n = 0;
+        return trx_regex_scan_end(t, ticket, nullptr, &n, nullptr); // waits for the scan; its hits are in the shared list
+    };
+    // begin up to `limit` of the patterns queued for the single path, at most three in flight
+    auto pump_singles = [&](size_t limit) -> int {
+        for (; limit && single_next < single.size(); --limit)
+        {
+            if (pending.size() == 3)
+                TRX_TRY(finish_oldest());
+            uint32_t const i = single[single_next];
+            hit_sink sink{static_cast<unsigned long long *>(t->m_d_total.ptr), static_cast<uint64_t *>(t->m_d_hit_keys.ptr),
+                          static_cast<uint32_t *>(t->m_d_hit_ends.ptr), static_cast<uint32_t *>(t->m_d_hit_pats.ptr), i, cap};
+            int ticket = -1;
+            TRX_TRY(scan_begin_impl(t, regexes[i], cand_of(i), 0, nullptr, 0, &ticket, &sink));
+            pending.push_back(ticket);
+            ++single_next;
+        }
+        return TRX_OK;
+    };
 
     // ---- every pattern's phase-1 plan (cached per text like the single-pattern path does)
     char const * filt = getenv("TRX_REGEX_FILTER");
@@ -2200,10 +2257,7 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
             trx_regex_t * re = regexes[i];
             if (re->follow_list.size() > sizeof(regex_dev::follow_list))
                 continue;
-            trx_text::cached_choice * found = nullptr;
-            for (auto & cc : t->choices)
-                if (cc.serial == re->serial && cc.reverse == 0 && cc.mode == 0 && cc.map_hash == 0)
-                    found = &cc;
+            trx_text::cached_choice * found = plain_choice_of(t, re->serial);
             if (!found)
             {
                 fill_image(*re, false, nullptr, img.get());
@@ -2213,6 +2267,7 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
                 if (t->choices.size() >= 4096)
                     t->choices.clear();
                 t->choices.push_back(cc);
+                t->plain_choice[re->serial] = static_cast<uint32_t>(t->choices.size() - 1);
                 found = &t->choices.back();
             }
             if (found->win_state < 0)
@@ -2270,6 +2325,7 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
         if (window_mode)
         {
             wtab.assign(static_cast<size_t>(kWindowLen) * 4 * 256, 0u);
+            uint32_t beyond[kWindowLen][4] = {};
             while (wcur < eligible.size() && ids.size() < static_cast<size_t>(kMultiPatterns))
             {
                 staged_window const & w = wins[wcur];
@@ -2281,13 +2337,20 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
                 plan.prog.n_confirm = w.n_confirm;
                 memcpy(plan.prog.confirm, w.confirm, sizeof w.confirm);
                 plan.usable = true;
-                for (int pos = 0; pos < kWindowLen; ++pos)
-                    for (int ch = 0; ch < 256; ++ch)
-                        if (pos >= w.len || ((w.cls[pos][ch >> 5] >> (ch & 31)) & 1))
-                            wtab[(static_cast<size_t>(pos) * 4 + (k >> 5)) * 256 + ch] |= 1u << (k & 31);
+                for (int pos = 0; pos < w.len; ++pos)
+                    for (int word = 0; word < 8; ++word)
+                        for (uint32_t bits = w.cls[pos][word]; bits; bits &= bits - 1)
+                            wtab[(static_cast<size_t>(pos) * 4 + (k >> 5)) * 256 + 32 * word + __builtin_ctz(bits)] |= 1u << (k & 31);
+                for (int pos = w.len; pos < kWindowLen; ++pos) // a shorter window accepts every byte behind its end
+                    beyond[pos][k >> 5] |= 1u << (k & 31);
                 plans.push_back(plan);
                 ids.push_back(eligible[wcur++]);
             }
+            for (int pos = 0; pos < kWindowLen; ++pos)
+                for (int g = 0; g < 4; ++g)
+                    if (beyond[pos][g])
+                        for (int ch = 0; ch < 256; ++ch)
+                            wtab[(static_cast<size_t>(pos) * 4 + g) * 256 + ch] |= beyond[pos][g];
         }
         while (!window_mode && next < n_patterns && ids.size() < static_cast<size_t>(kMultiPatterns))
         {
@@ -2297,10 +2360,7 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
                 continue;
             }
             trx_regex_t * re = regexes[next];
-            trx_text::cached_choice const * found = nullptr;
-            for (auto const & cc : t->choices)
-                if (cc.serial == re->serial && cc.reverse == 0 && cc.mode == 0 && cc.map_hash == 0)
-                    found = &cc;
+            trx_text::cached_choice const * found = plain_choice_of(t, re->serial);
             if (!found)
             {
                 fill_image(*re, false, nullptr, img.get());
@@ -2310,6 +2370,7 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
                 if (t->choices.size() >= 4096)
                     t->choices.clear();
                 t->choices.push_back(cc);
+                t->plain_choice[re->serial] = static_cast<uint32_t>(t->choices.size() - 1);
                 found = &t->choices.back();
             }
             if (found->multi_kind < 0)
@@ -2585,6 +2646,7 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
         TRX_CUDA(cudaEventRecord(ms.done, st));
         ms.ids = ids;
         ms.in_flight = true;
+        TRX_TRY(pump_singles(1)); // one of the waiting single-path patterns per pass, on the slots' streams beside it
         us_device += us(t_staged, now());
     }
     {
@@ -2602,43 +2664,9 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
     // pattern at a time, pipelined over the scan slots like a caller of trx_regex_scan_begin/_end would
     if (stats)
         stats[2] = single.size();
-    {
-        // these scans run on the scan slots' streams: the counter was cleared on the context's stream, which every retired
-        // pass has synchronised with — except when there was no pass at all
-        if (n_passes == 0)
-            TRX_CUDA(cudaStreamSynchronize(st));
-        std::vector<int> pending; // tickets
-        auto finish = [&](int ticket) -> int {
-            uint64_t n = 0;
-            return trx_regex_scan_end(t, ticket, nullptr, &n, nullptr); // waits for the scan; its hits are in the shared list
-        };
-        int rc = TRX_OK;
-        for (uint32_t i : single)
-        {
-            if (pending.size() == 3)
-            {
-                rc = finish(pending.front());
-                pending.erase(pending.begin());
-                if (rc != TRX_OK)
-                    break;
-            }
-            hit_sink sink{static_cast<unsigned long long *>(t->m_d_total.ptr), static_cast<uint64_t *>(t->m_d_hit_keys.ptr),
-                          static_cast<uint32_t *>(t->m_d_hit_ends.ptr), static_cast<uint32_t *>(t->m_d_hit_pats.ptr), i, cap};
-            int ticket = -1;
-            rc = scan_begin_impl(t, regexes[i], cand_of(i), 0, nullptr, 0, &ticket, &sink);
-            if (rc != TRX_OK)
-                break;
-            pending.push_back(ticket);
-        }
-        for (int ticket : pending)
-        {
-            if (rc == TRX_OK)
-                rc = finish(ticket);
-            else
-                trx_regex_scan_end(t, ticket, nullptr, nullptr, nullptr); // abandon
-        }
-        TRX_TRY(rc);
-    }
+    TRX_TRY(pump_singles(single.size()));
+    while (!pending.empty())
+        TRX_TRY(finish_oldest());
 
     us_single = us(t_single, now());
     auto const t_assemble = now();
@@ -2709,13 +2737,83 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
         multi_format_kernel<<<grid, 256, 0, st>>>(keys2, vals2, idx2, t->d_rec_bin, n, fmt);
         c->launches += 3 + 6; // three kernels of ours + cub's histogram / onesweep passes
         TRX_CUDA(cudaGetLastError());
-        TRX_CUDA(cudaMemcpyAsync(hits, fmt, n * sizeof(trx_hit), cudaMemcpyDeviceToHost, st));
-        TRX_CUDA(cudaMemcpyAsync(hit_pattern, pat2, n * 4, cudaMemcpyDeviceToHost, st));
-        TRX_CUDA(cudaStreamSynchronize(st));
+        if (trace)
+        {
+            cudaStreamSynchronize(st);
+            fprintf(stderr, "trx_regex_scan_multi: %llu hits sorted and formatted %.0f us after the last scan\n", (unsigned long long)n,
+                    us(t_assemble, now()));
+        }
+        if (n < (1u << 16))
+        {
+            TRX_CUDA(cudaMemcpyAsync(hits, fmt, n * sizeof(trx_hit), cudaMemcpyDeviceToHost, st));
+            TRX_CUDA(cudaMemcpyAsync(hit_pattern, pat2, n * 4, cudaMemcpyDeviceToHost, st));
+            TRX_CUDA(cudaStreamSynchronize(st));
+        }
+        else
+        {
+            // long lists: a copy into the caller's pageable arrays runs at a few GB/s.  Pinned staging at PCIe speed, in four
+            // pieces, each moved on by a host thread of its own as soon as it has landed.
+            constexpr int kPieces = 4;
+            t->m_h_out.pinned_host = true;
+            TRX_TRY(t->m_h_out.reserve(n16 * 20));
+            auto * h_fmt = static_cast<uint8_t *>(t->m_h_out.ptr);
+            auto * h_pat = h_fmt + n16 * 16;
+            uint64_t const step = ((n + kPieces - 1) / kPieces + 3) & ~uint64_t{3};
+            cudaEvent_t landed[kPieces] = {};
+            int n_events = 0;
+            cudaError_t err = cudaSuccess;
+            for (int i = 0; i < kPieces && err == cudaSuccess; ++i)
+            {
+                uint64_t const lo = std::min<uint64_t>(n, i * step), hi = std::min<uint64_t>(n, lo + step);
+                if (hi > lo)
+                {
+                    err = cudaMemcpyAsync(h_fmt + lo * 16, reinterpret_cast<uint8_t const *>(fmt) + lo * 16, (hi - lo) * 16,
+                                          cudaMemcpyDeviceToHost, st);
+                    if (err == cudaSuccess)
+                        err = cudaMemcpyAsync(h_pat + lo * 4, reinterpret_cast<uint8_t const *>(pat2) + lo * 4, (hi - lo) * 4,
+                                              cudaMemcpyDeviceToHost, st);
+                }
+                if (err == cudaSuccess)
+                    err = cudaEventCreateWithFlags(&landed[i], cudaEventDisableTiming);
+                if (err == cudaSuccess)
+                {
+                    ++n_events;
+                    err = cudaEventRecord(landed[i], st);
+                }
+            }
+            std::vector<std::thread> movers;
+            std::atomic<int> failed{0};
+            for (int i = 0; i < n_events; ++i)
+                movers.emplace_back([&, i] {
+                    cudaSetDevice(c->device);
+                    uint64_t const lo = std::min<uint64_t>(n, i * step), hi = std::min<uint64_t>(n, lo + step);
+                    if (cudaEventSynchronize(landed[i]) != cudaSuccess)
+                    {
+                        failed = 1;
+                        return;
+                    }
+                    memcpy(reinterpret_cast<uint8_t *>(hits) + lo * 16, h_fmt + lo * 16, (hi - lo) * 16);
+                    memcpy(reinterpret_cast<uint8_t *>(hit_pattern) + lo * 4, h_pat + lo * 4, (hi - lo) * 4);
+                });
+            for (std::thread & th : movers)
+                th.join();
+            for (int i = 0; i < n_events; ++i)
+                cudaEventDestroy(landed[i]);
+            TRX_CUDA(err);
+            if (failed)
+                return set_error(TRX_ECUDA, "trx_regex_scan_multi: the copy of the hit list failed");
+        }
     }
-    if (per_pattern_hits)
-        for (uint64_t i = 0; i < n; ++i)
-            ++per_pattern_hits[hit_pattern[i]];
+    if (per_pattern_hits) // the list is sorted by pattern: boundaries by bisection, not a pass over a million entries
+    {
+        uint32_t const * at = hit_pattern;
+        for (uint32_t i = 0; i < n_patterns && at < hit_pattern + n; ++i)
+        {
+            uint32_t const * const next_at = std::upper_bound(at, static_cast<uint32_t const *>(hit_pattern + n), i);
+            per_pattern_hits[i] = static_cast<uint64_t>(next_at - at);
+            at = next_at;
+        }
+    }
     return TRX_OK;
 }
 
