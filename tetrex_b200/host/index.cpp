@@ -5,6 +5,10 @@
 // (user_bin_data_) and inserts them one by one; here the FASTA bytes go to the device once and K1
 // (trx_emplace_records) derives k-mers, hashes and sets bits in one pass — nothing is buffered per k-mer.
 // store()/load(): store_ibf / load_ibf through the cereal-compatible file of ibf_file.cpp.
+#include <exception>
+#include <thread>
+#include <mutex>
+#include <atomic>
 #include <algorithm>
 #include <cmath>
 #include <filesystem>
@@ -89,17 +93,59 @@ struct library
 
 // bins that are not wanted are skipped (they keep their ids and simply have no records): a verify shard, or a
 // one-shot query that only needs its candidate bins
+// `threads` (the command line's -t; the reference spends it on OpenMP over bins, include/query.h:113): the files are
+// parsed by that many host threads — inflate + kseq is the cost of a one-shot query — and joined in bin order.
+// 0 or 1 = as many as the machine has, at most 16.
 library read_library(std::vector<std::string> const & files, int molecule, unsigned k, bool announce_short,
-                     std::vector<bool> const * want = nullptr)
+                     std::vector<bool> const * want = nullptr, unsigned threads = 0)
 {
     library lib;
     lib.offsets.push_back(0);
     lib.bin_emits.assign(files.size(), 0);
+    std::vector<size_t> todo;
     for (size_t b = 0; b < files.size(); ++b)
+        if (!want || (*want)[b])
+            todo.push_back(b);
+    std::vector<std::vector<fasta_record>> parsed(todo.size());
     {
-        if (want && !(*want)[b])
-            continue;
-        for (fasta_record & rec : read_fasta(files[b]))
+        unsigned workers = threads > 1 ? threads : std::min(16u, std::max(1u, std::thread::hardware_concurrency()));
+        workers = static_cast<unsigned>(std::min<size_t>(workers, todo.size()));
+        std::atomic<size_t> next{0};
+        std::exception_ptr failure;
+        std::mutex failure_lock;
+        auto work = [&] {
+            for (size_t i = next++; i < todo.size(); i = next++)
+            {
+                try
+                {
+                    parsed[i] = read_fasta(files[todo[i]]);
+                }
+                catch (...)
+                {
+                    std::lock_guard<std::mutex> hold(failure_lock);
+                    if (!failure)
+                        failure = std::current_exception();
+                    next = todo.size();
+                }
+            }
+        };
+        if (workers <= 1)
+            work();
+        else
+        {
+            std::vector<std::thread> pool;
+            for (unsigned w = 0; w < workers; ++w)
+                pool.emplace_back(work);
+            for (std::thread & t : pool)
+                t.join();
+        }
+        if (failure)
+            std::rethrow_exception(failure);
+    }
+    for (size_t i = 0; i < todo.size(); ++i)
+    {
+        size_t const b = todo[i];
+        for (fasta_record & rec : parsed[i])
         {
             if (rec.seq.size() < k)
             {
@@ -116,6 +162,7 @@ library read_library(std::vector<std::string> const & files, int molecule, unsig
             lib.rec_bin.push_back(static_cast<uint32_t>(b));
             lib.names.push_back(">" + rec.name);
         }
+        std::vector<fasta_record>().swap(parsed[i]);
     }
     return lib;
 }
@@ -226,7 +273,7 @@ void DeviceIndex::build(index_arguments const & args)
     init_maps();
 
     int const molecule = args.dna ? TRX_MOL_NA : TRX_MOL_AA;
-    library lib = read_library(files, molecule, args.k, true);
+    library lib = read_library(files, molecule, args.k, true, nullptr, args.t);
     seq_count_ = lib.indexed;
     device_library dev(ctx_, lib);
 
@@ -478,7 +525,7 @@ DeviceIndex::text_store const & DeviceIndex::text(bitvector const & cand)
             for (size_t b = first_bin; b < last_bin; ++b)
                 if (load[b] && !wanted(b) && !std::filesystem::exists(img_.acid_libs[b]))
                     load[b] = false;
-        library lib = read_library(img_.acid_libs, is_dna() ? TRX_MOL_NA : TRX_MOL_AA, img_.k, false, &load);
+        library lib = read_library(img_.acid_libs, is_dna() ? TRX_MOL_NA : TRX_MOL_AA, img_.k, false, &load, threads_);
         if (text_ && text_->text)
             trx_text_destroy(text_->text);
         text_ = std::make_unique<text_store>();

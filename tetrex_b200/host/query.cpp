@@ -52,22 +52,26 @@ struct regex_handle
     ~regex_handle() { trx_regex_destroy(re); }
 };
 
+constexpr uint64_t kHitRoom = 1u << 20;
+
 std::vector<trx_hit> scan(DeviceIndex::text_store const & store, regex_handle & rx, bitvector const & cand, bool reverse,
                           uint8_t const * map)
 {
-    std::vector<trx_hit> hits(4096);
+    // room for kHitRoom hits up front — untouched memory costs nothing, and the device side keeps its buffers — so that a
+    // second scan is only ever needed beyond that
+    uint64_t room = kHitRoom;
     for (;;)
     {
+        std::unique_ptr<trx_hit[]> buf(new trx_hit[room]);
         uint64_t n = 0;
-        int rc = trx_regex_scan(store.text, rx.re, cand.data(), reverse ? 1 : 0, map, hits.data(), hits.size(), &n, nullptr);
+        int rc = trx_regex_scan(store.text, rx.re, cand.data(), reverse ? 1 : 0, map, buf.get(), room, &n, nullptr);
         if (rc == TRX_ECAPACITY)
         {
-            hits.resize(n + n / 8 + 16);
+            room = n + n / 8 + 16;
             continue;
         }
         check(rc);
-        hits.resize(n);
-        return hits;
+        return std::vector<trx_hit>(buf.get(), buf.get() + n);
     }
 }
 
@@ -140,7 +144,7 @@ uint64_t search_impl(bitvector const & hits_in, std::string const & query_in, De
         // both strands in flight at once (trx_regex_scan_begin/_end): the second scan's kernels follow the first one's
         // without a host round trip in between
         int t_fwd = -1, t_rev = -1;
-        uint64_t const cap = 4096;
+        uint64_t const cap = kHitRoom;
         check(trx_regex_scan_begin(store.text, rx.re, cand.data(), 0, map, cap, &t_fwd));
         int const rc_begin = trx_regex_scan_begin(store.text, rx.re, cand.data(), 1, nullptr, cap, &t_rev);
         // a ticket that is not ended keeps its slot busy on the persistent text handle: whatever happens below, both
@@ -156,15 +160,14 @@ uint64_t search_impl(bitvector const & hits_in, std::string const & query_in, De
             }
         } guard_fwd{store.text, &t_fwd}, guard_rev{store.text, &t_rev};
         auto finish = [&](int & ticket, bool reverse, uint8_t const * m) {
-            std::vector<trx_hit> hits(cap);
+            std::unique_ptr<trx_hit[]> hits(new trx_hit[cap]);
             uint64_t n = 0;
-            int const rc = trx_regex_scan_end(store.text, ticket, hits.data(), &n, nullptr);
+            int const rc = trx_regex_scan_end(store.text, ticket, hits.get(), &n, nullptr);
             ticket = -1;
             if (rc == TRX_ECAPACITY)
                 return scan(store, rx, cand, reverse, m); // more hits than the speculative buffer: once more, with room
             check(rc);
-            hits.resize(n);
-            return hits;
+            return std::vector<trx_hit>(hits.get(), hits.get() + n);
         };
         fwd = finish(t_fwd, false, map);
         if (rc_begin != TRX_OK)
@@ -537,6 +540,7 @@ void run_collection_multi_gpu(query_arguments & args, unsigned n)
                 {
                     DeviceIndex index(ctxs[i]);
                     index.set_shard(i, n);
+                    index.set_threads(args.t);
                     index.load(args.idx);
                     shard_hooks hooks;
                     hooks.comm = comms[i];
@@ -619,6 +623,7 @@ void drive_query(query_arguments & args)
     try
     {
         DeviceIndex index(ctx);
+        index.set_threads(args.t);
         index.load(args.idx);
         // run_collection loads the DGram index named by -g (include/query.h:258-264); run_conjunction only would if
         // has_dibf were already set, which nothing does (:300-301) — so `-c` walks with the gap bounds 0..0 and no filter

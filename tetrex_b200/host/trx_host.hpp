@@ -285,6 +285,7 @@ public:
     text_store const & text(std::vector<uint64_t> const & cand);
     // resident processes (servers, benchmarks) load every bin on first use instead of growing query by query
     void preload_all_text(bool on) { preload_all_ = on; }
+    void set_threads(unsigned n) { threads_ = n; } // -t: host threads that parse the bins' FASTA files
 
     // Device scratch of the collector, kept between queries: the path-slot pool (cudaMalloc + cudaFree of up to
     // 128 MB per query cost 0.6 ms — more than the whole walk) and the k-mer / hit-vector buffers of the HIBF route.
@@ -314,6 +315,7 @@ private:
     uint8_t aamap_[256]{}, redmap_[256]{};
     uint64_t seq_count_{};
     bool preload_all_{false};
+    unsigned threads_{0};
     std::unique_ptr<text_store> text_;
     collector_scratch scratch_;
     DGramIndex const * dgram_{nullptr};
