@@ -15,6 +15,9 @@
 // restates the container's slot placement, every rank is processed in exactly that order, and
 // tests/test_collector_vs_ref.py fuzzes the resulting candidate sets against the compiled reference's process_query.
 #include <algorithm>
+#include <cstdlib>
+#include <string>
+#include <unordered_map>
 
 #include "rh_order.hpp"
 #include "trx_host.hpp"
@@ -132,19 +135,154 @@ void reserve_dev(trx_ctx_t * ctx, void *& ptr, uint64_t & have, uint64_t want)
 
 } // namespace
 
-bitvector collect(kgraph const & g, DeviceIndex & index, collect_stats * stats, shard_hooks const * hooks)
+// HBM-resident path slots (a6): one launch per rank probes and ANDs, one performs the ORs; only alive bytes travel
+struct device_paths
+{
+    DeviceIndex & index;
+    shard_hooks const * hooks;
+    trx_comm_t * comm;
+    bool sharded;
+    uint64_t W;
+    slot_pool pool;
+    device_paths(DeviceIndex & ix, shard_hooks const * h, trx_comm_t * c, bool sh, uint64_t words)
+        : index(ix), hooks(h), comm(c), sharded(sh), W(words), pool(ix.scratch())
+    {}
+    uint32_t fresh() { return pool.fresh(); }
+    void fill(uint32_t slot, uint64_t bins) { check(trx_paths_fill(pool.paths(), slot, 1, bins)); }
+    void step(std::vector<uint64_t> const & kmers, std::vector<uint32_t> const & slots, std::vector<uint8_t> & res)
+    {
+        DeviceIndex::collector_scratch & sc = index.scratch();
+        if (comm) // probe + all-reduce(MAX) of the alive bytes on the device + one read-back
+            check(trx_paths_step_sharded(index.flat(), pool.paths(), comm, kmers.data(), slots.data(), kmers.size(), res.data()));
+        else if (!index.is_hibf())
+            check(trx_paths_step(index.flat(), pool.paths(), kmers.data(), slots.data(), kmers.size(), res.data()));
+        else
+        {
+            uint64_t const n = kmers.size();
+            reserve_dev(index.ctx(), sc.d_kmers, sc.kmers_bytes, n * 8);
+            reserve_dev(index.ctx(), sc.d_hits, sc.hits_bytes, n * W * 8);
+            check(trx_copy_h2d(index.ctx(), sc.d_kmers, kmers.data(), n * 8));
+            check(trx_hibf_membership_dev(index.hibf(), static_cast<uint64_t *>(sc.d_kmers), n,
+                                          static_cast<uint64_t *>(sc.d_hits), nullptr));
+            std::vector<uint32_t> idx(n);
+            for (uint64_t i = 0; i < n; ++i)
+                idx[i] = static_cast<uint32_t>(i);
+            check(trx_paths_and_hits(pool.paths(), static_cast<uint64_t *>(sc.d_hits), idx.data(), slots.data(), n, res.data()));
+        }
+        if (sharded && !comm)
+            hooks->any_alive(res.data(), res.size());
+    }
+    void step_dgram(std::vector<uint64_t> const & codes, std::vector<uint32_t> const & slots, std::vector<uint8_t> & res)
+    {
+        check(trx_paths_step(index.dgram()->flat(), pool.paths(), codes.data(), slots.data(), codes.size(), res.data()));
+    }
+    void or_pairs(std::vector<uint32_t> const & dst, std::vector<uint32_t> const & src)
+    {
+        check(trx_paths_or(pool.paths(), dst.data(), src.data(), dst.size()));
+    }
+};
+
+// Dry run: nothing dies, so the walk asks for every k-mer ANY pruning of it could ask for (an item's k-mer does not depend
+// on which paths are alive).  Over budget = the graph is too wide to probe speculatively.
+struct budget_exceeded
+{};
+struct recording_paths
+{
+    static constexpr size_t kMaxProbes = 1024, kMaxSlots = 1u << 15;
+    std::vector<uint64_t> kmers, codes; // distinct, in first-use order
+    std::unordered_map<uint64_t, uint32_t> kmer_row, code_row;
+    uint32_t slots{0};
+    uint32_t fresh()
+    {
+        if (slots >= kMaxSlots)
+            throw budget_exceeded{};
+        return slots++;
+    }
+    void fill(uint32_t, uint64_t) {}
+    static void note(std::vector<uint64_t> const & in, std::vector<uint64_t> & list, std::unordered_map<uint64_t, uint32_t> & row)
+    {
+        for (uint64_t v : in)
+            if (row.emplace(v, static_cast<uint32_t>(list.size())).second)
+            {
+                if (list.size() >= kMaxProbes)
+                    throw budget_exceeded{};
+                list.push_back(v);
+            }
+    }
+    void step(std::vector<uint64_t> const & in, std::vector<uint32_t> const &, std::vector<uint8_t> & res)
+    {
+        note(in, kmers, kmer_row);
+        std::fill(res.begin(), res.end(), uint8_t{1});
+    }
+    void step_dgram(std::vector<uint64_t> const & in, std::vector<uint32_t> const &, std::vector<uint8_t> & res)
+    {
+        note(in, codes, code_row);
+        std::fill(res.begin(), res.end(), uint8_t{1});
+    }
+    void or_pairs(std::vector<uint32_t> const &, std::vector<uint32_t> const &) {}
+};
+
+// Path bitvectors in host words over membership rows that are already here: the reference's own arithmetic
+// (`path_ &= ibf_->query(kmer)`, `path_ |= other.path_`, `path_.none()`), no device round trip per rank
+struct host_paths
+{
+    uint64_t W;
+    recording_paths const & known;
+    std::vector<uint64_t> const & kmer_rows; // known.kmers.size() x W
+    std::vector<uint64_t> const & code_rows;
+    std::vector<uint64_t> words;
+    uint32_t slots{0};
+    host_paths(uint64_t w, recording_paths const & k, std::vector<uint64_t> const & kr, std::vector<uint64_t> const & cr)
+        : W(w), known(k), kmer_rows(kr), code_rows(cr)
+    {
+        words.reserve(64 * W);
+    }
+    uint32_t fresh()
+    {
+        words.resize(words.size() + W, 0);
+        return slots++;
+    }
+    void fill(uint32_t slot, uint64_t bins)
+    {
+        for (uint64_t w = 0; w < W; ++w)
+            words[slot * W + w] = bins >= 64 * (w + 1) ? ~0ull : (bins > 64 * w ? (1ull << (bins - 64 * w)) - 1 : 0);
+    }
+    void and_rows(std::vector<uint64_t> const & in, std::vector<uint32_t> const & sl, std::vector<uint8_t> & res,
+                  std::unordered_map<uint64_t, uint32_t> const & row_of, std::vector<uint64_t> const & rows)
+    {
+        for (size_t i = 0; i < in.size(); ++i)
+        {
+            uint64_t const * row = rows.data() + static_cast<size_t>(row_of.at(in[i])) * W;
+            uint64_t * path = words.data() + static_cast<size_t>(sl[i]) * W;
+            uint64_t any = 0;
+            for (uint64_t w = 0; w < W; ++w)
+                any |= (path[w] &= row[w]);
+            res[i] = any != 0;
+        }
+    }
+    void step(std::vector<uint64_t> const & in, std::vector<uint32_t> const & sl, std::vector<uint8_t> & res)
+    {
+        and_rows(in, sl, res, known.kmer_row, kmer_rows);
+    }
+    void step_dgram(std::vector<uint64_t> const & in, std::vector<uint32_t> const & sl, std::vector<uint8_t> & res)
+    {
+        and_rows(in, sl, res, known.code_row, code_rows);
+    }
+    void or_pairs(std::vector<uint32_t> const & dst, std::vector<uint32_t> const & src)
+    {
+        for (size_t i = 0; i < dst.size(); ++i)
+            for (uint64_t w = 0; w < W; ++w)
+                words[static_cast<size_t>(dst[i]) * W + w] |= words[static_cast<size_t>(src[i]) * W + w];
+    }
+};
+
+// The walk itself, over any store of path bitvectors (`Paths`): HBM-resident slots driven rank by rank (device_paths),
+// a dry run that only records which k-mers the walk can ask for (recording_paths), or host words over membership rows
+// fetched in one batch (host_paths).  Returns the slot that holds path_matrix.
+template <class Paths>
+uint32_t walk(kgraph const & g, DeviceIndex & index, collect_stats * stats, Paths & paths, uint64_t bins)
 {
     size_t const n_nodes = g.size();
-    // a column shard of a flat index walks the same graph over its own bins only: paths are shard_words() wide and the
-    // pruning decision is made global through hooks->any_alive
-    bool const sharded = !index.is_hibf() && index.shard_count() > 1;
-    uint64_t const word_begin = sharded ? index.shard_word_begin() : 0;
-    uint64_t const W = index.path_words();
-    uint64_t const bins = sharded ? std::min<uint64_t>(W * 64, index.bin_count() > word_begin * 64 ? index.bin_count() - word_begin * 64 : 0)
-                                  : index.bin_count();
-    if (sharded && !(hooks && (hooks->any_alive || hooks->comm)))
-        throw error("a column-sharded index needs shard_hooks::any_alive or ::comm (the pruning decision spans all shards)");
-    trx_comm_t * const comm = sharded && hooks ? hooks->comm : nullptr;
     uint8_t const k = index.k();
     unsigned const bits = index.is_dna() ? 2 : 5;
     // create_selection_bitmask (otf_collector.h:168-182): the low (k-1) symbols
@@ -152,11 +290,9 @@ bitvector collect(kgraph const & g, DeviceIndex & index, collect_stats * stats, 
     for (unsigned i = 0; i + 1 < k; ++i)
         submask = (submask << bits) | ((1ull << bits) - 1);
 
-    prepare_pool(index, W);
-    slot_pool pool(index.scratch());
-    uint32_t const match_slot = pool.fresh(); // path_matrix = bitvector(bins): all clear (pool is zeroed)
-    uint32_t const start_slot = pool.fresh();
-    check(trx_paths_fill(pool.paths(), start_slot, 1, bins)); // hit_vector = bitvector(bins, true)
+    uint32_t const match_slot = paths.fresh(); // path_matrix = bitvector(bins): all clear (fresh slots are zero)
+    uint32_t const start_slot = paths.fresh();
+    paths.fill(start_slot, bins); // hit_vector = bitvector(bins, true)
 
     std::vector<bucket> table(n_nodes);
     std::vector<int> node_of_rank(n_nodes, -1);
@@ -177,7 +313,7 @@ bitvector collect(kgraph const & g, DeviceIndex & index, collect_stats * stats, 
         }
         if (!may_hand_over)
         {
-            uint32_t copy = pool.fresh(); // zero → OR = copy
+            uint32_t copy = paths.fresh(); // zero → OR = copy
             or_dst.push_back(copy);
             or_src.push_back(it.slot);
             it.slot = copy;
@@ -195,7 +331,6 @@ bitvector collect(kgraph const & g, DeviceIndex & index, collect_stats * stats, 
     std::vector<uint64_t> dgram_codes;
     std::vector<uint32_t> dgram_slots, dgram_item;
 
-    DeviceIndex::collector_scratch & sc = index.scratch();
     std::vector<uint64_t> probe_kmers;
     std::vector<uint32_t> probe_slots, probe_item;
     std::vector<uint8_t> alive;
@@ -318,30 +453,7 @@ bitvector collect(kgraph const & g, DeviceIndex & index, collect_stats * stats, 
             if (!probe_kmers.empty())
             {
                 std::vector<uint8_t> res(probe_kmers.size());
-                if (comm) // probe + all-reduce(MAX) of the alive bytes on the device + one read-back
-                    check(trx_paths_step_sharded(index.flat(), pool.paths(), comm, probe_kmers.data(), probe_slots.data(),
-                                                 probe_kmers.size(), res.data()));
-                else if (!index.is_hibf())
-                {
-                    check(trx_paths_step(index.flat(), pool.paths(), probe_kmers.data(), probe_slots.data(),
-                                         probe_kmers.size(), res.data()));
-                }
-                else
-                {
-                    uint64_t const n = probe_kmers.size();
-                    reserve_dev(index.ctx(), sc.d_kmers, sc.kmers_bytes, n * 8);
-                    reserve_dev(index.ctx(), sc.d_hits, sc.hits_bytes, n * W * 8);
-                    check(trx_copy_h2d(index.ctx(), sc.d_kmers, probe_kmers.data(), n * 8));
-                    check(trx_hibf_membership_dev(index.hibf(), static_cast<uint64_t *>(sc.d_kmers), n,
-                                                  static_cast<uint64_t *>(sc.d_hits), nullptr));
-                    std::vector<uint32_t> idx(n);
-                    for (uint64_t i = 0; i < n; ++i)
-                        idx[i] = static_cast<uint32_t>(i);
-                    check(trx_paths_and_hits(pool.paths(), static_cast<uint64_t *>(sc.d_hits), idx.data(),
-                                             probe_slots.data(), n, res.data()));
-                }
-                if (sharded && !comm)
-                    hooks->any_alive(res.data(), res.size());
+                paths.step(probe_kmers, probe_slots, res);
                 for (size_t j = 0; j < res.size(); ++j)
                     alive[probe_item[j]] = res[j];
                 if (stats)
@@ -350,8 +462,7 @@ bitvector collect(kgraph const & g, DeviceIndex & index, collect_stats * stats, 
             if (!dgram_codes.empty())
             {
                 std::vector<uint8_t> res(dgram_codes.size());
-                check(trx_paths_step(dibf->flat(), pool.paths(), dgram_codes.data(), dgram_slots.data(), dgram_codes.size(),
-                                     res.data()));
+                paths.step_dgram(dgram_codes, dgram_slots, res);
                 for (size_t j = 0; j < res.size(); ++j)
                     alive[dgram_item[j]] = res[j];
                 if (stats)
@@ -362,10 +473,69 @@ bitvector collect(kgraph const & g, DeviceIndex & index, collect_stats * stats, 
                     push(g.first[node], b.items[i], true);
         }
         if (!or_dst.empty())
-            check(trx_paths_or(pool.paths(), or_dst.data(), or_src.data(), or_dst.size()));
+            paths.or_pairs(or_dst, or_src);
         b.items.clear();
         b.by_key.clear();
     }
+    return match_slot;
+}
+
+bitvector collect(kgraph const & g, DeviceIndex & index, collect_stats * stats, shard_hooks const * hooks)
+{
+    // a column shard of a flat index walks the same graph over its own bins only: paths are shard_words() wide and the
+    // pruning decision is made global through hooks->any_alive
+    bool const sharded = !index.is_hibf() && index.shard_count() > 1;
+    uint64_t const word_begin = sharded ? index.shard_word_begin() : 0;
+    uint64_t const W = index.path_words();
+    uint64_t const bins = sharded ? std::min<uint64_t>(W * 64, index.bin_count() > word_begin * 64 ? index.bin_count() - word_begin * 64 : 0)
+                                  : index.bin_count();
+    if (sharded && !(hooks && (hooks->any_alive || hooks->comm)))
+        throw error("a column-sharded index needs shard_hooks::any_alive or ::comm (the pruning decision spans all shards)");
+    trx_comm_t * const comm = sharded && hooks ? hooks->comm : nullptr;
+
+    // One device round trip for the whole query where the k-graph is small enough to probe speculatively: a dry run of the
+    // walk lists every k-mer it can ask for, ONE membership batch brings their rows, and the walk proper runs on host
+    // words (the reference's own arithmetic).  Pruning then saves no probes — it never saved device time on these graphs,
+    // where a rank is one launch and one synchronisation (6.5 us flat, 19 us HIBF per rank) — and the candidate set and the
+    // statistics are those of the pruned walk.  Column shards and wide graphs keep their paths in HBM.
+    char const * const spec_env = getenv("TRX_COLLECT_SPECULATIVE"); // =off: A/B and tests
+    bool const speculative_off = spec_env && std::string(spec_env) == "off";
+    if (!sharded && !speculative_off)
+    {
+        recording_paths rec;
+        bool fits = true;
+        try
+        {
+            walk(g, index, nullptr, rec, bins);
+        }
+        catch (budget_exceeded const &)
+        {
+            fits = false;
+        }
+        if (fits)
+        {
+            std::vector<uint64_t> kmer_rows(rec.kmers.size() * W), code_rows(rec.codes.size() * W);
+            if (!rec.kmers.empty())
+            {
+                if (index.is_hibf())
+                    check(trx_hibf_membership(index.hibf(), rec.kmers.data(), rec.kmers.size(), kmer_rows.data(), nullptr));
+                else
+                    check(trx_bulk_contains(index.flat(), rec.kmers.data(), rec.kmers.size(), kmer_rows.data()));
+            }
+            if (!rec.codes.empty())
+                check(trx_bulk_contains(index.dgram()->flat(), rec.codes.data(), rec.codes.size(), code_rows.data()));
+            host_paths hp(W, rec, kmer_rows, code_rows);
+            uint32_t const match_slot = walk(g, index, stats, hp, bins);
+            bitvector out(index.bin_words(), 0);
+            std::copy(hp.words.begin() + static_cast<size_t>(match_slot) * W, hp.words.begin() + static_cast<size_t>(match_slot + 1) * W,
+                      out.begin());
+            return out;
+        }
+    }
+    prepare_pool(index, W);
+    device_paths paths(index, hooks, comm, sharded, W);
+    uint32_t const match_slot = walk(g, index, stats, paths, bins);
+    slot_pool & pool = paths.pool;
     bitvector out(index.bin_words(), 0);
     check(trx_paths_read(pool.paths(), match_slot, 1, out.data() + word_begin));
     if (comm) // every rank contributes its column block (equal sizes: the shard count divides bin_words) and gets all
