@@ -766,6 +766,20 @@ int trx_bulk_contains(trx_ibf_t * f, const uint64_t * kmers, uint64_t n, uint64_
     trx_ctx * c = f->ctx;
     TRX_TRY(c->use());
     uint64_t const out_bytes = n * f->shard_words * 8;
+    if (n <= 64 && out_bytes <= (64u << 10))
+    {
+        // a handful of k-mers (one query's k-graph): the kernel reads them from pinned host memory and writes the hit
+        // vectors back into it — one launch and one synchronisation instead of two staged copies around them
+        size_t const off_out = (n * 8 + 255) & ~size_t{255};
+        c->h_pin[0].pinned_host = true;
+        TRX_TRY(c->h_pin[0].reserve(off_out + out_bytes));
+        auto * pin = static_cast<uint8_t *>(c->h_pin[0].ptr);
+        memcpy(pin, kmers, n * 8);
+        TRX_TRY(trx_bulk_contains_dev(f, reinterpret_cast<uint64_t *>(pin), n, reinterpret_cast<uint64_t *>(pin + off_out)));
+        TRX_CUDA(cudaStreamSynchronize(c->stream));
+        memcpy(out_words, pin + off_out, out_bytes);
+        return TRX_OK;
+    }
     TRX_TRY(c->d_in[0].reserve(n * 8));
     TRX_TRY(c->d_out[0].reserve(out_bytes));
     TRX_CUDA(cudaMemcpyAsync(c->d_in[0].ptr, kmers, n * 8, cudaMemcpyHostToDevice, c->stream));
