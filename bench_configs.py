@@ -411,6 +411,24 @@ def measure_c3_augmented(t, ctx, ix, files, workdir, patterns, scan_all_bins, bu
     ix.attach_dgram(path)
     out["dgram_index"]["load_s"] = round(time.perf_counter() - t0, 2)
     res_g = measure_c3_patterns(ix, patterns, scan_all_bins, budget_s=budget_s / 2)
+    # `tetrex query -f`: the filter phase of the whole motif file with ONE membership batch (process_query_batch)
+    ix.local_candidates_batch(patterns[:16])
+    t0 = time.perf_counter()
+    words, status, st = ix.local_candidates_batch(patterns)
+    dt = time.perf_counter() - t0
+    same = True
+    for i in range(0, len(patterns), max(1, len(patterns) // 40)):
+        try:
+            one, _ = ix.local_candidates(patterns[i])
+            same = same and bool(status[i]) and bool((one == words[i]).all())
+        except sharded.HostError:
+            same = same and not status[i]
+    out["motif_file_filter_batch"] = {
+        "patterns": len(patterns), "answered": int(status.sum()), "patterns_per_s": len(patterns) / dt,
+        "us_per_pattern": dt / len(patterns) * 1e6, "kmers_probed_by_the_pruned_walks": int(st[:, 0].sum()),
+        "equals_one_pattern_at_a_time_on_a_sample": same,
+        "what": "process_query for all patterns of a motif file (-a -g): dry runs of the k-graph walks, one membership batch "
+                "for the union of their k-mers, the walks on host words"}
     ix.attach_dgram(None)
     ix.set_augment(False)
     for r in (res_no, res_g):

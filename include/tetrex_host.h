@@ -61,6 +61,13 @@ typedef void (*trxh_alive_fn)(uint8_t *alive, uint64_t n, void *user);
  * stats (nullable, 3 entries): k-mers probed, ranks visited, collector items. */
 int trxh_process_query(void *handle, const char *regex, trxh_alive_fn alive, void *user, uint64_t *out_words, uint64_t *stats);
 
+/* process_query for n patterns at once — the filter phase of `tetrex query -f FILE` (src/query.cpp:463-466 loops over the
+ * motifs and calls run_collection for each): the k-mers of ALL patterns' k-graphs go to the device in one membership
+ * batch, every walk then runs on host words.  out_words: n x bin_words; status[i] = 1 answered / 0 the pattern was
+ * refused (what trxh_process_query reports as an error); stats (nullable): n x 3. */
+int trxh_process_query_batch(void *handle, const char *const *regexes, uint64_t n, uint64_t *out_words, uint8_t *status,
+                             uint64_t *stats);
+
 /* iter_disk_search over the shard's own bins: the reference's output lines, in its -t 1 order, as one malloc'ed buffer
  * (trxh_free).  cand_words: bin_words words (bits of other shards' bins are ignored). */
 int trxh_verify(void *handle, const uint64_t *cand_words, const char *regex, char **out_text, uint64_t *out_len, uint64_t *n_lines);

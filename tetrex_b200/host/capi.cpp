@@ -238,6 +238,36 @@ int trxh_process_query(void * hv, const char * regex, trxh_alive_fn alive, void 
     });
 }
 
+// process_query for n patterns with ONE membership batch for all their k-mers (what `tetrex query -f` does for its motif
+// file).  out_words: n x bin_words; status[i] = 1 answered, 0 = process_query would have thrown for that pattern (its words
+// are zero); stats (nullable): n x 3 like trxh_process_query.
+int trxh_process_query_batch(void * hv, const char * const * regexes, uint64_t n, uint64_t * out_words, uint8_t * status, uint64_t * stats)
+{
+    return guarded([&] {
+        auto * h = static_cast<handle *>(hv);
+        auto & ix = h->index;
+        std::vector<std::string> patterns(regexes, regexes + n);
+        std::vector<trxh::batch_answer> got = trxh::process_query_batch(patterns, ix, h->augment);
+        uint64_t const words = ix.bin_words(), bins = ix.bin_count();
+        for (uint64_t i = 0; i < n; ++i)
+        {
+            status[i] = got[i].ok ? 1 : 0;
+            for (uint64_t w = 0; w < words; ++w)
+            {
+                uint64_t const first = w * 64;
+                uint64_t const mask = bins >= first + 64 ? ~0ull : (bins > first ? (1ull << (bins - first)) - 1 : 0);
+                out_words[i * words + w] = got[i].ok && w < got[i].bins.size() ? got[i].bins[w] & mask : 0;
+            }
+            if (stats)
+            {
+                stats[3 * i + 0] = got[i].stats.probes;
+                stats[3 * i + 1] = got[i].stats.ranks;
+                stats[3 * i + 2] = got[i].stats.items;
+            }
+        }
+    });
+}
+
 // iter_disk_search (include/query.h:97-188) over this shard's bins; the lines come back as one malloc'ed buffer
 // (free with trxh_free).
 int trxh_verify(void * hv, const uint64_t * cand_words, const char * regex, char ** out_text, uint64_t * out_len, uint64_t * n_lines)

@@ -226,14 +226,16 @@ struct recording_paths
 // (`path_ &= ibf_->query(kmer)`, `path_ |= other.path_`, `path_.none()`), no device round trip per rank
 struct host_paths
 {
+    using row_map = std::unordered_map<uint64_t, uint32_t>;
     uint64_t W;
-    recording_paths const & known;
-    std::vector<uint64_t> const & kmer_rows; // known.kmers.size() x W
+    row_map const & kmer_row; // k-mer → row of kmer_rows (W words each)
+    row_map const & code_row;
+    std::vector<uint64_t> const & kmer_rows;
     std::vector<uint64_t> const & code_rows;
     std::vector<uint64_t> words;
     uint32_t slots{0};
-    host_paths(uint64_t w, recording_paths const & k, std::vector<uint64_t> const & kr, std::vector<uint64_t> const & cr)
-        : W(w), known(k), kmer_rows(kr), code_rows(cr)
+    host_paths(uint64_t w, row_map const & km, row_map const & cm, std::vector<uint64_t> const & kr, std::vector<uint64_t> const & cr)
+        : W(w), kmer_row(km), code_row(cm), kmer_rows(kr), code_rows(cr)
     {
         words.reserve(64 * W);
     }
@@ -262,11 +264,11 @@ struct host_paths
     }
     void step(std::vector<uint64_t> const & in, std::vector<uint32_t> const & sl, std::vector<uint8_t> & res)
     {
-        and_rows(in, sl, res, known.kmer_row, kmer_rows);
+        and_rows(in, sl, res, kmer_row, kmer_rows);
     }
     void step_dgram(std::vector<uint64_t> const & in, std::vector<uint32_t> const & sl, std::vector<uint8_t> & res)
     {
-        and_rows(in, sl, res, known.code_row, code_rows);
+        and_rows(in, sl, res, code_row, code_rows);
     }
     void or_pairs(std::vector<uint32_t> const & dst, std::vector<uint32_t> const & src)
     {
@@ -524,7 +526,7 @@ bitvector collect(kgraph const & g, DeviceIndex & index, collect_stats * stats, 
             }
             if (!rec.codes.empty())
                 check(trx_bulk_contains(index.dgram()->flat(), rec.codes.data(), rec.codes.size(), code_rows.data()));
-            host_paths hp(W, rec, kmer_rows, code_rows);
+            host_paths hp(W, rec.kmer_row, rec.code_row, kmer_rows, code_rows);
             uint32_t const match_slot = walk(g, index, stats, hp, bins);
             bitvector out(index.bin_words(), 0);
             std::copy(hp.words.begin() + static_cast<size_t>(match_slot) * W, hp.words.begin() + static_cast<size_t>(match_slot + 1) * W,
@@ -545,6 +547,134 @@ bitvector collect(kgraph const & g, DeviceIndex & index, collect_stats * stats, 
     }
     return out;
 }
+
+namespace
+{
+kgraph graph_of(std::string const & regex, DeviceIndex & index, bool augment);
+}
+
+// process_query for a list of patterns (`-f`): every pattern's k-graph gets its dry run, the k-mers of ALL of them go to the
+// device in one membership batch (in pieces of at most kBatchRowBytes of rows), and each walk then runs on host words.
+// Patterns whose graph is over the dry run's budget, and column shards, take process_query one at a time.
+std::vector<batch_answer> process_query_batch(std::vector<std::string> const & regexes, DeviceIndex & index, bool augment)
+{
+    constexpr uint64_t kBatchRowBytes = 128ull << 20;
+    std::vector<batch_answer> out(regexes.size());
+    bool const sharded = !index.is_hibf() && index.shard_count() > 1;
+    char const * const spec_env = getenv("TRX_COLLECT_SPECULATIVE");
+    bool const one_by_one = sharded || (spec_env && std::string(spec_env) == "off");
+    uint64_t const W = index.path_words();
+    uint64_t const bins = index.bin_count();
+    struct waiting
+    {
+        size_t pattern;
+        kgraph g;
+    };
+    std::vector<waiting> group;
+    host_paths::row_map kmer_row, code_row;
+    std::vector<uint64_t> kmers, codes;
+    auto answer_alone = [&](size_t i) {
+        try
+        {
+            out[i].bins = process_query(regexes[i], index, &out[i].stats, nullptr, augment);
+            out[i].ok = true;
+        }
+        catch (std::exception const & e)
+        {
+            out[i].error = e.what();
+        }
+    };
+    auto flush = [&] {
+        if (group.empty())
+            return;
+        std::vector<uint64_t> kmer_rows(kmers.size() * W), code_rows(codes.size() * W);
+        if (!kmers.empty())
+        {
+            if (index.is_hibf())
+                check(trx_hibf_membership(index.hibf(), kmers.data(), kmers.size(), kmer_rows.data(), nullptr));
+            else
+                check(trx_bulk_contains(index.flat(), kmers.data(), kmers.size(), kmer_rows.data()));
+        }
+        if (!codes.empty())
+            check(trx_bulk_contains(index.dgram()->flat(), codes.data(), codes.size(), code_rows.data()));
+        for (waiting const & w : group)
+        {
+            try
+            {
+                host_paths hp(W, kmer_row, code_row, kmer_rows, code_rows);
+                uint32_t const match_slot = walk(w.g, index, &out[w.pattern].stats, hp, bins);
+                out[w.pattern].bins.assign(hp.words.begin() + static_cast<size_t>(match_slot) * W,
+                                           hp.words.begin() + static_cast<size_t>(match_slot + 1) * W);
+                out[w.pattern].ok = true;
+            }
+            catch (std::exception const & e)
+            {
+                out[w.pattern].error = e.what();
+            }
+        }
+        group.clear();
+        kmer_row.clear();
+        code_row.clear();
+        kmers.clear();
+        codes.clear();
+    };
+    for (size_t i = 0; i < regexes.size(); ++i)
+    {
+        if (one_by_one)
+        {
+            answer_alone(i);
+            continue;
+        }
+        try
+        {
+            kgraph g = graph_of(regexes[i], index, augment);
+            recording_paths rec;
+            try
+            {
+                walk(g, index, nullptr, rec, bins);
+            }
+            catch (budget_exceeded const &)
+            {
+                answer_alone(i);
+                continue;
+            }
+            for (uint64_t v : rec.kmers)
+                if (kmer_row.emplace(v, static_cast<uint32_t>(kmers.size())).second)
+                    kmers.push_back(v);
+            for (uint64_t v : rec.codes)
+                if (code_row.emplace(v, static_cast<uint32_t>(codes.size())).second)
+                    codes.push_back(v);
+            group.push_back(waiting{i, std::move(g)});
+            if ((kmers.size() + codes.size()) * W * 8 >= kBatchRowBytes)
+                flush();
+        }
+        catch (std::exception const & e)
+        {
+            out[i].error = e.what();
+        }
+    }
+    flush();
+    return out;
+}
+
+namespace
+{
+kgraph graph_of(std::string const & regex, DeviceIndex & index, bool augment)
+{
+    std::string rx = regex;
+    if (!index.is_dna())
+    {
+        if (index.reduction() > 0)
+            rx = reduce_query_alphabet(rx, index.redmap());
+        rx = trim_regex(rx);
+    }
+    std::string postfix = translate(rx);
+    kgraph g = construct_kgraph(postfix, index.k(), index.reduction() != TRX_RED_BASE);
+    if (augment)
+        g.augment();
+    return g;
+}
+} // namespace
 
 bitvector process_query(std::string const & regex, DeviceIndex & index, collect_stats * stats, shard_hooks const * hooks,
                         bool augment)

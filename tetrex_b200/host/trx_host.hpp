@@ -354,6 +354,17 @@ bitvector process_query(std::string const & regex, DeviceIndex & index, collect_
 // the collector alone on a ready k-graph (OTFCollector::collect, include/otf_collector.h:341-393)
 bitvector collect(kgraph const & g, DeviceIndex & index, collect_stats * stats = nullptr, shard_hooks const * hooks = nullptr);
 
+// process_query for a whole motif file (`tetrex query -f`): one membership batch for the k-mers of all patterns.  Per
+// pattern: the candidate bins (bin_words() words), or the text of the exception process_query would have thrown.
+struct batch_answer
+{
+    bool ok{false};
+    bitvector bins;
+    collect_stats stats{};
+    std::string error;
+};
+std::vector<batch_answer> process_query_batch(std::vector<std::string> const & regexes, DeviceIndex & index, bool augment = false);
+
 // iter_disk_search (include/query.h:97-188): verifies the candidate bins on the device (K4) and writes the
 // reference's lines "bin_path\t>name\tmatch\tstart,end\n" (+ "…\tREVERSE STRAND HIT" for DNA) to `dest`
 // ("-" = stdout).  Returns the number of lines written.

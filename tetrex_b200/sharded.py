@@ -46,6 +46,7 @@ def host_lib():
         h.trxh_info.argtypes = [vp, u64p]
         h.trxh_process_query.argtypes = [vp, C.c_char_p, _ALIVE_FN, vp, u64p, u64p]
         h.trxh_verify.argtypes = [vp, u64p, C.c_char_p, C.POINTER(C.c_void_p), u64p, u64p]
+        h.trxh_process_query_batch.argtypes = [vp, C.POINTER(C.c_char_p), C.c_uint64, u64p, C.POINTER(C.c_uint8), u64p]
         h.trxh_free.argtypes = [vp]
         h.trxh_free.restype = None
         h.trxh_attach_comm.argtypes = [vp, vp]
@@ -133,6 +134,19 @@ class ShardedIndex:
         _check(host_lib().trxh_process_query(self._h, regex.encode(), cb, None, words.ctypes.data_as(C.POINTER(C.c_uint64)),
                                              stats.ctypes.data_as(C.POINTER(C.c_uint64))))
         return words, dict(zip(("probes", "ranks", "items"), map(int, stats)))
+
+    def local_candidates_batch(self, regexes):
+        """process_query for a list of patterns with one membership batch for all their k-mers (`tetrex query -f`):
+        (n x bin_words words, n status bytes — 0 where the pattern was refused —, n x 3 stats)."""
+        n = len(regexes)
+        words = np.zeros((n, self.bin_words), dtype=np.uint64)
+        status = np.zeros(n, dtype=np.uint8)
+        stats = np.zeros((n, 3), dtype=np.uint64)
+        arr = (C.c_char_p * max(n, 1))(*[r.encode() for r in regexes])
+        _check(host_lib().trxh_process_query_batch(self._h, arr, n, words.ctypes.data_as(C.POINTER(C.c_uint64)),
+                                                   status.ctypes.data_as(C.POINTER(C.c_uint8)),
+                                                   stats.ctypes.data_as(C.POINTER(C.c_uint64))))
+        return words, status, stats
 
     def verify_local(self, candidate_words, regex: str) -> tuple[str, int]:
         """iter_disk_search over the shard's own bins: (lines in print order, line count)."""
