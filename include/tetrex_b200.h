@@ -269,7 +269,7 @@ void trx_text_destroy(trx_text_t *t);
  * literals, '.', [..] / [^..] without ranges, ( ) | * + ? {m} {m,n}, backslash escapes.  Anything
  * else, more than TRX_REGEX_MAX_POSITIONS symbol positions after {m,n} expansion, or a pattern that
  * matches the empty string (the reference spins forever on those) → TRX_EREGEX. */
-#define TRX_REGEX_MAX_POSITIONS 128
+#define TRX_REGEX_MAX_POSITIONS 250
 int trx_regex_compile(const char *pattern, int posix_longest, trx_regex_t **out);
 void trx_regex_destroy(trx_regex_t *re);
 int trx_regex_positions(const trx_regex_t *re);

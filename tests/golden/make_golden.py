@@ -98,6 +98,53 @@ def golden_regex():
     json.dump(cases, open(os.path.join(OUT, "regex.json"), "w"))
 
 
+REGEX_WIDE = [  # (pattern, posix, alphabet): 129..250 symbol positions after {m,n} expansion
+    ("M.{30,80}W.{20,60}K", True, b"ACDEGKLMNPQRSTW"), ("C.{10,50}C.{10,50}H.{5,40}H", True, b"ACDEGHKLMN"),
+    ("A{130}", True, b"AAAC"), ("(AC|GT){70}", True, b"ACGT"), ("[ACD]{100}E.{0,99}F", True, b"ACDEF"),
+    ("L.{100,200}L", True, b"ACDEGKLMNPQRSTW"), ("G.{249}", True, b"ACDEG"), ("^M.{130}", True, b"ACDEGKLM"),
+    (".{140}K$", True, b"ACDEGK"), ("W(AC|DE|KL){20,60}W", True, b"ACDEKLW"), ("ACGT.{100,150}TTGA", False, b"ACGT"),
+    ("T(A|AC|ACG){30}T", False, b"ACGT"), ("(A|C)+G{130}", False, b"ACG"), ("GA.{0,200}?TC", False, b"ACGT"),
+    ("C.{10,50}C.{10,50}H.{5,40}H", False, b"ACDEGHKLMN"), ("N[ACGT]{128}N", False, b"ACGTN"),
+]
+
+
+def golden_regex_wide():
+    """RE2's FindAndConsume sequence (the reference's own RE2, oracle/_ref) for patterns of 129..250 positions."""
+    rng = random.Random(17)
+    cases = []
+    for pat, posix, alpha in REGEX_WIDE:
+        for L in [0, 90, 300, 2500]:
+            text = bytearray(rand_seq(rng, alpha, L))
+            if pat == "A{130}" and L >= 300:
+                text[40:40 + 135] = b"A" * 135
+                text[200:200 + 90] = b"A" * 90
+            if pat == "(A|C)+G{130}" and L >= 300:
+                text[100:100 + 140] = b"G" * 140
+            if pat == "(AC|GT){70}" and L >= 300:
+                text[30:30 + 150] = (b"ACGTGT" * 30)[:150]
+            if pat == "[ACD]{100}E.{0,99}F" and L >= 300:
+                for i in range(20, 125):
+                    text[i] = rng.choice(b"ACD")
+                text[125] = ord("E")
+            if pat == "N[ACGT]{128}N" and L >= 300:
+                for i in range(50, 260):
+                    if text[i] == ord("N"):
+                        text[i] = ord("A")
+                text[60] = text[60 + 129] = ord("N")
+            if pat == "W(AC|DE|KL){20,60}W" and L >= 300:
+                text[10:10 + 62] = b"W" + b"ACDEKL" * 10 + b"W"
+            if pat == "T(A|AC|ACG){30}T" and L >= 300:
+                text[70:70 + 62] = b"T" + b"AC" * 30 + b"T"
+            text = bytes(text)
+            try:
+                m = ob.ref_find_all(pat, posix, text)
+            except ValueError:
+                continue
+            cases.append(dict(pattern=pat, posix=posix, text=text.decode(), matches=m))
+    json.dump(cases, open(os.path.join(OUT, "regex_wide.json"), "w"))
+    print(len(cases), "cases,", sum(len(c["matches"]) for c in cases), "matches;", sum(1 for c in cases if c["matches"]), "non-empty")
+
+
 def golden_kgraph():
     """k-graphs of the reference (node symbols, two-slot arc map, ranks) for the host layer's construct_kgraph."""
     cases = []
@@ -742,7 +789,7 @@ def golden_rh_order():
     print("rh_order.json:", len(cases), "cases")
 
 
-STEPS = {"decompose": golden_decompose, "ibf": golden_ibf, "hibf": golden_hibf, "regex": golden_regex,
+STEPS = {"decompose": golden_decompose, "ibf": golden_ibf, "hibf": golden_hibf, "regex": golden_regex, "regex_wide": golden_regex_wide,
          "kgraph": golden_kgraph, "cli": golden_cli, "c1": golden_c1, "collector_fuzz": golden_collector_fuzz, "rh_order": golden_rh_order,
          "prosite_batch": golden_prosite_batch, "c2_twin_hibf": golden_c2_twin_hibf, "cli_ws": golden_cli_ws, "prosite_filter": golden_prosite_filter, "cli_conj": golden_cli_conj, "dgram": golden_dgram, "kgraph_aug": golden_kgraph_aug, "hibf_layout": golden_hibf_layout}
 

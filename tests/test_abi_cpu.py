@@ -63,7 +63,11 @@ def test_regex_compile_errors_and_positions():
     assert t.Regex("LMA(E|Q)GLYN", True).positions == 9
     assert t.Regex("G.{2,4}K", True).positions == 6
     assert t.Regex("A(C+|G+)T", False).positions == 4
-    for bad in ["A*", "(A|)", "", "A(", "A)", "[AB", "A{3,2}", "A**", "\\d+", "A{2", "(?i)A", "x" * 129, "A{200}"]:
+    # up to 250 positions (one, two or four 64-bit words of automaton state)
+    assert t.Regex("x" * 129, True).positions == 129
+    assert t.Regex("M.{30,80}W.{20,60}K", True).positions == 143
+    assert t.Regex("G.{249}", False).positions == 250
+    for bad in ["A*", "(A|)", "", "A(", "A)", "[AB", "A{3,2}", "A**", "\\d+", "A{2", "(?i)A", "x" * 251, "A{251}", "(AC){126}", "G.{10,250}"]:
         with pytest.raises(t.TetrexError) as e:
             t.Regex(bad, True)
         assert e.value.code == -6, bad

@@ -51,6 +51,42 @@ def test_regex_golden_vectors(ctx, golden_dir):
         txt.close()
 
 
+def test_regex_wide_patterns_equal_re2(ctx, golden_dir, monkeypatch):
+    """Patterns of 129..250 symbol positions (`.{30,80}`-style PROSITE gaps; four 64-bit words of automaton state, the
+    W = 4 instantiations of the scan kernels) against the reference's own RE2 (tests/golden/regex_wide.json, written by
+    make_golden.py regex_wide): single scans with and without prefilter, and the same patterns through one
+    multi-pattern call together with narrow ones.  What does not compile is over 250 positions or non-greedy."""
+    cases = json.load(open(os.path.join(golden_dir, "regex_wide.json")))
+    groups = {}
+    for c in cases:
+        groups.setdefault((c["pattern"], c["posix"]), []).append(c)
+    done = 0
+    for (pat, posix), cs in groups.items():
+        try:
+            rx = t.Regex(pat, posix)
+        except t.TetrexError as e:
+            assert "250 symbol positions" in str(e) or "non-greedy" in str(e), (pat, str(e))
+            continue
+        assert 128 < rx.positions <= 250, pat
+        seqs = [c["text"].encode() for c in cs]
+        rec_bin = list(range(len(seqs)))
+        txt = build_text(ctx, seqs, rec_bin, len(seqs))
+        want = [[rec_bin[r], r, a, b] for r, c in enumerate(cs) for a, b in c["matches"]]
+        assert txt.scan(rx).tolist() == want, (pat, posix)
+        monkeypatch.setenv("TRX_REGEX_FILTER", "off")
+        assert txt.scan(rx).tolist() == want, (pat, posix, "no prefilter")
+        monkeypatch.delenv("TRX_REGEX_FILTER")
+        if posix:
+            narrow = [t.Regex(p, True) for p in ("K", "[CH].{2}[LM]")]
+            multi = txt.scan_multi([narrow[0], rx, narrow[1]], cap=1 << 18)
+            assert multi[1].tolist() == want, (pat, "multi")
+            for g, nrx in zip((multi[0], multi[2]), narrow):
+                assert np.array_equal(g, txt.scan(nrx, cap=1 << 18)), pat
+        txt.close()
+        done += 1
+    assert done >= 12
+
+
 PATTERNS_AA = ["LMA(E|Q)GLYN", "[ILV][ILV]K", "G.{2,4}K", "N[ST][^P]", "(AB|A)BC", "K+R?E", "C.{0,3}C", "W(A|C|D){1,3}W",
                "^M", "K$", "(GA)+G", "A{3,5}", "[DE]{2}.[KR]{2}", "(A|AA)(A|AA)C"]
 PATTERNS_NA = ["A(C+|G+)T", "ACGT", "(A|AC)(CG|G)", "T+A", "G.{1,3}C", "(AC)*G", "CA?T", "[AG]C[CT]", "A{2,4}C", "(TA|T)A+",

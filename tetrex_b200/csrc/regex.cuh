@@ -1,7 +1,8 @@
 // regex.cuh — compiled form of a verify regex shared by the host compiler and the K4 scan kernels.
 //
 // The automaton is the Glushkov (position) automaton of the pattern: one state per symbol position
-// after {m,n} expansion, at most TRX_REGEX_MAX_POSITIONS = 128 → two 64-bit words of state.  All
+// after {m,n} expansion, at most TRX_REGEX_MAX_POSITIONS = 250 → one, two or four 64-bit words of state (the kernels are
+// instantiated per width; position ids are bytes and 0xFF is ACCEPT, hence 250 and not 256).  All
 // transitions into position i carry the same symbol class, so one step is
 //      S' = (Follow(S) | inject·First) & B[c]          match ends here  ⇔  S' & Last ≠ 0
 // which is the whole inner loop of the streaming pass.  For leftmost-first (Perl/RE2 default)
@@ -16,7 +17,7 @@
 namespace trx
 {
 
-constexpr int kRegexWords = 2; // 128 positions
+constexpr int kRegexWords = 4; // room for 256 positions
 constexpr uint8_t kAccept = 0xFF;
 
 struct regex_masks

@@ -134,7 +134,8 @@ private:
         size_t const per = count_positions(atom.get());
         size_t const copies = static_cast<size_t>(hi < 0 ? (lo > 0 ? lo : 1) : hi);
         if (per * copies > TRX_REGEX_MAX_POSITIONS)
-            throw parse_error("pattern needs more than 128 symbol positions after {m,n} expansion");
+            throw parse_error("pattern needs more than " + std::to_string(TRX_REGEX_MAX_POSITIONS) +
+                              " symbol positions after {m,n} expansion");
         // x{lo,hi} = x^lo (x(x(x)?)?)?   — the nesting RE2's simplifier produces (lib/re2/re2/simplify.cc)
         node_p out;
         auto append = [&](node_p n) { out = out ? mk(nk::cat, std::move(out), std::move(n)) : std::move(n); };
@@ -471,7 +472,7 @@ int trx_regex_compile(const char * pattern, int posix_longest, trx_regex_t ** ou
     static std::atomic<uint64_t> next_serial{1};
     re->serial = next_serial.fetch_add(1);
     re->positions = m;
-    re->words = m <= 64 ? 1 : 2;
+    re->words = m <= 64 ? 1 : (m <= 128 ? 2 : 4);
     re->posix_longest = posix_longest != 0;
     re->anchor_begin = anchor_begin;
     re->anchor_end = anchor_end;
@@ -532,10 +533,10 @@ int64_t trx_regex_first_match_end(const trx_regex_t * re, const uint8_t * text, 
     if (!re || (!text && len))
         return -1;
     trx::regex_masks const & m = re->masks;
-    uint64_t s[trx::kRegexWords] = {0, 0};
+    uint64_t s[trx::kRegexWords] = {};
     for (uint64_t i = 0; i < len; ++i)
     {
-        uint64_t nx[trx::kRegexWords] = {0, 0};
+        uint64_t nx[trx::kRegexWords] = {};
         for (int w = 0; w < trx::kRegexWords; ++w)
         {
             uint64_t bits = s[w];

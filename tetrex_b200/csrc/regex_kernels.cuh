@@ -132,10 +132,11 @@ struct state
     uint64_t w[W];
     __device__ __forceinline__ bool any() const
     {
-        if constexpr (W == 1)
-            return w[0] != 0;
-        else
-            return (w[0] | w[1]) != 0;
+        uint64_t x = w[0];
+#pragma unroll
+        for (int k = 1; k < W; ++k)
+            x |= w[k];
+        return x != 0;
     }
 };
 
@@ -193,10 +194,11 @@ __device__ __forceinline__ void step(state<W> & S, scan_tables<W> const & T, uin
 template <int W>
 __device__ __forceinline__ bool accepts(state<W> const & S, scan_tables<W> const & T)
 {
-    if constexpr (W == 1)
-        return (S.w[0] & T.last[0]) != 0;
-    else
-        return ((S.w[0] & T.last[0]) | (S.w[1] & T.last[1])) != 0;
+    uint64_t x = S.w[0] & T.last[0];
+#pragma unroll
+    for (int k = 1; k < W; ++k)
+        x |= S.w[k] & T.last[k];
+    return x != 0;
 }
 
 __device__ __forceinline__ uint32_t smem_u32(void const * p)
@@ -727,7 +729,7 @@ __device__ int64_t match_first(regex_dev const & re, At at, int64_t s, int64_t L
     for (int64_t pos = s; pos < L && ncur > 0; ++pos)
     {
         uint8_t const c = at(pos);
-        uint64_t in_next[kRegexWords] = {0, 0};
+        uint64_t in_next[kRegexWords] = {};
         int nn = 0;
         bool cut = false;
         for (int t = 0; t < ncur && !cut; ++t)

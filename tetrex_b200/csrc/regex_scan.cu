@@ -448,11 +448,23 @@ void complement_table(uint8_t tab[256])
 constexpr double kDefaultMaxPass = 1e-3;
 constexpr double kMaxSimdPass = 2e-2; // admission of the gapped prefilter's SIMD stage when confirm checks follow
 
-struct bits128
+struct bits128 // a set of positions (the name is from the days of two words)
 {
-    uint64_t w[2]{0, 0};
-    bool any() const { return (w[0] | w[1]) != 0; }
-    bool intersects(uint64_t const * o) const { return ((w[0] & o[0]) | (w[1] & o[1])) != 0; }
+    uint64_t w[kRegexWords]{};
+    bool any() const
+    {
+        uint64_t x = 0;
+        for (int k = 0; k < kRegexWords; ++k)
+            x |= w[k];
+        return x != 0;
+    }
+    bool intersects(uint64_t const * o) const
+    {
+        uint64_t x = 0;
+        for (int k = 0; k < kRegexWords; ++k)
+            x |= w[k] & o[k];
+        return x != 0;
+    }
 };
 
 // Derives the necessary factor of filter_spec from the automaton's level sets: L_0 = First,
@@ -481,8 +493,8 @@ filter_spec derive_filter(regex_dev const & img, double const * freq, bool rever
     int literal[kMaxDepth];
     int depths = 0;
     bits128 L;
-    L.w[0] = img.first[0];
-    L.w[1] = img.first[1];
+    for (int k = 0; k < kRegexWords; ++k)
+        L.w[k] = img.first[k];
     for (; depths < kMaxDepth && L.any(); ++depths)
     {
         int count = 0, byte = -1;
@@ -499,12 +511,12 @@ filter_spec derive_filter(regex_dev const & img, double const * freq, bool rever
             break;
         }
         bits128 next;
-        for (int k = 0; k < 2; ++k)
+        for (int k = 0; k < kRegexWords; ++k)
             for (uint64_t s = L.w[k]; s; s &= s - 1)
             {
                 int pos = k * 64 + __builtin_ctzll(s);
-                next.w[0] |= img.follow[pos][0];
-                next.w[1] |= img.follow[pos][1];
+                for (int j = 0; j < kRegexWords; ++j)
+                    next.w[j] |= img.follow[pos][j];
             }
         L = next;
     }
@@ -1018,7 +1030,7 @@ void build_reverse_dfa(regex_dev const & img, std::vector<std::pair<uint64_t, ui
 {
     out.r_usable = false;
     out.r_trans.clear();
-    if (img.anchor_begin || img.anchor_end)
+    if (img.anchor_begin || img.anchor_end || img.positions > 128) // subsets are kept as two words here
         return;
     int const n = img.positions;
     // longest match = longest path first → last in the follow graph; a cycle means unbounded
@@ -1125,7 +1137,7 @@ void build_dfa(regex_dev const & img, dfa_table & out)
 {
     out.usable = false;
     out.trans.clear();
-    if (!img.posix_longest)
+    if (!img.posix_longest || img.positions > 128) // subsets are kept as two words here; wider patterns run the position automaton
         return;
     // byte classes
     std::vector<std::pair<uint64_t, uint64_t>> cols; // class → column
@@ -1395,7 +1407,7 @@ static int scan_begin_impl(trx_text_t * t, trx_regex_t * re, const uint64_t * ca
 
     t_plan = now();
     // ---- one pinned staging block: [candidate words | automaton image], one H2D copy
-    static_assert(sizeof(regex_dev) < 16384, "regex_dev grew unexpectedly");
+    static_assert(sizeof(regex_dev) < 24576, "regex_dev grew unexpectedly");
     size_t const off_cand = 0;
     size_t const off_regex = align16(off_cand + cand_words * 8);
     size_t const off_dfa = align16(off_regex + sizeof(regex_dev)); // [256 class bytes | transitions] when there is a DFA
@@ -1538,6 +1550,8 @@ static int scan_begin_impl(trx_text_t * t, trx_regex_t * re, const uint64_t * ca
         TRX_TRY(launch_atoms_any(c, st, sp, t->tmap));
     else if (use_window)
         TRX_TRY(launch_filter_any(c, st, sp, t->tmap));
+    else if (re->words > 2)
+        TRX_TRY(launch_phase1_w<4>(c, st, sp, t->tmap, reverse, use_tma));
     else if (re->words == 1)
         TRX_TRY(launch_phase1_w<1>(c, st, sp, t->tmap, reverse, use_tma));
     else
@@ -1589,6 +1603,8 @@ static int scan_begin_impl(trx_text_t * t, trx_regex_t * re, const uint64_t * ca
         ++c->launches;
         TRX_CUDA(cudaGetLastError());
     }
+    else if (re->words > 2)
+        TRX_TRY(launch_phase2_w<4>(c, st, rp, reverse));
     else if (re->words == 1)
         TRX_TRY(launch_phase2_w<1>(c, st, rp, reverse));
     else
@@ -2637,7 +2653,13 @@ int trx_regex_scan_multi(trx_text_t * t, trx_regex_t * const * regexes, uint32_t
                 dyn_smem = std::max(dyn_smem, dfa_smem_bytes(dfas[k]->n_states, dfas[k]->n_classes));
         // CTAs beyond a pattern's record list leave at once: the grid is sized for the longest lists (tens of thousands of
         // records), which otherwise sit on 128 warps long after the other patterns are done
-        regex_scan_phase2_multi<2, 1><<<dim3(window_mode ? 128 : 32, nb), 128, dyn_smem, st>>>(reinterpret_cast<resolve_params const *>(ds + off_rp));
+        bool wide = false; // a pattern of more than 128 positions in the batch: the four-word resolver for all of it
+        for (uint32_t k = 0; k < nb; ++k)
+            wide = wide || regexes[ids[k]]->words > 2;
+        if (wide)
+            regex_scan_phase2_multi<4, 1><<<dim3(window_mode ? 128 : 32, nb), 128, dyn_smem, st>>>(reinterpret_cast<resolve_params const *>(ds + off_rp));
+        else
+            regex_scan_phase2_multi<2, 1><<<dim3(window_mode ? 128 : 32, nb), 128, dyn_smem, st>>>(reinterpret_cast<resolve_params const *>(ds + off_rp));
         ++c->launches;
         TRX_CUDA(cudaGetLastError());
 
