@@ -59,6 +59,9 @@ struct trx_ctx
     // second stream + events for the host-buffer entry points that overlap result copies with compute
     cudaStream_t copy_stream{nullptr};
     std::vector<cudaEvent_t> copy_events;
+    // third stream: the k-mers of piece n + 1 arrive while piece n is computed and piece n - 1 leaves (PCIe is full duplex)
+    cudaStream_t in_stream{nullptr};
+    std::vector<cudaEvent_t> in_events;
     // staging for the host-buffer entry points
     trx::scratch d_in[4];
     trx::scratch d_out[2];

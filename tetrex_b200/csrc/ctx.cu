@@ -134,6 +134,13 @@ void trx_ctx_destroy(trx_ctx_t * ctx)
         cudaStreamSynchronize(ctx->copy_stream);
         cudaStreamDestroy(ctx->copy_stream);
     }
+    for (cudaEvent_t e : ctx->in_events)
+        cudaEventDestroy(e);
+    if (ctx->in_stream)
+    {
+        cudaStreamSynchronize(ctx->in_stream);
+        cudaStreamDestroy(ctx->in_stream);
+    }
     if (ctx->owns_stream)
         cudaStreamDestroy(ctx->stream);
     delete ctx;

@@ -598,31 +598,39 @@ static constexpr int kMaxLevels = 30;
 // ---- sparse result: result rows → (count per k-mer, ascending user-bin ids) ---------------------------------------------
 constexpr int kIdsBlock = 256;
 
-// counts[i] = popcount of row i; block_tot[b] = ids of block b's k-mers
+// counts[i] = popcount of row i; block_tot[b] = ids of block b's kIdsBlock k-mers.  A group of 16 lanes takes one row at a
+// time, one word per lane and round: the rows are read in whole 128-byte lines (a thread per row read them 128 bytes apart).
+constexpr int kIdsGroup = 16;
 __global__ void __launch_bounds__(kIdsBlock) ids_count_kernel(uint64_t const * __restrict__ rows, uint64_t n, uint32_t W,
                                                                uint32_t * __restrict__ counts, unsigned long long * __restrict__ block_tot)
 {
-    __shared__ unsigned int s_warp[kIdsBlock / 32];
-    uint64_t const i = static_cast<uint64_t>(blockIdx.x) * kIdsBlock + threadIdx.x;
-    unsigned int cnt = 0;
-    if (i < n)
+    __shared__ unsigned int s_total;
+    if (threadIdx.x == 0)
+        s_total = 0;
+    __syncthreads();
+    unsigned const lane = threadIdx.x % kIdsGroup, group = threadIdx.x / kIdsGroup;
+    uint64_t const first = static_cast<uint64_t>(blockIdx.x) * kIdsBlock;
+    unsigned int mine = 0;
+    for (unsigned j = group; j < kIdsBlock; j += kIdsBlock / kIdsGroup)
     {
-        for (uint32_t w = 0; w < W; ++w)
-            cnt += __popcll(rows[i * W + w]);
-        counts[i] = cnt;
+        uint64_t const i = first + j;
+        unsigned int cnt = 0;
+        if (i < n)
+            for (uint32_t w = lane; w < W; w += kIdsGroup)
+                cnt += __popcll(rows[i * W + w]);
+        for (int o = kIdsGroup / 2; o > 0; o >>= 1)
+            cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+        if (lane == 0 && i < n)
+        {
+            counts[i] = cnt;
+            mine += cnt;
+        }
     }
-    for (int o = 16; o > 0; o >>= 1)
-        cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
-    if ((threadIdx.x & 31) == 0)
-        s_warp[threadIdx.x >> 5] = cnt;
+    if (mine)
+        atomicAdd(&s_total, mine);
     __syncthreads();
     if (threadIdx.x == 0)
-    {
-        unsigned long long t = 0;
-        for (int w = 0; w < kIdsBlock / 32; ++w)
-            t += s_warp[w];
-        block_tot[blockIdx.x] = t;
-    }
+        block_tot[blockIdx.x] = s_total;
 }
 
 // in place: block_tot[b] → ids before block b; block_tot[blocks] = all ids of the piece.  One CTA (≤ 4096 blocks per piece).
@@ -657,40 +665,64 @@ __global__ void __launch_bounds__(1024) ids_scan_blocks_kernel(unsigned long lon
 }
 
 // ids of k-mer i go to out[block base + ids of the block's earlier k-mers ...): a CTA-wide exclusive scan of the counts
+// (already there from ids_count_kernel), then a group of 16 lanes per row — a word per lane, the lanes' ids placed by a
+// prefix sum inside the group, so that a row's ids and the rows of a block leave as one contiguous run.
 template <class id_t>
 __global__ void __launch_bounds__(kIdsBlock) ids_write_kernel(uint64_t const * __restrict__ rows, uint64_t n, uint32_t W,
+                                                               uint32_t const * __restrict__ counts,
                                                                unsigned long long const * __restrict__ block_base, id_t * __restrict__ out)
 {
+    __shared__ unsigned int s_off[kIdsBlock];
     __shared__ unsigned int s_warp[kIdsBlock / 32];
-    uint64_t const i = static_cast<uint64_t>(blockIdx.x) * kIdsBlock + threadIdx.x;
-    unsigned int cnt = 0;
-    if (i < n)
-        for (uint32_t w = 0; w < W; ++w)
-            cnt += __popcll(rows[i * W + w]);
-    unsigned int incl = cnt;
-    unsigned const lane = threadIdx.x & 31;
-    for (int o = 1; o < 32; o <<= 1)
+    uint64_t const first = static_cast<uint64_t>(blockIdx.x) * kIdsBlock;
     {
-        unsigned int const v = __shfl_up_sync(0xffffffffu, incl, o);
-        if (lane >= static_cast<unsigned>(o))
-            incl += v;
-    }
-    if (lane == 31)
-        s_warp[threadIdx.x >> 5] = incl;
-    __syncthreads();
-    unsigned int warp_base = 0;
-    for (unsigned w = 0; w < (threadIdx.x >> 5); ++w)
-        warp_base += s_warp[w];
-    if (i >= n || cnt == 0)
-        return;
-    id_t * dst = out + block_base[blockIdx.x] + warp_base + (incl - cnt);
-    for (uint32_t w = 0; w < W; ++w)
-    {
-        uint64_t bits = rows[i * W + w];
-        while (bits)
+        uint64_t const i = first + threadIdx.x;
+        unsigned int const cnt = i < n ? counts[i] : 0;
+        unsigned int incl = cnt;
+        unsigned const wl = threadIdx.x & 31;
+        for (int o = 1; o < 32; o <<= 1)
         {
-            *dst++ = static_cast<id_t>(w * 64 + (__ffsll(static_cast<long long>(bits)) - 1));
-            bits &= bits - 1;
+            unsigned int const v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (wl >= static_cast<unsigned>(o))
+                incl += v;
+        }
+        if (wl == 31)
+            s_warp[threadIdx.x >> 5] = incl;
+        __syncthreads();
+        unsigned int warp_base = 0;
+        for (unsigned w = 0; w < (threadIdx.x >> 5); ++w)
+            warp_base += s_warp[w];
+        s_off[threadIdx.x] = warp_base + incl - cnt;
+    }
+    __syncthreads();
+    unsigned const lane = threadIdx.x % kIdsGroup, group = threadIdx.x / kIdsGroup;
+    unsigned const group_mask = 0xFFFFu << (threadIdx.x & 16); // the 16 lanes of this group inside the warp
+    id_t * const base = out + block_base[blockIdx.x];
+    for (unsigned j = group; j < kIdsBlock; j += kIdsBlock / kIdsGroup)
+    {
+        uint64_t const i = first + j;
+        if (i >= n)
+            break; // the whole group leaves together
+        unsigned int run = s_off[j];
+        for (uint32_t w0 = 0; w0 < W; w0 += kIdsGroup)
+        {
+            uint32_t const w = w0 + lane;
+            uint64_t bits = w < W ? rows[i * W + w] : 0;
+            unsigned int const cnt = __popcll(bits);
+            unsigned int incl = cnt;
+            for (int o = 1; o < kIdsGroup; o <<= 1)
+            {
+                unsigned int const v = __shfl_up_sync(group_mask, incl, o, kIdsGroup);
+                if (lane >= static_cast<unsigned>(o))
+                    incl += v;
+            }
+            id_t * dst = base + run + (incl - cnt);
+            while (bits)
+            {
+                *dst++ = static_cast<id_t>(w * 64 + (__ffsll(static_cast<long long>(bits)) - 1));
+                bits &= bits - 1;
+            }
+            run += __shfl_sync(group_mask, incl, kIdsGroup - 1, kIdsGroup);
         }
     }
 }
@@ -747,6 +779,39 @@ static int launch_fused(trx_hibf * h, uint64_t const * d_kmers, uint64_t n, uint
     ++c->launches;
     return TRX_OK;
 }
+
+namespace
+{
+// k-mers of a host batch reach the device piece by piece on the context's inbound stream; events[k] fires when piece k
+// is there.  Everything is enqueued at once: the copies run back to back at PCIe speed, compute of piece k waits for
+// events[k] only.
+int stage_kmers_in_pieces(trx_ctx * c, uint64_t * d_kmers, const uint64_t * kmers, uint64_t n, uint64_t piece, bool & staged)
+{
+    staged = n > piece;
+    if (!staged) // one piece (a query's handful of k-mers): in order on the compute stream, no second stream to wait for
+    {
+        TRX_CUDA(cudaMemcpyAsync(d_kmers, kmers, n * 8, cudaMemcpyHostToDevice, c->stream));
+        return TRX_OK;
+    }
+    TRX_CUDA(cudaStreamSynchronize(c->stream)); // d_kmers may still be read by work enqueued before this call
+    if (!c->in_stream)
+        TRX_CUDA(cudaStreamCreateWithFlags(&c->in_stream, cudaStreamNonBlocking));
+    size_t k = 0;
+    for (uint64_t done = 0; done < n; done += piece, ++k)
+    {
+        uint64_t const m = n - done < piece ? n - done : piece;
+        TRX_CUDA(cudaMemcpyAsync(d_kmers + done, kmers + done, m * 8, cudaMemcpyHostToDevice, c->in_stream));
+        if (k >= c->in_events.size())
+        {
+            cudaEvent_t e;
+            TRX_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            c->in_events.push_back(e);
+        }
+        TRX_CUDA(cudaEventRecord(c->in_events[k], c->in_stream));
+    }
+    return TRX_OK;
+}
+} // namespace
 
 extern "C"
 {
@@ -1194,7 +1259,11 @@ int trx_hibf_membership_ids(trx_hibf_t * h, const uint64_t * kmers, uint64_t n, 
         return TRX_OK;
     trx_ctx * c = h->ctx;
     TRX_TRY(c->use());
-    uint64_t const piece = 1ull << 20;
+    static uint64_t const piece = [] {
+        char const * e = getenv("TRX_IDS_PIECE"); // k-mers per piece of the pipeline (A/B)
+        uint64_t const v = e ? strtoull(e, nullptr, 10) : 0;
+        return v >= 1024 ? v : (1ull << 20);
+    }();
     uint64_t const W = h->out_words;
     TRX_TRY(h->d_kmers.reserve(n * 8));
     TRX_TRY(h->d_out.reserve(piece * W * 8 * 2)); // two pieces of rows: one being compacted while the next is computed
@@ -1208,7 +1277,8 @@ int trx_hibf_membership_ids(trx_hibf_t * h, const uint64_t * kmers, uint64_t n, 
     auto * d_counts = static_cast<uint32_t *>(h->d_id_counts.ptr);
     auto * d_ids = static_cast<uint8_t *>(h->d_ids.ptr);
     auto * h_totals = static_cast<unsigned long long *>(h->h_id_total.ptr);
-    TRX_CUDA(cudaMemcpyAsync(d_kmers, kmers, n * 8, cudaMemcpyHostToDevice, c->stream));
+    bool staged = false;
+    TRX_TRY(stage_kmers_in_pieces(c, d_kmers, kmers, n, piece, staged));
     if (!c->copy_stream)
         TRX_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
     uint64_t visited = 0, written = 0;
@@ -1218,6 +1288,8 @@ int trx_hibf_membership_ids(trx_hibf_t * h, const uint64_t * kmers, uint64_t n, 
         uint64_t const m = n - done < piece ? n - done : piece;
         uint64_t * const rows = d_rows + (k & 1) * piece * W;
         uint64_t st[2] = {0, 0};
+        if (staged)
+            TRX_CUDA(cudaStreamWaitEvent(c->stream, c->in_events[k], 0));
         TRX_TRY(trx_hibf_membership_dev(h, d_kmers + done, m, rows, st));
         visited += st[0];
         unsigned const blocks = static_cast<unsigned>((m + kIdsBlock - 1) / kIdsBlock);
@@ -1238,10 +1310,10 @@ int trx_hibf_membership_ids(trx_hibf_t * h, const uint64_t * kmers, uint64_t n, 
         if (piece_ids)
         {
             if (id_bytes == 2)
-                ids_write_kernel<uint16_t><<<blocks, kIdsBlock, 0, c->stream>>>(rows, m, static_cast<uint32_t>(W), d_block_tot,
+                ids_write_kernel<uint16_t><<<blocks, kIdsBlock, 0, c->stream>>>(rows, m, static_cast<uint32_t>(W), d_counts + done, d_block_tot,
                                                                                reinterpret_cast<uint16_t *>(d_ids) + written);
             else
-                ids_write_kernel<uint32_t><<<blocks, kIdsBlock, 0, c->stream>>>(rows, m, static_cast<uint32_t>(W), d_block_tot,
+                ids_write_kernel<uint32_t><<<blocks, kIdsBlock, 0, c->stream>>>(rows, m, static_cast<uint32_t>(W), d_counts + done, d_block_tot,
                                                                                reinterpret_cast<uint32_t *>(d_ids) + written);
             ++c->launches;
         }
@@ -1286,10 +1358,12 @@ int trx_hibf_membership(trx_hibf_t * h, const uint64_t * kmers, uint64_t n, uint
     TRX_TRY(h->d_out.reserve(n * h->out_words * 8));
     auto * d_kmers = static_cast<uint64_t *>(h->d_kmers.ptr);
     auto * d_out = static_cast<uint64_t *>(h->d_out.ptr);
-    TRX_CUDA(cudaMemcpyAsync(d_kmers, kmers, n * 8, cudaMemcpyHostToDevice, c->stream));
     // The result (out_words x 8 B per k-mer, 128 B at C2) dwarfs the input: it leaves in pieces on a second stream
-    // while the next piece is being computed, so the call costs about max(compute, PCIe) instead of their sum.
+    // while the next piece is being computed, so the call costs about max(compute, PCIe) instead of their sum; the k-mers
+    // arrive piece by piece on a third.
     uint64_t const piece = 1ull << 20;
+    bool staged = false;
+    TRX_TRY(stage_kmers_in_pieces(c, d_kmers, kmers, n, piece, staged));
     if (!c->copy_stream)
         TRX_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
     uint64_t visited = 0;
@@ -1298,6 +1372,8 @@ int trx_hibf_membership(trx_hibf_t * h, const uint64_t * kmers, uint64_t n, uint
     {
         uint64_t const m = n - done < piece ? n - done : piece;
         uint64_t st[2] = {0, 0};
+        if (staged)
+            TRX_CUDA(cudaStreamWaitEvent(c->stream, c->in_events[k], 0));
         TRX_TRY(trx_hibf_membership_dev(h, d_kmers + done, m, d_out + done * h->out_words, st));
         visited += st[0];
         if (k >= c->copy_events.size())
