@@ -15,6 +15,11 @@
 // restates the container's slot placement, every rank is processed in exactly that order, and
 // tests/test_collector_vs_ref.py fuzzes the resulting candidate sets against the compiled reference's process_query.
 #include <algorithm>
+#include <memory>
+#include <cstdio>
+#include <chrono>
+#include <thread>
+#include <atomic>
 #include <cstdlib>
 #include <string>
 #include <unordered_map>
@@ -188,23 +193,25 @@ struct budget_exceeded
 {};
 struct recording_paths
 {
-    static constexpr size_t kMaxProbes = 1024, kMaxSlots = 1u << 15;
+    size_t max_probes{1024}, max_slots{1u << 15}; // one query: beyond this the rank-by-rank device walk is no slower
+    recording_paths() = default;
+    recording_paths(size_t probes, size_t slots) : max_probes(probes), max_slots(slots) {}
     std::vector<uint64_t> kmers, codes; // distinct, in first-use order
     std::unordered_map<uint64_t, uint32_t> kmer_row, code_row;
     uint32_t slots{0};
     uint32_t fresh()
     {
-        if (slots >= kMaxSlots)
+        if (slots >= max_slots)
             throw budget_exceeded{};
         return slots++;
     }
     void fill(uint32_t, uint64_t) {}
-    static void note(std::vector<uint64_t> const & in, std::vector<uint64_t> & list, std::unordered_map<uint64_t, uint32_t> & row)
+    void note(std::vector<uint64_t> const & in, std::vector<uint64_t> & list, std::unordered_map<uint64_t, uint32_t> & row) const
     {
         for (uint64_t v : in)
             if (row.emplace(v, static_cast<uint32_t>(list.size())).second)
             {
-                if (list.size() >= kMaxProbes)
+                if (list.size() >= max_probes)
                     throw budget_exceeded{};
                 list.push_back(v);
             }
@@ -230,11 +237,11 @@ struct host_paths
     uint64_t W;
     row_map const & kmer_row; // k-mer → row of kmer_rows (W words each)
     row_map const & code_row;
-    std::vector<uint64_t> const & kmer_rows;
-    std::vector<uint64_t> const & code_rows;
+    uint64_t const * kmer_rows;
+    uint64_t const * code_rows;
     std::vector<uint64_t> words;
     uint32_t slots{0};
-    host_paths(uint64_t w, row_map const & km, row_map const & cm, std::vector<uint64_t> const & kr, std::vector<uint64_t> const & cr)
+    host_paths(uint64_t w, row_map const & km, row_map const & cm, uint64_t const * kr, uint64_t const * cr)
         : W(w), kmer_row(km), code_row(cm), kmer_rows(kr), code_rows(cr)
     {
         words.reserve(64 * W);
@@ -250,11 +257,11 @@ struct host_paths
             words[slot * W + w] = bins >= 64 * (w + 1) ? ~0ull : (bins > 64 * w ? (1ull << (bins - 64 * w)) - 1 : 0);
     }
     void and_rows(std::vector<uint64_t> const & in, std::vector<uint32_t> const & sl, std::vector<uint8_t> & res,
-                  std::unordered_map<uint64_t, uint32_t> const & row_of, std::vector<uint64_t> const & rows)
+                  std::unordered_map<uint64_t, uint32_t> const & row_of, uint64_t const * rows)
     {
         for (size_t i = 0; i < in.size(); ++i)
         {
-            uint64_t const * row = rows.data() + static_cast<size_t>(row_of.at(in[i])) * W;
+            uint64_t const * row = rows + static_cast<size_t>(row_of.at(in[i])) * W;
             uint64_t * path = words.data() + static_cast<size_t>(sl[i]) * W;
             uint64_t any = 0;
             for (uint64_t w = 0; w < W; ++w)
@@ -526,7 +533,7 @@ bitvector collect(kgraph const & g, DeviceIndex & index, collect_stats * stats, 
             }
             if (!rec.codes.empty())
                 check(trx_bulk_contains(index.dgram()->flat(), rec.codes.data(), rec.codes.size(), code_rows.data()));
-            host_paths hp(W, rec.kmer_row, rec.code_row, kmer_rows, code_rows);
+            host_paths hp(W, rec.kmer_row, rec.code_row, kmer_rows.data(), code_rows.data());
             uint32_t const match_slot = walk(g, index, stats, hp, bins);
             bitvector out(index.bin_words(), 0);
             std::copy(hp.words.begin() + static_cast<size_t>(match_slot) * W, hp.words.begin() + static_cast<size_t>(match_slot + 1) * W,
@@ -558,21 +565,13 @@ kgraph graph_of(std::string const & regex, DeviceIndex & index, bool augment);
 // Patterns whose graph is over the dry run's budget, and column shards, take process_query one at a time.
 std::vector<batch_answer> process_query_batch(std::vector<std::string> const & regexes, DeviceIndex & index, bool augment)
 {
-    constexpr uint64_t kBatchRowBytes = 128ull << 20;
+    constexpr size_t kChunk = 256; // patterns per membership batch: at most 256 x 1024 k-mers' rows on the host at a time
     std::vector<batch_answer> out(regexes.size());
     bool const sharded = !index.is_hibf() && index.shard_count() > 1;
     char const * const spec_env = getenv("TRX_COLLECT_SPECULATIVE");
     bool const one_by_one = sharded || (spec_env && std::string(spec_env) == "off");
     uint64_t const W = index.path_words();
     uint64_t const bins = index.bin_count();
-    struct waiting
-    {
-        size_t pattern;
-        kgraph g;
-    };
-    std::vector<waiting> group;
-    host_paths::row_map kmer_row, code_row;
-    std::vector<uint64_t> kmers, codes;
     auto answer_alone = [&](size_t i) {
         try
         {
@@ -584,76 +583,145 @@ std::vector<batch_answer> process_query_batch(std::vector<std::string> const & r
             out[i].error = e.what();
         }
     };
-    auto flush = [&] {
-        if (group.empty())
-            return;
-        std::vector<uint64_t> kmer_rows(kmers.size() * W), code_rows(codes.size() * W);
-        if (!kmers.empty())
-        {
-            if (index.is_hibf())
-                check(trx_hibf_membership(index.hibf(), kmers.data(), kmers.size(), kmer_rows.data(), nullptr));
-            else
-                check(trx_bulk_contains(index.flat(), kmers.data(), kmers.size(), kmer_rows.data()));
-        }
-        if (!codes.empty())
-            check(trx_bulk_contains(index.dgram()->flat(), codes.data(), codes.size(), code_rows.data()));
-        for (waiting const & w : group)
-        {
-            try
-            {
-                host_paths hp(W, kmer_row, code_row, kmer_rows, code_rows);
-                uint32_t const match_slot = walk(w.g, index, &out[w.pattern].stats, hp, bins);
-                out[w.pattern].bins.assign(hp.words.begin() + static_cast<size_t>(match_slot) * W,
-                                           hp.words.begin() + static_cast<size_t>(match_slot + 1) * W);
-                out[w.pattern].ok = true;
-            }
-            catch (std::exception const & e)
-            {
-                out[w.pattern].error = e.what();
-            }
-        }
-        group.clear();
-        kmer_row.clear();
-        code_row.clear();
-        kmers.clear();
-        codes.clear();
-    };
-    for (size_t i = 0; i < regexes.size(); ++i)
+    if (one_by_one)
     {
-        if (one_by_one)
-        {
+        for (size_t i = 0; i < regexes.size(); ++i)
             answer_alone(i);
-            continue;
-        }
-        try
+        return out;
+    }
+    // host threads: k-graphs, dry runs and walks of different patterns have nothing in common but read-only tables
+    unsigned const workers = std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
+    auto parallel = [&](size_t n, auto && body) {
+        std::atomic<size_t> next{0};
+        auto work = [&] {
+            for (size_t i = next++; i < n; i = next++)
+                body(i);
+        };
+        unsigned const w = static_cast<unsigned>(std::min<size_t>(workers, n));
+        if (w <= 1)
         {
-            kgraph g = graph_of(regexes[i], index, augment);
-            recording_paths rec;
+            work();
+            return;
+        }
+        std::vector<std::thread> pool;
+        for (unsigned t = 0; t < w; ++t)
+            pool.emplace_back(work);
+        for (std::thread & t : pool)
+            t.join();
+    };
+    enum class fate : uint8_t { walk, alone, failed };
+    bool const trace = getenv("TRX_COLLECT_TRACE") != nullptr; // where a batch spends its time, on stderr
+    auto const now = [] { return std::chrono::steady_clock::now(); };
+    auto const ms = [](auto a, auto b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
+    double ms_dry = 0, ms_merge = 0, ms_device = 0, ms_walk = 0, ms_alone = 0;
+    std::atomic<uint64_t> us_graph{0}, us_dry{0};
+    for (size_t begin = 0; begin < regexes.size(); begin += kChunk)
+    {
+        auto const t0 = now();
+        size_t const n = std::min(kChunk, regexes.size() - begin);
+        std::vector<kgraph> graphs(n);
+        // the same budget as a single query: the dry run of a wide graph visits far more than its pruned walk does (measured
+        // with 32 768 k-mers per pattern: 181 ms per 1000 patterns against 160 ms)
+        std::vector<recording_paths> recs(n);
+        std::vector<fate> what(n, fate::walk);
+        parallel(n, [&](size_t j) {
             try
             {
-                walk(g, index, nullptr, rec, bins);
+                auto const g0 = now();
+                graphs[j] = graph_of(regexes[begin + j], index, augment);
+                auto const g1 = now();
+                walk(graphs[j], index, nullptr, recs[j], bins);
+                if (trace)
+                {
+                    us_graph += static_cast<uint64_t>(ms(g0, g1) * 1000);
+                    us_dry += static_cast<uint64_t>(ms(g1, now()) * 1000);
+                }
             }
             catch (budget_exceeded const &)
             {
-                answer_alone(i);
-                continue;
+                what[j] = fate::alone;
             }
-            for (uint64_t v : rec.kmers)
-                if (kmer_row.emplace(v, static_cast<uint32_t>(kmers.size())).second)
-                    kmers.push_back(v);
-            for (uint64_t v : rec.codes)
-                if (code_row.emplace(v, static_cast<uint32_t>(codes.size())).second)
-                    codes.push_back(v);
-            group.push_back(waiting{i, std::move(g)});
-            if ((kmers.size() + codes.size()) * W * 8 >= kBatchRowBytes)
-                flush();
-        }
-        catch (std::exception const & e)
+            catch (std::exception const & e)
+            {
+                what[j] = fate::failed;
+                out[begin + j].error = e.what();
+            }
+        });
+        // the union of the chunk's k-mers, in pattern order (the result does not depend on the order; the batch does not
+        // depend on the thread count)
+        auto const t1 = now();
+        // groups of patterns whose k-mers' rows fit kGroupRowBytes: one membership batch and one round of walks per group
+        constexpr uint64_t kGroupRowBytes = 256ull << 20;
+        size_t group_begin = 0;
+        while (group_begin < n)
         {
-            out[i].error = e.what();
+            auto const u0 = now();
+            // the union of the group's k-mers, in pattern order (the result does not depend on the order; the batch does
+            // not depend on the thread count)
+            host_paths::row_map kmer_row, code_row;
+            std::vector<uint64_t> kmers, codes;
+            size_t group_end = group_begin;
+            for (; group_end < n; ++group_end)
+            {
+                size_t const j = group_end;
+                if (what[j] != fate::walk)
+                    continue;
+                if (group_end > group_begin && (kmers.size() + codes.size() + recs[j].kmers.size() + recs[j].codes.size()) * W * 8 > kGroupRowBytes)
+                    break;
+                for (uint64_t v : recs[j].kmers)
+                    if (kmer_row.emplace(v, static_cast<uint32_t>(kmers.size())).second)
+                        kmers.push_back(v);
+                for (uint64_t v : recs[j].codes)
+                    if (code_row.emplace(v, static_cast<uint32_t>(codes.size())).second)
+                        codes.push_back(v);
+            }
+            auto const u1 = now();
+            std::unique_ptr<uint64_t[]> kmer_rows(new uint64_t[kmers.size() * W + 1]), code_rows(new uint64_t[codes.size() * W + 1]);
+            if (!kmers.empty())
+            {
+                if (index.is_hibf())
+                    check(trx_hibf_membership(index.hibf(), kmers.data(), kmers.size(), kmer_rows.get(), nullptr));
+                else
+                    check(trx_bulk_contains(index.flat(), kmers.data(), kmers.size(), kmer_rows.get()));
+            }
+            if (!codes.empty())
+                check(trx_bulk_contains(index.dgram()->flat(), codes.data(), codes.size(), code_rows.get()));
+            auto const u2 = now();
+            size_t const gb = group_begin;
+            parallel(group_end - group_begin, [&](size_t jj) {
+                size_t const j = gb + jj;
+                if (what[j] != fate::walk)
+                    return;
+                batch_answer & a = out[begin + j];
+                try
+                {
+                    host_paths hp(W, kmer_row, code_row, kmer_rows.get(), code_rows.get());
+                    uint32_t const match_slot = walk(graphs[j], index, &a.stats, hp, bins);
+                    a.bins.assign(hp.words.begin() + static_cast<size_t>(match_slot) * W,
+                                  hp.words.begin() + static_cast<size_t>(match_slot + 1) * W);
+                    a.ok = true;
+                }
+                catch (std::exception const & e)
+                {
+                    a.error = e.what();
+                }
+            });
+            ms_merge += ms(u0, u1);
+            ms_device += ms(u1, u2);
+            ms_walk += ms(u2, now());
+            group_begin = group_end;
         }
+        auto const t4 = now();
+        for (size_t j = 0; j < n; ++j) // graphs over the dry run's budget: the device-resident walk, one at a time
+            if (what[j] == fate::alone)
+                answer_alone(begin + j);
+        ms_dry += ms(t0, t1);
+        ms_alone += ms(t4, now());
     }
-    flush();
+    if (trace)
+        fprintf(stderr, "process_query_batch: %zu patterns, %u host threads: graphs + dry runs %.1f ms (thread time: graphs %.1f, dry runs "
+                        "%.1f), union of k-mers %.1f, membership %.1f, walks %.1f, one at a time %.1f\n", regexes.size(), workers, ms_dry,
+                us_graph.load() / 1000.0, us_dry.load() / 1000.0, ms_merge, ms_device, ms_walk, ms_alone);
     return out;
 }
 
