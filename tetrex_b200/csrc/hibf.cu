@@ -1121,7 +1121,10 @@ uint64_t trx_hibf_user_bin_words(const trx_hibf_t * h)
 }
 
 // one chunk of k-mers through all levels; returns TRX_ECAPACITY on frontier overflow
-static int run_chunk(trx_hibf * h, uint64_t const * d_kmers, uint64_t n, uint64_t * d_out, uint64_t * visited)
+// deferred_ctr (pinned host memory, kMaxLevels + 3 counters): for a small batch the level counters are copied there and
+// NOT waited for — the caller checks them after its own synchronisation ([0] != 0: frontier overflow)
+static int run_chunk(trx_hibf * h, uint64_t const * d_kmers, uint64_t n, uint64_t * d_out, uint64_t * visited,
+                     unsigned long long * deferred_ctr = nullptr)
 {
     trx_ctx * c = h->ctx;
     bool const small = n <= h->small_batch;
@@ -1196,6 +1199,11 @@ static int run_chunk(trx_hibf * h, uint64_t const * d_kmers, uint64_t n, uint64_
         cur ^= 1;
     }
     TRX_CUDA(cudaGetLastError());
+    if (deferred_ctr && small && !sort_frontier)
+    {
+        TRX_CUDA(cudaMemcpyAsync(deferred_ctr, ctr, (kMaxLevels + 3) * 8, cudaMemcpyDeviceToHost, c->stream));
+        return TRX_OK;
+    }
     unsigned long long host_ctr[kMaxLevels + 3];
     TRX_CUDA(cudaMemcpyAsync(host_ctr, ctr, sizeof host_ctr, cudaMemcpyDeviceToHost, c->stream));
     TRX_CUDA(cudaStreamSynchronize(c->stream));
@@ -1358,6 +1366,36 @@ int trx_hibf_membership(trx_hibf_t * h, const uint64_t * kmers, uint64_t n, uint
     TRX_TRY(h->d_out.reserve(n * h->out_words * 8));
     auto * d_kmers = static_cast<uint64_t *>(h->d_kmers.ptr);
     auto * d_out = static_cast<uint64_t *>(h->d_out.ptr);
+    if (n <= 64 && n <= h->small_batch && n * h->out_words * 8 <= (64u << 10))
+    {
+        // a query's handful of k-mers (the collector's one-batch walk): everything through ONE pinned block and one
+        // synchronisation — k-mers in, rows and level counters out — instead of three staged copies and two waits
+        size_t const row_bytes = n * h->out_words * 8;
+        size_t const off_rows = (n * 8 + 255) & ~size_t{255}, off_ctr = (off_rows + row_bytes + 255) & ~size_t{255};
+        c->h_pin[0].pinned_host = true;
+        TRX_TRY(c->h_pin[0].reserve(off_ctr + (kMaxLevels + 3) * 8));
+        auto * pin = static_cast<uint8_t *>(c->h_pin[0].ptr);
+        auto * pin_ctr = reinterpret_cast<unsigned long long *>(pin + off_ctr);
+        memcpy(pin, kmers, n * 8);
+        TRX_CUDA(cudaMemcpyAsync(d_kmers, pin, n * 8, cudaMemcpyHostToDevice, c->stream));
+        uint64_t visited_small = 0;
+        TRX_TRY(run_chunk(h, d_kmers, n, d_out, &visited_small, pin_ctr));
+        TRX_CUDA(cudaMemcpyAsync(pin + off_rows, d_out, row_bytes, cudaMemcpyDeviceToHost, c->stream));
+        TRX_CUDA(cudaStreamSynchronize(c->stream));
+        if (pin_ctr[0] == 0) // no frontier overflow (else: the general path below shrinks its passes)
+        {
+            memcpy(out_words, pin + off_rows, row_bytes);
+            if (stats)
+            {
+                uint64_t v = n;
+                for (int level = 1; level < h->depth; ++level)
+                    v += pin_ctr[1 + level];
+                stats[0] = v;
+                stats[1] = static_cast<uint64_t>(h->depth);
+            }
+            return TRX_OK;
+        }
+    }
     // The result (out_words x 8 B per k-mer, 128 B at C2) dwarfs the input: it leaves in pieces on a second stream
     // while the next piece is being computed, so the call costs about max(compute, PCIe) instead of their sum; the k-mers
     // arrive piece by piece on a third.
