@@ -326,10 +326,15 @@ int trx_regex_scan_end(trx_text_t *text, int ticket, trx_hit *hits, uint64_t *n_
  * src/query.cpp:318-339) without re-reading the text per pattern.  Pattern i is scanned over the bins set in
  * candidate_bin_words[i * cand_stride_words ...] (cand_stride_words = 0: all patterns share one bitmap); forward strand,
  * no byte map.  hits come back grouped by pattern, each group in trx_regex_scan's order; hit_pattern[j] = pattern of
- * hits[j]; per_pattern_hits (nullable) = group sizes.  More than cap hits: TRX_ECAPACITY, *n_hits = a lower bound.
- * Every tile of the union of candidate bins is read ONCE per launch of up to 128 patterns: occurrence bitmasks of the
- * batch's alphabet are built per tile and every pattern's necessary-factor plan is evaluated on them; patterns without
- * such a plan, or with more than 8192 candidate records, go through trx_regex_scan internally (same results).
+ * hits[j]; per_pattern_hits (nullable) = group sizes.  More than cap hits: TRX_ECAPACITY, *n_hits = how many there are
+ * (nothing is delivered).
+ * Every tile of the union of candidate bins is read ONCE per pass of up to 128 patterns.  First stage of a pass: the
+ * patterns' class windows, bit-parallel over the patterns (trx_regex_window_plan shows a pattern's window); patterns
+ * without one share a pass that evaluates their necessary-factor plans on occurrence bitmasks of the batch's alphabet;
+ * patterns with neither, or with more than 32 768 candidate records, are scanned one at a time inside the same call
+ * (same results).  The hits of all patterns stay in one device list until the call sorts them there — (pattern, record,
+ * start) — and copies them out once; passes are enqueued back to back, nothing is read back in between.
+ * TRX_MULTI_WINDOW=off / TRX_REGEX_MULTI=off switch the first stage / the shared passes off (A/B, tests).
  * stats (nullable, 4 entries): residues read by the shared passes, patterns answered by them, patterns answered one at a
  * time, shared passes launched. */
 int trx_regex_scan_multi(trx_text_t *text, trx_regex_t *const *regexes, uint32_t n_patterns,
