@@ -18,7 +18,7 @@ subprocess.run([os.path.join(ROOT, "tetrex_b200", "bin", "tetrex"), "index", "-i
                 os.path.join(tmp, "bins.lst")], check=True, capture_output=True)
 ctx = t.Context(0)
 ix = sharded.ShardedIndex(ctx, os.path.join(tmp, "flat.ibf"), 0, 1)
-for augment in (False, True):
+for augment in ((True,) if os.environ.get("AUGMENT_ONLY") else (False, True)):
     ix.set_augment(augment)
     ix.local_candidates_batch(pats[:32])
     t0 = time.perf_counter(); words, status, stats = ix.local_candidates_batch(pats); dt_b = time.perf_counter() - t0

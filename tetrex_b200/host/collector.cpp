@@ -620,9 +620,15 @@ std::vector<batch_answer> process_query_batch(std::vector<std::string> const & r
         auto const t0 = now();
         size_t const n = std::min(kChunk, regexes.size() - begin);
         std::vector<kgraph> graphs(n);
-        // the same budget as a single query: the dry run of a wide graph visits far more than its pruned walk does (measured
-        // with 32 768 k-mers per pattern: 181 ms per 1000 patterns against 160 ms)
-        std::vector<recording_paths> recs(n);
+        // four times a single query's budget — a batch has the host threads to walk wider graphs, but the dry run of a wide
+        // graph visits far more than its pruned walk does.  Measured on 1000 C3 patterns with -a: 1024 k-mers per pattern
+        // 160 ms, 2048 176, 4096 144, 8192 145, 32 768 181
+        static size_t const batch_probes = [] {
+            char const * e = getenv("TRX_COLLECT_BATCH_PROBES"); // A/B of the dry run's budget inside a batch
+            size_t const v = e ? strtoull(e, nullptr, 10) : 0;
+            return v ? v : size_t{4096};
+        }();
+        std::vector<recording_paths> recs(n, recording_paths(batch_probes, 1u << 17));
         std::vector<fate> what(n, fate::walk);
         parallel(n, [&](size_t j) {
             try
