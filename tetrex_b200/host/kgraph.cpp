@@ -51,19 +51,27 @@ void kgraph::compute_ranks()
     // a node gets number N-1, N-2, … in the order it is LEFT.  The collector's rank equals that number (the write
     // map skips the node numbered 0 — the start node — which therefore keeps rank 0).
     int const n = static_cast<int>(symbol.size());
-    std::vector<std::vector<int>> out(n); // arc ids per source, creation order
-    for (int a = 0; a < static_cast<int>(arcs.size()); ++a)
-        out[arcs[a].first].push_back(a);
+    int const n_arcs = static_cast<int>(arcs.size());
+    // arc ids per source in creation order, as compressed rows: out[off[u] .. off[u + 1])
+    std::vector<int> off(n + 1, 0), out(n_arcs), at;
+    for (int a = 0; a < n_arcs; ++a)
+        ++off[arcs[a].first + 1];
+    for (int i = 0; i < n; ++i)
+        off[i + 1] += off[i];
+    at.assign(off.begin(), off.end() - 1);
+    for (int a = 0; a < n_arcs; ++a)
+        out[at[arcs[a].first]++] = a;
     rank.assign(n, 0);
     std::vector<char> reached(n, 0);
+    std::vector<std::pair<int, int>> stack; // (node, next out-arc position counted from the newest)
     int num = n;
     for (int root = n - 1; root >= 0; --root)
     {
         if (reached[root])
             continue;
         reached[root] = 1;
-        std::vector<std::pair<int, int>> stack; // (node, next out-arc position counted from the newest)
-        stack.emplace_back(root, static_cast<int>(out[root].size()) - 1);
+        stack.clear();
+        stack.emplace_back(root, off[root + 1] - off[root] - 1);
         while (!stack.empty())
         {
             auto & [node, pos] = stack.back();
@@ -73,12 +81,12 @@ void kgraph::compute_ranks()
                 stack.pop_back();
                 continue;
             }
-            int const target = arcs[out[node][pos]].second;
+            int const target = arcs[out[off[node] + pos]].second;
             --pos;
             if (!reached[target])
             {
                 reached[target] = 1;
-                stack.emplace_back(target, static_cast<int>(out[target].size()) - 1);
+                stack.emplace_back(target, off[target + 1] - off[target] - 1);
             }
         }
     }
@@ -177,8 +185,9 @@ struct subgraph
     void concat_info(subgraph const & a, subgraph const & b)
     {
         paths = a.paths * b.paths;
-        for (uint64_t l : a.length_list())
-            for (uint64_t j : b.length_list())
+        std::vector<uint64_t> const x = a.length_list(), y = b.length_list();
+        for (uint64_t l : x)
+            for (uint64_t j : y)
                 lengths.insert_key(l + j);
         split_run_count = std::max(a.split_run_count, b.split_run_count);
     }
@@ -216,8 +225,9 @@ struct subgraph
     }
     void kleene_info(subgraph const & a, uint8_t repeats)
     {
+        std::vector<uint64_t> const x = a.length_list();
         for (size_t i = 0; i < repeats; ++i)
-            for (uint64_t l : a.length_list())
+            for (uint64_t l : x)
                 lengths.insert_key(i * l);
         split_run_count = a.split_run_count;
         paths = a.paths * repeats;
@@ -277,7 +287,7 @@ struct builder
     {
         if (stack.empty())
             throw error("malformed regular expression (operator without operand)");
-        subgraph s = stack.top();
+        subgraph s = std::move(stack.top());
         stack.pop();
         return s;
     }
@@ -303,13 +313,17 @@ struct builder
         }
         int const n = static_cast<int>(g.size());
         int const n_arcs = static_cast<int>(g.arcs.size());
-        std::vector<std::vector<int>> fwd(n), bwd(n);
-        for (auto const & [u, v] : g.arcs)
-        {
-            fwd[u].push_back(v);
-            bwd[v].push_back(u);
-        }
-        auto reach = [&](int from, std::vector<std::vector<int>> const & adj) {
+        // adjacency in compressed rows (three flat arrays per direction instead of a vector per node: this runs once per
+        // repetition of every {m,n} and the graphs have a hundred nodes)
+        auto reach = [&](int from, bool forward) {
+            std::vector<int> off(n + 1, 0), adj(n_arcs), at;
+            for (auto const & [u, v] : g.arcs)
+                ++off[(forward ? u : v) + 1];
+            for (int i = 0; i < n; ++i)
+                off[i + 1] += off[i];
+            at.assign(off.begin(), off.end() - 1);
+            for (auto const & [u, v] : g.arcs)
+                adj[at[forward ? u : v]++] = forward ? v : u;
             std::vector<char> seen(n, 0);
             std::vector<int> todo{from};
             seen[from] = 1;
@@ -317,16 +331,16 @@ struct builder
             {
                 int u = todo.back();
                 todo.pop_back();
-                for (int v : adj[u])
-                    if (!seen[v])
+                for (int e = off[u]; e < off[u + 1]; ++e)
+                    if (!seen[adj[e]])
                     {
-                        seen[v] = 1;
-                        todo.push_back(v);
+                        seen[adj[e]] = 1;
+                        todo.push_back(adj[e]);
                     }
             }
             return seen;
         };
-        std::vector<char> from_s = reach(sg.start, fwd), to_t = reach(sg.end, bwd);
+        std::vector<char> from_s = reach(sg.start, true), to_t = reach(sg.end, false);
         std::vector<int> twin(n, -1);
         for (int u = n - 1; u >= 0; --u)
             if (from_s[u] && to_t[u])
@@ -363,7 +377,7 @@ struct builder
         subgraph joined{a.start, b.end};
         joined.concat_info(a, b);
         detect_bad_graphs(a, b, joined);
-        stack.push(joined);
+        stack.push(std::move(joined));
     }
 
     void alternation()
@@ -392,7 +406,7 @@ struct builder
         g.add_arc(b.end, ghost);
         subgraph u{split, ghost};
         u.union_info(a, b);
-        stack.push(u);
+        stack.push(std::move(u));
     }
 
     void optional()
@@ -406,7 +420,7 @@ struct builder
         g.add_arc(a.end, ghost);
         subgraph o{split, ghost};
         o.option_info(a);
-        stack.push(o);
+        stack.push(std::move(o));
     }
 
     // '*' unrolled: ε, X, …, X^(k-1)   (src/construct_nfa.cpp:146-192)
@@ -435,7 +449,7 @@ struct builder
         }
         subgraph ks{split, ghost};
         ks.kleene_info(a, static_cast<uint8_t>(k));
-        stack.push(ks);
+        stack.push(std::move(ks));
     }
 
     // '+' unrolled: X, …, X^(k-1)   (src/construct_nfa.cpp:195-223)
