@@ -58,3 +58,41 @@ def test_patterns_without_a_window():
         rx = t.Regex(p, True)
         assert (rx.window_plan(freq) is not None) == ok, p
         rx.close()
+
+
+def test_plans_of_wide_patterns_are_necessary_for_every_re2_match(golden_dir):
+    """Patterns of 130..250 symbol positions (tests/golden/regex_wide.json, RE2's own match lists): whatever prefilter the
+    single-pattern path picks (trx_regex_filter_plan) and whatever class window the multi-pattern path picks
+    (trx_regex_window_plan) must allow every match RE2 reports — offsets beyond 127 bytes must not wrap anywhere."""
+    import json
+    from test_filter_plan_cpu import AA_FREQ, flagged_starts, frequencies
+    cases = json.load(open(os.path.join(golden_dir, "regex_wide.json")))
+    checked = plans = windows = 0
+    for c in cases:
+        try:
+            rx = t.Regex(c["pattern"], c["posix"])
+        except t.TetrexError:
+            continue
+        text = np.frombuffer(c["text"].encode(), dtype=np.uint8)
+        if len(text) == 0:
+            rx.close()
+            continue
+        # planned for a text with protein / uniform DNA frequencies (a necessary condition is one on ANY text; the golden
+        # texts use small alphabets, on whose own frequencies hardly any prefilter is selective enough to be chosen)
+        freq = frequencies(AA_FREQ) if c["posix"] else frequencies(dict.fromkeys("ACGT", 1.0))
+        plan = rx.filter_plan(freq)
+        if plan["kind"] != "none":
+            plans += 1
+            ok = flagged_starts(plan, text)
+            for a, _ in c["matches"]:
+                assert ok[a], (c["pattern"], plan, a)
+                checked += 1
+        if c["posix"]:
+            w = rx.window_plan(freq)
+            if w is not None:
+                windows += 1
+                for a, _ in c["matches"]:
+                    assert holds(c["text"].encode(), w, a), (c["pattern"], w, a)
+                    checked += 1
+        rx.close()
+    assert plans >= 8 and windows >= 3 and checked >= 25, (plans, windows, checked)
