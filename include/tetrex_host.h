@@ -68,6 +68,15 @@ int trxh_process_query(void *handle, const char *regex, trxh_alive_fn alive, voi
 int trxh_process_query_batch(void *handle, const char *const *regexes, uint64_t n, uint64_t *out_words, uint8_t *status,
                              uint64_t *stats);
 
+/* process_query (include/query.h:226-247) over membership rows the CALLER supplies — another filter implementation, a cache,
+ * a remote shard.  The k-graph is walked once without pruning to list the k-mers it can ask for, rows() is called once
+ * with all of them (out_words[i * ceil(bins/64) + w] = word w of IBFIndex::query(kmers[i])), then the walk proper runs on
+ * those rows with the reference's rules.  No index file, no device.  molecule: 0 DNA, 1 peptide; reduction 0 / 1 murphy /
+ * 2 li; out_words: ceil(bins/64) words; stats (nullable): probes, ranks, items of the pruned walk. */
+typedef void (*trxh_rows_fn)(const uint64_t *kmers, uint64_t n, uint64_t *out_words, void *user);
+int trxh_process_query_with_rows(int molecule, uint32_t k, int reduction, uint64_t bins, const char *regex, int augment,
+                                 trxh_rows_fn rows, void *user, uint64_t *out_words, uint64_t *stats);
+
 /* iter_disk_search over the shard's own bins: the reference's output lines, in its -t 1 order, as one malloc'ed buffer
  * (trxh_free).  cand_words: bin_words words (bits of other shards' bins are ignored). */
 int trxh_verify(void *handle, const uint64_t *cand_words, const char *regex, char **out_text, uint64_t *out_len, uint64_t *n_lines);

@@ -145,6 +145,78 @@ def golden_regex_wide():
     print(len(cases), "cases,", sum(len(c["matches"]) for c in cases), "matches;", sum(1 for c in cases if c["matches"]), "non-empty")
 
 
+def collector_rows_library(seed=23, bins=96, k=4):
+    """A small peptide collection for the CPU collector test: records that share planted motifs, so that walks prune, split,
+    absorb and match.  Returns (per-bin list of records, alphabet)."""
+    rng = random.Random(seed)
+    alpha = b"ACDEFGHIKLMNPQRSTVWY"
+    motifs = [b"LMAEGLYN", b"LMAQGLYN", b"CAHCWKKH", b"GATTWCAW", b"WWKDEFAC", b"MKVLAAGIV"]
+    lib = []
+    for b_ in range(bins):
+        recs = []
+        for _ in range(rng.randint(1, 3)):
+            s_ = bytearray(rng.choice(alpha) for _ in range(rng.randint(20, 90)))
+            for m in rng.sample(motifs, rng.randint(0, 2)):
+                at = rng.randint(0, len(s_) - len(m))
+                s_[at:at + len(m)] = m
+            recs.append(bytes(s_))
+        lib.append(recs)
+    return lib
+
+
+COLLECTOR_ROWS_REGEXES = [
+    "LMA(E|Q)GLYN", "L.AQGLYN", "CAHCWKKH", "LMA[EQ]GL", "(XAC|C)AHCW", "W{2}KDEF", "G.TTWC?AW", "MKV(L|I)A+G", "A{2,3}GIV",
+    "(LMA|CAH)(EGL|CWK)", "WKDE.{1,2}C", "M.V.A", "K+D", "LMAEGLYN|CAHCWKKH", "[LM][MA]AEG", "GAT{2}W", "(W|K)(K|D)(D|E)F",
+    "CA?HC", "LM.{0,2}GLY", "QGLYN", "ZZZZZ", "AAAA", "LMA", "L(M|A)(A|E)(E|G)(G|L)(L|Y)", "(LM|L)(A|AE)GLYN",
+]
+
+
+def golden_collector_rows():
+    """The reference's OTFCollector over a flat seqan IBF of collector_rows_library (oracle/_ref: RefIBF.collect) for k = 4
+    and 6, plain and augmented: the CPU test replays the same queries through trxh_process_query_with_rows with membership
+    rows from the C oracle's IBF."""
+    cases = []
+    for k in (4, 6):
+        lib = collector_rows_library(k=k)
+        bins = len(lib)
+        per_bin = [np.concatenate([ob.ref_decompose(1, k, 0, r) for r in recs]) for recs in lib]
+        bin_size = ob.compute_bitcount(max(len(v) for v in per_bin), 0.05)
+        ibf = ob.RefIBF(bins, bin_size, 3)
+        for b_, v in enumerate(per_bin):
+            ibf.emplace(v, np.full(len(v), b_, dtype=np.uint32))
+        rng = random.Random(k)
+        regexes = list(COLLECTOR_ROWS_REGEXES)
+        flat = [r for recs in lib for r in recs]
+        for _ in range(60):  # grown around true substrings, like the GPU fuzz
+            src = rng.choice(flat)
+            at = rng.randint(0, len(src) - 9)
+            core = src[at:at + rng.randint(k + 1, 9)].decode()
+            i = rng.randrange(len(core))
+            kind = rng.randrange(6)
+            if kind == 0:
+                rx = core[:i] + "(" + core[i] + "|" + rng.choice("ACDEFGHIKLMNPQRSTVWY") + ")" + core[i + 1:]
+            elif kind == 1:
+                rx = core[:i] + "." + core[i + 1:]
+            elif kind == 2:
+                rx = core[:i] + core[i] + "?" + core[i:]
+            elif kind == 3:
+                rx = core[:i] + "[" + core[i] + rng.choice("ACDEFGHIKLMNPQRSTVWY") + "]" + core[i + 1:]
+            elif kind == 4:
+                rx = core[:i] + core[i] + "{1,2}" + core[i + 1:]
+            else:
+                rx = "(X" + core[:2] + "|" + core[1] + ")" + core[2:]
+            regexes.append(rx)
+        for rx in regexes:
+            for augment in (False, True):
+                got = ob.guarded(lambda: ibf.collect(1, k, 0, rx, augment).tolist())
+                if got == "ABORTED":
+                    continue
+                cases.append({"k": k, "regex": rx, "augment": augment, "words": [int(x) for x in got]})
+    json.dump({"seed": 23, "bins": 96, "hash_funs": 3, "fpr": 0.05, "cases": cases},
+              open(os.path.join(OUT, "collector_rows.json"), "w"))
+    print(len(cases), "cases,", sum(1 for c in cases if any(c["words"])), "with candidates")
+
+
 def golden_kgraph():
     """k-graphs of the reference (node symbols, two-slot arc map, ranks) for the host layer's construct_kgraph."""
     cases = []
@@ -789,7 +861,7 @@ def golden_rh_order():
     print("rh_order.json:", len(cases), "cases")
 
 
-STEPS = {"decompose": golden_decompose, "ibf": golden_ibf, "hibf": golden_hibf, "regex": golden_regex, "regex_wide": golden_regex_wide,
+STEPS = {"decompose": golden_decompose, "ibf": golden_ibf, "hibf": golden_hibf, "regex": golden_regex, "regex_wide": golden_regex_wide, "collector_rows": golden_collector_rows,
          "kgraph": golden_kgraph, "cli": golden_cli, "c1": golden_c1, "collector_fuzz": golden_collector_fuzz, "rh_order": golden_rh_order,
          "prosite_batch": golden_prosite_batch, "c2_twin_hibf": golden_c2_twin_hibf, "cli_ws": golden_cli_ws, "prosite_filter": golden_prosite_filter, "cli_conj": golden_cli_conj, "dgram": golden_dgram, "kgraph_aug": golden_kgraph_aug, "hibf_layout": golden_hibf_layout}
 

@@ -268,6 +268,34 @@ int trxh_process_query_batch(void * hv, const char * const * regexes, uint64_t n
     });
 }
 
+// process_query over membership rows the caller supplies (trxh::process_query_with_rows): no index file, no device.
+// molecule 0 = DNA, 1 = peptide; rows(kmers, n, out_words, user) fills n x ceil(bins / 64) words.
+int trxh_process_query_with_rows(int molecule, uint32_t k, int reduction, uint64_t bins, const char * regex, int augment,
+                                 trxh_rows_fn rows, void * user, uint64_t * out_words, uint64_t * stats)
+{
+    return guarded([&] {
+        if (!regex || !rows || !out_words)
+            throw trxh::error("trxh_process_query_with_rows: NULL argument");
+        trxh::DeviceIndex ix(nullptr);
+        ix.describe_only(molecule == 0 ? "na" : "aa", static_cast<uint8_t>(k), static_cast<uint8_t>(reduction), bins);
+        trxh::collect_stats st;
+        trxh::bitvector got = trxh::process_query_with_rows(
+            regex, ix, [rows, user](uint64_t const * kmers, size_t n, uint64_t * out) { rows(kmers, n, out, user); }, &st, augment != 0);
+        for (uint64_t w = 0; w < got.size(); ++w)
+        {
+            uint64_t const first = w * 64;
+            uint64_t const mask = bins >= first + 64 ? ~0ull : (bins > first ? (1ull << (bins - first)) - 1 : 0);
+            out_words[w] = got[w] & mask;
+        }
+        if (stats)
+        {
+            stats[0] = st.probes;
+            stats[1] = st.ranks;
+            stats[2] = st.items;
+        }
+    });
+}
+
 // iter_disk_search (include/query.h:97-188) over this shard's bins; the lines come back as one malloc'ed buffer
 // (free with trxh_free).
 int trxh_verify(void * hv, const uint64_t * cand_words, const char * regex, char ** out_text, uint64_t * out_len, uint64_t * n_lines)

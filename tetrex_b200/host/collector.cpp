@@ -750,6 +750,23 @@ kgraph graph_of(std::string const & regex, DeviceIndex & index, bool augment)
 }
 } // namespace
 
+bitvector process_query_with_rows(std::string const & regex, DeviceIndex & index, rows_fn const & rows, collect_stats * stats,
+                                  bool augment)
+{
+    if (index.dgram())
+        throw error("process_query_with_rows: DGram filters are not supported");
+    kgraph g = graph_of(regex, index, augment);
+    uint64_t const W = index.bin_words(), bins = index.bin_count();
+    recording_paths rec(size_t{1} << 24, size_t{1} << 24); // the caller asked for this route: no budget
+    walk(g, index, nullptr, rec, bins);
+    std::vector<uint64_t> kmer_rows(rec.kmers.size() * W + 1, 0), no_codes(1, 0);
+    if (!rec.kmers.empty())
+        rows(rec.kmers.data(), rec.kmers.size(), kmer_rows.data());
+    host_paths hp(W, rec.kmer_row, rec.code_row, kmer_rows.data(), no_codes.data());
+    uint32_t const match_slot = walk(g, index, stats, hp, bins);
+    return bitvector(hp.words.begin() + static_cast<size_t>(match_slot) * W, hp.words.begin() + static_cast<size_t>(match_slot + 1) * W);
+}
+
 bitvector process_query(std::string const & regex, DeviceIndex & index, collect_stats * stats, shard_hooks const * hooks,
                         bool augment)
 {

@@ -48,6 +48,18 @@ void DeviceIndex::init_maps()
     trx_peptide_maps(img_.reduction, aamap_, redmap_);
 }
 
+void DeviceIndex::describe_only(std::string const & molecule, uint8_t k, uint8_t reduction, uint64_t bins)
+{
+    if (molecule != "na" && molecule != "aa")
+        throw error("molecule must be \"na\" or \"aa\"");
+    img_ = index_image{};
+    img_.molecule = molecule;
+    img_.k = k;
+    img_.reduction = reduction;
+    img_.bin_count = bins;
+    init_maps();
+}
+
 uint64_t DeviceIndex::update_kmer(int symbol, uint64_t & kmer) const
 {
     unsigned const k = img_.k;

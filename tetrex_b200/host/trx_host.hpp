@@ -251,6 +251,9 @@ public:
     void build(index_arguments const & args);
     void store(std::string const & path) const; // store_ibf
     void load(std::string const & path);        // load_ibf + upload to the device
+    // No filter at all: only what the regex front end and the k-graph walk need to know about an index (molecule "na" /
+    // "aa", k, reduction, number of bins).  For collect_with_rows, whose caller brings the membership rows; needs no device.
+    void describe_only(std::string const & molecule, uint8_t k, uint8_t reduction, uint64_t bins);
 
     uint8_t k() const { return img_.k; }
     bool is_dna() const { return img_.molecule == "na"; }
@@ -364,6 +367,15 @@ struct batch_answer
     std::string error;
 };
 std::vector<batch_answer> process_query_batch(std::vector<std::string> const & regexes, DeviceIndex & index, bool augment = false);
+
+// process_query over membership rows the CALLER supplies (another filter, a cache, a remote shard): the k-graph is walked
+// once without pruning to list the k-mers it can ask for, `rows(kmers, n, out)` fills n x bin_words() words
+// (out[i * bin_words + w] = IBFIndex::query(kmers[i]) word w), and the walk proper runs on them.  No device call is made
+// — which is also what lets the collector's rules be checked against the reference without a GPU (tests/test_host_cpu.py).
+// `index` only has to be described (DeviceIndex::describe_only); DGram filters are not supported here.
+using rows_fn = std::function<void(uint64_t const * kmers, size_t n, uint64_t * out_words)>;
+bitvector process_query_with_rows(std::string const & regex, DeviceIndex & index, rows_fn const & rows, collect_stats * stats = nullptr,
+                                  bool augment = false);
 
 // iter_disk_search (include/query.h:97-188): verifies the candidate bins on the device (K4) and writes the
 // reference's lines "bin_path\t>name\tmatch\tstart,end\n" (+ "…\tREVERSE STRAND HIT" for DNA) to `dest`
